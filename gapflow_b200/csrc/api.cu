@@ -1,0 +1,188 @@
+// extern "C" boundary of libgapflow_b200.so (see include/gapflow_b200.h).
+#include <cstring>
+#include <new>
+#include <string>
+#include "fv_host.h"
+
+namespace gpf {
+static thread_local std::string t_err;
+void set_error(const std::string& m) { t_err = m; }
+int cuda_fail(cudaError_t e, const char* what) {
+    t_err = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
+    return GPF_E_CUDA;
+}
+}  // namespace gpf
+
+using namespace gpf;
+
+struct gpf_fv {
+    FvSolver S;
+};
+
+#define GPF_TRY try {
+#define GPF_CATCH                                                            \
+    }                                                                        \
+    catch (const std::bad_alloc&) { set_error("out of host memory"); return GPF_E_NOMEM; } \
+    catch (const std::exception& e) { set_error(e.what()); return GPF_E_INVALID; }        \
+    catch (...) { set_error("unknown C++ exception"); return GPF_E_INVALID; }
+
+extern "C" {
+
+const char* gpf_last_error(void) { return t_err.c_str(); }
+int gpf_version(void) { return 100; }
+int64_t gpf_launch_count(void) { return (int64_t)g_launches.load(); }
+
+// masks[s][k][c]: s: 0 xE, 1 xW, 2 yS, 3 yN; k: 0 P, 1 D, 2 N.
+// Reference (problem.py:681-707, 736-754):
+//   ghost x0 (index 0):    gate all(xE_P); assigned through masks xE_{D,N}; values from
+//                           comps selected by xW_{D,N}, target xW_D_val, adjacent row 1
+//   ghost x1 (index -1):   gate all(xW_P); assigned through xW_*; values from xE_*, xE_D_val, row -2
+//   ghost y0 (index 0):    gate all(yS_P); assigned through yS_*; values from yN_*, yN_D_val, col 1
+//   ghost y1 (index -1):   gate all(yN_P); assigned through yN_*; values from yS_*, yS_D_val, col -2
+// NumPy assigns value array (k_val, 1, n) into (k_dst, 1, n): legal iff k_val == k_dst
+// or k_val == 1 (broadcast).
+int gpf_fv_cfg_set_bc(gpf_fv_cfg* cfg, const uint8_t masks[4][3][3], const double d_val[4]) {
+    GPF_TRY
+    if (!cfg || !masks || !d_val) { set_error("null argument"); return GPF_E_INVALID; }
+    // side -> (assign masks index, value masks index)
+    const int assign[4] = {0, 1, 2, 3};   // x0: xE, x1: xW, y0: yS, y1: yN
+    const int value[4] = {1, 0, 3, 2};    // x0: xW, x1: xE, y0: yN, y1: yS
+    for (int s = 0; s < 4; ++s) {
+        const int A = assign[s], Vv = value[s];
+        cfg->bc_val[s] = d_val[Vv];
+        bool allP = masks[A][0][0] && masks[A][0][1] && masks[A][0][2];
+        for (int c = 0; c < 3; ++c) { cfg->bc_type[s][c] = GPF_BC_P; cfg->bc_src[s][c] = c; }
+        if (allP) continue;
+        bool assigned[3] = {false, false, false};
+        for (int k = 1; k <= 2; ++k) {       // D then N, as the reference assigns them
+            int dst[3], nd = 0, src[3], ns = 0;
+            for (int c = 0; c < 3; ++c) { if (masks[A][k][c]) dst[nd++] = c; if (masks[Vv][k][c]) src[ns++] = c; }
+            if (nd == 0 && ns == 0) continue;
+            if (nd == 0) continue;           // nothing selected on the left-hand side: no-op in NumPy
+            if (!(ns == nd || ns == 1)) {
+                set_error("boundary masks: the reference's ghost-cell assignment would raise (shape mismatch between E/W or S/N masks)");
+                return GPF_E_INVALID;
+            }
+            for (int t = 0; t < nd; ++t) {
+                cfg->bc_type[s][dst[t]] = (k == 1) ? GPF_BC_D : GPF_BC_N;
+                cfg->bc_src[s][dst[t]] = (ns == 1) ? src[0] : src[t];
+                assigned[dst[t]] = true;
+            }
+        }
+        for (int c = 0; c < 3; ++c)
+            if (!assigned[c]) {
+                set_error("boundary masks: a side mixes periodic with D/N components; the reference leaves those ghost cells undefined");
+                return GPF_E_INVALID;
+            }
+    }
+    return GPF_OK;
+    GPF_CATCH
+}
+
+int gpf_fv_workspace_bytes(const gpf_fv_cfg* cfg, size_t* bytes) {
+    GPF_TRY
+    if (!cfg || !bytes) { set_error("null argument"); return GPF_E_INVALID; }
+    FvParams P;
+    int rc = pack_params(*cfg, &P);
+    if (rc) return rc;
+    *bytes = FvSolver::workspace_bytes(*cfg);
+    return GPF_OK;
+    GPF_CATCH
+}
+
+int gpf_fv_create(const gpf_fv_cfg* cfg, void* workspace, size_t bytes, gpf_fv** out) {
+    GPF_TRY
+    if (!cfg || !workspace || !out) { set_error("null argument"); return GPF_E_INVALID; }
+    gpf_fv* h = new gpf_fv();
+    int rc = h->S.init(*cfg, workspace, bytes);
+    if (rc) { delete h; return rc; }
+    *out = h;
+    return GPF_OK;
+    GPF_CATCH
+}
+
+int gpf_fv_destroy(gpf_fv* s) {
+    GPF_TRY
+    if (!s) return GPF_OK;
+    s->S.destroy();
+    delete s;
+    return GPF_OK;
+    GPF_CATCH
+}
+
+#define NEED(s) if (!(s)) { set_error("null handle"); return GPF_E_INVALID; }
+
+int gpf_fv_upload(gpf_fv* s, int field, const double* data, int ncomp, int on_device, void* stream) {
+    GPF_TRY NEED(s && data) return s->S.upload(field, data, ncomp, on_device, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_download(gpf_fv* s, int field, double* data, int ncomp, int on_device, void* stream) {
+    GPF_TRY NEED(s && data) return s->S.download(field, data, ncomp, on_device, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_pre_run(gpf_fv* s, int reset_ekin_old, void* stream) {
+    GPF_TRY NEED(s) return s->S.pre_run(reset_ekin_old, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_step(gpf_fv* s, int n, int until_converged, void* stream) {
+    GPF_TRY NEED(s) return s->S.step(n, until_converged, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_fill_ghosts(gpf_fv* s, void* stream) {
+    GPF_TRY NEED(s) return s->S.fill_ghosts((cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_get_scalars(gpf_fv* s, gpf_fv_scalars* out, void* stream) {
+    GPF_TRY NEED(s && out) return s->S.get_scalars(out, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_set_scalars(gpf_fv* s, const gpf_fv_scalars* in, void* stream) {
+    GPF_TRY NEED(s && in) return s->S.set_scalars(in, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_mass(gpf_fv* s, double* mass, void* stream) {
+    GPF_TRY NEED(s && mass) return s->S.mass(mass, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_closures(gpf_fv* s, double* pressure, double* wall_xz, double* wall_yz, double* bulk, int on_device,
+                    void* stream) {
+    GPF_TRY NEED(s) return s->S.closures(pressure, wall_xz, wall_yz, bulk, on_device, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, void* stream) {
+    GPF_TRY
+    NEED(s && q_host)
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc;
+    if ((rc = s->S.upload(GPF_F_Q, q_host, 3, 0, st))) return rc;
+    s->S.dirty_scalars = false;    // loop scalars (dt, ekin_old) are kept; only q is replaced
+    if ((rc = s->S.step(n, 0, st))) return rc;
+    if ((rc = s->S.download(GPF_F_Q, q_host, 3, 0, st))) return rc;
+    if (out) return s->S.get_scalars(out, st);
+    GPF_CUDA(cudaStreamSynchronize(st));
+    return GPF_OK;
+    GPF_CATCH
+}
+int gpf_fv_set_timing(gpf_fv* s, int enable) {
+    GPF_TRY NEED(s) s->S.timing = enable != 0; s->S.ev_steps = 0; return GPF_OK; GPF_CATCH
+}
+int gpf_fv_get_timing(gpf_fv* s, double* ms_predictor, double* ms_corrector, int64_t* launches) {
+    GPF_TRY NEED(s)
+    long long l = 0;
+    int rc = s->S.get_timing(ms_predictor, ms_corrector, &l);
+    if (launches) *launches = l;
+    return rc;
+    GPF_CATCH
+}
+
+int gpf_eos_pressure(const gpf_fv_cfg* cfg, const double* dens, double* out, size_t n, void* stream) {
+    GPF_TRY NEED(cfg && (n == 0 || (dens && out))) return launch_eos(*cfg, dens, out, n, false, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_eos_sound_velocity(const gpf_fv_cfg* cfg, const double* dens, double* out, size_t n, void* stream) {
+    GPF_TRY NEED(cfg && (n == 0 || (dens && out))) return launch_eos(*cfg, dens, out, n, true, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_stress_bottom(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls, double* out,
+                      size_t n, void* stream) {
+    GPF_TRY NEED(cfg && (n == 0 || (q && h && out))) return launch_stress(*cfg, 0, q, h, Ls, out, n, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_stress_top(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls, double* out, size_t n,
+                   void* stream) {
+    GPF_TRY NEED(cfg && (n == 0 || (q && h && out))) return launch_stress(*cfg, 1, q, h, Ls, out, n, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls, double* out, size_t n,
+                   void* stream) {
+    GPF_TRY NEED(cfg && (n == 0 || (q && h && out))) return launch_stress(*cfg, 2, q, h, Ls, out, n, (cudaStream_t)stream); GPF_CATCH
+}
+
+}  // extern "C"

@@ -1,0 +1,76 @@
+// Host-side solver object behind the opaque gpf_fv handle.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <atomic>
+#include <string>
+#include <vector>
+#include "gpf_types.h"
+
+namespace gpf {
+
+extern std::atomic<long long> g_launches;
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define GPF_CUDA(x)                                        \
+    do {                                                   \
+        cudaError_t _e = (x);                              \
+        if (_e != cudaSuccess) return cuda_fail(_e, #x);   \
+    } while (0)
+
+// reduction result of the "refresh" path (scalars of the current q)
+struct RefreshOut {
+    double ekin, vmax, vsound, mass;
+    int has_nan, has_neg;
+};
+
+struct FvSolver {
+    gpf_fv_cfg cfg;
+    FvParams P;
+    int device;
+    // carved from the caller's workspace
+    double* qbuf[3];
+    double* topo;      // 3 planes
+    double* extra;     // 1 plane
+    DevState* st;
+    Partial* partial;
+    int* pflags;
+    RefreshOut* refresh;
+    int npartial;      // capacity of partial/pflags
+    CUtensorMap qmap[3], topo_map, ls_map;
+    bool dirty_scalars;   // q changed from the host since scalars were computed
+    double** qtable;      // device copy of qbuf[3]
+    // timing
+    bool timing;
+    std::vector<cudaEvent_t> ev;   // 3 per step
+    int ev_steps;
+
+    static size_t workspace_bytes(const gpf_fv_cfg& c);
+    int init(const gpf_fv_cfg& c, void* ws, size_t bytes);
+    int destroy();
+    int upload(int field, const double* data, int ncomp, int on_device, cudaStream_t s);
+    int download(int field, double* data, int ncomp, int on_device, cudaStream_t s);
+    int pre_run(int reset_ekin_old, cudaStream_t s);
+    int step(int n, int until_converged, cudaStream_t s);
+    int fill_ghosts(cudaStream_t s);
+    int refresh_scalars(cudaStream_t s);
+    int get_scalars(gpf_fv_scalars* out, cudaStream_t s);
+    int set_scalars(const gpf_fv_scalars* in, cudaStream_t s);
+    int mass(double* m, cudaStream_t s);
+    int closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s);
+    int get_timing(double* ms_pred, double* ms_corr, long long* launches);
+    double* field_ptr(int field, int* ncomp_max);
+    int read_cur(cudaStream_t s, int* cur);
+};
+
+// parameter packing shared with the pure-function entry points
+int pack_params(const gpf_fv_cfg& c, FvParams* P);
+Layout make_layout(int Nx, int Ny);
+
+// pure functions
+int launch_eos(const gpf_fv_cfg& c, const double* dens, double* out, size_t n, bool sound, cudaStream_t s);
+int launch_stress(const gpf_fv_cfg& c, int which, const double* q, const double* h, const double* Ls,
+                  double* out, size_t n, cudaStream_t s);
+
+}  // namespace gpf

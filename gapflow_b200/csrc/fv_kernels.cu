@@ -1,0 +1,1008 @@
+// FV kernels + launchers.  Compile with -fmad=false (see closures.cuh).
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "fv_pass.cuh"
+#include "fv_host.h"
+
+namespace gpf {
+
+// shared-memory carve-up of the pass kernel (all TMA destinations 128-byte aligned)
+constexpr int BOX = BX * BY;                                    // doubles per staged plane
+constexpr size_t BOX3_BYTES = ((size_t)3 * BOX * 8 + 127) / 128 * 128;
+constexpr size_t BOX1_BYTES = ((size_t)BOX * 8 + 127) / 128 * 128;
+constexpr size_t SM_Q = 0;
+constexpr size_t SM_TOPO = SM_Q + BOX3_BYTES;
+constexpr size_t SM_LS = SM_TOPO + BOX3_BYTES;
+constexpr size_t SM_CLOS = SM_LS + BOX1_BYTES;                  // p, t0, t1, t2
+constexpr size_t SM_BAR = SM_CLOS + (size_t)4 * BOX * 8;
+constexpr size_t SM_RED = SM_BAR + 16;
+constexpr size_t SM_TOTAL = SM_RED + 8 * 4 * 8 + 128;           // + alignment slack
+
+struct PassArgs {
+    CUtensorMap qmap[3];
+    CUtensorMap topo_map;
+    CUtensorMap ls_map;
+    FvParams P;
+    double* qbuf[3];
+    DevState* st;
+    Partial* partial;
+    int* pflags;
+    int until_converged;
+};
+
+template <bool CORR, bool LS, int EOS>
+__global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_constant__ PassArgs A) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+    double* sq = reinterpret_cast<double*>(smem + SM_Q);
+    double* stp = reinterpret_cast<double*>(smem + SM_TOPO);
+    double* sls = reinterpret_cast<double*>(smem + SM_LS);
+    double* sp = reinterpret_cast<double*>(smem + SM_CLOS);
+    double* st0 = sp + BOX;
+    double* st1 = st0 + BOX;
+    double* st2 = st1 + BOX;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
+    double* sred = reinterpret_cast<double*>(smem + SM_RED);
+
+    const FvParams& P = A.P;
+    const DevState* st = A.st;
+    // run-loop condition (problem.py:401) evaluated on the device; uniform per grid
+    if (st->stop || (A.until_converged && st->halt)) return;
+
+    const int tid = threadIdx.x;
+    const int cur = st->cur;
+    const int in_idx = CORR ? (cur + 1) % 3 : cur;
+    const int out_idx = CORR ? (cur + 2) % 3 : (cur + 1) % 3;
+    // MacCormack order (problem.py:521-522)
+    const int sw = (P.mc_order == 0) ? (((st->step & 1LL) == 0) ? 1 : -1) : P.mc_order;
+    const int d = CORR ? -sw : sw;
+    const double dt = st->dt;
+
+    const int i0 = 1 + blockIdx.y * TX;     // first interior row / col of the tile
+    const int j0 = 1 + blockIdx.x * TY;
+    const int ox = (d > 0) ? 1 : 0;         // own cells sit at box offset (ox, oy)
+    const int oy = ox;
+
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const uint32_t bytes = (uint32_t)(3 * BOX * 8) * 2 + (LS ? (uint32_t)(BOX * 8) : 0u);
+        mbar_expect_tx(bar, bytes);
+        const int cm = (j0 - oy) + 1;       // memory column of box origin
+        const int cx = i0 - ox;
+        tma_load_3d(sq, &A.qmap[in_idx], bar, cm, cx, 0);
+        tma_load_3d(stp, &A.topo_map, bar, cm, cx, 0);
+        if (LS) tma_load_3d(sls, &A.ls_map, bar, cm, cx, 0);
+    }
+
+    // own cells: column ty, rows g*4 .. g*4+3
+    const int ty = tid & (TY - 1);
+    const int g = tid >> 6;
+    const int Nx = P.L.Nx, Ny = P.L.Ny;
+    const size_t plane = P.L.plane;
+    const int pitch = P.L.pitch;
+
+    // corrector: fetch q0 (own cells only) while the TMA is in flight
+    double q0v[4][3];
+    if (CORR) {
+        const double* q0b = A.qbuf[cur];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = i0 + g * 4 + k, j = j0 + ty;
+            const bool ok = (i <= Nx) && (j <= Ny);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) q0v[k][c] = ok ? q0b[c * plane + (size_t)i * pitch + (j + 1)] : 0.0;
+        }
+    }
+
+    mbar_wait(bar, 0);
+
+    auto load_cell = [&](int rb, int cb) {
+        Cell c;
+        const int o = rb * BY + cb;
+        c.q0 = sq[o];
+        c.q1 = sq[BOX + o];
+        c.q2 = sq[2 * BOX + o];
+        c.h = stp[o];
+        c.hx = stp[BOX + o];
+        c.hy = stp[2 * BOX + o];
+        c.Ls = LS ? sls[o] : 0.0;
+        return c;
+    };
+    auto phase1 = [&](int rb, int cb) {
+        // global indices of this staged cell; skip cells outside the padded array
+        const int i = i0 - ox + rb, j = j0 - oy + cb;
+        if (i > Nx + 1 || j > Ny + 1) return;
+        const Cell c = load_cell(rb, cb);
+        const int o = rb * BY + cb;
+        sp[o] = eos_pressure<EOS>(c.q0, P.eos);
+        double a, b, e;
+        stress_avg<LS>(c, reinterpret_cast<const Visc&>(P.visc), a, b, e);
+        st0[o] = a;
+        st1[o] = b;
+        st2[o] = e;
+    };
+
+    // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) phase1(g * 4 + k + ox, ty + oy);
+    if (tid < TY)
+        phase1((d > 0) ? 0 : TX, tid + oy);                    // halo row
+    else if (tid < TY + TX)
+        phase1(tid - TY + ox, (d > 0) ? 0 : TY);                // halo column
+    __syncthreads();
+
+    // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
+    double* qout = A.qbuf[out_idx];
+    const double* q0b = A.qbuf[cur];
+    const Visc& V = reinterpret_cast<const Visc&>(P.visc);
+    const double sgn = (double)(-d);
+    Red red;
+    red.ekin = 0.0;
+    red.vmax2 = -INFINITY;
+    red.cs2 = -INFINITY;
+    red.flags = 0;
+
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+        const int r = g * 4 + k;
+        const int i = i0 + r, j = j0 + ty;
+        if (i > Nx || j > Ny) continue;
+        const int rb = r + ox, cb = ty + oy;
+        const int o = rb * BY + cb;
+        const int on_x = (rb - d) * BY + cb;     // neighbour the x-difference reaches to
+        const int on_y = rb * BY + (cb - d);
+        const Cell c = load_cell(rb, cb);
+        const double p = sp[o], t0 = st0[o], t1 = st1[o], t2 = st2[o];
+
+        // fluxes: integrate.py:65-75.  Fx = (jx, p + txx, txy), Fy = (jy, txy, p + tyy)
+        const double fx0 = sgn * (sq[BOX + on_x] - c.q1);
+        const double fx1 = sgn * ((sp[on_x] + st0[on_x]) - (p + t0));
+        const double fx2 = sgn * (st2[on_x] - t2);
+        const double fy0 = sgn * (sq[2 * BOX + on_y] - c.q2);
+        const double fy1 = sgn * (st2[on_y] - t2);
+        const double fy2 = sgn * ((sp[on_y] + st1[on_y]) - (p + t1));
+
+        // wall stresses (stress.py:328-362) and their xz + yz sums (problem.py:554-555)
+        double b3, b4, u[6];
+        stress_bottom<LS>(c, V, b3, b4);
+        stress_top<LS, false>(c, V, u);
+        const double up0 = u[0] / 2.0 + u[0] / 2.0;
+        const double up1 = u[1] / 2.0 + u[1] / 2.0;
+        const double up5 = u[5] / 2.0 + u[5] / 2.0;
+        // source: integrate.py:118-128
+        const double s0 = (-c.q1 * c.hx - c.q2 * c.hy) / c.h;
+        const double s1 = ((t0 - up0) * c.hx + (t2 - up5) * c.hy + u[4] - b4) / c.h;
+        const double s2 = ((t2 - up5) * c.hx + (t1 - up1) * c.hy + u[3] - b3) / c.h;
+
+        // problem.py:558
+        double qn[3];
+        qn[0] = c.q0 - dt * (fx0 / P.dx + fy0 / P.dy - s0);
+        qn[1] = c.q1 - dt * (fx1 / P.dx + fy1 / P.dy - s1);
+        qn[2] = c.q2 - dt * (fx2 / P.dx + fy2 / P.dy - s2);
+
+        if (CORR) {
+            // validity is tested on the averaged array INCLUDING its averaged ghost cells
+            // (problem.py:563-565): ghost = (fill(q**) + ghost(q0)) / 2
+            for_each_ghost(P, i, j, qn, [&](int gi, int gj, const double* gv) {
+                const size_t a = (size_t)gi * pitch + (gj + 1);
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc) {
+                    const double av = (gv[cc] + q0b[cc * plane + a]) / 2.0;
+                    if (av != av) red.flags |= FLAG_NAN;
+                    if (cc == 0 && av < 0.0) red.flags |= FLAG_NEG;
+                }
+            });
+#pragma unroll
+            for (int cc = 0; cc < 3; ++cc) {
+                qn[cc] = (qn[cc] + q0v[k][cc]) / 2.0;
+                if (qn[cc] != qn[cc]) red.flags |= FLAG_NAN;
+            }
+            if (qn[0] < 0.0) red.flags |= FLAG_NEG;
+            red_accum<EOS>(red, qn, P.eos);
+        }
+
+        const size_t a = (size_t)i * pitch + (j + 1);
+        qout[a] = qn[0];
+        qout[plane + a] = qn[1];
+        qout[2 * plane + a] = qn[2];
+
+        // ghost cells derived from this cell (problem.py:560 / 576)
+        for_each_ghost(P, i, j, qn, [&](int gi, int gj, const double* gv) {
+            const size_t ga = (size_t)gi * pitch + (gj + 1);
+            qout[ga] = gv[0];
+            qout[plane + ga] = gv[1];
+            qout[2 * plane + ga] = gv[2];
+            if (CORR) red_accum<EOS>(red, gv, P.eos);
+        });
+    }
+
+    if (CORR) {
+        // warp shuffles, then one record per block (deterministic order)
+        double e = warp_sum(red.ekin);
+        double vm = warp_max(red.vmax2);
+        double cm = warp_max(red.cs2);
+        int fl = red.flags;
+#pragma unroll
+        for (int oo = 16; oo > 0; oo >>= 1) fl |= __shfl_xor_sync(0xffffffffu, fl, oo);
+        const int w = tid >> 5, lane = tid & 31;
+        if (lane == 0) {
+            sred[w * 4 + 0] = e;
+            sred[w * 4 + 1] = vm;
+            sred[w * 4 + 2] = cm;
+            sred[w * 4 + 3] = (double)fl;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double E = 0.0, VM = -INFINITY, CM = -INFINITY;
+            int F = 0;
+            for (int ww = 0; ww < FV_THREADS / 32; ++ww) {
+                E += sred[ww * 4 + 0];
+                VM = fmax(VM, sred[ww * 4 + 1]);
+                CM = fmax(CM, sred[ww * 4 + 2]);
+                F |= (int)sred[ww * 4 + 3];
+            }
+            const int b = blockIdx.y * gridDim.x + blockIdx.x;
+            A.partial[b].ekin = E;
+            A.partial[b].vmax2 = VM;
+            A.partial[b].cs2 = CM;
+            A.partial[b].mass = 0.0;
+            A.pflags[b] = F;
+        }
+    }
+}
+
+// =====================================================================================
+// Scalar bookkeeping kernels
+// =====================================================================================
+enum { FIN_STEP = 0, FIN_PRERUN = 1, FIN_PRERUN_KEEP_EKIN = 2, FIN_REFRESH = 3 };
+
+// Reduces the per-block records in a fixed order (deterministic), then thread 0 advances
+// the loop state the way Problem._post_update / _finalize / _pre_run do
+// (problem.py:571-610, 428-443).
+__global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ FvParams P, DevState* st,
+                                                        const Partial* part, const int* pflags, int nblk,
+                                                        int mode, int until_converged, RefreshOut* ro) {
+    if (mode == FIN_STEP && (st->stop || (until_converged && st->halt))) return;
+    __shared__ double sE[256], sV[256], sC[256], sM[256];
+    __shared__ int sF[256];
+    const int tid = threadIdx.x;
+    double E = 0.0, VM = -INFINITY, CM = -INFINITY, M = 0.0;
+    int F = 0;
+    for (int b = tid; b < nblk; b += 256) {
+        E += part[b].ekin;
+        M += part[b].mass;
+        VM = fmax(VM, part[b].vmax2);
+        CM = fmax(CM, part[b].cs2);
+        F |= pflags[b];
+    }
+    sE[tid] = E; sV[tid] = VM; sC[tid] = CM; sM[tid] = M; sF[tid] = F;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (tid < s) {
+            sE[tid] += sE[tid + s];
+            sM[tid] += sM[tid + s];
+            sV[tid] = fmax(sV[tid], sV[tid + s]);
+            sC[tid] = fmax(sC[tid], sC[tid + s]);
+            sF[tid] |= sF[tid + s];
+        }
+        __syncthreads();
+    }
+    if (tid != 0) return;
+    E = sE[0]; VM = sV[0]; CM = sC[0]; M = sM[0]; F = sF[0];
+    const double qnan = nan("");
+    // np.max propagates NaN (problem.py:347, stress.py:539)
+    const double vmax = (F & FLAG_VNAN) ? qnan : sqrt(VM);
+    const double vsound = (F & FLAG_CNAN) ? qnan : sqrt(CM);
+    const double dxy = (P.dy < P.dx) ? P.dy : P.dx;          // Python min(dx, dy)
+
+    if (mode == FIN_REFRESH) {
+        ro->ekin = E; ro->vmax = vmax; ro->vsound = vsound; ro->mass = M;
+        ro->has_nan = (F & FLAG_NAN) ? 1 : 0;
+        ro->has_neg = (F & FLAG_NEG) ? 1 : 0;
+        return;
+    }
+    if (mode == FIN_PRERUN || mode == FIN_PRERUN_KEEP_EKIN) {
+        st->ekin = E; st->vmax = vmax; st->vsound = vsound;
+        if (mode == FIN_PRERUN) st->ekin_old = E;              // problem.py:670
+        st->dt_crit = dxy / (vmax + vsound);
+        st->step = 0; st->simtime = 0.0; st->residual = 1.0;    // problem.py:429-432
+        st->resbuf[0] = 1.0; st->rescount = 1;
+        st->dt = P.adaptive ? P.CFL * st->dt_crit : P.dt0;      // problem.py:434-437
+        st->cfl = st->dt / st->dt_crit;
+        st->has_nan = 0; st->has_neg = 0; st->stop = 0;
+        st->converged = (1.0 < P.tol) ? 1 : 0;
+        st->halt = (st->converged || st->step >= P.max_it) ? 1 : 0;
+        return;
+    }
+    // ---- FIN_STEP ----
+    st->has_nan = (F & FLAG_NAN) ? 1 : 0;
+    st->has_neg = (F & FLAG_NEG) ? 1 : 0;
+    if (F & (FLAG_NAN | FLAG_NEG)) {
+        // _finalize (problem.py:588-610): q0 is still the current buffer -> nothing to restore
+        st->stop = 1;
+        st->halt = 1;
+        return;
+    }
+    st->cur = (st->cur + 2) % 3;
+    st->ekin = E; st->vmax = vmax; st->vsound = vsound;
+    st->dt_crit = dxy / (vmax + vsound);
+    st->cfl = st->dt / st->dt_crit;
+    const double res = fabs(E - st->ekin_old) / st->ekin_old / st->cfl;   // problem.py:578
+    st->residual = res;
+    if (st->rescount < 5) {
+        st->resbuf[st->rescount++] = res;
+    } else {
+        for (int k = 0; k < 4; ++k) st->resbuf[k] = st->resbuf[k + 1];
+        st->resbuf[4] = res;
+    }
+    st->ekin_old = E;
+    st->step += 1;
+    st->simtime += st->dt;
+    if (P.adaptive) {
+        st->dt = P.CFL * st->dt_crit;                                     // problem.py:585-586
+        st->cfl = st->dt / st->dt_crit;
+    }
+    int conv = 1;
+    for (int k = 0; k < st->rescount; ++k) conv &= (st->resbuf[k] < P.tol) ? 1 : 0;   // problem.py:360-362
+    st->converged = conv;
+    st->halt = (conv || st->step >= P.max_it) ? 1 : 0;
+}
+
+// Scalars of the current q over the whole padded array (problem.py:320-347).
+template <int EOS>
+__global__ void __launch_bounds__(256) fv_reduce_kernel(const __grid_constant__ FvParams P, const DevState* st,
+                                                        double* const* qbufs, const double* topo,
+                                                        Partial* part, int* pflags) {
+    const double* q = qbufs[st->cur];
+    const int Nx2 = P.L.Nx + 2, Ny2 = P.L.Ny + 2;
+    const size_t plane = P.L.plane;
+    Red red; red.ekin = 0.0; red.vmax2 = -INFINITY; red.cs2 = -INFINITY; red.flags = 0;
+    double mass = 0.0;
+    const size_t total = (size_t)Nx2 * Ny2;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (size_t)gridDim.x * blockDim.x) {
+        const int i = (int)(idx / Ny2), j = (int)(idx % Ny2);
+        const size_t a = (size_t)i * P.L.pitch + (j + 1);
+        double v[3] = {q[a], q[plane + a], q[2 * plane + a]};
+        if (v[0] != v[0] || v[1] != v[1] || v[2] != v[2]) red.flags |= FLAG_NAN;
+        if (v[0] < 0.0) red.flags |= FLAG_NEG;
+        red_accum<EOS>(red, v, P.eos);
+        mass += v[0] * topo[a] * P.dx * P.dy;                 // problem.py:337
+    }
+    __shared__ double sred[8 * 4];
+    __shared__ int sfl[8];
+    double e = warp_sum(red.ekin), vm = warp_max(red.vmax2), cm = warp_max(red.cs2), ms = warp_sum(mass);
+    int fl = red.flags;
+#pragma unroll
+    for (int oo = 16; oo > 0; oo >>= 1) fl |= __shfl_xor_sync(0xffffffffu, fl, oo);
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sred[w * 4] = e; sred[w * 4 + 1] = vm; sred[w * 4 + 2] = cm; sred[w * 4 + 3] = ms; sfl[w] = fl; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double E = 0.0, VM = -INFINITY, CM = -INFINITY, M = 0.0; int F = 0;
+        for (int ww = 0; ww < 8; ++ww) {
+            E += sred[ww * 4]; VM = fmax(VM, sred[ww * 4 + 1]); CM = fmax(CM, sred[ww * 4 + 2]);
+            M += sred[ww * 4 + 3]; F |= sfl[ww];
+        }
+        part[blockIdx.x].ekin = E; part[blockIdx.x].vmax2 = VM; part[blockIdx.x].cs2 = CM;
+        part[blockIdx.x].mass = M; pflags[blockIdx.x] = F;
+    }
+}
+
+// _communicate_ghost_buffers on the current q (problem.py:676-707): one thread per
+// perimeter interior cell.
+__global__ void fv_fill_ghosts_kernel(const __grid_constant__ FvParams P, const DevState* st, double* const* qbufs) {
+    double* q = qbufs[st->cur];
+    const int Nx = P.L.Nx, Ny = P.L.Ny;
+    const int n = 2 * Nx + 2 * Ny;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    int i, j;
+    if (t < Ny) { i = 1; j = t + 1; }
+    else if (t < 2 * Ny) { i = Nx; j = t - Ny + 1; if (Nx == 1) return; }
+    else if (t < 2 * Ny + Nx) { i = t - 2 * Ny + 1; j = 1; if (i == 1 || i == Nx) return; }
+    else { i = t - 2 * Ny - Nx + 1; j = Ny; if (i == 1 || i == Nx || Ny == 1) return; }
+    const size_t plane = P.L.plane;
+    const size_t a = (size_t)i * P.L.pitch + (j + 1);
+    const double v[3] = {q[a], q[plane + a], q[2 * plane + a]};
+    for_each_ghost(P, i, j, v, [&](int gi, int gj, const double* gv) {
+        const size_t ga = (size_t)gi * P.L.pitch + (gj + 1);
+        q[ga] = gv[0]; q[plane + ga] = gv[1]; q[2 * plane + ga] = gv[2];
+    });
+}
+
+// Closure fields as the reference stores them for sol.nc (stress.py:346-362, 452-459,
+// 619-622): dense (ncomp, Nx+2, Ny+2) outputs; NULL outputs are skipped.
+template <bool LS, int EOS>
+__global__ void __launch_bounds__(256) fv_closures_kernel(const __grid_constant__ FvParams P, const DevState* st,
+                                                          double* const* qbufs, const double* topo,
+                                                          const double* extra, double* pr, double* wxz,
+                                                          double* wyz, double* bulk) {
+    const double* q = qbufs[st->cur];
+    const int Nx2 = P.L.Nx + 2, Ny2 = P.L.Ny + 2;
+    const size_t np = (size_t)Nx2 * Ny2, plane = P.L.plane;
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= np) return;
+    const int i = (int)(idx / Ny2), j = (int)(idx % Ny2);
+    const size_t a = (size_t)i * P.L.pitch + (j + 1);
+    Cell c;
+    c.q0 = q[a]; c.q1 = q[plane + a]; c.q2 = q[2 * plane + a];
+    c.h = topo[a]; c.hx = topo[plane + a]; c.hy = topo[2 * plane + a];
+    c.Ls = LS ? extra[a] : 0.0;
+    const Visc& V = reinterpret_cast<const Visc&>(P.visc);
+    if (pr) pr[idx] = eos_pressure<EOS>(c.q0, P.eos);
+    if (bulk) {
+        double t0, t1, t2;
+        stress_avg<LS>(c, V, t0, t1, t2);
+        bulk[idx] = t0; bulk[np + idx] = t1; bulk[2 * np + idx] = t2;
+    }
+    if (wxz || wyz) {
+        double b3, b4, u[6];
+        stress_bottom<LS>(c, V, b3, b4);
+        stress_top<LS, true>(c, V, u);
+        // lower: comps 0-2 and 5 halved (zero for slip-top bottom wall); own shear in full
+        for (int f = 0; f < 2; ++f) {
+            double* w = f == 0 ? wxz : wyz;
+            if (!w) continue;
+            const int own = f == 0 ? 4 : 3;
+            for (int k = 0; k < 12; ++k) w[k * np + idx] = 0.0;
+            w[own * np + idx] = own == 4 ? b4 : b3;
+            w[6 * np + idx] = u[0] / 2.0; w[7 * np + idx] = u[1] / 2.0; w[8 * np + idx] = u[2] / 2.0;
+            w[11 * np + idx] = u[5] / 2.0;
+            w[(own + 6) * np + idx] = u[own];
+        }
+    }
+}
+
+// ---- pure functions (B2 cut of the drop-in boundary) ---------------------------------
+template <bool SOUND>
+__global__ void eos_kernel(EosParams e, const double* dens, double* out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = SOUND ? sqrt(eos_sound2<-1>(dens[i], e)) : eos_pressure<-1>(dens[i], e);
+}
+
+template <bool LS>
+__global__ void stress_kernel(ViscParams vp, int which, const double* q, const double* h, const double* Ls,
+                              double* out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Cell c;
+    c.q0 = q[i]; c.q1 = q[n + i]; c.q2 = q[2 * n + i];
+    c.h = h[i]; c.hx = h[n + i]; c.hy = h[2 * n + i];
+    c.Ls = LS ? Ls[i] : 0.0;
+    const Visc& V = reinterpret_cast<const Visc&>(vp);
+    if (which == 0) {          // stress_bottom
+        double b3, b4;
+        stress_bottom<LS>(c, V, b3, b4);
+        for (int k = 0; k < 6; ++k) out[k * n + i] = 0.0;
+        out[3 * n + i] = b3; out[4 * n + i] = b4;
+    } else if (which == 1) {   // stress_top
+        double u[6];
+        stress_top<LS, true>(c, V, u);
+        for (int k = 0; k < 6; ++k) out[k * n + i] = u[k];
+    } else {                   // stress_avg
+        double t0, t1, t2;
+        stress_avg<LS>(c, V, t0, t1, t2);
+        out[i] = t0; out[n + i] = t1; out[2 * n + i] = t2;
+    }
+}
+
+// =====================================================================================
+// Host side
+// =====================================================================================
+std::atomic<long long> g_launches{0};
+
+Layout make_layout(int Nx, int Ny) {
+    Layout L;
+    L.Nx = Nx; L.Ny = Ny;
+    int pitch = ((Ny + 3 + 15) / 16) * 16;
+    if (pitch < 80) pitch = 80;                 // >= staged box width
+    L.pitch = pitch;
+    L.rows = (Nx + 2 < BX + 1) ? BX + 1 : Nx + 2;
+    L.plane = (size_t)L.rows * L.pitch;
+    return L;
+}
+
+static const double BWR_X[32] = {
+    0.8623085097507421, 2.976218765822098, -8.402230115796038, 0.1054136629203555,
+    -0.8564583828174598, 1.582759470107601, 0.7639421948305453, 1.753173414312048,
+    2.798291772190376e+03, -4.8394220260857657e-02, 0.9963265197721935, -3.698000291272493e+01,
+    2.084012299434647e+01, 8.305402124717285e+01, -9.574799715203068e+02, -1.477746229234994e+02,
+    6.398607852471505e+01, 1.603993673294834e+01, 6.805916615864377e+01, -2.791293578795945e+03,
+    -6.245128304568454, -8.116836104958410e+03, 1.488735559561229e+01, -1.059346754655084e+04,
+    -1.131607632802822e+02, -8.867771540418822e+03, -3.986982844450543e+01, -4.689270299917261e+03,
+    2.593535277438717e+02, -2.694523589434903e+03, -7.218487631550215e+02, 1.721802063863269e+02};
+
+// Combines EOS parameters exactly as the reference's Python float expressions do.
+// (host compiler: no FMA contraction -- build.py passes -ffp-contract=off)
+static int eos_pack(const gpf_fv_cfg& c, EosParams* e) {
+    const double* a = c.eos_par;
+    for (int k = 0; k < 10; ++k) e->p[k] = 0.0;
+    for (int k = 0; k < 14; ++k) e->c[k] = 0.0;
+    e->kind = c.eos;
+    switch (c.eos) {
+    case GPF_EOS_DH:      // rho0, P0, C1, C2
+        e->p[0] = a[0]; e->p[1] = a[1]; e->p[2] = a[2]; e->p[3] = a[3];
+        e->p[4] = 0.99 * a[3] * a[0];
+        e->p[5] = a[2] * a[0] * (a[3] - 1.0);
+        e->p[6] = a[3] * a[0];
+        return GPF_OK;
+    case GPF_EOS_PL:      // rho0, P0, alpha
+        e->p[0] = a[0]; e->p[1] = a[1]; e->p[2] = a[2];
+        e->p[3] = 1. / (1. - 0.5 * a[2]);
+        e->p[5] = -2.0 * a[1];
+        e->p[6] = -2.0 / (a[2] - 2.0);
+        e->p[7] = a[2] - 2;
+        return GPF_OK;
+    case GPF_EOS_VDW: {   // M, T, a, b
+        const double R = 8.31446261815324;
+        e->p[0] = a[0]; e->p[1] = R * a[1]; e->p[2] = a[2] / 10.; e->p[3] = a[3] / 1000.;
+        e->p[4] = 2. * e->p[2];
+        return GPF_OK;
+    }
+    case GPF_EOS_MT:      // rho0, P0, K, n
+        e->p[0] = a[0]; e->p[1] = a[1]; e->p[2] = a[2] / a[3]; e->p[3] = a[3];
+        e->p[5] = a[2] / pow(a[0], a[3]);
+        e->p[6] = a[3] - 1;
+        return GPF_OK;
+    case GPF_EOS_CUBIC:   // a, b, c, d
+        e->p[0] = a[0]; e->p[1] = a[1]; e->p[2] = a[2]; e->p[3] = a[3];
+        e->p[4] = 3 * a[0]; e->p[5] = 2 * a[1];
+        return GPF_OK;
+    case GPF_EOS_BWR: {   // T, gamma
+        const double T = a[0], T2 = pow(T, 2), T3 = pow(T, 3), T4 = pow(T, 4);   // Python float **
+        const double* x = BWR_X;
+        e->p[0] = T; e->p[1] = a[1];
+        e->c[0] = x[0] * T + x[1] * sqrt(T) + x[2] + x[3] / T + x[4] / T2;
+        e->c[1] = x[5] * T + x[6] + x[7] / T + x[8] / T2;
+        e->c[2] = x[9] * T + x[10] + x[11] / T;
+        e->c[3] = x[12];
+        e->c[4] = x[13] / T + x[14] / T2;
+        e->c[5] = x[15] / T;
+        e->c[6] = x[16] / T + x[17] / T2;
+        e->c[7] = x[18] / T2;
+        e->c[8] = x[19] / T2 + x[20] / T3;
+        e->c[9] = x[21] / T2 + x[22] / T4;
+        e->c[10] = x[23] / T2 + x[24] / T3;
+        e->c[11] = x[25] / T2 + x[26] / T4;
+        e->c[12] = x[27] / T2 + x[28] / T3;
+        e->c[13] = x[29] / T2 + x[30] / T3 + x[31] / T4;
+        return GPF_OK;
+    }
+    case GPF_EOS_BAYADA: {   // rho_l, rho_v, c_l, c_v
+        const double rl = a[0], rv = a[1], cl2 = pow(a[2], 2), cv2 = pow(a[3], 2);
+        const double rv2 = pow(rv, 2), rl2 = pow(rl, 2);
+        const double N = rv * cv2 * rl * cl2 * (rv - rl) / (rv2 * cv2 - rl2 * cl2);
+        const double Pcav = rv * cv2 - N * log(rv2 * cv2 / (rl2 * cl2));
+        const double cc = a[3] * a[2];
+        e->p[0] = rl; e->p[1] = rv; e->p[2] = cl2; e->p[3] = cv2; e->p[4] = N; e->p[5] = Pcav;
+        e->p[6] = rv * cv2; e->p[7] = rl * cl2; e->p[8] = rv * rl * pow(cc, 2);
+        return GPF_OK;
+    }
+    }
+    set_error("unknown EOS id");
+    return GPF_E_INVALID;
+}
+
+int pack_params(const gpf_fv_cfg& c, FvParams* P) {
+    if (c.Nx < 1 || c.Ny < 1) { set_error("Nx, Ny must be >= 1"); return GPF_E_INVALID; }
+    if (c.mc_order != 0 && c.mc_order != 1 && c.mc_order != -1) { set_error("MC_order must be -1, 0 or 1"); return GPF_E_INVALID; }
+    P->L = make_layout(c.Nx, c.Ny);
+    P->dx = c.dx; P->dy = c.dy;
+    ViscParams& v = P->visc;
+    v.U = c.U; v.V = c.V; v.eta = c.eta; v.zeta = c.zeta;
+    v.v1 = c.zeta + 4. / 3. * c.eta;          // Python: zeta + 4 / 3 * eta
+    v.v2 = c.zeta - 2. / 3. * c.eta;
+    v.two_eta = 2 * c.eta;
+    v.two_v2 = 2 * v.v2;
+    int rc = eos_pack(c, &P->eos);
+    if (rc) return rc;
+    for (int s = 0; s < 4; ++s) {
+        P->bc.val[s] = c.bc_val[s];
+        for (int k = 0; k < 3; ++k) {
+            const int t = c.bc_type[s][k];
+            if (t < 0 || t > 3 || c.bc_src[s][k] < 0 || c.bc_src[s][k] > 2) { set_error("bad boundary table"); return GPF_E_INVALID; }
+            const int t0 = c.bc_type[s][0];
+            const bool whole = (t0 == GPF_BC_P || t0 == GPF_BC_HALO);   // side-wide kinds
+            if (whole ? (t != t0) : !(t == GPF_BC_D || t == GPF_BC_N)) {
+                set_error("a side mixes periodic with D/N components: the reference leaves such ghost cells undefined");
+                return GPF_E_INVALID;
+            }
+            if (s >= 2 && t == GPF_BC_HALO) { set_error("HALO sides are x-only (slab decomposition along x)"); return GPF_E_INVALID; }
+            P->bc.type[s][k] = t; P->bc.src[s][k] = c.bc_src[s][k];
+        }
+    }
+    P->CFL = c.CFL; P->tol = c.tol; P->dt0 = c.dt;
+    P->adaptive = c.adaptive; P->max_it = c.max_it; P->mc_order = c.mc_order;
+    P->has_extra = c.has_extra;
+    P->nblk_y = (c.Nx + TX - 1) / TX;
+    P->nblk_x = (c.Ny + TY - 1) / TY;
+    return GPF_OK;
+}
+
+// ---- TMA descriptors ----------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// planes of `ncomp` x rows x pitch doubles; box = (BY, BX, ncomp)
+static int make_map(CUtensorMap* m, double* base, const Layout& L, int ncomp) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return GPF_E_CUDA; }
+    cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.rows, (cuuint64_t)ncomp};
+    cuuint64_t strides[2] = {(cuuint64_t)L.pitch * 8, (cuuint64_t)L.plane * 8};
+    cuuint32_t box[3] = {(cuuint32_t)BY, (cuuint32_t)BX, (cuuint32_t)ncomp};
+    cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed, CUresult " + std::to_string((int)r)); return GPF_E_CUDA; }
+    return GPF_OK;
+}
+
+// ---- solver --------------------------------------------------------------------------
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static const int REDUCE_BLOCKS = 148 * 8;
+
+size_t FvSolver::workspace_bytes(const gpf_fv_cfg& c) {
+    Layout L = make_layout(c.Nx, c.Ny);
+    size_t plane_b = align_up(L.plane * 8, 256);
+    int nb = ((c.Nx + TX - 1) / TX) * ((c.Ny + TY - 1) / TY);
+    if (nb < REDUCE_BLOCKS) nb = REDUCE_BLOCKS;
+    size_t b = 0;
+    b += 3 * 3 * plane_b;      // q x3 buffers
+    b += 3 * plane_b;          // topo
+    b += plane_b;              // extra
+    b += align_up(sizeof(DevState), 256) + align_up(sizeof(RefreshOut), 256);
+    b += align_up((size_t)nb * sizeof(Partial), 256) + align_up((size_t)nb * sizeof(int), 256);
+    b += 256 + 256;            // qbuf pointer table + slack for base alignment
+    return b;
+}
+
+int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
+    cfg = c;
+    int rc = pack_params(c, &P);
+    if (rc) return rc;
+    if (bytes < workspace_bytes(c)) { set_error("workspace too small"); return GPF_E_INVALID; }
+    GPF_CUDA(cudaGetDevice(&device));
+    cudaPointerAttributes at;
+    GPF_CUDA(cudaPointerGetAttributes(&at, ws));
+    if (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged) { set_error("workspace is not device memory"); return GPF_E_INVALID; }
+    const Layout& L = P.L;
+    size_t plane_b = align_up(L.plane * 8, 256);
+    unsigned char* p = reinterpret_cast<unsigned char*>(align_up(reinterpret_cast<size_t>(ws), 256));
+    GPF_CUDA(cudaMemset(ws, 0, bytes));
+    for (int k = 0; k < 3; ++k) { qbuf[k] = reinterpret_cast<double*>(p); p += 3 * plane_b; }
+    topo = reinterpret_cast<double*>(p); p += 3 * plane_b;
+    extra = reinterpret_cast<double*>(p); p += plane_b;
+    st = reinterpret_cast<DevState*>(p); p += align_up(sizeof(DevState), 256);
+    refresh = reinterpret_cast<RefreshOut*>(p); p += align_up(sizeof(RefreshOut), 256);
+    npartial = P.nblk_x * P.nblk_y;
+    if (npartial < REDUCE_BLOCKS) npartial = REDUCE_BLOCKS;
+    partial = reinterpret_cast<Partial*>(p); p += align_up((size_t)npartial * sizeof(Partial), 256);
+    pflags = reinterpret_cast<int*>(p); p += align_up((size_t)npartial * sizeof(int), 256);
+    qtable = reinterpret_cast<double**>(p); p += 256;
+    // planes are allocated with stride plane_b; the layout's plane stride must match
+    P.L.plane = plane_b / 8;
+    GPF_CUDA(cudaMemcpy(qtable, qbuf, sizeof(qbuf), cudaMemcpyHostToDevice));
+    for (int k = 0; k < 3; ++k) if ((rc = make_map(&qmap[k], qbuf[k], P.L, 3))) return rc;
+    if ((rc = make_map(&topo_map, topo, P.L, 3))) return rc;
+    if ((rc = make_map(&ls_map, extra, P.L, 1))) return rc;
+    // _initialize (problem.py:662-670): rho0, rho0*U/2, rho0*V/2 everywhere incl. ghosts
+    {
+        const size_t np = (size_t)(c.Nx + 2) * (c.Ny + 2);
+        std::vector<double> h(3 * np);
+        const double v[3] = {c.rho0, c.rho0 * c.U / 2.0, c.rho0 * c.V / 2.0};
+        for (int k = 0; k < 3; ++k) for (size_t t = 0; t < np; ++t) h[k * np + t] = v[k];
+        rc = upload(GPF_F_Q, h.data(), 3, 0, 0);
+        if (rc) return rc;
+        GPF_CUDA(cudaStreamSynchronize(0));
+    }
+    DevState s0;
+    memset(&s0, 0, sizeof(s0));
+    s0.dt = c.dt; s0.residual = 1.0; s0.resbuf[0] = 1.0; s0.rescount = 1;
+    GPF_CUDA(cudaMemcpy(st, &s0, sizeof(s0), cudaMemcpyHostToDevice));
+    dirty_scalars = true;
+    timing = false;
+    ev_steps = 0;
+    return GPF_OK;
+}
+
+int FvSolver::destroy() {
+    for (auto e : ev) cudaEventDestroy(e);
+    ev.clear();
+    return GPF_OK;
+}
+
+double* FvSolver::field_ptr(int field, int* nc) {
+    switch (field) {
+    case GPF_F_TOPO: *nc = 3; return topo;
+    case GPF_F_EXTRA: *nc = 1; return extra;
+    }
+    *nc = 0;
+    return nullptr;
+}
+
+int FvSolver::read_cur(cudaStream_t s, int* cur) {
+    DevState h;
+    GPF_CUDA(cudaMemcpyAsync(&h, st, sizeof(h), cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    *cur = h.cur;
+    return GPF_OK;
+}
+
+int FvSolver::upload(int field, const double* data, int ncomp, int on_device, cudaStream_t s) {
+    int ncmax = 3;
+    double* base;
+    if (field == GPF_F_Q) {
+        int cur; int rc = read_cur(s, &cur); if (rc) return rc;
+        base = qbuf[cur];
+        if (ncomp != 3) { set_error("q has 3 components"); return GPF_E_INVALID; }
+    } else {
+        base = field_ptr(field, &ncmax);
+        if (!base) { set_error("unknown field id"); return GPF_E_INVALID; }
+        if (ncomp < ncmax || ncomp > ncmax + 1) { set_error("wrong component count"); return GPF_E_INVALID; }
+    }
+    const size_t Ny2 = cfg.Ny + 2, Nx2 = cfg.Nx + 2;
+    for (int k = 0; k < ncmax; ++k)
+        GPF_CUDA(cudaMemcpy2DAsync(base + k * P.L.plane + 1, (size_t)P.L.pitch * 8, data + (size_t)k * Nx2 * Ny2,
+                                   Ny2 * 8, Ny2 * 8, Nx2, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
+    if (field == GPF_F_Q) dirty_scalars = true;
+    return GPF_OK;
+}
+
+int FvSolver::download(int field, double* data, int ncomp, int on_device, cudaStream_t s) {
+    int ncmax = 3;
+    const double* base;
+    if (field == GPF_F_Q) {
+        int cur; int rc = read_cur(s, &cur); if (rc) return rc;
+        base = qbuf[cur];
+    } else {
+        base = field_ptr(field, &ncmax);
+        if (!base) { set_error("unknown field id"); return GPF_E_INVALID; }
+    }
+    if (ncomp < ncmax) { set_error("wrong component count"); return GPF_E_INVALID; }
+    const size_t Ny2 = cfg.Ny + 2, Nx2 = cfg.Nx + 2;
+    for (int k = 0; k < ncmax; ++k)
+        GPF_CUDA(cudaMemcpy2DAsync(data + (size_t)k * Nx2 * Ny2, Ny2 * 8, base + k * P.L.plane + 1, (size_t)P.L.pitch * 8,
+                                   Ny2 * 8, Nx2, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    return GPF_OK;
+}
+
+template <bool CORR>
+static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
+    PassArgs A;
+    for (int k = 0; k < 3; ++k) { A.qmap[k] = S.qmap[k]; A.qbuf[k] = S.qbuf[k]; }
+    A.topo_map = S.topo_map; A.ls_map = S.ls_map;
+    A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags;
+    A.until_converged = until_converged;
+    dim3 grid(S.P.nblk_x, S.P.nblk_y), block(FV_THREADS);
+    const bool ls = S.P.has_extra != 0;
+    const bool dh = S.P.eos.kind == GPF_EOS_DH;
+    void (*k)(const PassArgs);
+    if (ls) k = dh ? fv_pass_kernel<CORR, true, GPF_EOS_DH> : fv_pass_kernel<CORR, true, -1>;
+    else    k = dh ? fv_pass_kernel<CORR, false, GPF_EOS_DH> : fv_pass_kernel<CORR, false, -1>;
+    static bool attr_set[8] = {false};
+    const int id = (CORR ? 4 : 0) + (ls ? 2 : 0) + (dh ? 1 : 0);
+    if (!attr_set[id]) {
+        GPF_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL));
+        attr_set[id] = true;
+    }
+    k<<<grid, block, SM_TOTAL, s>>>(A);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+static int launch_finish(FvSolver& S, int nblk, int mode, int until_converged, cudaStream_t s) {
+    fv_finish_kernel<<<1, 256, 0, s>>>(S.P, S.st, S.partial, S.pflags, nblk, mode, until_converged, S.refresh);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+static int launch_reduce(FvSolver& S, cudaStream_t s) {
+    if (S.P.eos.kind == GPF_EOS_DH)
+        fv_reduce_kernel<GPF_EOS_DH><<<REDUCE_BLOCKS, 256, 0, s>>>(S.P, S.st, S.qtable, S.topo, S.partial, S.pflags);
+    else
+        fv_reduce_kernel<-1><<<REDUCE_BLOCKS, 256, 0, s>>>(S.P, S.st, S.qtable, S.topo, S.partial, S.pflags);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+int FvSolver::step(int n, int until_converged, cudaStream_t s) {
+    if (n < 0) { set_error("n < 0"); return GPF_E_INVALID; }
+    const int nblk = P.nblk_x * P.nblk_y;
+    if (timing) {
+        while ((int)ev.size() < 3 * n + 1) { cudaEvent_t e; GPF_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
+        ev_steps = n;
+        GPF_CUDA(cudaEventRecord(ev[0], s));
+    }
+    for (int it = 0; it < n; ++it) {
+        int rc;
+        if ((rc = launch_pass<false>(*this, until_converged, s))) return rc;
+        if (timing) GPF_CUDA(cudaEventRecord(ev[3 * it + 1], s));
+        if ((rc = launch_pass<true>(*this, until_converged, s))) return rc;
+        if (timing) GPF_CUDA(cudaEventRecord(ev[3 * it + 2], s));
+        if ((rc = launch_finish(*this, nblk, FIN_STEP, until_converged, s))) return rc;
+        if (timing) GPF_CUDA(cudaEventRecord(ev[3 * it + 3], s));
+    }
+    dirty_scalars = false;     // the corrector's reductions describe the new q
+    return GPF_OK;
+}
+
+int FvSolver::get_timing(double* ms_pred, double* ms_corr, long long* launches) {
+    double a = 0, b = 0;
+    if (timing && ev_steps > 0) {
+        GPF_CUDA(cudaEventSynchronize(ev[3 * ev_steps]));
+        for (int it = 0; it < ev_steps; ++it) {
+            float t;
+            GPF_CUDA(cudaEventElapsedTime(&t, ev[3 * it], ev[3 * it + 1])); a += t;
+            GPF_CUDA(cudaEventElapsedTime(&t, ev[3 * it + 1], ev[3 * it + 2])); b += t;
+        }
+        a /= ev_steps; b /= ev_steps;
+    }
+    if (ms_pred) *ms_pred = a;
+    if (ms_corr) *ms_corr = b;
+    if (launches) *launches = 3LL * ev_steps;
+    return GPF_OK;
+}
+
+int FvSolver::pre_run(int reset_ekin_old, cudaStream_t s) {
+    int rc;
+    if ((rc = launch_reduce(*this, s))) return rc;
+    if ((rc = launch_finish(*this, REDUCE_BLOCKS, reset_ekin_old ? FIN_PRERUN : FIN_PRERUN_KEEP_EKIN, 0, s))) return rc;
+    GPF_CUDA(cudaStreamSynchronize(s));
+    dirty_scalars = false;
+    return GPF_OK;
+}
+
+int FvSolver::refresh_scalars(cudaStream_t s) {
+    int rc;
+    if ((rc = launch_reduce(*this, s))) return rc;
+    return launch_finish(*this, REDUCE_BLOCKS, FIN_REFRESH, 0, s);
+}
+
+int FvSolver::fill_ghosts(cudaStream_t s) {
+    const int n = 2 * cfg.Nx + 2 * cfg.Ny;
+    fv_fill_ghosts_kernel<<<(n + 127) / 128, 128, 0, s>>>(P, st, qtable);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    dirty_scalars = true;
+    return GPF_OK;
+}
+
+int FvSolver::get_scalars(gpf_fv_scalars* o, cudaStream_t s) {
+    DevState h;
+    RefreshOut r;
+    if (dirty_scalars) {
+        int rc = refresh_scalars(s);
+        if (rc) return rc;
+        GPF_CUDA(cudaMemcpyAsync(&r, refresh, sizeof(r), cudaMemcpyDeviceToHost, s));
+    }
+    GPF_CUDA(cudaMemcpyAsync(&h, st, sizeof(h), cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    memset(o, 0, sizeof(*o));
+    o->step = h.step; o->simtime = h.simtime; o->dt = h.dt; o->residual = h.residual;
+    for (int k = 0; k < 5; ++k) o->residual_buffer[k] = h.resbuf[k];
+    o->residual_count = h.rescount;
+    o->ekin_old = h.ekin_old;
+    if (dirty_scalars) {
+        o->ekin = r.ekin; o->v_max = r.vmax; o->v_sound = r.vsound;
+        const double dxy = (cfg.dy < cfg.dx) ? cfg.dy : cfg.dx;
+        o->dt_crit = dxy / (r.vmax + r.vsound);
+        o->cfl = h.dt / o->dt_crit;
+    } else {
+        o->ekin = h.ekin; o->v_max = h.vmax; o->v_sound = h.vsound; o->dt_crit = h.dt_crit;
+        o->cfl = h.dt / h.dt_crit;
+    }
+    o->has_nan = h.has_nan; o->has_neg = h.has_neg; o->stop = h.stop; o->converged = h.converged;
+    return GPF_OK;
+}
+
+int FvSolver::set_scalars(const gpf_fv_scalars* in, cudaStream_t s) {
+    DevState h;
+    GPF_CUDA(cudaMemcpyAsync(&h, st, sizeof(h), cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    h.step = in->step; h.simtime = in->simtime; h.dt = in->dt; h.residual = in->residual;
+    h.rescount = in->residual_count < 1 ? 0 : (in->residual_count > 5 ? 5 : in->residual_count);
+    for (int k = 0; k < 5; ++k) h.resbuf[k] = in->residual_buffer[k];
+    h.ekin_old = in->ekin_old;
+    h.stop = in->stop;
+    int conv = 1;
+    for (int k = 0; k < h.rescount; ++k) conv &= (h.resbuf[k] < cfg.tol) ? 1 : 0;
+    h.converged = conv;
+    h.halt = (conv || h.step >= cfg.max_it || h.stop) ? 1 : 0;
+    GPF_CUDA(cudaMemcpyAsync(st, &h, sizeof(h), cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    return GPF_OK;
+}
+
+int FvSolver::mass(double* m, cudaStream_t s) {
+    int rc = refresh_scalars(s);
+    if (rc) return rc;
+    RefreshOut r;
+    GPF_CUDA(cudaMemcpyAsync(&r, refresh, sizeof(r), cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    *m = r.mass;
+    return GPF_OK;
+}
+
+int FvSolver::closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s) {
+    const size_t np = (size_t)(cfg.Nx + 2) * (cfg.Ny + 2);
+    double* d[4] = {p, wxz, wyz, bulk};
+    const int nc[4] = {1, 12, 12, 3};
+    double* tmp[4] = {nullptr, nullptr, nullptr, nullptr};
+    if (!on_device)
+        for (int k = 0; k < 4; ++k)
+            if (d[k]) GPF_CUDA(cudaMallocAsync(&tmp[k], nc[k] * np * 8, s));
+    double** o = on_device ? d : tmp;
+    const int blocks = (int)((np + 255) / 256);
+    const bool ls = P.has_extra != 0, dh = P.eos.kind == GPF_EOS_DH;
+    if (ls) { if (dh) fv_closures_kernel<true, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]);
+              else    fv_closures_kernel<true, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]); }
+    else    { if (dh) fv_closures_kernel<false, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]);
+              else    fv_closures_kernel<false, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]); }
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    if (!on_device) {
+        for (int k = 0; k < 4; ++k)
+            if (d[k]) {
+                GPF_CUDA(cudaMemcpyAsync(d[k], tmp[k], nc[k] * np * 8, cudaMemcpyDeviceToHost, s));
+                GPF_CUDA(cudaFreeAsync(tmp[k], s));
+            }
+        GPF_CUDA(cudaStreamSynchronize(s));
+    }
+    return GPF_OK;
+}
+
+int launch_eos(const gpf_fv_cfg& c, const double* dens, double* out, size_t n, bool sound, cudaStream_t s) {
+    EosParams e;
+    int rc = eos_pack(c, &e);
+    if (rc) return rc;
+    if (n == 0) return GPF_OK;
+    const int blocks = (int)((n + 255) / 256);
+    if (sound) eos_kernel<true><<<blocks, 256, 0, s>>>(e, dens, out, n);
+    else eos_kernel<false><<<blocks, 256, 0, s>>>(e, dens, out, n);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+int launch_stress(const gpf_fv_cfg& c, int which, const double* q, const double* h, const double* Ls,
+                  double* out, size_t n, cudaStream_t s) {
+    FvParams P;
+    gpf_fv_cfg c2 = c;
+    if (c2.Nx < 1) c2.Nx = 1;
+    if (c2.Ny < 1) c2.Ny = 1;
+    int rc = pack_params(c2, &P);
+    if (rc) return rc;
+    if (n == 0) return GPF_OK;
+    const int blocks = (int)((n + 255) / 256);
+    if (Ls) stress_kernel<true><<<blocks, 256, 0, s>>>(P.visc, which, q, h, Ls, out, n);
+    else stress_kernel<false><<<blocks, 256, 0, s>>>(P.visc, which, q, h, Ls, out, n);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+}  // namespace gpf

@@ -1,0 +1,76 @@
+// Internal types shared by the kernels and the C ABI (not part of the public header).
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/gapflow_b200.h"
+
+namespace gpf {
+
+// EOS parameters, pre-combined on the host in the reference's own (Python float)
+// operation order so device code only does the per-cell part.  See eos_pack() in api.cu.
+struct EosParams {
+    int kind;
+    double p[10];
+    double c[14];      // BWR temperature brackets
+};
+
+struct ViscParams {
+    double U, V, eta, zeta, v1, v2, two_eta, two_v2;
+};
+
+// boundary table (device copy of gpf_fv_cfg.bc_*)
+struct BcTable {
+    int type[4][3];
+    int src[4][3];
+    double val[4];
+};
+
+// tile geometry of the FV pass kernels
+constexpr int TX = 16;              // tile rows (x, slow axis)
+constexpr int TY = 64;              // tile cols (y, contiguous axis)
+constexpr int BX = TX + 1;          // staged rows  (one upwind/downwind halo row)
+constexpr int BY = TY + 2;          // staged cols  (halo col + one pad col: 16-byte box rule)
+constexpr int FV_THREADS = 256;
+
+// storage layout: plane-major, rows padded.  Cell (i, j) of the reference's padded array
+// (i in [0, Nx+1], j in [0, Ny+1]) lives at  comp*plane + i*pitch + (j + 1):
+// one pad column in front so interior rows start on a 16-byte boundary.
+struct Layout {
+    int Nx, Ny;
+    int pitch;          // doubles per row (multiple of 16)
+    int rows;           // allocated rows (>= Nx+2, >= BX)
+    size_t plane;       // doubles per component plane = rows*pitch
+};
+
+// device-resident loop state (one per solver); the finalize kernel advances it
+struct DevState {
+    long long step;
+    double simtime, dt;
+    double residual;
+    double resbuf[5];
+    int rescount;
+    double ekin, ekin_old, vmax, vsound, dt_crit, cfl;
+    int has_nan, has_neg, stop, converged;
+    int halt;           // run-loop condition false: later steps are no-ops
+    int cur;            // index of the buffer holding the current q (0..2)
+    int pad;
+};
+
+// per-block partial record written by reducing kernels, consumed by fv_finish_kernel
+struct Partial {
+    double ekin, vmax2, cs2, mass;
+};
+
+struct FvParams {
+    Layout L;
+    double dx, dy;
+    ViscParams visc;
+    EosParams eos;
+    BcTable bc;
+    double CFL, tol, dt0;
+    int adaptive, max_it, mc_order;
+    int has_extra;
+    int nblk_x, nblk_y;           // tile grid
+};
+
+}  // namespace gpf

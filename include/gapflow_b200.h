@@ -1,0 +1,175 @@
+/* gapflow_b200 -- C ABI of the B200-native GaPFlow hot path.
+ *
+ * GaPFlow (hannes-holey/GaPFlow) has no FFI or plugin interface: its hot path is Python
+ * methods on NumPy arrays.  Each entry point below states the reference interface it
+ * replaces (file:line relative to the GaPFlow repository).  INTEGRATION.md shows the
+ * ctypes binding a maintainer would add to the reference.
+ *
+ * Conventions
+ *  - plain C, no C++/torch types; every function returns 0 (GPF_OK) or a negative
+ *    GPF_E_* code; gpf_last_error() gives the text for the calling thread.
+ *  - "dense" arrays have the reference's layout: float64, C order,
+ *    shape (ncomp, Nx+2, Ny+2) (one ghost layer, GaPFlow/problem.py:122-124).
+ *  - `stream` arguments are cudaStream_t passed as void* (0 = legacy default stream).
+ *    Functions enqueue work on that stream and do not synchronise unless they return
+ *    host scalars (documented per function).
+ *  - a handle is bound to the CUDA device current at creation; not thread-safe.
+ */
+#ifndef GAPFLOW_B200_H
+#define GAPFLOW_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPF_OK 0
+#define GPF_E_INVALID (-1)     /* bad argument / unsupported configuration */
+#define GPF_E_CUDA (-2)        /* CUDA runtime or driver error             */
+#define GPF_E_NOMEM (-3)
+#define GPF_E_STATE (-4)       /* call sequence error                       */
+
+/* equation of state ids (GaPFlow/models/pressure.py:49-70) */
+enum { GPF_EOS_DH = 0, GPF_EOS_PL = 1, GPF_EOS_VDW = 2, GPF_EOS_MT = 3,
+       GPF_EOS_CUBIC = 4, GPF_EOS_BWR = 5, GPF_EOS_BAYADA = 6 };
+
+/* boundary kinds per side and component */
+enum { GPF_BC_P = 0, GPF_BC_D = 1, GPF_BC_N = 2, GPF_BC_HALO = 3 };
+/* sides: x0 = array index 0, x1 = index Nx+1, y0 = index 0, y1 = index Ny+1 */
+enum { GPF_SIDE_X0 = 0, GPF_SIDE_X1 = 1, GPF_SIDE_Y0 = 2, GPF_SIDE_Y1 = 3 };
+
+/* field ids for upload/download */
+enum { GPF_F_Q = 0, GPF_F_TOPO = 1, GPF_F_EXTRA = 2 };
+
+/* Problem description: the sanitised `grid`, `geometry`, `numerics`, `properties`
+ * dicts of GaPFlow/io.py:139-395, flattened. */
+typedef struct gpf_fv_cfg {
+    int32_t Nx, Ny;            /* interior cells of THIS rank's slab */
+    double dx, dy;
+    /* Boundary table.  Build it with gpf_fv_cfg_set_bc() from the reference's 12 mask
+     * lists; it encodes the reference's cross-lookups (GaPFlow/problem.py:676-768). */
+    int32_t bc_type[4][3];     /* GPF_BC_* per side, component            */
+    int32_t bc_src[4][3];      /* component whose adjacent value is used  */
+    double bc_val[4];          /* Dirichlet target per side               */
+    double U, V;               /* wall velocities (geometry)              */
+    double eta, zeta;          /* shear, bulk viscosity (properties)      */
+    int32_t eos;               /* GPF_EOS_*                               */
+    double eos_par[8];         /* DH: rho0,P0,C1,C2 | PL: rho0,P0,alpha | vdW: M,T,a,b |
+                                  MT: rho0,P0,K,n | cubic: a,b,c,d | BWR: T,gamma |
+                                  Bayada: rho_l,rho_v,c_l,c_v              */
+    double rho0;               /* initial density (properties['rho0'])    */
+    int32_t adaptive;          /* numerics['adaptive']                    */
+    double CFL, dt, tol;       /* numerics                                */
+    int32_t max_it, mc_order;  /* numerics['max_it'], numerics['MC_order'] */
+    int32_t has_extra;         /* 0: slip-length field identically zero   */
+    int32_t reserved[7];
+} gpf_fv_cfg;
+
+/* Host-visible scalars of the time loop (GaPFlow/problem.py:314-362, 571-586). */
+typedef struct gpf_fv_scalars {
+    int64_t step;              /* Problem.step                            */
+    double simtime, dt;        /* Problem.simtime, Problem.dt             */
+    double residual;           /* Problem.residual                        */
+    double residual_buffer[5]; /* Problem.residual_buffer (oldest first)  */
+    int32_t residual_count;    /* entries valid in residual_buffer        */
+    double ekin, ekin_old;     /* kinetic_energy (of current q), kinetic_energy_old */
+    double v_max, v_sound;     /* Problem.v_max, Problem.pressure.v_sound */
+    double dt_crit, cfl;
+    int32_t has_nan, has_neg;  /* q_has_nan, q_has_negative_density of the LAST attempted step */
+    int32_t stop;              /* Problem._stop (set by _finalize)        */
+    int32_t converged;         /* Problem.converged                       */
+} gpf_fv_scalars;
+
+typedef struct gpf_fv gpf_fv;  /* opaque solver handle */
+
+const char* gpf_last_error(void);
+int gpf_version(void);
+
+/* Fill cfg->bc_* from the reference's boolean masks (io.py:176-217).
+ * masks[s][k][c]: s in {xE,xW,yS,yN}, k in {P,D,N}, c component; d_val[s] = bc_<s>_D_val.
+ * Reproduces GaPFlow/problem.py:676-768 including its E/W and S/N cross-lookups.
+ * Returns GPF_E_INVALID for mask combinations on which the reference itself raises
+ * (shape mismatch) or leaves ghost cells undefined (mixed P / non-P on one side). */
+int gpf_fv_cfg_set_bc(gpf_fv_cfg* cfg, const uint8_t masks[4][3][3], const double d_val[4]);
+
+/* Device memory needed by a solver for cfg (bytes); the caller allocates it (e.g. a
+ * torch uint8 tensor) and keeps it alive for the handle's lifetime. */
+int gpf_fv_workspace_bytes(const gpf_fv_cfg* cfg, size_t* bytes);
+
+/* Replaces Problem.__init__/_initialize/_pre_run for the FV fields
+ * (GaPFlow/problem.py:77-152, 412-443, 662-670).  `workspace` is device memory.
+ * Fields start as _initialize leaves them; upload topography (and extra) next, then
+ * call gpf_fv_pre_run(). */
+int gpf_fv_create(const gpf_fv_cfg* cfg, void* workspace, size_t bytes, gpf_fv** out);
+int gpf_fv_destroy(gpf_fv* s);
+
+/* Dense (ncomp, Nx+2, Ny+2) float64 <-> solver storage.  ncomp: Q 3, TOPO 3 (h, dh/dx,
+ * dh/dy; a 4-component array may be passed with ncomp=4, comp 3 is ignored), EXTRA 1.
+ * `on_device` != 0: `data` is a device pointer.  Host pointers are copied with
+ * cudaMemcpyAsync on `stream` (pinned memory makes them asynchronous).
+ * Replaces direct writes to Problem.q / topo.full / extra (problem.py:314-317). */
+int gpf_fv_upload(gpf_fv* s, int field, const double* data, int ncomp, int on_device, void* stream);
+int gpf_fv_download(gpf_fv* s, int field, double* data, int ncomp, int on_device, void* stream);
+
+/* Problem._pre_run (problem.py:428-443): step=0, simtime=0, residual=1, residual
+ * buffer, dt = CFL*dt_crit or numerics['dt'];  also (re)computes kinetic_energy_old as
+ * _initialize does (problem.py:670) when reset_ekin_old != 0.  Synchronises. */
+int gpf_fv_pre_run(gpf_fv* s, int reset_ekin_old, void* stream);
+
+/* n x Problem.update() (problem.py:509-569) enqueued on `stream`, no synchronisation.
+ * until_converged != 0 reproduces the loop condition of Problem.run (problem.py:401):
+ * steps become no-ops on the device once converged, step >= max_it or _stop. */
+int gpf_fv_step(gpf_fv* s, int n, int until_converged, void* stream);
+
+/* Ghost-cell refresh of the current q: Problem._communicate_ghost_buffers
+ * (problem.py:676-707). */
+int gpf_fv_fill_ghosts(gpf_fv* s, void* stream);
+
+/* Reads the loop scalars (synchronises `stream`).  ekin, v_max, v_sound, dt_crit, cfl
+ * are those of the current q as the reference's properties would return them. */
+int gpf_fv_get_scalars(gpf_fv* s, gpf_fv_scalars* out, void* stream);
+/* Overwrites step/simtime/dt/residual(+buffer)/ekin_old/stop from `in` (host is
+ * authoritative, e.g. after a test assigned Problem.dt). */
+int gpf_fv_set_scalars(gpf_fv* s, const gpf_fv_scalars* in, void* stream);
+
+/* Problem.mass (problem.py:335-337); synchronises. */
+int gpf_fv_mass(gpf_fv* s, double* mass, void* stream);
+
+/* Closure fields of the current q as sol.nc stores them: pressure (1), wall_stress_xz
+ * (12), wall_stress_yz (12), bulk_viscous_stress (3); dense outputs, device or host.
+ * Replaces Pressure.update / WallStress.update / BulkStress.update
+ * (GaPFlow/models/stress.py:289-362, 427-459, 600-622).  NULL outputs are skipped. */
+int gpf_fv_closures(gpf_fv* s, double* pressure, double* wall_xz, double* wall_yz,
+                    double* bulk, int on_device, void* stream);
+
+/* One-call host-buffer step for reference-side bindings: uploads q_host (dense, host),
+ * runs n x update(), downloads q back, returns the scalars.  Synchronises. */
+int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, void* stream);
+
+/* --- pure functions (GaPFlow/models/*.py, GaPFlow/integrate.py); device pointers ---- */
+/* eos_pressure(density, prop) -> pressure.py:35;  eos_sound_velocity -> sound.py:35 */
+int gpf_eos_pressure(const gpf_fv_cfg* cfg, const double* dens, double* out, size_t n, void* stream);
+int gpf_eos_sound_velocity(const gpf_fv_cfg* cfg, const double* dens, double* out, size_t n, void* stream);
+/* stress_bottom / stress_top (6, n) and stress_avg (3, n), slip="top", dq=0
+ * (viscous.py:37, 281, 612).  q (3, n), h (3, n), Ls (n) or NULL. */
+int gpf_stress_bottom(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls,
+                      double* out, size_t n, void* stream);
+int gpf_stress_top(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls,
+                   double* out, size_t n, void* stream);
+int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls,
+                   double* out, size_t n, void* stream);
+
+/* --- instrumentation ------------------------------------------------------------- */
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+int64_t gpf_launch_count(void);
+/* average device time (ms) of the last gpf_fv_step() batch's predictor / corrector
+ * kernels measured with CUDA events on the launching stream; 0 if timing disabled */
+int gpf_fv_set_timing(gpf_fv* s, int enable);
+int gpf_fv_get_timing(gpf_fv* s, double* ms_predictor, double* ms_corrector, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GAPFLOW_B200_H */
