@@ -1,6 +1,8 @@
 // FV kernels + launchers.  Compile with -fmad=false (see closures.cuh).
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <string>
 #include <vector>
 #include "fv_pass.cuh"
 #include "fv_host.h"
@@ -62,7 +64,7 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
     const int i0 = 1 + blockIdx.y * TX;     // first interior row / col of the tile
     const int j0 = 1 + blockIdx.x * TY;
     const int ox = (d > 0) ? 1 : 0;         // own cells sit at box offset (ox, oy)
-    const int oy = ox;
+    constexpr int oy = 2;                   // box origin = own column - 2 (even -> 16-byte aligned)
 
     if (tid == 0) {
         mbar_init(bar, 1);
@@ -72,7 +74,7 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
     if (tid == 0) {
         const uint32_t bytes = (uint32_t)(3 * BOX * 8) * 2 + (LS ? (uint32_t)(BOX * 8) : 0u);
         mbar_expect_tx(bar, bytes);
-        const int cm = (j0 - oy) + 1;       // memory column of box origin
+        const int cm = (j0 - oy) + 1;       // memory column of box origin (j0 = 1 + 64k -> even)
         const int cx = i0 - ox;
         tma_load_3d(sq, &A.qmap[in_idx], bar, cm, cx, 0);
         tma_load_3d(stp, &A.topo_map, bar, cm, cx, 0);
@@ -133,7 +135,7 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
     if (tid < TY)
         phase1((d > 0) ? 0 : TX, tid + oy);                    // halo row
     else if (tid < TY + TX)
-        phase1(tid - TY + ox, (d > 0) ? 0 : TY);                // halo column
+        phase1(tid - TY + ox, (d > 0) ? oy - 1 : oy + TY);      // halo column
     __syncthreads();
 
     // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
@@ -498,6 +500,18 @@ __global__ void stress_kernel(ViscParams vp, int which, const double* q, const d
 // =====================================================================================
 std::atomic<long long> g_launches{0};
 
+// GPF_DEBUG_SYNC=1: synchronise after every launch and name the kernel that faulted
+static int debug_check(const char* name, cudaStream_t s) {
+    static const bool on = getenv("GPF_DEBUG_SYNC") != nullptr;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && on) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) {
+        set_error(std::string("CUDA error in kernel ") + name + ": " + cudaGetErrorString(e));
+        return GPF_E_CUDA;
+    }
+    return GPF_OK;
+}
+
 Layout make_layout(int Nx, int Ny) {
     Layout L;
     L.Nx = Nx; L.Ny = Ny;
@@ -808,15 +822,13 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
     }
     k<<<grid, block, SM_TOTAL, s>>>(A);
     g_launches++;
-    GPF_CUDA(cudaGetLastError());
-    return GPF_OK;
+    return debug_check(CORR ? "fv_pass_kernel<corrector>" : "fv_pass_kernel<predictor>", s);
 }
 
 static int launch_finish(FvSolver& S, int nblk, int mode, int until_converged, cudaStream_t s) {
     fv_finish_kernel<<<1, 256, 0, s>>>(S.P, S.st, S.partial, S.pflags, nblk, mode, until_converged, S.refresh);
     g_launches++;
-    GPF_CUDA(cudaGetLastError());
-    return GPF_OK;
+    return debug_check("fv_finish_kernel", s);
 }
 
 static int launch_reduce(FvSolver& S, cudaStream_t s) {

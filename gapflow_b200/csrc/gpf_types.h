@@ -29,7 +29,9 @@ struct BcTable {
 constexpr int TX = 16;              // tile rows (x, slow axis)
 constexpr int TY = 64;              // tile cols (y, contiguous axis)
 constexpr int BX = TX + 1;          // staged rows  (one upwind/downwind halo row)
-constexpr int BY = TY + 2;          // staged cols  (halo col + one pad col: 16-byte box rule)
+constexpr int BY = TY + 4;          // staged cols: 2 left + TY + 2 right.  TMA needs the box origin on a
+                                    // 16-byte boundary (even column) and a 16-byte multiple inner extent,
+                                    // so the halo column on either side comes with one pad column
 constexpr int FV_THREADS = 256;
 
 // storage layout: plane-major, rows padded.  Cell (i, j) of the reference's padded array

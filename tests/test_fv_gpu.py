@@ -67,9 +67,10 @@ def test_stress_functions_bit_exact_vs_reference_golden(gc, fn):
 def test_eos_functions_vs_reference_golden(gc):
     from gapflow_b200 import fv
     from oracle.make_golden import EOS_PROPS
-    # DH, vdW, cubic (x**3 via a correctly rounded product chain): exact.  PL, MT, BWR, Bayada call
-    # pow/exp/log whose CUDA implementations differ from glibc by <= 2 ulp: 1e-14 relative.
-    exact = {'DH', 'vdW', 'cubic'}
+    # DH, vdW use only + - * / sqrt: exact.  PL, MT, cubic, BWR, Bayada call pow/exp/log: NumPy itself
+    # dispatches those to CPU-specific SIMD routines (~1 ulp, e.g. x**3 != correctly rounded x^3 on
+    # 5 % of inputs on the build machine), so the reference is only defined to ~1e-15 there.
+    exact = {'DH', 'vdW'}
     for prop in EOS_PROPS:
         e = prop['EOS']
         d = dev(gc[f'dens_{e}'])
@@ -91,8 +92,9 @@ def test_step_vs_reference_golden(gs, name):
     s, o = make_solver(name)
     assert np.array_equal(s.get_q(), gs[f'{name}_q0'])
     sc = s.scalars()
-    assert sc.dt == float(gs[f'{name}_dt0'])
-    exact = STEP_CASES[name]['yaml'].find('EOS: DH') >= 0
+    exact = STEP_CASES[name]['yaml'].find('EOS: DH') >= 0     # BWR: pow/exp -> tolerance (see EOS test)
+    dt0 = float(gs[f'{name}_dt0'])
+    assert sc.dt == dt0 if exact else abs(sc.dt - dt0) <= 1e-12 * dt0
     for nsteps, tag in ((1, '1'), (2, '3')):
         s.step(nsteps)
         q = s.get_q()
