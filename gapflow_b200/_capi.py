@@ -77,6 +77,7 @@ SIGNATURES = {
     "gpf_stress_bottom": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
     "gpf_stress_top": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
     "gpf_stress_avg": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
+    "gpf_selftest_division": (_i, [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), _vp]),
 }
 
 _lib = None

@@ -185,4 +185,13 @@ int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
     GPF_TRY NEED(cfg && (n == 0 || (q && h && out))) return launch_stress(*cfg, 2, q, h, Ls, out, n, (cudaStream_t)stream); GPF_CATCH
 }
 
+int gpf_selftest_division(uint64_t n, uint64_t seed, uint64_t mismatches[2], void* stream) {
+    GPF_TRY NEED(mismatches)
+    unsigned long long o[2] = {0, 0};
+    int rc = launch_selftest_div(n, seed, o, (cudaStream_t)stream);
+    mismatches[0] = o[0]; mismatches[1] = o[1];
+    return rc;
+    GPF_CATCH
+}
+
 }  // extern "C"

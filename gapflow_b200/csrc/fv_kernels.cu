@@ -33,7 +33,74 @@ struct PassArgs {
     int until_converged;
 };
 
-template <bool CORR, bool LS, int EOS>
+
+// ---- per-cell arithmetic of the two phases (FAST: branch-free divisions, see closures.cuh) ----
+template <bool LS>
+__device__ __forceinline__ bool cell_in_fast_range(const Cell& c) {
+    bool ok = in_fast_range(c.q0) & in_fast_range(c.q1) & in_fast_range(c.q2) & in_fast_range(c.h) &
+              in_fast_range(c.hx) & in_fast_range(c.hy);
+    if (LS) ok &= in_fast_range(c.Ls);
+    return ok;
+}
+
+struct Clos4 { double p, t0, t1, t2; };
+
+template <bool LS, int EOS, bool FAST, bool XF>
+__device__ __forceinline__ Clos4 phase1_cell(const Cell& c, const FvParams& P) {
+    Clos4 r;
+    r.p = eos_pressure<EOS, FAST>(c.q0, P.eos);
+    stress_avg<LS, FAST, XF>(c, reinterpret_cast<const Visc&>(P.visc), r.t0, r.t1, r.t2);
+    return r;
+}
+template <bool LS, int EOS>
+__device__ __noinline__ Clos4 phase1_cell_slow(const Cell c, const FvParams& P) {
+    return phase1_cell<LS, EOS, false, false>(c, P);
+}
+
+struct Nb { double q1x, Ax, t2x, q2y, t2y, Cy; };   // neighbour fluxes: Fx = (q1, A, t2), Fy = (q2, t2, C)
+struct Q3 { double v0, v1, v2; };
+
+// fluxes (integrate.py:65-75), wall stresses (stress.py:328-362), source (integrate.py:118-128)
+// and the update q - dt*(fX/dx + fY/dy - src) (problem.py:558) of one interior cell.
+// flux = -d*(F[nb] - F[own]): the sign flip is exact and done on the integer pipe.  The xz + yz
+// field sums of problem.py:554-555 are u/2 + u/2 == u (exact) and u + 0.
+template <bool LS, bool FAST, bool XF>
+__device__ __forceinline__ Q3 phase2_cell(const Cell& c, const Clos4& k, const Nb& n, const FvParams& P,
+                                          unsigned sbit, double dt) {
+    const Visc& V = reinterpret_cast<const Visc&>(P.visc);
+    const double fx0 = flip(n.q1x - c.q1, sbit);
+    const double fx1 = flip(n.Ax - (k.p + k.t0), sbit);
+    const double fx2 = flip(n.t2x - k.t2, sbit);
+    const double fy0 = flip(n.q2y - c.q2, sbit);
+    const double fy1 = flip(n.t2y - k.t2, sbit);
+    const double fy2 = flip(n.Cy - (k.p + k.t1), sbit);
+    double b3, b4, u[6];
+    stress_bottom<LS, FAST, XF>(c, V, b3, b4);
+    stress_top<LS, false, FAST, XF>(c, V, u);
+    const double rh = rcp_sel<FAST>(c.h);
+    double s0, s1, s2;
+    if constexpr (XF) {      // hy == 0: the hy terms are exact zeros
+        s0 = div_sel<FAST>(-c.q1 * c.hx, c.h, rh);
+        s1 = div_sel<FAST>((k.t0 - u[0]) * c.hx + u[4] - b4, c.h, rh);
+        s2 = div_sel<FAST>((k.t2 - u[5]) * c.hx + u[3] - b3, c.h, rh);
+    } else {
+        s0 = div_sel<FAST>(-c.q1 * c.hx - c.q2 * c.hy, c.h, rh);
+        s1 = div_sel<FAST>((k.t0 - u[0]) * c.hx + (k.t2 - u[5]) * c.hy + u[4] - b4, c.h, rh);
+        s2 = div_sel<FAST>((k.t2 - u[5]) * c.hx + (k.t1 - u[1]) * c.hy + u[3] - b3, c.h, rh);
+    }
+    Q3 q;
+    q.v0 = c.q0 - dt * (div_sel<FAST>(fx0, P.dx, P.rdx) + div_sel<FAST>(fy0, P.dy, P.rdy) - s0);
+    q.v1 = c.q1 - dt * (div_sel<FAST>(fx1, P.dx, P.rdx) + div_sel<FAST>(fy1, P.dy, P.rdy) - s1);
+    q.v2 = c.q2 - dt * (div_sel<FAST>(fx2, P.dx, P.rdx) + div_sel<FAST>(fy2, P.dy, P.rdy) - s2);
+    return q;
+}
+template <bool LS>
+__device__ __noinline__ Q3 phase2_cell_slow(const Cell c, const Clos4 k, const Nb n, const FvParams& P,
+                                            unsigned sbit, double dt) {
+    return phase2_cell<LS, false, false>(c, k, n, P, sbit, dt);
+}
+
+template <bool CORR, bool LS, int EOS, bool XF>
 __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_constant__ PassArgs A) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -46,6 +113,7 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
     double* st2 = st1 + BOX;
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
     double* sred = reinterpret_cast<double*>(smem + SM_RED);
+    int* sbad = reinterpret_cast<int*>(smem + SM_BAR + 8);
 
     const FvParams& P = A.P;
     const DevState* st = A.st;
@@ -69,6 +137,7 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
     if (tid == 0) {
         mbar_init(bar, 1);
         fence_mbar_init();
+        *sbad = 0;
     }
     __syncthreads();
     if (tid == 0) {
@@ -87,19 +156,6 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
     const int Nx = P.L.Nx, Ny = P.L.Ny;
     const size_t plane = P.L.plane;
     const int pitch = P.L.pitch;
-
-    // corrector: fetch q0 (own cells only) while the TMA is in flight
-    double q0v[4][3];
-    if (CORR) {
-        const double* q0b = A.qbuf[cur];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int i = i0 + g * 4 + k, j = j0 + ty;
-            const bool ok = (i <= Nx) && (j <= Ny);
-#pragma unroll
-            for (int c = 0; c < 3; ++c) q0v[k][c] = ok ? q0b[c * plane + (size_t)i * pitch + (j + 1)] : 0.0;
-        }
-    }
 
     mbar_wait(bar, 0);
 
@@ -121,12 +177,17 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
         if (i > Nx + 1 || j > Ny + 1) return;
         const Cell c = load_cell(rb, cb);
         const int o = rb * BY + cb;
-        sp[o] = eos_pressure<EOS>(c.q0, P.eos);
-        double a, b, e;
-        stress_avg<LS>(c, reinterpret_cast<const Visc&>(P.visc), a, b, e);
-        st0[o] = a;
-        st1[o] = b;
-        st2[o] = e;
+        Clos4 k;
+        if (P.scalars_fast && cell_in_fast_range<LS>(c)) {
+            k = phase1_cell<LS, EOS, true, XF>(c, P);
+        } else {
+            k = phase1_cell_slow<LS, EOS>(c, P);
+            *sbad = 1;            // this tile takes the plain-division path in phase 2
+        }
+        sp[o] = k.p;
+        st0[o] = k.t0;
+        st1[o] = k.t1;
+        st2[o] = k.t2;
     };
 
     // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
@@ -141,13 +202,16 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
     // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
     double* qout = A.qbuf[out_idx];
     const double* q0b = A.qbuf[cur];
-    const Visc& V = reinterpret_cast<const Visc&>(P.visc);
-    const double sgn = (double)(-d);
+    // straight-line divisions are valid when every staged input, dt, dx and dy are in [2^-100, 2^100]
+    const bool fast = (*sbad == 0) && in_fast_range(dt) && (dt != 0.0) && P.scalars_fast;
+    const unsigned sbit = (d > 0) ? 0x80000000u : 0u;     // -d * x  ==  x with its sign bit flipped when d = +1
     Red red;
     red.ekin = 0.0;
     red.vmax2 = -INFINITY;
     red.cs2 = -INFINITY;
     red.flags = 0;
+    constexpr bool DEFER_C = CORR && (EOS == GPF_EOS_DH);
+    double rmax = -INFINITY;
 
 #pragma unroll 1
     for (int k = 0; k < 4; ++k) {
@@ -159,53 +223,43 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
         const int on_x = (rb - d) * BY + cb;     // neighbour the x-difference reaches to
         const int on_y = rb * BY + (cb - d);
         const Cell c = load_cell(rb, cb);
-        const double p = sp[o], t0 = st0[o], t1 = st1[o], t2 = st2[o];
-
-        // fluxes: integrate.py:65-75.  Fx = (jx, p + txx, txy), Fy = (jy, txy, p + tyy)
-        const double fx0 = sgn * (sq[BOX + on_x] - c.q1);
-        const double fx1 = sgn * ((sp[on_x] + st0[on_x]) - (p + t0));
-        const double fx2 = sgn * (st2[on_x] - t2);
-        const double fy0 = sgn * (sq[2 * BOX + on_y] - c.q2);
-        const double fy1 = sgn * (st2[on_y] - t2);
-        const double fy2 = sgn * ((sp[on_y] + st1[on_y]) - (p + t1));
-
-        // wall stresses (stress.py:328-362) and their xz + yz sums (problem.py:554-555)
-        double b3, b4, u[6];
-        stress_bottom<LS>(c, V, b3, b4);
-        stress_top<LS, false>(c, V, u);
-        const double up0 = u[0] / 2.0 + u[0] / 2.0;
-        const double up1 = u[1] / 2.0 + u[1] / 2.0;
-        const double up5 = u[5] / 2.0 + u[5] / 2.0;
-        // source: integrate.py:118-128
-        const double s0 = (-c.q1 * c.hx - c.q2 * c.hy) / c.h;
-        const double s1 = ((t0 - up0) * c.hx + (t2 - up5) * c.hy + u[4] - b4) / c.h;
-        const double s2 = ((t2 - up5) * c.hx + (t1 - up1) * c.hy + u[3] - b3) / c.h;
-
-        // problem.py:558
-        double qn[3];
-        qn[0] = c.q0 - dt * (fx0 / P.dx + fy0 / P.dy - s0);
-        qn[1] = c.q1 - dt * (fx1 / P.dx + fy1 / P.dy - s1);
-        qn[2] = c.q2 - dt * (fx2 / P.dx + fy2 / P.dy - s2);
-
+        if (CORR) {      // q0 of this cell is needed after the update: start pulling its lines now
+            const size_t a0 = (size_t)i * pitch + (j + 1);
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(q0b + a0));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(q0b + plane + a0));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(q0b + 2 * plane + a0));
+        }
+        Clos4 kk;
+        kk.p = sp[o]; kk.t0 = st0[o]; kk.t1 = st1[o]; kk.t2 = st2[o];
+        Nb nb;
+        nb.q1x = sq[BOX + on_x]; nb.Ax = sp[on_x] + st0[on_x]; nb.t2x = st2[on_x];
+        nb.q2y = sq[2 * BOX + on_y]; nb.t2y = st2[on_y]; nb.Cy = sp[on_y] + st1[on_y];
+        const Q3 qq = fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
+                           : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
+        double qn[3] = {qq.v0, qq.v1, qq.v2};
+        const double qs0 = qn[0], qs1 = qn[1], qs2 = qn[2];     // q** (before averaging)
         if (CORR) {
-            // validity is tested on the averaged array INCLUDING its averaged ghost cells
-            // (problem.py:563-565): ghost = (fill(q**) + ghost(q0)) / 2
-            for_each_ghost(P, i, j, qn, [&](int gi, int gj, const double* gv) {
-                const size_t a = (size_t)gi * pitch + (gj + 1);
-#pragma unroll
-                for (int cc = 0; cc < 3; ++cc) {
-                    const double av = (gv[cc] + q0b[cc * plane + a]) / 2.0;
-                    if (av != av) red.flags |= FLAG_NAN;
-                    if (cc == 0 && av < 0.0) red.flags |= FLAG_NEG;
-                }
-            });
-#pragma unroll
-            for (int cc = 0; cc < 3; ++cc) {
-                qn[cc] = (qn[cc] + q0v[k][cc]) / 2.0;
-                if (qn[cc] != qn[cc]) red.flags |= FLAG_NAN;
-            }
+            const size_t a0 = (size_t)i * pitch + (j + 1);
+            const double o0 = q0b[a0], o1 = q0b[plane + a0], o2 = q0b[2 * plane + a0];
+            qn[0] = (qn[0] + o0) * 0.5;                          // problem.py:563 ((q + q0)/2.0, exact)
+            qn[1] = (qn[1] + o1) * 0.5;
+            qn[2] = (qn[2] + o2) * 0.5;
+            if (qn[0] != qn[0] || qn[1] != qn[1] || qn[2] != qn[2]) red.flags |= FLAG_NAN;
             if (qn[0] < 0.0) red.flags |= FLAG_NEG;
-            red_accum<EOS>(red, qn, P.eos);
+            // kinetic energy and speed (problem.py:342, 347): w = (jx^2 + jy^2)/rho
+            const double num = qn[1] * qn[1] + qn[2] * qn[2];
+            const double w = (fast && in_fast_range(qn[0]) && in_fast_range(num))
+                                 ? div_fast(num, qn[0], rcp_fast(qn[0])) : num / qn[0];
+            red.ekin += w * 0.5;
+            if (!(w >= 0.0)) red.flags |= FLAG_VNAN;
+            red.vmax2 = fmax(red.vmax2, w);
+            if (DEFER_C) {
+                sq[o] = qn[0];        // own rho slot is dead now: park the new density for the max search
+                rmax = fmax(rmax, qn[0]);
+                if (!(qn[0] == qn[0])) rmax = qn[0];
+            } else {
+                red_accum_c<EOS>(red, qn[0], P.eos);
+            }
         }
 
         const size_t a = (size_t)i * pitch + (j + 1);
@@ -214,16 +268,36 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
         qout[2 * plane + a] = qn[2];
 
         // ghost cells derived from this cell (problem.py:560 / 576)
-        for_each_ghost(P, i, j, qn, [&](int gi, int gj, const double* gv) {
-            const size_t ga = (size_t)gi * pitch + (gj + 1);
-            qout[ga] = gv[0];
-            qout[plane + ga] = gv[1];
-            qout[2 * plane + ga] = gv[2];
-            if (CORR) red_accum<EOS>(red, gv, P.eos);
-        });
+        if ((i == 1) | (i == Nx) | (j == 1) | (j == Ny)) {
+            const Red br = boundary_cell<CORR, EOS>(P, i, j, qs0, qs1, qs2, qn[0], qn[1], qn[2], qout, q0b);
+            if (CORR) {
+                red.ekin += br.ekin;
+                red.vmax2 = fmax(red.vmax2, br.vmax2);
+                red.cs2 = fmax(red.cs2, br.cs2);
+                red.flags |= br.flags;
+            }
+        }
     }
 
     if (CORR) {
+        if (DEFER_C) {
+            // v_sound = max sqrt(dp/drho).  For Dowson-Higginson dp/drho = K/(C2*rho0 - rho)^2 rises
+            // monotonically with rho below the pole, by >= 7e-13 relative per 2^-40 relative step in
+            // rho (for rho >= rho0/2), while its 7-operation FP64 evaluation errs by < 1e-15.  So the
+            // cell that attains the maximum of the ROUNDED values lies within 2^-40 of the warp's
+            // maximum density: only those cells are evaluated -- the result is bit-identical to
+            // evaluating every cell.  Outside the proven range every cell is evaluated.
+            double wmax = warp_max(rmax);
+            const bool ok = (wmax >= 0.5 * P.eos.p[0]) && (wmax <= P.eos.p[4]);
+            const double thr = ok ? wmax * (1.0 - 0x1p-40) : -INFINITY;
+#pragma unroll 1
+            for (int k = 0; k < 4; ++k) {
+                const int r = g * 4 + k;
+                if (i0 + r > Nx || j0 + ty > Ny) continue;
+                const double rho = sq[(r + ox) * BY + ty + oy];
+                if (!(rho < thr)) red_accum_c<EOS>(red, rho, P.eos);
+            }
+        }
         // warp shuffles, then one record per block (deterministic order)
         double e = warp_sum(red.ekin);
         double vm = warp_max(red.vmax2);
@@ -546,6 +620,7 @@ static int eos_pack(const gpf_fv_cfg& c, EosParams* e) {
         e->p[4] = 0.99 * a[3] * a[0];
         e->p[5] = a[2] * a[0] * (a[3] - 1.0);
         e->p[6] = a[3] * a[0];
+        e->p[9] = 1.0 / a[0];                 // RN(1/rho0) for div_fast
         return GPF_OK;
     case GPF_EOS_PL:      // rho0, P0, alpha
         e->p[0] = a[0]; e->p[1] = a[1]; e->p[2] = a[2];
@@ -609,6 +684,7 @@ int pack_params(const gpf_fv_cfg& c, FvParams* P) {
     if (c.mc_order != 0 && c.mc_order != 1 && c.mc_order != -1) { set_error("MC_order must be -1, 0 or 1"); return GPF_E_INVALID; }
     P->L = make_layout(c.Nx, c.Ny);
     P->dx = c.dx; P->dy = c.dy;
+    P->rdx = 1.0 / c.dx; P->rdy = 1.0 / c.dy;     // RN reciprocals for div_fast
     ViscParams& v = P->visc;
     v.U = c.U; v.V = c.V; v.eta = c.eta; v.zeta = c.zeta;
     v.v1 = c.zeta + 4. / 3. * c.eta;          // Python: zeta + 4 / 3 * eta
@@ -632,12 +708,27 @@ int pack_params(const gpf_fv_cfg& c, FvParams* P) {
             P->bc.type[s][k] = t; P->bc.src[s][k] = c.bc_src[s][k];
         }
     }
+    {
+        auto okr = [](double x) { return x == 0.0 || (fabs(x) >= 0x1p-100 && fabs(x) < 0x1p100); };
+        bool ok = okr(c.dx) && c.dx != 0.0 && okr(c.dy) && c.dy != 0.0 && okr(v.U) && okr(v.V) && okr(v.eta) &&
+                  okr(v.zeta) && okr(v.v1) && okr(v.v2);
+        for (int k = 0; k < 10; ++k) ok = ok && okr(P->eos.p[k]);
+        P->scalars_fast = ok ? 1 : 0;
+    }
     P->CFL = c.CFL; P->tol = c.tol; P->dt0 = c.dt;
     P->adaptive = c.adaptive; P->max_it = c.max_it; P->mc_order = c.mc_order;
     P->has_extra = c.has_extra;
+    P->xflow = 0;                 // decided when the topography is uploaded
     P->nblk_y = (c.Nx + TX - 1) / TX;
     P->nblk_x = (c.Ny + TY - 1) / TY;
     return GPF_OK;
+}
+
+__global__ void any_nonzero_kernel(const double* plane, int pitch, int nx2, int ny2, int* flag) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)nx2 * ny2) return;
+    const int i = (int)(idx / ny2), j = (int)(idx % ny2);
+    if (plane[(size_t)i * pitch + (j + 1)] != 0.0) *flag = 1;
 }
 
 // ---- TMA descriptors ----------------------------------------------------------------
@@ -780,6 +871,19 @@ int FvSolver::upload(int field, const double* data, int ncomp, int on_device, cu
         GPF_CUDA(cudaMemcpy2DAsync(base + k * P.L.plane + 1, (size_t)P.L.pitch * 8, data + (size_t)k * Nx2 * Ny2,
                                    Ny2 * 8, Ny2 * 8, Nx2, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
     if (field == GPF_F_Q) dirty_scalars = true;
+    if (field == GPF_F_TOPO) {
+        // x-driven film specialisation: V == 0 and dh/dy == 0 everywhere (exact zeros drop out)
+        int* flag = reinterpret_cast<int*>(refresh);
+        GPF_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), s));
+        const size_t np = Nx2 * Ny2;
+        any_nonzero_kernel<<<(int)((np + 255) / 256), 256, 0, s>>>(topo + 2 * P.L.plane, P.L.pitch, (int)Nx2, (int)Ny2, flag);
+        g_launches++;
+        GPF_CUDA(cudaGetLastError());
+        int h = 1;
+        GPF_CUDA(cudaMemcpyAsync(&h, flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+        GPF_CUDA(cudaStreamSynchronize(s));
+        P.xflow = (h == 0 && cfg.V == 0.0) ? 1 : 0;
+    }
     return GPF_OK;
 }
 
@@ -812,10 +916,19 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
     const bool ls = S.P.has_extra != 0;
     const bool dh = S.P.eos.kind == GPF_EOS_DH;
     void (*k)(const PassArgs);
-    if (ls) k = dh ? fv_pass_kernel<CORR, true, GPF_EOS_DH> : fv_pass_kernel<CORR, true, -1>;
-    else    k = dh ? fv_pass_kernel<CORR, false, GPF_EOS_DH> : fv_pass_kernel<CORR, false, -1>;
-    static bool attr_set[8] = {false};
-    const int id = (CORR ? 4 : 0) + (ls ? 2 : 0) + (dh ? 1 : 0);
+    const bool xf = S.P.xflow != 0;
+    const int id = (CORR ? 8 : 0) + (ls ? 4 : 0) + (dh ? 2 : 0) + (xf ? 1 : 0);
+    switch (id & 7) {
+    case 0: k = fv_pass_kernel<CORR, false, -1, false>; break;
+    case 1: k = fv_pass_kernel<CORR, false, -1, true>; break;
+    case 2: k = fv_pass_kernel<CORR, false, GPF_EOS_DH, false>; break;
+    case 3: k = fv_pass_kernel<CORR, false, GPF_EOS_DH, true>; break;
+    case 4: k = fv_pass_kernel<CORR, true, -1, false>; break;
+    case 5: k = fv_pass_kernel<CORR, true, -1, true>; break;
+    case 6: k = fv_pass_kernel<CORR, true, GPF_EOS_DH, false>; break;
+    default: k = fv_pass_kernel<CORR, true, GPF_EOS_DH, true>; break;
+    }
+    static bool attr_set[16] = {false};
     if (!attr_set[id]) {
         GPF_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL));
         attr_set[id] = true;
@@ -1014,6 +1127,51 @@ int launch_stress(const gpf_fv_cfg& c, int which, const double* q, const double*
     else stress_kernel<false><<<blocks, 256, 0, s>>>(P.visc, which, q, h, Ls, out, n);
     g_launches++;
     GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+
+// ---- self-test of the branch-free reciprocal / quotient against the IEEE operations -------
+__global__ void selftest_div_kernel(unsigned long long n, unsigned long long seed, unsigned long long* out) {
+    unsigned long long bad_rcp = 0, bad_div = 0;
+    const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long s0 = seed ^ (tid * 0x9E3779B97F4A7C15ULL + 0x632BE59BD9B4E019ULL), s1 = seed + tid * 0xD1B54A32D192ED03ULL + 1;
+    auto next = [&]() {
+        unsigned long long a = s0, b = s1;
+        s0 = b; a ^= a << 23; s1 = a ^ b ^ (a >> 17) ^ (b >> 26);
+        return s1 + b;
+    };
+    auto draw = [&]() {
+        unsigned long long m = next() & ((1ULL << 52) - 1);
+        const unsigned mode = (unsigned)(next() % 6);
+        if (mode == 1) m &= ~((1ULL << (next() % 52)) - 1);       // trailing zeros
+        if (mode == 2) m |= ((1ULL << (next() % 52)) - 1);        // trailing ones
+        if (mode == 3) m = (1ULL << 52) - 1 - (next() & 0xFF);    // near all ones
+        if (mode == 4) m = next() & 0xFF;                         // near a power of two
+        const unsigned long long e = 1023ULL + (next() % 180) - 90;   // inside the fast range
+        const unsigned long long u = ((next() & 1ULL) << 63) | (e << 52) | m;
+        return __longlong_as_double((long long)u);
+    };
+    for (unsigned long long it = tid; it < n; it += (unsigned long long)gridDim.x * blockDim.x) {
+        const double a = draw(), b = draw();
+        const double y = rcp_fast(b);
+        if (y != __drcp_rn(b)) ++bad_rcp;
+        if (div_fast(a, b, y) != __ddiv_rn(a, b)) ++bad_div;
+    }
+    if (bad_rcp) atomicAdd(&out[0], bad_rcp);
+    if (bad_div) atomicAdd(&out[1], bad_div);
+}
+
+int launch_selftest_div(unsigned long long n, unsigned long long seed, unsigned long long* out_host, cudaStream_t s) {
+    unsigned long long* d;
+    GPF_CUDA(cudaMalloc(&d, 16));
+    GPF_CUDA(cudaMemsetAsync(d, 0, 16, s));
+    selftest_div_kernel<<<148 * 8, 256, 0, s>>>(n, seed, d);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    GPF_CUDA(cudaMemcpyAsync(out_host, d, 16, cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    GPF_CUDA(cudaFree(d));
     return GPF_OK;
 }
 

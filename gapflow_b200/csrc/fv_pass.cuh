@@ -58,6 +58,11 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
         : "memory");
 }
 
+// x with its sign bit XOR-ed (exact negation when sbit = 0x80000000), integer pipe
+__device__ __forceinline__ double flip(double x, unsigned sbit) {
+    return __hiloint2double(__double2hiint(x) ^ (int)sbit, __double2loint(x));
+}
+
 // ------------------------------ ghost cells ---------------------------------------
 // Ghost value of one side from the adjacent (or periodic image) cell's 3 components.
 // problem.py:761-768:  D: (target - 0.5*q + 0.0*0.0)/(0.5 - 0.0);  N: ((1-0.5)*q + 0.0*0.0)/(0.5-0.0)
@@ -120,15 +125,59 @@ struct Red {
 };
 constexpr int FLAG_NAN = 1, FLAG_NEG = 2, FLAG_VNAN = 4, FLAG_CNAN = 8;
 
-template <int EOS>
-__device__ __forceinline__ void red_accum(Red& r, const double v[3], const EosParams& e) {
+// kinetic energy and speed of one cell (problem.py:342, 347)
+__device__ __forceinline__ void red_accum_v(Red& r, const double v[3]) {
     const double w = (v[1] * v[1] + v[2] * v[2]) / v[0];
     r.ekin += w / 2.0;
-    const double c2 = eos_sound2<EOS>(v[0], e);
     if (!(w >= 0.0)) r.flags |= FLAG_VNAN;     // np.sqrt(negative) = NaN and np.max propagates it
-    if (!(c2 >= 0.0)) r.flags |= FLAG_CNAN;
     r.vmax2 = fmax(r.vmax2, w);
+}
+// squared sound speed of one cell (stress.py:539)
+template <int EOS>
+__device__ __forceinline__ void red_accum_c(Red& r, double rho, const EosParams& e) {
+    const double c2 = eos_sound2<EOS>(rho, e);
+    if (!(c2 >= 0.0)) r.flags |= FLAG_CNAN;
     r.cs2 = fmax(r.cs2, c2);
+}
+template <int EOS>
+__device__ __forceinline__ void red_accum(Red& r, const double v[3], const EosParams& e) {
+    red_accum_v(r, v);
+    red_accum_c<EOS>(r, v[0], e);
+}
+
+// Boundary cells only (kept out of line so the interior path stays in registers): writes the
+// ghost cells that derive from interior cell (i, j) and returns their share of the reductions.
+//   qs[3]: value after this pass (before averaging), qn[3]: value stored for the cell.
+// Corrector: validity is tested on the averaged array INCLUDING its averaged ghost cells
+// (problem.py:563-565): ghost = (fill(q**) + ghost(q0)) / 2.
+template <bool CORR, int EOS>
+__device__ __noinline__ Red boundary_cell(const FvParams& P, int i, int j, double s0, double s1, double s2,
+                                          double n0, double n1, double n2, double* qout, const double* q0b) {
+    Red r;
+    r.ekin = 0.0; r.vmax2 = -INFINITY; r.cs2 = -INFINITY; r.flags = 0;
+    const size_t plane = P.L.plane;
+    const int pitch = P.L.pitch;
+    if (CORR) {
+        const double qs[3] = {s0, s1, s2};
+        for_each_ghost(P, i, j, qs, [&](int gi, int gj, const double* gv) {
+            const size_t a = (size_t)gi * pitch + (gj + 1);
+#pragma unroll
+            for (int cc = 0; cc < 3; ++cc) {
+                const double av = (gv[cc] + q0b[cc * plane + a]) / 2.0;
+                if (av != av) r.flags |= FLAG_NAN;
+                if (cc == 0 && av < 0.0) r.flags |= FLAG_NEG;
+            }
+        });
+    }
+    const double qn[3] = {n0, n1, n2};
+    for_each_ghost(P, i, j, qn, [&](int gi, int gj, const double* gv) {
+        const size_t ga = (size_t)gi * pitch + (gj + 1);
+        qout[ga] = gv[0];
+        qout[plane + ga] = gv[1];
+        qout[2 * plane + ga] = gv[2];
+        if (CORR) red_accum<EOS>(r, gv, P.eos);
+    });
+    return r;
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

@@ -65,13 +65,15 @@ struct Partial {
 
 struct FvParams {
     Layout L;
-    double dx, dy;
+    double dx, dy, rdx, rdy;
     ViscParams visc;
     EosParams eos;
     BcTable bc;
     double CFL, tol, dt0;
     int adaptive, max_it, mc_order;
     int has_extra;
+    int xflow;                    // V == 0 and dh/dy == 0 everywhere (x-driven film)
+    int scalars_fast;             // dx, dy, viscosities, wall speeds, EOS parameters all in [2^-100, 2^100] or 0
     int nblk_x, nblk_y;           // tile grid
 };
 

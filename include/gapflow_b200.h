@@ -169,6 +169,11 @@ int64_t gpf_launch_count(void);
 int gpf_fv_set_timing(gpf_fv* s, int enable);
 int gpf_fv_get_timing(gpf_fv* s, double* ms_predictor, double* ms_corrector, int64_t* launches);
 
+/* Self-test: n seeded operand pairs (structured mantissas, |x| in [2^-90, 2^90]); counts where
+ * the kernels' branch-free reciprocal / quotient differ from the IEEE-754 operations
+ * (__drcp_rn, __ddiv_rn).  mismatches[0]: reciprocal, [1]: quotient.  Synchronises. */
+int gpf_selftest_division(uint64_t n, uint64_t seed, uint64_t mismatches[2], void* stream);
+
 #ifdef __cplusplus
 }
 #endif
