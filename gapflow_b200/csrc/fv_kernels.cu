@@ -101,7 +101,7 @@ __device__ __noinline__ Q3 phase2_cell_slow(const Cell c, const Clos4 k, const N
 }
 
 template <bool CORR, bool LS, int EOS, bool XF>
-__global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_constant__ PassArgs A) {
+__global__ void __launch_bounds__(FV_THREADS, FV_MIN_CTAS) fv_pass_kernel(const __grid_constant__ PassArgs A) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
     double* sq = reinterpret_cast<double*>(smem + SM_Q);
@@ -152,7 +152,8 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
 
     // own cells: column ty, rows g*4 .. g*4+3
     const int ty = tid & (TY - 1);
-    const int g = tid >> 6;
+    const int g = tid >> 6;                 // FV_THREADS / TY row groups of 4 rows each
+    static_assert(FV_THREADS / TY * 4 == TX && TY == 64, "thread-to-cell map assumes 4 rows per thread");
     const int Nx = P.L.Nx, Ny = P.L.Ny;
     const size_t plane = P.L.plane;
     const int pitch = P.L.pitch;
@@ -249,7 +250,7 @@ __global__ void __launch_bounds__(FV_THREADS, 2) fv_pass_kernel(const __grid_con
             // kinetic energy and speed (problem.py:342, 347): w = (jx^2 + jy^2)/rho
             const double num = qn[1] * qn[1] + qn[2] * qn[2];
             const double w = (fast && in_fast_range(qn[0]) && in_fast_range(num))
-                                 ? div_fast(num, qn[0], rcp_fast(qn[0])) : num / qn[0];
+                                 ? div_fast(num, qn[0], rcp_sel<true>(qn[0])) : num / qn[0];
             red.ekin += w * 0.5;
             if (!(w >= 0.0)) red.flags |= FLAG_VNAN;
             red.vmax2 = fmax(red.vmax2, w);
@@ -1154,7 +1155,7 @@ __global__ void selftest_div_kernel(unsigned long long n, unsigned long long see
     };
     for (unsigned long long it = tid; it < n; it += (unsigned long long)gridDim.x * blockDim.x) {
         const double a = draw(), b = draw();
-        const double y = rcp_fast(b);
+        const double y = rcp_sel<true>(b);      // the reciprocal the kernels use
         if (y != __drcp_rn(b)) ++bad_rcp;
         if (div_fast(a, b, y) != __ddiv_rn(a, b)) ++bad_div;
     }

@@ -26,13 +26,14 @@ struct BcTable {
 };
 
 // tile geometry of the FV pass kernels
-constexpr int TX = 16;              // tile rows (x, slow axis)
+constexpr int TX = 8;               // tile rows (x, slow axis)
 constexpr int TY = 64;              // tile cols (y, contiguous axis)
 constexpr int BX = TX + 1;          // staged rows  (one upwind/downwind halo row)
 constexpr int BY = TY + 4;          // staged cols: 2 left + TY + 2 right.  TMA needs the box origin on a
                                     // 16-byte boundary (even column) and a 16-byte multiple inner extent,
                                     // so the halo column on either side comes with one pad column
-constexpr int FV_THREADS = 256;
+constexpr int FV_THREADS = 128;     // 4 cells per thread
+constexpr int FV_MIN_CTAS = 4;      // resident CTAs per SM (54 KB of shared memory, 128 registers each)
 
 // storage layout: plane-major, rows padded.  Cell (i, j) of the reference's padded array
 // (i in [0, Nx+1], j in [0, Ny+1]) lives at  comp*plane + i*pitch + (j + 1):
