@@ -73,21 +73,31 @@ def slider_inputs(Nx, Ny):
     return config.read_yaml_string(SLIDER_YAML.format(Nx=Nx, Ny=Ny, Lx=0.0762 * Nx / Ny))
 
 
-def initial_fields(d, seed=1234):
-    """_initialize + the seeded perturbation (SURVEY 8(d) #2) + topography, host NumPy."""
+def initial_fields(d, seed=1234, rows=None):
+    """_initialize + the seeded perturbation + topography, host NumPy.
+
+    ``rows=(a, b)``: padded x-rows a..b-1 of the global field only (one rank's slab).  The
+    perturbation is drawn per global row from its own generator, so every decomposition sees
+    the same global field; ghost cells are filled by the solver afterwards."""
     import numpy as np
     from gapflow_b200.topography import make_topography
     g, geo, prop = d['grid'], d['geometry'], d['properties']
-    shape = (g['Nx'] + 2, g['Ny'] + 2)
+    a, b = rows if rows is not None else (0, g['Nx'] + 2)
+    shape = (b - a, g['Ny'] + 2)
     q = np.empty((3, *shape))
     q[0] = prop['rho0']
     q[1] = prop['rho0'] * geo['U'] / 2.0
     q[2] = prop['rho0'] * geo['V'] / 2.0
-    rng = np.random.default_rng(seed)
-    q[0] *= 1 + 1e-6 * rng.standard_normal(shape)
-    q[1] += 1e-3 * prop['rho0'] * geo['U'] * rng.standard_normal(shape)
-    q[2] += 1e-3 * prop['rho0'] * geo['U'] * rng.standard_normal(shape)
-    return q, make_topography(g, geo)
+    blk = 256                                           # rows per generator
+    for b0 in range(a // blk * blk, b, blk):
+        rng = np.random.default_rng([seed, b0 // blk])
+        n = rng.standard_normal((3, blk, shape[1]))
+        lo, hi = max(a, b0), min(b, b0 + blk)
+        sl, ns = slice(lo - a, hi - a), slice(lo - b0, hi - b0)
+        q[0, sl] *= 1 + 1e-6 * n[0, ns]
+        q[1, sl] += 1e-3 * prop['rho0'] * geo['U'] * n[1, ns]
+        q[2, sl] += 1e-3 * prop['rho0'] * geo['U'] * n[2, ns]
+    return q, make_topography(g, geo, rows=rows)
 
 
 class ClockSampler:
@@ -230,11 +240,17 @@ def run_gpu(args):
         q0, topo = initial_fields(d)
         solver = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo)
         solver.set_q(q0)
+        solver.fill_ghosts()
         solver.pre_run(False)
         step = solver.step
     else:
-        from gapflow_b200.dist import SlabSolver
-        solver = SlabSolver.from_global(d, initial_fields, rank, world)
+        from gapflow_b200.dist import SlabSolver, slab_rows
+        start, nloc = slab_rows(d['grid']['Nx'], world)[rank]
+        q0, topo = initial_fields(d, rows=(start, start + nloc + 2))
+        solver = SlabSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, q=q0,
+                            rank=rank, world=world)
+        solver.fill_ghosts()
+        solver.pre_run(False)
         step = solver.step
         q0 = None
     cells_per_step = n * n * world
@@ -283,22 +299,29 @@ def run_gpu(args):
                               "algorithmic_bytes_per_launch": per_gpu_cells * BYTES_PRED},
                 "step_frac_of_hbm_roofline": (value / world) * BYTES_PER_CELL_UPDATE / 1e9 / peak}
 
-    # ---- end to end through the host-buffer entry point (N=1) --------------------------------
-    e2e = None
-    if world == 1:
-        qh = torch.empty((3, n + 2, n + 2), dtype=torch.float64, pin_memory=True)
-        qh.copy_(torch.from_numpy(solver.get_q()))
-        k2 = max(3, min(args.steps, 10))
-        solver.update_host(qh, 1)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(k2):
-            solver.update_host(qh, 1)        # H2D q, update(), D2H q + scalars; synchronises
-        t1 = time.perf_counter()
-        nbytes = qh.numel() * 8
-        e2e = {"value": n * n * k2 / (t1 - t0), "unit": "cell-updates/s", "h2d_bytes_per_step": nbytes,
-               "d2h_bytes_per_step": nbytes + 160, "steps": k2,
-               "api": "gpf_fv_update_host (C ABI) via FVSolver.update_host, pinned host q"}
+    # ---- end to end through the host-buffer entry point ---------------------------------------
+    # every step: H2D of this rank's q from pinned host memory, update(), D2H of q (+ scalars)
+    qh = torch.empty((3, n + 2, n + 2), dtype=torch.float64, pin_memory=True)
+    qh.copy_(torch.from_numpy(solver.get_q()))
+    k2 = max(3, min(args.steps, 10))
+    solver.update_host(qh, 1)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(k2):
+        solver.update_host(qh, 1)            # synchronises
+    barrier()
+    t1 = time.perf_counter()
+    t_e2e = t1 - t0
+    if world > 1:
+        t = torch.tensor([t_e2e], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
+    nbytes = qh.numel() * 8 * world
+    e2e = {"value": cells_per_step * k2 / t_e2e, "unit": "cell-updates/s", "h2d_bytes_per_step": nbytes,
+           "d2h_bytes_per_step": nbytes + (160 if world == 1 else 0), "steps": k2,
+           "api": ("gpf_fv_update_host (C ABI) via FVSolver.update_host" if world == 1 else
+                   "SlabSolver.update_host (gpf_fv_upload / slab step / gpf_fv_download per rank)")
+                  + ", pinned host q, all ranks' bytes"}
 
     if rank == 0:
         cpu = None

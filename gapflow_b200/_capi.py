@@ -28,6 +28,7 @@ EOS_KEYS = {'DH': ['rho0', 'P0', 'C1', 'C2'], 'PL': ['rho0', 'P0', 'alpha'], 'vd
             'Bayada': ['rho_l', 'rho_v', 'c_l', 'c_v']}
 BC_P, BC_D, BC_N, BC_HALO = 0, 1, 2, 3
 F_Q, F_TOPO, F_EXTRA = 0, 1, 2
+FIN_STEP, FIN_PRERUN, FIN_PRERUN_KEEP_EKIN, FIN_REFRESH = 0, 1, 2, 3
 
 
 class FvCfg(C.Structure):
@@ -37,7 +38,7 @@ class FvCfg(C.Structure):
                 ("eos", C.c_int32), ("eos_par", C.c_double * 8), ("rho0", C.c_double),
                 ("adaptive", C.c_int32), ("CFL", C.c_double), ("dt", C.c_double), ("tol", C.c_double),
                 ("max_it", C.c_int32), ("mc_order", C.c_int32), ("has_extra", C.c_int32),
-                ("reserved", C.c_int32 * 7)]
+                ("halo_edge", C.c_int32 * 2), ("reserved", C.c_int32 * 5)]
 
 
 class FvScalars(C.Structure):
@@ -70,6 +71,11 @@ SIGNATURES = {
     "gpf_fv_mass": (_i, [_vp, C.POINTER(C.c_double), _vp]),
     "gpf_fv_closures": (_i, [_vp, _dp, _dp, _dp, _dp, _i, _vp]),
     "gpf_fv_update_host": (_i, [_vp, _dp, _i, C.POINTER(FvScalars), _vp]),
+    "gpf_fv_pass": (_i, [_vp, _i, _vp]),
+    "gpf_fv_halo_pack": (_i, [_vp, _i, _dp, _vp]),
+    "gpf_fv_halo_unpack": (_i, [_vp, _i, _dp, _vp]),
+    "gpf_fv_reduce_local": (_i, [_vp, _i, _dp, _vp]),
+    "gpf_fv_finish": (_i, [_vp, _i, _dp, _i, _vp]),
     "gpf_fv_set_timing": (_i, [_vp, _i]),
     "gpf_fv_get_timing": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "gpf_eos_pressure": (_i, [_cfgp, _dp, _dp, _sz, _vp]),
@@ -116,10 +122,11 @@ def check(rc):
         raise GapflowError(rc, load().gpf_last_error().decode())
 
 
-def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False)):
+def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), halo_edge=(False, False)):
     """Flatten the reference's sanitised dicts (GaPFlow/io.py:139-395) into gpf_fv_cfg.
 
-    ``halo=(lo, hi)`` marks x sides that are slab-internal (multi-GPU)."""
+    ``halo=(lo, hi)`` marks x sides whose ghost row comes from a neighbour rank (multi-GPU);
+    ``halo_edge`` marks those of them that are the global domain's periodic edge."""
     lib = load()
     c = FvCfg()
     c.Nx, c.Ny, c.dx, c.dy = grid['Nx'], grid['Ny'], grid['dx'], grid['dy']
@@ -136,6 +143,7 @@ def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False)):
         if h:
             for comp in range(3):
                 c.bc_type[s][comp] = BC_HALO
+            c.halo_edge[s] = 1 if halo_edge[s] else 0
     c.U, c.V = geo['U'], geo['V']
     c.eta, c.zeta = prop['shear'], prop['bulk']
     if prop['EOS'] not in EOS_IDS:

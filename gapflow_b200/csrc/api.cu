@@ -154,6 +154,21 @@ int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, vo
     return GPF_OK;
     GPF_CATCH
 }
+int gpf_fv_pass(gpf_fv* s, int corrector, void* stream) {
+    GPF_TRY NEED(s) return s->S.pass(corrector, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_halo_pack(gpf_fv* s, int rel, double* sendbuf, void* stream) {
+    GPF_TRY NEED(s && sendbuf) return s->S.halo_pack(rel, sendbuf, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_halo_unpack(gpf_fv* s, int rel, const double* recvbuf, void* stream) {
+    GPF_TRY NEED(s && recvbuf) return s->S.halo_unpack(rel, recvbuf, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_reduce_local(gpf_fv* s, int kind, double* rec5, void* stream) {
+    GPF_TRY NEED(s && rec5) return s->S.reduce_local(kind, rec5, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_finish(gpf_fv* s, int mode, const double* recs, int nrec, void* stream) {
+    GPF_TRY NEED(s) return s->S.finish(mode, recs, nrec, (cudaStream_t)stream); GPF_CATCH
+}
 int gpf_fv_set_timing(gpf_fv* s, int enable) {
     GPF_TRY NEED(s) s->S.timing = enable != 0; s->S.ev_steps = 0; return GPF_OK; GPF_CATCH
 }

@@ -40,6 +40,7 @@ struct FvSolver {
     int npartial;      // capacity of partial/pflags
     CUtensorMap qmap[3], topo_map, ls_map;
     bool dirty_scalars;   // q changed from the host since scalars were computed
+    bool refresh_valid;   // `refresh` holds the scalars of the current q (all ranks folded)
     double** qtable;      // device copy of qbuf[3]
     // timing
     bool timing;
@@ -59,6 +60,11 @@ struct FvSolver {
     int set_scalars(const gpf_fv_scalars* in, cudaStream_t s);
     int mass(double* m, cudaStream_t s);
     int closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s);
+    int pass(int corrector, cudaStream_t s);
+    int halo_pack(int rel, double* send, cudaStream_t s);
+    int halo_unpack(int rel, const double* recv, cudaStream_t s);
+    int reduce_local(int kind, double* rec5, cudaStream_t s);
+    int finish(int mode, const double* recs, int nrec, cudaStream_t s);
     int get_timing(double* ms_pred, double* ms_corr, long long* launches);
     double* field_ptr(int field, int* ncomp_max);
     int read_cur(cudaStream_t s, int* cur);

@@ -341,21 +341,36 @@ enum { FIN_STEP = 0, FIN_PRERUN = 1, FIN_PRERUN_KEEP_EKIN = 2, FIN_REFRESH = 3 }
 // Reduces the per-block records in a fixed order (deterministic), then thread 0 advances
 // the loop state the way Problem._post_update / _finalize / _pre_run do
 // (problem.py:571-610, 428-443).
+// Slab decomposition: `recs` (one Rec5 per rank, gathered in rank order) replaces the per-block
+// records, so every rank folds the same numbers in the same order and advances identically.
+// `rec_out` != nullptr: only fold this rank's per-block records into one Rec5 and return.
 __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ FvParams P, DevState* st,
                                                         const Partial* part, const int* pflags, int nblk,
-                                                        int mode, int until_converged, RefreshOut* ro) {
+                                                        int mode, int until_converged, RefreshOut* ro,
+                                                        const Rec5* recs, int nrec, Rec5* rec_out) {
     if (mode == FIN_STEP && (st->stop || (until_converged && st->halt))) return;
     __shared__ double sE[256], sV[256], sC[256], sM[256];
     __shared__ int sF[256];
     const int tid = threadIdx.x;
     double E = 0.0, VM = -INFINITY, CM = -INFINITY, M = 0.0;
     int F = 0;
-    for (int b = tid; b < nblk; b += 256) {
-        E += part[b].ekin;
-        M += part[b].mass;
-        VM = fmax(VM, part[b].vmax2);
-        CM = fmax(CM, part[b].cs2);
-        F |= pflags[b];
+    if (recs) {
+        if (tid == 0)
+            for (int r = 0; r < nrec; ++r) {      // rank order, sequential: identical on every rank
+                E += recs[r].ekin;
+                M += recs[r].mass;
+                VM = fmax(VM, recs[r].vmax2);
+                CM = fmax(CM, recs[r].cs2);
+                F |= (int)recs[r].flags;
+            }
+    } else {
+        for (int b = tid; b < nblk; b += 256) {
+            E += part[b].ekin;
+            M += part[b].mass;
+            VM = fmax(VM, part[b].vmax2);
+            CM = fmax(CM, part[b].cs2);
+            F |= pflags[b];
+        }
     }
     sE[tid] = E; sV[tid] = VM; sC[tid] = CM; sM[tid] = M; sF[tid] = F;
     __syncthreads();
@@ -371,6 +386,10 @@ __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ 
     }
     if (tid != 0) return;
     E = sE[0]; VM = sV[0]; CM = sC[0]; M = sM[0]; F = sF[0];
+    if (rec_out) {
+        rec_out->ekin = E; rec_out->vmax2 = VM; rec_out->cs2 = CM; rec_out->mass = M; rec_out->flags = (double)F;
+        return;
+    }
     const double qnan = nan("");
     // np.max propagates NaN (problem.py:347, stress.py:539)
     const double vmax = (F & FLAG_VNAN) ? qnan : sqrt(VM);
@@ -444,6 +463,9 @@ __global__ void __launch_bounds__(256) fv_reduce_kernel(const __grid_constant__ 
     for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
          idx += (size_t)gridDim.x * blockDim.x) {
         const int i = (int)(idx / Ny2), j = (int)(idx % Ny2);
+        // slab-internal halo rows are the neighbour rank's interior cells: counted there
+        if ((i == 0 && P.bc.type[0][0] == GPF_BC_HALO && !P.bc.edge[0]) ||
+            (i == Nx2 - 1 && P.bc.type[1][0] == GPF_BC_HALO && !P.bc.edge[1])) continue;
         const size_t a = (size_t)i * P.L.pitch + (j + 1);
         double v[3] = {q[a], q[plane + a], q[2 * plane + a]};
         if (v[0] != v[0] || v[1] != v[1] || v[2] != v[2]) red.flags |= FLAG_NAN;
@@ -491,6 +513,71 @@ __global__ void fv_fill_ghosts_kernel(const __grid_constant__ FvParams P, const 
         const size_t ga = (size_t)gi * P.L.pitch + (gj + 1);
         q[ga] = gv[0]; q[plane + ga] = gv[1]; q[2 * plane + ga] = gv[2];
     });
+}
+
+// Slab decomposition along x (no counterpart in the reference, whose _communicate_ghost_buffers
+// is a local copy, problem.py:676-707): rows 1 and Nx of buffer (cur + rel) % 3, y-ghost columns
+// included, to/from a contiguous [side][comp][Ny+2] buffer.  A neighbour's interior row with its
+// y ghosts filled is exactly what the reference's x-then-y fill order leaves in the x-ghost row.
+__global__ void fv_halo_pack_kernel(const __grid_constant__ FvParams P, const DevState* st, double* const* qbufs,
+                                    int rel, double* send) {
+    const double* q = qbufs[(st->cur + rel) % 3];
+    const int Ny2 = P.L.Ny + 2;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 6 * Ny2) return;
+    const int side = t / (3 * Ny2), c = (t / Ny2) % 3, j = t % Ny2;
+    const int i = side == 0 ? 1 : P.L.Nx;
+    send[t] = q[c * P.L.plane + (size_t)i * P.L.pitch + (j + 1)];
+}
+__global__ void fv_halo_unpack_kernel(const __grid_constant__ FvParams P, const DevState* st, double* const* qbufs,
+                                      int rel, const double* recv) {
+    double* q = qbufs[(st->cur + rel) % 3];
+    const int Ny2 = P.L.Ny + 2;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 6 * Ny2) return;
+    const int side = t / (3 * Ny2), c = (t / Ny2) % 3, j = t % Ny2;
+    if (P.bc.type[side][0] != GPF_BC_HALO) return;
+    const int i = side == 0 ? 0 : P.L.Nx + 1;
+    q[c * P.L.plane + (size_t)i * P.L.pitch + (j + 1)] = recv[t];
+}
+
+// Periodic-x ring: the global ghost rows (row 0 on the first rank, row Nx+1 on the last) belong
+// to the reference's padded array, so validity, kinetic energy and the maxima count them
+// (problem.py:320-347).  They arrive by exchange after the corrector pass; this folds them into
+// one extra per-block record (slot `slot`).  One block.
+template <int EOS>
+__global__ void __launch_bounds__(256) fv_edge_rows_kernel(const __grid_constant__ FvParams P, const DevState* st,
+                                                           double* const* qbufs, int rel, Partial* part, int* pflags,
+                                                           int slot) {
+    const double* q = qbufs[(st->cur + rel) % 3];
+    const int Ny2 = P.L.Ny + 2;
+    const size_t plane = P.L.plane;
+    Red red; red.ekin = 0.0; red.vmax2 = -INFINITY; red.cs2 = -INFINITY; red.flags = 0;
+    for (int side = 0; side < 2; ++side) {
+        if (!(P.bc.type[side][0] == GPF_BC_HALO && P.bc.edge[side])) continue;
+        const int i = side == 0 ? 0 : P.L.Nx + 1;
+        for (int j = threadIdx.x; j < Ny2; j += blockDim.x) {
+            const size_t a = (size_t)i * P.L.pitch + (j + 1);
+            double v[3] = {q[a], q[plane + a], q[2 * plane + a]};
+            if (v[0] != v[0] || v[1] != v[1] || v[2] != v[2]) red.flags |= FLAG_NAN;
+            if (v[0] < 0.0) red.flags |= FLAG_NEG;
+            red_accum<EOS>(red, v, P.eos);
+        }
+    }
+    __shared__ double sred[8 * 3];
+    __shared__ int sfl[8];
+    double e = warp_sum(red.ekin), vm = warp_max(red.vmax2), cm = warp_max(red.cs2);
+    int fl = red.flags;
+#pragma unroll
+    for (int oo = 16; oo > 0; oo >>= 1) fl |= __shfl_xor_sync(0xffffffffu, fl, oo);
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sred[w * 3] = e; sred[w * 3 + 1] = vm; sred[w * 3 + 2] = cm; sfl[w] = fl; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double E = 0.0, VM = -INFINITY, CM = -INFINITY; int F = 0;
+        for (int ww = 0; ww < 8; ++ww) { E += sred[ww * 3]; VM = fmax(VM, sred[ww * 3 + 1]); CM = fmax(CM, sred[ww * 3 + 2]); F |= sfl[ww]; }
+        part[slot].ekin = E; part[slot].vmax2 = VM; part[slot].cs2 = CM; part[slot].mass = 0.0; pflags[slot] = F;
+    }
 }
 
 // Closure fields as the reference stores them for sol.nc (stress.py:346-362, 452-459,
@@ -709,6 +796,7 @@ int pack_params(const gpf_fv_cfg& c, FvParams* P) {
             P->bc.type[s][k] = t; P->bc.src[s][k] = c.bc_src[s][k];
         }
     }
+    for (int s = 0; s < 2; ++s) P->bc.edge[s] = (c.bc_type[s][0] == GPF_BC_HALO && c.halo_edge[s]) ? 1 : 0;
     {
         auto okr = [](double x) { return x == 0.0 || (fabs(x) >= 0x1p-100 && fabs(x) < 0x1p100); };
         bool ok = okr(c.dx) && c.dx != 0.0 && okr(c.dy) && c.dy != 0.0 && okr(v.U) && okr(v.V) && okr(v.eta) &&
@@ -771,7 +859,7 @@ static const int REDUCE_BLOCKS = 148 * 8;
 size_t FvSolver::workspace_bytes(const gpf_fv_cfg& c) {
     Layout L = make_layout(c.Nx, c.Ny);
     size_t plane_b = align_up(L.plane * 8, 256);
-    int nb = ((c.Nx + TX - 1) / TX) * ((c.Ny + TY - 1) / TY);
+    int nb = ((c.Nx + TX - 1) / TX) * ((c.Ny + TY - 1) / TY) + 1;     // + the edge-row record
     if (nb < REDUCE_BLOCKS) nb = REDUCE_BLOCKS;
     size_t b = 0;
     b += 3 * 3 * plane_b;      // q x3 buffers
@@ -801,7 +889,7 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     extra = reinterpret_cast<double*>(p); p += plane_b;
     st = reinterpret_cast<DevState*>(p); p += align_up(sizeof(DevState), 256);
     refresh = reinterpret_cast<RefreshOut*>(p); p += align_up(sizeof(RefreshOut), 256);
-    npartial = P.nblk_x * P.nblk_y;
+    npartial = P.nblk_x * P.nblk_y + 1;
     if (npartial < REDUCE_BLOCKS) npartial = REDUCE_BLOCKS;
     partial = reinterpret_cast<Partial*>(p); p += align_up((size_t)npartial * sizeof(Partial), 256);
     pflags = reinterpret_cast<int*>(p); p += align_up((size_t)npartial * sizeof(int), 256);
@@ -827,6 +915,7 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     s0.dt = c.dt; s0.residual = 1.0; s0.resbuf[0] = 1.0; s0.rescount = 1;
     GPF_CUDA(cudaMemcpy(st, &s0, sizeof(s0), cudaMemcpyHostToDevice));
     dirty_scalars = true;
+    refresh_valid = false;
     timing = false;
     ev_steps = 0;
     return GPF_OK;
@@ -871,7 +960,7 @@ int FvSolver::upload(int field, const double* data, int ncomp, int on_device, cu
     for (int k = 0; k < ncmax; ++k)
         GPF_CUDA(cudaMemcpy2DAsync(base + k * P.L.plane + 1, (size_t)P.L.pitch * 8, data + (size_t)k * Nx2 * Ny2,
                                    Ny2 * 8, Ny2 * 8, Nx2, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
-    if (field == GPF_F_Q) dirty_scalars = true;
+    if (field == GPF_F_Q) { dirty_scalars = true; refresh_valid = false; }
     if (field == GPF_F_TOPO) {
         // x-driven film specialisation: V == 0 and dh/dy == 0 everywhere (exact zeros drop out)
         int* flag = reinterpret_cast<int*>(refresh);
@@ -939,8 +1028,10 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
     return debug_check(CORR ? "fv_pass_kernel<corrector>" : "fv_pass_kernel<predictor>", s);
 }
 
-static int launch_finish(FvSolver& S, int nblk, int mode, int until_converged, cudaStream_t s) {
-    fv_finish_kernel<<<1, 256, 0, s>>>(S.P, S.st, S.partial, S.pflags, nblk, mode, until_converged, S.refresh);
+static int launch_finish(FvSolver& S, int nblk, int mode, int until_converged, cudaStream_t s,
+                         const Rec5* recs = nullptr, int nrec = 0, Rec5* rec_out = nullptr) {
+    fv_finish_kernel<<<1, 256, 0, s>>>(S.P, S.st, S.partial, S.pflags, nblk, mode, until_converged, S.refresh,
+                                       recs, nrec, rec_out);
     g_launches++;
     return debug_check("fv_finish_kernel", s);
 }
@@ -973,6 +1064,57 @@ int FvSolver::step(int n, int until_converged, cudaStream_t s) {
         if (timing) GPF_CUDA(cudaEventRecord(ev[3 * it + 3], s));
     }
     dirty_scalars = false;     // the corrector's reductions describe the new q
+    return GPF_OK;
+}
+
+// ---- slab decomposition building blocks (gapflow_b200/dist.py drives them) ---------------
+int FvSolver::pass(int corrector, cudaStream_t s) {
+    return corrector ? launch_pass<true>(*this, 0, s) : launch_pass<false>(*this, 0, s);
+}
+
+int FvSolver::halo_pack(int rel, double* send, cudaStream_t s) {
+    if (rel < 0 || rel > 2) { set_error("rel must be 0, 1 or 2"); return GPF_E_INVALID; }
+    const int n = 6 * (cfg.Ny + 2);
+    fv_halo_pack_kernel<<<(n + 255) / 256, 256, 0, s>>>(P, st, qtable, rel, send);
+    g_launches++;
+    return debug_check("fv_halo_pack_kernel", s);
+}
+
+int FvSolver::halo_unpack(int rel, const double* recv, cudaStream_t s) {
+    if (rel < 0 || rel > 2) { set_error("rel must be 0, 1 or 2"); return GPF_E_INVALID; }
+    const int n = 6 * (cfg.Ny + 2);
+    fv_halo_unpack_kernel<<<(n + 255) / 256, 256, 0, s>>>(P, st, qtable, rel, recv);
+    g_launches++;
+    if (rel == 0) { dirty_scalars = true; refresh_valid = false; }
+    int rc = debug_check("fv_halo_unpack_kernel", s);
+    if (rc) return rc;
+    if (rel == 2 && (P.bc.edge[0] || P.bc.edge[1])) {
+        const int slot = P.nblk_x * P.nblk_y;
+        if (P.eos.kind == GPF_EOS_DH) fv_edge_rows_kernel<GPF_EOS_DH><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
+        else fv_edge_rows_kernel<-1><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
+        g_launches++;
+        rc = debug_check("fv_edge_rows_kernel", s);
+    }
+    return rc;
+}
+
+// kind 0: fold the records of the last corrector pass; kind 1: reduce the current q first
+int FvSolver::reduce_local(int kind, double* rec5, cudaStream_t s) {
+    int rc;
+    int nblk = P.nblk_x * P.nblk_y + ((P.bc.edge[0] || P.bc.edge[1]) ? 1 : 0);
+    if (kind == 1) {
+        if ((rc = launch_reduce(*this, s))) return rc;
+        nblk = REDUCE_BLOCKS;
+    }
+    return launch_finish(*this, nblk, FIN_REFRESH, 0, s, nullptr, 0, reinterpret_cast<Rec5*>(rec5));
+}
+
+int FvSolver::finish(int mode, const double* recs, int nrec, cudaStream_t s) {
+    if (mode < FIN_STEP || mode > FIN_REFRESH || !recs || nrec < 1) { set_error("bad finish arguments"); return GPF_E_INVALID; }
+    int rc = launch_finish(*this, 0, mode, 0, s, reinterpret_cast<const Rec5*>(recs), nrec);
+    if (rc) return rc;
+    if (mode != FIN_REFRESH) dirty_scalars = false;
+    else refresh_valid = true;
     return GPF_OK;
 }
 
@@ -1014,6 +1156,7 @@ int FvSolver::fill_ghosts(cudaStream_t s) {
     g_launches++;
     GPF_CUDA(cudaGetLastError());
     dirty_scalars = true;
+    refresh_valid = false;
     return GPF_OK;
 }
 
@@ -1021,8 +1164,10 @@ int FvSolver::get_scalars(gpf_fv_scalars* o, cudaStream_t s) {
     DevState h;
     RefreshOut r;
     if (dirty_scalars) {
-        int rc = refresh_scalars(s);
-        if (rc) return rc;
+        if (!refresh_valid) {      // slab mode: dist.py has already folded all ranks' records (finish(REFRESH))
+            int rc = refresh_scalars(s);
+            if (rc) return rc;
+        }
         GPF_CUDA(cudaMemcpyAsync(&r, refresh, sizeof(r), cudaMemcpyDeviceToHost, s));
     }
     GPF_CUDA(cudaMemcpyAsync(&h, st, sizeof(h), cudaMemcpyDeviceToHost, s));

@@ -23,6 +23,7 @@ struct BcTable {
     int type[4][3];
     int src[4][3];
     double val[4];
+    int edge[2];        // HALO x side whose ghost row is the global periodic ghost row (counted in reductions)
 };
 
 // tile geometry of the FV pass kernels
@@ -62,6 +63,11 @@ struct DevState {
 // per-block partial record written by reducing kernels, consumed by fv_finish_kernel
 struct Partial {
     double ekin, vmax2, cs2, mass;
+};
+
+// one rank's folded record, all-gathered between ranks (slab decomposition)
+struct Rec5 {
+    double ekin, vmax2, cs2, mass, flags;
 };
 
 struct FvParams {

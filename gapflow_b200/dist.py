@@ -1,0 +1,318 @@
+"""Slab decomposition of the FV step along x: one process per GPU, halo rows and loop scalars
+exchanged with ``torch.distributed`` (NCCL over NVLink on the GPUs, gloo in the CPU tests).
+
+The reference is single-process (GaPFlow/problem.py:122-124; its ``_communicate_ghost_buffers``,
+problem.py:676-707, is a local copy), so this module has no counterpart there.  What it
+must preserve is the reference's result: a rank's x-ghost row on a slab-internal side
+holds the neighbour's adjacent interior row *with its y ghosts filled* -- exactly what the
+reference's x-then-y fill order leaves there -- so ``q`` is bit-identical to the
+single-domain run for any number of ranks.  The loop scalars are folded from one
+5-double record per rank, gathered in rank order, so every rank advances ``dt`` identically
+(maxima are order-independent -> ``dt`` is bit-identical to the single-domain run; the
+kinetic-energy sum differs in the last bits, like any re-ordered sum).
+
+Per ``Problem.update()``: 2 passes x (1 neighbour exchange of 3*(Ny+2) doubles per side)
++ 1 all-gather of 5 doubles.  No data-path collective beyond that.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _capi
+
+
+def slab_rows(Nx, world):
+    """[(first interior row (0-based, global), rows)] per rank: as even as possible."""
+    base, rem = divmod(Nx, world)
+    out, start = [], 0
+    for r in range(world):
+        n = base + (1 if r < rem else 0)
+        out.append((start, n))
+        start += n
+    return out
+
+
+def x_periodic(grid):
+    """Periodicity of the x sides as the reference gates it (problem.py:681, 688)."""
+    e, w = all(grid['bc_xE_P']), all(grid['bc_xW_P'])
+    if e != w:
+        raise _capi.GapflowError(_capi.GPF_E_INVALID, "slab decomposition needs both x sides periodic or neither")
+    return e
+
+
+class HaloExchanger:
+    """Neighbour exchange of ``[2, ...]`` buffers: ``send[0]`` (first interior row) goes to the
+    lower neighbour, ``send[1]`` (last interior row) to the upper one; ``recv[0]`` comes from
+    the lower neighbour, ``recv[1]`` from the upper one.  Works on CPU (gloo) and CUDA (nccl)
+    tensors.  With 2 ranks on a ring both neighbours are the same peer: sends are posted
+    upper-first and receives lower-first so that the peer's messages pair up in order."""
+
+    def __init__(self, rank, world, periodic, group=None):
+        self.rank, self.world, self.group = rank, world, group
+        self.lo = rank - 1 if rank > 0 else (world - 1 if periodic and world > 1 else None)
+        self.hi = rank + 1 if rank < world - 1 else (0 if periodic and world > 1 else None)
+
+    def exchange(self, send, recv):
+        ops = []
+        if self.hi is not None:
+            ops.append(dist.P2POp(dist.isend, send[1], self.hi, self.group))
+        if self.lo is not None:
+            ops.append(dist.P2POp(dist.isend, send[0], self.lo, self.group))
+        if self.lo is not None:
+            ops.append(dist.P2POp(dist.irecv, recv[0], self.lo, self.group))
+        if self.hi is not None:
+            ops.append(dist.P2POp(dist.irecv, recv[1], self.hi, self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()          # CUDA: stream dependency only, the host does not block
+
+    def gather(self, rec, out):
+        """all-gather of one small record per rank into ``out[world, ...]`` (rank order)."""
+        if self.world == 1:
+            out.copy_(rec.reshape(out.shape))
+        else:
+            dist.all_gather_into_tensor(out.view(-1), rec.view(-1), group=self.group)
+
+
+def local_grid(grid, rank, world):
+    """This rank's grid dict: Nx, Lx of the slab; everything else global."""
+    start, n = slab_rows(grid['Nx'], world)[rank]
+    g = dict(grid)
+    g['Nx'] = n
+    g['Lx'] = grid['dx'] * n
+    return g, start
+
+
+class SlabSolver:
+    """One rank's slab of a global FV problem.  ``topo``/``q``/``extra`` are this rank's padded
+    rows ``start .. start+n+1`` of the global padded arrays (shape ``(ncomp, n+2, Ny+2)``)."""
+
+    def __init__(self, grid, geo, prop, numerics, topo, q=None, extra=None, rank=None, world=None, group=None,
+                 device=None, exchanger=None):
+        from .fv import FVSolver
+        self.rank = dist.get_rank(group) if rank is None else rank
+        self.world = dist.get_world_size(group) if world is None else world
+        self.grid_global = grid
+        per = x_periodic(grid)
+        self.ex = exchanger or HaloExchanger(self.rank, self.world, per, group)
+        g, self.row0 = local_grid(grid, self.rank, self.world)
+        if g['Nx'] < 1:
+            raise _capi.GapflowError(_capi.GPF_E_INVALID, "more ranks than grid rows")
+        halo = (self.ex.lo is not None, self.ex.hi is not None)
+        edge = (halo[0] and self.rank == 0, halo[1] and self.rank == self.world - 1)    # periodic ring ends
+        self.fv = FVSolver(g, geo, prop, numerics, topo=topo, extra=extra, device=device, halo=halo,
+                           halo_edge=edge)
+        self.lib, self.h = self.fv.lib, self.fv.h
+        dev = self.fv.device
+        Ny2 = g['Ny'] + 2
+        self.send = torch.zeros((2, 3, Ny2), dtype=torch.float64, device=dev)
+        self.recv = torch.zeros((2, 3, Ny2), dtype=torch.float64, device=dev)
+        self.rec = torch.zeros(5, dtype=torch.float64, device=dev)
+        self.recs = torch.zeros((self.world, 5), dtype=torch.float64, device=dev)
+        self._timing, self._ev = False, []
+        if exchanger is None:
+            # Problem.__init__ computes kinetic_energy_old on the _initialize state (problem.py:670)
+            self.pre_run(reset_ekin_old=True)
+            if q is not None:
+                self.set_q(q)
+                self.pre_run(reset_ekin_old=False)
+
+    # -- building blocks ---------------------------------------------------------------
+    def _s(self):
+        return self.fv._stream()
+
+    def set_q(self, q):
+        """this rank's padded slab (3, n+2, Ny+2) of the global padded q"""
+        self.fv.set_q(q)
+
+    # the five device-side phases (each enqueues on the current stream)
+    def _pass(self, corrector):
+        if self._timing:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        _capi.check(self.lib.gpf_fv_pass(self.h, corrector, self._s()))
+        if self._timing:
+            e1.record()
+            self._ev.append((corrector, e0, e1))
+
+    def _pack(self, rel):
+        _capi.check(self.lib.gpf_fv_halo_pack(self.h, rel, C.c_void_p(self.send.data_ptr()), self._s()))
+
+    def _unpack(self, rel):
+        _capi.check(self.lib.gpf_fv_halo_unpack(self.h, rel, C.c_void_p(self.recv.data_ptr()), self._s()))
+
+    def _record(self, kind):
+        _capi.check(self.lib.gpf_fv_reduce_local(self.h, kind, C.c_void_p(self.rec.data_ptr()), self._s()))
+
+    def _finish(self, mode):
+        _capi.check(self.lib.gpf_fv_finish(self.h, mode, C.c_void_p(self.recs.data_ptr()), self.world, self._s()))
+
+    def _exchange(self, rel):
+        """halo rows of buffer `rel` (0 current, 1 predictor output, 2 corrector output)"""
+        if self.world == 1:
+            return
+        self._pack(rel)
+        self.ex.exchange(self.send, self.recv)
+        self._unpack(rel)
+
+    def _fold(self, kind, mode):
+        self._record(kind)
+        self.ex.gather(self.rec, self.recs)
+        self._finish(mode)
+
+    # -- Problem-level operations ----------------------------------------------------------
+    def pre_run(self, reset_ekin_old=False):
+        """Problem._pre_run on the global field (problem.py:428-443)."""
+        self._fold(1, _capi.FIN_PRERUN if reset_ekin_old else _capi.FIN_PRERUN_KEEP_EKIN)
+
+    def fill_ghosts(self):
+        """_communicate_ghost_buffers (problem.py:676-707) across slabs: physical sides locally
+        (x first, then y), then the slab-internal rows."""
+        self.fv.fill_ghosts()
+        self._exchange(0)
+
+    def step(self, n=1):
+        """n x Problem.update() (problem.py:509-569); enqueues only."""
+        for _ in range(n):
+            self._pass(0)
+            self._exchange(1)
+            self._pass(1)
+            self._exchange(2)
+            self._fold(0, _capi.FIN_STEP)
+
+    def scalars(self):
+        self._fold(1, _capi.FIN_REFRESH)
+        return self.fv.scalars()
+
+    def update_host(self, q_host, n=1):
+        """Host-buffer step of this rank's slab: upload q_host (padded slab, pinned), n x update(),
+        download into q_host.  Loop scalars (dt, kinetic_energy_old) are kept, as in
+        gpf_fv_update_host."""
+        p, dev = C.c_void_p(q_host.data_ptr()), 0
+        _capi.check(self.lib.gpf_fv_upload(self.h, _capi.F_Q, p, 3, dev, self._s()))
+        self.step(n)
+        _capi.check(self.lib.gpf_fv_download(self.h, _capi.F_Q, p, 3, dev, self._s()))
+        torch.cuda.current_stream(self.fv.device).synchronize()
+
+    @property
+    def mass(self):
+        self._fold(1, _capi.FIN_REFRESH)
+        torch.cuda.current_stream(self.fv.device).synchronize()
+        return float(self.recs[:, 3].sum().item())
+
+    def get_q(self):
+        """this rank's padded slab (3, n+2, Ny+2)"""
+        return self.fv.get_q()
+
+    def gather_q(self):
+        """Global padded q on every rank (tests / output staging; host arrays)."""
+        loc = torch.from_numpy(self.get_q())
+        rows = slab_rows(self.grid_global['Nx'], self.world)
+        Ny2 = self.grid_global['Ny'] + 2
+        out = np.empty((3, self.grid_global['Nx'] + 2, Ny2))
+        parts = [None] * self.world
+        dist.all_gather_object(parts, loc.numpy(), group=self.ex.group)
+        for r, (start, n) in enumerate(rows):
+            lo = 0 if r == 0 else 1                      # physical ghost row only from the edge ranks
+            hi = n + 2 if r == self.world - 1 else n + 1
+            out[:, start + lo:start + hi] = parts[r][:, lo:hi]
+        return out
+
+    def set_timing(self, on):
+        """CUDA events (current stream) around every pass kernel launched from now on."""
+        self._timing, self._ev = bool(on), []
+
+    def timing(self):
+        """(mean predictor ms, mean corrector ms, launches timed)"""
+        torch.cuda.current_stream(self.fv.device).synchronize()
+        t = {0: [], 1: []}
+        for c, e0, e1 in self._ev:
+            t[c].append(e0.elapsed_time(e1))
+        mean = lambda v: sum(v) / len(v) if v else 0.0
+        return mean(t[0]), mean(t[1]), len(self._ev)
+
+    # -- construction from global host arrays (tests, small problems) -----------------------
+    @classmethod
+    def from_global(cls, d, q_global, topo_global, extra_global=None, rank=None, world=None, group=None, **kw):
+        rank = dist.get_rank(group) if rank is None else rank
+        world = dist.get_world_size(group) if world is None else world
+        start, n = slab_rows(d['grid']['Nx'], world)[rank]
+        sl = slice(start, start + n + 2)
+        ex = None if extra_global is None else np.ascontiguousarray(np.asarray(extra_global)[..., sl, :])
+        q = None if q_global is None else np.ascontiguousarray(q_global[:, sl])
+        return cls(d['grid'], d['geometry'], d['properties'], d['numerics'],
+                   topo=np.ascontiguousarray(topo_global[:, sl]), q=q,
+                   extra=ex, rank=rank, world=world, group=group, **kw)
+
+
+class InProcessSlabs:
+    """All ranks' slabs on ONE GPU in one process, driven phase by phase in lock step with plain
+    tensor copies in place of the NCCL calls.  Exercises every device-side piece of the slab path
+    (HALO sides, pack/unpack, per-rank records, gathered finish) where only one GPU is at hand."""
+
+    class _NoComm:
+        lo = hi = None
+        group = None
+
+    def __init__(self, d, q_global, topo_global, world, extra_global=None):
+        per = x_periodic(d['grid'])
+        self.world = world
+        self.s = []
+        rows = slab_rows(d['grid']['Nx'], world)
+        for r in range(world):
+            ex = HaloExchanger(r, world, per)          # neighbour table only; never communicates
+            self.s.append(SlabSolver.from_global(d, None, topo_global, extra_global, rank=r, world=world,
+                                                 exchanger=ex))
+        self.d = d
+        self._fold(1, _capi.FIN_PRERUN)                # kinetic_energy_old of the _initialize state
+        for r, (start, n) in enumerate(rows):
+            self.s[r].set_q(np.ascontiguousarray(q_global[:, start:start + n + 2]))
+        self._fold(1, _capi.FIN_PRERUN_KEEP_EKIN)
+
+    def _exchange(self, rel):
+        for s in self.s:
+            s._pack(rel)
+        for s in self.s:
+            if s.ex.lo is not None:
+                s.recv[0].copy_(self.s[s.ex.lo].send[1])
+            if s.ex.hi is not None:
+                s.recv[1].copy_(self.s[s.ex.hi].send[0])
+        for s in self.s:
+            s._unpack(rel)
+
+    def _fold(self, kind, mode):
+        for s in self.s:
+            s._record(kind)
+        recs = torch.stack([s.rec for s in self.s])
+        for s in self.s:
+            s.recs.copy_(recs)
+            s._finish(mode)
+
+    def step(self, n=1):
+        for _ in range(n):
+            for c, rel in ((0, 1), (1, 2)):
+                for s in self.s:
+                    s._pass(c)
+                self._exchange(rel)
+            self._fold(0, _capi.FIN_STEP)
+
+    def fill_ghosts(self):
+        for s in self.s:
+            s.fv.fill_ghosts()
+        self._exchange(0)
+
+    def scalars(self):
+        self._fold(1, _capi.FIN_REFRESH)
+        return [s.fv.scalars() for s in self.s]
+
+    def gather_q(self):
+        g = self.d['grid']
+        out = np.empty((3, g['Nx'] + 2, g['Ny'] + 2))
+        for r, (start, n) in enumerate(slab_rows(g['Nx'], self.world)):
+            loc = self.s[r].get_q()
+            lo = 0 if r == 0 else 1
+            hi = n + 2 if r == self.world - 1 else n + 1
+            out[:, start + lo:start + hi] = loc[:, lo:hi]
+        return out

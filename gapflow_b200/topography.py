@@ -7,10 +7,15 @@ reference's ``topography`` field: (4, Nx+2, Ny+2) = h, dh/dx, dh/dy, deformation
 import numpy as np
 
 
-def midpoint_grid(grid):
-    def axis(n, L):
-        return np.arange(-1, n + 1) / n * L + (L / n) / 2.
-    return np.meshgrid(axis(grid['Nx'], grid['Lx']), axis(grid['Ny'], grid['Ly']), indexing='ij')
+def midpoint_grid(grid, rows=None):
+    """Cell midpoints of the padded grid; ``rows=(a, b)`` keeps padded x-rows a..b-1 only
+    (a slab of the global grid: same element-wise arithmetic, so values are identical)."""
+    def axis(n, L, sl=None):
+        idx = np.arange(-1, n + 1)
+        if sl is not None:
+            idx = idx[sl[0]:sl[1]]
+        return idx / n * L + (L / n) / 2.
+    return np.meshgrid(axis(grid['Nx'], grid['Lx'], rows), axis(grid['Ny'], grid['Ly']), indexing='ij')
 
 
 def _journal(xx, yy, grid, geo):
@@ -65,8 +70,11 @@ _GENERATORS = {'journal': _journal, 'inclined': _inclined, 'parabolic': _parabol
                'asperity': _asperity}
 
 
-def make_topography(grid, geo):
-    xx, yy = midpoint_grid(grid)
+def make_topography(grid, geo, rows=None):
+    """``rows=(a, b)``: only padded x-rows a..b-1 of the global field (slab decomposition)."""
+    if rows is not None and (geo['type'] == 'asperity' or geo.get('flip', False)):
+        raise NotImplementedError("row-range generation needs a generator that is point-wise in x")
+    xx, yy = midpoint_grid(grid, rows)
     h, hx, hy = _GENERATORS[geo['type']](xx, yy, grid, geo)
     out = np.zeros((4, *h.shape))
     if geo.get('flip', False):

@@ -64,7 +64,10 @@ typedef struct gpf_fv_cfg {
     double CFL, dt, tol;       /* numerics                                */
     int32_t max_it, mc_order;  /* numerics['max_it'], numerics['MC_order'] */
     int32_t has_extra;         /* 0: slip-length field identically zero   */
-    int32_t reserved[7];
+    int32_t halo_edge[2];      /* GPF_BC_HALO x side that is the global domain's periodic edge: its
+                                  ghost row is part of the reference's padded array and is counted
+                                  in the reductions (problem.py:337-347) by this rank */
+    int32_t reserved[5];
 } gpf_fv_cfg;
 
 /* Host-visible scalars of the time loop (GaPFlow/problem.py:314-362, 571-586). */
@@ -147,6 +150,32 @@ int gpf_fv_closures(gpf_fv* s, double* pressure, double* wall_xz, double* wall_y
 /* One-call host-buffer step for reference-side bindings: uploads q_host (dense, host),
  * runs n x update(), downloads q back, returns the scalars.  Synchronises. */
 int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, void* stream);
+
+/* --- slab decomposition along x (multi-GPU) ---------------------------------------
+ * The reference runs on one process (problem.py:122-124; its _communicate_ghost_buffers,
+ * problem.py:676-707, is a local copy), so these have no counterpart there.  A rank's
+ * cfg has Nx = its slab's rows and GPF_BC_HALO on slab-internal x sides; gapflow_b200/dist.py
+ * drives one Problem.update() as
+ *   pass(0); halo_pack(1); <exchange>; halo_unpack(1);
+ *   pass(1); halo_pack(2); <exchange>; halo_unpack(2);
+ *   reduce_local(0); <all-gather of the 5-double records>; finish(GPF_FIN_STEP).
+ * All calls enqueue on `stream` and never synchronise. */
+enum { GPF_FIN_STEP = 0, GPF_FIN_PRERUN = 1, GPF_FIN_PRERUN_KEEP_EKIN = 2, GPF_FIN_REFRESH = 3 };
+/* one MacCormack pass (predictor: corrector = 0), problem.py:524-560 */
+int gpf_fv_pass(gpf_fv* s, int corrector, void* stream);
+/* rows 1 and Nx (y ghosts included) of buffer `rel` (0: current q, 1: predictor output, 2:
+ * corrector output) -> sendbuf[2][3][Ny+2] (device);  recvbuf[0] -> row 0, recvbuf[1] -> row
+ * Nx+1, HALO sides only. */
+int gpf_fv_halo_pack(gpf_fv* s, int rel, double* sendbuf, void* stream);
+int gpf_fv_halo_unpack(gpf_fv* s, int rel, const double* recvbuf, void* stream);
+/* this rank's record {sum ekin, max v^2, max c^2, mass, flags} (5 doubles, device):
+ * kind 0 folds the per-tile records of the last corrector pass, kind 1 reduces the current q
+ * (halo rows excluded; they are counted by the rank that owns them) */
+int gpf_fv_reduce_local(gpf_fv* s, int kind, double* rec5, void* stream);
+/* advances the loop state from `nrec` gathered records (device, rank order):
+ * _post_update / _finalize (GPF_FIN_STEP), _pre_run (GPF_FIN_PRERUN*), or only the scalars
+ * of the current q (GPF_FIN_REFRESH) */
+int gpf_fv_finish(gpf_fv* s, int mode, const double* recs, int nrec, void* stream);
 
 /* --- pure functions (GaPFlow/models/*.py, GaPFlow/integrate.py); device pointers ---- */
 /* eos_pressure(density, prop) -> pressure.py:35;  eos_sound_velocity -> sound.py:35 */

@@ -1,0 +1,81 @@
+"""CPU, world_size 2 and 3 over gloo: the slab partition, neighbour table, message pairing and
+rank-ordered scalar fold of gapflow_b200/dist.py reproduce the single-domain result
+bit-for-bit (q, dt) when they drive the NumPy oracle on slabs (tests/slab_oracle.py)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from gapflow_b200.dist import HaloExchanger, slab_rows
+from tests.cases import build_case, inputs
+
+NSTEPS = 4
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, name, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.slab_oracle import SlabOracle
+        d, extra = inputs(name)
+        ref = build_case(name)                     # every rank builds the same global start state
+        s = SlabOracle(d, ref.q, ref.topo, extra, rank, world)
+        dts = [s.dt]
+        for _ in range(NSTEPS):
+            s.update()
+            dts.append(s.dt)
+        q = s.gather_q(d['grid']['Nx'])
+        if rank == 0:
+            np.savez(out_path, q=q, dts=np.array(dts), ekin=s.kinetic_energy_old, step=s.step, res=s.residual)
+        else:
+            _ = s.kinetic_energy_old
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name,world", [("journal2d_periodic", 2), ("slider2d_xDN", 2), ("slider2d_allDN_slip", 3),
+                                        ("journal2d_flip_mc0", 2)])
+def test_slab_oracle_matches_single_domain(tmp_path, name, world):
+    out = str(tmp_path / "out.npz")
+    mp.spawn(_worker, args=(world, _free_port(), name, out), nprocs=world, join=True)
+    got = np.load(out)
+    ref = build_case(name)
+    dts = [ref.dt]
+    for _ in range(NSTEPS):
+        ref.update()
+        dts.append(ref.dt)
+    assert int(got['step']) == NSTEPS
+    assert np.array_equal(got['q'], ref.q), (name, np.abs(got['q'] - ref.q).max())
+    assert np.array_equal(got['dts'], np.array(dts))            # maxima are order-independent
+    assert abs(float(got['ekin']) - ref.kinetic_energy_old) <= 1e-13 * abs(ref.kinetic_energy_old)
+    assert abs(float(got['res']) - ref.residual) <= 1e-9 * abs(ref.residual) + 1e-14
+
+
+def test_slab_rows_cover_the_grid():
+    for Nx in (1, 7, 64, 100, 4097):
+        for w in (1, 2, 3, 8):
+            rows = slab_rows(Nx, w)
+            assert sum(n for _, n in rows) == Nx
+            assert rows[0][0] == 0 and all(rows[i][0] + rows[i][1] == rows[i + 1][0] for i in range(w - 1))
+            assert max(n for _, n in rows) - min(n for _, n in rows) <= 1
+
+
+def test_neighbour_table():
+    assert (HaloExchanger(0, 1, True).lo, HaloExchanger(0, 1, True).hi) == (None, None)
+    assert (HaloExchanger(0, 4, True).lo, HaloExchanger(0, 4, True).hi) == (3, 1)
+    assert (HaloExchanger(3, 4, True).lo, HaloExchanger(3, 4, True).hi) == (2, 0)
+    assert (HaloExchanger(0, 4, False).lo, HaloExchanger(3, 4, False).hi) == (None, None)
+    assert (HaloExchanger(1, 2, True).lo, HaloExchanger(1, 2, True).hi) == (0, 0)

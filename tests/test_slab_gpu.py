@@ -1,0 +1,114 @@
+"""GPU tests of the slab decomposition (gapflow_b200/dist.py).
+
+* one GPU: all ranks' slabs in one process, driven in lock step (InProcessSlabs) -- every
+  device-side piece of the multi-GPU path (HALO sides, pack/unpack, per-rank records, gathered
+  finish, ring-edge ghost rows) against the single-domain solver and the oracle;
+* >= 2 GPUs: the real thing, one process per GPU over NCCL (skipped on a 1-GPU box).
+
+q and dt must be bit-identical to the single-domain run for any number of ranks; the
+kinetic-energy sum is re-ordered (1e-13)."""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+from tests.cases import build_case, inputs  # noqa: E402
+from tests.test_fv_gpu import make_solver  # noqa: E402
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("name,world", [("journal2d_periodic", 2), ("journal2d_periodic", 3), ("slider2d_xDN", 2),
+                                        ("slider2d_allDN_slip", 3), ("journal2d_flip_mc0", 4),
+                                        ("journal2d_mcm1_bulk", 2)])
+def test_in_process_slabs_match_single_domain(name, world):
+    from gapflow_b200.dist import InProcessSlabs
+    d, extra = inputs(name)
+    o = build_case(name)
+    single, _ = make_solver(name, oracle=o)
+    slabs = InProcessSlabs(d, o.q, o.topo, world, extra_global=extra)
+    assert np.array_equal(slabs.gather_q(), o.q)
+    sc0 = slabs.scalars()
+    assert all(s.dt == single.scalars().dt for s in sc0)
+    for k in range(5):
+        o.update()
+        single.step(1)
+        slabs.step(1)
+        q = slabs.gather_q()
+        assert np.array_equal(q, single.get_q()), (name, world, k, int((q != single.get_q()).sum()))
+        assert np.array_equal(q, o.q)
+        ref = single.scalars()
+        for s in slabs.scalars():
+            assert s.dt == ref.dt == o.dt and s.step == ref.step
+            assert s.v_max == ref.v_max and s.v_sound == ref.v_sound
+            assert abs(s.ekin - ref.ekin) <= 1e-13 * abs(ref.ekin)
+            assert abs(s.residual - ref.residual) <= 1e-9 * abs(ref.residual) + 1e-14
+
+
+def test_in_process_slabs_invalid_step_stops_every_rank():
+    from gapflow_b200.dist import InProcessSlabs
+    name = "journal2d_periodic"
+    d, extra = inputs(name)
+    o = build_case(name)
+    slabs = InProcessSlabs(d, o.q, o.topo, 2)
+    slabs.step(1)
+    q1 = slabs.gather_q()
+    for s in slabs.s:
+        s.fv.set_scalars(dt=1e-3)
+    slabs.step(1)
+    for s in slabs.s:
+        sc = s.fv.scalars()
+        assert sc.stop == 1 and sc.step == 1
+    assert np.array_equal(slabs.gather_q(), q1)
+
+
+NCCL_WORKER = r"""
+import os, sys, numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+from tests.cases import build_case, inputs
+from gapflow_b200.dist import SlabSolver
+for name in ("journal2d_periodic", "slider2d_xDN", "slider2d_allDN_slip"):
+    d, extra = inputs(name)
+    o = build_case(name)
+    s = SlabSolver.from_global(d, o.q, o.topo, extra)
+    for k in range(6):
+        o.update()
+    s.step(6)
+    q = s.gather_q()
+    sc = s.scalars()
+    assert np.array_equal(q, o.q), (name, rank, int((q != o.q).sum()))
+    assert sc.dt == o.dt and sc.step == o.step, (name, sc.dt, o.dt)
+    assert abs(sc.ekin - o.kinetic_energy) <= 1e-13 * abs(o.kinetic_energy)
+    m = s.mass
+    assert abs(m - o.mass) <= 1e-12 * abs(o.mass)
+dist.barrier()
+if rank == 0:
+    print("NCCL_SLABS_OK")
+dist.destroy_process_group()
+"""
+
+
+def test_nccl_slabs_match_oracle(tmp_path):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(n, 4)
+    script = tmp_path / "worker.py"
+    script.write_text(NCCL_WORKER)
+    sock = socket.socket()
+    sock.bind(("127.0.0.1", 0))
+    port = sock.getsockname()[1]
+    sock.close()
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), ROOT],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0 and "NCCL_SLABS_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
