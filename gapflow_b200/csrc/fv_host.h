@@ -38,7 +38,8 @@ struct FvSolver {
     int* pflags;
     RefreshOut* refresh;
     int npartial;      // capacity of partial/pflags
-    CUtensorMap qmap[3], topo_map, ls_map;
+    CUtensorMap qmap[3], q0map[3], topo_map, topo2_map, ls_map;
+    int topo_fast, ls_fast;   // range flags of the uploaded topography / slip length (see FvParams::static_fast)
     bool dirty_scalars;   // q changed from the host since scalars were computed
     bool refresh_valid;   // `refresh` holds the scalars of the current q (all ranks folded)
     double** qtable;      // device copy of qbuf[3]

@@ -9,38 +9,51 @@
 
 namespace gpf {
 
-// shared-memory carve-up of the pass kernel (all TMA destinations 128-byte aligned)
+// ---- shared-memory carve-up of the pass kernel (every TMA destination 128-byte aligned) -------
 constexpr int BOX = BX * BY;                                    // doubles per staged plane
-constexpr size_t BOX3_BYTES = ((size_t)3 * BOX * 8 + 127) / 128 * 128;
-constexpr size_t BOX1_BYTES = ((size_t)BOX * 8 + 127) / 128 * 128;
-constexpr size_t SM_Q = 0;
-constexpr size_t SM_TOPO = SM_Q + BOX3_BYTES;
-constexpr size_t SM_LS = SM_TOPO + BOX3_BYTES;
-constexpr size_t SM_CLOS = SM_LS + BOX1_BYTES;                  // p, t0, t1, t2
-constexpr size_t SM_BAR = SM_CLOS + (size_t)4 * BOX * 8;
-constexpr size_t SM_RED = SM_BAR + 16;
-constexpr size_t SM_TOTAL = SM_RED + 8 * 4 * 8 + 128;           // + alignment slack
+constexpr size_t al128(size_t x) { return (x + 127) / 128 * 128; }
+constexpr size_t BOX3_BYTES = al128((size_t)3 * BOX * 8);
+constexpr size_t BOX2_BYTES = al128((size_t)2 * BOX * 8);
+constexpr size_t BOX1_BYTES = al128((size_t)BOX * 8);
+constexpr size_t OWN3_BYTES = (size_t)3 * TX * TY * 8;          // q0 of the tile's own cells (corrector)
+constexpr int NSTAGE = 2;                                       // TMA ring depth
+
+template <bool CORR, bool LS, bool XF>
+struct Smem {
+    static constexpr size_t Q = 0;
+    static constexpr size_t TOPO = Q + BOX3_BYTES;
+    static constexpr size_t LSO = TOPO + (XF ? BOX2_BYTES : BOX3_BYTES);    // x-driven film: dh/dy plane not loaded
+    static constexpr size_t Q0 = LSO + (LS ? BOX1_BYTES : 0);
+    static constexpr size_t STAGE = Q0 + (CORR ? OWN3_BYTES : 0);
+    static constexpr size_t CLOS = NSTAGE * STAGE;              // p, t0, t1, t2 of the staged cells
+    static constexpr size_t BAR = CLOS + al128((size_t)4 * BOX * 8);
+    static constexpr size_t RED = BAR + 128;                    // 2 mbarriers, 2 tile flags
+    static constexpr size_t TOTAL = RED + (FV_THREADS / 32) * 4 * 8;
+    static constexpr uint32_t TX_BYTES = (uint32_t)(3 * BOX * 8) + (uint32_t)((XF ? 2 : 3) * BOX * 8) +
+                                         (LS ? (uint32_t)(BOX * 8) : 0u) + (CORR ? (uint32_t)OWN3_BYTES : 0u);
+};
 
 struct PassArgs {
-    CUtensorMap qmap[3];
-    CUtensorMap topo_map;
-    CUtensorMap ls_map;
+    CUtensorMap qmap[3];       // box (BY, BX, 3) of each rotating q buffer
+    CUtensorMap q0map[3];      // box (TY, TX, 3): own cells only
+    CUtensorMap topo_map;      // box (BY, BX, 3)
+    CUtensorMap topo2_map;     // box (BY, BX, 2): h, dh/dx
+    CUtensorMap ls_map;        // box (BY, BX, 1)
     FvParams P;
     double* qbuf[3];
     DevState* st;
     Partial* partial;
     int* pflags;
     int until_converged;
+    int ntiles;
 };
 
-
 // ---- per-cell arithmetic of the two phases (FAST: branch-free divisions, see closures.cuh) ----
-template <bool LS>
-__device__ __forceinline__ bool cell_in_fast_range(const Cell& c) {
-    bool ok = in_fast_range(c.q0) & in_fast_range(c.q1) & in_fast_range(c.q2) & in_fast_range(c.h) &
-              in_fast_range(c.hx) & in_fast_range(c.hy);
-    if (LS) ok &= in_fast_range(c.Ls);
-    return ok;
+// The straight-line quotients need every operand in [2^-100, 2^100] (jx, jy may also be exactly 0).
+// Topography, slip length and the scalar parameters are checked once when they are uploaded
+// (FvParams::static_fast); the solution is checked here, per staged cell, on the integer pipe.
+__device__ __forceinline__ bool q_in_fast_range(const Cell& c) {
+    return in_fast_range_nz(c.q0) & in_fast_range(c.q1) & in_fast_range(c.q2);
 }
 
 struct Clos4 { double p, t0, t1, t2; };
@@ -100,20 +113,28 @@ __device__ __noinline__ Q3 phase2_cell_slow(const Cell c, const Clos4 k, const N
     return phase2_cell<LS, false, false>(c, k, n, P, sbit, dt);
 }
 
+// exact flags of one stored cell, off the hot path (problem.py:320-332)
+__device__ __noinline__ int cell_flags_slow(double a, double b, double c, double w) {
+    int f = 0;
+    if (a != a || b != b || c != c) f |= FLAG_NAN;
+    if (a < 0.0) f |= FLAG_NEG;
+    if (!(w >= 0.0)) f |= FLAG_VNAN;
+    return f;
+}
+
+// Persistent kernel: fv_ctas_per_sm(CORR) CTAs per SM walk the tiles round-robin.  A 2-deep ring of
+// TMA-staged boxes keeps the loads of tile n+1 in flight under the arithmetic of tile n.
 template <bool CORR, bool LS, int EOS, bool XF>
-__global__ void __launch_bounds__(FV_THREADS, FV_MIN_CTAS) fv_pass_kernel(const __grid_constant__ PassArgs A) {
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-    double* sq = reinterpret_cast<double*>(smem + SM_Q);
-    double* stp = reinterpret_cast<double*>(smem + SM_TOPO);
-    double* sls = reinterpret_cast<double*>(smem + SM_LS);
-    double* sp = reinterpret_cast<double*>(smem + SM_CLOS);
-    double* st0 = sp + BOX;
-    double* st1 = st0 + BOX;
-    double* st2 = st1 + BOX;
-    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + SM_BAR);
-    double* sred = reinterpret_cast<double*>(smem + SM_RED);
-    int* sbad = reinterpret_cast<int*>(smem + SM_BAR + 8);
+__global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kernel(const __grid_constant__ PassArgs A) {
+    using S = Smem<CORR, LS, XF>;
+    extern __shared__ __align__(1024) unsigned char smem[];      // no static shared memory: offset 0
+    double* const sp = reinterpret_cast<double*>(smem + S::CLOS);
+    double* const st0 = sp + BOX;
+    double* const st1 = st0 + BOX;
+    double* const st2 = st1 + BOX;
+    uint64_t* const bar = reinterpret_cast<uint64_t*>(smem + S::BAR);
+    int* const sbad = reinterpret_cast<int*>(smem + S::BAR + 32);
+    double* const sred = reinterpret_cast<double*>(smem + S::RED);
 
     const FvParams& P = A.P;
     const DevState* st = A.st;
@@ -128,178 +149,200 @@ __global__ void __launch_bounds__(FV_THREADS, FV_MIN_CTAS) fv_pass_kernel(const 
     const int sw = (P.mc_order == 0) ? (((st->step & 1LL) == 0) ? 1 : -1) : P.mc_order;
     const int d = CORR ? -sw : sw;
     const double dt = st->dt;
-
-    const int i0 = 1 + blockIdx.y * TX;     // first interior row / col of the tile
-    const int j0 = 1 + blockIdx.x * TY;
     const int ox = (d > 0) ? 1 : 0;         // own cells sit at box offset (ox, oy)
     constexpr int oy = 2;                   // box origin = own column - 2 (even -> 16-byte aligned)
-
-    if (tid == 0) {
-        mbar_init(bar, 1);
-        fence_mbar_init();
-        *sbad = 0;
-    }
-    __syncthreads();
-    if (tid == 0) {
-        const uint32_t bytes = (uint32_t)(3 * BOX * 8) * 2 + (LS ? (uint32_t)(BOX * 8) : 0u);
-        mbar_expect_tx(bar, bytes);
-        const int cm = (j0 - oy) + 1;       // memory column of box origin (j0 = 1 + 64k -> even)
-        const int cx = i0 - ox;
-        tma_load_3d(sq, &A.qmap[in_idx], bar, cm, cx, 0);
-        tma_load_3d(stp, &A.topo_map, bar, cm, cx, 0);
-        if (LS) tma_load_3d(sls, &A.ls_map, bar, cm, cx, 0);
-    }
-
-    // own cells: column ty, rows g*4 .. g*4+3
-    const int ty = tid & (TY - 1);
-    const int g = tid >> 6;                 // FV_THREADS / TY row groups of 4 rows each
-    static_assert(FV_THREADS / TY * 4 == TX && TY == 64, "thread-to-cell map assumes 4 rows per thread");
     const int Nx = P.L.Nx, Ny = P.L.Ny;
     const size_t plane = P.L.plane;
     const int pitch = P.L.pitch;
+    const int nty = P.nblk_x;               // tiles along y
 
-    mbar_wait(bar, 0);
-
-    auto load_cell = [&](int rb, int cb) {
-        Cell c;
-        const int o = rb * BY + cb;
-        c.q0 = sq[o];
-        c.q1 = sq[BOX + o];
-        c.q2 = sq[2 * BOX + o];
-        c.h = stp[o];
-        c.hx = stp[BOX + o];
-        c.hy = stp[2 * BOX + o];
-        c.Ls = LS ? sls[o] : 0.0;
-        return c;
-    };
-    auto phase1 = [&](int rb, int cb) {
-        // global indices of this staged cell; skip cells outside the padded array
-        const int i = i0 - ox + rb, j = j0 - oy + cb;
-        if (i > Nx + 1 || j > Ny + 1) return;
-        const Cell c = load_cell(rb, cb);
-        const int o = rb * BY + cb;
-        Clos4 k;
-        if (P.scalars_fast && cell_in_fast_range<LS>(c)) {
-            k = phase1_cell<LS, EOS, true, XF>(c, P);
-        } else {
-            k = phase1_cell_slow<LS, EOS>(c, P);
-            *sbad = 1;            // this tile takes the plain-division path in phase 2
-        }
-        sp[o] = k.p;
-        st0[o] = k.t0;
-        st1[o] = k.t1;
-        st2[o] = k.t2;
+    auto issue = [&](int tile, int stage) {          // thread 0 only
+        const int i0 = 1 + (tile / nty) * TX, j0 = 1 + (tile % nty) * TY;
+        unsigned char* base = smem + (size_t)stage * S::STAGE;
+        uint64_t* b = bar + stage;
+        mbar_expect_tx(b, S::TX_BYTES);
+        const int cm = (j0 - oy) + 1;       // memory column of the box origin (j0 = 1 + 64k -> even)
+        const int cx = i0 - ox;
+        tma_load_3d(base + S::Q, &A.qmap[in_idx], b, cm, cx, 0);
+        tma_load_3d(base + S::TOPO, XF ? &A.topo2_map : &A.topo_map, b, cm, cx, 0);
+        if (LS) tma_load_3d(base + S::LSO, &A.ls_map, b, cm, cx, 0);
+        if (CORR) tma_load_3d(base + S::Q0, &A.q0map[cur], b, j0 + 1, i0, 0);
     };
 
-    // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
-#pragma unroll 1
-    for (int k = 0; k < 4; ++k) phase1(g * 4 + k + ox, ty + oy);
-    if (tid < TY)
-        phase1((d > 0) ? 0 : TX, tid + oy);                    // halo row
-    else if (tid < TY + TX)
-        phase1(tid - TY + ox, (d > 0) ? oy - 1 : oy + TY);      // halo column
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_init(bar + 1, 1);
+        fence_mbar_init();
+        sbad[0] = 0;
+        sbad[1] = 0;
+    }
     __syncthreads();
+    int tile = blockIdx.x;
+    if (tid == 0 && tile < A.ntiles) issue(tile, 0);
 
-    // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
-    double* qout = A.qbuf[out_idx];
-    const double* q0b = A.qbuf[cur];
-    // straight-line divisions are valid when every staged input, dt, dx and dy are in [2^-100, 2^100]
-    const bool fast = (*sbad == 0) && in_fast_range(dt) && (dt != 0.0) && P.scalars_fast;
-    const unsigned sbit = (d > 0) ? 0x80000000u : 0u;     // -d * x  ==  x with its sign bit flipped when d = +1
+    // thread -> cells: column ty, rows 2g and 2g+1 of the tile
+    const int ty = tid & (TY - 1);
+    const int g = tid >> 6;
+    static_assert(FV_THREADS / TY * 2 == TX && TY == 64, "thread-to-cell map assumes 2 rows per thread");
+    const int o_own = (2 * g + ox) * BY + ty + oy;                 // box offset of the first own cell
+    // halo cell of this thread (warps 0-1: the halo row; warp 2: the halo column, lanes >= TX repeat
+    // cell TX-1 so the warp stays convergent; the duplicate stores write identical values)
+    const int hrow = (d > 0) ? 0 : TX, hcol = (d > 0) ? oy - 1 : oy + TY;
+    const int hcl = (tid - TY < TX - 1) ? tid - TY : TX - 1;
+    const int o_halo = (tid < TY) ? hrow * BY + tid + oy : (hcl + ox) * BY + hcol;
+    const bool has_halo = tid < TY + 32;
+    const int on_dx = -d * BY, on_dy = -d;                        // offsets to the neighbours differenced against
+    const unsigned sbit = (d > 0) ? 0x80000000u : 0u;             // -d * x == x with its sign bit flipped when d = +1
+    const bool dt_fast = in_fast_range_nz(dt) && P.static_fast;
+
+    double* const qout = A.qbuf[out_idx];
+    const double* const q0b = A.qbuf[cur];
     Red red;
     red.ekin = 0.0;
     red.vmax2 = -INFINITY;
     red.cs2 = -INFINITY;
     red.flags = 0;
     constexpr bool DEFER_C = CORR && (EOS == GPF_EOS_DH);
-    double rmax = -INFINITY;
+    double run_thr = -INFINITY;                                    // (1 - 2^-40) x the largest density this warp has seen
 
-#pragma unroll 1
-    for (int k = 0; k < 4; ++k) {
-        const int r = g * 4 + k;
-        const int i = i0 + r, j = j0 + ty;
-        if (i > Nx || j > Ny) continue;
-        const int rb = r + ox, cb = ty + oy;
-        const int o = rb * BY + cb;
-        const int on_x = (rb - d) * BY + cb;     // neighbour the x-difference reaches to
-        const int on_y = rb * BY + (cb - d);
-        const Cell c = load_cell(rb, cb);
-        if (CORR) {      // q0 of this cell is needed after the update: start pulling its lines now
-            const size_t a0 = (size_t)i * pitch + (j + 1);
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(q0b + a0));
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(q0b + plane + a0));
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(q0b + 2 * plane + a0));
-        }
-        Clos4 kk;
-        kk.p = sp[o]; kk.t0 = st0[o]; kk.t1 = st1[o]; kk.t2 = st2[o];
-        Nb nb;
-        nb.q1x = sq[BOX + on_x]; nb.Ax = sp[on_x] + st0[on_x]; nb.t2x = st2[on_x];
-        nb.q2y = sq[2 * BOX + on_y]; nb.t2y = st2[on_y]; nb.Cy = sp[on_y] + st1[on_y];
-        const Q3 qq = fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
-                           : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
-        double qn[3] = {qq.v0, qq.v1, qq.v2};
-        const double qs0 = qn[0], qs1 = qn[1], qs2 = qn[2];     // q** (before averaging)
-        if (CORR) {
-            const size_t a0 = (size_t)i * pitch + (j + 1);
-            const double o0 = q0b[a0], o1 = q0b[plane + a0], o2 = q0b[2 * plane + a0];
-            qn[0] = (qn[0] + o0) * 0.5;                          // problem.py:563 ((q + q0)/2.0, exact)
-            qn[1] = (qn[1] + o1) * 0.5;
-            qn[2] = (qn[2] + o2) * 0.5;
-            if (qn[0] != qn[0] || qn[1] != qn[1] || qn[2] != qn[2]) red.flags |= FLAG_NAN;
-            if (qn[0] < 0.0) red.flags |= FLAG_NEG;
-            // kinetic energy and speed (problem.py:342, 347): w = (jx^2 + jy^2)/rho
-            const double num = qn[1] * qn[1] + qn[2] * qn[2];
-            const double w = (fast && in_fast_range(qn[0]) && in_fast_range(num))
-                                 ? div_fast(num, qn[0], rcp_sel<true>(qn[0])) : num / qn[0];
-            red.ekin += w * 0.5;
-            if (!(w >= 0.0)) red.flags |= FLAG_VNAN;
-            red.vmax2 = fmax(red.vmax2, w);
-            if (DEFER_C) {
-                sq[o] = qn[0];        // own rho slot is dead now: park the new density for the max search
-                rmax = fmax(rmax, qn[0]);
-                if (!(qn[0] == qn[0])) rmax = qn[0];
+    for (int it = 0; tile < A.ntiles; tile += gridDim.x, ++it) {
+        const int stage = it & 1;
+        const int nxt = tile + gridDim.x;
+        if (tid == 0 && nxt < A.ntiles) issue(nxt, stage ^ 1);    // stage^1 was released by the barrier ending tile it-1
+        const unsigned char* base = smem + (size_t)stage * S::STAGE;
+        const double* sq = reinterpret_cast<const double*>(base + S::Q);
+        const double* stp = reinterpret_cast<const double*>(base + S::TOPO);
+        const double* sls = reinterpret_cast<const double*>(base + S::LSO);
+        const double* sq0 = reinterpret_cast<const double*>(base + S::Q0);
+        const int i0 = 1 + (tile / nty) * TX, j0 = 1 + (tile % nty) * TY;
+        mbar_wait(bar + stage, (it >> 1) & 1);
+
+        auto load_cell = [&](int o) {
+            Cell c;
+            c.q0 = sq[o];
+            c.q1 = sq[BOX + o];
+            c.q2 = sq[2 * BOX + o];
+            c.h = stp[o];
+            c.hx = stp[BOX + o];
+            c.hy = XF ? 0.0 : stp[2 * BOX + o];
+            c.Ls = LS ? sls[o] : 0.0;
+            return c;
+        };
+
+        // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
+        {
+            const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
+            Cell ch = ca;
+            if (has_halo) ch = load_cell(o_halo);
+            const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb) & q_in_fast_range(ch);
+            Clos4 ka, kb, kh;
+            if (__all_sync(0xffffffffu, ok) && P.static_fast) {   // warp-uniform
+                ka = phase1_cell<LS, EOS, true, XF>(ca, P);
+                kb = phase1_cell<LS, EOS, true, XF>(cb, P);
+                if (has_halo) kh = phase1_cell<LS, EOS, true, XF>(ch, P);
             } else {
-                red_accum_c<EOS>(red, qn[0], P.eos);
+                ka = phase1_cell_slow<LS, EOS>(ca, P);
+                kb = phase1_cell_slow<LS, EOS>(cb, P);
+                if (has_halo) kh = phase1_cell_slow<LS, EOS>(ch, P);
+                sbad[stage] = 1;          // this tile takes the plain-division path in phase 2
             }
+            sp[o_own] = ka.p; st0[o_own] = ka.t0; st1[o_own] = ka.t1; st2[o_own] = ka.t2;
+            sp[o_own + BY] = kb.p; st0[o_own + BY] = kb.t0; st1[o_own + BY] = kb.t1; st2[o_own + BY] = kb.t2;
+            if (has_halo) { sp[o_halo] = kh.p; st0[o_halo] = kh.t0; st1[o_halo] = kh.t1; st2[o_halo] = kh.t2; }
         }
+        __syncthreads();
 
-        const size_t a = (size_t)i * pitch + (j + 1);
-        qout[a] = qn[0];
-        qout[plane + a] = qn[1];
-        qout[2 * plane + a] = qn[2];
-
-        // ghost cells derived from this cell (problem.py:560 / 576)
-        if ((i == 1) | (i == Nx) | (j == 1) | (j == Ny)) {
-            const Red br = boundary_cell<CORR, EOS>(P, i, j, qs0, qs1, qs2, qn[0], qn[1], qn[2], qout, q0b);
+        // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
+        const bool fast = (sbad[stage] == 0) && dt_fast;                           // tile-uniform
+        if (tid == 0) sbad[stage ^ 1] = 0;                                          // next tile's flag
+        const bool full = (i0 + TX - 1 <= Nx) && (j0 + TY - 1 <= Ny);
+        const bool btile = (i0 == 1) | (i0 + TX - 1 >= Nx) | (j0 == 1) | (j0 + TY - 1 >= Ny);
+        const int j = j0 + ty;
+        double rho[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int i = i0 + 2 * g + k;
+            // cells of a ragged tile that lie outside the grid are computed (on zero-filled or
+            // foreign data) but neither stored nor counted: every lane must reach the warp votes
+            const bool act = full || (i <= Nx && j <= Ny);
+            const int o = o_own + k * BY;
+            const Cell c = load_cell(o);
+            Clos4 kk;
+            kk.p = sp[o]; kk.t0 = st0[o]; kk.t1 = st1[o]; kk.t2 = st2[o];
+            Nb nb;
+            nb.q1x = sq[BOX + o + on_dx]; nb.Ax = sp[o + on_dx] + st0[o + on_dx]; nb.t2x = st2[o + on_dx];
+            nb.q2y = sq[2 * BOX + o + on_dy]; nb.t2y = st2[o + on_dy]; nb.Cy = sp[o + on_dy] + st1[o + on_dy];
+            const Q3 qq = fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
+                               : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
+            double qn0 = qq.v0, qn1 = qq.v1, qn2 = qq.v2;
             if (CORR) {
-                red.ekin += br.ekin;
-                red.vmax2 = fmax(red.vmax2, br.vmax2);
-                red.cs2 = fmax(red.cs2, br.cs2);
-                red.flags |= br.flags;
+                const int oo = (2 * g + k) * TY + ty;
+                qn0 = (qn0 + sq0[oo]) * 0.5;                       // problem.py:563 ((q + q0)/2.0, exact)
+                qn1 = (qn1 + sq0[TX * TY + oo]) * 0.5;
+                qn2 = (qn2 + sq0[2 * TX * TY + oo]) * 0.5;
+                // kinetic energy and speed (problem.py:342, 347): w = (jx^2 + jy^2)/rho
+                const double num = qn1 * qn1 + qn2 * qn2;
+                const bool wok = fast & in_fast_range_nz(qn0) & in_fast_range(num);
+                double w;
+                if (__all_sync(0xffffffffu, wok)) w = div_fast(num, qn0, rcp_sel<true>(qn0));
+                else w = num / qn0;
+                if (act) {
+                    red.ekin += w * 0.5;
+                    red.vmax2 = fmax(red.vmax2, w);
+                    // NaN anywhere in the cell makes w NaN; a negative density has its sign bit set
+                    if (!(w >= 0.0) || __double2hiint(qn0) < 0) red.flags |= cell_flags_slow(qn0, qn1, qn2, w);
+                    if (DEFER_C) rho[k] = qn0;
+                    else red_accum_c<EOS>(red, qn0, P.eos);
+                }
+            }
+            if (act) {
+                const size_t a = (size_t)i * pitch + (j + 1);
+                qout[a] = qn0;
+                qout[plane + a] = qn1;
+                qout[2 * plane + a] = qn2;
+            }
+            // ghost cells derived from this cell (problem.py:560 / 576)
+            if (btile && act && ((i == 1) | (i == Nx) | (j == 1) | (j == Ny))) {
+                const Red br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b);
+                if (CORR) {
+                    red.ekin += br.ekin;
+                    red.vmax2 = fmax(red.vmax2, br.vmax2);
+                    red.cs2 = fmax(red.cs2, br.cs2);
+                    red.flags |= br.flags;
+                }
             }
         }
-    }
-
-    if (CORR) {
         if (DEFER_C) {
             // v_sound = max sqrt(dp/drho).  For Dowson-Higginson dp/drho = K/(C2*rho0 - rho)^2 rises
             // monotonically with rho below the pole, by >= 7e-13 relative per 2^-40 relative step in
             // rho (for rho >= rho0/2), while its 7-operation FP64 evaluation errs by < 1e-15.  So the
-            // cell that attains the maximum of the ROUNDED values lies within 2^-40 of the warp's
-            // maximum density: only those cells are evaluated -- the result is bit-identical to
-            // evaluating every cell.  Outside the proven range every cell is evaluated.
-            double wmax = warp_max(rmax);
+            // cell that attains the maximum of the ROUNDED values lies within 2^-40 of the largest
+            // density: only cells that close to the largest density this warp has met so far are
+            // evaluated -- bit-identical to evaluating every cell.  Outside the proven range every
+            // cell is evaluated.  Positive doubles order like their bit patterns: the warp's exact
+            // maximum takes two 32-bit REDUX operations.
+            const double m = fmax(rho[0], rho[1]);
+            const int whi = __reduce_max_sync(0xffffffffu, __double2hiint(m));
+            const unsigned wlo = __reduce_max_sync(0xffffffffu, (__double2hiint(m) == whi) ? (unsigned)__double2loint(m) : 0u);
+            const double wmax = __hiloint2double(whi, (int)wlo);
             const bool ok = (wmax >= 0.5 * P.eos.p[0]) && (wmax <= P.eos.p[4]);
-            const double thr = ok ? wmax * (1.0 - 0x1p-40) : -INFINITY;
-#pragma unroll 1
-            for (int k = 0; k < 4; ++k) {
-                const int r = g * 4 + k;
-                if (i0 + r > Nx || j0 + ty > Ny) continue;
-                const double rho = sq[(r + ox) * BY + ty + oy];
-                if (!(rho < thr)) red_accum_c<EOS>(red, rho, P.eos);
+            if (!ok) {
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                    if (rho[k] != -INFINITY) red_accum_c<EOS>(red, rho[k], P.eos);
+            } else if (wmax >= run_thr) {
+                const double thr = wmax * (1.0 - 0x1p-40);
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                    if (rho[k] >= thr) red_accum_c<EOS>(red, rho[k], P.eos);
+                run_thr = fmax(run_thr, thr);
             }
         }
-        // warp shuffles, then one record per block (deterministic order)
+        __syncthreads();          // closures and this stage's boxes are free again
+    }
+
+    if (CORR) {
+        // warp shuffles, then one record per CTA (fixed order: deterministic)
         double e = warp_sum(red.ekin);
         double vm = warp_max(red.vmax2);
         double cm = warp_max(red.cs2);
@@ -323,12 +366,11 @@ __global__ void __launch_bounds__(FV_THREADS, FV_MIN_CTAS) fv_pass_kernel(const 
                 CM = fmax(CM, sred[ww * 4 + 2]);
                 F |= (int)sred[ww * 4 + 3];
             }
-            const int b = blockIdx.y * gridDim.x + blockIdx.x;
-            A.partial[b].ekin = E;
-            A.partial[b].vmax2 = VM;
-            A.partial[b].cs2 = CM;
-            A.partial[b].mass = 0.0;
-            A.pflags[b] = F;
+            A.partial[blockIdx.x].ekin = E;
+            A.partial[blockIdx.x].vmax2 = VM;
+            A.partial[blockIdx.x].cs2 = CM;
+            A.partial[blockIdx.x].mass = 0.0;
+            A.pflags[blockIdx.x] = F;
         }
     }
 }
@@ -767,6 +809,19 @@ static int eos_pack(const gpf_fv_cfg& c, EosParams* e) {
     return GPF_E_INVALID;
 }
 
+// persistent CTAs of a pass launch: fv_ctas_per_sm() per SM of the current device, at most one per tile
+static int pass_ctas(int ntiles, bool corr) {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+            sms = 148;            // B200 (also used when no device is present: workspace sizing only)
+        cudaGetLastError();
+    }
+    const int n = sms * fv_ctas_per_sm(corr);
+    return ntiles < n ? ntiles : n;
+}
+
 int pack_params(const gpf_fv_cfg& c, FvParams* P) {
     if (c.Nx < 1 || c.Ny < 1) { set_error("Nx, Ny must be >= 1"); return GPF_E_INVALID; }
     if (c.mc_order != 0 && c.mc_order != 1 && c.mc_order != -1) { set_error("MC_order must be -1, 0 or 1"); return GPF_E_INVALID; }
@@ -808,8 +863,10 @@ int pack_params(const gpf_fv_cfg& c, FvParams* P) {
     P->adaptive = c.adaptive; P->max_it = c.max_it; P->mc_order = c.mc_order;
     P->has_extra = c.has_extra;
     P->xflow = 0;                 // decided when the topography is uploaded
+    P->static_fast = 0;           // decided when topography / slip length are uploaded
     P->nblk_y = (c.Nx + TX - 1) / TX;
     P->nblk_x = (c.Ny + TY - 1) / TY;
+    P->ncta = pass_ctas(P->nblk_x * P->nblk_y, true);      // the corrector writes the records
     return GPF_OK;
 }
 
@@ -818,6 +875,17 @@ __global__ void any_nonzero_kernel(const double* plane, int pitch, int nx2, int 
     if (idx >= (size_t)nx2 * ny2) return;
     const int i = (int)(idx / ny2), j = (int)(idx % ny2);
     if (plane[(size_t)i * pitch + (j + 1)] != 0.0) *flag = 1;
+}
+
+// flag |= 1 if any value of the plane lies outside the straight-line division range
+// (nz: zero not allowed; nonneg: negative not allowed)
+__global__ void range_check_kernel(const double* plane, int pitch, int nx2, int ny2, int nz, int nonneg, int* flag) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)nx2 * ny2) return;
+    const int i = (int)(idx / ny2), j = (int)(idx % ny2);
+    const double v = plane[(size_t)i * pitch + (j + 1)];
+    const bool ok = (nz ? in_fast_range_nz(v) : in_fast_range(v)) && !(nonneg && __double2hiint(v) < 0 && v != 0.0);
+    if (!ok) *flag = 1;
 }
 
 // ---- TMA descriptors ----------------------------------------------------------------
@@ -837,13 +905,13 @@ static EncodeTiledFn get_encode() {
     return fn;
 }
 
-// planes of `ncomp` x rows x pitch doubles; box = (BY, BX, ncomp)
-static int make_map(CUtensorMap* m, double* base, const Layout& L, int ncomp) {
+// planes of `ncomp` x rows x pitch doubles; box = (by, bx, nbox) (default (BY, BX, ncomp))
+static int make_map(CUtensorMap* m, double* base, const Layout& L, int ncomp, int by = BY, int bx = BX, int nbox = 0) {
     EncodeTiledFn enc = get_encode();
     if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return GPF_E_CUDA; }
     cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)L.rows, (cuuint64_t)ncomp};
     cuuint64_t strides[2] = {(cuuint64_t)L.pitch * 8, (cuuint64_t)L.plane * 8};
-    cuuint32_t box[3] = {(cuuint32_t)BY, (cuuint32_t)BX, (cuuint32_t)ncomp};
+    cuuint32_t box[3] = {(cuuint32_t)by, (cuuint32_t)bx, (cuuint32_t)(nbox ? nbox : ncomp)};
     cuuint32_t es[3] = {1, 1, 1};
     CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, es,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -859,8 +927,7 @@ static const int REDUCE_BLOCKS = 148 * 8;
 size_t FvSolver::workspace_bytes(const gpf_fv_cfg& c) {
     Layout L = make_layout(c.Nx, c.Ny);
     size_t plane_b = align_up(L.plane * 8, 256);
-    int nb = ((c.Nx + TX - 1) / TX) * ((c.Ny + TY - 1) / TY) + 1;     // + the edge-row record
-    if (nb < REDUCE_BLOCKS) nb = REDUCE_BLOCKS;
+    int nb = REDUCE_BLOCKS + 1;                        // >= persistent CTAs of a pass + the edge-row record
     size_t b = 0;
     b += 3 * 3 * plane_b;      // q x3 buffers
     b += 3 * plane_b;          // topo
@@ -889,8 +956,8 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     extra = reinterpret_cast<double*>(p); p += plane_b;
     st = reinterpret_cast<DevState*>(p); p += align_up(sizeof(DevState), 256);
     refresh = reinterpret_cast<RefreshOut*>(p); p += align_up(sizeof(RefreshOut), 256);
-    npartial = P.nblk_x * P.nblk_y + 1;
-    if (npartial < REDUCE_BLOCKS) npartial = REDUCE_BLOCKS;
+    npartial = REDUCE_BLOCKS + 1;
+    if (P.ncta + 1 > npartial) { set_error("device has more SMs than the record table allows"); return GPF_E_INVALID; }
     partial = reinterpret_cast<Partial*>(p); p += align_up((size_t)npartial * sizeof(Partial), 256);
     pflags = reinterpret_cast<int*>(p); p += align_up((size_t)npartial * sizeof(int), 256);
     qtable = reinterpret_cast<double**>(p); p += 256;
@@ -898,8 +965,12 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     P.L.plane = plane_b / 8;
     GPF_CUDA(cudaMemcpy(qtable, qbuf, sizeof(qbuf), cudaMemcpyHostToDevice));
     for (int k = 0; k < 3; ++k) if ((rc = make_map(&qmap[k], qbuf[k], P.L, 3))) return rc;
+    for (int k = 0; k < 3; ++k) if ((rc = make_map(&q0map[k], qbuf[k], P.L, 3, TY, TX))) return rc;
     if ((rc = make_map(&topo_map, topo, P.L, 3))) return rc;
+    if ((rc = make_map(&topo2_map, topo, P.L, 3, BY, BX, 2))) return rc;
     if ((rc = make_map(&ls_map, extra, P.L, 1))) return rc;
+    topo_fast = 0;
+    ls_fast = 1;               // the slip-length plane starts as zeros
     // _initialize (problem.py:662-670): rho0, rho0*U/2, rho0*V/2 everywhere incl. ghosts
     {
         const size_t np = (size_t)(c.Nx + 2) * (c.Ny + 2);
@@ -961,18 +1032,34 @@ int FvSolver::upload(int field, const double* data, int ncomp, int on_device, cu
         GPF_CUDA(cudaMemcpy2DAsync(base + k * P.L.plane + 1, (size_t)P.L.pitch * 8, data + (size_t)k * Nx2 * Ny2,
                                    Ny2 * 8, Ny2 * 8, Nx2, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
     if (field == GPF_F_Q) { dirty_scalars = true; refresh_valid = false; }
-    if (field == GPF_F_TOPO) {
-        // x-driven film specialisation: V == 0 and dh/dy == 0 everywhere (exact zeros drop out)
+    if (field == GPF_F_TOPO || field == GPF_F_EXTRA) {
+        // static inputs are classified once: x-driven film specialisation (V == 0 and dh/dy == 0
+        // everywhere: exact zeros drop out) and the straight-line division range
         int* flag = reinterpret_cast<int*>(refresh);
-        GPF_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), s));
+        GPF_CUDA(cudaMemsetAsync(flag, 0, 2 * sizeof(int), s));
         const size_t np = Nx2 * Ny2;
-        any_nonzero_kernel<<<(int)((np + 255) / 256), 256, 0, s>>>(topo + 2 * P.L.plane, P.L.pitch, (int)Nx2, (int)Ny2, flag);
-        g_launches++;
+        const int blocks = (int)((np + 255) / 256);
+        if (field == GPF_F_TOPO) {
+            any_nonzero_kernel<<<blocks, 256, 0, s>>>(topo + 2 * P.L.plane, P.L.pitch, (int)Nx2, (int)Ny2, flag);
+            range_check_kernel<<<blocks, 256, 0, s>>>(topo, P.L.pitch, (int)Nx2, (int)Ny2, 1, 0, flag + 1);
+            range_check_kernel<<<blocks, 256, 0, s>>>(topo + P.L.plane, P.L.pitch, (int)Nx2, (int)Ny2, 0, 0, flag + 1);
+            range_check_kernel<<<blocks, 256, 0, s>>>(topo + 2 * P.L.plane, P.L.pitch, (int)Nx2, (int)Ny2, 0, 0, flag + 1);
+            g_launches += 4;
+        } else {
+            range_check_kernel<<<blocks, 256, 0, s>>>(extra, P.L.pitch, (int)Nx2, (int)Ny2, 0, 1, flag + 1);
+            g_launches++;
+        }
         GPF_CUDA(cudaGetLastError());
-        int h = 1;
-        GPF_CUDA(cudaMemcpyAsync(&h, flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+        int h[2] = {1, 1};
+        GPF_CUDA(cudaMemcpyAsync(h, flag, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
         GPF_CUDA(cudaStreamSynchronize(s));
-        P.xflow = (h == 0 && cfg.V == 0.0) ? 1 : 0;
+        if (field == GPF_F_TOPO) {
+            P.xflow = (h[0] == 0 && cfg.V == 0.0) ? 1 : 0;
+            topo_fast = h[1] == 0;
+        } else {
+            ls_fast = h[1] == 0;
+        }
+        P.static_fast = (P.scalars_fast && topo_fast && ls_fast) ? 1 : 0;
     }
     return GPF_OK;
 }
@@ -995,35 +1082,42 @@ int FvSolver::download(int field, double* data, int ncomp, int on_device, cudaSt
     return GPF_OK;
 }
 
+template <bool CORR, bool LS, int EOS, bool XF>
+static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
+    using Sm = Smem<CORR, LS, XF>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        attr_set = true;
+    }
+    fv_pass_kernel<CORR, LS, EOS, XF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    return GPF_OK;
+}
+
 template <bool CORR>
 static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
     PassArgs A;
-    for (int k = 0; k < 3; ++k) { A.qmap[k] = S.qmap[k]; A.qbuf[k] = S.qbuf[k]; }
-    A.topo_map = S.topo_map; A.ls_map = S.ls_map;
+    for (int k = 0; k < 3; ++k) { A.qmap[k] = S.qmap[k]; A.q0map[k] = S.q0map[k]; A.qbuf[k] = S.qbuf[k]; }
+    A.topo_map = S.topo_map; A.topo2_map = S.topo2_map; A.ls_map = S.ls_map;
     A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags;
     A.until_converged = until_converged;
-    dim3 grid(S.P.nblk_x, S.P.nblk_y), block(FV_THREADS);
+    A.ntiles = S.P.nblk_x * S.P.nblk_y;
     const bool ls = S.P.has_extra != 0;
     const bool dh = S.P.eos.kind == GPF_EOS_DH;
-    void (*k)(const PassArgs);
     const bool xf = S.P.xflow != 0;
-    const int id = (CORR ? 8 : 0) + (ls ? 4 : 0) + (dh ? 2 : 0) + (xf ? 1 : 0);
-    switch (id & 7) {
-    case 0: k = fv_pass_kernel<CORR, false, -1, false>; break;
-    case 1: k = fv_pass_kernel<CORR, false, -1, true>; break;
-    case 2: k = fv_pass_kernel<CORR, false, GPF_EOS_DH, false>; break;
-    case 3: k = fv_pass_kernel<CORR, false, GPF_EOS_DH, true>; break;
-    case 4: k = fv_pass_kernel<CORR, true, -1, false>; break;
-    case 5: k = fv_pass_kernel<CORR, true, -1, true>; break;
-    case 6: k = fv_pass_kernel<CORR, true, GPF_EOS_DH, false>; break;
-    default: k = fv_pass_kernel<CORR, true, GPF_EOS_DH, true>; break;
+    const int n = pass_ctas(A.ntiles, CORR);
+    int rc;
+    switch ((ls ? 4 : 0) + (dh ? 2 : 0) + (xf ? 1 : 0)) {
+    case 0: rc = launch_pass_variant<CORR, false, -1, false>(A, n, s); break;
+    case 1: rc = launch_pass_variant<CORR, false, -1, true>(A, n, s); break;
+    case 2: rc = launch_pass_variant<CORR, false, GPF_EOS_DH, false>(A, n, s); break;
+    case 3: rc = launch_pass_variant<CORR, false, GPF_EOS_DH, true>(A, n, s); break;
+    case 4: rc = launch_pass_variant<CORR, true, -1, false>(A, n, s); break;
+    case 5: rc = launch_pass_variant<CORR, true, -1, true>(A, n, s); break;
+    case 6: rc = launch_pass_variant<CORR, true, GPF_EOS_DH, false>(A, n, s); break;
+    default: rc = launch_pass_variant<CORR, true, GPF_EOS_DH, true>(A, n, s); break;
     }
-    static bool attr_set[16] = {false};
-    if (!attr_set[id]) {
-        GPF_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL));
-        attr_set[id] = true;
-    }
-    k<<<grid, block, SM_TOTAL, s>>>(A);
+    if (rc) return rc;
     g_launches++;
     return debug_check(CORR ? "fv_pass_kernel<corrector>" : "fv_pass_kernel<predictor>", s);
 }
@@ -1048,7 +1142,7 @@ static int launch_reduce(FvSolver& S, cudaStream_t s) {
 
 int FvSolver::step(int n, int until_converged, cudaStream_t s) {
     if (n < 0) { set_error("n < 0"); return GPF_E_INVALID; }
-    const int nblk = P.nblk_x * P.nblk_y;
+    const int nblk = P.ncta;
     if (timing) {
         while ((int)ev.size() < 3 * n + 1) { cudaEvent_t e; GPF_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
         ev_steps = n;
@@ -1089,7 +1183,7 @@ int FvSolver::halo_unpack(int rel, const double* recv, cudaStream_t s) {
     int rc = debug_check("fv_halo_unpack_kernel", s);
     if (rc) return rc;
     if (rel == 2 && (P.bc.edge[0] || P.bc.edge[1])) {
-        const int slot = P.nblk_x * P.nblk_y;
+        const int slot = P.ncta;
         if (P.eos.kind == GPF_EOS_DH) fv_edge_rows_kernel<GPF_EOS_DH><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
         else fv_edge_rows_kernel<-1><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
         g_launches++;
@@ -1101,7 +1195,7 @@ int FvSolver::halo_unpack(int rel, const double* recv, cudaStream_t s) {
 // kind 0: fold the records of the last corrector pass; kind 1: reduce the current q first
 int FvSolver::reduce_local(int kind, double* rec5, cudaStream_t s) {
     int rc;
-    int nblk = P.nblk_x * P.nblk_y + ((P.bc.edge[0] || P.bc.edge[1]) ? 1 : 0);
+    int nblk = P.ncta + ((P.bc.edge[0] || P.bc.edge[1]) ? 1 : 0);
     if (kind == 1) {
         if ((rc = launch_reduce(*this, s))) return rc;
         nblk = REDUCE_BLOCKS;

@@ -33,8 +33,16 @@ constexpr int BX = TX + 1;          // staged rows  (one upwind/downwind halo ro
 constexpr int BY = TY + 4;          // staged cols: 2 left + TY + 2 right.  TMA needs the box origin on a
                                     // 16-byte boundary (even column) and a 16-byte multiple inner extent,
                                     // so the halo column on either side comes with one pad column
-constexpr int FV_THREADS = 128;     // 4 cells per thread
-constexpr int FV_MIN_CTAS = 4;      // resident CTAs per SM (54 KB of shared memory, 128 registers each)
+constexpr int FV_THREADS = 256;     // 2 cells per thread
+// persistent CTAs per SM: the predictor's ring + closure planes take 69 KB (x-driven film), so 3 CTAs
+// of 80 registers fit; the corrector also stages q0 (93 KB): 2 CTAs of 128 registers
+#ifndef GPF_CTAS_PRED
+#define GPF_CTAS_PRED 3
+#endif
+#ifndef GPF_CTAS_CORR
+#define GPF_CTAS_CORR 2
+#endif
+constexpr int fv_ctas_per_sm(bool corr) { return corr ? GPF_CTAS_CORR : GPF_CTAS_PRED; }
 
 // storage layout: plane-major, rows padded.  Cell (i, j) of the reference's padded array
 // (i in [0, Nx+1], j in [0, Ny+1]) lives at  comp*plane + i*pitch + (j + 1):
@@ -81,7 +89,9 @@ struct FvParams {
     int has_extra;
     int xflow;                    // V == 0 and dh/dy == 0 everywhere (x-driven film)
     int scalars_fast;             // dx, dy, viscosities, wall speeds, EOS parameters all in [2^-100, 2^100] or 0
-    int nblk_x, nblk_y;           // tile grid
+    int static_fast;              // scalars_fast and every h in range, dh/dx, dh/dy, Ls in range or 0, Ls >= 0
+    int nblk_x, nblk_y;           // tile grid (nblk_x tiles along y, nblk_y along x)
+    int ncta;                     // persistent CTAs of a pass launch = per-CTA reduction records
 };
 
 }  // namespace gpf
