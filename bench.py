@@ -350,7 +350,7 @@ def run_gpu(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one corrector launch at 4096^2 from the
 # committed `ncu --set full` capture (profiles/); None until a capture exists.
-TRAFFIC_CORR_BYTES = 1600147152  # profiles/r1a_ncu_fv_pass_summary.csv: 1.213890 GB read + 386.257 MB written
+TRAFFIC_CORR_BYTES = 1570300552  # profiles/r1f_ncu_fv_pass_summary.csv: 1.178533 GB read + 391.768 MB written
 
 
 def main():

@@ -156,8 +156,12 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     const int pitch = P.L.pitch;
     const int nty = P.nblk_x;               // tiles along y
 
-    auto issue = [&](int tile, int stage) {          // thread 0 only
-        const int i0 = 1 + (tile / nty) * TX, j0 = 1 + (tile % nty) * TY;
+    // tiles are walked round-robin: tile t = (bx, by), bx = t / nty along x, by = t % nty along y.
+    // The walk advances (bx, by) by a fixed step, so no division runs in the loop.
+    const int step_bx = (int)gridDim.x / nty, step_by = (int)gridDim.x % nty;
+
+    auto issue = [&](int bx, int by, int stage) {          // thread 0 only
+        const int i0 = 1 + bx * TX, j0 = 1 + by * TY;
         unsigned char* base = smem + (size_t)stage * S::STAGE;
         uint64_t* b = bar + stage;
         mbar_expect_tx(b, S::TX_BYTES);
@@ -178,7 +182,8 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     }
     __syncthreads();
     int tile = blockIdx.x;
-    if (tid == 0 && tile < A.ntiles) issue(tile, 0);
+    int bx = tile / nty, by = tile % nty;
+    if (tid == 0 && tile < A.ntiles) issue(bx, by, 0);
 
     // thread -> cells: column ty, rows 2g and 2g+1 of the tile
     const int ty = tid & (TY - 1);
@@ -190,13 +195,15 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     const int hrow = (d > 0) ? 0 : TX, hcol = (d > 0) ? oy - 1 : oy + TY;
     const int hcl = (tid - TY < TX - 1) ? tid - TY : TX - 1;
     const int o_halo = (tid < TY) ? hrow * BY + tid + oy : (hcl + ox) * BY + hcol;
-    const bool has_halo = tid < TY + 32;
+    const bool has_halo = tid < TY + 32;                           // warp-uniform
     const int on_dx = -d * BY, on_dy = -d;                        // offsets to the neighbours differenced against
     const unsigned sbit = (d > 0) ? 0x80000000u : 0u;             // -d * x == x with its sign bit flipped when d = +1
     const bool dt_fast = in_fast_range_nz(dt) && P.static_fast;
 
     double* const qout = A.qbuf[out_idx];
     const double* const q0b = A.qbuf[cur];
+    // this thread's first own cell of tile (0, 0); a tile adds bx*TX rows and by*TY columns
+    const size_t a_thread = (size_t)(1 + 2 * g) * pitch + (1 + ty) + 1;
     Red red;
     red.ekin = 0.0;
     red.vmax2 = -INFINITY;
@@ -205,16 +212,20 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     constexpr bool DEFER_C = CORR && (EOS == GPF_EOS_DH);
     double run_thr = -INFINITY;                                    // (1 - 2^-40) x the largest density this warp has seen
 
-    for (int it = 0; tile < A.ntiles; tile += gridDim.x, ++it) {
+    auto store_clos = [&](int o, const Clos4& k) { sp[o] = k.p; st0[o] = k.t0; st1[o] = k.t1; st2[o] = k.t2; };
+
+    for (int it = 0; tile < A.ntiles; ++it) {
         const int stage = it & 1;
-        const int nxt = tile + gridDim.x;
-        if (tid == 0 && nxt < A.ntiles) issue(nxt, stage ^ 1);    // stage^1 was released by the barrier ending tile it-1
+        // next tile of this CTA
+        const int ntile = tile + (int)gridDim.x;
+        int nbx = bx + step_bx, nby = by + step_by;
+        if (nby >= nty) { nby -= nty; ++nbx; }
+        if (tid == 0 && ntile < A.ntiles) issue(nbx, nby, stage ^ 1);   // stage^1 was released by the barrier ending tile it-1
         const unsigned char* base = smem + (size_t)stage * S::STAGE;
         const double* sq = reinterpret_cast<const double*>(base + S::Q);
         const double* stp = reinterpret_cast<const double*>(base + S::TOPO);
         const double* sls = reinterpret_cast<const double*>(base + S::LSO);
         const double* sq0 = reinterpret_cast<const double*>(base + S::Q0);
-        const int i0 = 1 + (tile / nty) * TX, j0 = 1 + (tile % nty) * TY;
         mbar_wait(bar + stage, (it >> 1) & 1);
 
         auto load_cell = [&](int o) {
@@ -232,39 +243,40 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
         {
             const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
-            Cell ch = ca;
-            if (has_halo) ch = load_cell(o_halo);
-            const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb) & q_in_fast_range(ch);
-            Clos4 ka, kb, kh;
+            const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb);
             if (__all_sync(0xffffffffu, ok) && P.static_fast) {   // warp-uniform
-                ka = phase1_cell<LS, EOS, true, XF>(ca, P);
-                kb = phase1_cell<LS, EOS, true, XF>(cb, P);
-                if (has_halo) kh = phase1_cell<LS, EOS, true, XF>(ch, P);
+                store_clos(o_own, phase1_cell<LS, EOS, true, XF>(ca, P));
+                store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF>(cb, P));
             } else {
-                ka = phase1_cell_slow<LS, EOS>(ca, P);
-                kb = phase1_cell_slow<LS, EOS>(cb, P);
-                if (has_halo) kh = phase1_cell_slow<LS, EOS>(ch, P);
+                store_clos(o_own, phase1_cell_slow<LS, EOS>(ca, P));
+                store_clos(o_own + BY, phase1_cell_slow<LS, EOS>(cb, P));
                 sbad[stage] = 1;          // this tile takes the plain-division path in phase 2
             }
-            sp[o_own] = ka.p; st0[o_own] = ka.t0; st1[o_own] = ka.t1; st2[o_own] = ka.t2;
-            sp[o_own + BY] = kb.p; st0[o_own + BY] = kb.t0; st1[o_own + BY] = kb.t1; st2[o_own + BY] = kb.t2;
-            if (has_halo) { sp[o_halo] = kh.p; st0[o_halo] = kh.t0; st1[o_halo] = kh.t1; st2[o_halo] = kh.t2; }
+        }
+        if (has_halo) {
+            const Cell ch = load_cell(o_halo);
+            if (__all_sync(0xffffffffu, q_in_fast_range(ch)) && P.static_fast) {
+                store_clos(o_halo, phase1_cell<LS, EOS, true, XF>(ch, P));
+            } else {
+                store_clos(o_halo, phase1_cell_slow<LS, EOS>(ch, P));
+                sbad[stage] = 1;
+            }
         }
         __syncthreads();
 
         // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
         const bool fast = (sbad[stage] == 0) && dt_fast;                           // tile-uniform
         if (tid == 0) sbad[stage ^ 1] = 0;                                          // next tile's flag
+        const int i0 = 1 + bx * TX, j0 = 1 + by * TY;
         const bool full = (i0 + TX - 1 <= Nx) && (j0 + TY - 1 <= Ny);
-        const bool btile = (i0 == 1) | (i0 + TX - 1 >= Nx) | (j0 == 1) | (j0 + TY - 1 >= Ny);
-        const int j = j0 + ty;
+        const bool btile = (bx == 0) | (i0 + TX - 1 >= Nx) | (by == 0) | (j0 + TY - 1 >= Ny);
+        const size_t a_tile = a_thread + (size_t)(bx * TX) * pitch + (size_t)(by * TY);
         double rho[2] = {-INFINITY, -INFINITY};
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
-            const int i = i0 + 2 * g + k;
             // cells of a ragged tile that lie outside the grid are computed (on zero-filled or
             // foreign data) but neither stored nor counted: every lane must reach the warp votes
-            const bool act = full || (i <= Nx && j <= Ny);
+            const bool act = full || ((i0 + 2 * g + k <= Nx) && (j0 + ty <= Ny));
             const int o = o_own + k * BY;
             const Cell c = load_cell(o);
             Clos4 kk;
@@ -296,19 +308,22 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
                 }
             }
             if (act) {
-                const size_t a = (size_t)i * pitch + (j + 1);
-                qout[a] = qn0;
-                qout[plane + a] = qn1;
-                qout[2 * plane + a] = qn2;
+                double* dst = qout + a_tile + (size_t)k * pitch;
+                dst[0] = qn0;
+                dst[plane] = qn1;
+                dst[2 * plane] = qn2;
             }
             // ghost cells derived from this cell (problem.py:560 / 576)
-            if (btile && act && ((i == 1) | (i == Nx) | (j == 1) | (j == Ny))) {
-                const Red br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b);
-                if (CORR) {
-                    red.ekin += br.ekin;
-                    red.vmax2 = fmax(red.vmax2, br.vmax2);
-                    red.cs2 = fmax(red.cs2, br.cs2);
-                    red.flags |= br.flags;
+            if (btile) {
+                const int i = i0 + 2 * g + k, j = j0 + ty;
+                if (act && ((i == 1) | (i == Nx) | (j == 1) | (j == Ny))) {
+                    const Red br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b);
+                    if (CORR) {
+                        red.ekin += br.ekin;
+                        red.vmax2 = fmax(red.vmax2, br.vmax2);
+                        red.cs2 = fmax(red.cs2, br.cs2);
+                        red.flags |= br.flags;
+                    }
                 }
             }
         }
@@ -339,6 +354,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             }
         }
         __syncthreads();          // closures and this stage's boxes are free again
+        tile = ntile; bx = nbx; by = nby;
     }
 
     if (CORR) {
