@@ -83,6 +83,15 @@ SIGNATURES = {
     "gpf_stress_bottom": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
     "gpf_stress_top": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
     "gpf_stress_avg": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
+    "gpf_gp_workspace_bytes": (_i, [_i, _i, _i, C.POINTER(C.c_size_t)]),
+    "gpf_gp_create": (_i, [_i, _i, _i, _vp, _sz, C.POINTER(_vp)]),
+    "gpf_gp_destroy": (_i, [_vp]),
+    "gpf_gp_factor": (_i, [_vp, _dp, _i, C.c_double, _dp, C.c_double, _dp, _vp]),
+    "gpf_gp_get_factor": (_i, [_vp, _dp, _dp, _vp]),
+    "gpf_gp_mean": (_i, [_vp, _dp, C.c_int64, _dp, C.POINTER(C.c_double), _vp]),
+    "gpf_gp_mean_var": (_i, [_vp, _dp, C.c_int64, _dp, C.c_double, _dp, _dp, C.POINTER(C.c_double),
+                             C.POINTER(C.c_int64), _vp]),
+    "gpf_gp_features": (_i, [_vp, _dp, C.POINTER(C.c_int32), _i, _dp, _vp]),
     "gpf_selftest_division": (_i, [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), _vp]),
 }
 

@@ -3,6 +3,7 @@
 #include <new>
 #include <string>
 #include "fv_host.h"
+#include "gp_host.h"
 
 namespace gpf {
 static thread_local std::string t_err;
@@ -17,6 +18,9 @@ using namespace gpf;
 
 struct gpf_fv {
     FvSolver S;
+};
+struct gpf_gp {
+    GpModel G;
 };
 
 #define GPF_TRY try {
@@ -198,6 +202,53 @@ int gpf_stress_top(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
 int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls, double* out, size_t n,
                    void* stream) {
     GPF_TRY NEED(cfg && (n == 0 || (q && h && out))) return launch_stress(*cfg, 2, q, h, Ls, out, n, (cudaStream_t)stream); GPF_CATCH
+}
+
+int gpf_gp_workspace_bytes(int M_max, int D, int n_out, size_t* bytes) {
+    GPF_TRY
+    if (!bytes || M_max < 1 || D < 1 || D > 8 || n_out < 1 || n_out > 2) { set_error("bad GP dimensions (D <= 8, n_out <= 2)"); return GPF_E_INVALID; }
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaGetLastError();
+    if (sms <= 0) sms = 148;
+    *bytes = GpModel::workspace_bytes(M_max, D, n_out, sms);
+    return GPF_OK;
+    GPF_CATCH
+}
+int gpf_gp_create(int M_max, int D, int n_out, void* workspace, size_t bytes, gpf_gp** out) {
+    GPF_TRY
+    if (!workspace || !out) { set_error("null argument"); return GPF_E_INVALID; }
+    gpf_gp* h = new gpf_gp();
+    int rc = h->G.init(M_max, D, n_out, workspace, bytes);
+    if (rc) { delete h; return rc; }
+    *out = h;
+    return GPF_OK;
+    GPF_CATCH
+}
+int gpf_gp_destroy(gpf_gp* g) {
+    GPF_TRY delete g; return GPF_OK; GPF_CATCH
+}
+int gpf_gp_factor(gpf_gp* g, const double* Xtrain, int M, double log_amp, const double* log_scale, double yerr,
+                  const double* Y, void* stream) {
+    GPF_TRY NEED(g && Xtrain && log_scale && Y) return g->G.factor(Xtrain, M, log_amp, log_scale, yerr, Y, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_gp_get_factor(gpf_gp* g, double* L_out, double* alpha_out, void* stream) {
+    GPF_TRY NEED(g) return g->G.get_factor(L_out, alpha_out, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_gp_mean(gpf_gp* g, const double* Xtest, int64_t N, double* mean, double* dmean_dx0_max, void* stream) {
+    GPF_TRY NEED(g && (N == 0 || (Xtest && mean))) return g->G.mean(Xtest, N, mean, dmean_dx0_max, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_gp_mean_var(gpf_gp* g, const double* Xtest, int64_t N, const double* noise, double noise_scalar, double* mean,
+                    double* var, double* var_max, int64_t* arg_max, void* stream) {
+    GPF_TRY NEED(g && (N == 0 || (Xtest && mean && var)))
+    long long im = 0;
+    int rc = g->G.mean_var(Xtest, N, noise, noise_scalar, mean, var, var_max, arg_max ? &im : nullptr, (cudaStream_t)stream);
+    if (arg_max) *arg_max = im;
+    return rc;
+    GPF_CATCH
+}
+int gpf_gp_features(gpf_fv* s, const double* x_scale, const int32_t* active_dims, int D, double* X, void* stream) {
+    GPF_TRY NEED(s && x_scale && active_dims && X) return launch_gp_features(s->S, x_scale, active_dims, D, X, (cudaStream_t)stream); GPF_CATCH
 }
 
 int gpf_selftest_division(uint64_t n, uint64_t seed, uint64_t mismatches[2], void* stream) {

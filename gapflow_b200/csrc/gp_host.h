@@ -1,0 +1,42 @@
+// Host-side GP model object behind the opaque gpf_gp handle.
+#pragma once
+#include <cuda_runtime.h>
+#include "gpf_types.h"
+
+namespace gpf {
+
+struct GpKern {          // amp * Matern32(|| s . (x - x') ||)
+    int D;
+    double amp;
+    double s[8];         // exp(-log_scale)
+};
+
+struct FvSolver;
+
+struct GpModel {
+    int Mmax, D, nout, M, Mp, nslots;
+    GpKern kp;
+    // carved from the caller's workspace
+    double* Xs;          // (Mp, D) pre-scaled training inputs
+    double* L;           // (Mp, Mp) row-major lower Cholesky factor (identity in the padding)
+    double* Dinv;        // (Mp/64, 64, 64) inverses of L's diagonal blocks
+    double* alpha;       // (2, Mp) K^-1 Y, one row per output
+    double* scratch;     // (nslots, Mp, 128) v panels of the variance kernel
+    double* gpart;       // partial maxima of the mean kernel
+    double* vpart;       // per-CTA variance maxima
+    long long* ipart;    // per-CTA arg-maxima
+    double* scal;        // result scalars
+
+    static size_t workspace_bytes(int Mmax, int D, int nout, int nslots);
+    int init(int Mmax, int D, int nout, void* ws, size_t bytes);
+    int factor(const double* Xtrain, int M, double log_amp, const double* log_scale, double yerr, const double* Y,
+               cudaStream_t s);
+    int get_factor(double* L_out, double* alpha_out, cudaStream_t s);
+    int mean(const double* Xtest, long long N, double* mean_out, double* dmax_host, cudaStream_t s);
+    int mean_var(const double* Xtest, long long N, const double* noise, double noise_scalar, double* mean_out,
+                 double* var_out, double* vmax_host, long long* imax_host, cudaStream_t s);
+};
+
+int launch_gp_features(FvSolver& S, const double* x_scale7, const int* dims, int D, double* X, cudaStream_t s);
+
+}  // namespace gpf

@@ -1,0 +1,706 @@
+// GP surrogate inference on sm_100a (rows G1-G10 of SURVEY.md section 8a).
+//
+// Replaces, for one GP model (reference file:line in GaPFlow/):
+//   models/gp.py:576-603   multi_in_single_out -> GaussianProcess(kernel, X, diag=yerr^2):
+//                          K = amp*Matern32(||s.(x - x')||) + yerr^2 I,  L = chol(K)      gpf_gp_factor
+//   models/gp.py:546-568   alpha = K^-1 y per output column (tinygp condition)              gpf_gp_factor
+//   models/gp.py:525-535   _repredict_mean:     mean = Ks^T alpha                           gpf_gp_mean
+//   models/stress.py:522-537 v_sound^2 ~ max_i d mean/d x_0 (closed form of vmap(grad))     gpf_gp_mean
+//   models/gp.py:509-522   _repredict_mean_var: v = L^-1 Ks, var = amp + noise - sum v^2    gpf_gp_mean_var
+//   models/gp.py:406-430   maximum_variance, argmax of the variance                         gpf_gp_mean_var
+//   models/gp.py:223-232, stress.py:194-197  feature matrix (N, D)                          gpf_gp_features
+//
+// Design.  Training inputs are pre-scaled once (Xs = X . exp(-log_scale)); the cross-covariance
+// Ks (M x N) is never written to HBM: the mean kernel evaluates it tile by tile from shared
+// memory, the variance kernel evaluates the 64 x 128 block it needs directly in the accumulator
+// layout of the FP64 tensor-core tiles.  L is factored by a blocked right-looking Cholesky
+// (64-wide panels; panel solve and trailing update are DMMA m8n8k4 tiles), the inverses of its
+// 64 x 64 diagonal blocks are kept, and every triangular solve (alpha, v) is the blocked
+// substitution  x_k = inv(L_kk) (b_k - sum_{j<k} L_kj x_j)  whose inner sum is a dense FP64
+// contraction on the tensor pipe.  The variance kernel is persistent: a CTA owns 128 query
+// columns, walks the block rows of L in order (all CTAs stream L in the same order, so L is read
+// from HBM about once per wave and served from the 126 MB L2 otherwise), keeps its v panel in a
+// private HBM scratch slot and accumulates sum v^2 in registers.
+// FP64 only; tcgen05 has no FP64 kind, the FP64 tensor path on sm_100a is mma.sync DMMA.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "fv_host.h"
+#include "gp_host.h"
+
+namespace gpf {
+
+constexpr int NB = 64;          // block size of the factorisation and of the substitutions
+constexpr int NQ = 128;         // query columns per CTA of the variance kernel
+constexpr int LDT = NB + 4;     // shared-memory row stride of a 64-wide FP64 tile (2 wavefronts per fragment load)
+constexpr int LDQ = NQ + 4;
+constexpr double SQRT3 = 1.7320508075688772;
+
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Matern-3/2 on pre-scaled points
+template <int D>
+__device__ __forceinline__ double m32(const double* a, const double* b, double amp) {
+    double d2 = 0.0;
+#pragma unroll
+    for (int k = 0; k < D; ++k) { const double t = a[k] - b[k]; d2 += t * t; }
+    const double r = SQRT3 * sqrt(d2);
+    return amp * (1.0 + r) * exp(-r);
+}
+__device__ __forceinline__ double m32_rt(const double* a, const double* b, int D, double amp) {
+    double d2 = 0.0;
+    for (int k = 0; k < D; ++k) { const double t = a[k] - b[k]; d2 += t * t; }
+    const double r = SQRT3 * sqrt(d2);
+    return amp * (1.0 + r) * exp(-r);
+}
+
+// warp tile 32 x 32 of a CTA tile: acc[mi][ni][2] += A(32 x 4*KK, row-major in smem) x B
+//   BT = true : B given as rows n with k contiguous (C += A B^T),   Bs[n][k]
+//   BT = false: B given as rows k with n contiguous (C += A B),     Bs[k][n]
+template <bool BT, int KK>
+__device__ __forceinline__ void warp_mma(double (&acc)[4][4][2], const double* As, int lda, const double* Bs, int ldb,
+                                         int lane) {
+    const int r = lane >> 2, c = lane & 3;
+#pragma unroll
+    for (int kk = 0; kk < KK; ++kk) {
+        double a[4], b[4];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi) a[mi] = As[(mi * 8 + r) * lda + kk * 4 + c];
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) b[ni] = BT ? Bs[(ni * 8 + r) * ldb + kk * 4 + c] : Bs[(kk * 4 + c) * ldb + ni * 8 + r];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) dmma(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// K = k(X, X) + yerr^2 I on the padded Mp x Mp matrix (identity in the padding)
+// ------------------------------------------------------------------------------------
+__global__ void gp_build_K_kernel(const double* Xs, int M, int Mp, int D, double amp, double yerr2, double* A) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= Mp) return;
+    double v;
+    if (i >= M || j >= M) v = (i == j) ? 1.0 : 0.0;
+    else {
+        v = m32_rt(Xs + (size_t)i * D, Xs + (size_t)j * D, D, amp);
+        if (i == j) v += yerr2;
+    }
+    A[(size_t)i * Mp + j] = v;
+}
+
+// ------------------------------------------------------------------------------------
+// Cholesky step k, part 1: factor the diagonal block in shared memory, write L_kk back
+// and inv(L_kk) to Dinv[k].  One CTA of 256 threads.  info != 0: not positive definite.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, int k, double* Dinv, int* info) {
+    extern __shared__ double potrf_sm[];
+    double (*S)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);
+    double (*X)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm + NB * (NB + 1));
+    const int tid = threadIdx.x;
+    double* Akk = A + (size_t)k * NB * Mp + (size_t)k * NB;
+    for (int e = tid; e < NB * NB; e += 256) S[e / NB][e % NB] = Akk[(size_t)(e / NB) * Mp + e % NB];
+    __syncthreads();
+    for (int j = 0; j < NB; ++j) {
+        if (tid == 0) {
+            const double d = S[j][j];
+            if (!(d > 0.0)) atomicExch(info, k * NB + j + 1);
+            S[j][j] = sqrt(d);
+        }
+        __syncthreads();
+        const double djj = S[j][j];
+        if (tid > j && tid < NB) S[tid][j] /= djj;
+        __syncthreads();
+        // trailing update of the lower triangle: rows i > j, cols j < c <= i
+        for (int e = tid; e < NB * NB; e += 256) {
+            const int i = e / NB, c = e % NB;
+            if (i > j && c > j && c <= i) S[i][c] -= S[i][j] * S[c][j];
+        }
+        __syncthreads();
+    }
+    // inverse of the lower-triangular block: thread c solves column c
+    if (tid < NB) {
+        const int c = tid;
+        for (int i = 0; i < c; ++i) X[i][c] = 0.0;
+        X[c][c] = 1.0 / S[c][c];
+        for (int i = c + 1; i < NB; ++i) {
+            double s = 0.0;
+            for (int j = c; j < i; ++j) s += S[i][j] * X[j][c];
+            X[i][c] = -s / S[i][i];
+        }
+    }
+    __syncthreads();
+    double* Dk = Dinv + (size_t)k * NB * NB;
+    for (int e = tid; e < NB * NB; e += 256) {
+        const int i = e / NB, c = e % NB;
+        Akk[(size_t)i * Mp + c] = (c <= i) ? S[i][c] : 0.0;
+        Dk[e] = X[i][c];
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// Cholesky step k, part 2: panel solve  A[i,k] <- A[i,k] inv(L_kk)^T  for block rows i > k.
+// One CTA (128 threads, 2 x 2 warps of 32 x 32) per block row.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) gp_panel_kernel(double* A, int Mp, int k, const double* Dinv) {
+    extern __shared__ double sm[];
+    double* As = sm;
+    double* Bs = sm + NB * LDT;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 1, wn = w & 1;
+    const int i = k + 1 + blockIdx.x;
+    double* Aik = A + (size_t)i * NB * Mp + (size_t)k * NB;
+    const double* Dk = Dinv + (size_t)k * NB * NB;
+    for (int e = tid; e < NB * NB; e += 128) {
+        As[(e / NB) * LDT + e % NB] = Aik[(size_t)(e / NB) * Mp + e % NB];
+        Bs[(e / NB) * LDT + e % NB] = Dk[e];
+    }
+    __syncthreads();
+    double acc[4][4][2] = {};
+    warp_mma<true, NB / 4>(acc, As + wm * 32 * LDT, LDT, Bs + wn * 32 * LDT, LDT, lane);
+    const int r = lane >> 2, c = lane & 3;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            double* p = Aik + (size_t)(wm * 32 + mi * 8 + r) * Mp + wn * 32 + ni * 8 + c * 2;
+            p[0] = acc[mi][ni][0];
+            p[1] = acc[mi][ni][1];
+        }
+}
+
+// ------------------------------------------------------------------------------------
+// Cholesky step k, part 3: trailing update  A[i,j] -= A[i,k] A[j,k]^T  for k < j <= i.
+// One CTA per lower block pair (linear index -> (i, j)).
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) gp_syrk_kernel(double* A, int Mp, int k) {
+    extern __shared__ double sm[];
+    double* As = sm;
+    double* Bs = sm + NB * LDT;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 1, wn = w & 1;
+    // pair index p -> (ii, jj), jj <= ii, in the trailing matrix
+    const int p = blockIdx.x;
+    int ii = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
+    while ((ii + 1) * (ii + 2) / 2 <= p) ++ii;
+    while (ii * (ii + 1) / 2 > p) --ii;
+    const int jj = p - ii * (ii + 1) / 2;
+    const int i = k + 1 + ii, j = k + 1 + jj;
+    const double* Aik = A + (size_t)i * NB * Mp + (size_t)k * NB;
+    const double* Ajk = A + (size_t)j * NB * Mp + (size_t)k * NB;
+    for (int e = tid; e < NB * NB; e += 128) {
+        As[(e / NB) * LDT + e % NB] = Aik[(size_t)(e / NB) * Mp + e % NB];
+        Bs[(e / NB) * LDT + e % NB] = Ajk[(size_t)(e / NB) * Mp + e % NB];
+    }
+    __syncthreads();
+    double acc[4][4][2] = {};
+    warp_mma<true, NB / 4>(acc, As + wm * 32 * LDT, LDT, Bs + wn * 32 * LDT, LDT, lane);
+    double* Cij = A + (size_t)i * NB * Mp + (size_t)j * NB;
+    const int r = lane >> 2, c = lane & 3;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            double* q = Cij + (size_t)(wm * 32 + mi * 8 + r) * Mp + wn * 32 + ni * 8 + c * 2;
+            q[0] -= acc[mi][ni][0];
+            q[1] -= acc[mi][ni][1];
+        }
+}
+
+// ------------------------------------------------------------------------------------
+// alpha = K^-1 Y by blocked substitution, one CTA (256 threads) per block step.
+//   forward : z_k = Dinv_k (y_k - sum_{j<k} L_kj z_j)
+//   backward: a_k = Dinv_k^T (z_k - sum_{i>k} L_ik^T a_i)
+// X (Mp x nrhs, column-major: X[o*Mp + m]) is overwritten in place.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gp_trsv_fwd_kernel(const double* L, int Mp, int k, const double* Dinv, double* X,
+                                                          int nrhs) {
+    __shared__ double r[2][NB];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int o = 0; o < nrhs; ++o) {
+        const double* x = X + (size_t)o * Mp;
+        for (int row = w; row < NB; row += 8) {
+            const double* Lr = L + (size_t)(k * NB + row) * Mp;
+            double s = 0.0;
+            for (int c = lane; c < k * NB; c += 32) s += Lr[c] * x[c];
+#pragma unroll
+            for (int oo = 16; oo > 0; oo >>= 1) s += __shfl_xor_sync(0xffffffffu, s, oo);
+            if (lane == 0) r[o][row] = x[k * NB + row] - s;
+        }
+    }
+    __syncthreads();
+    const double* Dk = Dinv + (size_t)k * NB * NB;
+    for (int e = tid; e < NB * nrhs; e += 256) {
+        const int o = e / NB, row = e % NB;
+        double s = 0.0;
+        for (int c = 0; c <= row; ++c) s += Dk[row * NB + c] * r[o][c];
+        X[(size_t)o * Mp + k * NB + row] = s;
+    }
+}
+__global__ void __launch_bounds__(256) gp_trsv_bwd_kernel(const double* L, int Mp, int nb, int k, const double* Dinv,
+                                                          double* X, int nrhs) {
+    __shared__ double part[4][2][NB];
+    __shared__ double r[2][NB];
+    const int tid = threadIdx.x, c = tid & 63, g = tid >> 6;
+    for (int o = 0; o < nrhs; ++o) {
+        const double* x = X + (size_t)o * Mp;
+        double s = 0.0;
+        for (int row = (k + 1) * NB + g; row < nb * NB; row += 4) s += L[(size_t)row * Mp + k * NB + c] * x[row];
+        part[g][o][c] = s;
+    }
+    __syncthreads();
+    if (tid < NB)
+        for (int o = 0; o < nrhs; ++o)
+            r[o][tid] = X[(size_t)o * Mp + k * NB + tid] - (part[0][o][tid] + part[1][o][tid] + part[2][o][tid] + part[3][o][tid]);
+    __syncthreads();
+    const double* Dk = Dinv + (size_t)k * NB * NB;
+    for (int e = tid; e < NB * nrhs; e += 256) {
+        const int o = e / NB, col = e % NB;
+        double s = 0.0;
+        for (int row = col; row < NB; ++row) s += Dk[row * NB + col] * r[o][row];     // Dinv^T
+        X[(size_t)o * Mp + k * NB + col] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// mean (n_out, N) = alpha^T Ks, and d mean_0 / d x_0 (max over the queries of this block).
+// One thread per query, training points staged through shared memory.
+// ------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const double* alpha, int M, int Mp, int nout,
+                                                      GpKern kp, const double* Xtest, long long N, long long off,
+                                                      long long cnt, double* mean, double* gmax_part) {
+    constexpr int TM = 256;
+    __shared__ double sx[TM * D];
+    __shared__ double sa[2][TM];
+    __shared__ double sred[8];
+    const long long i = off + (long long)blockIdx.x * 256 + threadIdx.x;
+    const bool valid = i < off + cnt;
+    double x[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) x[k] = valid ? Xtest[i * D + k] * kp.s[k] : 0.0;
+    double m0 = 0.0, m1 = 0.0, g0 = 0.0;
+    for (int t0 = 0; t0 < M; t0 += TM) {
+        const int n = min(TM, M - t0);
+        __syncthreads();
+        for (int e = threadIdx.x; e < n * D; e += 256) sx[e] = Xs[(size_t)t0 * D + e];
+        for (int e = threadIdx.x; e < n; e += 256) {
+            sa[0][e] = alpha[t0 + e];
+            sa[1][e] = nout > 1 ? alpha[(size_t)Mp + t0 + e] : 0.0;
+        }
+        __syncthreads();
+        for (int j = 0; j < n; ++j) {
+            double d2 = 0.0;
+#pragma unroll
+            for (int k = 0; k < D; ++k) { const double t = x[k] - sx[j * D + k]; d2 += t * t; }
+            const double r = SQRT3 * sqrt(d2);
+            const double e = exp(-r);
+            const double kv = (1.0 + r) * e;
+            m0 += sa[0][j] * kv;
+            m1 += sa[1][j] * kv;
+            g0 += sa[0][j] * ((x[0] - sx[j * D]) * e);
+        }
+    }
+    double g = -INFINITY;
+    if (valid) {
+        mean[i] = kp.amp * m0;
+        if (nout > 1) mean[N + i] = kp.amp * m1;
+        g = -3.0 * kp.amp * kp.s[0] * g0;          // d/dx_0 in the (unscaled) normalised input
+    }
+    // block max (NaN-propagating like jnp.max is not needed: a NaN gradient makes the mean NaN too)
+#pragma unroll
+    for (int oo = 16; oo > 0; oo >>= 1) g = fmax(g, __shfl_xor_sync(0xffffffffu, g, oo));
+    if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = g;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int ww = 1; ww < 8; ++ww) g = fmax(g, sred[ww]);
+        gmax_part[blockIdx.x] = g;
+    }
+}
+
+__global__ void gp_max_reduce_kernel(const double* part, int n, double* out) {
+    __shared__ double s[256];
+    double g = -INFINITY;
+    for (int e = threadIdx.x; e < n; e += 256) g = fmax(g, part[e]);
+    s[threadIdx.x] = g;
+    __syncthreads();
+    for (int st = 128; st > 0; st >>= 1) {
+        if (threadIdx.x < st) s[threadIdx.x] = fmax(s[threadIdx.x], s[threadIdx.x + st]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = s[0];
+}
+
+// ------------------------------------------------------------------------------------
+// var (N) = amp + noise - sum_m v[m]^2,  v = L^-1 Ks, by blocked forward substitution.
+// Persistent CTAs (256 threads = 2 x 4 warps of 32 x 32): a CTA owns NQ = 128 query columns.
+// ------------------------------------------------------------------------------------
+constexpr int VBK = 16;                       // k-depth of one pipeline stage
+constexpr int VST = 3;                        // cp.async stages
+constexpr int LDA_V = VBK + 2;                // stride of the staged L sub-tile rows
+constexpr size_t VAR_STAGE = (size_t)(NB * LDA_V + VBK * LDQ) * 8;
+constexpr size_t VAR_SOLVE = (size_t)(NB * LDQ + NB * LDT) * 8;
+constexpr size_t VAR_MAIN = (VST * VAR_STAGE > VAR_SOLVE) ? VST * VAR_STAGE : VAR_SOLVE;
+constexpr int GP_MAXD = 8;
+constexpr size_t VAR_SMEM = VAR_MAIN + (size_t)(NQ * GP_MAXD + NB * GP_MAXD + NQ * 2) * 8;
+
+__global__ void __launch_bounds__(256, 1) gp_var_kernel(const double* L, const double* Dinv, const double* Xs, int M, int Mp,
+                                                        GpKern kp, const double* Xtest, long long N, const double* noise,
+                                                        double noise_scalar, double* var, double* scratch,
+                                                        double* vmax_part, long long* imax_part) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    double* sm = reinterpret_cast<double*>(smraw);
+    double* sxq = reinterpret_cast<double*>(smraw + VAR_MAIN);     // scaled query features [NQ][D]
+    double* sxt = sxq + NQ * GP_MAXD;                               // scaled training features of block kb [NB][D]
+    double* scol = sxt + NB * GP_MAXD;                              // column sums from the two warp rows [2][NQ]
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 2, wn = w & 3;
+    const int r = lane >> 2, c = lane & 3;
+    const int D = kp.D;
+    const int nb = Mp / NB;
+    double* V = scratch + (size_t)blockIdx.x * Mp * NQ;             // this CTA's v panel (Mp x NQ)
+    const long long ntiles = (N + NQ - 1) / NQ;
+    double best = -INFINITY;
+    long long besti = 0;
+
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long q0 = tile * NQ;
+        __syncthreads();
+        for (int e = tid; e < NQ * D; e += 256) {
+            const long long qi = q0 + e / D;
+            sxq[(e / D) * GP_MAXD + e % D] = (qi < N) ? Xtest[qi * D + e % D] * kp.s[e % D] : 0.0;
+        }
+        double colsum[4][2] = {};
+        for (int kb = 0; kb < nb; ++kb) {
+            // ---- acc = sum_{k < kb*NB} L[kb rows][k] * V[k][cols], 3-stage cp.async pipeline ----
+            double acc[4][4][2] = {};
+            const int nk = kb * NB / VBK;
+            const double* Lrow = L + (size_t)kb * NB * Mp;
+            auto stage_load = [&](int s, int kt) {
+                double* As = sm + (size_t)s * (VAR_STAGE / 8);
+                double* Bs = As + NB * LDA_V;
+                // L sub-tile: 64 rows x 16 doubles = 512 16-byte chunks; V sub-tile: 16 rows x 128 = 1024 chunks
+                for (int e = tid; e < 512; e += 256) {
+                    const int row = e >> 3, ch = e & 7;
+                    cp_async16(As + row * LDA_V + ch * 2, Lrow + (size_t)row * Mp + (size_t)kt * VBK + ch * 2);
+                }
+                for (int e = tid; e < 1024; e += 256) {
+                    const int row = e >> 6, ch = e & 63;
+                    cp_async16(Bs + row * LDQ + ch * 2, V + (size_t)(kt * VBK + row) * NQ + ch * 2);
+                }
+            };
+            __syncthreads();                      // previous block's solve buffers / V stores are done
+            for (int s = 0; s < VST - 1; ++s) {
+                if (s < nk) stage_load(s, s);
+                cp_async_commit();
+            }
+            for (int kt = 0; kt < nk; ++kt) {
+                cp_async_wait<VST - 2>();
+                __syncthreads();
+                const int nx = kt + VST - 1;
+                if (nx < nk) stage_load(nx % VST, nx);
+                cp_async_commit();
+                const double* As = sm + (size_t)(kt % VST) * (VAR_STAGE / 8);
+                const double* Bs = As + NB * LDA_V;
+                warp_mma<false, VBK / 4>(acc, As + wm * 32 * LDA_V, LDA_V, Bs + wn * 32, LDQ, lane);
+            }
+            cp_async_wait<0>();
+            __syncthreads();
+            // ---- R = Ks[kb] - acc, evaluated in the accumulator layout; staged as the B operand ----
+            for (int e = tid; e < NB * D; e += 256) {
+                const int m = kb * NB + e / D;
+                sxt[(e / D) * GP_MAXD + e % D] = (m < M) ? Xs[(size_t)m * D + e % D] : 0.0;
+            }
+            double* Rs = sm;                              // [NB][LDQ]
+            double* Ds = sm + NB * LDQ;                   // [NB][LDT]
+            const double* Dk = Dinv + (size_t)kb * NB * NB;
+            for (int e = tid; e < NB * NB; e += 256) Ds[(e / NB) * LDT + e % NB] = Dk[e];
+            __syncthreads();
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi) {
+                const int m = wm * 32 + mi * 8 + r;
+                const bool real = kb * NB + m < M;
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int n = wn * 32 + ni * 8 + c * 2 + h;
+                        const double kv = real ? m32_rt(sxt + m * GP_MAXD, sxq + n * GP_MAXD, D, kp.amp) : 0.0;
+                        Rs[m * LDQ + n] = kv - acc[mi][ni][h];
+                    }
+            }
+            __syncthreads();
+            // ---- V[kb] = inv(L_kk) R ----
+            double vv[4][4][2] = {};
+            warp_mma<false, NB / 4>(vv, Ds + wm * 32 * LDT, LDT, Rs + wn * 32, LDQ, lane);
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) {
+                    const int m = kb * NB + wm * 32 + mi * 8 + r, n = wn * 32 + ni * 8 + c * 2;
+                    *reinterpret_cast<double2*>(V + (size_t)m * NQ + n) = make_double2(vv[mi][ni][0], vv[mi][ni][1]);
+                    colsum[ni][0] += vv[mi][ni][0] * vv[mi][ni][0];
+                    colsum[ni][1] += vv[mi][ni][1] * vv[mi][ni][1];
+                }
+        }
+        // ---- fold the column sums: 8 lanes share a column (xor 4, 8, 16), 2 warp rows through smem ----
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                double s = colsum[ni][h];
+                s += __shfl_xor_sync(0xffffffffu, s, 4);
+                s += __shfl_xor_sync(0xffffffffu, s, 8);
+                s += __shfl_xor_sync(0xffffffffu, s, 16);
+                if (r == 0) scol[wm * NQ + wn * 32 + ni * 8 + c * 2 + h] = s;
+            }
+        __syncthreads();
+        if (tid < NQ) {
+            const long long qi = q0 + tid;
+            if (qi < N) {
+                const double nz = noise ? noise[qi] : noise_scalar;
+                const double v = kp.amp + nz - (scol[tid] + scol[NQ + tid]);
+                var[qi] = v;
+                if (v > best || v != v) { if (!(best != best)) { best = v; besti = qi; } }   // first maximum; NaN sticks
+            }
+        }
+    }
+    // per-CTA (max, first index); tid < NQ hold candidates
+    __shared__ double sb[NQ];
+    __shared__ long long si[NQ];
+    if (tid < NQ) { sb[tid] = best; si[tid] = besti; }
+    __syncthreads();
+    if (tid == 0) {
+        double b = -INFINITY; long long bi = 0x7fffffffffffffffLL; bool nanv = false;
+        for (int t = 0; t < NQ; ++t) {
+            const double v = sb[t];
+            if (v != v) { if (!nanv || si[t] < bi) { nanv = true; b = v; bi = si[t]; } continue; }
+            if (nanv) continue;
+            if (v > b || (v == b && si[t] < bi)) { b = v; bi = si[t]; }
+        }
+        vmax_part[blockIdx.x] = b;
+        imax_part[blockIdx.x] = bi;
+    }
+}
+
+__global__ void gp_argmax_reduce_kernel(const double* vpart, const long long* ipart, int n, double* vout, long long* iout) {
+    if (threadIdx.x != 0) return;
+    double b = -INFINITY; long long bi = 0x7fffffffffffffffLL; bool nanv = false;
+    for (int t = 0; t < n; ++t) {
+        const double v = vpart[t];
+        if (v != v) { if (!nanv || ipart[t] < bi) { nanv = true; b = v; bi = ipart[t]; } continue; }
+        if (nanv) continue;
+        if (v > b || (v == b && ipart[t] < bi)) { b = v; bi = ipart[t]; }
+    }
+    *vout = b;
+    *iout = bi;
+}
+
+// ------------------------------------------------------------------------------------
+// Feature matrix (gp.py:223-232, stress.py:194-197): row i*(Ny+2)+j, columns = active dims of
+// [rho, jx, jy, h, dh/dx, dh/dy, extra] / X_scale, read from the FV solver's own storage.
+// ------------------------------------------------------------------------------------
+struct FeatArgs { int D; int dims[GP_MAXD]; double inv_dummy; double scale[GP_MAXD]; };
+__global__ void gp_features_kernel(const double* q, const double* topo, const double* extra, size_t plane, int pitch,
+                                   int Nx2, int Ny2, FeatArgs fa, double* X) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)Nx2 * Ny2) return;
+    const int i = (int)(idx / Ny2), j = (int)(idx % Ny2);
+    const size_t a = (size_t)i * pitch + (j + 1);
+    for (int k = 0; k < fa.D; ++k) {
+        const int f = fa.dims[k];
+        double v;
+        if (f < 3) v = q[f * plane + a];
+        else if (f < 6) v = topo[(f - 3) * plane + a];
+        else v = extra[a];
+        X[idx * fa.D + k] = v / fa.scale[k];
+    }
+}
+
+// =====================================================================================
+// Host side
+// =====================================================================================
+static size_t al(size_t x) { return (x + 255) / 256 * 256; }
+
+size_t GpModel::workspace_bytes(int Mmax, int D, int nout, int nslots) {
+    const size_t Mp = (size_t)(Mmax + NB - 1) / NB * NB;
+    size_t b = 256;
+    b += al(Mp * D * 8);                 // Xs
+    b += al(Mp * Mp * 8);                // L
+    b += al(Mp / NB * NB * NB * 8);      // Dinv
+    b += al(Mp * 2 * 8);                 // alpha (column-major, 2 columns)
+    b += al((size_t)nslots * Mp * NQ * 8);   // v panels of the variance kernel
+    b += al(65536 * 8) + al(4096 * 8) + al(4096 * 8) + 256;   // partial maxima, argmax parts, scalars
+    (void)nout;
+    return b;
+}
+
+int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
+    if (Mmax_ < 1 || D_ < 1 || D_ > GP_MAXD || nout_ < 1 || nout_ > 2) { set_error("bad GP dimensions (D <= 8, n_out <= 2)"); return GPF_E_INVALID; }
+    Mmax = Mmax_; D = D_; nout = nout_; M = 0; Mp = 0;
+    int dev = 0, sms = 148;
+    GPF_CUDA(cudaGetDevice(&dev));
+    GPF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    nslots = sms;
+    if (bytes < workspace_bytes(Mmax, D, nout, nslots)) { set_error("GP workspace too small"); return GPF_E_INVALID; }
+    const size_t Mpm = (size_t)(Mmax + NB - 1) / NB * NB;
+    unsigned char* p = reinterpret_cast<unsigned char*>(al(reinterpret_cast<size_t>(ws)));
+    Xs = reinterpret_cast<double*>(p); p += al(Mpm * D * 8);
+    L = reinterpret_cast<double*>(p); p += al(Mpm * Mpm * 8);
+    Dinv = reinterpret_cast<double*>(p); p += al(Mpm / NB * NB * NB * 8);
+    alpha = reinterpret_cast<double*>(p); p += al(Mpm * 2 * 8);
+    scratch = reinterpret_cast<double*>(p); p += al((size_t)nslots * Mpm * NQ * 8);
+    gpart = reinterpret_cast<double*>(p); p += al(65536 * 8);
+    vpart = reinterpret_cast<double*>(p); p += al(4096 * 8);
+    ipart = reinterpret_cast<long long*>(p); p += al(4096 * 8);
+    scal = reinterpret_cast<double*>(p);
+    return GPF_OK;
+}
+
+int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* log_scale, double yerr, const double* Y,
+                    cudaStream_t s) {
+    if (M_ < 1 || M_ > Mmax) { set_error("training-set size outside [1, M_max]"); return GPF_E_INVALID; }
+    M = M_;
+    Mp = (M + NB - 1) / NB * NB;
+    kp.D = D;
+    kp.amp = exp(log_amp);
+    for (int k = 0; k < GP_MAXD; ++k) kp.s[k] = k < D ? exp(-log_scale[k]) : 0.0;
+    // pre-scaled training inputs and right-hand sides (host -> device)
+    std::vector<double> xs((size_t)Mp * D, 0.0), y((size_t)Mp * 2, 0.0);
+    for (int i = 0; i < M; ++i)
+        for (int k = 0; k < D; ++k) xs[(size_t)i * D + k] = Xtrain[(size_t)i * D + k] * kp.s[k];
+    for (int i = 0; i < M; ++i)
+        for (int o = 0; o < nout; ++o) y[(size_t)o * Mp + i] = Y[(size_t)i * nout + o];
+    GPF_CUDA(cudaMemcpyAsync(Xs, xs.data(), xs.size() * 8, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaMemcpyAsync(alpha, y.data(), (size_t)Mp * 2 * 8, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaStreamSynchronize(s));       // the host vectors go out of scope
+    int* info = reinterpret_cast<int*>(scal + 8);
+    GPF_CUDA(cudaMemsetAsync(info, 0, sizeof(int), s));
+    gp_build_K_kernel<<<dim3((Mp + 255) / 256, Mp), 256, 0, s>>>(Xs, M, Mp, D, kp.amp, yerr * yerr, L);
+    g_launches++;
+    const int nb = Mp / NB;
+    const size_t sm2 = (size_t)2 * NB * LDT * 8;
+    const size_t smp = (size_t)2 * NB * (NB + 1) * 8;
+    static bool attr = false;
+    if (!attr) {
+        GPF_CUDA(cudaFuncSetAttribute(gp_potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp));
+        GPF_CUDA(cudaFuncSetAttribute(gp_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+        GPF_CUDA(cudaFuncSetAttribute(gp_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+        GPF_CUDA(cudaFuncSetAttribute(gp_var_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)VAR_SMEM));
+        attr = true;
+    }
+    for (int k = 0; k < nb; ++k) {
+        gp_potrf_diag_kernel<<<1, 256, smp, s>>>(L, Mp, k, Dinv, info);
+        g_launches++;
+        const int rem = nb - 1 - k;
+        if (rem > 0) {
+            gp_panel_kernel<<<rem, 128, sm2, s>>>(L, Mp, k, Dinv);
+            gp_syrk_kernel<<<rem * (rem + 1) / 2, 128, sm2, s>>>(L, Mp, k);
+            g_launches += 2;
+        }
+    }
+    for (int k = 0; k < nb; ++k) { gp_trsv_fwd_kernel<<<1, 256, 0, s>>>(L, Mp, k, Dinv, alpha, nout); g_launches++; }
+    for (int k = nb - 1; k >= 0; --k) { gp_trsv_bwd_kernel<<<1, 256, 0, s>>>(L, Mp, nb, k, Dinv, alpha, nout); g_launches++; }
+    GPF_CUDA(cudaGetLastError());
+    int h = 0;
+    GPF_CUDA(cudaMemcpyAsync(&h, info, sizeof(int), cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    if (h) { set_error("K + yerr^2 I is not positive definite at row " + std::to_string(h - 1)); M = 0; return GPF_E_INVALID; }
+    return GPF_OK;
+}
+
+int GpModel::get_factor(double* L_out, double* alpha_out, cudaStream_t s) {
+    if (M < 1) { set_error("no factorisation"); return GPF_E_STATE; }
+    if (L_out) GPF_CUDA(cudaMemcpy2DAsync(L_out, (size_t)M * 8, L, (size_t)Mp * 8, (size_t)M * 8, M, cudaMemcpyDeviceToHost, s));
+    if (alpha_out) {
+        std::vector<double> a((size_t)Mp * 2);
+        GPF_CUDA(cudaMemcpyAsync(a.data(), alpha, a.size() * 8, cudaMemcpyDeviceToHost, s));
+        GPF_CUDA(cudaStreamSynchronize(s));
+        for (int i = 0; i < M; ++i)
+            for (int o = 0; o < nout; ++o) alpha_out[(size_t)i * nout + o] = a[(size_t)o * Mp + i];
+    }
+    GPF_CUDA(cudaStreamSynchronize(s));
+    return GPF_OK;
+}
+
+int GpModel::mean(const double* Xtest, long long N, double* mean_out, double* dmax_host, cudaStream_t s) {
+    if (M < 1) { set_error("no factorisation"); return GPF_E_STATE; }
+    if (N < 1) return GPF_OK;
+    // at most 65536 partial maxima per launch
+    double gmax = -INFINITY;
+    const long long chunk = 65536LL * 256;
+    for (long long off = 0; off < N; off += chunk) {
+        const long long cnt = std::min<long long>(chunk, N - off);
+        const int nbk = (int)((cnt + 255) / 256);
+        switch (D) {
+#define GP_MEAN_CASE(DD) case DD: gp_mean_kernel<DD><<<nbk, 256, 0, s>>>(Xs, alpha, M, Mp, nout, kp, Xtest, N, off, cnt, mean_out, gpart); break;
+            GP_MEAN_CASE(1) GP_MEAN_CASE(2) GP_MEAN_CASE(3) GP_MEAN_CASE(4) GP_MEAN_CASE(5) GP_MEAN_CASE(6) GP_MEAN_CASE(7) GP_MEAN_CASE(8)
+#undef GP_MEAN_CASE
+        }
+        gp_max_reduce_kernel<<<1, 256, 0, s>>>(gpart, nbk, scal);
+        g_launches += 2;
+        if (dmax_host) {
+            double g;
+            GPF_CUDA(cudaMemcpyAsync(&g, scal, 8, cudaMemcpyDeviceToHost, s));
+            GPF_CUDA(cudaStreamSynchronize(s));
+            gmax = std::fmax(gmax, g);
+        }
+    }
+    GPF_CUDA(cudaGetLastError());
+    if (dmax_host) *dmax_host = gmax;
+    return GPF_OK;
+}
+
+int GpModel::mean_var(const double* Xtest, long long N, const double* noise, double noise_scalar, double* mean_out,
+                      double* var_out, double* vmax_host, long long* imax_host, cudaStream_t s) {
+    int rc = mean(Xtest, N, mean_out, nullptr, s);
+    if (rc) return rc;
+    if (N < 1) return GPF_OK;
+    const long long ntiles = (N + NQ - 1) / NQ;
+    const int grid = (int)std::min<long long>(ntiles, nslots);
+    gp_var_kernel<<<grid, 256, VAR_SMEM, s>>>(L, Dinv, Xs, M, Mp, kp, Xtest, N, noise, noise_scalar, var_out, scratch, vpart,
+                                              ipart);
+    gp_argmax_reduce_kernel<<<1, 32, 0, s>>>(vpart, ipart, grid, scal + 1, reinterpret_cast<long long*>(scal + 2));
+    g_launches += 2;
+    GPF_CUDA(cudaGetLastError());
+    if (vmax_host || imax_host) {
+        double h[2];
+        GPF_CUDA(cudaMemcpyAsync(h, scal + 1, 16, cudaMemcpyDeviceToHost, s));
+        GPF_CUDA(cudaStreamSynchronize(s));
+        if (vmax_host) *vmax_host = h[0];
+        if (imax_host) memcpy(imax_host, &h[1], 8);
+    }
+    return GPF_OK;
+}
+
+int launch_gp_features(FvSolver& S, const double* x_scale7, const int* dims, int D, double* X, cudaStream_t s) {
+    if (D < 1 || D > GP_MAXD) { set_error("1 <= D <= 8"); return GPF_E_INVALID; }
+    FeatArgs fa;
+    fa.D = D;
+    for (int k = 0; k < D; ++k) {
+        if (dims[k] < 0 || dims[k] > 6) { set_error("active dimension outside [0, 6]"); return GPF_E_INVALID; }
+        fa.dims[k] = dims[k];
+        fa.scale[k] = x_scale7[dims[k]];
+    }
+    int cur;
+    int rc = S.read_cur(s, &cur);
+    if (rc) return rc;
+    const int Nx2 = S.cfg.Nx + 2, Ny2 = S.cfg.Ny + 2;
+    const size_t np = (size_t)Nx2 * Ny2;
+    gp_features_kernel<<<(int)((np + 255) / 256), 256, 0, s>>>(S.qbuf[cur], S.topo, S.extra, S.P.L.plane, S.P.L.pitch, Nx2, Ny2,
+                                                             fa, X);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+}  // namespace gpf

@@ -190,6 +190,40 @@ int gpf_stress_top(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
 int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls,
                    double* out, size_t n, void* stream);
 
+/* --- GP surrogate inference (GaPFlow/models/gp.py) -------------------------------------
+ * One handle per GP model (pressure: n_out = 1; wall shear: n_out = 2 outputs sharing one
+ * kernel, gp.py:546-552).  Kernel: exp(log_amp) * Matern32(|| exp(-log_scale) . (x - x') ||)
+ * (gp.py:576-603).  Inputs are the reference's NORMALISED arrays: Xtrain = database.Xtrain[:,
+ * active_dims], Y = Ytrain / Yscale, Xtest = (_Xtest / X_scale)[:, active_dims]; outputs are in
+ * normalised units (the caller multiplies by Yscale, Yscale^2 as gp.py:362, 384-386 do). */
+typedef struct gpf_gp gpf_gp;
+int gpf_gp_workspace_bytes(int M_max, int D, int n_out, size_t* bytes);
+int gpf_gp_create(int M_max, int D, int n_out, void* workspace, size_t bytes, gpf_gp** out);
+int gpf_gp_destroy(gpf_gp* g);
+/* build_gp + the solves of gp.condition (gp.py:268-288, 546-568): K + yerr^2 I, its Cholesky
+ * factor, alpha = K^-1 Y.  Xtrain (M, D), Y (M, n_out), log_scale (D): HOST arrays (they come
+ * from the host-side database and optimiser).  This is the refactorisation that follows every
+ * added MD point (gp.py:290-335).  Synchronises; GPF_E_INVALID if not positive definite. */
+int gpf_gp_factor(gpf_gp* g, const double* Xtrain, int M, double log_amp, const double* log_scale,
+                  double yerr, const double* Y, void* stream);
+/* copies of L (M, M; lower) and alpha (M, n_out) to HOST arrays (tests, gp_*.txt); NULL skips */
+int gpf_gp_get_factor(gpf_gp* g, double* L_out, double* alpha_out, void* stream);
+/* _repredict_mean (gp.py:525-535): Xtest (N, D) device -> mean (n_out, N) device.  If
+ * dmean_dx0_max != NULL also max_i d mean_0 / d x_0 (host scalar; Pressure.v_sound's
+ * vmap(grad(eos))(Xtest)[:, 0].max(), stress.py:522-537) and the call synchronises. */
+int gpf_gp_mean(gpf_gp* g, const double* Xtest, int64_t N, double* mean, double* dmean_dx0_max, void* stream);
+/* _repredict_mean_var (gp.py:509-522): also var (N) = amp + noise - sum (L^-1 Ks)^2.  noise: device
+ * array (N) or NULL for the scalar `noise_scalar` (tinygp's conditioned-GP jitter: an input, not
+ * guessed).  var_max / arg_max (host; gp.py:406, 424: first maximum, ghost cells included) may be
+ * NULL; if either is given the call synchronises. */
+int gpf_gp_mean_var(gpf_gp* g, const double* Xtest, int64_t N, const double* noise, double noise_scalar,
+                    double* mean, double* var, double* var_max, int64_t* arg_max, void* stream);
+/* Feature matrix of the current solution straight from the FV solver's storage (gp.py:223-232,
+ * stress.py:194-197): X (Np, D) device, Np = (Nx+2)(Ny+2), row i*(Ny+2)+j; column k is feature
+ * active_dims[k] of [rho, jx, jy, h, dh/dx, dh/dy, extra] divided by x_scale[active_dims[k]].
+ * x_scale (7) and active_dims (D) are host arrays. */
+int gpf_gp_features(gpf_fv* s, const double* x_scale, const int32_t* active_dims, int D, double* X, void* stream);
+
 /* --- instrumentation ------------------------------------------------------------- */
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
 int64_t gpf_launch_count(void);
