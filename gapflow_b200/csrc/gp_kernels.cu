@@ -620,7 +620,13 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
 
 int GpModel::get_factor(double* L_out, double* alpha_out, cudaStream_t s) {
     if (M < 1) { set_error("no factorisation"); return GPF_E_STATE; }
-    if (L_out) GPF_CUDA(cudaMemcpy2DAsync(L_out, (size_t)M * 8, L, (size_t)Mp * 8, (size_t)M * 8, M, cudaMemcpyDeviceToHost, s));
+    if (L_out) {
+        // the strict upper triangle of the device array still holds K (never read): report zeros
+        GPF_CUDA(cudaMemcpy2DAsync(L_out, (size_t)M * 8, L, (size_t)Mp * 8, (size_t)M * 8, M, cudaMemcpyDeviceToHost, s));
+        GPF_CUDA(cudaStreamSynchronize(s));
+        for (int i = 0; i < M; ++i)
+            for (int j = i + 1; j < M; ++j) L_out[(size_t)i * M + j] = 0.0;
+    }
     if (alpha_out) {
         std::vector<double> a((size_t)Mp * 2);
         GPF_CUDA(cudaMemcpyAsync(a.data(), alpha, a.size() * 8, cudaMemcpyDeviceToHost, s));

@@ -1,0 +1,81 @@
+"""CPU: the GP oracle (oracle/gp.py) against closed forms and the reference's own GP identity.
+
+The reference has no golden GP vectors and tinygp is absent (parity unpinned at that boundary), so
+the restatement is pinned by (i) closed-form 1- and 2-point posteriors, (ii) the identity that
+tests/test_inference.py:86-111 of the reference asserts -- conditioning formula == cached re-predict
+formula -- and (iii) a finite-difference check of the closed-form sound-speed gradient."""
+import numpy as np
+
+from oracle import gp as G
+from tests.gp_cases import query_set, training_set
+
+
+def test_one_point_posterior_closed_form():
+    X = np.array([[0.3]])
+    y = np.array([1.7])
+    la, ls, yerr = np.log(2.5), np.array([np.log(0.4)]), 0.1
+    L = G.build(X, yerr, la, ls)
+    a = G.alpha(L, y)
+    xt = np.array([[0.3], [0.5], [2.0]])
+    k = G.kernel(X, xt, la, ls)[0]
+    amp = np.exp(la)
+    m, v = G.repredict_mean_var(X, la, ls, L, a, 0.0, xt)
+    assert np.allclose(m[0], k * y[0] / (amp + yerr**2), rtol=1e-14)
+    assert np.allclose(v, amp - k**2 / (amp + yerr**2), rtol=1e-13)
+    r = np.sqrt(3) * np.abs(xt[:, 0] - 0.3) / 0.4
+    assert np.allclose(k, amp * (1 + r) * np.exp(-r), rtol=1e-15)
+
+
+def test_two_point_posterior_closed_form():
+    X = np.array([[0.0, 0.0], [1.0, 0.5]])
+    Y = np.array([[1.0, -1.0], [2.0, 0.5]])
+    la, ls, yerr = 0.3, np.log(np.array([0.7, 1.3])), 0.05
+    K = G.kernel(X, X, la, ls) + yerr**2 * np.eye(2)
+    L = G.build(X, yerr, la, ls)
+    assert np.allclose(L @ L.T, K, rtol=1e-15)
+    a = G.alpha(L, Y)
+    assert np.allclose(a, np.linalg.inv(K) @ Y, rtol=1e-13)
+    xt = np.array([[0.2, 0.1], [0.9, 0.6]])
+    ks = G.kernel(X, xt, la, ls)
+    m, v = G.repredict_mean_var(X, la, ls, L, a, 1e-8, xt)
+    assert np.allclose(m, (ks.T @ np.linalg.inv(K) @ Y).T, rtol=1e-12)
+    assert np.allclose(v, np.exp(la) + 1e-8 - np.einsum('ij,ik,kj->j', ks, np.linalg.inv(K), ks), rtol=1e-11)
+
+
+def test_condition_equals_repredict_like_reference_test_inference():
+    for model in ('press', 'shear_x'):
+        c = training_set(40, model)
+        L = G.build(c['X'], c['Yerr'], c['log_amp'], c['log_scale'])
+        a = G.alpha(L, c['Y'])
+        xt = query_set(300, c)
+        noise = 1.4901161193847656e-08
+        m, v = G.repredict_mean_var(c['X'], c['log_amp'], c['log_scale'], L, a, noise, xt)
+        for o in range(c['n_out']):
+            mc, vc = G.condition(c['X'], c['log_amp'], c['log_scale'], L, c['Y'][:, o], noise, xt)
+            assert np.allclose(mc, m[o], rtol=0, atol=1e-8)        # jnp.isclose(..., 0.) of the reference
+            assert np.allclose(vc, v, rtol=0, atol=1e-8)
+        assert np.allclose(G.repredict_mean(c['X'], c['log_amp'], c['log_scale'], a, xt), m, rtol=1e-15)
+
+
+def test_sound_speed_gradient_matches_finite_differences():
+    c = training_set(30, 'press2')
+    L = G.build(c['X'], c['Yerr'], c['log_amp'], c['log_scale'])
+    a = G.alpha(L, c['Y'])
+    xt = query_set(50, c)
+    g = G.dmean_dx0(c['X'], c['log_amp'], c['log_scale'], a, xt)
+    eps = 1e-6
+    xp, xm = xt.copy(), xt.copy()
+    xp[:, 0] += eps
+    xm[:, 0] -= eps
+    fd = (G.repredict_mean(c['X'], c['log_amp'], c['log_scale'], a, xp)[0]
+          - G.repredict_mean(c['X'], c['log_amp'], c['log_scale'], a, xm)[0]) / (2 * eps)
+    assert np.allclose(g, fd, rtol=1e-6, atol=1e-7 * np.abs(fd).max())
+
+
+def test_features_layout():
+    rng = np.random.default_rng(0)
+    q, topo, extra = rng.random((3, 4, 5)), rng.random((4, 4, 5)), rng.random((1, 4, 5))
+    xs = np.arange(1., 8.)
+    F = G.features(q, topo, extra, xs, [0, 2, 6])
+    assert F.shape == (20, 3)
+    assert F[1 * 5 + 3, 0] == q[0, 1, 3] / 1. and F[7, 1] == q[2, 1, 2] / 3. and F[19, 2] == extra[0, 3, 4] / 7.
