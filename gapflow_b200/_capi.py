@@ -70,6 +70,7 @@ SIGNATURES = {
     "gpf_fv_set_scalars": (_i, [_vp, C.POINTER(FvScalars), _vp]),
     "gpf_fv_mass": (_i, [_vp, C.POINTER(C.c_double), _vp]),
     "gpf_fv_closures": (_i, [_vp, _dp, _dp, _dp, _dp, _i, _vp]),
+    "gpf_fv_closures_of": (_i, [_vp, _i, _dp, _dp, _dp, _dp, _i, _vp]),
     "gpf_fv_update_host": (_i, [_vp, _dp, _i, C.POINTER(FvScalars), _vp]),
     "gpf_fv_pass": (_i, [_vp, _i, _vp]),
     "gpf_fv_halo_pack": (_i, [_vp, _i, _dp, _vp]),

@@ -60,7 +60,7 @@ struct FvSolver {
     int get_scalars(gpf_fv_scalars* out, cudaStream_t s);
     int set_scalars(const gpf_fv_scalars* in, cudaStream_t s);
     int mass(double* m, cudaStream_t s);
-    int closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s);
+    int closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s, int rel = 0);
     int pass(int corrector, cudaStream_t s);
     int halo_pack(int rel, double* send, cudaStream_t s);
     int halo_unpack(int rel, const double* recv, cudaStream_t s);

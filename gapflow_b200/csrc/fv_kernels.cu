@@ -644,8 +644,8 @@ template <bool LS, int EOS>
 __global__ void __launch_bounds__(256) fv_closures_kernel(const __grid_constant__ FvParams P, const DevState* st,
                                                           double* const* qbufs, const double* topo,
                                                           const double* extra, double* pr, double* wxz,
-                                                          double* wyz, double* bulk) {
-    const double* q = qbufs[st->cur];
+                                                          double* wyz, double* bulk, int rel) {
+    const double* q = qbufs[(st->cur + rel) % 3];
     const int Nx2 = P.L.Nx + 2, Ny2 = P.L.Ny + 2;
     const size_t np = (size_t)Nx2 * Ny2, plane = P.L.plane;
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1328,7 +1328,7 @@ int FvSolver::mass(double* m, cudaStream_t s) {
     return GPF_OK;
 }
 
-int FvSolver::closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s) {
+int FvSolver::closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s, int rel) {
     const size_t np = (size_t)(cfg.Nx + 2) * (cfg.Ny + 2);
     double* d[4] = {p, wxz, wyz, bulk};
     const int nc[4] = {1, 12, 12, 3};
@@ -1339,10 +1339,10 @@ int FvSolver::closures(double* p, double* wxz, double* wyz, double* bulk, int on
     double** o = on_device ? d : tmp;
     const int blocks = (int)((np + 255) / 256);
     const bool ls = P.has_extra != 0, dh = P.eos.kind == GPF_EOS_DH;
-    if (ls) { if (dh) fv_closures_kernel<true, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]);
-              else    fv_closures_kernel<true, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]); }
-    else    { if (dh) fv_closures_kernel<false, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]);
-              else    fv_closures_kernel<false, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3]); }
+    if (ls) { if (dh) fv_closures_kernel<true, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel);
+              else    fv_closures_kernel<true, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel); }
+    else    { if (dh) fv_closures_kernel<false, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel);
+              else    fv_closures_kernel<false, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel); }
     g_launches++;
     GPF_CUDA(cudaGetLastError());
     if (!on_device) {

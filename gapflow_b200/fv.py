@@ -82,15 +82,17 @@ class FVSolver:
         torch.cuda.current_stream(self.device).synchronize()
         return out
 
-    def closures(self, on_device=False):
-        """(pressure, wall_stress_xz, wall_stress_yz, bulk_viscous_stress) of the current q."""
+    def closures(self, on_device=False, stale=False):
+        """(pressure, wall_stress_xz, wall_stress_yz, bulk_viscous_stress) of the current q, or with
+        ``stale=True`` of the last corrector pass's input: the state the reference's fields are in
+        when ``Problem.write()`` stores them (problem.py:532-540, 629)."""
         if on_device:
             mk = lambda n: torch.empty((n, *self.shape), dtype=torch.float64, device=self.device)
         else:
             mk = lambda n: np.empty((n, *self.shape))
         outs = [mk(1), mk(12), mk(12), mk(3)]
         ptrs = [_ptr(o)[0] for o in outs]
-        _capi.check(self.lib.gpf_fv_closures(self.h, *ptrs, 1 if on_device else 0, self._stream()))
+        _capi.check(self.lib.gpf_fv_closures_of(self.h, 1 if stale else 0, *ptrs, 1 if on_device else 0, self._stream()))
         torch.cuda.current_stream(self.device).synchronize()
         return outs[0][0], outs[1], outs[2], outs[3]
 

@@ -1,0 +1,322 @@
+"""Drop-in ``Problem`` for the fixed-form path: same constructor chain, attributes and files as
+``GaPFlow.problem.Problem`` (problem.py:56-881), with ``update()`` executed by the CUDA library.
+
+Kept from the reference: ``from_yaml`` / ``from_string`` / ``_from_dict`` (problem.py:251-308),
+``run(keep_open)`` (368-410), ``_pre_run`` (412-443), ``update`` (509-569), ``write`` (616-637),
+``_post_run`` (453-503); attributes ``q`` (writable in place, as tests do: tests/test_wave_decay.py:101),
+``dt``, ``step``, ``simtime``, ``residual``, ``residual_buffer``, ``kinetic_energy_old``, ``_stop``;
+properties ``mass``, ``kinetic_energy``, ``v_max``, ``dt_crit``, ``cfl``, ``converged``; sub-objects
+``pressure.pressure`` / ``.v_sound``, ``wall_stress_xz|yz.lower/.upper/.full``, ``bulk_stress.stress``,
+``topo.full/.h/.x/.y``; outputs ``config.yml``, ``topo.nc``, ``sol.nc``, ``history.csv``.
+
+Device residency: ``q`` lives on the GPU.  Reading ``problem.q`` copies it to a host array and marks it
+*exposed*: the next ``update()`` uploads that array again, so in-place edits by user code are honoured;
+a ``run()`` never exposes it, so the loop runs without host traffic: ``write_freq`` updates are enqueued
+at once and the loop condition (problem.py:401) is evaluated on the device.
+
+Not here (host-side): GP surrogate orchestration (database, MD, hyperparameter
+fit), elastic deformation, plotting.  NetCDF: muGrid's ``FileIONetCDF`` is not available; ``sol.nc`` /
+``topo.nc`` are written as NetCDF-3 with ``scipy.io.netcdf_file`` using the reference's field names
+(the exact dimension names of muGrid's files are unverified).
+"""
+import csv
+import io as _io
+import os
+import signal
+from collections import deque
+from datetime import datetime
+
+import numpy as np
+import yaml
+
+from . import config
+from .fv import FVSolver
+from .topography import make_topography, midpoint_grid
+
+
+class _Topo:
+    def __init__(self, grid, geo):
+        self.full = make_topography(grid, geo)
+        self.x, self.y = midpoint_grid(grid)
+
+    @property
+    def h(self):
+        return self.full[0]
+
+    def update(self):            # elastic deformation is out of scope: no-op (topography.py:257-271)
+        pass
+
+
+class _Closure:
+    """Read-only view of one closure field, fetched from the device on access."""
+
+    def __init__(self, problem, index, name):
+        self._p, self._i, self.name = problem, index, name
+        self.geo, self.prop = problem.geo, problem.prop
+        self.is_gp_model = False
+
+    def _get(self):
+        return self._p._closures()[self._i]
+
+
+class _Pressure(_Closure):
+    @property
+    def pressure(self):
+        return self._get()
+
+    @property
+    def v_sound(self):
+        return self._p._scalars().v_sound
+
+    def write(self):
+        pass
+
+
+class _WallStress(_Closure):
+    @property
+    def full(self):
+        return self._get()
+
+    @property
+    def lower(self):
+        return self._get()[:6]
+
+    @property
+    def upper(self):
+        return self._get()[6:]
+
+    def write(self):
+        pass
+
+
+class _BulkStress(_Closure):
+    @property
+    def stress(self):
+        return self._get()
+
+
+class Problem:
+    def __init__(self, options, grid, numerics, prop, geo, gp=None, database=None, extra=None):
+        if gp is not None or database is not None:
+            raise NotImplementedError("GP surrogate orchestration stays on the host (use gapflow_b200.gp.GPModel)")
+        if prop.get('elastic', {}).get('enabled', False):
+            raise NotImplementedError("elastic deformation (ContactMechanics) stays on the host")
+        self.options, self.grid, self.numerics, self.prop, self.geo = options, grid, numerics, prop, geo
+        self.topo = _Topo(grid, geo)
+        shape = (grid['Nx'] + 2, grid['Ny'] + 2)
+        self._extra = None if extra is None else np.broadcast_to(np.asarray(extra, dtype=float), (1, *shape)).copy()
+        self._solver = FVSolver(grid, geo, prop, numerics, topo=self.topo.full, extra=self._extra)
+        self._q_host = np.empty((3, *shape))
+        self._q_synced = False       # _q_host equals the device field
+        self._q_exposed = False      # user code may have edited _q_host
+        self._dt_override = None
+        self.pressure = _Pressure(self, 0, 'zz')
+        self.wall_stress_xz = _WallStress(self, 1, 'xz')
+        self.wall_stress_yz = _WallStress(self, 2, 'yz')
+        self.bulk_stress = _BulkStress(self, 3, 'bulk')
+        self.step = None
+        self.simtime = 0.
+        self.residual = 1.
+        self.residual_buffer = deque([1.], 5)
+        self.tol, self.max_it = numerics['tol'], numerics['max_it']
+        self._stop = False
+        self._clos_cache = None
+        self.history = {"step": [], "time": [], "ekin": [], "residual": [], "vsound": []}
+        self.outdir, self._sol, self._frames = None, None, 0
+        if not options['silent']:
+            self._open_output()
+
+    # -- constructors (problem.py:251-308) --------------------------------------------------
+    @classmethod
+    def from_yaml(cls, fname):
+        with open(fname, 'r') as f:
+            return cls._from_dict(config.read_yaml_input(f))
+
+    @classmethod
+    def from_string(cls, ymlstring):
+        with _io.StringIO(ymlstring) as f:
+            return cls._from_dict(config.read_yaml_input(f))
+
+    @classmethod
+    def _from_dict(cls, d):
+        return cls(d['options'], d['grid'], d['numerics'], d['properties'], d['geometry'],
+                   gp=d.get('gp'), database=None)
+
+    # -- state ------------------------------------------------------------------------------
+    @property
+    def q(self):
+        self._push_dt()
+        if not self._q_synced:
+            self._solver.get_q(self._q_host)
+            self._q_synced = True
+        self._q_exposed = True
+        return self._q_host
+
+    def _sync_to_device(self):
+        if self._q_exposed:
+            self._solver.set_q(self._q_host)
+            self._q_exposed = False
+            self._clos_cache = None
+
+    @property
+    def dt(self):
+        return self._dt_override if self._dt_override is not None else self._solver.scalars().dt
+
+    @dt.setter
+    def dt(self, value):
+        self._dt_override = float(value)
+
+    def _push_dt(self):
+        if self._dt_override is not None:
+            self._solver.set_scalars(dt=self._dt_override)
+            self._dt_override = None
+
+    def _scalars(self):
+        self._sync_to_device()
+        self._push_dt()
+        return self._solver.scalars()
+
+    def _pull(self, sc=None):
+        sc = sc or self._solver.scalars()
+        self.step, self.simtime, self.residual = int(sc.step), sc.simtime, sc.residual
+        self.residual_buffer = deque([sc.residual_buffer[k] for k in range(sc.residual_count)], 5)
+        self.kinetic_energy_old = sc.ekin_old
+        if sc.stop:
+            self._stop = True
+        return sc
+
+    def _closures(self):
+        if self._clos_cache is None:
+            self._sync_to_device()
+            self._clos_cache = self._solver.closures(stale=bool(self.step))
+        return self._clos_cache
+
+    mass = property(lambda self: (self._sync_to_device(), np.float64(self._solver.mass))[1])
+    kinetic_energy = property(lambda self: self._scalars().ekin)
+    v_max = property(lambda self: self._scalars().v_max)
+    dt_crit = property(lambda self: self._scalars().dt_crit)
+    cfl = property(lambda self: self._scalars().cfl)
+
+    @property
+    def converged(self):
+        return bool(np.all(np.array(self.residual_buffer) < self.tol))
+
+    # -- time loop ----------------------------------------------------------------------------
+    def _pre_run(self):
+        """problem.py:412-443 (fixed-form branch)."""
+        self._sync_to_device()
+        self._solver.pre_run(reset_ekin_old=False)
+        self._pull()
+
+    def update(self):
+        """One MacCormack step (problem.py:509-569)."""
+        if self.step is None:
+            self._pre_run()
+        self._sync_to_device()
+        self._push_dt()
+        self._solver.step(1)
+        self._q_synced, self._clos_cache = False, None
+        sc = self._pull()
+        if sc.stop and not self.options['silent']:
+            print("Stopping: NaN or negative density detected (state of the previous step restored).")
+
+    def run(self, keep_open=False):
+        if self.step is None:
+            self._pre_run()
+        self._stop = False
+        self._solver.set_scalars(stop=0)
+        self.history = {"step": [], "time": [], "ekin": [], "residual": [], "vsound": []}
+        silent = self.options['silent']
+        if not silent:
+            print(61 * '-')
+            print(f"{'Step':6s} {'Timestep':10s} {'Time':10s} {'CFL':10s} {'Residual':10s}")
+            print(61 * '-')
+            self.write(params=False)
+        old = {s: signal.signal(s, self._receive_signal) for s in (signal.SIGINT, signal.SIGTERM)}
+        self._tic = datetime.now()
+        wf = max(1, int(self.options['write_freq']))
+        try:
+            while not self.converged and self.step < self.max_it and not self._stop:
+                self._sync_to_device()
+                self._push_dt()
+                n = wf - self.step % wf                       # up to the next multiple of write_freq
+                self._solver.step(n, until_converged=True)    # loop condition evaluated on the device
+                self._q_synced, self._clos_cache = False, None
+                self._pull()
+                if self.step % wf == 0 and not silent:
+                    self.write()
+        finally:
+            for s, h in old.items():
+                signal.signal(s, h)
+        if not keep_open:
+            self._post_run()
+
+    def _receive_signal(self, signum, frame):
+        self._stop = True
+
+    def _post_run(self):
+        walltime = datetime.now() - self._tic
+        silent = self.options['silent']
+        if self.step % max(1, int(self.options['write_freq'])) != 0 and not silent:
+            self.write()
+        if not silent and self._sol is not None:
+            self._sol.close()
+            self._sol = None
+        speed = self.step / max(walltime.total_seconds(), 1e-12)
+        print(33 * '=')
+        print("Total walltime   : ", str(walltime).split('.')[0])
+        print(f"({speed:.2f} steps/s)")
+        print(33 * '=')
+        if not silent:
+            with open(os.path.join(self.outdir, 'history.csv'), 'w', newline='') as f:
+                w = csv.writer(f)
+                w.writerow(list(self.history))
+                w.writerows(zip(*self.history.values()))
+
+    # -- output (problem.py:154-205, 616-637) ---------------------------------------------------
+    def _open_output(self):
+        from scipy.io import netcdf_file
+        name, ts = self.options['output'], self.options['use_tstamp']
+        stamp = datetime.now().replace(microsecond=0).strftime("%Y-%m-%d_%H%M%S") + '_' if ts else ''
+        self.outdir = os.path.join(os.path.dirname(name), stamp + os.path.basename(name))
+        if not os.path.exists(self.outdir):
+            os.makedirs(self.outdir)
+        elif len(os.listdir(self.outdir)) > 0:
+            raise RuntimeError('Output path exists and is not empty.')
+        with open(os.path.join(self.outdir, 'config.yml'), 'w') as f:
+            yaml.dump(dict(version='gapflow_b200', options=self.options, grid=self.grid, numerics=self.numerics,
+                           geo=self.geo, prop=self.prop), f)
+        nx, ny = self.grid['Nx'] + 2, self.grid['Ny'] + 2
+        with netcdf_file(os.path.join(self.outdir, 'topo.nc'), 'w') as t:
+            for d, n in (('frame', None), ('comp4', 4), ('nx', nx), ('ny', ny)):
+                t.createDimension(d, n)
+            v = t.createVariable('topography', 'f8', ('frame', 'comp4', 'nx', 'ny'))
+            v[0] = self.topo.full
+        self._sol = netcdf_file(os.path.join(self.outdir, 'sol.nc'), 'w')
+        for d, n in (('frame', None), ('comp3', 3), ('comp12', 12), ('nx', nx), ('ny', ny)):
+            self._sol.createDimension(d, n)
+        self._sol.createVariable('solution', 'f8', ('frame', 'comp3', 'nx', 'ny'))
+        self._sol.createVariable('pressure', 'f8', ('frame', 'nx', 'ny'))
+        self._sol.createVariable('wall_stress_xz', 'f8', ('frame', 'comp12', 'nx', 'ny'))
+        self._sol.createVariable('wall_stress_yz', 'f8', ('frame', 'comp12', 'nx', 'ny'))
+
+    def write(self, scalars=True, fields=True, params=True):
+        if self.step is None:
+            self._pre_run()
+        if scalars:
+            sc = self._scalars()
+            print(f"{self.step:<6d} {sc.dt:.4e} {self.simtime:.4e} {sc.cfl:.4e} {self.residual:.4e}")
+            for k, v in zip(self.history, (self.step, self.simtime, sc.ekin, self.residual, sc.v_sound)):
+                self.history[k].append(v)
+        if fields and self._sol is not None:
+            p, wxz, wyz, _ = self._closures()
+            if not self._q_synced:
+                self._solver.get_q(self._q_host)
+                self._q_synced = True
+            f = self._frames
+            self._sol.variables['solution'][f] = self._q_host
+            self._sol.variables['pressure'][f] = p
+            self._sol.variables['wall_stress_xz'][f] = wxz
+            self._sol.variables['wall_stress_yz'][f] = wyz
+            self._frames += 1
+            self._sol.flush()

@@ -147,6 +147,13 @@ int gpf_fv_mass(gpf_fv* s, double* mass, void* stream);
 int gpf_fv_closures(gpf_fv* s, double* pressure, double* wall_xz, double* wall_yz,
                     double* bulk, int on_device, void* stream);
 
+/* Same, selecting the state the fields are evaluated on: which = 0 the current q; which = 1 the
+ * input of the last corrector pass (the predictor's output), which is what the reference's
+ * pressure / wall_stress / bulk fields hold when Problem.write() stores them: they are refreshed
+ * at the START of each pass only (problem.py:532-540 vs :563, :629).  Valid after >= 1 step. */
+int gpf_fv_closures_of(gpf_fv* s, int which, double* pressure, double* wall_xz, double* wall_yz,
+                       double* bulk, int on_device, void* stream);
+
 /* One-call host-buffer step for reference-side bindings: uploads q_host (dense, host),
  * runs n x update(), downloads q back, returns the scalars.  Synchronises. */
 int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, void* stream);

@@ -1,0 +1,146 @@
+"""GPU: the reference's own integration tests, run through the drop-in ``Problem``
+(gapflow_b200/problem.py).  YAML texts are the reference's (tests/test_sommerfeld.py:32-68,
+tests/test_mass_conservation.py:30-64, tests/test_flip_axes.py:30-65)."""
+import io
+import os
+from copy import deepcopy
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+from gapflow_b200 import config  # noqa: E402
+
+_PROP = """
+properties:
+    shear: 0.0794
+    bulk: 0.
+    EOS: DH
+    P0: 101325.
+    rho0: 877.7007
+    T0: 323.15
+    C1: {C1}
+    C2: 1.23
+"""
+_PER = "    xE: ['P', 'P', 'P']\n    xW: ['P', 'P', 'P']\n    yS: ['P', 'P', 'P']\n    yN: ['P', 'P', 'P']\n"
+SOMMERFELD = ("options:\n    output: data/journal\n    write_freq: 1000\n    silent: True\n"
+              "grid:\n    dx: 1.e-5\n    dy: 1.\n    Nx: 100\n    Ny: 1\n" + _PER +
+              "geometry:\n    type: journal\n    CR: 1.e-2\n    eps: 0.7\n    U: 0.1\n    V: 0.\n"
+              "numerics:\n    CFL: 0.5\n    adaptive: 1\n    tol: 1e-8\n    dt: 1e-10\n    max_it: 10_000\n"
+              + _PROP.format(C1='3.5e12'))
+JOURNAL2D = ("options:\n    output: data/journal\n    write_freq: 1000\n    silent: True\n"
+             "grid:\n    dx: 1.e-5\n    dy: 1.e-5\n    Nx: {n}\n    Ny: {n}\n" + _PER +
+             "geometry:\n    type: journal\n    CR: 1.e-2\n    eps: 0.7\n    U: 0.1\n    V: 0.\n"
+             "numerics:\n    CFL: 0.5\n    adaptive: 1\n    tol: 1e-8\n    dt: 1e-10\n    max_it: 5000\n"
+             + _PROP.format(C1='3.5e10'))
+
+
+def sommerfeld_solution(x, Lx, mu, U, clearance_ratio, eps, P0):
+    Rb = Lx / (2. * np.pi)
+    c = clearance_ratio * Rb
+    omega = U / Rb
+    prefac = 6. * mu * omega * (Rb / c)**2 * eps
+    return P0 + prefac * np.sin(x / Rb) * (2. + eps * np.cos(x / Rb)) / ((2. + eps**2) * (1. + eps * np.cos(x / Rb))**2)
+
+
+@pytest.mark.parametrize('eps', [0.5, 0.7, 0.9])
+def test_pressure_profile_sommerfeld(eps):
+    """tests/test_sommerfeld.py:115-141."""
+    from gapflow_b200.problem import Problem
+    with io.StringIO(SOMMERFELD) as f:
+        d = config.read_yaml_input(f)
+    d['geometry']['eps'] = eps
+    problem = Problem._from_dict(d)
+    problem.run()
+    p_num = problem.pressure.pressure[1:-1, 1]
+    Lx = problem.grid['Lx']
+    x_ana = np.linspace(0., Lx, 101)
+    x_num = (x_ana[1:] + x_ana[:-1]) / 2.
+    dp = p_num[1] - p_num[0]
+    p_ana = sommerfeld_solution(x_num, Lx, problem.pressure.prop['shear'], problem.pressure.geo['U'],
+                                problem.pressure.geo['CR'], eps, p_num[0] - dp / 2)
+    assert np.linalg.norm(p_ana - p_num) / np.linalg.norm(p_ana) < 0.02
+    assert problem.step > 100
+
+
+def test_mass_conservation():
+    """tests/test_mass_conservation.py:67-77."""
+    from gapflow_b200.problem import Problem
+    problem = Problem.from_string(JOURNAL2D.format(n=50))
+    problem._pre_run()
+    mass_before = problem.mass.copy()
+    for _ in range(50):
+        problem.update()
+    assert np.isclose(problem.mass, mass_before)
+    assert problem.step == 50
+
+
+def test_flip_axes():
+    """tests/test_flip_axes.py:68-96."""
+    from gapflow_b200.problem import Problem
+    with io.StringIO(JOURNAL2D.format(n=100)) as f:
+        input_x = config.read_yaml_input(f)
+    input_y = deepcopy(input_x)
+    input_y['geometry']['U'] = 0.
+    input_y['geometry']['V'] = input_x['geometry']['U']
+    input_y['geometry']['flip'] = True
+    px, py = Problem._from_dict(input_x), Problem._from_dict(input_y)
+    px._pre_run()
+    py._pre_run()
+    for _ in range(5):
+        px.update()
+        py.update()
+        np.testing.assert_almost_equal(px.q[0, 1:-1, 1:-1], py.q[0, 1:-1, 1:-1].T)
+        np.testing.assert_almost_equal(px.q[1, 1:-1, 1:-1], py.q[2, 1:-1, 1:-1].T)
+        np.testing.assert_almost_equal(px.q[2, 1:-1, 1:-1], py.q[1, 1:-1, 1:-1].T)
+
+
+def test_host_edits_of_q_are_honoured_and_match_oracle():
+    """User code writes problem.q[...] between steps (tests/test_wave_decay.py:101)."""
+    from gapflow_b200.problem import Problem
+    from oracle.fv import FVOracle
+    d = config.read_yaml_string(JOURNAL2D.format(n=24))
+    problem = Problem._from_dict(d)
+    o = FVOracle(d['grid'], d['geometry'], d['properties'], d['numerics'])
+    rng = np.random.default_rng(3)
+    bump = 1 + 1e-6 * rng.standard_normal(o.q[0].shape)
+    problem.q[0] *= bump
+    o.q[0] *= bump
+    problem._pre_run()
+    o.dt = d['numerics']['CFL'] * o.dt_crit
+    assert problem.dt == o.dt
+    for k in range(3):
+        problem.update()
+        o.update()
+        assert np.array_equal(problem.q, o.q)
+    problem.q[1] += 1e-4           # edit in place mid-run, no _pre_run
+    o.q[1] += 1e-4
+    problem.update()
+    o.update()
+    assert np.array_equal(problem.q, o.q) and problem.dt == o.dt
+    # stale closure fields, as the reference stores them: those of the corrector pass's input
+    assert np.array_equal(problem.pressure.pressure, o.pressure)
+    assert np.array_equal(problem.wall_stress_xz.full, o.wall_xz)
+    assert np.array_equal(problem.bulk_stress.stress, o.bulk)
+
+
+def test_run_writes_the_reference_files(tmp_path, capsys):
+    from scipy.io import netcdf_file
+    from gapflow_b200.problem import Problem
+    d = config.read_yaml_string(SOMMERFELD.replace('C1: 3.5e12', 'C1: 3.5e10'))
+    d['options'].update(output=str(tmp_path / 'run'), silent=False, use_tstamp=False, write_freq=100)
+    d['numerics']['max_it'] = 250
+    problem = Problem._from_dict(d)
+    problem.run()
+    out = tmp_path / 'run'
+    assert sorted(os.listdir(out)) == ['config.yml', 'history.csv', 'sol.nc', 'topo.nc']
+    rows = (out / 'history.csv').read_text().strip().split('\n')
+    assert rows[0] == 'step,time,ekin,residual,vsound'
+    assert [int(r.split(',')[0]) for r in rows[1:]] == [0, 100, 200, 250]
+    with netcdf_file(str(out / 'sol.nc'), 'r', mmap=False) as f:
+        assert f.variables['solution'].shape == (4, 3, 102, 3)
+        assert f.variables['wall_stress_xz'].shape == (4, 12, 102, 3)
+        assert np.array_equal(f.variables['solution'][3], problem.q)
+    assert "steps/s" in capsys.readouterr().out
