@@ -316,3 +316,64 @@ class InProcessSlabs:
             hi = n + 2 if r == self.world - 1 else n + 1
             out[:, start + lo:start + hi] = loc[:, lo:hi]
         return out
+
+
+# -------------------------------------------------------------------------------------------
+# GP inference across ranks: training set (L, alpha) replicated, query cells partitioned
+# -------------------------------------------------------------------------------------------
+def fold_argmax(vmax, imax, group=None):
+    """Global (maximum variance, index of its FIRST occurrence) from each rank's local pair
+    (gp.py:406, 424: jnp.max / jnp.argmax over all cells; NaN propagates like jnp.max).
+    ``imax`` must already be a GLOBAL cell index.  Works on CPU (gloo) and CUDA (nccl) tensors."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rec = torch.stack([vmax.reshape(()).to(torch.float64), imax.reshape(()).to(torch.float64)])
+    if world == 1:
+        return float(rec[0]), int(rec[1])
+    out = torch.zeros((world, 2), dtype=torch.float64, device=rec.device)
+    dist.all_gather_into_tensor(out.view(-1), rec.view(-1), group=group)
+    v, i = out[:, 0].cpu().numpy(), out[:, 1].cpu().numpy().astype(np.int64)
+    if np.isnan(v).any():
+        k = int(np.min(i[np.isnan(v)]))
+        return float('nan'), k
+    best = v.max()
+    return float(best), int(i[v == best].min())
+
+
+class PartitionedGP:
+    """One GP model replicated on every rank; each rank predicts on its slab's cells only.
+
+    ``offset`` is the global flat index (row-major over the global padded grid) of this rank's
+    first query row, so the arg-max is the reference's global ``imax`` (gp.py:424).  Slab-internal
+    halo rows must not be queried twice: pass the rank's OWNED rows (``owned_rows``)."""
+
+    def __init__(self, model, group=None):
+        self.model, self.group = model, group
+
+    def factor(self, *a, **k):
+        self.model.factor(*a, **k)           # M^3/3 flops, redundantly on every rank: no broadcast of L needed
+
+    def mean(self, X_local):
+        return self.model.repredict_mean(X_local)
+
+    def mean_var(self, X_local, offset, noise=0.0):
+        m, v = self.model.repredict_mean_var(X_local, noise)
+        vmax = torch.tensor(self.model._vmax_norm, dtype=torch.float64, device=X_local.device)
+        imax = torch.tensor(float(self.model.argmax + offset), dtype=torch.float64, device=X_local.device)
+        self.maximum_variance, self.argmax = fold_argmax(vmax, imax, self.group)
+        return m, v
+
+    def v_sound_gradient_max(self, X_local):
+        _, g = self.model.repredict_mean(X_local, with_gradient_max=True)
+        t = torch.tensor([g], dtype=torch.float64, device=X_local.device)
+        if dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return float(t.item())
+
+
+def owned_rows(Nx, rank, world):
+    """Padded-array rows [a, b) of the GLOBAL grid that rank `rank` owns for cell-wise work
+    (every global row exactly once; the edge ranks own the global ghost rows)."""
+    start, n = slab_rows(Nx, world)[rank]
+    a = start + (0 if rank == 0 else 1)
+    b = start + n + (2 if rank == world - 1 else 1)
+    return a, b

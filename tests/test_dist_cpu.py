@@ -79,3 +79,49 @@ def test_neighbour_table():
     assert (HaloExchanger(3, 4, True).lo, HaloExchanger(3, 4, True).hi) == (2, 0)
     assert (HaloExchanger(0, 4, False).lo, HaloExchanger(3, 4, False).hi) == (None, None)
     assert (HaloExchanger(1, 2, True).lo, HaloExchanger(1, 2, True).hi) == (0, 0)
+
+
+def _argmax_worker(rank, world, port, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from gapflow_b200.dist import fold_argmax, owned_rows
+        Nx, Ny2 = 10, 7
+        rng = np.random.default_rng(5)
+        var = rng.random((Nx + 2) * Ny2)
+        var[[11, 40, 70]] = 2.0                       # the maximum occurs three times: the first index wins
+        a, b = owned_rows(Nx, rank, world)
+        loc = var[a * Ny2:b * Ny2]
+        v, i = fold_argmax(torch.tensor(loc.max()), torch.tensor(float(np.argmax(loc) + a * Ny2)))
+        vn = var.copy()
+        vn[55] = np.nan
+        locn = vn[a * Ny2:b * Ny2]
+        has = np.isnan(locn).any()
+        vv = torch.tensor(float('nan') if has else locn.max())
+        ii = torch.tensor(float((np.argmax(np.isnan(locn)) if has else np.argmax(locn)) + a * Ny2))
+        v2, i2 = fold_argmax(vv, ii)
+        if rank == 0:
+            np.savez(out_path, v=v, i=i, i2=i2, nan=np.isnan(v2))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_partitioned_argmax_is_the_global_first_maximum(tmp_path, world):
+    out = str(tmp_path / "am.npz")
+    mp.spawn(_argmax_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    got = np.load(out)
+    assert float(got['v']) == 2.0 and int(got['i']) == 11
+    assert bool(got['nan']) and int(got['i2']) == 55
+
+
+def test_owned_rows_partition_every_row_once():
+    from gapflow_b200.dist import owned_rows
+    for Nx in (5, 64, 101):
+        for w in (1, 2, 3, 8):
+            if w > Nx:
+                continue
+            rows = [owned_rows(Nx, r, w) for r in range(w)]
+            assert rows[0][0] == 0 and rows[-1][1] == Nx + 2
+            assert all(rows[r][1] == rows[r + 1][0] for r in range(w - 1))

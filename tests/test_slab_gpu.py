@@ -90,6 +90,33 @@ for name in ("journal2d_periodic", "slider2d_xDN", "slider2d_allDN_slip"):
     assert abs(sc.ekin - o.kinetic_energy) <= 1e-13 * abs(o.kinetic_energy)
     m = s.mass
     assert abs(m - o.mass) <= 1e-12 * abs(o.mass)
+# GP inference with the query cells partitioned over the ranks (training set replicated)
+from gapflow_b200.gp import GPModel, features
+from gapflow_b200.dist import PartitionedGP, owned_rows, slab_rows
+from oracle import gp as G
+from tests.gp_cases import training_set
+name = "slider2d_allDN_slip"
+d, extra = inputs(name)
+o = build_case(name)
+s = SlabSolver.from_global(d, o.q, o.topo, extra)
+c = training_set(150, 'press_wide')
+xs = np.array([o.q[0].max() / 0.9, 1., 1., 1., 1., 1., 1.])      # maps rho into the training range
+gp = PartitionedGP(GPModel(200, 1, 1))
+gp.factor(c['X'], c['Y'], c['log_amp'], c['log_scale'], c['Yerr'])
+Xloc = features(s.fv, xs, [0])
+Ny2 = d['grid']['Ny'] + 2
+a, b = owned_rows(d['grid']['Nx'], rank, world)
+start = slab_rows(d['grid']['Nx'], world)[rank][0]
+Xown = Xloc[(a - start) * Ny2:(b - start) * Ny2].contiguous()
+m, v = gp.mean_var(Xown, a * Ny2, 1.5e-8)
+Xg = G.features(o.q, o.topo, o.extra, xs, [0])
+L = G.build(c['X'], c['Yerr'], c['log_amp'], c['log_scale'])
+al = G.alpha(L, c['Y'])
+m_ref, v_ref = G.repredict_mean_var(c['X'], c['log_amp'], c['log_scale'], L, al, 1.5e-8, Xg)
+assert np.abs(v.cpu().numpy() - v_ref[a * Ny2:b * Ny2]).max() <= 1e-9
+assert np.abs(m.cpu().numpy()[0] - m_ref[0, a * Ny2:b * Ny2]).max() <= 1e-9 * np.abs(m_ref).max()
+assert gp.argmax == int(np.argmax(v_ref)), (gp.argmax, int(np.argmax(v_ref)))
+assert abs(gp.maximum_variance - v_ref.max()) <= 1e-9
 dist.barrier()
 if rank == 0:
     print("NCCL_SLABS_OK")
