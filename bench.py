@@ -238,7 +238,7 @@ def run_gpu(args):
     if world == 1:
         from gapflow_b200.fv import FVSolver
         q0, topo = initial_fields(d)
-        solver = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo)
+        solver = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, arith=args.arith)
         solver.set_q(q0)
         solver.fill_ghosts()
         solver.pre_run(False)
@@ -248,7 +248,7 @@ def run_gpu(args):
         start, nloc = slab_rows(d['grid']['Nx'], world)[rank]
         q0, topo = initial_fields(d, rows=(start, start + nloc + 2))
         solver = SlabSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, q=q0,
-                            rank=rank, world=world)
+                            rank=rank, world=world, arith=args.arith)
         solver.fill_ghosts()
         solver.pre_run(False)
         step = solver.step
@@ -323,6 +323,30 @@ def run_gpu(args):
                    "SlabSolver.update_host (gpf_fv_upload / slab step / gpf_fv_download per rank)")
                   + ", pinned host q, all ranks' bytes"}
 
+    # ---- the other arithmetic contract, same workload (N=1 only) -------------------------------
+    other = None
+    if world == 1:
+        mode = "exact" if args.arith == "fast" else "fast"
+        del solver
+        torch.cuda.empty_cache()
+        from gapflow_b200.fv import FVSolver
+        s2 = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, arith=mode)
+        s2.set_q(q0)
+        s2.fill_ghosts()
+        s2.pre_run(False)
+        s2.step(args.warmup)
+        torch.cuda.synchronize()
+        k3 = max(3, args.steps // 2)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        s2.step(k3)
+        f1.record()
+        torch.cuda.synchronize()
+        ms2 = f0.elapsed_time(f1) / k3
+        other = {"arith": mode, "value": n * n / (ms2 * 1e-3), "ms_per_step": ms2, "steps": k3,
+                 "step_frac_of_hbm_roofline": n * n / (ms2 * 1e-3) * BYTES_PER_CELL_UPDATE / 1e9 / peak}
+        del s2
+
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:
@@ -338,9 +362,11 @@ def run_gpu(args):
             "config": {"workload": f"2D parabolic slider bearing {n * world}x{n} ({n}x{n} per GPU), FP64, DH EOS, "
                                    "fixed-form stress, x: D/N/N, y periodic, adaptive dt (BASELINE config 2)",
                        "parallelism": f"x-slabs x{world}" if world > 1 else "single GPU",
+                       "arith": args.arith + (" (FMA contraction, a*rcp(b) quotients; parity 1e-12/step, 1e-9/1000 steps)"
+                                              if args.arith == "fast" else " (bit-identical to the reference's NumPy path)"),
                        "l2": "inputs larger than L2: 1.2 GB of fields streamed per step vs 126 MB L2"},
             "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline,
-            "e2e": e2e, "cpu_baseline": cpu,
+            "e2e": e2e, "cpu_baseline": cpu, "other_arith": other,
             "final": {"step": int(sc.step), "dt": sc.dt, "residual": sc.residual},
         }
         print(json.dumps(line))
@@ -360,6 +386,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="gapflow_b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--arith", default="fast", choices=["fast", "exact"],
+                    help="arithmetic contract of the pass kernels (include/gapflow_b200.h: gpf_fv_cfg.arith)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

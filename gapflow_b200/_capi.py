@@ -38,7 +38,7 @@ class FvCfg(C.Structure):
                 ("eos", C.c_int32), ("eos_par", C.c_double * 8), ("rho0", C.c_double),
                 ("adaptive", C.c_int32), ("CFL", C.c_double), ("dt", C.c_double), ("tol", C.c_double),
                 ("max_it", C.c_int32), ("mc_order", C.c_int32), ("has_extra", C.c_int32),
-                ("halo_edge", C.c_int32 * 2), ("reserved", C.c_int32 * 5)]
+                ("halo_edge", C.c_int32 * 2), ("arith", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class FvScalars(C.Structure):
@@ -132,7 +132,11 @@ def check(rc):
         raise GapflowError(rc, load().gpf_last_error().decode())
 
 
-def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), halo_edge=(False, False)):
+ARITH = {'exact': 0, 'fast': 1}
+
+
+def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), halo_edge=(False, False),
+             arith='exact'):
     """Flatten the reference's sanitised dicts (GaPFlow/io.py:139-395) into gpf_fv_cfg.
 
     ``halo=(lo, hi)`` marks x sides whose ghost row comes from a neighbour rank (multi-GPU);
@@ -167,4 +171,5 @@ def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), ha
     c.CFL, c.dt, c.tol = numerics['CFL'], numerics['dt'], numerics['tol']
     c.max_it, c.mc_order = numerics['max_it'], numerics['MC_order']
     c.has_extra = 1 if has_extra else 0
+    c.arith = ARITH[arith]
     return c

@@ -16,10 +16,14 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # (explicit __fma_rn intrinsics are unaffected).
 SOURCES = {
     "fv_kernels.cu": ["-fmad=false"],
+    "fv_pass_exact.cu": ["-fmad=false"],
+    "fv_pass_fast.cu": ["-fmad=true"],
     "api.cu": ["-fmad=false"],
     "gp_kernels.cu": [],
 }
-COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+# GPF_NVCC_DEFS="-DGPF_NST_PRED=3 -DGPF_CTAS_PRED=2": tuning experiments (forces a rebuild by hand: --force)
+EXTRA = os.environ.get("GPF_NVCC_DEFS", "").split()
+COMMON = EXTRA + ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
           "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-I", os.path.join(HERE, "..", "include")]
 
 

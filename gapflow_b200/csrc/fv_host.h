@@ -71,6 +71,22 @@ struct FvSolver {
     int read_cur(cudaStream_t s, int* cur);
 };
 
+// kernel argument block of the pass kernels (fv_pass_kernel.cuh)
+struct PassArgs {
+    CUtensorMap qmap[3];       // box (BY, BX, 3) of each rotating q buffer
+    CUtensorMap q0map[3];      // box (TY, TX, 3): own cells only
+    CUtensorMap topo_map;      // box (BY, BX, 3)
+    CUtensorMap topo2_map;     // box (BY, BX, 2): h, dh/dx
+    CUtensorMap ls_map;        // box (BY, BX, 1)
+    FvParams P;
+    double* qbuf[3];
+    DevState* st;
+    Partial* partial;
+    int* pflags;
+    int until_converged;
+    int ntiles;
+};
+
 // parameter packing shared with the pure-function entry points
 int pack_params(const gpf_fv_cfg& c, FvParams* P);
 Layout make_layout(int Nx, int Ny);

@@ -9,388 +9,6 @@
 
 namespace gpf {
 
-// ---- shared-memory carve-up of the pass kernel (every TMA destination 128-byte aligned) -------
-constexpr int BOX = BX * BY;                                    // doubles per staged plane
-constexpr size_t al128(size_t x) { return (x + 127) / 128 * 128; }
-constexpr size_t BOX3_BYTES = al128((size_t)3 * BOX * 8);
-constexpr size_t BOX2_BYTES = al128((size_t)2 * BOX * 8);
-constexpr size_t BOX1_BYTES = al128((size_t)BOX * 8);
-constexpr size_t OWN3_BYTES = (size_t)3 * TX * TY * 8;          // q0 of the tile's own cells (corrector)
-constexpr int NSTAGE = 2;                                       // TMA ring depth
-
-template <bool CORR, bool LS, bool XF>
-struct Smem {
-    static constexpr size_t Q = 0;
-    static constexpr size_t TOPO = Q + BOX3_BYTES;
-    static constexpr size_t LSO = TOPO + (XF ? BOX2_BYTES : BOX3_BYTES);    // x-driven film: dh/dy plane not loaded
-    static constexpr size_t Q0 = LSO + (LS ? BOX1_BYTES : 0);
-    static constexpr size_t STAGE = Q0 + (CORR ? OWN3_BYTES : 0);
-    static constexpr size_t CLOS = NSTAGE * STAGE;              // p, t0, t1, t2 of the staged cells
-    static constexpr size_t BAR = CLOS + al128((size_t)4 * BOX * 8);
-    static constexpr size_t RED = BAR + 128;                    // 2 mbarriers, 2 tile flags
-    static constexpr size_t TOTAL = RED + (FV_THREADS / 32) * 4 * 8;
-    static constexpr uint32_t TX_BYTES = (uint32_t)(3 * BOX * 8) + (uint32_t)((XF ? 2 : 3) * BOX * 8) +
-                                         (LS ? (uint32_t)(BOX * 8) : 0u) + (CORR ? (uint32_t)OWN3_BYTES : 0u);
-};
-
-struct PassArgs {
-    CUtensorMap qmap[3];       // box (BY, BX, 3) of each rotating q buffer
-    CUtensorMap q0map[3];      // box (TY, TX, 3): own cells only
-    CUtensorMap topo_map;      // box (BY, BX, 3)
-    CUtensorMap topo2_map;     // box (BY, BX, 2): h, dh/dx
-    CUtensorMap ls_map;        // box (BY, BX, 1)
-    FvParams P;
-    double* qbuf[3];
-    DevState* st;
-    Partial* partial;
-    int* pflags;
-    int until_converged;
-    int ntiles;
-};
-
-// ---- per-cell arithmetic of the two phases (FAST: branch-free divisions, see closures.cuh) ----
-// The straight-line quotients need every operand in [2^-100, 2^100] (jx, jy may also be exactly 0).
-// Topography, slip length and the scalar parameters are checked once when they are uploaded
-// (FvParams::static_fast); the solution is checked here, per staged cell, on the integer pipe.
-__device__ __forceinline__ bool q_in_fast_range(const Cell& c) {
-    return in_fast_range_nz(c.q0) & in_fast_range(c.q1) & in_fast_range(c.q2);
-}
-
-struct Clos4 { double p, t0, t1, t2; };
-
-template <bool LS, int EOS, bool FAST, bool XF>
-__device__ __forceinline__ Clos4 phase1_cell(const Cell& c, const FvParams& P) {
-    Clos4 r;
-    r.p = eos_pressure<EOS, FAST>(c.q0, P.eos);
-    stress_avg<LS, FAST, XF>(c, reinterpret_cast<const Visc&>(P.visc), r.t0, r.t1, r.t2);
-    return r;
-}
-template <bool LS, int EOS>
-__device__ __noinline__ Clos4 phase1_cell_slow(const Cell c, const FvParams& P) {
-    return phase1_cell<LS, EOS, false, false>(c, P);
-}
-
-struct Nb { double q1x, Ax, t2x, q2y, t2y, Cy; };   // neighbour fluxes: Fx = (q1, A, t2), Fy = (q2, t2, C)
-struct Q3 { double v0, v1, v2; };
-
-// fluxes (integrate.py:65-75), wall stresses (stress.py:328-362), source (integrate.py:118-128)
-// and the update q - dt*(fX/dx + fY/dy - src) (problem.py:558) of one interior cell.
-// flux = -d*(F[nb] - F[own]): the sign flip is exact and done on the integer pipe.  The xz + yz
-// field sums of problem.py:554-555 are u/2 + u/2 == u (exact) and u + 0.
-template <bool LS, bool FAST, bool XF>
-__device__ __forceinline__ Q3 phase2_cell(const Cell& c, const Clos4& k, const Nb& n, const FvParams& P,
-                                          unsigned sbit, double dt) {
-    const Visc& V = reinterpret_cast<const Visc&>(P.visc);
-    const double fx0 = flip(n.q1x - c.q1, sbit);
-    const double fx1 = flip(n.Ax - (k.p + k.t0), sbit);
-    const double fx2 = flip(n.t2x - k.t2, sbit);
-    const double fy0 = flip(n.q2y - c.q2, sbit);
-    const double fy1 = flip(n.t2y - k.t2, sbit);
-    const double fy2 = flip(n.Cy - (k.p + k.t1), sbit);
-    double b3, b4, u[6];
-    stress_bottom<LS, FAST, XF>(c, V, b3, b4);
-    stress_top<LS, false, FAST, XF>(c, V, u);
-    const double rh = rcp_sel<FAST>(c.h);
-    double s0, s1, s2;
-    if constexpr (XF) {      // hy == 0: the hy terms are exact zeros
-        s0 = div_sel<FAST>(-c.q1 * c.hx, c.h, rh);
-        s1 = div_sel<FAST>((k.t0 - u[0]) * c.hx + u[4] - b4, c.h, rh);
-        s2 = div_sel<FAST>((k.t2 - u[5]) * c.hx + u[3] - b3, c.h, rh);
-    } else {
-        s0 = div_sel<FAST>(-c.q1 * c.hx - c.q2 * c.hy, c.h, rh);
-        s1 = div_sel<FAST>((k.t0 - u[0]) * c.hx + (k.t2 - u[5]) * c.hy + u[4] - b4, c.h, rh);
-        s2 = div_sel<FAST>((k.t2 - u[5]) * c.hx + (k.t1 - u[1]) * c.hy + u[3] - b3, c.h, rh);
-    }
-    Q3 q;
-    q.v0 = c.q0 - dt * (div_sel<FAST>(fx0, P.dx, P.rdx) + div_sel<FAST>(fy0, P.dy, P.rdy) - s0);
-    q.v1 = c.q1 - dt * (div_sel<FAST>(fx1, P.dx, P.rdx) + div_sel<FAST>(fy1, P.dy, P.rdy) - s1);
-    q.v2 = c.q2 - dt * (div_sel<FAST>(fx2, P.dx, P.rdx) + div_sel<FAST>(fy2, P.dy, P.rdy) - s2);
-    return q;
-}
-template <bool LS>
-__device__ __noinline__ Q3 phase2_cell_slow(const Cell c, const Clos4 k, const Nb n, const FvParams& P,
-                                            unsigned sbit, double dt) {
-    return phase2_cell<LS, false, false>(c, k, n, P, sbit, dt);
-}
-
-// exact flags of one stored cell, off the hot path (problem.py:320-332)
-__device__ __noinline__ int cell_flags_slow(double a, double b, double c, double w) {
-    int f = 0;
-    if (a != a || b != b || c != c) f |= FLAG_NAN;
-    if (a < 0.0) f |= FLAG_NEG;
-    if (!(w >= 0.0)) f |= FLAG_VNAN;
-    return f;
-}
-
-// Persistent kernel: fv_ctas_per_sm(CORR) CTAs per SM walk the tiles round-robin.  A 2-deep ring of
-// TMA-staged boxes keeps the loads of tile n+1 in flight under the arithmetic of tile n.
-template <bool CORR, bool LS, int EOS, bool XF>
-__global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kernel(const __grid_constant__ PassArgs A) {
-    using S = Smem<CORR, LS, XF>;
-    extern __shared__ __align__(1024) unsigned char smem[];      // no static shared memory: offset 0
-    double* const sp = reinterpret_cast<double*>(smem + S::CLOS);
-    double* const st0 = sp + BOX;
-    double* const st1 = st0 + BOX;
-    double* const st2 = st1 + BOX;
-    uint64_t* const bar = reinterpret_cast<uint64_t*>(smem + S::BAR);
-    int* const sbad = reinterpret_cast<int*>(smem + S::BAR + 32);
-    double* const sred = reinterpret_cast<double*>(smem + S::RED);
-
-    const FvParams& P = A.P;
-    const DevState* st = A.st;
-    // run-loop condition (problem.py:401) evaluated on the device; uniform per grid
-    if (st->stop || (A.until_converged && st->halt)) return;
-
-    const int tid = threadIdx.x;
-    const int cur = st->cur;
-    const int in_idx = CORR ? (cur + 1) % 3 : cur;
-    const int out_idx = CORR ? (cur + 2) % 3 : (cur + 1) % 3;
-    // MacCormack order (problem.py:521-522)
-    const int sw = (P.mc_order == 0) ? (((st->step & 1LL) == 0) ? 1 : -1) : P.mc_order;
-    const int d = CORR ? -sw : sw;
-    const double dt = st->dt;
-    const int ox = (d > 0) ? 1 : 0;         // own cells sit at box offset (ox, oy)
-    constexpr int oy = 2;                   // box origin = own column - 2 (even -> 16-byte aligned)
-    const int Nx = P.L.Nx, Ny = P.L.Ny;
-    const size_t plane = P.L.plane;
-    const int pitch = P.L.pitch;
-    const int nty = P.nblk_x;               // tiles along y
-
-    // tiles are walked round-robin: tile t = (bx, by), bx = t / nty along x, by = t % nty along y.
-    // The walk advances (bx, by) by a fixed step, so no division runs in the loop.
-    const int step_bx = (int)gridDim.x / nty, step_by = (int)gridDim.x % nty;
-
-    auto issue = [&](int bx, int by, int stage) {          // thread 0 only
-        const int i0 = 1 + bx * TX, j0 = 1 + by * TY;
-        unsigned char* base = smem + (size_t)stage * S::STAGE;
-        uint64_t* b = bar + stage;
-        mbar_expect_tx(b, S::TX_BYTES);
-        const int cm = (j0 - oy) + 1;       // memory column of the box origin (j0 = 1 + 64k -> even)
-        const int cx = i0 - ox;
-        tma_load_3d(base + S::Q, &A.qmap[in_idx], b, cm, cx, 0);
-        tma_load_3d(base + S::TOPO, XF ? &A.topo2_map : &A.topo_map, b, cm, cx, 0);
-        if (LS) tma_load_3d(base + S::LSO, &A.ls_map, b, cm, cx, 0);
-        if (CORR) tma_load_3d(base + S::Q0, &A.q0map[cur], b, j0 + 1, i0, 0);
-    };
-
-    if (tid == 0) {
-        mbar_init(bar, 1);
-        mbar_init(bar + 1, 1);
-        fence_mbar_init();
-        sbad[0] = 0;
-        sbad[1] = 0;
-    }
-    __syncthreads();
-    int tile = blockIdx.x;
-    int bx = tile / nty, by = tile % nty;
-    if (tid == 0 && tile < A.ntiles) issue(bx, by, 0);
-
-    // thread -> cells: column ty, rows 2g and 2g+1 of the tile
-    const int ty = tid & (TY - 1);
-    const int g = tid >> 6;
-    static_assert(FV_THREADS / TY * 2 == TX && TY == 64, "thread-to-cell map assumes 2 rows per thread");
-    const int o_own = (2 * g + ox) * BY + ty + oy;                 // box offset of the first own cell
-    // halo cell of this thread (warps 0-1: the halo row; warp 2: the halo column, lanes >= TX repeat
-    // cell TX-1 so the warp stays convergent; the duplicate stores write identical values)
-    const int hrow = (d > 0) ? 0 : TX, hcol = (d > 0) ? oy - 1 : oy + TY;
-    const int hcl = (tid - TY < TX - 1) ? tid - TY : TX - 1;
-    const int o_halo = (tid < TY) ? hrow * BY + tid + oy : (hcl + ox) * BY + hcol;
-    const bool has_halo = tid < TY + 32;                           // warp-uniform
-    const int on_dx = -d * BY, on_dy = -d;                        // offsets to the neighbours differenced against
-    const unsigned sbit = (d > 0) ? 0x80000000u : 0u;             // -d * x == x with its sign bit flipped when d = +1
-    const bool dt_fast = in_fast_range_nz(dt) && P.static_fast;
-
-    double* const qout = A.qbuf[out_idx];
-    const double* const q0b = A.qbuf[cur];
-    // this thread's first own cell of tile (0, 0); a tile adds bx*TX rows and by*TY columns
-    const size_t a_thread = (size_t)(1 + 2 * g) * pitch + (1 + ty) + 1;
-    Red red;
-    red.ekin = 0.0;
-    red.vmax2 = -INFINITY;
-    red.cs2 = -INFINITY;
-    red.flags = 0;
-    constexpr bool DEFER_C = CORR && (EOS == GPF_EOS_DH);
-    double run_thr = -INFINITY;                                    // (1 - 2^-40) x the largest density this warp has seen
-
-    auto store_clos = [&](int o, const Clos4& k) { sp[o] = k.p; st0[o] = k.t0; st1[o] = k.t1; st2[o] = k.t2; };
-
-    for (int it = 0; tile < A.ntiles; ++it) {
-        const int stage = it & 1;
-        // next tile of this CTA
-        const int ntile = tile + (int)gridDim.x;
-        int nbx = bx + step_bx, nby = by + step_by;
-        if (nby >= nty) { nby -= nty; ++nbx; }
-        if (tid == 0 && ntile < A.ntiles) issue(nbx, nby, stage ^ 1);   // stage^1 was released by the barrier ending tile it-1
-        const unsigned char* base = smem + (size_t)stage * S::STAGE;
-        const double* sq = reinterpret_cast<const double*>(base + S::Q);
-        const double* stp = reinterpret_cast<const double*>(base + S::TOPO);
-        const double* sls = reinterpret_cast<const double*>(base + S::LSO);
-        const double* sq0 = reinterpret_cast<const double*>(base + S::Q0);
-        mbar_wait(bar + stage, (it >> 1) & 1);
-
-        auto load_cell = [&](int o) {
-            Cell c;
-            c.q0 = sq[o];
-            c.q1 = sq[BOX + o];
-            c.q2 = sq[2 * BOX + o];
-            c.h = stp[o];
-            c.hx = stp[BOX + o];
-            c.hy = XF ? 0.0 : stp[2 * BOX + o];
-            c.Ls = LS ? sls[o] : 0.0;
-            return c;
-        };
-
-        // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
-        {
-            const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
-            const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb);
-            if (__all_sync(0xffffffffu, ok) && P.static_fast) {   // warp-uniform
-                store_clos(o_own, phase1_cell<LS, EOS, true, XF>(ca, P));
-                store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF>(cb, P));
-            } else {
-                store_clos(o_own, phase1_cell_slow<LS, EOS>(ca, P));
-                store_clos(o_own + BY, phase1_cell_slow<LS, EOS>(cb, P));
-                sbad[stage] = 1;          // this tile takes the plain-division path in phase 2
-            }
-        }
-        if (has_halo) {
-            const Cell ch = load_cell(o_halo);
-            if (__all_sync(0xffffffffu, q_in_fast_range(ch)) && P.static_fast) {
-                store_clos(o_halo, phase1_cell<LS, EOS, true, XF>(ch, P));
-            } else {
-                store_clos(o_halo, phase1_cell_slow<LS, EOS>(ch, P));
-                sbad[stage] = 1;
-            }
-        }
-        __syncthreads();
-
-        // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
-        const bool fast = (sbad[stage] == 0) && dt_fast;                           // tile-uniform
-        if (tid == 0) sbad[stage ^ 1] = 0;                                          // next tile's flag
-        const int i0 = 1 + bx * TX, j0 = 1 + by * TY;
-        const bool full = (i0 + TX - 1 <= Nx) && (j0 + TY - 1 <= Ny);
-        const bool btile = (bx == 0) | (i0 + TX - 1 >= Nx) | (by == 0) | (j0 + TY - 1 >= Ny);
-        const size_t a_tile = a_thread + (size_t)(bx * TX) * pitch + (size_t)(by * TY);
-        double rho[2] = {-INFINITY, -INFINITY};
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            // cells of a ragged tile that lie outside the grid are computed (on zero-filled or
-            // foreign data) but neither stored nor counted: every lane must reach the warp votes
-            const bool act = full || ((i0 + 2 * g + k <= Nx) && (j0 + ty <= Ny));
-            const int o = o_own + k * BY;
-            const Cell c = load_cell(o);
-            Clos4 kk;
-            kk.p = sp[o]; kk.t0 = st0[o]; kk.t1 = st1[o]; kk.t2 = st2[o];
-            Nb nb;
-            nb.q1x = sq[BOX + o + on_dx]; nb.Ax = sp[o + on_dx] + st0[o + on_dx]; nb.t2x = st2[o + on_dx];
-            nb.q2y = sq[2 * BOX + o + on_dy]; nb.t2y = st2[o + on_dy]; nb.Cy = sp[o + on_dy] + st1[o + on_dy];
-            const Q3 qq = fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
-                               : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
-            double qn0 = qq.v0, qn1 = qq.v1, qn2 = qq.v2;
-            if (CORR) {
-                const int oo = (2 * g + k) * TY + ty;
-                qn0 = (qn0 + sq0[oo]) * 0.5;                       // problem.py:563 ((q + q0)/2.0, exact)
-                qn1 = (qn1 + sq0[TX * TY + oo]) * 0.5;
-                qn2 = (qn2 + sq0[2 * TX * TY + oo]) * 0.5;
-                // kinetic energy and speed (problem.py:342, 347): w = (jx^2 + jy^2)/rho
-                const double num = qn1 * qn1 + qn2 * qn2;
-                const bool wok = fast & in_fast_range_nz(qn0) & in_fast_range(num);
-                double w;
-                if (__all_sync(0xffffffffu, wok)) w = div_fast(num, qn0, rcp_sel<true>(qn0));
-                else w = num / qn0;
-                if (act) {
-                    red.ekin += w * 0.5;
-                    red.vmax2 = fmax(red.vmax2, w);
-                    // NaN anywhere in the cell makes w NaN; a negative density has its sign bit set
-                    if (!(w >= 0.0) || __double2hiint(qn0) < 0) red.flags |= cell_flags_slow(qn0, qn1, qn2, w);
-                    if (DEFER_C) rho[k] = qn0;
-                    else red_accum_c<EOS>(red, qn0, P.eos);
-                }
-            }
-            if (act) {
-                double* dst = qout + a_tile + (size_t)k * pitch;
-                dst[0] = qn0;
-                dst[plane] = qn1;
-                dst[2 * plane] = qn2;
-            }
-            // ghost cells derived from this cell (problem.py:560 / 576)
-            if (btile) {
-                const int i = i0 + 2 * g + k, j = j0 + ty;
-                if (act && ((i == 1) | (i == Nx) | (j == 1) | (j == Ny))) {
-                    const Red br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b);
-                    if (CORR) {
-                        red.ekin += br.ekin;
-                        red.vmax2 = fmax(red.vmax2, br.vmax2);
-                        red.cs2 = fmax(red.cs2, br.cs2);
-                        red.flags |= br.flags;
-                    }
-                }
-            }
-        }
-        if (DEFER_C) {
-            // v_sound = max sqrt(dp/drho).  For Dowson-Higginson dp/drho = K/(C2*rho0 - rho)^2 rises
-            // monotonically with rho below the pole, by >= 7e-13 relative per 2^-40 relative step in
-            // rho (for rho >= rho0/2), while its 7-operation FP64 evaluation errs by < 1e-15.  So the
-            // cell that attains the maximum of the ROUNDED values lies within 2^-40 of the largest
-            // density: only cells that close to the largest density this warp has met so far are
-            // evaluated -- bit-identical to evaluating every cell.  Outside the proven range every
-            // cell is evaluated.  Positive doubles order like their bit patterns: the warp's exact
-            // maximum takes two 32-bit REDUX operations.
-            const double m = fmax(rho[0], rho[1]);
-            const int whi = __reduce_max_sync(0xffffffffu, __double2hiint(m));
-            const unsigned wlo = __reduce_max_sync(0xffffffffu, (__double2hiint(m) == whi) ? (unsigned)__double2loint(m) : 0u);
-            const double wmax = __hiloint2double(whi, (int)wlo);
-            const bool ok = (wmax >= 0.5 * P.eos.p[0]) && (wmax <= P.eos.p[4]);
-            if (!ok) {
-#pragma unroll
-                for (int k = 0; k < 2; ++k)
-                    if (rho[k] != -INFINITY) red_accum_c<EOS>(red, rho[k], P.eos);
-            } else if (wmax >= run_thr) {
-                const double thr = wmax * (1.0 - 0x1p-40);
-#pragma unroll
-                for (int k = 0; k < 2; ++k)
-                    if (rho[k] >= thr) red_accum_c<EOS>(red, rho[k], P.eos);
-                run_thr = fmax(run_thr, thr);
-            }
-        }
-        __syncthreads();          // closures and this stage's boxes are free again
-        tile = ntile; bx = nbx; by = nby;
-    }
-
-    if (CORR) {
-        // warp shuffles, then one record per CTA (fixed order: deterministic)
-        double e = warp_sum(red.ekin);
-        double vm = warp_max(red.vmax2);
-        double cm = warp_max(red.cs2);
-        int fl = red.flags;
-#pragma unroll
-        for (int oo = 16; oo > 0; oo >>= 1) fl |= __shfl_xor_sync(0xffffffffu, fl, oo);
-        const int w = tid >> 5, lane = tid & 31;
-        if (lane == 0) {
-            sred[w * 4 + 0] = e;
-            sred[w * 4 + 1] = vm;
-            sred[w * 4 + 2] = cm;
-            sred[w * 4 + 3] = (double)fl;
-        }
-        __syncthreads();
-        if (tid == 0) {
-            double E = 0.0, VM = -INFINITY, CM = -INFINITY;
-            int F = 0;
-            for (int ww = 0; ww < FV_THREADS / 32; ++ww) {
-                E += sred[ww * 4 + 0];
-                VM = fmax(VM, sred[ww * 4 + 1]);
-                CM = fmax(CM, sred[ww * 4 + 2]);
-                F |= (int)sred[ww * 4 + 3];
-            }
-            A.partial[blockIdx.x].ekin = E;
-            A.partial[blockIdx.x].vmax2 = VM;
-            A.partial[blockIdx.x].cs2 = CM;
-            A.partial[blockIdx.x].mass = 0.0;
-            A.pflags[blockIdx.x] = F;
-        }
-    }
-}
-
 // =====================================================================================
 // Scalar bookkeeping kernels
 // =====================================================================================
@@ -841,6 +459,7 @@ static int pass_ctas(int ntiles, bool corr) {
 int pack_params(const gpf_fv_cfg& c, FvParams* P) {
     if (c.Nx < 1 || c.Ny < 1) { set_error("Nx, Ny must be >= 1"); return GPF_E_INVALID; }
     if (c.mc_order != 0 && c.mc_order != 1 && c.mc_order != -1) { set_error("MC_order must be -1, 0 or 1"); return GPF_E_INVALID; }
+    if (c.arith != GPF_ARITH_EXACT && c.arith != GPF_ARITH_FAST) { set_error("arith must be GPF_ARITH_EXACT or GPF_ARITH_FAST"); return GPF_E_INVALID; }
     P->L = make_layout(c.Nx, c.Ny);
     P->dx = c.dx; P->dy = c.dy;
     P->rdx = 1.0 / c.dx; P->rdy = 1.0 / c.dy;     // RN reciprocals for div_fast
@@ -1098,17 +717,9 @@ int FvSolver::download(int field, double* data, int ncomp, int on_device, cudaSt
     return GPF_OK;
 }
 
-template <bool CORR, bool LS, int EOS, bool XF>
-static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
-    using Sm = Smem<CORR, LS, XF>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
-        attr_set = true;
-    }
-    fv_pass_kernel<CORR, LS, EOS, XF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
-    return GPF_OK;
-}
+// the pass kernels live in fv_pass_exact.cu / fv_pass_fast.cu (same source, two arithmetic contracts)
+int launch_pass_exact(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, int n, cudaStream_t s);
+int launch_pass_fast(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, int n, cudaStream_t s);
 
 template <bool CORR>
 static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
@@ -1122,17 +733,8 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
     const bool dh = S.P.eos.kind == GPF_EOS_DH;
     const bool xf = S.P.xflow != 0;
     const int n = pass_ctas(A.ntiles, CORR);
-    int rc;
-    switch ((ls ? 4 : 0) + (dh ? 2 : 0) + (xf ? 1 : 0)) {
-    case 0: rc = launch_pass_variant<CORR, false, -1, false>(A, n, s); break;
-    case 1: rc = launch_pass_variant<CORR, false, -1, true>(A, n, s); break;
-    case 2: rc = launch_pass_variant<CORR, false, GPF_EOS_DH, false>(A, n, s); break;
-    case 3: rc = launch_pass_variant<CORR, false, GPF_EOS_DH, true>(A, n, s); break;
-    case 4: rc = launch_pass_variant<CORR, true, -1, false>(A, n, s); break;
-    case 5: rc = launch_pass_variant<CORR, true, -1, true>(A, n, s); break;
-    case 6: rc = launch_pass_variant<CORR, true, GPF_EOS_DH, false>(A, n, s); break;
-    default: rc = launch_pass_variant<CORR, true, GPF_EOS_DH, true>(A, n, s); break;
-    }
+    const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, n, s)
+                                                   : launch_pass_exact(A, CORR, ls, dh, xf, n, s);
     if (rc) return rc;
     g_launches++;
     return debug_check(CORR ? "fv_pass_kernel<corrector>" : "fv_pass_kernel<predictor>", s);

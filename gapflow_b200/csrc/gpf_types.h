@@ -42,7 +42,15 @@ constexpr int FV_THREADS = 256;     // 2 cells per thread
 #ifndef GPF_CTAS_CORR
 #define GPF_CTAS_CORR 2
 #endif
-constexpr int fv_ctas_per_sm(bool corr) { return corr ? GPF_CTAS_CORR : GPF_CTAS_PRED; }
+__host__ __device__ constexpr int fv_ctas_per_sm(bool corr) { return corr ? GPF_CTAS_CORR : GPF_CTAS_PRED; }
+// depth of the TMA ring per pass
+#ifndef GPF_NST_PRED
+#define GPF_NST_PRED 2
+#endif
+#ifndef GPF_NST_CORR
+#define GPF_NST_CORR 2
+#endif
+__host__ __device__ constexpr int fv_nstage(bool corr) { return corr ? GPF_NST_CORR : GPF_NST_PRED; }
 
 // storage layout: plane-major, rows padded.  Cell (i, j) of the reference's padded array
 // (i in [0, Nx+1], j in [0, Ny+1]) lives at  comp*plane + i*pitch + (j + 1):

@@ -90,7 +90,7 @@ class SlabSolver:
     rows ``start .. start+n+1`` of the global padded arrays (shape ``(ncomp, n+2, Ny+2)``)."""
 
     def __init__(self, grid, geo, prop, numerics, topo, q=None, extra=None, rank=None, world=None, group=None,
-                 device=None, exchanger=None):
+                 device=None, exchanger=None, arith='exact'):
         from .fv import FVSolver
         self.rank = dist.get_rank(group) if rank is None else rank
         self.world = dist.get_world_size(group) if world is None else world
@@ -103,7 +103,7 @@ class SlabSolver:
         halo = (self.ex.lo is not None, self.ex.hi is not None)
         edge = (halo[0] and self.rank == 0, halo[1] and self.rank == self.world - 1)    # periodic ring ends
         self.fv = FVSolver(g, geo, prop, numerics, topo=topo, extra=extra, device=device, halo=halo,
-                           halo_edge=edge)
+                           halo_edge=edge, arith=arith)
         self.lib, self.h = self.fv.lib, self.fv.h
         dev = self.fv.device
         Ny2 = g['Ny'] + 2

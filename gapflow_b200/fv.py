@@ -23,7 +23,7 @@ def _ptr(x):
 
 class FVSolver:
     def __init__(self, grid, geo, prop, numerics, topo, extra=None, device=None, halo=(False, False),
-                 halo_edge=(False, False)):
+                 halo_edge=(False, False), arith='exact'):
         if not torch.cuda.is_available():
             raise _capi.GapflowLibraryError("gapflow_b200 needs a CUDA device; there is no CPU path")
         self.lib = _capi.load()
@@ -32,7 +32,8 @@ class FVSolver:
         self.grid, self.geo, self.prop, self.numerics = grid, geo, prop, numerics
         self.shape = (grid['Nx'] + 2, grid['Ny'] + 2)
         has_extra = extra is not None and bool(np.any(np.asarray(extra) != 0.0))
-        self.cfg = _capi.make_cfg(grid, geo, prop, numerics, has_extra=has_extra, halo=halo, halo_edge=halo_edge)
+        self.cfg = _capi.make_cfg(grid, geo, prop, numerics, has_extra=has_extra, halo=halo, halo_edge=halo_edge,
+                                  arith=arith)
         nbytes = C.c_size_t()
         _capi.check(self.lib.gpf_fv_workspace_bytes(C.byref(self.cfg), C.byref(nbytes)))
         self.workspace = torch.empty(nbytes.value, dtype=torch.uint8, device=self.device)

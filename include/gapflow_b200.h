@@ -40,6 +40,9 @@ enum { GPF_BC_P = 0, GPF_BC_D = 1, GPF_BC_N = 2, GPF_BC_HALO = 3 };
 /* sides: x0 = array index 0, x1 = index Nx+1, y0 = index 0, y1 = index Ny+1 */
 enum { GPF_SIDE_X0 = 0, GPF_SIDE_X1 = 1, GPF_SIDE_Y0 = 2, GPF_SIDE_Y1 = 3 };
 
+/* arithmetic contract of the pass kernels (gpf_fv_cfg.arith) */
+enum { GPF_ARITH_EXACT = 0, GPF_ARITH_FAST = 1 };
+
 /* field ids for upload/download */
 enum { GPF_F_Q = 0, GPF_F_TOPO = 1, GPF_F_EXTRA = 2 };
 
@@ -67,7 +70,11 @@ typedef struct gpf_fv_cfg {
     int32_t halo_edge[2];      /* GPF_BC_HALO x side that is the global domain's periodic edge: its
                                   ghost row is part of the reference's padded array and is counted
                                   in the reductions (problem.py:337-347) by this rank */
-    int32_t reserved[5];
+    int32_t arith;             /* GPF_ARITH_EXACT (0): every operation rounded as the reference's NumPy
+                                  expressions round it -> bit-identical fields for the + - * / sqrt EOS;
+                                  GPF_ARITH_FAST (1): FMA contraction and a*rcp(b) quotients in the pass
+                                  kernels -> within 1e-12 relative per step, ~1.4x faster */
+    int32_t reserved[4];
 } gpf_fv_cfg;
 
 /* Host-visible scalars of the time loop (GaPFlow/problem.py:314-362, 571-586). */

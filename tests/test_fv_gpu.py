@@ -30,11 +30,14 @@ def relerr(a, b):
     return float(max(e_rho, e_j))
 
 
-def make_solver(name, oracle=None):
+ARITH = ['exact', 'fast']      # gpf_fv_cfg.arith: bit-identical arithmetic / contracted arithmetic (1e-12 per step)
+
+
+def make_solver(name, oracle=None, arith='exact'):
     from gapflow_b200.fv import FVSolver
     d, extra = inputs(name)
     o = oracle or build_case(name)
-    s = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=o.topo, extra=extra)
+    s = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=o.topo, extra=extra, arith=arith)
     s.set_q(o.q)
     s.pre_run(reset_ekin_old=False)      # dt = CFL*dt_crit of the perturbed field, Ekin_old of _initialize
     return s, o
@@ -89,12 +92,14 @@ def test_eos_functions_vs_reference_golden(gc):
             assert np.allclose(c[m], wc[m], rtol=1e-13), e
 
 
+@pytest.mark.parametrize("arith", ARITH)
 @pytest.mark.parametrize("name", list(STEP_CASES))
-def test_step_vs_reference_golden(gs, name):
-    s, o = make_solver(name)
+def test_step_vs_reference_golden(gs, name, arith):
+    s, o = make_solver(name, arith=arith)
     assert np.array_equal(s.get_q(), gs[f'{name}_q0'])
     sc = s.scalars()
-    exact = STEP_CASES[name]['yaml'].find('EOS: DH') >= 0     # BWR: pow/exp -> tolerance (see EOS test)
+    # BWR: pow/exp -> tolerance (see EOS test); fast arithmetic: tolerance by contract
+    exact = STEP_CASES[name]['yaml'].find('EOS: DH') >= 0 and arith == 'exact'
     dt0 = float(gs[f'{name}_dt0'])
     assert sc.dt == dt0 if exact else abs(sc.dt - dt0) <= 1e-12 * dt0
     for nsteps, tag in ((1, '1'), (2, '3')):
@@ -117,8 +122,9 @@ def test_step_vs_reference_golden(gs, name):
         assert sc.step == int(tag) and not sc.stop
 
 
+@pytest.mark.parametrize("arith", ARITH)
 @pytest.mark.parametrize("name", ['journal2d_periodic', 'slider2d_xDN', 'slider2d_allDN_slip'])
-def test_multi_tile_grid_vs_oracle(name):
+def test_multi_tile_grid_vs_oracle(name, arith):
     """Grids spanning several 16x64 tiles with ragged edges; 4 steps against the oracle."""
     import copy
     from gapflow_b200.fv import FVSolver
@@ -138,15 +144,25 @@ def test_multi_tile_grid_vs_oracle(name):
     perturb(o.q, d['properties']['rho0'], max(abs(d['geometry']['U']), abs(d['geometry']['V'])), 4321)
     o.fill_ghosts()
     o.dt = d['numerics']['CFL'] * o.dt_crit
-    s = FVSolver(g, d['geometry'], d['properties'], d['numerics'], topo=o.topo, extra=extra)
+    s = FVSolver(g, d['geometry'], d['properties'], d['numerics'], topo=o.topo, extra=extra, arith=arith)
     s.set_q(o.q)
     s.pre_run(False)
     for k in range(4):
         o.update()
         s.step(1)
         q = s.get_q()
-        assert np.array_equal(q, o.q), (name, k, int((q != o.q).sum()), relerr(q, o.q))
-        assert s.scalars().dt == o.dt
+        if arith == 'exact':
+            assert np.array_equal(q, o.q), (name, k, int((q != o.q).sum()), relerr(q, o.q))
+            assert s.scalars().dt == o.dt
+        else:
+            assert relerr(q, o.q) <= REL_STEP * (k + 1), (name, k, relerr(q, o.q))
+            assert abs(s.scalars().dt - o.dt) <= 1e-12 * o.dt
+            # boundary and index handling stay bit-exact: ghost cells are exact functions of the interior
+            ref = type(o).__new__(type(o))
+            ref.__dict__.update(o.__dict__)
+            ref.q = q.copy()
+            ref.fill_ghosts()
+            assert np.array_equal(ref.q, q)
 
 
 def test_closure_fields_match_oracle():
@@ -212,9 +228,10 @@ def test_run_until_converged_freezes_at_the_reference_step():
     assert np.array_equal(s.get_q(), o.q)
 
 
+@pytest.mark.parametrize("arith", ARITH)
 @pytest.mark.parametrize("name", ['journal1d_readme', 'journal2d_periodic', 'slider2d_xDN'])
-def test_1000_steps(name):
-    s, o = make_solver(name)
+def test_1000_steps(name, arith):
+    s, o = make_solver(name, arith=arith)
     n = 1000 if name != 'journal1d_readme' else 200      # README case: max_it = 200
     for _ in range(n):
         o.update()
@@ -222,9 +239,11 @@ def test_1000_steps(name):
     q = s.get_q()
     err = relerr(q, o.q)
     assert err <= REL_1000, (name, err)
-    assert np.array_equal(q, o.q), (name, int((q != o.q).sum()), err)
     sc = s.scalars()
-    assert sc.step == o.step and sc.dt == o.dt
+    if arith == 'exact':
+        assert np.array_equal(q, o.q), (name, int((q != o.q).sum()), err)
+        assert sc.dt == o.dt
+    assert sc.step == o.step and abs(sc.dt - o.dt) <= 1e-9 * o.dt
     assert abs(sc.simtime - o.simtime) <= 1e-12 * o.simtime
 
 
