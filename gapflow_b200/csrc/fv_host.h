@@ -38,6 +38,7 @@ struct FvSolver {
     int* pflags;
     RefreshOut* refresh;
     int npartial;      // capacity of partial/pflags
+    int* redo;         // [2] device flags, see fv_pass_kernel
     CUtensorMap qmap[3], q0map[3], topo_map, topo2_map, ls_map;
     int topo_fast, ls_fast;   // range flags of the uploaded topography / slip length (see FvParams::static_fast)
     bool dirty_scalars;   // q changed from the host since scalars were computed
@@ -83,6 +84,7 @@ struct PassArgs {
     DevState* st;
     Partial* partial;
     int* pflags;
+    int* redo;                 // [2]: pass (0 predictor, 1 corrector) must be redone by the general kernel
     int until_converged;
     int ntiles;
 };

@@ -595,7 +595,9 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     if (P.ncta + 1 > npartial) { set_error("device has more SMs than the record table allows"); return GPF_E_INVALID; }
     partial = reinterpret_cast<Partial*>(p); p += align_up((size_t)npartial * sizeof(Partial), 256);
     pflags = reinterpret_cast<int*>(p); p += align_up((size_t)npartial * sizeof(int), 256);
-    qtable = reinterpret_cast<double**>(p); p += 256;
+    qtable = reinterpret_cast<double**>(p);
+    redo = reinterpret_cast<int*>(p + 128);         // zeroed with the workspace
+    p += 256;
     // planes are allocated with stride plane_b; the layout's plane stride must match
     P.L.plane = plane_b / 8;
     GPF_CUDA(cudaMemcpy(qtable, qbuf, sizeof(qbuf), cudaMemcpyHostToDevice));
@@ -726,7 +728,7 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
     PassArgs A;
     for (int k = 0; k < 3; ++k) { A.qmap[k] = S.qmap[k]; A.q0map[k] = S.q0map[k]; A.qbuf[k] = S.qbuf[k]; }
     A.topo_map = S.topo_map; A.topo2_map = S.topo2_map; A.ls_map = S.ls_map;
-    A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags;
+    A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags; A.redo = S.redo;
     A.until_converged = until_converged;
     A.ntiles = S.P.nblk_x * S.P.nblk_y;
     const bool ls = S.P.has_extra != 0;
@@ -736,7 +738,7 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
     const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, n, s)
                                                    : launch_pass_exact(A, CORR, ls, dh, xf, n, s);
     if (rc) return rc;
-    g_launches++;
+    g_launches += 2;           // straight-line kernel + general kernel (returns at once unless flagged)
     return debug_check(CORR ? "fv_pass_kernel<corrector>" : "fv_pass_kernel<predictor>", s);
 }
 

@@ -52,6 +52,17 @@ __device__ __forceinline__ bool q_in_fast_range(const Cell& c) {
     return in_fast_range_nz(c.q0) & in_fast_range(c.q1) & in_fast_range(c.q2);
 }
 
+// what the straight-line (GEN = false) kernel must know about a staged cell: with contracted
+// arithmetic only denominators matter (a * rcp(b): the density; gap height and parameters are
+// static), the exact contract also needs the numerators of its Markstein quotients in range
+__device__ __forceinline__ bool cell_in_fast_range(const Cell& c) {
+#if GPF_FAST_ARITH
+    return in_fast_range_nz(c.q0);
+#else
+    return q_in_fast_range(c);
+#endif
+}
+
 struct Clos4 { double p, t0, t1, t2; };
 
 template <bool LS, int EOS, bool FAST, bool XF>
@@ -179,7 +190,18 @@ __device__ __noinline__ int cell_flags_slow(double a, double b, double c, double
 
 // Persistent kernel: fv_ctas_per_sm(CORR) CTAs per SM walk the tiles round-robin.  A 2-deep ring of
 // TMA-staged boxes keeps the loads of tile n+1 in flight under the arithmetic of tile n.
-template <bool CORR, bool LS, int EOS, bool XF>
+//
+// Every pass is two launches of this template:
+//   GEN = false  straight-line arithmetic only (reciprocal-based quotients valid for operands in
+//                [2^-100, 2^100]).  It range-checks what it divides by on the integer pipe and, if
+//                any cell (or dt, or a static field) is outside, raises A.redo[CORR]; its output is
+//                then garbage.  No out-of-line call sits in its loop: the general kernel's cold calls
+//                cost 20 % of the pass through the registers they pin (r1h -> r1i).
+//   GEN = true   the general kernel (tile-uniform choice between the same straight-line code and
+//                plain IEEE divisions, exact validity flags).  Returns at once unless A.redo[CORR] is
+//                raised, else recomputes the whole pass: a pass reads only buffers it does not write.
+// Each GEN = false launch lowers the other pass's flag; a stale raised flag only costs time.
+template <bool CORR, bool LS, int EOS, bool XF, bool GEN>
 __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kernel(const __grid_constant__ PassArgs A) {
     constexpr int NST = fv_nstage(CORR);
     using S = Smem<CORR, LS, XF, NST>;
@@ -196,6 +218,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     const DevState* st = A.st;
     // run-loop condition (problem.py:401) evaluated on the device; uniform per grid
     if (st->stop || (A.until_converged && st->halt)) return;
+    if (GEN && A.redo[CORR] == 0) return;
 
     const int tid = threadIdx.x;
     const int cur = st->cur;
@@ -265,6 +288,14 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     const int on_dx = -d * BY, on_dy = -d;                        // offsets to the neighbours differenced against
     const unsigned sbit = (d > 0) ? 0x80000000u : 0u;             // -d * x == x with its sign bit flipped when d = +1
     const bool dt_fast = in_fast_range_nz(dt) && P.static_fast;
+    if (!GEN) {
+        if (tid == 0 && blockIdx.x == 0) A.redo[CORR ? 0 : 1] = 0;
+        if (!dt_fast) {                                            // grid-uniform
+            if (tid == 0) A.redo[CORR] = 1;
+            return;
+        }
+    }
+    bool bad = false;                                              // GEN = false: an operand left the fast range
 
     double* const qout = A.qbuf[out_idx];
     const double* const q0b = A.qbuf[cur];
@@ -309,7 +340,17 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         };
 
         // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
-        {
+        if constexpr (!GEN) {
+            const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
+            bad |= !(cell_in_fast_range(ca) & cell_in_fast_range(cb));
+            store_clos(o_own, phase1_cell<LS, EOS, true, XF>(ca, P));
+            store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF>(cb, P));
+            if (has_halo) {
+                const Cell ch = load_cell(o_halo);
+                bad |= !cell_in_fast_range(ch);
+                store_clos(o_halo, phase1_cell<LS, EOS, true, XF>(ch, P));
+            }
+        } else {
             const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
             const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb);
             if (__all_sync(0xffffffffu, ok) && P.static_fast) {   // warp-uniform
@@ -321,7 +362,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
                 sbad[fl] = 1;             // this tile takes the plain-division path in phase 2
             }
         }
-        if (has_halo) {
+        if (GEN && has_halo) {
             const Cell ch = load_cell(o_halo);
             if (__all_sync(0xffffffffu, q_in_fast_range(ch)) && P.static_fast) {
                 store_clos(o_halo, phase1_cell<LS, EOS, true, XF>(ch, P));
@@ -333,8 +374,8 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         __syncthreads();
 
         // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
-        const bool fast = (sbad[fl] == 0) && dt_fast;                              // tile-uniform
-        if (tid == 0) sbad[fl ^ 1] = 0;                                             // next tile's flag
+        const bool fast = !GEN || ((sbad[fl] == 0) && dt_fast);                    // tile-uniform
+        if (GEN && tid == 0) sbad[fl ^ 1] = 0;                                      // next tile's flag
         const int i0 = 1 + bx * TX, j0 = 1 + by * TY;
         const bool full = (i0 + TX - 1 <= Nx) && (j0 + TY - 1 <= Ny);
         const bool btile = (bx == 0) | (i0 + TX - 1 >= Nx) | (by == 0) | (j0 + TY - 1 >= Ny);
@@ -352,8 +393,13 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             Nb nb;
             nb.q1x = sq[BOX + o + on_dx]; nb.Ax = sp[o + on_dx] + st0[o + on_dx]; nb.t2x = st2[o + on_dx];
             nb.q2y = sq[2 * BOX + o + on_dy]; nb.t2y = st2[o + on_dy]; nb.Cy = sp[o + on_dy] + st1[o + on_dy];
-            const Q3 qq = fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
-                               : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
+            Q3 qq;
+            if constexpr (GEN) {
+                qq = fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
+                          : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
+            } else {
+                qq = phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt);
+            }
             double qn0 = qq.v0, qn1 = qq.v1, qn2 = qq.v2;
             if (CORR) {
                 const int oo = (2 * g + k) * TY + ty;
@@ -362,15 +408,26 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
                 qn2 = (qn2 + sq0[2 * TX * TY + oo]) * 0.5;
                 // kinetic energy and speed (problem.py:342, 347): w = (jx^2 + jy^2)/rho
                 const double num = qn1 * qn1 + qn2 * qn2;
-                const bool wok = fast & in_fast_range_nz(qn0) & in_fast_range(num);
                 double w;
-                if (__all_sync(0xffffffffu, wok)) w = div_fast(num, qn0, rcp_sel<true>(qn0));
-                else w = num / qn0;
+                if constexpr (GEN) {
+                    const bool wok = fast & in_fast_range_nz(qn0) & in_fast_range(num);
+                    if (__all_sync(0xffffffffu, wok)) w = div_sel<true>(num, qn0, rcp_exact(qn0));
+                    else w = num / qn0;
+                } else {
+                    // an invalid cell (NaN, negative density) is never in range: the general kernel
+                    // then redoes the pass and sets the exact flags
+                    w = div_sel<true>(num, qn0, rcp_exact(qn0));
+#if GPF_FAST_ARITH
+                    if (act) bad |= !in_fast_range_nz(qn0) | !(w >= 0.0) | (__double2hiint(qn0) < 0);
+#else
+                    if (act) bad |= !(in_fast_range_nz(qn0) & in_fast_range(num)) | !(w >= 0.0) | (__double2hiint(qn0) < 0);
+#endif
+                }
                 if (act) {
                     red.ekin += w * 0.5;
                     red.vmax2 = fmax(red.vmax2, w);
                     // NaN anywhere in the cell makes w NaN; a negative density has its sign bit set
-                    if (!(w >= 0.0) || __double2hiint(qn0) < 0) red.flags |= cell_flags_slow(qn0, qn1, qn2, w);
+                    if (GEN && (!(w >= 0.0) || __double2hiint(qn0) < 0)) red.flags |= cell_flags_slow(qn0, qn1, qn2, w);
                     if (DEFER_C) rho[k] = qn0;
                     else red_accum_c<EOS>(red, qn0, P.eos);
                 }
@@ -426,6 +483,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         if (++stage == NST) { stage = 0; phase ^= 1u; }
     }
 
+    if (!GEN && bad) A.redo[CORR] = 1;
     if (CORR) {
         // warp shuffles, then one record per CTA (fixed order: deterministic)
         double e = warp_sum(red.ekin);
@@ -465,10 +523,12 @@ static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
     using Sm = Smem<CORR, LS, XF, fv_nstage(CORR)>;
     static bool attr_set = false;
     if (!attr_set) {
-        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
         attr_set = true;
     }
-    fv_pass_kernel<CORR, LS, EOS, XF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    fv_pass_kernel<CORR, LS, EOS, XF, false><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    fv_pass_kernel<CORR, LS, EOS, XF, true><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
     return GPF_OK;
 }
 

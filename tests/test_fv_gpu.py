@@ -194,9 +194,10 @@ def test_fill_ghosts_and_host_update():
     assert np.array_equal(qh, s2.get_q())
 
 
-def test_invalid_state_restores_previous_step_and_stops():
+@pytest.mark.parametrize("arith", ARITH)
+def test_invalid_state_restores_previous_step_and_stops(arith):
     """problem.py:565-610: NaN / negative density -> q restored, _stop set."""
-    s, o = make_solver('journal2d_periodic')
+    s, o = make_solver('journal2d_periodic', arith=arith)
     s.step(1)
     q1 = s.get_q()
     s.set_scalars(dt=1e-3)            # absurd time step -> negative density or NaN
@@ -207,6 +208,32 @@ def test_invalid_state_restores_previous_step_and_stops():
     assert np.array_equal(s.get_q(), q1)
     s.step(3)                         # further updates are no-ops
     assert np.array_equal(s.get_q(), q1) and s.scalars().step == 1
+
+
+@pytest.mark.parametrize("name", ['journal2d_periodic', 'slider2d_xDN', 'slider2d_allDN_slip'])
+def test_operands_outside_the_fast_range_take_the_general_kernel(name):
+    """A pass is a straight-line kernel (quotients over reciprocals, operands in [2^-100, 2^100])
+    followed by the general kernel, which redoes the pass with IEEE divisions where a cell left
+    that range.  Fluxes of 1e-40 and 1e-300 (subnormal products) force the second; the result must
+    stay bit-identical to the NumPy oracle, and a later in-range step must return to the first."""
+    s, o = make_solver(name)
+    q = o.q.copy()
+    q[1, 3, 5] = 1e-40
+    q[2, 7, 2] = -3e-300
+    q[1, -2, -2] = 7e-35
+    o.q[...] = q
+    o.fill_ghosts()
+    if o.numerics['adaptive']:
+        o.dt = o.numerics['CFL'] * o.dt_crit
+    s.set_q(o.q)
+    s.pre_run(reset_ekin_old=False)
+    for _ in range(3):
+        o.update()
+    s.step(3)
+    assert np.array_equal(s.get_q(), o.q)
+    sc = s.scalars()
+    assert sc.dt == o.dt
+    assert abs(sc.residual - o.residual) <= 1e-9 * abs(o.residual)      # the Ekin sum is re-ordered
 
 
 def test_run_until_converged_freezes_at_the_reference_step():
