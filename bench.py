@@ -291,7 +291,7 @@ def run_gpu(args):
     per_gpu_cells = n * n
     ach_corr = per_gpu_cells * BYTES_CORR / (t_corr * 1e-3) / 1e9
     ach_pred = per_gpu_cells * BYTES_PRED / (t_pred * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "fv_pass_kernel<corrector>", "achieved": ach_corr, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "fv_pass_kernel<corrector> (timed: the straight-line launch + the general launch that returns at once)", "achieved": ach_corr, "peak": peak,
                 "unit": "GB/s", "frac": ach_corr / peak, "traffic": TRAFFIC_CORR_BYTES,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": per_gpu_cells * BYTES_CORR,
                 "ms_per_launch": t_corr,
@@ -376,7 +376,7 @@ def run_gpu(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one corrector launch at 4096^2 from the
 # committed `ncu --set full` capture (profiles/); None until a capture exists.
-TRAFFIC_CORR_BYTES = 1570300552  # profiles/r1f_ncu_fv_pass_summary.csv: 1.178533 GB read + 391.768 MB written
+TRAFFIC_CORR_BYTES = 1557810552  # profiles/r1j_ncu_fv_pass_summary.csv: 1.166907 GB read + 390.904 MB written
 
 
 def main():

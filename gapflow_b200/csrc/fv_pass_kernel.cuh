@@ -381,11 +381,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         const bool btile = (bx == 0) | (i0 + TX - 1 >= Nx) | (by == 0) | (j0 + TY - 1 >= Ny);
         const size_t a_tile = a_thread + (size_t)(bx * TX) * pitch + (size_t)(by * TY);
         double rho[2] = {-INFINITY, -INFINITY};
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            // cells of a ragged tile that lie outside the grid are computed (on zero-filled or
-            // foreign data) but neither stored nor counted: every lane must reach the warp votes
-            const bool act = full || ((i0 + 2 * g + k <= Nx) && (j0 + ty <= Ny));
+        auto update_cell = [&](int k) {
             const int o = o_own + k * BY;
             const Cell c = load_cell(o);
             Clos4 kk;
@@ -393,13 +389,27 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             Nb nb;
             nb.q1x = sq[BOX + o + on_dx]; nb.Ax = sp[o + on_dx] + st0[o + on_dx]; nb.t2x = st2[o + on_dx];
             nb.q2y = sq[2 * BOX + o + on_dy]; nb.t2y = st2[o + on_dy]; nb.Cy = sp[o + on_dy] + st1[o + on_dy];
-            Q3 qq;
             if constexpr (GEN) {
-                qq = fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
-                          : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
+                return fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
+                            : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
             } else {
-                qq = phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt);
+                return phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt);
             }
+        };
+        // corrector (116 registers at 2 CTAs/SM): both cells of a thread in one straight-line block,
+        // two independent FP64 chains; the predictor's 80-register budget has no room for that
+        constexpr bool ILP2 = !GEN && CORR;
+        Q3 q2c[2];
+        if constexpr (ILP2) {
+            q2c[0] = update_cell(0);
+            q2c[1] = update_cell(1);
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            // cells of a ragged tile that lie outside the grid are computed (on zero-filled or
+            // foreign data) but neither stored nor counted: every lane must reach the warp votes
+            const bool act = full || ((i0 + 2 * g + k <= Nx) && (j0 + ty <= Ny));
+            const Q3 qq = ILP2 ? q2c[k] : update_cell(k);
             double qn0 = qq.v0, qn1 = qq.v1, qn2 = qq.v2;
             if (CORR) {
                 const int oo = (2 * g + k) * TY + ty;

@@ -16,6 +16,6 @@ timeout 120 python bench.py --steps 3 --warmup 3 --no-cpu > $out/plain.log 2>&1 
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $out/launches.csv \
     python bench.py --steps 3 --warmup 3 --no-cpu > $out/ncu_list.log 2>&1
 timeout 120 python bench.py --steps 3 --warmup 3 --no-cpu > $out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:fv_pass -s 6 -c 2 -o $out/prof \
+ncu --set full --clock-control none --import-source on -k regex:fv_pass -s 8 -c 4 -o $out/prof \
     python bench.py --steps 3 --warmup 3 --no-cpu > $out/ncu_full.log 2>&1
 ls -la $out
