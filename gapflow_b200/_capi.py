@@ -28,6 +28,7 @@ EOS_KEYS = {'DH': ['rho0', 'P0', 'C1', 'C2'], 'PL': ['rho0', 'P0', 'alpha'], 'vd
             'Bayada': ['rho_l', 'rho_v', 'c_l', 'c_v']}
 BC_P, BC_D, BC_N, BC_HALO = 0, 1, 2, 3
 F_Q, F_TOPO, F_EXTRA = 0, 1, 2
+PART_ALL, PART_EDGE, PART_INTERIOR = 0, 1, 2
 FIN_STEP, FIN_PRERUN, FIN_PRERUN_KEEP_EKIN, FIN_REFRESH = 0, 1, 2, 3
 
 
@@ -73,6 +74,7 @@ SIGNATURES = {
     "gpf_fv_closures_of": (_i, [_vp, _i, _dp, _dp, _dp, _dp, _i, _vp]),
     "gpf_fv_update_host": (_i, [_vp, _dp, _i, C.POINTER(FvScalars), _vp]),
     "gpf_fv_pass": (_i, [_vp, _i, _vp]),
+    "gpf_fv_pass_part": (_i, [_vp, _i, _i, _vp]),
     "gpf_fv_halo_pack": (_i, [_vp, _i, _dp, _vp]),
     "gpf_fv_halo_unpack": (_i, [_vp, _i, _dp, _vp]),
     "gpf_fv_reduce_local": (_i, [_vp, _i, _dp, _vp]),

@@ -166,7 +166,10 @@ int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, vo
     GPF_CATCH
 }
 int gpf_fv_pass(gpf_fv* s, int corrector, void* stream) {
-    GPF_TRY NEED(s) return s->S.pass(corrector, (cudaStream_t)stream); GPF_CATCH
+    GPF_TRY NEED(s) return s->S.pass(corrector, GPF_PART_ALL, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_pass_part(gpf_fv* s, int corrector, int part, void* stream) {
+    GPF_TRY NEED(s) return s->S.pass(corrector, part, (cudaStream_t)stream); GPF_CATCH
 }
 int gpf_fv_halo_pack(gpf_fv* s, int rel, double* sendbuf, void* stream) {
     GPF_TRY NEED(s && sendbuf) return s->S.halo_pack(rel, sendbuf, (cudaStream_t)stream); GPF_CATCH

@@ -39,6 +39,7 @@ struct FvSolver {
     RefreshOut* refresh;
     int npartial;      // capacity of partial/pflags
     int* redo;         // [2] device flags, see fv_pass_kernel
+    int nrec_corr = 0; // record slots written by the last corrector pass (all its launches)
     CUtensorMap qmap[3], q0map[3], topo_map, topo2_map, ls_map;
     int topo_fast, ls_fast;   // range flags of the uploaded topography / slip length (see FvParams::static_fast)
     bool dirty_scalars;   // q changed from the host since scalars were computed
@@ -62,7 +63,7 @@ struct FvSolver {
     int set_scalars(const gpf_fv_scalars* in, cudaStream_t s);
     int mass(double* m, cudaStream_t s);
     int closures(double* p, double* wxz, double* wyz, double* bulk, int on_device, cudaStream_t s, int rel = 0);
-    int pass(int corrector, cudaStream_t s);
+    int pass(int corrector, int part, cudaStream_t s);
     int halo_pack(int rel, double* send, cudaStream_t s);
     int halo_unpack(int rel, const double* recv, cudaStream_t s);
     int reduce_local(int kind, double* rec5, cudaStream_t s);
@@ -86,7 +87,9 @@ struct PassArgs {
     int* pflags;
     int* redo;                 // [2]: pass (0 predictor, 1 corrector) must be redone by the general kernel
     int until_converged;
-    int ntiles;
+    int ntiles;                // tiles of this launch (virtual index t -> tile row (t / nty) * bx_mul + bx_off)
+    int bx_mul, bx_off;
+    int rec0;                  // first record slot of this launch
 };
 
 // parameter packing shared with the pure-function entry points

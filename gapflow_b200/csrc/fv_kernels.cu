@@ -23,7 +23,7 @@ enum { FIN_STEP = 0, FIN_PRERUN = 1, FIN_PRERUN_KEEP_EKIN = 2, FIN_REFRESH = 3 }
 __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ FvParams P, DevState* st,
                                                         const Partial* part, const int* pflags, int nblk,
                                                         int mode, int until_converged, RefreshOut* ro,
-                                                        const Rec5* recs, int nrec, Rec5* rec_out) {
+                                                        const Rec5* recs, int nrec, Rec5* rec_out, int xslot) {
     if (mode == FIN_STEP && (st->stop || (until_converged && st->halt))) return;
     __shared__ double sE[256], sV[256], sC[256], sM[256];
     __shared__ int sF[256];
@@ -46,6 +46,13 @@ __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ 
             VM = fmax(VM, part[b].vmax2);
             CM = fmax(CM, part[b].cs2);
             F |= pflags[b];
+        }
+        if (xslot >= 0 && tid == 255) {           // the ring-edge ghost rows' record (fv_edge_rows_kernel)
+            E += part[xslot].ekin;
+            M += part[xslot].mass;
+            VM = fmax(VM, part[xslot].vmax2);
+            CM = fmax(CM, part[xslot].cs2);
+            F |= pflags[xslot];
         }
     }
     sE[tid] = E; sV[tid] = VM; sC[tid] = CM; sM[tid] = M; sF[tid] = F;
@@ -723,18 +730,43 @@ int FvSolver::download(int field, double* data, int ncomp, int on_device, cudaSt
 int launch_pass_exact(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, int n, cudaStream_t s);
 int launch_pass_fast(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, int n, cudaStream_t s);
 
+// part: GPF_PART_ALL every tile row; GPF_PART_EDGE the first and the last tile row (whose rows the
+// slab neighbours need); GPF_PART_INTERIOR the rest -- so that a slab driver can exchange the edge
+// rows while the interior is being computed.  Grids of fewer than 3 tile rows are not split
+// (EDGE = everything, INTERIOR = nothing).
 template <bool CORR>
-static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
+static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int part = GPF_PART_ALL) {
+    const int nty = S.P.nblk_x, nbx = S.P.nblk_y;          // tiles along y, tile rows along x
+    if (part < GPF_PART_ALL || part > GPF_PART_INTERIOR) { set_error("bad pass part"); return GPF_E_INVALID; }
+    if (nbx < 3) {
+        if (part == GPF_PART_INTERIOR) return GPF_OK;
+        part = GPF_PART_ALL;
+    }
     PassArgs A;
     for (int k = 0; k < 3; ++k) { A.qmap[k] = S.qmap[k]; A.q0map[k] = S.q0map[k]; A.qbuf[k] = S.qbuf[k]; }
     A.topo_map = S.topo_map; A.topo2_map = S.topo2_map; A.ls_map = S.ls_map;
     A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags; A.redo = S.redo;
     A.until_converged = until_converged;
-    A.ntiles = S.P.nblk_x * S.P.nblk_y;
+    // INTERIOR leaves a few CTA slots empty so that the exchange kernels of the side stream (pack,
+    // NCCL send/recv, unpack) find room beside the persistent CTAs (GPF_INTERIOR_SLACK, default 4)
+    static const int slack = [] { const char* e = getenv("GPF_INTERIOR_SLACK"); return e ? atoi(e) : 4; }();
+    const int n_edge = pass_ctas(2 * nty, CORR);
+    int n_int = pass_ctas((nbx - 2) * nty, CORR);
+    if (n_int > 4 * slack) n_int -= slack;
+    if (part == GPF_PART_ALL) {
+        A.ntiles = nbx * nty; A.bx_mul = 1; A.bx_off = 0; A.rec0 = 0;
+        if (CORR) S.nrec_corr = pass_ctas(A.ntiles, true);
+    } else if (part == GPF_PART_EDGE) {
+        A.ntiles = 2 * nty; A.bx_mul = nbx - 1; A.bx_off = 0; A.rec0 = 0;
+        if (CORR) S.nrec_corr = n_edge + n_int;
+    } else {
+        A.ntiles = (nbx - 2) * nty; A.bx_mul = 1; A.bx_off = 1; A.rec0 = n_edge;
+        if (CORR) S.nrec_corr = n_edge + n_int;
+    }
     const bool ls = S.P.has_extra != 0;
     const bool dh = S.P.eos.kind == GPF_EOS_DH;
     const bool xf = S.P.xflow != 0;
-    const int n = pass_ctas(A.ntiles, CORR);
+    const int n = (part == GPF_PART_INTERIOR) ? n_int : pass_ctas(A.ntiles, CORR);
     const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, n, s)
                                                    : launch_pass_exact(A, CORR, ls, dh, xf, n, s);
     if (rc) return rc;
@@ -743,9 +775,9 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s) {
 }
 
 static int launch_finish(FvSolver& S, int nblk, int mode, int until_converged, cudaStream_t s,
-                         const Rec5* recs = nullptr, int nrec = 0, Rec5* rec_out = nullptr) {
+                         const Rec5* recs = nullptr, int nrec = 0, Rec5* rec_out = nullptr, int xslot = -1) {
     fv_finish_kernel<<<1, 256, 0, s>>>(S.P, S.st, S.partial, S.pflags, nblk, mode, until_converged, S.refresh,
-                                       recs, nrec, rec_out);
+                                       recs, nrec, rec_out, xslot);
     g_launches++;
     return debug_check("fv_finish_kernel", s);
 }
@@ -762,7 +794,7 @@ static int launch_reduce(FvSolver& S, cudaStream_t s) {
 
 int FvSolver::step(int n, int until_converged, cudaStream_t s) {
     if (n < 0) { set_error("n < 0"); return GPF_E_INVALID; }
-    const int nblk = P.ncta;
+    const int nblk = P.ncta;               // = nrec_corr of an unsplit corrector launch
     if (timing) {
         while ((int)ev.size() < 3 * n + 1) { cudaEvent_t e; GPF_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
         ev_steps = n;
@@ -782,8 +814,8 @@ int FvSolver::step(int n, int until_converged, cudaStream_t s) {
 }
 
 // ---- slab decomposition building blocks (gapflow_b200/dist.py drives them) ---------------
-int FvSolver::pass(int corrector, cudaStream_t s) {
-    return corrector ? launch_pass<true>(*this, 0, s) : launch_pass<false>(*this, 0, s);
+int FvSolver::pass(int corrector, int part, cudaStream_t s) {
+    return corrector ? launch_pass<true>(*this, 0, s, part) : launch_pass<false>(*this, 0, s, part);
 }
 
 int FvSolver::halo_pack(int rel, double* send, cudaStream_t s) {
@@ -803,7 +835,7 @@ int FvSolver::halo_unpack(int rel, const double* recv, cudaStream_t s) {
     int rc = debug_check("fv_halo_unpack_kernel", s);
     if (rc) return rc;
     if (rel == 2 && (P.bc.edge[0] || P.bc.edge[1])) {
-        const int slot = P.ncta;
+        const int slot = npartial - 1;       // fixed slot, folded as the extra record by reduce_local
         if (P.eos.kind == GPF_EOS_DH) fv_edge_rows_kernel<GPF_EOS_DH><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
         else fv_edge_rows_kernel<-1><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
         g_launches++;
@@ -815,12 +847,14 @@ int FvSolver::halo_unpack(int rel, const double* recv, cudaStream_t s) {
 // kind 0: fold the records of the last corrector pass; kind 1: reduce the current q first
 int FvSolver::reduce_local(int kind, double* rec5, cudaStream_t s) {
     int rc;
-    int nblk = P.ncta + ((P.bc.edge[0] || P.bc.edge[1]) ? 1 : 0);
+    int nblk = nrec_corr;
+    int xslot = (P.bc.edge[0] || P.bc.edge[1]) ? npartial - 1 : -1;
     if (kind == 1) {
         if ((rc = launch_reduce(*this, s))) return rc;
         nblk = REDUCE_BLOCKS;
+        xslot = -1;
     }
-    return launch_finish(*this, nblk, FIN_REFRESH, 0, s, nullptr, 0, reinterpret_cast<Rec5*>(rec5));
+    return launch_finish(*this, nblk, FIN_REFRESH, 0, s, nullptr, 0, reinterpret_cast<Rec5*>(rec5), xslot);
 }
 
 int FvSolver::finish(int mode, const double* recs, int nrec, cudaStream_t s) {

@@ -239,8 +239,11 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     // The walk advances (bx, by) by a fixed step, so no division runs in the loop.
     const int step_bx = (int)gridDim.x / nty, step_by = (int)gridDim.x % nty;
 
-    auto issue = [&](int bx, int by, int stage) {          // thread 0 only
-        const int i0 = 1 + bx * TX, j0 = 1 + by * TY;
+    // a launch covers all tile rows (mul 1, off 0), the interior ones (mul 1, off 1) or the first
+    // and the last one (mul = rows - 1, off 0): see FvSolver::pass
+    const int bx_mul = A.bx_mul, bx_off = A.bx_off;
+    auto issue = [&](int vbx, int by, int stage) {         // thread 0 only
+        const int i0 = 1 + (vbx * bx_mul + bx_off) * TX, j0 = 1 + by * TY;
         unsigned char* base = smem + (size_t)stage * S::STAGE;
         uint64_t* b = bar + stage;
         mbar_expect_tx(b, S::TX_BYTES);
@@ -376,10 +379,11 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
         const bool fast = !GEN || ((sbad[fl] == 0) && dt_fast);                    // tile-uniform
         if (GEN && tid == 0) sbad[fl ^ 1] = 0;                                      // next tile's flag
-        const int i0 = 1 + bx * TX, j0 = 1 + by * TY;
+        const int rbx = bx * bx_mul + bx_off;                                      // tile row in the grid
+        const int i0 = 1 + rbx * TX, j0 = 1 + by * TY;
         const bool full = (i0 + TX - 1 <= Nx) && (j0 + TY - 1 <= Ny);
-        const bool btile = (bx == 0) | (i0 + TX - 1 >= Nx) | (by == 0) | (j0 + TY - 1 >= Ny);
-        const size_t a_tile = a_thread + (size_t)(bx * TX) * pitch + (size_t)(by * TY);
+        const bool btile = (rbx == 0) | (i0 + TX - 1 >= Nx) | (by == 0) | (j0 + TY - 1 >= Ny);
+        const size_t a_tile = a_thread + (size_t)(rbx * TX) * pitch + (size_t)(by * TY);
         double rho[2] = {-INFINITY, -INFINITY};
         auto update_cell = [&](int k) {
             const int o = o_own + k * BY;
@@ -519,11 +523,12 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
                 CM = fmax(CM, sred[ww * 4 + 2]);
                 F |= (int)sred[ww * 4 + 3];
             }
-            A.partial[blockIdx.x].ekin = E;
-            A.partial[blockIdx.x].vmax2 = VM;
-            A.partial[blockIdx.x].cs2 = CM;
-            A.partial[blockIdx.x].mass = 0.0;
-            A.pflags[blockIdx.x] = F;
+            const int slot = A.rec0 + (int)blockIdx.x;
+            A.partial[slot].ekin = E;
+            A.partial[slot].vmax2 = VM;
+            A.partial[slot].cs2 = CM;
+            A.partial[slot].mass = 0.0;
+            A.pflags[slot] = F;
         }
     }
 }

@@ -90,7 +90,7 @@ class SlabSolver:
     rows ``start .. start+n+1`` of the global padded arrays (shape ``(ncomp, n+2, Ny+2)``)."""
 
     def __init__(self, grid, geo, prop, numerics, topo, q=None, extra=None, rank=None, world=None, group=None,
-                 device=None, exchanger=None, arith='exact'):
+                 device=None, exchanger=None, arith='exact', overlap=True):
         from .fv import FVSolver
         self.rank = dist.get_rank(group) if rank is None else rank
         self.world = dist.get_world_size(group) if world is None else world
@@ -112,6 +112,9 @@ class SlabSolver:
         self.rec = torch.zeros(5, dtype=torch.float64, device=dev)
         self.recs = torch.zeros((self.world, 5), dtype=torch.float64, device=dev)
         self._timing, self._ev = False, []
+        # edge tile rows first, their exchange on a side stream under the interior launch
+        self.overlap = overlap and self.world > 1
+        self._side = torch.cuda.Stream(device=dev) if self.overlap else None
         if exchanger is None:
             # Problem.__init__ computes kinetic_energy_old on the _initialize state (problem.py:670)
             self.pre_run(reset_ekin_old=True)
@@ -128,14 +131,14 @@ class SlabSolver:
         self.fv.set_q(q)
 
     # the five device-side phases (each enqueues on the current stream)
-    def _pass(self, corrector):
+    def _pass(self, corrector, part=_capi.PART_ALL):
         if self._timing:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-        _capi.check(self.lib.gpf_fv_pass(self.h, corrector, self._s()))
+        _capi.check(self.lib.gpf_fv_pass_part(self.h, corrector, part, self._s()))
         if self._timing:
             e1.record()
-            self._ev.append((corrector, e0, e1))
+            self._ev.append((corrector, part, e0, e1))
 
     def _pack(self, rel):
         _capi.check(self.lib.gpf_fv_halo_pack(self.h, rel, C.c_void_p(self.send.data_ptr()), self._s()))
@@ -175,11 +178,21 @@ class SlabSolver:
 
     def step(self, n=1):
         """n x Problem.update() (problem.py:509-569); enqueues only."""
+        main = torch.cuda.current_stream(self.fv.device)
         for _ in range(n):
-            self._pass(0)
-            self._exchange(1)
-            self._pass(1)
-            self._exchange(2)
+            for c, rel in ((0, 1), (1, 2)):
+                if not self.overlap:
+                    self._pass(c)
+                    self._exchange(rel)
+                    continue
+                # the first and the last tile row, then their exchange on the side stream while
+                # the interior tile rows are computed (a pass never reads the buffer it writes)
+                self._pass(c, _capi.PART_EDGE)
+                self._side.wait_stream(main)
+                with torch.cuda.stream(self._side):
+                    self._exchange(rel)
+                self._pass(c, _capi.PART_INTERIOR)
+                main.wait_stream(self._side)
             self._fold(0, _capi.FIN_STEP)
 
     def scalars(self):
@@ -227,11 +240,12 @@ class SlabSolver:
     def timing(self):
         """(mean predictor ms, mean corrector ms, launches timed)"""
         torch.cuda.current_stream(self.fv.device).synchronize()
-        t = {0: [], 1: []}
-        for c, e0, e1 in self._ev:
-            t[c].append(e0.elapsed_time(e1))
-        mean = lambda v: sum(v) / len(v) if v else 0.0
-        return mean(t[0]), mean(t[1]), len(self._ev)
+        t, n = {0: 0.0, 1: 0.0}, {0: 0, 1: 0}
+        for c, part, e0, e1 in self._ev:
+            t[c] += e0.elapsed_time(e1)
+            n[c] += part != _capi.PART_INTERIOR            # EDGE + INTERIOR are one pass
+        mean = lambda c: t[c] / n[c] if n[c] else 0.0
+        return mean(0), mean(1), len(self._ev)
 
     # -- construction from global host arrays (tests, small problems) -----------------------
     @classmethod
@@ -256,9 +270,10 @@ class InProcessSlabs:
         lo = hi = None
         group = None
 
-    def __init__(self, d, q_global, topo_global, world, extra_global=None):
+    def __init__(self, d, q_global, topo_global, world, extra_global=None, split=True):
         per = x_periodic(d['grid'])
         self.world = world
+        self.split = split             # passes as EDGE + INTERIOR launches, like SlabSolver's overlapped step
         self.s = []
         rows = slab_rows(d['grid']['Nx'], world)
         for r in range(world):
@@ -294,7 +309,11 @@ class InProcessSlabs:
         for _ in range(n):
             for c, rel in ((0, 1), (1, 2)):
                 for s in self.s:
-                    s._pass(c)
+                    if self.split:
+                        s._pass(c, _capi.PART_EDGE)
+                        s._pass(c, _capi.PART_INTERIOR)
+                    else:
+                        s._pass(c)
                 self._exchange(rel)
             self._fold(0, _capi.FIN_STEP)
 

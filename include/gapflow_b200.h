@@ -177,6 +177,13 @@ int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, vo
 enum { GPF_FIN_STEP = 0, GPF_FIN_PRERUN = 1, GPF_FIN_PRERUN_KEEP_EKIN = 2, GPF_FIN_REFRESH = 3 };
 /* one MacCormack pass (predictor: corrector = 0), problem.py:524-560 */
 int gpf_fv_pass(gpf_fv* s, int corrector, void* stream);
+/* the same pass in two launches, so that the exchange of the edge rows runs under the interior:
+ *   pass_part(c, GPF_PART_EDGE, main); <event>; on a side stream: halo_pack, exchange, halo_unpack;
+ *   pass_part(c, GPF_PART_INTERIOR, main); main waits for the side stream.
+ * EDGE = the first and the last row of 8x64 tiles (rows 1..8 and the last <= 8 rows), INTERIOR =
+ * the rest; EDGE + INTERIOR == ALL bit for bit (a pass reads only buffers it does not write). */
+enum { GPF_PART_ALL = 0, GPF_PART_EDGE = 1, GPF_PART_INTERIOR = 2 };
+int gpf_fv_pass_part(gpf_fv* s, int corrector, int part, void* stream);
 /* rows 1 and Nx (y ghosts included) of buffer `rel` (0: current q, 1: predictor output, 2:
  * corrector output) -> sendbuf[2][3][Ny+2] (device);  recvbuf[0] -> row 0, recvbuf[1] -> row
  * Nx+1, HALO sides only. */

@@ -51,6 +51,42 @@ def test_in_process_slabs_match_single_domain(name, world):
             assert abs(s.residual - ref.residual) <= 1e-9 * abs(ref.residual) + 1e-14
 
 
+@pytest.mark.parametrize("world", [1, 2])
+@pytest.mark.parametrize("name", ['journal2d_periodic', 'slider2d_xDN', 'slider2d_allDN_slip'])
+def test_edge_plus_interior_launches_equal_one_pass(name, world):
+    """gpf_fv_pass_part: EDGE (first and last row of tiles) + INTERIOR launches == the single
+    launch, bit for bit, on a grid of 11 x 3 ragged tiles (83 x 150), also across 2 slabs."""
+    import copy
+    from gapflow_b200.dist import InProcessSlabs
+    from gapflow_b200.fv import FVSolver
+    from oracle.fv import FVOracle
+    from tests.cases import STEP_CASES, perturb, slip_field
+    d, _ = inputs(name)
+    d = copy.deepcopy(d)
+    g = d['grid']
+    g['Nx'], g['Ny'] = 83, 150
+    if name == 'slider2d_xDN':
+        g['dx'], g['dy'] = g['Lx'] / 83, g['Ly'] / 150
+    else:
+        g['Lx'], g['Ly'] = g['dx'] * 83, g['dy'] * 150
+    extra = slip_field((85, 152), 1e-6) if STEP_CASES[name].get('extra') else None
+    o = FVOracle(g, d['geometry'], d['properties'], d['numerics'], extra=extra)
+    perturb(o.q, d['properties']['rho0'], max(abs(d['geometry']['U']), abs(d['geometry']['V'])), 99)
+    o.fill_ghosts()
+    single = FVSolver(g, d['geometry'], d['properties'], d['numerics'], topo=o.topo, extra=extra)
+    single.set_q(o.q)
+    single.pre_run(False)
+    slabs = InProcessSlabs(d, o.q, o.topo, world, extra_global=extra, split=True)
+    for k in range(4):
+        single.step(1)
+        slabs.step(1)
+        assert np.array_equal(slabs.gather_q(), single.get_q()), (name, world, k)
+        ref = single.scalars()
+        for sc in slabs.scalars():
+            assert sc.dt == ref.dt and sc.v_max == ref.v_max and sc.v_sound == ref.v_sound
+            assert abs(sc.ekin - ref.ekin) <= 1e-13 * abs(ref.ekin)
+
+
 def test_in_process_slabs_invalid_step_stops_every_rank():
     from gapflow_b200.dist import InProcessSlabs
     name = "journal2d_periodic"
