@@ -218,57 +218,71 @@ __global__ void __launch_bounds__(128) gp_syrk_kernel(double* A, int Mp, int k) 
 }
 
 // ------------------------------------------------------------------------------------
-// alpha = K^-1 Y by blocked substitution, one CTA (256 threads) per block step.
-//   forward : z_k = Dinv_k (y_k - sum_{j<k} L_kj z_j)
-//   backward: a_k = Dinv_k^T (z_k - sum_{i>k} L_ik^T a_i)
-// X (Mp x nrhs, column-major: X[o*Mp + m]) is overwritten in place.
+// alpha = K^-1 Y by blocked, right-looking substitution: step k solves block k with the stored
+// inverse of L_kk and at once removes its contribution from every remaining block, one CTA per
+// remaining block (the left-looking form -- one CTA streaming a whole block row of L per step --
+// took 174 of the 207 ms of a factorisation at M = 10^4).
+//   forward  (k = 0 .. nb-1):  z_k = Dinv_k w_k;    w_i -= L_ik z_k     for i > k
+//   backward (k = nb-1 .. 0):  a_k = Dinv_k^T z_k;  z_j -= L_kj^T a_k   for j < k
+// Every CTA of a step recomputes the 64 x 64 solve (32 KB of Dinv from L2); the vectors are
+// (nrhs, Mp) row-major, nrhs <= 2.  W is destroyed, Z holds z and is destroyed by the backward sweep.
 // ------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) gp_trsv_fwd_kernel(const double* L, int Mp, int k, const double* Dinv, double* X,
-                                                          int nrhs) {
-    __shared__ double r[2][NB];
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    for (int o = 0; o < nrhs; ++o) {
-        const double* x = X + (size_t)o * Mp;
-        for (int row = w; row < NB; row += 8) {
-            const double* Lr = L + (size_t)(k * NB + row) * Mp;
-            double s = 0.0;
-            for (int c = lane; c < k * NB; c += 32) s += Lr[c] * x[c];
-#pragma unroll
-            for (int oo = 16; oo > 0; oo >>= 1) s += __shfl_xor_sync(0xffffffffu, s, oo);
-            if (lane == 0) r[o][row] = x[k * NB + row] - s;
-        }
-    }
-    __syncthreads();
+__global__ void __launch_bounds__(256) gp_trsv_fwd_kernel(const double* L, int Mp, int k, const double* Dinv, double* W,
+                                                          double* Z, int nrhs) {
+    __shared__ double r[2][NB], z[2][NB];
+    const int tid = threadIdx.x;
     const double* Dk = Dinv + (size_t)k * NB * NB;
-    for (int e = tid; e < NB * nrhs; e += 256) {
-        const int o = e / NB, row = e % NB;
+    if (tid < NB * nrhs) r[tid / NB][tid % NB] = W[(size_t)(tid / NB) * Mp + k * NB + tid % NB];
+    __syncthreads();
+    if (tid < NB * nrhs) {
+        const int o = tid / NB, row = tid % NB;
         double s = 0.0;
         for (int c = 0; c <= row; ++c) s += Dk[row * NB + c] * r[o][c];
-        X[(size_t)o * Mp + k * NB + row] = s;
+        z[o][row] = s;
+        if (blockIdx.x == 0) Z[(size_t)o * Mp + k * NB + row] = s;
+    }
+    if (blockIdx.x == 0) return;
+    __syncthreads();
+    const int row = (k + blockIdx.x) * NB + (tid >> 2), part = tid & 3;
+    const double* Lr = L + (size_t)row * Mp + k * NB + part * 16;
+    for (int o = 0; o < nrhs; ++o) {
+        double s = 0.0;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) s += Lr[c] * z[o][part * 16 + c];
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        if (part == 0) W[(size_t)o * Mp + row] -= s;
     }
 }
-__global__ void __launch_bounds__(256) gp_trsv_bwd_kernel(const double* L, int Mp, int nb, int k, const double* Dinv,
-                                                          double* X, int nrhs) {
+__global__ void __launch_bounds__(256) gp_trsv_bwd_kernel(const double* L, int Mp, int k, const double* Dinv, double* Z,
+                                                          double* A, int nrhs) {
+    __shared__ double r[2][NB], a[2][NB];
     __shared__ double part[4][2][NB];
-    __shared__ double r[2][NB];
-    const int tid = threadIdx.x, c = tid & 63, g = tid >> 6;
-    for (int o = 0; o < nrhs; ++o) {
-        const double* x = X + (size_t)o * Mp;
+    const int tid = threadIdx.x;
+    const double* Dk = Dinv + (size_t)k * NB * NB;
+    if (tid < NB * nrhs) r[tid / NB][tid % NB] = Z[(size_t)(tid / NB) * Mp + k * NB + tid % NB];
+    __syncthreads();
+    if (tid < NB * nrhs) {
+        const int o = tid / NB, col = tid % NB;
         double s = 0.0;
-        for (int row = (k + 1) * NB + g; row < nb * NB; row += 4) s += L[(size_t)row * Mp + k * NB + c] * x[row];
+        for (int row = col; row < NB; ++row) s += Dk[row * NB + col] * r[o][row];     // Dinv^T
+        a[o][col] = s;
+        if ((int)blockIdx.x == k) A[(size_t)o * Mp + k * NB + col] = s;
+    }
+    if ((int)blockIdx.x == k) return;
+    __syncthreads();
+    const int j = blockIdx.x, c = tid & 63, g = tid >> 6;
+    const double* Lb = L + (size_t)(k * NB + g * 16) * Mp + j * NB + c;
+    for (int o = 0; o < nrhs; ++o) {
+        double s = 0.0;
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) s += Lb[(size_t)rr * Mp] * a[o][g * 16 + rr];
         part[g][o][c] = s;
     }
     __syncthreads();
-    if (tid < NB)
-        for (int o = 0; o < nrhs; ++o)
-            r[o][tid] = X[(size_t)o * Mp + k * NB + tid] - (part[0][o][tid] + part[1][o][tid] + part[2][o][tid] + part[3][o][tid]);
-    __syncthreads();
-    const double* Dk = Dinv + (size_t)k * NB * NB;
-    for (int e = tid; e < NB * nrhs; e += 256) {
-        const int o = e / NB, col = e % NB;
-        double s = 0.0;
-        for (int row = col; row < NB; ++row) s += Dk[row * NB + col] * r[o][row];     // Dinv^T
-        X[(size_t)o * Mp + k * NB + col] = s;
+    if (tid < NB * nrhs) {
+        const int o = tid / NB, cc = tid % NB;
+        Z[(size_t)o * Mp + j * NB + cc] -= part[0][o][cc] + part[1][o][cc] + part[2][o][cc] + part[3][o][cc];
     }
 }
 
@@ -608,8 +622,10 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
             g_launches += 2;
         }
     }
-    for (int k = 0; k < nb; ++k) { gp_trsv_fwd_kernel<<<1, 256, 0, s>>>(L, Mp, k, Dinv, alpha, nout); g_launches++; }
-    for (int k = nb - 1; k >= 0; --k) { gp_trsv_bwd_kernel<<<1, 256, 0, s>>>(L, Mp, nb, k, Dinv, alpha, nout); g_launches++; }
+    // alpha: the right-hand sides are in `alpha`; the variance kernel's scratch serves as the z vector
+    double* zvec = scratch;
+    for (int k = 0; k < nb; ++k) { gp_trsv_fwd_kernel<<<nb - k, 256, 0, s>>>(L, Mp, k, Dinv, alpha, zvec, nout); g_launches++; }
+    for (int k = nb - 1; k >= 0; --k) { gp_trsv_bwd_kernel<<<k + 1, 256, 0, s>>>(L, Mp, k, Dinv, zvec, alpha, nout); g_launches++; }
     GPF_CUDA(cudaGetLastError());
     int h = 0;
     GPF_CUDA(cudaMemcpyAsync(&h, info, sizeof(int), cudaMemcpyDeviceToHost, s));
