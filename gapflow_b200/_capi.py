@@ -91,6 +91,8 @@ SIGNATURES = {
     "gpf_gp_destroy": (_i, [_vp]),
     "gpf_gp_factor": (_i, [_vp, _dp, _i, C.c_double, _dp, C.c_double, _dp, _vp]),
     "gpf_gp_get_factor": (_i, [_vp, _dp, _dp, _vp]),
+    "gpf_gp_train_workspace_bytes": (_i, [_i, C.POINTER(C.c_size_t)]),
+    "gpf_gp_nlml": (_i, [_vp, _vp, C.c_size_t, _dp, _dp, _vp]),
     "gpf_gp_mean": (_i, [_vp, _dp, C.c_int64, _dp, C.POINTER(C.c_double), _vp]),
     "gpf_gp_mean_var": (_i, [_vp, _dp, C.c_int64, _dp, C.c_double, _dp, _dp, C.POINTER(C.c_double),
                              C.POINTER(C.c_int64), _vp]),

@@ -245,6 +245,12 @@ int gpf_gp_factor(gpf_gp* g, const double* Xtrain, int M, double log_amp, const 
 int gpf_gp_get_factor(gpf_gp* g, double* L_out, double* alpha_out, void* stream) {
     GPF_TRY NEED(g) return g->G.get_factor(L_out, alpha_out, (cudaStream_t)stream); GPF_CATCH
 }
+int gpf_gp_train_workspace_bytes(int M, size_t* bytes) {
+    GPF_TRY NEED(bytes && M > 0) *bytes = gpf::GpModel::train_workspace_bytes(M); return GPF_OK; GPF_CATCH
+}
+int gpf_gp_nlml(gpf_gp* g, void* work, size_t bytes, double* loss, double* grad, void* stream) {
+    GPF_TRY NEED(g && work) return g->G.nlml(work, bytes, loss, grad, (cudaStream_t)stream); GPF_CATCH
+}
 int gpf_gp_mean(gpf_gp* g, const double* Xtest, int64_t N, double* mean, double* dmean_dx0_max, void* stream) {
     GPF_TRY NEED(g && (N == 0 || (Xtest && mean))) return g->G.mean(Xtest, N, mean, dmean_dx0_max, (cudaStream_t)stream); GPF_CATCH
 }

@@ -21,6 +21,7 @@ struct GpModel {
     double* L;           // (Mp, Mp) row-major lower Cholesky factor (identity in the padding)
     double* Dinv;        // (Mp/64, 64, 64) inverses of L's diagonal blocks
     double* alpha;       // (2, Mp) K^-1 Y, one row per output
+    double* ycopy;       // (2, Mp) the right-hand sides Y (training loss)
     double* scratch;     // (nslots, Mp, 128) v panels of the variance kernel
     double* gpart;       // partial maxima of the mean kernel
     double* vpart;       // per-CTA variance maxima
@@ -32,6 +33,8 @@ struct GpModel {
     int factor(const double* Xtrain, int M, double log_amp, const double* log_scale, double yerr, const double* Y,
                cudaStream_t s);
     int get_factor(double* L_out, double* alpha_out, cudaStream_t s);
+    static size_t train_workspace_bytes(int Mmax);
+    int nlml(void* work, size_t bytes, double* loss, double* grad, cudaStream_t s);
     int mean(const double* Xtest, long long N, double* mean_out, double* dmax_host, cudaStream_t s);
     int mean_var(const double* Xtest, long long N, const double* noise, double noise_scalar, double* mean_out,
                  double* var_out, double* vmax_host, long long* imax_host, cudaStream_t s);

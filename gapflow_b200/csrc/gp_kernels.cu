@@ -541,6 +541,182 @@ __global__ void gp_features_kernel(const double* q, const double* topo, const do
 }
 
 // =====================================================================================
+// Hyperparameter training (row G9, gp.py:290-335): negative log marginal likelihood and its
+// analytic gradient at the parameters of the last factorisation.
+//   loss = sum_o [ 1/2 y_o^T alpha_o ] + n_out (sum_i log L_ii + M/2 log 2 pi)
+//   d loss / d theta = 1/2 sum_ij W_ij dK_ij/dtheta,  W = n_out K^-1 - sum_o alpha_o alpha_o^T
+//   dk/dlog_amp = k,   dk/dlog_scale_d = 3 amp exp(-sqrt3 r) (s_d (x_d - x'_d))^2
+// K^-1 = Linv^T Linv with Linv = L^-1 built block column by block column from the stored
+// inverses of the diagonal blocks.
+// =====================================================================================
+__device__ __forceinline__ void load_tile(double* dst, const double* src, int ld, int tid, int nthr) {
+    for (int e = tid; e < NB * NB; e += nthr) dst[(e / NB) * LDT + e % NB] = src[(size_t)(e / NB) * ld + e % NB];
+}
+__device__ __forceinline__ void load_tile_t(double* dst, const double* src, int ld, int tid, int nthr) {
+    for (int e = tid; e < NB * NB; e += nthr) dst[(e % NB) * LDT + e / NB] = src[(size_t)(e / NB) * ld + e % NB];
+}
+
+// X = L^-1 (lower triangular, Mp x Mp, blocks above the diagonal are not written).  One CTA per
+// block column j:  X_jj = Dinv_j;  X_ij = -Dinv_i sum_{k=j}^{i-1} L_ik X_kj  for i = j+1 .. nb-1.
+__global__ void __launch_bounds__(128) gp_trtri_kernel(const double* L, const double* Dinv, int Mp, double* X) {
+    extern __shared__ double sm[];
+    double* As = sm;
+    double* Bs = sm + NB * LDT;
+    double* Ss = sm + 2 * NB * LDT;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 1, wn = w & 1;
+    const int nb = Mp / NB, j = blockIdx.x;
+    const int r = lane >> 2, c = lane & 3;
+    for (int e = tid; e < NB * NB; e += 128)
+        X[(size_t)(j * NB + e / NB) * Mp + j * NB + e % NB] = Dinv[(size_t)j * NB * NB + e];
+    __syncthreads();
+    for (int i = j + 1; i < nb; ++i) {
+        double acc[4][4][2] = {};
+        for (int k = j; k < i; ++k) {
+            load_tile(As, L + (size_t)i * NB * Mp + (size_t)k * NB, Mp, tid, 128);
+            load_tile(Bs, X + (size_t)k * NB * Mp + (size_t)j * NB, Mp, tid, 128);
+            __syncthreads();
+            warp_mma<false, NB / 4>(acc, As + wm * 32 * LDT, LDT, Bs + wn * 32, LDT, lane);
+            __syncthreads();
+        }
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                double* q = Ss + (wm * 32 + mi * 8 + r) * LDT + wn * 32 + ni * 8 + c * 2;
+                q[0] = acc[mi][ni][0];
+                q[1] = acc[mi][ni][1];
+            }
+        load_tile(As, Dinv + (size_t)i * NB * NB, NB, tid, 128);
+        __syncthreads();
+        double out[4][4][2] = {};
+        warp_mma<false, NB / 4>(out, As + wm * 32 * LDT, LDT, Ss + wn * 32, LDT, lane);
+        double* Xij = X + (size_t)i * NB * Mp + (size_t)j * NB;
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                double* q = Xij + (size_t)(wm * 32 + mi * 8 + r) * Mp + wn * 32 + ni * 8 + c * 2;
+                q[0] = -out[mi][ni][0];
+                q[1] = -out[mi][ni][1];
+            }
+        __threadfence_block();
+        __syncthreads();             // X_ij is read back by this CTA in the next steps
+    }
+}
+
+// Kinv_ij = sum_{k >= i} X_ki^T X_kj for block pairs i >= j (lower triangle of K^-1).
+__global__ void __launch_bounds__(128) gp_lauum_kernel(const double* X, int Mp, double* Kinv) {
+    extern __shared__ double sm[];
+    double* As = sm;
+    double* Bs = sm + NB * LDT;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 1, wn = w & 1;
+    const int nb = Mp / NB;
+    const int p = blockIdx.x;
+    int i = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
+    while ((i + 1) * (i + 2) / 2 <= p) ++i;
+    while (i * (i + 1) / 2 > p) --i;
+    const int j = p - i * (i + 1) / 2;
+    double acc[4][4][2] = {};
+    for (int k = i; k < nb; ++k) {
+        load_tile_t(As, X + (size_t)k * NB * Mp + (size_t)i * NB, Mp, tid, 128);     // As[m][kk] = X_ki[kk][m]
+        load_tile(Bs, X + (size_t)k * NB * Mp + (size_t)j * NB, Mp, tid, 128);
+        __syncthreads();
+        warp_mma<false, NB / 4>(acc, As + wm * 32 * LDT, LDT, Bs + wn * 32, LDT, lane);
+        __syncthreads();
+    }
+    const int r = lane >> 2, c = lane & 3;
+    double* Cij = Kinv + (size_t)i * NB * Mp + (size_t)j * NB;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            double* q = Cij + (size_t)(wm * 32 + mi * 8 + r) * Mp + wn * 32 + ni * 8 + c * 2;
+            q[0] = acc[mi][ni][0];
+            q[1] = acc[mi][ni][1];
+        }
+}
+
+// partial gradient sums of one 64 x 64 tile of the lower triangle: part[tile][0] (log_amp),
+// part[tile][1 + d] (log_scale_d).  Off-diagonal elements count twice (symmetry).
+__global__ void __launch_bounds__(256) gp_grad_kernel(const double* Kinv, const double* alpha, const double* Xs, int M, int Mp,
+                                                      int D, int nout, GpKern kp, double* part) {
+    const int p = blockIdx.x;
+    int bi = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
+    while ((bi + 1) * (bi + 2) / 2 <= p) ++bi;
+    while (bi * (bi + 1) / 2 > p) --bi;
+    const int bj = p - bi * (bi + 1) / 2;
+    double g[1 + GP_MAXD];
+#pragma unroll
+    for (int k = 0; k <= GP_MAXD; ++k) g[k] = 0.0;
+    for (int e = threadIdx.x; e < NB * NB; e += 256) {
+        const int i = bi * NB + e / NB, j = bj * NB + e % NB;
+        if (i >= M || j > i) continue;
+        double wgt = nout * Kinv[(size_t)i * Mp + j];
+        for (int o = 0; o < nout; ++o) wgt -= alpha[(size_t)o * Mp + i] * alpha[(size_t)o * Mp + j];
+        if (i != j) wgt *= 2.0;
+        double d2 = 0.0, t2[GP_MAXD];
+#pragma unroll
+        for (int k = 0; k < GP_MAXD; ++k) {
+            t2[k] = 0.0;
+            if (k < D) { const double t = Xs[(size_t)i * D + k] - Xs[(size_t)j * D + k]; t2[k] = t * t; d2 += t2[k]; }
+        }
+        const double a = SQRT3 * sqrt(d2), ex = exp(-a);
+        g[0] += wgt * kp.amp * (1.0 + a) * ex;
+        const double f = wgt * 3.0 * kp.amp * ex;
+#pragma unroll
+        for (int k = 0; k < GP_MAXD; ++k) g[1 + k] += f * t2[k];
+    }
+    __shared__ double red[8][1 + GP_MAXD];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k <= GP_MAXD; ++k) {
+        double v = g[k];
+#pragma unroll
+        for (int oo = 16; oo > 0; oo >>= 1) v += __shfl_xor_sync(0xffffffffu, v, oo);
+        if (lane == 0) red[w][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x <= GP_MAXD) {
+        double v = 0.0;
+        for (int ww = 0; ww < 8; ++ww) v += red[ww][threadIdx.x];
+        part[(size_t)p * (1 + GP_MAXD) + threadIdx.x] = v;
+    }
+}
+
+// out[0] = loss, out[1 + k] = d loss / d theta_k; one block, fixed summation order
+__global__ void __launch_bounds__(256) gp_nlml_finish_kernel(const double* L, const double* alpha, const double* y, int M,
+                                                             int Mp, int nout, const double* part, int ntile, double* out) {
+    __shared__ double red[256];
+    const int tid = threadIdx.x;
+    double quad = 0.0, logdet = 0.0;
+    for (int i = tid; i < M; i += 256) {
+        logdet += log(L[(size_t)i * Mp + i]);
+        for (int o = 0; o < nout; ++o) quad += y[(size_t)o * Mp + i] * alpha[(size_t)o * Mp + i];
+    }
+    double vals[2 + 1 + GP_MAXD];
+    vals[0] = quad; vals[1] = logdet;
+    for (int k = 0; k <= GP_MAXD; ++k) {
+        double v = 0.0;
+        for (int t = tid; t < ntile; t += 256) v += part[(size_t)t * (1 + GP_MAXD) + k];
+        vals[2 + k] = v;
+    }
+    for (int q = 0; q < 3 + GP_MAXD; ++q) {
+        red[tid] = vals[q];
+        __syncthreads();
+        for (int s = 128; s > 0; s >>= 1) {
+            if (tid < s) red[tid] += red[tid + s];
+            __syncthreads();
+        }
+        if (tid == 0) vals[q] = red[0];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        out[0] = 0.5 * vals[0] + nout * (vals[1] + 0.5 * M * 1.8378770664093453);      // log(2 pi)
+        for (int k = 0; k <= GP_MAXD; ++k) out[1 + k] = 0.5 * vals[2 + k];
+    }
+}
+
+// =====================================================================================
 // Host side
 // =====================================================================================
 static size_t al(size_t x) { return (x + 255) / 256 * 256; }
@@ -552,6 +728,7 @@ size_t GpModel::workspace_bytes(int Mmax, int D, int nout, int nslots) {
     b += al(Mp * Mp * 8);                // L
     b += al(Mp / NB * NB * NB * 8);      // Dinv
     b += al(Mp * 2 * 8);                 // alpha (column-major, 2 columns)
+    b += al(Mp * 2 * 8);                 // copy of the right-hand sides (training loss)
     b += al((size_t)nslots * Mp * NQ * 8);   // v panels of the variance kernel
     b += al(65536 * 8) + al(4096 * 8) + al(4096 * 8) + 256;   // partial maxima, argmax parts, scalars
     (void)nout;
@@ -572,6 +749,7 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
     L = reinterpret_cast<double*>(p); p += al(Mpm * Mpm * 8);
     Dinv = reinterpret_cast<double*>(p); p += al(Mpm / NB * NB * NB * 8);
     alpha = reinterpret_cast<double*>(p); p += al(Mpm * 2 * 8);
+    ycopy = reinterpret_cast<double*>(p); p += al(Mpm * 2 * 8);
     scratch = reinterpret_cast<double*>(p); p += al((size_t)nslots * Mpm * NQ * 8);
     gpart = reinterpret_cast<double*>(p); p += al(65536 * 8);
     vpart = reinterpret_cast<double*>(p); p += al(4096 * 8);
@@ -596,6 +774,7 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
         for (int o = 0; o < nout; ++o) y[(size_t)o * Mp + i] = Y[(size_t)i * nout + o];
     GPF_CUDA(cudaMemcpyAsync(Xs, xs.data(), xs.size() * 8, cudaMemcpyHostToDevice, s));
     GPF_CUDA(cudaMemcpyAsync(alpha, y.data(), (size_t)Mp * 2 * 8, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaMemcpyAsync(ycopy, y.data(), (size_t)Mp * 2 * 8, cudaMemcpyHostToDevice, s));
     GPF_CUDA(cudaStreamSynchronize(s));       // the host vectors go out of scope
     int* info = reinterpret_cast<int*>(scal + 8);
     GPF_CUDA(cudaMemsetAsync(info, 0, sizeof(int), s));
@@ -631,6 +810,42 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
     GPF_CUDA(cudaMemcpyAsync(&h, info, sizeof(int), cudaMemcpyDeviceToHost, s));
     GPF_CUDA(cudaStreamSynchronize(s));
     if (h) { set_error("K + yerr^2 I is not positive definite at row " + std::to_string(h - 1)); M = 0; return GPF_E_INVALID; }
+    return GPF_OK;
+}
+
+size_t GpModel::train_workspace_bytes(int Mmax) {
+    const size_t Mp = (size_t)(Mmax + NB - 1) / NB * NB, nb = Mp / NB;
+    return 256 + 2 * al(Mp * Mp * 8) + al(nb * (nb + 1) / 2 * (1 + GP_MAXD) * 8) + al((2 + GP_MAXD) * 8);
+}
+
+int GpModel::nlml(void* work, size_t bytes, double* loss, double* grad, cudaStream_t s) {
+    if (M < 1) { set_error("no factorisation"); return GPF_E_STATE; }
+    if (!work || bytes < train_workspace_bytes(M)) { set_error("training workspace too small"); return GPF_E_INVALID; }
+    const size_t Mpp = Mp;
+    const int nb = Mp / NB, ntile = nb * (nb + 1) / 2;
+    unsigned char* p = reinterpret_cast<unsigned char*>(al(reinterpret_cast<size_t>(work)));
+    double* X = reinterpret_cast<double*>(p); p += al(Mpp * Mpp * 8);
+    double* Kinv = reinterpret_cast<double*>(p); p += al(Mpp * Mpp * 8);
+    double* part = reinterpret_cast<double*>(p); p += al((size_t)ntile * (1 + GP_MAXD) * 8);
+    double* out = reinterpret_cast<double*>(p);
+    const size_t sm3 = (size_t)3 * NB * LDT * 8, sm2 = (size_t)2 * NB * LDT * 8;
+    static bool attr = false;
+    if (!attr) {
+        GPF_CUDA(cudaFuncSetAttribute(gp_trtri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm3));
+        GPF_CUDA(cudaFuncSetAttribute(gp_lauum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+        attr = true;
+    }
+    gp_trtri_kernel<<<nb, 128, sm3, s>>>(L, Dinv, Mp, X);
+    gp_lauum_kernel<<<ntile, 128, sm2, s>>>(X, Mp, Kinv);
+    gp_grad_kernel<<<ntile, 256, 0, s>>>(Kinv, alpha, Xs, M, Mp, D, nout, kp, part);
+    gp_nlml_finish_kernel<<<1, 256, 0, s>>>(L, alpha, ycopy, M, Mp, nout, part, ntile, out);
+    g_launches += 4;
+    GPF_CUDA(cudaGetLastError());
+    double h[2 + GP_MAXD];
+    GPF_CUDA(cudaMemcpyAsync(h, out, sizeof(h), cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    if (loss) *loss = h[0];
+    if (grad) for (int k = 0; k <= D; ++k) grad[k] = h[1 + k];
     return GPF_OK;
 }
 

@@ -54,6 +54,43 @@ class GPModel:
                                            self._stream()))
         self.M, self.log_amp, self.log_scale, self.yerr = len(X), float(log_amp), ls.copy(), float(yerr)
 
+    # -- training (gp.py:290-335) -----------------------------------------------------------
+    def nlml(self):
+        """(loss, gradient w.r.t. (log_amp, log_scale[0..D-1])) at the parameters of the last
+        ``factor``: the objective of ``_train`` and what JAX autodiff hands its optimiser."""
+        nb = C.c_size_t()
+        _capi.check(self.lib.gpf_gp_train_workspace_bytes(self.M, C.byref(nb)))
+        if getattr(self, '_train_ws', None) is None or self._train_ws.numel() < nb.value:
+            self._train_ws = torch.empty(nb.value, dtype=torch.uint8, device=self.device)
+        loss = C.c_double()
+        grad = (C.c_double * (1 + self.D))()
+        _capi.check(self.lib.gpf_gp_nlml(self.h, C.c_void_p(self._train_ws.data_ptr()), self._train_ws.numel(),
+                                         C.byref(loss), grad, self._stream()))
+        return loss.value, np.array(grad[:])
+
+    def train(self, Xtrain, Y, yerr, log_amp0=0.0, log_scale0=None):
+        """``_train``: minimise the negative log marginal likelihood from ``params_init``
+        (stress.py:281-284: log_amp = 0, log_scale = log(std(Xtrain, axis=0))) with SciPy's BFGS -- the
+        default method behind jaxopt.ScipyMinimize -- every evaluation a device factorisation plus
+        the device gradient; ends with the final build (factor) at the optimum.
+        -> (log_amp, log_scale, loss)"""
+        from scipy.optimize import minimize
+        X = np.ascontiguousarray(Xtrain, dtype=np.float64).reshape(-1, self.D)
+        if log_scale0 is None:
+            log_scale0 = np.log(np.std(X, axis=0))
+        x0 = np.concatenate([[float(log_amp0)], np.asarray(log_scale0, dtype=np.float64).reshape(self.D)])
+
+        def fun(t):
+            try:
+                self.factor(X, Y, t[0], t[1:], yerr)
+            except _capi.GapflowError:          # not positive definite at a trial point of the line search
+                return np.inf, np.zeros_like(t)
+            return self.nlml()
+
+        res = minimize(fun, x0, jac=True, method='BFGS')
+        self.factor(X, Y, res.x[0], res.x[1:], yerr)
+        return float(res.x[0]), res.x[1:].copy(), float(res.fun)
+
     def get_factor(self):
         """(L (M, M) lower, alpha (M, n_out)) as host arrays."""
         L = np.empty((self.M, self.M))

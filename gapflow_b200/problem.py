@@ -110,6 +110,7 @@ class Problem:
         self._q_synced = False       # _q_host equals the device field
         self._q_exposed = False      # user code may have edited _q_host
         self._dt_override = None
+        self._ekin_old = None
         self.pressure = _Pressure(self, 0, 'zz')
         self.wall_stress_xz = _WallStress(self, 1, 'xz')
         self.wall_stress_yz = _WallStress(self, 2, 'yz')
@@ -166,6 +167,17 @@ class Problem:
     def dt(self, value):
         self._dt_override = float(value)
 
+    @property
+    def kinetic_energy_old(self):
+        return self._ekin_old
+
+    @kinetic_energy_old.setter
+    def kinetic_energy_old(self, value):
+        """tests and scripts assign it after editing q (tests/test_wave_decay.py:102): the residual of
+        the next step is taken against it (problem.py:578)."""
+        self._ekin_old = float(value)
+        self._solver.set_scalars(ekin_old=self._ekin_old)
+
     def _push_dt(self):
         if self._dt_override is not None:
             self._solver.set_scalars(dt=self._dt_override)
@@ -180,7 +192,7 @@ class Problem:
         sc = sc or self._solver.scalars()
         self.step, self.simtime, self.residual = int(sc.step), sc.simtime, sc.residual
         self.residual_buffer = deque([sc.residual_buffer[k] for k in range(sc.residual_count)], 5)
-        self.kinetic_energy_old = sc.ekin_old
+        self._ekin_old = sc.ekin_old
         if sc.stop:
             self._stop = True
         return sc

@@ -229,6 +229,13 @@ int gpf_gp_factor(gpf_gp* g, const double* Xtrain, int M, double log_amp, const 
                   double yerr, const double* Y, void* stream);
 /* copies of L (M, M; lower) and alpha (M, n_out) to HOST arrays (tests, gp_*.txt); NULL skips */
 int gpf_gp_get_factor(gpf_gp* g, double* L_out, double* alpha_out, void* stream);
+/* The training objective of _train (gp.py:290-335) at the parameters of the last gpf_gp_factor:
+ *   loss = -sum_outputs log N(Y_o; 0, K + yerr^2 I)   (loss_so / loss_mo, gp.py:306-318)
+ * and its gradient grad[0] = d loss / d log_amp, grad[1 + d] = d loss / d log_scale[d] (what
+ * jaxopt.ScipyMinimize obtains by autodiff), so that a host optimiser can drive factor + nlml.
+ * `work`: device scratch of gpf_gp_train_workspace_bytes(M) bytes (2 M^2 doubles).  Synchronises. */
+int gpf_gp_train_workspace_bytes(int M, size_t* bytes);
+int gpf_gp_nlml(gpf_gp* g, void* work, size_t bytes, double* loss, double* grad, void* stream);
 /* _repredict_mean (gp.py:525-535): Xtest (N, D) device -> mean (n_out, N) device.  If
  * dmean_dx0_max != NULL also max_i d mean_0 / d x_0 (host scalar; Pressure.v_sound's
  * vmap(grad(eos))(Xtest)[:, 0].max(), stress.py:522-537) and the call synchronises. */

@@ -13,6 +13,9 @@ Follows (reference file:line):
 * GaPFlow/models/gp.py:223-232   _Xtest = vstack([solution, topo[:3], extra]).reshape(n_feat, -1).T
 * GaPFlow/models/stress.py:522-537  v_sound^2 = max_i d mean / d x_0 * Yscale / X_scale[0]
 * GaPFlow/db.py:264-266          normaliser: max(|x|) per column, floored at 1e-12
+* GaPFlow/models/gp.py:290-335   _train: loss = -sum_outputs gp.log_probability(Y_o), minimised by
+                                 jaxopt.ScipyMinimize (SciPy's default: BFGS) from params_init
+* GaPFlow/models/stress.py:281-284, 592-595  params_init = {log_amp: 0, log_scale: log(std(Xtrain, axis=0))}
 
 PARITY UNPINNED at the tinygp boundary: tinygp / JAX / jaxopt are neither installed nor vendored
 (pyproject.toml:33-37 pins tinygp>=0.3.0, jax<=0.9.0, jaxopt==0.8.5) and the reference holds no
@@ -120,3 +123,52 @@ def normalizer(x):
 def variance_tol(atol, rtol, Yerr, Yscale):
     """gp.py:408-410."""
     return np.maximum(atol * Yerr * Yscale, rtol * Yscale)**2
+
+
+def nlml(Xtrain, Y, yerr, log_amp, log_scale):
+    """gp.py:306-318: -sum_o log N(Y_o; 0, K + yerr^2 I) (tinygp log_probability: -1/2 y^T K^-1 y -
+    sum log L_ii - M/2 log 2 pi)."""
+    Y = np.asarray(Y, dtype=float)
+    if Y.ndim == 1:
+        Y = Y[:, None]
+    L = build(Xtrain, yerr, log_amp, log_scale)
+    a = cho_solve((L, True), Y)
+    M = len(Y)
+    return 0.5 * np.sum(Y * a) + Y.shape[1] * (np.sum(np.log(np.diag(L))) + 0.5 * M * np.log(2.0 * np.pi))
+
+
+def nlml_grad(Xtrain, Y, yerr, log_amp, log_scale):
+    """Analytic gradient of ``nlml`` w.r.t. (log_amp, log_scale[0..D-1]) -- what JAX autodiff gives the
+    reference's optimiser: 1/2 sum_ij (n_out K^-1 - sum_o a_o a_o^T)_ij dK_ij/dtheta."""
+    Y = np.asarray(Y, dtype=float)
+    if Y.ndim == 1:
+        Y = Y[:, None]
+    s = np.exp(-np.asarray(log_scale, dtype=float))
+    A = np.asarray(Xtrain, dtype=float) * s
+    L = build(Xtrain, yerr, log_amp, log_scale)
+    a = cho_solve((L, True), Y)
+    W = Y.shape[1] * cho_solve((L, True), np.eye(len(Y))) - a @ a.T
+    diff2 = (A[:, None, :] - A[None, :, :])**2
+    r = np.sqrt(diff2.sum(-1))
+    amp = np.exp(log_amp)
+    ex = np.exp(-SQRT3 * r)
+    g = [0.5 * np.sum(W * amp * (1.0 + SQRT3 * r) * ex)]
+    for d in range(A.shape[1]):
+        g.append(0.5 * np.sum(W * 3.0 * amp * ex * diff2[:, :, d]))
+    return np.array(g)
+
+
+def params_init(Xtrain):
+    """stress.py:281-284."""
+    return 0.0, np.log(np.std(np.asarray(Xtrain, dtype=float), axis=0))
+
+
+def train(Xtrain, Y, yerr, log_amp0=None, log_scale0=None):
+    """gp.py:320-323 with SciPy's BFGS and the analytic gradient -> (log_amp, log_scale, loss)."""
+    from scipy.optimize import minimize
+    D = np.asarray(Xtrain).shape[1]
+    a0, s0 = params_init(Xtrain)
+    x0 = np.concatenate([[a0 if log_amp0 is None else log_amp0], s0 if log_scale0 is None else log_scale0])
+    res = minimize(lambda t: (nlml(Xtrain, Y, yerr, t[0], t[1:]), nlml_grad(Xtrain, Y, yerr, t[0], t[1:])), x0, jac=True,
+                   method='BFGS')
+    return res.x[0], res.x[1:1 + D], res.fun

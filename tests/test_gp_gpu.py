@@ -112,3 +112,33 @@ def test_features_from_solver_storage():
     for dims in ([0], [0, 1, 6], [0, 2, 6], [0, 3]):
         X = features(s, xs, dims).cpu().numpy()
         assert np.array_equal(X, G.features(o.q, o.topo, o.extra, xs, dims))
+
+
+@pytest.mark.parametrize("model,M", [("press", 150), ("press2", 257), ("shear_x", 200)])
+def test_training_loss_and_gradient_vs_oracle(model, M):
+    """Row G9: the objective of _train (gp.py:306-318) and its gradient on the device vs the SciPy
+    oracle (1e-9 relative on the loss, 1e-7 of the gradient norm on the gradient)."""
+    from gapflow_b200.gp import GPModel
+    c = training_set(M, model)
+    gp = GPModel(M + 10, len(c['dims']), c['n_out'])
+    for la, ls in ((c['log_amp'], c['log_scale']), (0.4, c['log_scale'] - 0.3)):
+        gp.factor(c['X'], c['Y'], la, ls, c['Yerr'])
+        loss, grad = gp.nlml()
+        ref = G.nlml(c['X'], c['Y'], c['Yerr'], la, ls)
+        gref = G.nlml_grad(c['X'], c['Y'], c['Yerr'], la, ls)
+        assert abs(loss - ref) <= 1e-9 * abs(ref), (loss, ref)
+        assert np.abs(grad - gref).max() <= 1e-7 * np.abs(gref).max(), (grad, gref)
+
+
+def test_train_reaches_the_oracle_optimum():
+    """_train (gp.py:290-335): BFGS from params_init on the device objective ends where the same
+    optimiser ends on the oracle objective; the final build is the factorisation at the optimum."""
+    from gapflow_b200.gp import GPModel
+    c = training_set(80, 'press2')
+    gp = GPModel(100, len(c['dims']), c['n_out'])
+    la, ls, loss = gp.train(c['X'], c['Y'], c['Yerr'])
+    la_o, ls_o, loss_o = G.train(c['X'], c['Y'], c['Yerr'])
+    assert abs(loss - loss_o) <= 1e-6 * abs(loss_o), (loss, loss_o)
+    L, a = gp.get_factor()
+    Lr = G.build(c['X'], c['Yerr'], la, ls)
+    assert np.abs(L - Lr).max() <= 1e-9 * np.abs(Lr).max()

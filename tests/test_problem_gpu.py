@@ -144,3 +144,66 @@ def test_run_writes_the_reference_files(tmp_path, capsys):
         assert f.variables['wall_stress_xz'].shape == (4, 12, 102, 3)
         assert np.array_equal(f.variables['solution'][3], problem.q)
     assert "steps/s" in capsys.readouterr().out
+
+
+# ---------------------------------------------------------------------------------------------
+# tests/test_wave_decay.py:31-146: decay of a shear wave and of a sound wave in a flat channel
+# (cubic EOS, fixed dt, host edits of problem.q before the first update)
+# ---------------------------------------------------------------------------------------------
+DECAY = ("options:\n    output: data/decay\n    write_freq: 100\n    use_tstamp: False\n    silent: True\n"
+         "grid:\n    Lx: 3.2e-7\n    Ly: 1\n    Nx: 256\n    Ny: 1\n" + _PER +
+         "geometry:\n    type: inclined\n    hmin: 5e-9\n    hmax: 5e-9\n    U: 0.\n    V: 0.\n"
+         "numerics:\n    adaptive: 0\n    CFL: 0.5\n    dt: 1e-13\n    max_it: 5_000\n"
+         "properties:\n    EOS: cubic\n    shear: 3.92293e-05\n    bulk: 0.\n    rho0: 762.8617\n"
+         "    a: 1.33030e-1\n    b: -1.41778e2\n    c: 8.35134e4\n    d: -2.86532e6\n")
+
+
+def _decay_problem():
+    from gapflow_b200.problem import Problem
+    with io.StringIO(DECAY) as f:
+        d = config.read_yaml_input(f)
+    problem = Problem._from_dict(d)
+    problem._pre_run()
+    return problem
+
+
+@pytest.mark.parametrize('n', [1, 2, 4, 8])
+def test_shear_wave_decay(n):
+    """tests/test_wave_decay.py:85-108."""
+    problem = _decay_problem()
+    h = problem.geo['hmin']
+    kin_visc = problem.prop['shear'] / problem.prop['rho0']
+    kn = n * 2. * np.pi / problem.grid['Lx']
+    tau = h**2 / (6 * kin_visc)
+    x = problem.topo.x[1:-1, 1]
+    problem.q[2, 1:-1, :] = np.sin(kn * x)[:, None]
+    problem.kinetic_energy_old = problem.kinetic_energy
+    for i in range(200):
+        problem.update()
+        jy_ana = np.sin(kn * x) * np.exp(-2 * problem.simtime / tau)
+        np.testing.assert_almost_equal(problem.q[2, 1:-1, 1], jy_ana, decimal=4)
+
+
+@pytest.mark.parametrize('n', [1, 2, 3, 4])
+def test_sound_wave_decay(n):
+    """tests/test_wave_decay.py:111-146."""
+    problem = _decay_problem()
+    h = problem.geo['hmin']
+    kin_visc = problem.prop['shear'] / problem.prop['rho0']
+    kn = n * 2. * np.pi / problem.grid['Lx']
+    tau = h**2 / (6 * kin_visc)
+    cT = problem.pressure.v_sound
+    x = problem.topo.x[1:-1, 1]
+    problem.q[1, 1:-1, :] = np.sin(kn * x)[:, None]
+    problem.kinetic_energy_old = problem.kinetic_energy
+    k_crit = 6. * kin_visc / (h**2 * cT)
+    for i in range(400):
+        problem.update()
+        t = problem.simtime
+        if kn > k_crit:
+            sT = np.sqrt(cT**2 - (1 / tau / kn)**2)
+            env = np.exp(-t / tau) * (np.cos(sT * kn * t) - np.sin(sT * kn * t) / (tau * sT * kn))
+        else:
+            isT = np.sqrt((1 / tau / kn)**2 - cT**2)
+            env = np.exp(-t / tau) * (np.cosh(isT * kn * t) - np.sinh(isT * kn * t) / (tau * isT * kn))
+        np.testing.assert_almost_equal(problem.q[1, 1:-1, 1], np.sin(kn * x) * env, decimal=3)
