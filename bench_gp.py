@@ -80,12 +80,15 @@ def main():
         xs = xt[:ns].contiguous()
         t_mv = timed(torch, lambda: g.repredict_mean_var(xs, 1.5e-8))
         t_m_s = timed(torch, lambda: g.repredict_mean(xs), reps=3)
+        # one evaluation of the training objective and its gradient (gp.py:306-318) after a factorisation
+        t_nlml = timed(torch, lambda: g.nlml())
         launches = lib.gpf_launch_count() - l0
         Mp = (args.M + 63) // 64 * 64
         flop_var = float(Mp) * Mp * ns            # forward substitution: M^2/2 multiply-adds per query
         flop_fac = args.M**3 / 3.0
         res = {"D": D, "n_out": nout,
                "factor_ms": t_fac, "factor_tflops": flop_fac / (t_fac * 1e-3) / 1e12,
+               "nlml_grad_ms": t_nlml, "nlml_grad_tflops": 2.0 * flop_fac / (t_nlml * 1e-3) / 1e12,
                "mean": {"value": args.N / (t_mean * 1e-3), "ms": t_mean, "N": args.N,
                         "kernel_evals_per_s": args.N * args.M / (t_mean * 1e-3)},
                "mean_var": {"value": ns / (t_mv * 1e-3), "ms": t_mv, "N": ns,
