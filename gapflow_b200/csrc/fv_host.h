@@ -40,6 +40,8 @@ struct FvSolver {
     int npartial;      // capacity of partial/pflags
     int* redo;         // [2] device flags, see fv_pass_kernel
     int nrec_corr = 0; // record slots written by the last corrector pass (all its launches)
+    cudaGraphExec_t step_graph[2] = {nullptr, nullptr};   // one captured step, [until_converged]
+    void drop_graphs();
     CUtensorMap qmap[3], q0map[3], topo_map, topo2_map, ls_map;
     int topo_fast, ls_fast;   // range flags of the uploaded topography / slip length (see FvParams::static_fast)
     bool dirty_scalars;   // q changed from the host since scalars were computed

@@ -636,9 +636,15 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     return GPF_OK;
 }
 
+void FvSolver::drop_graphs() {
+    for (auto& g : step_graph)
+        if (g) { cudaGraphExecDestroy(g); g = nullptr; }
+}
+
 int FvSolver::destroy() {
     for (auto e : ev) cudaEventDestroy(e);
     ev.clear();
+    drop_graphs();
     return GPF_OK;
 }
 
@@ -704,6 +710,7 @@ int FvSolver::upload(int field, const double* data, int ncomp, int on_device, cu
             ls_fast = h[1] == 0;
         }
         P.static_fast = (P.scalars_fast && topo_fast && ls_fast) ? 1 : 0;
+        drop_graphs();            // the captured launches carry P by value
     }
     return GPF_OK;
 }
@@ -799,6 +806,46 @@ int FvSolver::step(int n, int until_converged, cudaStream_t s) {
         while ((int)ev.size() < 3 * n + 1) { cudaEvent_t e; GPF_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
         ev_steps = n;
         GPF_CUDA(cudaEventRecord(ev[0], s));
+    }
+    // One step = 5 launches whose arguments never change (all loop state lives in DevState): replayed
+    // as a CUDA graph, which takes the launch gaps between them off the step (GPF_NO_GRAPH=1: plain launches)
+    static const bool graphs = getenv("GPF_NO_GRAPH") == nullptr && getenv("GPF_DEBUG_SYNC") == nullptr;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    GPF_CUDA(cudaStreamIsCapturing(s, &cap));
+    if (graphs && !timing && n >= 1 && cap == cudaStreamCaptureStatusNone) {
+        cudaGraphExec_t& ge = step_graph[until_converged ? 1 : 0];
+        if (!ge) {
+            // first use of the variant outside a capture: sets the kernels' shared-memory attribute
+            int rc;
+            if ((rc = launch_pass<false>(*this, until_converged, s))) return rc;
+            if ((rc = launch_pass<true>(*this, until_converged, s))) return rc;
+            if ((rc = launch_finish(*this, nblk, FIN_STEP, until_converged, s))) return rc;
+            --n;
+            const long long l0 = g_launches;
+            cudaGraph_t g = nullptr;
+            cudaStream_t cs;         // the caller's stream may be the legacy default stream, which cannot capture
+            GPF_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+            cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+            if (e != cudaSuccess) { cudaStreamDestroy(cs); set_error(std::string("cudaStreamBeginCapture: ") + cudaGetErrorString(e)); return GPF_E_CUDA; }
+            rc = launch_pass<false>(*this, until_converged, cs);
+            if (!rc) rc = launch_pass<true>(*this, until_converged, cs);
+            if (!rc) rc = launch_finish(*this, nblk, FIN_STEP, until_converged, cs);
+            e = cudaStreamEndCapture(cs, &g);
+            cudaStreamDestroy(cs);
+            g_launches = l0;
+            if (rc || e != cudaSuccess) {
+                if (g) cudaGraphDestroy(g);
+                if (!rc) { set_error(std::string("CUDA graph capture of the step failed: ") + cudaGetErrorString(e)); rc = GPF_E_CUDA; }
+                return rc;
+            }
+            e = cudaGraphInstantiate(&ge, g, 0);
+            cudaGraphDestroy(g);
+            if (e != cudaSuccess) { ge = nullptr; set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); return GPF_E_CUDA; }
+        }
+        for (int it = 0; it < n; ++it) GPF_CUDA(cudaGraphLaunch(ge, s));
+        g_launches += 5LL * n;
+        dirty_scalars = false;
+        return GPF_OK;
     }
     for (int it = 0; it < n; ++it) {
         int rc;
