@@ -29,6 +29,7 @@ EOS_KEYS = {'DH': ['rho0', 'P0', 'C1', 'C2'], 'PL': ['rho0', 'P0', 'alpha'], 'vd
 BC_P, BC_D, BC_N, BC_HALO = 0, 1, 2, 3
 F_Q, F_TOPO, F_EXTRA = 0, 1, 2
 PART_ALL, PART_EDGE, PART_INTERIOR = 0, 1, 2
+IPC_HANDLE_BYTES = 64
 FIN_STEP, FIN_PRERUN, FIN_PRERUN_KEEP_EKIN, FIN_REFRESH = 0, 1, 2, 3
 
 
@@ -75,6 +76,14 @@ SIGNATURES = {
     "gpf_fv_update_host": (_i, [_vp, _dp, _i, C.POINTER(FvScalars), _vp]),
     "gpf_fv_pass": (_i, [_vp, _i, _vp]),
     "gpf_fv_pass_part": (_i, [_vp, _i, _i, _vp]),
+    "gpf_comm_create": (_i, [_i, _i, _i, _vp, C.POINTER(C.c_void_p)]),
+    "gpf_comm_connect": (_i, [_vp, _vp]),
+    "gpf_comm_destroy": (_i, [_vp]),
+    "gpf_comm_error": (_i, [_vp, C.POINTER(C.c_int)]),
+    "gpf_fv_halo_send": (_i, [_vp, _vp, _i, _i, _i, C.c_uint64, _vp]),
+    "gpf_fv_halo_recv": (_i, [_vp, _vp, _i, C.c_uint64, _vp]),
+    "gpf_fv_record_send": (_i, [_vp, _vp, _i, C.c_uint64, _vp]),
+    "gpf_fv_finish_recv": (_i, [_vp, _vp, _i, C.c_uint64, _vp, _vp]),
     "gpf_fv_halo_pack": (_i, [_vp, _i, _dp, _vp]),
     "gpf_fv_halo_unpack": (_i, [_vp, _i, _dp, _vp]),
     "gpf_fv_reduce_local": (_i, [_vp, _i, _dp, _vp]),

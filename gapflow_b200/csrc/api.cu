@@ -4,6 +4,7 @@
 #include <string>
 #include "fv_host.h"
 #include "gp_host.h"
+#include "slab_comm.cuh"
 
 namespace gpf {
 static thread_local std::string t_err;
@@ -21,6 +22,9 @@ struct gpf_fv {
 };
 struct gpf_gp {
     GpModel G;
+};
+struct gpf_comm {
+    SlabComm C;
 };
 
 #define GPF_TRY try {
@@ -244,6 +248,43 @@ int gpf_gp_factor(gpf_gp* g, const double* Xtrain, int M, double log_amp, const 
 }
 int gpf_gp_get_factor(gpf_gp* g, double* L_out, double* alpha_out, void* stream) {
     GPF_TRY NEED(g) return g->G.get_factor(L_out, alpha_out, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_comm_create(int world, int rank, int Ny, unsigned char* handle_out, gpf_comm** out) {
+    GPF_TRY
+    NEED(handle_out && out)
+    static_assert(sizeof(cudaIpcMemHandle_t) == GPF_IPC_HANDLE_BYTES, "IPC handle size");
+    gpf_comm* c = new gpf_comm();
+    int rc = c->C.create(world, rank, Ny);
+    if (rc) { delete c; return rc; }
+    memcpy(handle_out, &c->C.handle, GPF_IPC_HANDLE_BYTES);
+    *out = c;
+    return GPF_OK;
+    GPF_CATCH
+}
+int gpf_comm_connect(gpf_comm* c, const unsigned char* handles) {
+    GPF_TRY NEED(c && handles) return c->C.connect(handles); GPF_CATCH
+}
+int gpf_comm_destroy(gpf_comm* c) {
+    GPF_TRY NEED(c) c->C.destroy(); delete c; return GPF_OK; GPF_CATCH
+}
+int gpf_comm_error(gpf_comm* c, int* err) {
+    GPF_TRY
+    NEED(c && err)
+    if (cudaMemcpy(err, c->C.err(), sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) { set_error("cudaMemcpy failed in gpf_comm_error"); return GPF_E_CUDA; }
+    return GPF_OK;
+    GPF_CATCH
+}
+int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, uint64_t seq, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.halo_send(c->C, rel, lo, hi, seq, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_halo_recv(gpf_fv* s, gpf_comm* c, int rel, uint64_t seq, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.halo_recv(c->C, rel, seq, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_record_send(gpf_fv* s, gpf_comm* c, int kind, uint64_t seq, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.record_send(c->C, kind, seq, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_finish_recv(gpf_fv* s, gpf_comm* c, int mode, uint64_t seq, double* recs_out, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.finish_recv(c->C, mode, seq, recs_out, (cudaStream_t)stream); GPF_CATCH
 }
 int gpf_gp_train_workspace_bytes(int M, size_t* bytes) {
     GPF_TRY NEED(bytes && M > 0) *bytes = gpf::GpModel::train_workspace_bytes(M); return GPF_OK; GPF_CATCH

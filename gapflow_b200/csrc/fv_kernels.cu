@@ -6,6 +6,7 @@
 #include <vector>
 #include "fv_pass.cuh"
 #include "fv_host.h"
+#include "slab_comm.cuh"
 
 namespace gpf {
 
@@ -20,24 +21,59 @@ enum { FIN_STEP = 0, FIN_PRERUN = 1, FIN_PRERUN_KEEP_EKIN = 2, FIN_REFRESH = 3 }
 // Slab decomposition: `recs` (one Rec5 per rank, gathered in rank order) replaces the per-block
 // records, so every rank folds the same numbers in the same order and advances identically.
 // `rec_out` != nullptr: only fold this rank's per-block records into one Rec5 and return.
+// ---- system-scope flag protocol of the peer-memory exchange (slab_comm.cuh) ----------------
+constexpr unsigned long long SPIN_NS = 5ull * 1000 * 1000 * 1000;
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// waits until *flag >= seq; gives up after SPIN_NS (a peer died) and raises *err instead of hanging the GPU
+__device__ __forceinline__ void spin_until(const unsigned long long* flag, unsigned long long seq, int* err) {
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys(flag) < seq) {
+        if (global_ns() - t0 > SPIN_NS) {
+            if (err) *err = 1;
+            return;
+        }
+        __nanosleep(64);
+    }
+}
+
 __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ FvParams P, DevState* st,
                                                         const Partial* part, const int* pflags, int nblk,
                                                         int mode, int until_converged, RefreshOut* ro,
-                                                        const Rec5* recs, int nrec, Rec5* rec_out, int xslot) {
+                                                        const Rec5* recs, int nrec, Rec5* rec_out, int xslot,
+                                                        const unsigned long long* wait_flags = nullptr,
+                                                        unsigned long long wait_seq = 0, int* werr = nullptr,
+                                                        int rec_stride = 5) {
+    const int tid = threadIdx.x;
+    if (wait_flags) {        // records written into this rank's buffer by its peers (slab_comm.cuh)
+        if (tid < nrec) spin_until(wait_flags + tid, wait_seq, werr);
+        __syncthreads();
+    }
     if (mode == FIN_STEP && (st->stop || (until_converged && st->halt))) return;
     __shared__ double sE[256], sV[256], sC[256], sM[256];
     __shared__ int sF[256];
-    const int tid = threadIdx.x;
     double E = 0.0, VM = -INFINITY, CM = -INFINITY, M = 0.0;
     int F = 0;
     if (recs) {
         if (tid == 0)
             for (int r = 0; r < nrec; ++r) {      // rank order, sequential: identical on every rank
-                E += recs[r].ekin;
-                M += recs[r].mass;
-                VM = fmax(VM, recs[r].vmax2);
-                CM = fmax(CM, recs[r].cs2);
-                F |= (int)recs[r].flags;
+                const double* rr = reinterpret_cast<const double*>(recs) + (size_t)r * rec_stride;   // L2 reads: peers wrote them
+                E += __ldcg(rr + 0);
+                M += __ldcg(rr + 3);
+                VM = fmax(VM, __ldcg(rr + 1));
+                CM = fmax(CM, __ldcg(rr + 2));
+                F |= (int)__ldcg(rr + 4);
             }
     } else {
         for (int b = tid; b < nblk; b += 256) {
@@ -222,6 +258,86 @@ __global__ void fv_halo_unpack_kernel(const __grid_constant__ FvParams P, const 
     if (P.bc.type[side][0] != GPF_BC_HALO) return;
     const int i = side == 0 ? 0 : P.L.Nx + 1;
     q[c * P.L.plane + (size_t)i * P.L.pitch + (j + 1)] = recv[t];
+}
+
+// The same exchange over peer memory (slab_comm.cuh): the sender stores its edge rows straight into
+// the neighbours' buffers through NVLink and publishes a sequence number; the receiver waits for
+// that number and fills its ghost rows.  One block each: they must fit beside the persistent CTAs
+// of the interior launch that runs meanwhile.
+__global__ void __launch_bounds__(512) fv_halo_send_kernel(const __grid_constant__ FvParams P, const DevState* st,
+                                                           double* const* qbufs, int rel, double* dst_lo, double* dst_hi,
+                                                           unsigned long long* flag_lo, unsigned long long* flag_hi,
+                                                           unsigned long long seq) {
+    const double* q = qbufs[(st->cur + rel) % 3];
+    const int Ny2 = P.L.Ny + 2;
+    for (int t = threadIdx.x; t < 6 * Ny2; t += blockDim.x) {
+        const int side = t / (3 * Ny2), rem = t % (3 * Ny2), c = rem / Ny2, j = rem % Ny2;
+        double* dst = side == 0 ? dst_lo : dst_hi;       // row 1 -> lower neighbour, row Nx -> upper neighbour
+        if (!dst) continue;
+        const int i = side == 0 ? 1 : P.L.Nx;
+        dst[rem] = q[c * P.L.plane + (size_t)i * P.L.pitch + (j + 1)];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0 && flag_lo) st_release_sys(flag_lo, seq);
+    if (threadIdx.x == 1 && flag_hi) st_release_sys(flag_hi, seq);
+}
+__global__ void __launch_bounds__(512) fv_halo_recv_kernel(const __grid_constant__ FvParams P, const DevState* st,
+                                                           double* const* qbufs, int rel, const double* src,
+                                                           const unsigned long long* flags, unsigned long long seq, int* err) {
+    if (threadIdx.x < 2 && P.bc.type[threadIdx.x][0] == GPF_BC_HALO) spin_until(flags + threadIdx.x, seq, err);
+    __syncthreads();
+    double* q = qbufs[(st->cur + rel) % 3];
+    const int Ny2 = P.L.Ny + 2;
+    for (int t = threadIdx.x; t < 6 * Ny2; t += blockDim.x) {
+        const int side = t / (3 * Ny2), c = (t / Ny2) % 3, j = t % Ny2;
+        if (P.bc.type[side][0] != GPF_BC_HALO) continue;
+        const int i = side == 0 ? 0 : P.L.Nx + 1;
+        q[c * P.L.plane + (size_t)i * P.L.pitch + (j + 1)] = __ldcg(src + t);     // L2: a peer wrote it
+    }
+}
+// this rank's per-block records folded into one Rec5 (as fv_finish_kernel does for rec_out) and
+// stored into every rank's record table, each followed by its sequence number
+__global__ void __launch_bounds__(256) fv_record_send_kernel(const Partial* part, const int* pflags, int nblk, int xslot,
+                                                             unsigned char* const* peers, size_t off_recs, size_t off_rflag,
+                                                             int world, int rank, int parity, unsigned long long seq) {
+    __shared__ double sE[256], sV[256], sC[256], sM[256];
+    __shared__ int sF[256];
+    const int tid = threadIdx.x;
+    double E = 0.0, VM = -INFINITY, CM = -INFINITY, M = 0.0;
+    int F = 0;
+    for (int b = tid; b < nblk; b += 256) {
+        E += part[b].ekin;
+        M += part[b].mass;
+        VM = fmax(VM, part[b].vmax2);
+        CM = fmax(CM, part[b].cs2);
+        F |= pflags[b];
+    }
+    if (xslot >= 0 && tid == 255) {
+        E += part[xslot].ekin;
+        M += part[xslot].mass;
+        VM = fmax(VM, part[xslot].vmax2);
+        CM = fmax(CM, part[xslot].cs2);
+        F |= pflags[xslot];
+    }
+    sE[tid] = E; sV[tid] = VM; sC[tid] = CM; sM[tid] = M; sF[tid] = F;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (tid < s) {
+            sE[tid] += sE[tid + s];
+            sM[tid] += sM[tid + s];
+            sV[tid] = fmax(sV[tid], sV[tid + s]);
+            sC[tid] = fmax(sC[tid], sC[tid + s]);
+            sF[tid] |= sF[tid + s];
+        }
+        __syncthreads();
+    }
+    if (tid < world) {
+        double* dst = reinterpret_cast<double*>(peers[tid] + off_recs) + ((size_t)parity * world + rank) * 8;
+        dst[0] = sE[0]; dst[1] = sV[0]; dst[2] = sC[0]; dst[3] = sM[0]; dst[4] = (double)sF[0];
+        __threadfence_system();
+        st_release_sys(reinterpret_cast<unsigned long long*>(peers[tid] + off_rflag) + rank, seq);
+    }
 }
 
 // Periodic-x ring: the global ghost rows (row 0 on the first rank, row Nx+1 on the last) belong
@@ -450,8 +566,15 @@ static int eos_pack(const gpf_fv_cfg& c, EosParams* e) {
     return GPF_E_INVALID;
 }
 
-// persistent CTAs of a pass launch: fv_ctas_per_sm() per SM of the current device, at most one per tile
-static int pass_ctas(int ntiles, bool corr) {
+// persistent CTAs of a pass launch: fv_ctas_per_sm() per SM of the current device minus `reserve`,
+// at most one per tile -- and then the largest count G below that whose column stride G mod nty is
+// coprime with nty (nty = tiles along y).  CTA b walks tiles b, b + G, b + 2G, ...; tile t sits in
+// tile column t mod nty.  When G mod nty shares a factor >= 4 with nty every CTA keeps returning to
+// the same few tile columns, and on B200 that costs 15-20 % of the pass (4096^2, nty = 64: 296 CTAs
+// 0.310 ms, 295 CTAs 0.256 ms per corrector pass; 444 / 443: 0.210 / 0.194 ms per predictor pass;
+// every multiple of 4 is slow, everything else fast: profiles/r1r_grid_scan.txt).
+static int gcd_int(int a, int b) { while (b) { const int t = a % b; a = b; b = t; } return a; }
+static int pass_ctas(int ntiles, bool corr, int nty = 0, int reserve = 0) {
     static int sms = 0;
     if (!sms) {
         int dev = 0;
@@ -459,8 +582,13 @@ static int pass_ctas(int ntiles, bool corr) {
             sms = 148;            // B200 (also used when no device is present: workspace sizing only)
         cudaGetLastError();
     }
-    const int n = sms * fv_ctas_per_sm(corr);
-    return ntiles < n ? ntiles : n;
+    int n = sms * fv_ctas_per_sm(corr);
+    if (n > 4 * reserve) n -= reserve;
+    if (ntiles <= n) return ntiles;              // one tile per CTA: no walk
+    if (nty > 1)
+        for (int g = n; g > n - 16 && g > 1; --g)
+            if (gcd_int(g % nty, nty) == 1) return g;
+    return n;
 }
 
 int pack_params(const gpf_fv_cfg& c, FvParams* P) {
@@ -508,7 +636,7 @@ int pack_params(const gpf_fv_cfg& c, FvParams* P) {
     P->static_fast = 0;           // decided when topography / slip length are uploaded
     P->nblk_y = (c.Nx + TX - 1) / TX;
     P->nblk_x = (c.Ny + TY - 1) / TY;
-    P->ncta = pass_ctas(P->nblk_x * P->nblk_y, true);      // the corrector writes the records
+    P->ncta = pass_ctas(P->nblk_x * P->nblk_y, true, P->nblk_x);      // the corrector writes the records
     return GPF_OK;
 }
 
@@ -755,14 +883,13 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags; A.redo = S.redo;
     A.until_converged = until_converged;
     // INTERIOR leaves a few CTA slots empty so that the exchange kernels of the side stream (pack,
-    // NCCL send/recv, unpack) find room beside the persistent CTAs (GPF_INTERIOR_SLACK, default 4)
-    static const int slack = [] { const char* e = getenv("GPF_INTERIOR_SLACK"); return e ? atoi(e) : 4; }();
-    const int n_edge = pass_ctas(2 * nty, CORR);
-    int n_int = pass_ctas((nbx - 2) * nty, CORR);
-    if (n_int > 4 * slack) n_int -= slack;
+    // send, receive) find room beside the persistent CTAs (GPF_INTERIOR_SLACK, default 2)
+    static const int slack = [] { const char* e = getenv("GPF_INTERIOR_SLACK"); return e ? atoi(e) : 2; }();
+    const int n_edge = pass_ctas(2 * nty, CORR, nty);
+    const int n_int = pass_ctas((nbx - 2) * nty, CORR, nty, slack);
     if (part == GPF_PART_ALL) {
         A.ntiles = nbx * nty; A.bx_mul = 1; A.bx_off = 0; A.rec0 = 0;
-        if (CORR) S.nrec_corr = pass_ctas(A.ntiles, true);
+        if (CORR) S.nrec_corr = pass_ctas(A.ntiles, true, nty);
     } else if (part == GPF_PART_EDGE) {
         A.ntiles = 2 * nty; A.bx_mul = nbx - 1; A.bx_off = 0; A.rec0 = 0;
         if (CORR) S.nrec_corr = n_edge + n_int;
@@ -773,7 +900,7 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     const bool ls = S.P.has_extra != 0;
     const bool dh = S.P.eos.kind == GPF_EOS_DH;
     const bool xf = S.P.xflow != 0;
-    const int n = (part == GPF_PART_INTERIOR) ? n_int : pass_ctas(A.ntiles, CORR);
+    const int n = (part == GPF_PART_INTERIOR) ? n_int : pass_ctas(A.ntiles, CORR, nty);
     const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, n, s)
                                                    : launch_pass_exact(A, CORR, ls, dh, xf, n, s);
     if (rc) return rc;
@@ -908,6 +1035,128 @@ int FvSolver::finish(int mode, const double* recs, int nrec, cudaStream_t s) {
     if (mode < FIN_STEP || mode > FIN_REFRESH || !recs || nrec < 1) { set_error("bad finish arguments"); return GPF_E_INVALID; }
     int rc = launch_finish(*this, 0, mode, 0, s, reinterpret_cast<const Rec5*>(recs), nrec);
     if (rc) return rc;
+    if (mode != FIN_REFRESH) dirty_scalars = false;
+    else refresh_valid = true;
+    return GPF_OK;
+}
+
+// ---- peer-memory exchange (slab_comm.cuh) --------------------------------------------------
+SlabCommLayout SlabComm::layout(int world, int rank, int Ny2) {
+    SlabCommLayout l;
+    l.world = world; l.rank = rank; l.Ny2 = Ny2;
+    size_t o = 0;
+    l.off_halo = o; o += align_up((size_t)2 * 2 * 3 * Ny2 * 8, 256);
+    l.off_hflag = o; o += 256;
+    l.off_recs = o; o += align_up((size_t)2 * world * 8 * 8, 256);
+    l.off_rflag = o; o += align_up((size_t)world * 8, 256);
+    l.off_err = o; o += 256;
+    l.off_ptrs = o; o += align_up((size_t)world * sizeof(void*), 256);
+    l.bytes = o;
+    return l;
+}
+
+int SlabComm::create(int world, int rank, int Ny) {
+    if (world < 1 || rank < 0 || rank >= world || Ny < 1 || world > 256) { set_error("bad communicator shape"); return GPF_E_INVALID; }
+    lay = layout(world, rank, Ny + 2);
+    GPF_CUDA(cudaMalloc(&local, lay.bytes));
+    GPF_CUDA(cudaMemset(local, 0, lay.bytes));
+    GPF_CUDA(cudaDeviceSynchronize());
+    GPF_CUDA(cudaIpcGetMemHandle(&handle, local));
+    peer.assign(world, nullptr);
+    peer[rank] = local;
+    d_peer = reinterpret_cast<unsigned char**>(local + lay.off_ptrs);
+    return GPF_OK;
+}
+
+int SlabComm::connect(const unsigned char* handles) {
+    for (int r = 0; r < lay.world; ++r) {
+        if (r == lay.rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + (size_t)r * sizeof(h), sizeof(h));
+        void* p = nullptr;
+        GPF_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        peer[r] = static_cast<unsigned char*>(p);
+    }
+    GPF_CUDA(cudaMemcpy(d_peer, peer.data(), (size_t)lay.world * sizeof(void*), cudaMemcpyHostToDevice));
+    connected = true;
+    return GPF_OK;
+}
+
+int SlabComm::destroy() {
+    for (int r = 0; r < (int)peer.size(); ++r)
+        if (r != lay.rank && peer[r]) cudaIpcCloseMemHandle(peer[r]);
+    peer.clear();
+    if (local) cudaFree(local);
+    local = nullptr;
+    return GPF_OK;
+}
+
+static int comm_ok(const FvSolver& S, const SlabComm& c) {
+    if (!c.connected) { set_error("communicator not connected"); return GPF_E_STATE; }
+    if (c.lay.Ny2 != S.cfg.Ny + 2) { set_error("communicator built for another Ny"); return GPF_E_INVALID; }
+    return GPF_OK;
+}
+
+int FvSolver::halo_send(SlabComm& c, int rel, int lo, int hi, unsigned long long seq, cudaStream_t s) {
+    int rc = comm_ok(*this, c);
+    if (rc) return rc;
+    if (rel < 0 || rel > 2 || lo >= c.lay.world || hi >= c.lay.world) { set_error("bad halo_send arguments"); return GPF_E_INVALID; }
+    const int par = (int)(seq & 1ull);
+    // my row 1 is the lower neighbour's upper ghost row (its side 1); my row Nx the upper neighbour's side 0
+    fv_halo_send_kernel<<<1, 512, 0, s>>>(P, st, qtable, rel, lo >= 0 ? c.halo(lo, par, 1) : nullptr,
+                                          hi >= 0 ? c.halo(hi, par, 0) : nullptr, lo >= 0 ? c.hflag(lo, 1) : nullptr,
+                                          hi >= 0 ? c.hflag(hi, 0) : nullptr, seq);
+    g_launches++;
+    return debug_check("fv_halo_send_kernel", s);
+}
+
+int FvSolver::halo_recv(SlabComm& c, int rel, unsigned long long seq, cudaStream_t s) {
+    int rc = comm_ok(*this, c);
+    if (rc) return rc;
+    if (rel < 0 || rel > 2) { set_error("rel must be 0, 1 or 2"); return GPF_E_INVALID; }
+    const int par = (int)(seq & 1ull);
+    fv_halo_recv_kernel<<<1, 512, 0, s>>>(P, st, qtable, rel, c.halo(c.lay.rank, par, 0), c.hflag(c.lay.rank, 0), seq, c.err());
+    g_launches++;
+    if (rel == 0) { dirty_scalars = true; refresh_valid = false; }
+    rc = debug_check("fv_halo_recv_kernel", s);
+    if (rc) return rc;
+    if (rel == 2 && (P.bc.edge[0] || P.bc.edge[1])) {
+        const int slot = npartial - 1;
+        if (P.eos.kind == GPF_EOS_DH) fv_edge_rows_kernel<GPF_EOS_DH><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
+        else fv_edge_rows_kernel<-1><<<1, 256, 0, s>>>(P, st, qtable, rel, partial, pflags, slot);
+        g_launches++;
+        rc = debug_check("fv_edge_rows_kernel", s);
+    }
+    return rc;
+}
+
+int FvSolver::record_send(SlabComm& c, int kind, unsigned long long seq, cudaStream_t s) {
+    int rc = comm_ok(*this, c);
+    if (rc) return rc;
+    int nblk = nrec_corr;
+    int xslot = (P.bc.edge[0] || P.bc.edge[1]) ? npartial - 1 : -1;
+    if (kind == 1) {
+        if ((rc = launch_reduce(*this, s))) return rc;
+        nblk = REDUCE_BLOCKS;
+        xslot = -1;
+    }
+    fv_record_send_kernel<<<1, 256, 0, s>>>(partial, pflags, nblk, xslot, c.d_peer, c.lay.off_recs, c.lay.off_rflag,
+                                            c.lay.world, c.lay.rank, (int)(seq & 1ull), seq);
+    g_launches++;
+    return debug_check("fv_record_send_kernel", s);
+}
+
+int FvSolver::finish_recv(SlabComm& c, int mode, unsigned long long seq, double* recs_out, cudaStream_t s) {
+    int rc = comm_ok(*this, c);
+    if (rc) return rc;
+    if (mode < FIN_STEP || mode > FIN_REFRESH) { set_error("bad finish mode"); return GPF_E_INVALID; }
+    const double* recs = c.recs(c.lay.rank, (int)(seq & 1ull));
+    fv_finish_kernel<<<1, 256, 0, s>>>(P, st, partial, pflags, 0, mode, 0, refresh, reinterpret_cast<const Rec5*>(recs),
+                                       c.lay.world, nullptr, -1, c.rflag(c.lay.rank), seq, c.err(), 8);
+    g_launches++;
+    if ((rc = debug_check("fv_finish_kernel", s))) return rc;
+    if (recs_out)
+        GPF_CUDA(cudaMemcpy2DAsync(recs_out, 5 * 8, recs, 8 * 8, 5 * 8, c.lay.world, cudaMemcpyDeviceToDevice, s));
     if (mode != FIN_REFRESH) dirty_scalars = false;
     else refresh_valid = true;
     return GPF_OK;

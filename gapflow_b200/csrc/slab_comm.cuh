@@ -1,0 +1,46 @@
+// Slab neighbours and record fold over peer memory (NVLink P2P stores), no NCCL on the step path.
+//
+// Each rank owns one small cudaMalloc'd buffer that its peers map through CUDA IPC:
+//   halo [2 parities][2 sides][3][Ny+2]   edge rows written by the neighbours (side 0: from the lower
+//                                          neighbour -> ghost row 0; side 1: from the upper -> row Nx+1)
+//   hflag[2 sides]                         sequence number of the last completed halo write per side
+//   recs [2 parities][world][8]            one folded record (Rec5, padded) per rank
+//   rflag[world]                           sequence number of the last record written by rank w
+//   err                                    set when a wait timed out (a peer died): results are garbage
+// A sender stores the data into the receiver's buffer, fences at system scope and then publishes the
+// sequence number; the receiver's kernel spins on its own flag (bounded by SPIN_NS) and copies the
+// rows into its ghost cells.  Slots alternate with the sequence parity: a slot is rewritten two
+// exchanges later, which the sender's own stream order places after the receiver has consumed it.
+#pragma once
+#include <cuda_runtime.h>
+#include <vector>
+#include "gpf_types.h"
+
+namespace gpf {
+
+struct SlabCommLayout {
+    int world, rank, Ny2;
+    size_t off_halo, off_hflag, off_recs, off_rflag, off_err, off_ptrs, bytes;
+};
+
+struct SlabComm {
+    SlabCommLayout lay;
+    unsigned char* local = nullptr;
+    std::vector<unsigned char*> peer;      // [world]; peer[rank] == local
+    unsigned char** d_peer = nullptr;      // the same table on the device (inside `local`)
+    cudaIpcMemHandle_t handle;
+    bool connected = false;
+    static SlabCommLayout layout(int world, int rank, int Ny2);
+    int create(int world, int rank, int Ny);
+    int connect(const unsigned char* handles);     // [world][sizeof(cudaIpcMemHandle_t)]
+    int destroy();
+    double* halo(int r, int parity, int side) const {
+        return reinterpret_cast<double*>(peer[r] + lay.off_halo) + ((size_t)parity * 2 + side) * 3 * lay.Ny2;
+    }
+    unsigned long long* hflag(int r, int side) const { return reinterpret_cast<unsigned long long*>(peer[r] + lay.off_hflag) + side; }
+    double* recs(int r, int parity) const { return reinterpret_cast<double*>(peer[r] + lay.off_recs) + (size_t)parity * lay.world * 8; }
+    unsigned long long* rflag(int r) const { return reinterpret_cast<unsigned long long*>(peer[r] + lay.off_rflag); }
+    int* err() const { return reinterpret_cast<int*>(local + lay.off_err); }
+};
+
+}  // namespace gpf

@@ -15,6 +15,7 @@ Per ``Problem.update()``: 2 passes x (1 neighbour exchange of 3*(Ny+2) doubles p
 + 1 all-gather of 5 doubles.  No data-path collective beyond that.
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -90,7 +91,7 @@ class SlabSolver:
     rows ``start .. start+n+1`` of the global padded arrays (shape ``(ncomp, n+2, Ny+2)``)."""
 
     def __init__(self, grid, geo, prop, numerics, topo, q=None, extra=None, rank=None, world=None, group=None,
-                 device=None, exchanger=None, arith='exact', overlap=True):
+                 device=None, exchanger=None, arith='exact', overlap=True, peer=None):
         from .fv import FVSolver
         self.rank = dist.get_rank(group) if rank is None else rank
         self.world = dist.get_world_size(group) if world is None else world
@@ -114,7 +115,16 @@ class SlabSolver:
         self._timing, self._ev = False, []
         # edge tile rows first, their exchange on a side stream under the interior launch
         self.overlap = overlap and self.world > 1
-        self._side = torch.cuda.Stream(device=dev) if self.overlap else None
+        self._side = torch.cuda.Stream(device=dev, priority=-1) if self.overlap else None
+        # peer=True: halo rows and records go through peer-mapped memory (CUDA IPC over NVLink) written
+        # and awaited by the library's own kernels; None: whenever ranks are separate processes on CUDA
+        # devices of one node (GPF_SLAB_PEER=0 keeps the grouped NCCL send/recv + all-gather)
+        self._comm, self._hseq, self._rseq = None, 0, 0
+        if peer is None:
+            peer = (exchanger is None and self.world > 1 and dist.is_initialized() and dist.get_backend(group) == 'nccl'
+                    and os.environ.get('GPF_SLAB_PEER', '1') != '0')
+        if peer:
+            self._connect_peers(g['Ny'], group)
         if exchanger is None:
             # Problem.__init__ computes kinetic_energy_old on the _initialize state (problem.py:670)
             self.pre_run(reset_ekin_old=True)
@@ -125,6 +135,37 @@ class SlabSolver:
     # -- building blocks ---------------------------------------------------------------
     def _s(self):
         return self.fv._stream()
+
+    def _connect_peers(self, Ny, group):
+        """Every rank creates its buffer, the IPC handles are all-gathered, every rank maps the others'."""
+        n = _capi.IPC_HANDLE_BYTES
+        mine = (C.c_ubyte * n)()
+        comm = C.c_void_p()
+        _capi.check(self.lib.gpf_comm_create(self.world, self.rank, int(Ny), mine, C.byref(comm)))
+        dev = self.fv.device
+        local = torch.tensor(list(mine), dtype=torch.uint8, device=dev)
+        allh = torch.zeros(self.world * n, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(allh, local, group=group)
+        buf = (C.c_ubyte * (self.world * n)).from_buffer_copy(allh.cpu().numpy().tobytes())
+        _capi.check(self.lib.gpf_comm_connect(comm, buf))
+        dist.barrier(group=group)            # nobody writes into a buffer that is still being zeroed
+        self._comm = comm
+
+    def close(self):
+        if self._comm is not None:
+            torch.cuda.synchronize(self.fv.device)
+            if dist.is_initialized():
+                dist.barrier(group=self.ex.group)
+            self.lib.gpf_comm_destroy(self._comm)
+            self._comm = None
+
+    def comm_error(self):
+        """True if a wait on a peer timed out (a peer process died): the fields are then garbage."""
+        if self._comm is None:
+            return False
+        e = C.c_int()
+        _capi.check(self.lib.gpf_comm_error(self._comm, C.byref(e)))
+        return bool(e.value)
 
     def set_q(self, q):
         """this rank's padded slab (3, n+2, Ny+2) of the global padded q"""
@@ -156,11 +197,24 @@ class SlabSolver:
         """halo rows of buffer `rel` (0 current, 1 predictor output, 2 corrector output)"""
         if self.world == 1:
             return
+        if self._comm is not None:
+            self._hseq += 1
+            lo = -1 if self.ex.lo is None else self.ex.lo
+            hi = -1 if self.ex.hi is None else self.ex.hi
+            _capi.check(self.lib.gpf_fv_halo_send(self.h, self._comm, rel, lo, hi, self._hseq, self._s()))
+            _capi.check(self.lib.gpf_fv_halo_recv(self.h, self._comm, rel, self._hseq, self._s()))
+            return
         self._pack(rel)
         self.ex.exchange(self.send, self.recv)
         self._unpack(rel)
 
     def _fold(self, kind, mode):
+        if self._comm is not None:
+            self._rseq += 1
+            _capi.check(self.lib.gpf_fv_record_send(self.h, self._comm, kind, self._rseq, self._s()))
+            _capi.check(self.lib.gpf_fv_finish_recv(self.h, self._comm, mode, self._rseq,
+                                                    C.c_void_p(self.recs.data_ptr()), self._s()))
+            return
         self._record(kind)
         self.ex.gather(self.rec, self.recs)
         self._finish(mode)
@@ -181,15 +235,16 @@ class SlabSolver:
         main = torch.cuda.current_stream(self.fv.device)
         for _ in range(n):
             for c, rel in ((0, 1), (1, 2)):
-                if not self.overlap:
+                if not self.overlap or self._timing:
                     self._pass(c)
                     self._exchange(rel)
                     continue
-                # the first and the last tile row, then their exchange on the side stream while
-                # the interior tile rows are computed (a pass never reads the buffer it writes)
-                self._pass(c, _capi.PART_EDGE)
+                # side stream (high priority): the first and the last tile row, then their exchange;
+                # main stream: the interior tile rows meanwhile.  The two launches touch disjoint
+                # tiles, records and ghost rows, and a pass never reads the buffer it writes.
                 self._side.wait_stream(main)
                 with torch.cuda.stream(self._side):
+                    self._pass(c, _capi.PART_EDGE)
                     self._exchange(rel)
                 self._pass(c, _capi.PART_INTERIOR)
                 main.wait_stream(self._side)

@@ -211,6 +211,29 @@ int gpf_stress_top(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
 int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls,
                    double* out, size_t n, void* stream);
 
+/* The same two exchanges over peer memory instead of a communication library: every rank owns a
+ * small buffer that its peers map through CUDA IPC (one node, NVLink / NVSwitch).  The sending
+ * kernel stores the edge rows (the folded record) straight into the receivers' buffers and then
+ * publishes a sequence number; the receiving kernel waits for it (bounded: a dead peer raises the
+ * error flag after 5 s instead of hanging the GPU) and fills the ghost rows (folds the records and
+ * advances the loop state).  No reference counterpart (problem.py:676-707 is a local copy).
+ *   create on every rank -> all-gather the GPF_IPC_HANDLE_BYTES handles by any means -> connect ->
+ *   barrier; then per exchange k = 1, 2, ... (the same k on every rank):
+ *     halo_send(rel, lo, hi, k); halo_recv(rel, k)        lo / hi: neighbour ranks, -1 = none
+ *   and per fold m = 1, 2, ...:
+ *     record_send(kind, m); finish_recv(mode, m, recs_out)   kind, mode as reduce_local / finish;
+ *     recs_out: device array [world][5] or NULL. */
+#define GPF_IPC_HANDLE_BYTES 64
+typedef struct gpf_comm gpf_comm;
+int gpf_comm_create(int world, int rank, int Ny, unsigned char* handle_out, gpf_comm** out);
+int gpf_comm_connect(gpf_comm* c, const unsigned char* handles /* [world][GPF_IPC_HANDLE_BYTES] */);
+int gpf_comm_destroy(gpf_comm* c);
+int gpf_comm_error(gpf_comm* c, int* err);       /* synchronises; 1 = a wait timed out */
+int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, uint64_t seq, void* stream);
+int gpf_fv_halo_recv(gpf_fv* s, gpf_comm* c, int rel, uint64_t seq, void* stream);
+int gpf_fv_record_send(gpf_fv* s, gpf_comm* c, int kind, uint64_t seq, void* stream);
+int gpf_fv_finish_recv(gpf_fv* s, gpf_comm* c, int mode, uint64_t seq, double* recs_out, void* stream);
+
 /* --- GP surrogate inference (GaPFlow/models/gp.py) -------------------------------------
  * One handle per GP model (pressure: n_out = 1; wall shear: n_out = 2 outputs sharing one
  * kernel, gp.py:546-552).  Kernel: exp(log_amp) * Matern32(|| exp(-log_scale) . (x - x') ||)
