@@ -380,7 +380,7 @@ def run_gpu(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one corrector launch at 4096^2 from the
 # committed `ncu --set full` capture (profiles/); None until a capture exists.
-TRAFFIC_CORR_BYTES = 1557810552  # profiles/r1j_ncu_fv_pass_summary.csv: 1.166907 GB read + 390.904 MB written
+TRAFFIC_CORR_BYTES = 1486998624  # profiles/r1s_ncu_fv_pass_summary.csv: 1.105212 GB read + 381.787 MB written
 
 
 _RESULT_FD = None

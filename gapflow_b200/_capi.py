@@ -80,10 +80,11 @@ SIGNATURES = {
     "gpf_comm_connect": (_i, [_vp, _vp]),
     "gpf_comm_destroy": (_i, [_vp]),
     "gpf_comm_error": (_i, [_vp, C.POINTER(C.c_int)]),
-    "gpf_fv_halo_send": (_i, [_vp, _vp, _i, _i, _i, C.c_uint64, _vp]),
-    "gpf_fv_halo_recv": (_i, [_vp, _vp, _i, C.c_uint64, _vp]),
-    "gpf_fv_record_send": (_i, [_vp, _vp, _i, C.c_uint64, _vp]),
-    "gpf_fv_finish_recv": (_i, [_vp, _vp, _i, C.c_uint64, _vp, _vp]),
+    "gpf_fv_halo_send": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "gpf_fv_halo_recv": (_i, [_vp, _vp, _i, _vp]),
+    "gpf_fv_record_send": (_i, [_vp, _vp, _i, _vp]),
+    "gpf_fv_finish_recv": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "gpf_fv_slab_step": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "gpf_fv_halo_pack": (_i, [_vp, _i, _dp, _vp]),
     "gpf_fv_halo_unpack": (_i, [_vp, _i, _dp, _vp]),
     "gpf_fv_reduce_local": (_i, [_vp, _i, _dp, _vp]),

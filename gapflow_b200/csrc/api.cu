@@ -274,17 +274,20 @@ int gpf_comm_error(gpf_comm* c, int* err) {
     return GPF_OK;
     GPF_CATCH
 }
-int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, uint64_t seq, void* stream) {
-    GPF_TRY NEED(s && c) return s->S.halo_send(c->C, rel, lo, hi, seq, (cudaStream_t)stream); GPF_CATCH
+int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.halo_send(c->C, rel, lo, hi, (cudaStream_t)stream); GPF_CATCH
 }
-int gpf_fv_halo_recv(gpf_fv* s, gpf_comm* c, int rel, uint64_t seq, void* stream) {
-    GPF_TRY NEED(s && c) return s->S.halo_recv(c->C, rel, seq, (cudaStream_t)stream); GPF_CATCH
+int gpf_fv_halo_recv(gpf_fv* s, gpf_comm* c, int rel, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.halo_recv(c->C, rel, (cudaStream_t)stream); GPF_CATCH
 }
-int gpf_fv_record_send(gpf_fv* s, gpf_comm* c, int kind, uint64_t seq, void* stream) {
-    GPF_TRY NEED(s && c) return s->S.record_send(c->C, kind, seq, (cudaStream_t)stream); GPF_CATCH
+int gpf_fv_record_send(gpf_fv* s, gpf_comm* c, int kind, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.record_send(c->C, kind, (cudaStream_t)stream); GPF_CATCH
 }
-int gpf_fv_finish_recv(gpf_fv* s, gpf_comm* c, int mode, uint64_t seq, double* recs_out, void* stream) {
-    GPF_TRY NEED(s && c) return s->S.finish_recv(c->C, mode, seq, recs_out, (cudaStream_t)stream); GPF_CATCH
+int gpf_fv_finish_recv(gpf_fv* s, gpf_comm* c, int mode, double* recs_out, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.finish_recv(c->C, mode, recs_out, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_fv_slab_step(gpf_fv* s, gpf_comm* c, int lo, int hi, int n, double* recs_out, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.slab_step(c->C, lo, hi, n, recs_out, (cudaStream_t)stream); GPF_CATCH
 }
 int gpf_gp_train_workspace_bytes(int M, size_t* bytes) {
     GPF_TRY NEED(bytes && M > 0) *bytes = gpf::GpModel::train_workspace_bytes(M); return GPF_OK; GPF_CATCH

@@ -69,10 +69,14 @@ struct FvSolver {
     int halo_pack(int rel, double* send, cudaStream_t s);
     int halo_unpack(int rel, const double* recv, cudaStream_t s);
     int reduce_local(int kind, double* rec5, cudaStream_t s);
-    int halo_send(struct SlabComm& c, int rel, int lo, int hi, unsigned long long seq, cudaStream_t s);
-    int halo_recv(struct SlabComm& c, int rel, unsigned long long seq, cudaStream_t s);
-    int record_send(struct SlabComm& c, int kind, unsigned long long seq, cudaStream_t s);
-    int finish_recv(struct SlabComm& c, int mode, unsigned long long seq, double* recs_out, cudaStream_t s);
+    int halo_send(struct SlabComm& c, int rel, int lo, int hi, cudaStream_t s);
+    int halo_recv(struct SlabComm& c, int rel, cudaStream_t s);
+    int record_send(struct SlabComm& c, int kind, cudaStream_t s);
+    int finish_recv(struct SlabComm& c, int mode, double* recs_out, cudaStream_t s, int until_converged = 0);
+    int slab_step_once(struct SlabComm& c, int lo, int hi, double* recs_out, cudaStream_t s);
+    int slab_step(struct SlabComm& c, int lo, int hi, int n, double* recs_out, cudaStream_t s);
+    bool graph_stale = false;
+    int slab_launches = 0;
     int finish(int mode, const double* recs, int nrec, cudaStream_t s);
     int get_timing(double* ms_pred, double* ms_corr, long long* launches);
     double* field_ptr(int field, int* ncomp_max);

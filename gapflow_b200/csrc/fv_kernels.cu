@@ -1,4 +1,5 @@
 // FV kernels + launchers.  Compile with -fmad=false (see closures.cuh).
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -53,12 +54,17 @@ __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ 
                                                         int mode, int until_converged, RefreshOut* ro,
                                                         const Rec5* recs, int nrec, Rec5* rec_out, int xslot,
                                                         const unsigned long long* wait_flags = nullptr,
-                                                        unsigned long long wait_seq = 0, int* werr = nullptr,
-                                                        int rec_stride = 5) {
+                                                        unsigned long long* seqp = nullptr, int* werr = nullptr,
+                                                        int rec_stride = 5, double* recs_copy = nullptr) {
     const int tid = threadIdx.x;
     if (wait_flags) {        // records written into this rank's buffer by its peers (slab_comm.cuh)
-        if (tid < nrec) spin_until(wait_flags + tid, wait_seq, werr);
+        const unsigned long long seq = *seqp + 1;
+        if (tid < nrec) spin_until(wait_flags + tid, seq, werr);
         __syncthreads();
+        if (tid == 0) *seqp = seq;                       // this fold is consumed
+        recs = reinterpret_cast<const Rec5*>(reinterpret_cast<const double*>(recs) + (size_t)(seq & 1ull) * nrec * rec_stride);
+        if (recs_copy && tid < nrec)
+            for (int k = 0; k < 5; ++k) recs_copy[tid * 5 + k] = __ldcg(reinterpret_cast<const double*>(recs) + (size_t)tid * rec_stride + k);
     }
     if (mode == FIN_STEP && (st->stop || (until_converged && st->halt))) return;
     __shared__ double sE[256], sV[256], sC[256], sM[256];
@@ -264,43 +270,64 @@ __global__ void fv_halo_unpack_kernel(const __grid_constant__ FvParams P, const 
 // the neighbours' buffers through NVLink and publishes a sequence number; the receiver waits for
 // that number and fills its ghost rows.  One block each: they must fit beside the persistent CTAs
 // of the interior launch that runs meanwhile.
-__global__ void __launch_bounds__(512) fv_halo_send_kernel(const __grid_constant__ FvParams P, const DevState* st,
+// `done` counts finished blocks; the last one publishes (send) / advances the counter (receive).
+__global__ void __launch_bounds__(256) fv_halo_send_kernel(const __grid_constant__ FvParams P, const DevState* st,
                                                            double* const* qbufs, int rel, double* dst_lo, double* dst_hi,
-                                                           unsigned long long* flag_lo, unsigned long long* flag_hi,
-                                                           unsigned long long seq) {
+                                                           size_t par_stride, unsigned long long* flag_lo,
+                                                           unsigned long long* flag_hi, const unsigned long long* seqp,
+                                                           unsigned int* done) {
+    const unsigned long long seq = *seqp + 1;             // this exchange; the receive kernel advances *seqp
     const double* q = qbufs[(st->cur + rel) % 3];
     const int Ny2 = P.L.Ny + 2;
-    for (int t = threadIdx.x; t < 6 * Ny2; t += blockDim.x) {
+    if (dst_lo) dst_lo += (seq & 1ull) * par_stride;
+    if (dst_hi) dst_hi += (seq & 1ull) * par_stride;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 6 * Ny2; t += gridDim.x * blockDim.x) {
         const int side = t / (3 * Ny2), rem = t % (3 * Ny2), c = rem / Ny2, j = rem % Ny2;
         double* dst = side == 0 ? dst_lo : dst_hi;       // row 1 -> lower neighbour, row Nx -> upper neighbour
         if (!dst) continue;
         const int i = side == 0 ? 1 : P.L.Nx;
         dst[rem] = q[c * P.L.plane + (size_t)i * P.L.pitch + (j + 1)];
     }
-    __threadfence_system();
     __syncthreads();
-    if (threadIdx.x == 0 && flag_lo) st_release_sys(flag_lo, seq);
-    if (threadIdx.x == 1 && flag_hi) st_release_sys(flag_hi, seq);
+    if (threadIdx.x == 0) {
+        __threadfence_system();                           // cumulative: orders the whole block's stores
+        if (atomicAdd(done, 1u) == gridDim.x - 1) {       // every block's stores are fenced
+            *done = 0;
+            __threadfence_system();
+            if (flag_lo) st_release_sys(flag_lo, seq);
+            if (flag_hi) st_release_sys(flag_hi, seq);
+        }
+    }
 }
-__global__ void __launch_bounds__(512) fv_halo_recv_kernel(const __grid_constant__ FvParams P, const DevState* st,
-                                                           double* const* qbufs, int rel, const double* src,
-                                                           const unsigned long long* flags, unsigned long long seq, int* err) {
+__global__ void __launch_bounds__(256) fv_halo_recv_kernel(const __grid_constant__ FvParams P, const DevState* st,
+                                                           double* const* qbufs, int rel, const double* src, size_t par_stride,
+                                                           const unsigned long long* flags, unsigned long long* seqp, int* err,
+                                                           unsigned int* done) {
+    const unsigned long long seq = *seqp + 1;
     if (threadIdx.x < 2 && P.bc.type[threadIdx.x][0] == GPF_BC_HALO) spin_until(flags + threadIdx.x, seq, err);
     __syncthreads();
+    src += (seq & 1ull) * par_stride;
     double* q = qbufs[(st->cur + rel) % 3];
     const int Ny2 = P.L.Ny + 2;
-    for (int t = threadIdx.x; t < 6 * Ny2; t += blockDim.x) {
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < 6 * Ny2; t += gridDim.x * blockDim.x) {
         const int side = t / (3 * Ny2), c = (t / Ny2) % 3, j = t % Ny2;
         if (P.bc.type[side][0] != GPF_BC_HALO) continue;
         const int i = side == 0 ? 0 : P.L.Nx + 1;
         q[c * P.L.plane + (size_t)i * P.L.pitch + (j + 1)] = __ldcg(src + t);     // L2: a peer wrote it
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(done, 1u) == gridDim.x - 1) {              // every block has read *seqp
+        *done = 0;
+        *seqp = seq;
     }
 }
 // this rank's per-block records folded into one Rec5 (as fv_finish_kernel does for rec_out) and
 // stored into every rank's record table, each followed by its sequence number
 __global__ void __launch_bounds__(256) fv_record_send_kernel(const Partial* part, const int* pflags, int nblk, int xslot,
                                                              unsigned char* const* peers, size_t off_recs, size_t off_rflag,
-                                                             int world, int rank, int parity, unsigned long long seq) {
+                                                             int world, int rank, const unsigned long long* seqp) {
+    const unsigned long long seq = *seqp + 1;             // this fold; fv_finish_kernel advances *seqp
+    const int parity = (int)(seq & 1ull);
     __shared__ double sE[256], sV[256], sC[256], sM[256];
     __shared__ int sF[256];
     const int tid = threadIdx.x;
@@ -767,6 +794,7 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
 void FvSolver::drop_graphs() {
     for (auto& g : step_graph)
         if (g) { cudaGraphExecDestroy(g); g = nullptr; }
+    graph_stale = true;          // a slab-step graph held by a communicator is rebuilt on its next use
 }
 
 int FvSolver::destroy() {
@@ -1050,6 +1078,7 @@ SlabCommLayout SlabComm::layout(int world, int rank, int Ny2) {
     l.off_recs = o; o += align_up((size_t)2 * world * 8 * 8, 256);
     l.off_rflag = o; o += align_up((size_t)world * 8, 256);
     l.off_err = o; o += 256;
+    l.off_seq = o; o += 256;
     l.off_ptrs = o; o += align_up((size_t)world * sizeof(void*), 256);
     l.bytes = o;
     return l;
@@ -1083,6 +1112,7 @@ int SlabComm::connect(const unsigned char* handles) {
 }
 
 int SlabComm::destroy() {
+    if (step_graph) { cudaGraphExecDestroy(step_graph); step_graph = nullptr; }
     for (int r = 0; r < (int)peer.size(); ++r)
         if (r != lay.rank && peer[r]) cudaIpcCloseMemHandle(peer[r]);
     peer.clear();
@@ -1097,25 +1127,27 @@ static int comm_ok(const FvSolver& S, const SlabComm& c) {
     return GPF_OK;
 }
 
-int FvSolver::halo_send(SlabComm& c, int rel, int lo, int hi, unsigned long long seq, cudaStream_t s) {
+int FvSolver::halo_send(SlabComm& c, int rel, int lo, int hi, cudaStream_t s) {
     int rc = comm_ok(*this, c);
     if (rc) return rc;
     if (rel < 0 || rel > 2 || lo >= c.lay.world || hi >= c.lay.world) { set_error("bad halo_send arguments"); return GPF_E_INVALID; }
-    const int par = (int)(seq & 1ull);
     // my row 1 is the lower neighbour's upper ghost row (its side 1); my row Nx the upper neighbour's side 0
-    fv_halo_send_kernel<<<1, 512, 0, s>>>(P, st, qtable, rel, lo >= 0 ? c.halo(lo, par, 1) : nullptr,
-                                          hi >= 0 ? c.halo(hi, par, 0) : nullptr, lo >= 0 ? c.hflag(lo, 1) : nullptr,
-                                          hi >= 0 ? c.hflag(hi, 0) : nullptr, seq);
+    const int nblk = std::max(1, std::min(128, (6 * (cfg.Ny + 2) + 255) / 256));
+    fv_halo_send_kernel<<<nblk, 256, 0, s>>>(P, st, qtable, rel, lo >= 0 ? c.halo(lo, 0, 1) : nullptr,
+                                             hi >= 0 ? c.halo(hi, 0, 0) : nullptr, c.halo_par_stride(),
+                                             lo >= 0 ? c.hflag(lo, 1) : nullptr, hi >= 0 ? c.hflag(hi, 0) : nullptr, c.seq(0),
+                                             c.done(0));
     g_launches++;
     return debug_check("fv_halo_send_kernel", s);
 }
 
-int FvSolver::halo_recv(SlabComm& c, int rel, unsigned long long seq, cudaStream_t s) {
+int FvSolver::halo_recv(SlabComm& c, int rel, cudaStream_t s) {
     int rc = comm_ok(*this, c);
     if (rc) return rc;
     if (rel < 0 || rel > 2) { set_error("rel must be 0, 1 or 2"); return GPF_E_INVALID; }
-    const int par = (int)(seq & 1ull);
-    fv_halo_recv_kernel<<<1, 512, 0, s>>>(P, st, qtable, rel, c.halo(c.lay.rank, par, 0), c.hflag(c.lay.rank, 0), seq, c.err());
+    const int nblk = std::max(1, std::min(128, (6 * (cfg.Ny + 2) + 255) / 256));
+    fv_halo_recv_kernel<<<nblk, 256, 0, s>>>(P, st, qtable, rel, c.halo(c.lay.rank, 0, 0), c.halo_par_stride(),
+                                             c.hflag(c.lay.rank, 0), c.seq(0), c.err(), c.done(1));
     g_launches++;
     if (rel == 0) { dirty_scalars = true; refresh_valid = false; }
     rc = debug_check("fv_halo_recv_kernel", s);
@@ -1130,7 +1162,7 @@ int FvSolver::halo_recv(SlabComm& c, int rel, unsigned long long seq, cudaStream
     return rc;
 }
 
-int FvSolver::record_send(SlabComm& c, int kind, unsigned long long seq, cudaStream_t s) {
+int FvSolver::record_send(SlabComm& c, int kind, cudaStream_t s) {
     int rc = comm_ok(*this, c);
     if (rc) return rc;
     int nblk = nrec_corr;
@@ -1141,24 +1173,84 @@ int FvSolver::record_send(SlabComm& c, int kind, unsigned long long seq, cudaStr
         xslot = -1;
     }
     fv_record_send_kernel<<<1, 256, 0, s>>>(partial, pflags, nblk, xslot, c.d_peer, c.lay.off_recs, c.lay.off_rflag,
-                                            c.lay.world, c.lay.rank, (int)(seq & 1ull), seq);
+                                            c.lay.world, c.lay.rank, c.seq(1));
     g_launches++;
     return debug_check("fv_record_send_kernel", s);
 }
 
-int FvSolver::finish_recv(SlabComm& c, int mode, unsigned long long seq, double* recs_out, cudaStream_t s) {
+int FvSolver::finish_recv(SlabComm& c, int mode, double* recs_out, cudaStream_t s, int until_converged) {
     int rc = comm_ok(*this, c);
     if (rc) return rc;
     if (mode < FIN_STEP || mode > FIN_REFRESH) { set_error("bad finish mode"); return GPF_E_INVALID; }
-    const double* recs = c.recs(c.lay.rank, (int)(seq & 1ull));
-    fv_finish_kernel<<<1, 256, 0, s>>>(P, st, partial, pflags, 0, mode, 0, refresh, reinterpret_cast<const Rec5*>(recs),
-                                       c.lay.world, nullptr, -1, c.rflag(c.lay.rank), seq, c.err(), 8);
+    fv_finish_kernel<<<1, 256, 0, s>>>(P, st, partial, pflags, 0, mode, until_converged, refresh,
+                                       reinterpret_cast<const Rec5*>(c.recs(c.lay.rank, 0)), c.lay.world, nullptr, -1,
+                                       c.rflag(c.lay.rank), c.seq(1), c.err(), 8, recs_out);
     g_launches++;
     if ((rc = debug_check("fv_finish_kernel", s))) return rc;
-    if (recs_out)
-        GPF_CUDA(cudaMemcpy2DAsync(recs_out, 5 * 8, recs, 8 * 8, 5 * 8, c.lay.world, cudaMemcpyDeviceToDevice, s));
     if (mode != FIN_REFRESH) dirty_scalars = false;
     else refresh_valid = true;
+    return GPF_OK;
+}
+
+// n x Problem.update() of this rank's slab: pass, edge rows to the neighbours, ghost rows from them
+// (twice), records to every rank, fold.  All sequence numbers live on the device, so one step is
+// captured once as a CUDA graph (11 kernels) and replayed.
+int FvSolver::slab_step_once(SlabComm& c, int lo, int hi, double* recs_out, cudaStream_t s) {
+    int rc;
+    if ((rc = launch_pass<false>(*this, 0, s))) return rc;
+    if ((rc = halo_send(c, 1, lo, hi, s))) return rc;
+    if ((rc = halo_recv(c, 1, s))) return rc;
+    if ((rc = launch_pass<true>(*this, 0, s))) return rc;
+    if ((rc = halo_send(c, 2, lo, hi, s))) return rc;
+    if ((rc = halo_recv(c, 2, s))) return rc;
+    if ((rc = record_send(c, 0, s))) return rc;
+    return finish_recv(c, FIN_STEP, recs_out, s, 0);
+}
+
+int FvSolver::slab_step(SlabComm& c, int lo, int hi, int n, double* recs_out, cudaStream_t s) {
+    if (n < 0) { set_error("n < 0"); return GPF_E_INVALID; }
+    int rc = comm_ok(*this, c);
+    if (rc) return rc;
+    static const bool graphs = getenv("GPF_NO_GRAPH") == nullptr && getenv("GPF_DEBUG_SYNC") == nullptr;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    GPF_CUDA(cudaStreamIsCapturing(s, &cap));
+    if (!graphs || cap != cudaStreamCaptureStatusNone) {
+        for (int it = 0; it < n; ++it)
+            if ((rc = slab_step_once(c, lo, hi, recs_out, s))) return rc;
+        return GPF_OK;
+    }
+    if (c.step_graph && (c.graph_lo != lo || c.graph_hi != hi || c.graph_owner != this || c.graph_recs != recs_out || graph_stale)) {
+        cudaGraphExecDestroy(c.step_graph);
+        c.step_graph = nullptr;
+    }
+    if (!c.step_graph && n > 0) {
+        if ((rc = slab_step_once(c, lo, hi, recs_out, s))) return rc;     // also sets the kernels' attributes outside a capture
+        --n;
+        const long long l0 = g_launches;
+        cudaStream_t cs;
+        cudaGraph_t g = nullptr;
+        GPF_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+        cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+        if (e != cudaSuccess) { cudaStreamDestroy(cs); set_error(std::string("cudaStreamBeginCapture: ") + cudaGetErrorString(e)); return GPF_E_CUDA; }
+        rc = slab_step_once(c, lo, hi, recs_out, cs);
+        e = cudaStreamEndCapture(cs, &g);
+        cudaStreamDestroy(cs);
+        slab_launches = (int)(g_launches - l0);
+        g_launches = l0;
+        if (rc || e != cudaSuccess) {
+            if (g) cudaGraphDestroy(g);
+            if (!rc) { set_error(std::string("CUDA graph capture of the slab step failed: ") + cudaGetErrorString(e)); rc = GPF_E_CUDA; }
+            return rc;
+        }
+        e = cudaGraphInstantiate(&c.step_graph, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) { c.step_graph = nullptr; set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); return GPF_E_CUDA; }
+        c.graph_lo = lo; c.graph_hi = hi; c.graph_owner = this; c.graph_recs = recs_out;
+        graph_stale = false;
+    }
+    for (int it = 0; it < n; ++it) GPF_CUDA(cudaGraphLaunch(c.step_graph, s));
+    g_launches += (long long)slab_launches * n;
+    dirty_scalars = false;
     return GPF_OK;
 }
 

@@ -7,6 +7,8 @@
 //   recs [2 parities][world][8]            one folded record (Rec5, padded) per rank
 //   rflag[world]                           sequence number of the last record written by rank w
 //   err                                    set when a wait timed out (a peer died): results are garbage
+//   seq  [2]                               exchanges / folds this rank has completed (device-resident, so that
+//                                          a captured step can be replayed: no sequence number is a kernel argument)
 // A sender stores the data into the receiver's buffer, fences at system scope and then publishes the
 // sequence number; the receiver's kernel spins on its own flag (bounded by SPIN_NS) and copies the
 // rows into its ghost cells.  Slots alternate with the sequence parity: a slot is rewritten two
@@ -20,7 +22,7 @@ namespace gpf {
 
 struct SlabCommLayout {
     int world, rank, Ny2;
-    size_t off_halo, off_hflag, off_recs, off_rflag, off_err, off_ptrs, bytes;
+    size_t off_halo, off_hflag, off_recs, off_rflag, off_err, off_seq, off_ptrs, bytes;
 };
 
 struct SlabComm {
@@ -34,6 +36,10 @@ struct SlabComm {
     int create(int world, int rank, int Ny);
     int connect(const unsigned char* handles);     // [world][sizeof(cudaIpcMemHandle_t)]
     int destroy();
+    cudaGraphExec_t step_graph = nullptr;  // one captured slab step (FvSolver::slab_step)
+    int graph_lo = -2, graph_hi = -2;
+    const void* graph_owner = nullptr;
+    double* graph_recs = nullptr;
     double* halo(int r, int parity, int side) const {
         return reinterpret_cast<double*>(peer[r] + lay.off_halo) + ((size_t)parity * 2 + side) * 3 * lay.Ny2;
     }
@@ -41,6 +47,9 @@ struct SlabComm {
     double* recs(int r, int parity) const { return reinterpret_cast<double*>(peer[r] + lay.off_recs) + (size_t)parity * lay.world * 8; }
     unsigned long long* rflag(int r) const { return reinterpret_cast<unsigned long long*>(peer[r] + lay.off_rflag); }
     int* err() const { return reinterpret_cast<int*>(local + lay.off_err); }
+    unsigned long long* seq(int which) const { return reinterpret_cast<unsigned long long*>(local + lay.off_seq) + which; }
+    unsigned int* done(int which) const { return reinterpret_cast<unsigned int*>(local + lay.off_seq + 64) + which; }   // block counters
+    size_t halo_par_stride() const { return (size_t)2 * 3 * lay.Ny2; }       // doubles between the two parities
 };
 
 }  // namespace gpf

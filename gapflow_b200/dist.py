@@ -119,7 +119,7 @@ class SlabSolver:
         # peer=True: halo rows and records go through peer-mapped memory (CUDA IPC over NVLink) written
         # and awaited by the library's own kernels; None: whenever ranks are separate processes on CUDA
         # devices of one node (GPF_SLAB_PEER=0 keeps the grouped NCCL send/recv + all-gather)
-        self._comm, self._hseq, self._rseq = None, 0, 0
+        self._comm = None
         if peer is None:
             peer = (exchanger is None and self.world > 1 and dist.is_initialized() and dist.get_backend(group) == 'nccl'
                     and os.environ.get('GPF_SLAB_PEER', '1') != '0')
@@ -198,22 +198,21 @@ class SlabSolver:
         if self.world == 1:
             return
         if self._comm is not None:
-            self._hseq += 1
-            lo = -1 if self.ex.lo is None else self.ex.lo
-            hi = -1 if self.ex.hi is None else self.ex.hi
-            _capi.check(self.lib.gpf_fv_halo_send(self.h, self._comm, rel, lo, hi, self._hseq, self._s()))
-            _capi.check(self.lib.gpf_fv_halo_recv(self.h, self._comm, rel, self._hseq, self._s()))
+            lo, hi = self._neighbours()
+            _capi.check(self.lib.gpf_fv_halo_send(self.h, self._comm, rel, lo, hi, self._s()))
+            _capi.check(self.lib.gpf_fv_halo_recv(self.h, self._comm, rel, self._s()))
             return
         self._pack(rel)
         self.ex.exchange(self.send, self.recv)
         self._unpack(rel)
 
+    def _neighbours(self):
+        return (-1 if self.ex.lo is None else self.ex.lo), (-1 if self.ex.hi is None else self.ex.hi)
+
     def _fold(self, kind, mode):
         if self._comm is not None:
-            self._rseq += 1
-            _capi.check(self.lib.gpf_fv_record_send(self.h, self._comm, kind, self._rseq, self._s()))
-            _capi.check(self.lib.gpf_fv_finish_recv(self.h, self._comm, mode, self._rseq,
-                                                    C.c_void_p(self.recs.data_ptr()), self._s()))
+            _capi.check(self.lib.gpf_fv_record_send(self.h, self._comm, kind, self._s()))
+            _capi.check(self.lib.gpf_fv_finish_recv(self.h, self._comm, mode, C.c_void_p(self.recs.data_ptr()), self._s()))
             return
         self._record(kind)
         self.ex.gather(self.rec, self.recs)
@@ -232,6 +231,12 @@ class SlabSolver:
 
     def step(self, n=1):
         """n x Problem.update() (problem.py:509-569); enqueues only."""
+        if self._comm is not None and not self._timing:
+            # peer memory: the whole step is the library's own kernels, replayed as one CUDA graph
+            lo, hi = self._neighbours()
+            _capi.check(self.lib.gpf_fv_slab_step(self.h, self._comm, lo, hi, int(n), C.c_void_p(self.recs.data_ptr()),
+                                                  self._s()))
+            return
         main = torch.cuda.current_stream(self.fv.device)
         for _ in range(n):
             for c, rel in ((0, 1), (1, 2)):

@@ -218,21 +218,24 @@ int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
  * error flag after 5 s instead of hanging the GPU) and fills the ghost rows (folds the records and
  * advances the loop state).  No reference counterpart (problem.py:676-707 is a local copy).
  *   create on every rank -> all-gather the GPF_IPC_HANDLE_BYTES handles by any means -> connect ->
- *   barrier; then per exchange k = 1, 2, ... (the same k on every rank):
- *     halo_send(rel, lo, hi, k); halo_recv(rel, k)        lo / hi: neighbour ranks, -1 = none
- *   and per fold m = 1, 2, ...:
- *     record_send(kind, m); finish_recv(mode, m, recs_out)   kind, mode as reduce_local / finish;
- *     recs_out: device array [world][5] or NULL. */
+ *   barrier; then, in the same order on every rank,
+ *     halo_send(rel, lo, hi); halo_recv(rel)              lo / hi: neighbour ranks, -1 = none
+ *     record_send(kind); finish_recv(mode, recs_out)      kind, mode as reduce_local / finish;
+ *                                                         recs_out: device array [world][5] or NULL
+ * Exchange and fold counters live on the device, so no call carries a sequence number and
+ * gpf_fv_slab_step replays one captured step (passes, both exchanges, fold: 11 kernels) as a CUDA graph. */
 #define GPF_IPC_HANDLE_BYTES 64
 typedef struct gpf_comm gpf_comm;
 int gpf_comm_create(int world, int rank, int Ny, unsigned char* handle_out, gpf_comm** out);
 int gpf_comm_connect(gpf_comm* c, const unsigned char* handles /* [world][GPF_IPC_HANDLE_BYTES] */);
 int gpf_comm_destroy(gpf_comm* c);
 int gpf_comm_error(gpf_comm* c, int* err);       /* synchronises; 1 = a wait timed out */
-int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, uint64_t seq, void* stream);
-int gpf_fv_halo_recv(gpf_fv* s, gpf_comm* c, int rel, uint64_t seq, void* stream);
-int gpf_fv_record_send(gpf_fv* s, gpf_comm* c, int kind, uint64_t seq, void* stream);
-int gpf_fv_finish_recv(gpf_fv* s, gpf_comm* c, int mode, uint64_t seq, double* recs_out, void* stream);
+int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, void* stream);
+int gpf_fv_halo_recv(gpf_fv* s, gpf_comm* c, int rel, void* stream);
+int gpf_fv_record_send(gpf_fv* s, gpf_comm* c, int kind, void* stream);
+int gpf_fv_finish_recv(gpf_fv* s, gpf_comm* c, int mode, double* recs_out, void* stream);
+/* n x Problem.update() of this rank's slab (problem.py:509-569) */
+int gpf_fv_slab_step(gpf_fv* s, gpf_comm* c, int lo, int hi, int n, double* recs_out, void* stream);
 
 /* --- GP surrogate inference (GaPFlow/models/gp.py) -------------------------------------
  * One handle per GP model (pressure: n_out = 1; wall shear: n_out = 2 outputs sharing one

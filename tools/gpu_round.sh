@@ -13,9 +13,9 @@ grep -q "pytest exit 0" $out/pytest.log || { tail -40 $out/pytest.log; exit 1; }
 timeout 300 python bench.py --steps 200 --warmup 10 > $out/bench.json 2> $out/bench.err; echo "bench exit $?"
 cat $out/bench.json
 timeout 120 python bench.py --steps 3 --warmup 3 --no-cpu > $out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $out/launches.csv \
+GPF_NO_GRAPH=1 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $out/launches.csv \
     python bench.py --steps 3 --warmup 3 --no-cpu > $out/ncu_list.log 2>&1
 timeout 120 python bench.py --steps 3 --warmup 3 --no-cpu > $out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:fv_pass -s 8 -c 4 -o $out/prof \
+GPF_NO_GRAPH=1 ncu --set full --clock-control none --import-source on -k regex:fv_pass -s 8 -c 4 -o $out/prof \
     python bench.py --steps 3 --warmup 3 --no-cpu > $out/ncu_full.log 2>&1
 ls -la $out
