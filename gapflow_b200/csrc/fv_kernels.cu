@@ -1194,7 +1194,7 @@ int FvSolver::finish_recv(SlabComm& c, int mode, double* recs_out, cudaStream_t 
 
 // n x Problem.update() of this rank's slab: pass, edge rows to the neighbours, ghost rows from them
 // (twice), records to every rank, fold.  All sequence numbers live on the device, so one step is
-// captured once as a CUDA graph (11 kernels) and replayed.
+// captured once as a CUDA graph (10 kernels) and replayed.
 int FvSolver::slab_step_once(SlabComm& c, int lo, int hi, double* recs_out, cudaStream_t s) {
     int rc;
     if ((rc = launch_pass<false>(*this, 0, s))) return rc;

@@ -223,7 +223,7 @@ int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
  *     record_send(kind); finish_recv(mode, recs_out)      kind, mode as reduce_local / finish;
  *                                                         recs_out: device array [world][5] or NULL
  * Exchange and fold counters live on the device, so no call carries a sequence number and
- * gpf_fv_slab_step replays one captured step (passes, both exchanges, fold: 11 kernels) as a CUDA graph. */
+ * gpf_fv_slab_step replays one captured step (passes, both exchanges, fold: 10 kernels) as a CUDA graph. */
 #define GPF_IPC_HANDLE_BYTES 64
 typedef struct gpf_comm gpf_comm;
 int gpf_comm_create(int world, int rank, int Ny, unsigned char* handle_out, gpf_comm** out);
