@@ -174,6 +174,12 @@ def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), ha
             c.halo_edge[s] = 1 if halo_edge[s] else 0
     c.U, c.V = geo['U'], geo['V']
     c.eta, c.zeta = prop['shear'], prop['bulk']
+    # stress.py:306-326, 430-450: a 'piezo' / 'thinning' block makes the viscosity a field.  Not built yet
+    # (oracle/closures.py::piezoviscosity restates the laws): refuse, never run Newtonian
+    for sec in ('piezo', 'thinning'):
+        if sec in prop and prop[sec].get('name', 'none') not in ('none', ''):
+            raise NotImplementedError(f"properties.{sec} ({prop[sec]['name']}): viscosity modifiers are not implemented "
+                                      "in the CUDA path; the step would silently differ from the reference")
     if prop['EOS'] not in EOS_IDS:
         raise GapflowError(GPF_E_INVALID, f"EOS {prop['EOS']!r} has no fixed-form branch")
     c.eos = EOS_IDS[prop['EOS']]

@@ -262,3 +262,31 @@ def stress_avg(q, h, U, V, eta, zeta, Ls):
           (+1, (h0, hx, q0, q2)), (+1, (h0, hy, q0, q1))]
     tau[2] = eta * _sum_terms(xy) / den
     return tau
+
+
+# ---------------------------------------------------------------------------------
+# Viscosity modifiers (row F11; not on the CUDA path yet, restated for the next round's parity tests)
+# ---------------------------------------------------------------------------------
+def piezoviscosity(p, mu0, piezo):
+    """GaPFlow/models/viscosity.py:34-66 -> 144-259.  ``p`` is the pressure field, or the density for
+    the Bayada-Chupin mixture laws (stress.py:306-309)."""
+    name = piezo.get('name', 'none')
+    if name == 'Barus':                  # viscosity.py:165
+        return mu0 * np.exp(piezo['aB'] * p)
+    if name == 'Roelands':               # viscosity.py:197
+        return mu0 * np.exp(np.log(mu0 / piezo['mu_inf']) * (-1 + (1 + p / piezo['p_ref'])**piezo['z']))
+    if name in ('Dukler', 'McAdams'):
+        alpha = (p - piezo['rho_l']) / (piezo['rho_v'] - piezo['rho_l'])
+        if name == 'Dukler':             # viscosity.py:227-228
+            return alpha * piezo['eta_v'] + (1 - alpha) * mu0
+        M = alpha * piezo['rho_v'] / p   # viscosity.py:257-259
+        return piezo['eta_v'] * mu0 / (mu0 * M + piezo['eta_v'] * (1 - M))
+    return np.ones_like(p) * mu0         # viscosity.py:64
+
+
+def shear_rate_avg(dp_dx, dp_dy, h, u1, u2, mu):
+    """viscosity.py:99-141 (Newtonian profile, mean of the absolute wall shear rates)."""
+    grad_p = np.hypot(dp_dx, dp_dy)
+    du_pois = h * grad_p / (2 * mu)
+    du_carr = (u2 - u1) / h
+    return (np.abs(du_pois + du_carr) + np.abs(-du_pois + du_carr)) / 2.

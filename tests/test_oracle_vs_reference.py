@@ -51,3 +51,20 @@ def test_ten_steps(R, name):
         b.update()
     assert np.array_equal(a.q, b.q)
     assert a.dt == b.dt and a.residual == b.residual
+
+
+def test_piezoviscosity_laws_match_reference():
+    """oracle/closures.py::piezoviscosity vs GaPFlow/models/viscosity.py:34-66 (all four laws + none)."""
+    from oracle import closures as C
+    R = ref_loader.modules()['viscosity']
+    rng = np.random.default_rng(11)
+    p = rng.uniform(1e5, 5e8, (13, 7))
+    rho = rng.uniform(1.0, 849.0, (13, 7))
+    cases = [(p, dict(name='Barus', aB=2e-8)), (p, dict(name='Roelands', mu_inf=1e-3, p_ref=1.96e8, z=0.68)),
+             (rho, dict(name='Dukler', eta_v=3.9e-5, rho_l=850., rho_v=0.019)),
+             (rho, dict(name='McAdams', eta_v=3.9e-5, rho_l=850., rho_v=0.019)), (p, dict(name='none'))]
+    for x, pz in cases:
+        assert np.array_equal(C.piezoviscosity(x, 0.039, pz), R.piezoviscosity(x, 0.039, dict(pz))), pz['name']
+    g = rng.uniform(-1e9, 1e9, (13, 7))
+    h = rng.uniform(1e-6, 1e-4, (13, 7))
+    assert np.array_equal(C.shear_rate_avg(g, 0.5 * g, h, 0.1, 0., 0.039), R.shear_rate_avg(g, 0.5 * g, h, 0.1, 0., 0.039))
