@@ -30,6 +30,11 @@ BC_P, BC_D, BC_N, BC_HALO = 0, 1, 2, 3
 F_Q, F_TOPO, F_EXTRA = 0, 1, 2
 PART_ALL, PART_EDGE, PART_INTERIOR = 0, 1, 2
 IPC_HANDLE_BYTES = 64
+PIEZO_IDS = {'Barus': 2, 'Roelands': 3, 'Dukler': 4, 'McAdams': 5}       # GPF_PIEZO_*; any other name: 1 (identity)
+PIEZO_KEYS = {'Barus': ['aB'], 'Roelands': ['mu_inf', 'p_ref', 'z'], 'Dukler': ['eta_v', 'rho_l', 'rho_v'],
+              'McAdams': ['eta_v', 'rho_l', 'rho_v']}
+THIN_IDS = {'Eyring': 2, 'Carreau': 3}                                    # GPF_THIN_*
+THIN_KEYS = {'Eyring': ['tauE'], 'Carreau': ['mu_inf', 'lam', 'a', 'N']}
 FIN_STEP, FIN_PRERUN, FIN_PRERUN_KEEP_EKIN, FIN_REFRESH = 0, 1, 2, 3
 
 
@@ -40,7 +45,8 @@ class FvCfg(C.Structure):
                 ("eos", C.c_int32), ("eos_par", C.c_double * 8), ("rho0", C.c_double),
                 ("adaptive", C.c_int32), ("CFL", C.c_double), ("dt", C.c_double), ("tol", C.c_double),
                 ("max_it", C.c_int32), ("mc_order", C.c_int32), ("has_extra", C.c_int32),
-                ("halo_edge", C.c_int32 * 2), ("arith", C.c_int32), ("reserved", C.c_int32 * 4)]
+                ("halo_edge", C.c_int32 * 2), ("arith", C.c_int32), ("visc_field", C.c_int32),
+                ("reserved", C.c_int32 * 3)]
 
 
 class FvScalars(C.Structure):
@@ -73,6 +79,8 @@ SIGNATURES = {
     "gpf_fv_mass": (_i, [_vp, C.POINTER(C.c_double), _vp]),
     "gpf_fv_closures": (_i, [_vp, _dp, _dp, _dp, _dp, _i, _vp]),
     "gpf_fv_closures_of": (_i, [_vp, _i, _dp, _dp, _dp, _dp, _i, _vp]),
+    "gpf_fv_set_viscosity": (_i, [_vp, _i, C.POINTER(C.c_double), _i, C.POINTER(C.c_double), _dp, _dp]),
+    "gpf_fv_viscosity": (_i, [_vp, _i, _dp, _i, _vp]),
     "gpf_fv_update_host": (_i, [_vp, _dp, _i, C.POINTER(FvScalars), _vp]),
     "gpf_fv_pass": (_i, [_vp, _i, _vp]),
     "gpf_fv_pass_part": (_i, [_vp, _i, _i, _vp]),
@@ -174,12 +182,12 @@ def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), ha
             c.halo_edge[s] = 1 if halo_edge[s] else 0
     c.U, c.V = geo['U'], geo['V']
     c.eta, c.zeta = prop['shear'], prop['bulk']
-    # stress.py:306-326, 430-450: a 'piezo' / 'thinning' block makes the viscosity a field.  Not built yet
-    # (oracle/closures.py::piezoviscosity restates the laws): refuse, never run Newtonian
-    for sec in ('piezo', 'thinning'):
-        if sec in prop and prop[sec].get('name', 'none') not in ('none', ''):
-            raise NotImplementedError(f"properties.{sec} ({prop[sec]['name']}): viscosity modifiers are not implemented "
-                                      "in the CUDA path; the step would silently differ from the reference")
+    # stress.py:306-326, 430-450: a 'piezo' / 'thinning' block makes the viscosity a field (even with a law
+    # name the reference does not know: identity law, same field path); gpf_fv_set_viscosity() must follow
+    c.visc_field = 1 if ('piezo' in prop or 'thinning' in prop) else 0
+    if c.visc_field and any(halo):
+        raise NotImplementedError("properties.piezo / properties.thinning on a slab-decomposed grid: the pressure "
+                                  "gradient at a halo row needs a second halo row (not built); run on one GPU")
     if prop['EOS'] not in EOS_IDS:
         raise GapflowError(GPF_E_INVALID, f"EOS {prop['EOS']!r} has no fixed-form branch")
     c.eos = EOS_IDS[prop['EOS']]
@@ -193,3 +201,17 @@ def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), ha
     c.has_extra = 1 if has_extra else 0
     c.arith = ARITH[arith]
     return c
+
+
+def viscosity_args(prop):
+    """(piezo id, piezo parameters, thinning id, thinning parameters) of gpf_fv_set_viscosity from the
+    sanitised properties dict (GaPFlow/io.py:318-362); parameter order as include/gapflow_b200.h states."""
+    def one(sec, ids, keys):
+        if sec not in prop:
+            return 0, None
+        name = prop[sec].get('name', 'none')
+        if name not in ids:
+            return 1, None                  # unknown name: the reference applies the identity law
+        vals = [float(prop[sec][k]) for k in keys[name]]
+        return ids[name], (C.c_double * len(vals))(*vals)
+    return one('piezo', PIEZO_IDS, PIEZO_KEYS) + one('thinning', THIN_IDS, THIN_KEYS)

@@ -155,6 +155,16 @@ int gpf_fv_closures_of(gpf_fv* s, int which, double* pressure, double* wall_xz, 
     return s->S.closures(pressure, wall_xz, wall_yz, bulk, on_device, (cudaStream_t)stream, which ? 2 : 0);
     GPF_CATCH
 }
+int gpf_fv_set_viscosity(gpf_fv* s, int piezo, const double* piezo_par, int thinning, const double* thin_par,
+                         const double* x, const double* y) {
+    GPF_TRY NEED(s) return s->S.set_viscosity(piezo, piezo_par, thinning, thin_par, x, y); GPF_CATCH
+}
+int gpf_fv_viscosity(gpf_fv* s, int which, double* eta, int on_device, void* stream) {
+    GPF_TRY NEED(s && eta)
+    if (which != 0 && which != 1) { set_error("which must be 0 (current q) or 1 (corrector-pass input)"); return GPF_E_INVALID; }
+    return s->S.viscosity(which, eta, on_device, (cudaStream_t)stream);
+    GPF_CATCH
+}
 int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, void* stream) {
     GPF_TRY
     NEED(s && q_host)

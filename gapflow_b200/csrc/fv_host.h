@@ -33,6 +33,14 @@ struct FvSolver {
     double* qbuf[3];
     double* topo;      // 3 planes
     double* extra;     // 1 plane
+    double* eta = nullptr;       // 1 plane: per-cell shear viscosity (cfg.visc_field), rewritten before every pass
+    double* gradtab = nullptr;   // np.gradient coefficient tables: 3 (Nx+2) + 3 (Ny+2) doubles
+    ViscModel VM;
+    bool visc_set = false;
+    CUtensorMap eta_map;
+    int set_viscosity(int piezo, const double* pp, int thin, const double* tp, const double* x, const double* y);
+    int launch_viscosity(int rel, cudaStream_t s);
+    int viscosity(int which, double* out, int on_device, cudaStream_t s);
     DevState* st;
     Partial* partial;
     int* pflags;
@@ -90,6 +98,7 @@ struct PassArgs {
     CUtensorMap topo_map;      // box (BY, BX, 3)
     CUtensorMap topo2_map;     // box (BY, BX, 2): h, dh/dx
     CUtensorMap ls_map;        // box (BY, BX, 1)
+    CUtensorMap eta_map;       // box (BY, BX, 1): per-cell shear viscosity (viscosity-field variants only)
     FvParams P;
     double* qbuf[3];
     DevState* st;

@@ -406,13 +406,88 @@ __global__ void __launch_bounds__(256) fv_edge_rows_kernel(const __grid_constant
     }
 }
 
+// ---- viscosity modifiers (row F11) -----------------------------------------------------
+// piezoviscosity (viscosity.py:34-66, 144-259); `arg` = pressure, or density for the mixture laws
+__device__ __forceinline__ double piezo_law(const ViscModel& M, double mu0, double arg) {
+    switch (M.piezo) {
+    case GPF_PIEZO_BARUS:        // :165  mu0 * exp(aB * p)
+        return mu0 * exp(M.pp[0] * arg);
+    case GPF_PIEZO_ROELANDS:     // :197  mu0 * exp(log(mu0 / mu_inf) * (-1 + (1 + p / p_ref)**z)); pp[3] = the log
+        return mu0 * exp(M.pp[3] * (-1 + pow(1 + arg / M.pp[1], M.pp[2])));
+    case GPF_PIEZO_DUKLER: {     // :227-228  pp = {eta_v, rho_l, rho_v}
+        const double alpha = (arg - M.pp[1]) / (M.pp[2] - M.pp[1]);
+        return alpha * M.pp[0] + (1 - alpha) * mu0;
+    }
+    case GPF_PIEZO_MCADAMS: {    // :257-259
+        const double alpha = (arg - M.pp[1]) / (M.pp[2] - M.pp[1]);
+        const double Mf = alpha * M.pp[2] / arg;
+        return M.pp[0] * mu0 / (mu0 * Mf + M.pp[0] * (1 - Mf));
+    }
+    default:                     // :64  np.ones_like(p) * mu
+        return 1.0 * mu0;
+    }
+}
+
+// np.gradient along one axis at index i (f[i-1], f[i], f[i+1]; edge_order = 1)
+__device__ __forceinline__ double grad_axis(const GradAxis& G, int i, double fm, double f0, double fp) {
+    if (i == 0) return (fp - f0) / G.d_first;
+    if (i == G.n - 1) return (f0 - fm) / G.d_last;
+    if (G.uniform) return (fp - fm) / G.two_d;
+    return G.abc[i] * fm + G.abc[G.n + i] * f0 + G.abc[2 * G.n + i] * fp;
+}
+
+// Shear viscosity of every cell of the padded array, as WallStress.update and BulkStress.update build it
+// at the head of each pass (stress.py:305-326 == 429-450) from the pressure field of the pass's input q:
+// piezo law, then mu0 * thinning factor at the average shear rate (viscosity.py:99-141; the reference
+// passes geo['U'], geo['V'] as the two wall speeds u1, u2).  The pressure of the cell and of its four
+// neighbours is recomputed from the density (never stored); one plane is written.
+__global__ void __launch_bounds__(256) fv_viscosity_kernel(const __grid_constant__ FvParams P,
+                                                           const __grid_constant__ ViscModel M, const DevState* st,
+                                                           double* const* qbufs, const double* topo, double* eta,
+                                                           int rel) {
+    const double* q0 = qbufs[(st->cur + rel) % 3];
+    const int Nx2 = P.L.Nx + 2, Ny2 = P.L.Ny + 2;
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)Nx2 * Ny2) return;
+    const int i = (int)(idx / Ny2), j = (int)(idx % Ny2);
+    const size_t a = (size_t)i * P.L.pitch + (j + 1);
+    const double rho = q0[a];
+    const double p = eos_pressure<-1>(rho, P.eos);
+    const double shear = P.visc.eta;
+    double mu0 = shear;
+    if (M.piezo != GPF_PIEZO_ABSENT) mu0 = piezo_law(M, shear, M.use_dens ? rho : p);
+    double out = mu0;
+    if (M.thin != GPF_THIN_ABSENT) {
+        const double pxm = (i > 0) ? eos_pressure<-1>(q0[a - P.L.pitch], P.eos) : 0.0;
+        const double pxp = (i < Nx2 - 1) ? eos_pressure<-1>(q0[a + P.L.pitch], P.eos) : 0.0;
+        const double pym = (j > 0) ? eos_pressure<-1>(q0[a - 1], P.eos) : 0.0;
+        const double pyp = (j < Ny2 - 1) ? eos_pressure<-1>(q0[a + 1], P.eos) : 0.0;
+        const double gp = hypot(grad_axis(M.gx, i, pxm, p, pxp), grad_axis(M.gy, j, pym, p, pyp));
+        const double h = topo[a];
+        const double du_pois = h * gp / (2 * mu0);           // viscosity.py:106
+        const double du_carr = (P.visc.V - P.visc.U) / h;    // :107 with (u1, u2) = (U, V)  (stress.py:317-318)
+        const double rate = (fabs(du_pois + du_carr) + fabs(-du_pois + du_carr)) / 2.;
+        double fac = 1.0;                                    // viscosity.py:94
+        if (M.thin == GPF_THIN_EYRING) {                     // :284-285  tp = {tauE}
+            const double tau0 = mu0 * rate;
+            fac = M.tp[0] / tau0 * asinh(tau0 / M.tp[0]);
+        } else if (M.thin == GPF_THIN_CARREAU) {             // :316-318  tp = {mu_inf, lam, a, N, (N - 1) / a}
+            const double mu = M.tp[0] + (mu0 - M.tp[0]) * pow(1 + pow(M.tp[1] * rate, M.tp[2]), M.tp[4]);
+            fac = mu / mu0;
+        }
+        out = mu0 * fac;
+    }
+    eta[a] = out;
+}
+
 // Closure fields as the reference stores them for sol.nc (stress.py:346-362, 452-459,
 // 619-622): dense (ncomp, Nx+2, Ny+2) outputs; NULL outputs are skipped.
 template <bool LS, int EOS>
 __global__ void __launch_bounds__(256) fv_closures_kernel(const __grid_constant__ FvParams P, const DevState* st,
                                                           double* const* qbufs, const double* topo,
                                                           const double* extra, double* pr, double* wxz,
-                                                          double* wyz, double* bulk, int rel) {
+                                                          double* wyz, double* bulk, int rel,
+                                                          const double* eta) {
     const double* q = qbufs[(st->cur + rel) % 3];
     const int Nx2 = P.L.Nx + 2, Ny2 = P.L.Ny + 2;
     const size_t np = (size_t)Nx2 * Ny2, plane = P.L.plane;
@@ -424,7 +499,14 @@ __global__ void __launch_bounds__(256) fv_closures_kernel(const __grid_constant_
     c.q0 = q[a]; c.q1 = q[plane + a]; c.q2 = q[2 * plane + a];
     c.h = topo[a]; c.hx = topo[plane + a]; c.hy = topo[2 * plane + a];
     c.Ls = LS ? extra[a] : 0.0;
-    const Visc& V = reinterpret_cast<const Visc&>(P.visc);
+    Visc V = reinterpret_cast<const Visc&>(P.visc);
+    if (eta) {               // viscosity field (stress.py:305-326); v1, v2 per cell as viscous.py:82-83
+        V.eta = eta[a];
+        V.v1 = V.zeta + 4. / 3. * V.eta;
+        V.v2 = V.zeta - 2. / 3. * V.eta;
+        V.two_eta = 2 * V.eta;
+        V.two_v2 = 2 * V.v2;
+    }
     if (pr) pr[idx] = eos_pressure<EOS>(c.q0, P.eos);
     if (bulk) {
         double t0, t1, t2;
@@ -659,6 +741,7 @@ int pack_params(const gpf_fv_cfg& c, FvParams* P) {
     P->CFL = c.CFL; P->tol = c.tol; P->dt0 = c.dt;
     P->adaptive = c.adaptive; P->max_it = c.max_it; P->mc_order = c.mc_order;
     P->has_extra = c.has_extra;
+    P->visc_field = c.visc_field ? 1 : 0;
     P->xflow = 0;                 // decided when the topography is uploaded
     P->static_fast = 0;           // decided when topography / slip length are uploaded
     P->nblk_y = (c.Nx + TX - 1) / TX;
@@ -729,6 +812,8 @@ size_t FvSolver::workspace_bytes(const gpf_fv_cfg& c) {
     b += 3 * 3 * plane_b;      // q x3 buffers
     b += 3 * plane_b;          // topo
     b += plane_b;              // extra
+    if (c.visc_field)          // viscosity plane + np.gradient tables
+        b += plane_b + align_up((size_t)3 * (c.Nx + 2) * 8, 256) + align_up((size_t)3 * (c.Ny + 2) * 8, 256);
     b += align_up(sizeof(DevState), 256) + align_up(sizeof(RefreshOut), 256);
     b += align_up((size_t)nb * sizeof(Partial), 256) + align_up((size_t)nb * sizeof(int), 256);
     b += 256 + 256;            // qbuf pointer table + slack for base alignment
@@ -751,6 +836,12 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     for (int k = 0; k < 3; ++k) { qbuf[k] = reinterpret_cast<double*>(p); p += 3 * plane_b; }
     topo = reinterpret_cast<double*>(p); p += 3 * plane_b;
     extra = reinterpret_cast<double*>(p); p += plane_b;
+    if (c.visc_field) {
+        eta = reinterpret_cast<double*>(p); p += plane_b;
+        gradtab = reinterpret_cast<double*>(p);
+        p += align_up((size_t)3 * (c.Nx + 2) * 8, 256) + align_up((size_t)3 * (c.Ny + 2) * 8, 256);
+    }
+    visc_set = false;
     st = reinterpret_cast<DevState*>(p); p += align_up(sizeof(DevState), 256);
     refresh = reinterpret_cast<RefreshOut*>(p); p += align_up(sizeof(RefreshOut), 256);
     npartial = REDUCE_BLOCKS + 1;
@@ -768,6 +859,7 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     if ((rc = make_map(&topo_map, topo, P.L, 3))) return rc;
     if ((rc = make_map(&topo2_map, topo, P.L, 3, BY, BX, 2))) return rc;
     if ((rc = make_map(&ls_map, extra, P.L, 1))) return rc;
+    if (eta && (rc = make_map(&eta_map, eta, P.L, 1))) return rc;
     topo_fast = 0;
     ls_fast = 1;               // the slip-length plane starts as zeros
     // _initialize (problem.py:662-670): rho0, rho0*U/2, rho0*V/2 everywhere incl. ghosts
@@ -890,8 +982,93 @@ int FvSolver::download(int field, double* data, int ncomp, int on_device, cudaSt
 }
 
 // the pass kernels live in fv_pass_exact.cu / fv_pass_fast.cu (same source, two arithmetic contracts)
-int launch_pass_exact(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, int n, cudaStream_t s);
-int launch_pass_fast(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, int n, cudaStream_t s);
+int launch_pass_exact(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, bool vf, int n, cudaStream_t s);
+int launch_pass_fast(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, bool vf, int n, cudaStream_t s);
+
+// ---- viscosity modifiers: host side ----------------------------------------------------
+// np.gradient's per-axis set-up (numpy/lib/_function_base_impl.py, gradient(): `distances` given as
+// coordinates): diffx = np.diff(x); constant spacing (diffx == diffx[0]).all() collapses to the scalar
+// form, else the three coefficient arrays of the second-order non-uniform stencil.  Host arithmetic is
+// compiled with -ffp-contract=off: same roundings as NumPy's.
+static void grad_axis_setup(const double* x, int n, GradAxis* G, std::vector<double>* abc) {
+    std::vector<double> d(n - 1);
+    for (int i = 0; i + 1 < n; ++i) d[i] = x[i + 1] - x[i];
+    bool uni = true;
+    for (int i = 0; i + 1 < n; ++i) uni = uni && (d[i] == d[0]);
+    G->n = n;
+    G->uniform = uni ? 1 : 0;
+    G->two_d = 2. * d[0];
+    G->d_first = d[0];
+    G->d_last = uni ? d[0] : d[n - 2];
+    abc->assign((size_t)3 * n, 0.0);
+    if (!uni)
+        for (int i = 1; i + 1 < n; ++i) {
+            const double dx1 = d[i - 1], dx2 = d[i];
+            (*abc)[i] = -(dx2) / (dx1 * (dx1 + dx2));
+            (*abc)[n + i] = (dx2 - dx1) / (dx1 * dx2);
+            (*abc)[2 * n + i] = dx1 / (dx2 * (dx1 + dx2));
+        }
+}
+
+int FvSolver::set_viscosity(int piezo, const double* pp, int thin, const double* tp, const double* x, const double* y) {
+    if (!P.visc_field) { set_error("gpf_fv_set_viscosity: the solver was created with cfg.visc_field = 0"); return GPF_E_STATE; }
+    if (piezo < GPF_PIEZO_ABSENT || piezo > GPF_PIEZO_MCADAMS || thin < GPF_THIN_ABSENT || thin > GPF_THIN_CARREAU) {
+        set_error("unknown piezoviscosity / shear-thinning law id"); return GPF_E_INVALID;
+    }
+    if (piezo == GPF_PIEZO_ABSENT && thin == GPF_THIN_ABSENT) { set_error("visc_field set but neither block present"); return GPF_E_INVALID; }
+    for (int sd = 0; sd < 2; ++sd)
+        if (P.bc.type[sd][0] == GPF_BC_HALO) {
+            set_error("viscosity modifiers on a slab (GPF_BC_HALO) solver: the pressure gradient at a halo row needs a "
+                      "second halo row; not supported");
+            return GPF_E_INVALID;
+        }
+    memset(&VM, 0, sizeof(VM));
+    VM.piezo = piezo; VM.thin = thin;
+    VM.use_dens = (P.eos.kind == GPF_EOS_BAYADA) ? 1 : 0;
+    const int npp = (piezo == GPF_PIEZO_BARUS) ? 1 : (piezo >= GPF_PIEZO_ROELANDS ? 3 : 0);
+    const int ntp = (thin == GPF_THIN_EYRING) ? 1 : (thin == GPF_THIN_CARREAU ? 4 : 0);
+    if ((npp && !pp) || (ntp && !tp)) { set_error("law parameters missing"); return GPF_E_INVALID; }
+    for (int k = 0; k < npp; ++k) VM.pp[k] = pp[k];
+    for (int k = 0; k < ntp; ++k) VM.tp[k] = tp[k];
+    if (piezo == GPF_PIEZO_ROELANDS) VM.pp[3] = log(cfg.eta / VM.pp[0]);
+    if (thin == GPF_THIN_CARREAU) VM.tp[4] = (VM.tp[3] - 1) / VM.tp[2];
+    const int nx = cfg.Nx + 2, ny = cfg.Ny + 2;
+    if (thin != GPF_THIN_ABSENT) {
+        if (!x || !y) { set_error("shear thinning needs the cell-centre coordinates x, y"); return GPF_E_INVALID; }
+        std::vector<double> ax, ay;
+        grad_axis_setup(x, nx, &VM.gx, &ax);
+        grad_axis_setup(y, ny, &VM.gy, &ay);
+        double* dx_tab = gradtab;
+        double* dy_tab = gradtab + align_up((size_t)3 * nx * 8, 256) / 8;
+        GPF_CUDA(cudaMemcpy(dx_tab, ax.data(), ax.size() * 8, cudaMemcpyHostToDevice));
+        GPF_CUDA(cudaMemcpy(dy_tab, ay.data(), ay.size() * 8, cudaMemcpyHostToDevice));
+        VM.gx.abc = dx_tab;
+        VM.gy.abc = dy_tab;
+    }
+    visc_set = true;
+    drop_graphs();
+    return GPF_OK;
+}
+
+int FvSolver::launch_viscosity(int rel, cudaStream_t s) {
+    if (!visc_set) { set_error("cfg.visc_field is set: call gpf_fv_set_viscosity() before stepping"); return GPF_E_STATE; }
+    const size_t np = (size_t)(cfg.Nx + 2) * (cfg.Ny + 2);
+    fv_viscosity_kernel<<<(int)((np + 255) / 256), 256, 0, s>>>(P, VM, st, qtable, topo, eta, rel);
+    g_launches++;
+    return debug_check("fv_viscosity_kernel", s);
+}
+
+int FvSolver::viscosity(int which, double* out, int on_device, cudaStream_t s) {
+    if (!P.visc_field) { set_error("gpf_fv_viscosity: the solver has no viscosity field"); return GPF_E_STATE; }
+    if (which < 0 || which > 1 || !out) { set_error("gpf_fv_viscosity: bad argument"); return GPF_E_INVALID; }
+    int rc = launch_viscosity(which ? 2 : 0, s);      // after a step the predictor's output sits two buffers on
+    if (rc) return rc;
+    const size_t Ny2 = cfg.Ny + 2, Nx2 = cfg.Nx + 2;
+    GPF_CUDA(cudaMemcpy2DAsync(out, Ny2 * 8, eta + 1, (size_t)P.L.pitch * 8, Ny2 * 8, Nx2,
+                               on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    if (!on_device) GPF_CUDA(cudaStreamSynchronize(s));
+    return GPF_OK;
+}
 
 // part: GPF_PART_ALL every tile row; GPF_PART_EDGE the first and the last tile row (whose rows the
 // slab neighbours need); GPF_PART_INTERIOR the rest -- so that a slab driver can exchange the edge
@@ -908,6 +1085,18 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     PassArgs A;
     for (int k = 0; k < 3; ++k) { A.qmap[k] = S.qmap[k]; A.q0map[k] = S.q0map[k]; A.qbuf[k] = S.qbuf[k]; }
     A.topo_map = S.topo_map; A.topo2_map = S.topo2_map; A.ls_map = S.ls_map;
+    const bool vf = S.P.visc_field != 0;
+    if (vf) {
+        // the viscosity of every cell of the pass's input (stress.py:305-326), once per pass: the
+        // INTERIOR launch of a split pass reads the plane its EDGE launch left
+        A.eta_map = S.eta_map;
+        if (part != GPF_PART_INTERIOR) {
+            const int rc = S.launch_viscosity(CORR ? 1 : 0, s);
+            if (rc) return rc;
+        }
+    } else {
+        A.eta_map = S.ls_map;
+    }
     A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags; A.redo = S.redo;
     A.until_converged = until_converged;
     // INTERIOR leaves a few CTA slots empty so that the exchange kernels of the side stream (pack,
@@ -929,8 +1118,8 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     const bool dh = S.P.eos.kind == GPF_EOS_DH;
     const bool xf = S.P.xflow != 0;
     const int n = (part == GPF_PART_INTERIOR) ? n_int : pass_ctas(A.ntiles, CORR, nty);
-    const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, n, s)
-                                                   : launch_pass_exact(A, CORR, ls, dh, xf, n, s);
+    const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, vf, n, s)
+                                                   : launch_pass_exact(A, CORR, ls, dh, xf, vf, n, s);
     if (rc) return rc;
     g_launches += 2;           // straight-line kernel + general kernel (returns at once unless flagged)
     return debug_check(CORR ? "fv_pass_kernel<corrector>" : "fv_pass_kernel<predictor>", s);
@@ -998,7 +1187,7 @@ int FvSolver::step(int n, int until_converged, cudaStream_t s) {
             if (e != cudaSuccess) { ge = nullptr; set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); return GPF_E_CUDA; }
         }
         for (int it = 0; it < n; ++it) GPF_CUDA(cudaGraphLaunch(ge, s));
-        g_launches += 5LL * n;
+        g_launches += (P.visc_field ? 7LL : 5LL) * n;
         dirty_scalars = false;
         return GPF_OK;
     }
@@ -1365,10 +1554,16 @@ int FvSolver::closures(double* p, double* wxz, double* wyz, double* bulk, int on
     double** o = on_device ? d : tmp;
     const int blocks = (int)((np + 255) / 256);
     const bool ls = P.has_extra != 0, dh = P.eos.kind == GPF_EOS_DH;
-    if (ls) { if (dh) fv_closures_kernel<true, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel);
-              else    fv_closures_kernel<true, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel); }
-    else    { if (dh) fv_closures_kernel<false, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel);
-              else    fv_closures_kernel<false, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel); }
+    const double* ef = nullptr;          // viscosity field of the same state
+    if (P.visc_field) {
+        int rc = launch_viscosity(rel, s);
+        if (rc) return rc;
+        ef = eta;
+    }
+    if (ls) { if (dh) fv_closures_kernel<true, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel, ef);
+              else    fv_closures_kernel<true, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel, ef); }
+    else    { if (dh) fv_closures_kernel<false, GPF_EOS_DH><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel, ef);
+              else    fv_closures_kernel<false, -1><<<blocks, 256, 0, s>>>(P, st, qtable, topo, extra, o[0], o[1], o[2], o[3], rel, ef); }
     g_launches++;
     GPF_CUDA(cudaGetLastError());
     if (!on_device) {

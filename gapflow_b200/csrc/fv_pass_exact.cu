@@ -4,7 +4,7 @@
 #include "fv_pass_kernel.cuh"
 
 namespace gpf {
-int launch_pass_exact(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, int n, cudaStream_t s) {
-    return corr ? exact::launch_pass_dispatch<true>(A, ls, dh, xf, n, s) : exact::launch_pass_dispatch<false>(A, ls, dh, xf, n, s);
+int launch_pass_exact(const PassArgs& A, bool corr, bool ls, bool dh, bool xf, bool vf, int n, cudaStream_t s) {
+    return corr ? exact::launch_pass_dispatch<true>(A, ls, dh, xf, vf, n, s) : exact::launch_pass_dispatch<false>(A, ls, dh, xf, vf, n, s);
 }
 }  // namespace gpf

@@ -27,19 +27,21 @@ constexpr size_t BOX1_BYTES = al128((size_t)BOX * 8);
 constexpr size_t OWN3_BYTES = (size_t)3 * TX * TY * 8;          // q0 of the tile's own cells (corrector)
 
 // NST: depth of the TMA ring (tiles in flight ahead of the one being computed: NST - 1)
-template <bool CORR, bool LS, bool XF, int NST>
+template <bool CORR, bool LS, bool XF, int NST, bool VF = false>
 struct Smem {
     static constexpr size_t Q = 0;
     static constexpr size_t TOPO = Q + BOX3_BYTES;
     static constexpr size_t LSO = TOPO + (XF ? BOX2_BYTES : BOX3_BYTES);    // x-driven film: dh/dy plane not loaded
-    static constexpr size_t Q0 = LSO + (LS ? BOX1_BYTES : 0);
+    static constexpr size_t ETA = LSO + (LS ? BOX1_BYTES : 0);               // per-cell shear viscosity (piezo / thinning)
+    static constexpr size_t Q0 = ETA + (VF ? BOX1_BYTES : 0);
     static constexpr size_t STAGE = Q0 + (CORR ? OWN3_BYTES : 0);
     static constexpr size_t CLOS = NST * STAGE;                 // p, t0, t1, t2 of the staged cells
     static constexpr size_t BAR = CLOS + al128((size_t)4 * BOX * 8);
     static constexpr size_t RED = BAR + 128;                    // <= 4 mbarriers, 2 tile flags
     static constexpr size_t TOTAL = RED + (FV_THREADS / 32) * 4 * 8;
     static constexpr uint32_t TX_BYTES = (uint32_t)(3 * BOX * 8) + (uint32_t)((XF ? 2 : 3) * BOX * 8) +
-                                         (LS ? (uint32_t)(BOX * 8) : 0u) + (CORR ? (uint32_t)OWN3_BYTES : 0u);
+                                         (LS ? (uint32_t)(BOX * 8) : 0u) + (VF ? (uint32_t)(BOX * 8) : 0u) +
+                                         (CORR ? (uint32_t)OWN3_BYTES : 0u);
 };
 
 
@@ -65,8 +67,23 @@ __device__ __forceinline__ bool cell_in_fast_range(const Cell& c) {
 
 struct Clos4 { double p, t0, t1, t2; };
 
-template <bool LS, int EOS, bool FAST, bool XF>
-__device__ __forceinline__ Clos4 phase1_cell(const Cell& c, const FvParams& P) {
+// viscosity scalars of one cell: the configuration's, or (VF) those of the cell's own shear viscosity
+// eta (stress.py:305-326 makes `eta` a field; viscous.py:82-83 then evaluates v1, v2 per cell)
+template <bool VF>
+__device__ __forceinline__ Visc cell_visc(const FvParams& P, double eta) {
+    Visc m = reinterpret_cast<const Visc&>(P.visc);
+    if constexpr (VF) {
+        m.eta = eta;
+        m.v1 = m.zeta + 4. / 3. * eta;
+        m.v2 = m.zeta - 2. / 3. * eta;
+        m.two_eta = 2 * eta;
+        m.two_v2 = 2 * m.v2;
+    }
+    return m;
+}
+
+template <bool LS, int EOS, bool FAST, bool XF, bool VF = false>
+__device__ __forceinline__ Clos4 phase1_cell(const Cell& c, const FvParams& P, double eta = 0.0) {
     Clos4 r;
 #if GPF_FAST_ARITH
     if constexpr (FAST && !LS) {
@@ -91,12 +108,17 @@ __device__ __forceinline__ Clos4 phase1_cell(const Cell& c, const FvParams& P) {
     }
 #endif
     r.p = eos_pressure<EOS, FAST>(c.q0, P.eos);
-    stress_avg<LS, FAST, XF>(c, reinterpret_cast<const Visc&>(P.visc), r.t0, r.t1, r.t2);
+    if constexpr (VF) {
+        const Visc m = cell_visc<true>(P, eta);
+        stress_avg<LS, FAST, XF>(c, m, r.t0, r.t1, r.t2);
+    } else {
+        stress_avg<LS, FAST, XF>(c, reinterpret_cast<const Visc&>(P.visc), r.t0, r.t1, r.t2);
+    }
     return r;
 }
-template <bool LS, int EOS>
-__device__ __noinline__ Clos4 phase1_cell_slow(const Cell c, const FvParams& P) {
-    return phase1_cell<LS, EOS, false, false>(c, P);
+template <bool LS, int EOS, bool VF = false>
+__device__ __noinline__ Clos4 phase1_cell_slow(const Cell c, const FvParams& P, double eta = 0.0) {
+    return phase1_cell<LS, EOS, false, false, VF>(c, P, eta);
 }
 
 struct Nb { double q1x, Ax, t2x, q2y, t2y, Cy; };   // neighbour fluxes: Fx = (q1, A, t2), Fy = (q2, t2, C)
@@ -106,10 +128,13 @@ struct Q3 { double v0, v1, v2; };
 // and the update q - dt*(fX/dx + fY/dy - src) (problem.py:558) of one interior cell.
 // flux = -d*(F[nb] - F[own]): the sign flip is exact and done on the integer pipe.  The xz + yz
 // field sums of problem.py:554-555 are u/2 + u/2 == u (exact) and u + 0.
-template <bool LS, bool FAST, bool XF>
+template <bool LS, bool FAST, bool XF, bool VF = false>
 __device__ __forceinline__ Q3 phase2_cell(const Cell& c, const Clos4& k, const Nb& n, const FvParams& P,
-                                          unsigned sbit, double dt) {
-    const Visc& V = reinterpret_cast<const Visc&>(P.visc);
+                                          unsigned sbit, double dt, double eta = 0.0) {
+    static_assert(!VF || LS, "the viscosity-field variants use the general (slip-length) closures");
+    Visc Vcell;
+    if constexpr (VF) Vcell = cell_visc<true>(P, eta);
+    const Visc& V = VF ? Vcell : reinterpret_cast<const Visc&>(P.visc);
     const double fx0 = flip(n.q1x - c.q1, sbit);
     const double fx1 = flip(n.Ax - (k.p + k.t0), sbit);
     const double fx2 = flip(n.t2x - k.t2, sbit);
@@ -173,10 +198,10 @@ __device__ __forceinline__ Q3 phase2_cell(const Cell& c, const Clos4& k, const N
     q.v2 = c.q2 - dt * (div_sel<FAST>(fx2, P.dx, P.rdx) + div_sel<FAST>(fy2, P.dy, P.rdy) - s2);
     return q;
 }
-template <bool LS>
+template <bool LS, bool VF = false>
 __device__ __noinline__ Q3 phase2_cell_slow(const Cell c, const Clos4 k, const Nb n, const FvParams& P,
-                                            unsigned sbit, double dt) {
-    return phase2_cell<LS, false, false>(c, k, n, P, sbit, dt);
+                                            unsigned sbit, double dt, double eta = 0.0) {
+    return phase2_cell<LS, false, false, VF>(c, k, n, P, sbit, dt, eta);
 }
 
 // exact flags of one stored cell, off the hot path (problem.py:320-332)
@@ -201,10 +226,10 @@ __device__ __noinline__ int cell_flags_slow(double a, double b, double c, double
 //                plain IEEE divisions, exact validity flags).  Returns at once unless A.redo[CORR] is
 //                raised, else recomputes the whole pass: a pass reads only buffers it does not write.
 // Each GEN = false launch lowers the other pass's flag; a stale raised flag only costs time.
-template <bool CORR, bool LS, int EOS, bool XF, bool GEN>
+template <bool CORR, bool LS, int EOS, bool XF, bool GEN, bool VF = false>
 __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kernel(const __grid_constant__ PassArgs A) {
     constexpr int NST = fv_nstage(CORR);
-    using S = Smem<CORR, LS, XF, NST>;
+    using S = Smem<CORR, LS, XF, NST, VF>;
     extern __shared__ __align__(1024) unsigned char smem[];      // no static shared memory: offset 0
     uint64_t* const bar = reinterpret_cast<uint64_t*>(smem + S::BAR);
     double* const sp = reinterpret_cast<double*>(smem + S::CLOS);
@@ -252,6 +277,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         tma_load_3d(base + S::Q, &A.qmap[in_idx], b, cm, cx, 0);
         tma_load_3d(base + S::TOPO, XF ? &A.topo2_map : &A.topo_map, b, cm, cx, 0);
         if (LS) tma_load_3d(base + S::LSO, &A.ls_map, b, cm, cx, 0);
+        if (VF) tma_load_3d(base + S::ETA, &A.eta_map, b, cm, cx, 0);
         if (CORR) tma_load_3d(base + S::Q0, &A.q0map[cur], b, j0 + 1, i0, 0);
     };
 
@@ -328,7 +354,11 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         const double* stp = reinterpret_cast<const double*>(base + S::TOPO);
         const double* sls = reinterpret_cast<const double*>(base + S::LSO);
         const double* sq0 = reinterpret_cast<const double*>(base + S::Q0);
+        const double* seta = reinterpret_cast<const double*>(base + S::ETA);
         mbar_wait(bar + stage, phase);
+        // the cell's shear viscosity (VF) must be a divisor-safe operand like the other static fields
+        auto load_eta = [&](int o) { return VF ? seta[o] : 0.0; };
+        auto eta_ok = [&](double e) { return !VF || in_fast_range_nz(e); };
 
         auto load_cell = [&](int o) {
             Cell c;
@@ -345,32 +375,36 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         // ---- phase 1: pressure + gap-averaged stress on tile + halo row + halo column ----
         if constexpr (!GEN) {
             const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
-            bad |= !(cell_in_fast_range(ca) & cell_in_fast_range(cb));
-            store_clos(o_own, phase1_cell<LS, EOS, true, XF>(ca, P));
-            store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF>(cb, P));
+            const double ea = load_eta(o_own), eb = load_eta(o_own + BY);
+            bad |= !(cell_in_fast_range(ca) & cell_in_fast_range(cb) & eta_ok(ea) & eta_ok(eb));
+            store_clos(o_own, phase1_cell<LS, EOS, true, XF, VF>(ca, P, ea));
+            store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF, VF>(cb, P, eb));
             if (has_halo) {
                 const Cell ch = load_cell(o_halo);
-                bad |= !cell_in_fast_range(ch);
-                store_clos(o_halo, phase1_cell<LS, EOS, true, XF>(ch, P));
+                const double eh = load_eta(o_halo);
+                bad |= !(cell_in_fast_range(ch) & eta_ok(eh));
+                store_clos(o_halo, phase1_cell<LS, EOS, true, XF, VF>(ch, P, eh));
             }
         } else {
             const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
-            const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb);
+            const double ea = load_eta(o_own), eb = load_eta(o_own + BY);
+            const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb) & eta_ok(ea) & eta_ok(eb);
             if (__all_sync(0xffffffffu, ok) && P.static_fast) {   // warp-uniform
-                store_clos(o_own, phase1_cell<LS, EOS, true, XF>(ca, P));
-                store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF>(cb, P));
+                store_clos(o_own, phase1_cell<LS, EOS, true, XF, VF>(ca, P, ea));
+                store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF, VF>(cb, P, eb));
             } else {
-                store_clos(o_own, phase1_cell_slow<LS, EOS>(ca, P));
-                store_clos(o_own + BY, phase1_cell_slow<LS, EOS>(cb, P));
+                store_clos(o_own, phase1_cell_slow<LS, EOS, VF>(ca, P, ea));
+                store_clos(o_own + BY, phase1_cell_slow<LS, EOS, VF>(cb, P, eb));
                 sbad[fl] = 1;             // this tile takes the plain-division path in phase 2
             }
         }
         if (GEN && has_halo) {
             const Cell ch = load_cell(o_halo);
-            if (__all_sync(0xffffffffu, q_in_fast_range(ch)) && P.static_fast) {
-                store_clos(o_halo, phase1_cell<LS, EOS, true, XF>(ch, P));
+            const double eh = load_eta(o_halo);
+            if (__all_sync(0xffffffffu, q_in_fast_range(ch) & eta_ok(eh)) && P.static_fast) {
+                store_clos(o_halo, phase1_cell<LS, EOS, true, XF, VF>(ch, P, eh));
             } else {
-                store_clos(o_halo, phase1_cell_slow<LS, EOS>(ch, P));
+                store_clos(o_halo, phase1_cell_slow<LS, EOS, VF>(ch, P, eh));
                 sbad[fl] = 1;
             }
         }
@@ -393,11 +427,12 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             Nb nb;
             nb.q1x = sq[BOX + o + on_dx]; nb.Ax = sp[o + on_dx] + st0[o + on_dx]; nb.t2x = st2[o + on_dx];
             nb.q2y = sq[2 * BOX + o + on_dy]; nb.t2y = st2[o + on_dy]; nb.Cy = sp[o + on_dy] + st1[o + on_dy];
+            const double e = load_eta(o);
             if constexpr (GEN) {
-                return fast ? phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt)
-                            : phase2_cell_slow<LS>(c, kk, nb, P, sbit, dt);
+                return fast ? phase2_cell<LS, true, XF, VF>(c, kk, nb, P, sbit, dt, e)
+                            : phase2_cell_slow<LS, VF>(c, kk, nb, P, sbit, dt, e);
             } else {
-                return phase2_cell<LS, true, XF>(c, kk, nb, P, sbit, dt);
+                return phase2_cell<LS, true, XF, VF>(c, kk, nb, P, sbit, dt, e);
             }
         };
         // corrector (116 registers at 2 CTAs/SM): both cells of a thread in one straight-line block,
@@ -533,23 +568,26 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     }
 }
 
-template <bool CORR, bool LS, int EOS, bool XF>
+template <bool CORR, bool LS, int EOS, bool XF, bool VF = false>
 static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
-    using Sm = Smem<CORR, LS, XF, fv_nstage(CORR)>;
+    using Sm = Smem<CORR, LS, XF, fv_nstage(CORR), VF>;
     static bool attr_set = false;
     if (!attr_set) {
-        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
-        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, false, VF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, true, VF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
         attr_set = true;
     }
-    fv_pass_kernel<CORR, LS, EOS, XF, false><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
-    fv_pass_kernel<CORR, LS, EOS, XF, true><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    fv_pass_kernel<CORR, LS, EOS, XF, false, VF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    fv_pass_kernel<CORR, LS, EOS, XF, true, VF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
     return GPF_OK;
 }
 
-// variant dispatch: slip-length field, Dowson-Higginson inlined, x-driven film
+// variant dispatch: slip-length field, Dowson-Higginson inlined, x-driven film, viscosity field
 template <bool CORR>
-int launch_pass_dispatch(const PassArgs& A, bool ls, bool dh, bool xf, int n, cudaStream_t s) {
+int launch_pass_dispatch(const PassArgs& A, bool ls, bool dh, bool xf, bool vf, int n, cudaStream_t s) {
+    // viscosity field (piezo / thinning): one variant, the general closures with the slip-length plane
+    // (zeros when the configuration has none: the LS forms with Ls = 0 round like the reference's)
+    if (vf) return launch_pass_variant<CORR, true, -1, false, true>(A, n, s);
     switch ((ls ? 4 : 0) + (dh ? 2 : 0) + (xf ? 1 : 0)) {
     case 0: return launch_pass_variant<CORR, false, -1, false>(A, n, s);
     case 1: return launch_pass_variant<CORR, false, -1, true>(A, n, s);

@@ -18,6 +18,22 @@ struct ViscParams {
     double U, V, eta, zeta, v1, v2, two_eta, two_v2;
 };
 
+// viscosity modifiers (stress.py:305-326; gpf_fv_set_viscosity)
+struct GradAxis {           // np.gradient along one axis of the padded array
+    int n;                  // points
+    int uniform;            // NumPy found constant spacing: interior (f[i+1] - f[i-1]) / two_d
+    double two_d;           // 2. * dx            (uniform)
+    double d_first, d_last; // spacing of the one-sided differences at the two edges
+    const double* abc;      // non-uniform: a[n], b[n], c[n] of  a f[i-1] + b f[i] + c f[i+1]  (device)
+};
+struct ViscModel {
+    int piezo, thin;        // GPF_PIEZO_*, GPF_THIN_*
+    int use_dens;           // Bayada-Chupin EOS: the piezo law takes the density (stress.py:307)
+    double pp[4];           // piezo parameters (Roelands: pp[3] = log(mu0 / mu_inf), host)
+    double tp[5];           // thinning parameters (Carreau: tp[4] = (N - 1) / a, host)
+    GradAxis gx, gy;
+};
+
 // boundary table (device copy of gpf_fv_cfg.bc_*)
 struct BcTable {
     int type[4][3];
@@ -95,6 +111,7 @@ struct FvParams {
     double CFL, tol, dt0;
     int adaptive, max_it, mc_order;
     int has_extra;
+    int visc_field;               // shear viscosity is a per-cell field (piezo / thinning), staged like the slip length
     int xflow;                    // V == 0 and dh/dy == 0 everywhere (x-driven film)
     int scalars_fast;             // dx, dy, viscosities, wall speeds, EOS parameters all in [2^-100, 2^100] or 0
     int static_fast;              // scalars_fast and every h in range, dh/dx, dh/dy, Ls in range or 0, Ls >= 0

@@ -41,6 +41,15 @@ class FVSolver:
         _capi.check(self.lib.gpf_fv_create(C.byref(self.cfg), C.c_void_p(self.workspace.data_ptr()),
                                            nbytes.value, C.byref(h)))
         self.h = h
+        if self.cfg.visc_field:
+            # viscosity modifiers (stress.py:305-326): laws + the cell-centre coordinates np.gradient gets
+            # (stress.py:180, 192: topo.x[:, 0], topo.y[0, :]; topography.py:38-54)
+            from .topography import midpoint_grid
+            xx, yy = midpoint_grid(grid)
+            self._xy = (np.ascontiguousarray(xx[:, 0], dtype=np.float64), np.ascontiguousarray(yy[0, :], dtype=np.float64))
+            pz, pp, th, tp = _capi.viscosity_args(prop)
+            _capi.check(self.lib.gpf_fv_set_viscosity(self.h, pz, pp, th, tp, C.c_void_p(self._xy[0].ctypes.data),
+                                                      C.c_void_p(self._xy[1].ctypes.data)))
         self.upload_topo(topo)
         if has_extra:
             e = np.ascontiguousarray(np.broadcast_to(np.asarray(extra, dtype=np.float64), (1, *self.shape)))
@@ -98,6 +107,13 @@ class FVSolver:
         return outs[0][0], outs[1], outs[2], outs[3]
 
     # -- time loop --------------------------------------------------------------------
+    def viscosity(self, stale=False):
+        """The shear-viscosity field (Nx+2, Ny+2) of the current q (``stale``: of the last corrector pass's
+        input) when properties has a piezo / thinning block (stress.py:305-326); NumPy array."""
+        out = np.empty(self.shape)
+        _capi.check(self.lib.gpf_fv_viscosity(self.h, 1 if stale else 0, C.c_void_p(out.ctypes.data), 0, self._stream()))
+        return out
+
     def pre_run(self, reset_ekin_old=False):
         _capi.check(self.lib.gpf_fv_pre_run(self.h, 1 if reset_ekin_old else 0, self._stream()))
 

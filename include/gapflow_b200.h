@@ -43,6 +43,13 @@ enum { GPF_SIDE_X0 = 0, GPF_SIDE_X1 = 1, GPF_SIDE_Y0 = 2, GPF_SIDE_Y1 = 3 };
 /* arithmetic contract of the pass kernels (gpf_fv_cfg.arith) */
 enum { GPF_ARITH_EXACT = 0, GPF_ARITH_FAST = 1 };
 
+/* viscosity modifiers (GaPFlow/models/viscosity.py:34-96): piezoviscosity and shear-thinning law ids.
+ * GPF_*_IDENTITY is a block whose name the reference does not know: the law is the identity
+ * (viscosity.py:64, 94) but the viscosity is still evaluated as a field. */
+enum { GPF_PIEZO_ABSENT = 0, GPF_PIEZO_IDENTITY = 1, GPF_PIEZO_BARUS = 2, GPF_PIEZO_ROELANDS = 3,
+       GPF_PIEZO_DUKLER = 4, GPF_PIEZO_MCADAMS = 5 };
+enum { GPF_THIN_ABSENT = 0, GPF_THIN_IDENTITY = 1, GPF_THIN_EYRING = 2, GPF_THIN_CARREAU = 3 };
+
 /* field ids for upload/download */
 enum { GPF_F_Q = 0, GPF_F_TOPO = 1, GPF_F_EXTRA = 2 };
 
@@ -74,7 +81,10 @@ typedef struct gpf_fv_cfg {
                                   expressions round it -> bit-identical fields for the + - * / sqrt EOS;
                                   GPF_ARITH_FAST (1): FMA contraction and a*rcp(b) quotients in the pass
                                   kernels -> within 1e-12 relative per step, ~1.4x faster */
-    int32_t reserved[4];
+    int32_t visc_field;        /* != 0: properties has a 'piezo' and / or 'thinning' block, the shear viscosity is
+                                  a per-cell field (stress.py:305-326); gpf_fv_set_viscosity() must follow
+                                  gpf_fv_create().  Adds one plane + the gradient tables to the workspace */
+    int32_t reserved[3];
 } gpf_fv_cfg;
 
 /* Host-visible scalars of the time loop (GaPFlow/problem.py:314-362, 571-586). */
@@ -114,6 +124,26 @@ int gpf_fv_workspace_bytes(const gpf_fv_cfg* cfg, size_t* bytes);
  * call gpf_fv_pre_run(). */
 int gpf_fv_create(const gpf_fv_cfg* cfg, void* workspace, size_t bytes, gpf_fv** out);
 int gpf_fv_destroy(gpf_fv* s);
+
+/* Viscosity modifiers of a solver created with cfg.visc_field != 0.  Replaces the piezoviscosity /
+ * shear_rate_avg / shear_thinning_factor chain at the head of WallStress.update and BulkStress.update
+ * (GaPFlow/models/stress.py:305-326, 429-450; laws in GaPFlow/models/viscosity.py:99-318): before every
+ * pass the viscosity of each cell of the padded array is evaluated from the pass's own pressure field,
+ *   mu0 = piezo(p)  (piezo(rho) for the Bayada-Chupin EOS, stress.py:307),
+ *   eta = mu0 * thinning(shear_rate_avg(dp/dx, dp/dy, h, U, V, mu0), mu0),
+ * with dp/dx, dp/dy = np.gradient(p, x, axis) over the padded array (stress.py:171-192: central in
+ * the interior, one-sided at the two edges, uniform or non-uniform form chosen as NumPy chooses it
+ * from the coordinates).  piezo_par: Barus {aB} | Roelands {mu_inf, p_ref, z} | Dukler, McAdams
+ * {eta_v, rho_l, rho_v};  thin_par: Eyring {tauE} | Carreau {mu_inf, lam, a, N}.  x (Nx+2), y (Ny+2):
+ * HOST arrays, the cell-centre coordinates topo.x[:, 0], topo.y[0, :] (topography.py:38-54); may be
+ * NULL when thinning is absent.  Slab (GPF_BC_HALO) solvers are refused: the gradient at a halo row
+ * needs a second halo row.  exp / log / pow / asinh / hypot make this path tolerance-based (1e-12 per
+ * step) in both arithmetic contracts. */
+int gpf_fv_set_viscosity(gpf_fv* s, int piezo, const double* piezo_par, int thinning, const double* thin_par,
+                         const double* x, const double* y);
+/* the viscosity field of the current q (which = 0) or of the last corrector pass's input (which = 1),
+ * dense (Nx+2, Ny+2), device or host; synchronises for host output */
+int gpf_fv_viscosity(gpf_fv* s, int which, double* eta, int on_device, void* stream);
 
 /* Dense (ncomp, Nx+2, Ny+2) float64 <-> solver storage.  ncomp: Q 3, TOPO 3 (h, dh/dx,
  * dh/dy; a 4-component array may be passed with ncomp=4, comp 3 is ignored), EXTRA 1.

@@ -265,7 +265,7 @@ def stress_avg(q, h, U, V, eta, zeta, Ls):
 
 
 # ---------------------------------------------------------------------------------
-# Viscosity modifiers (row F11; not on the CUDA path yet, restated for the next round's parity tests)
+# Viscosity modifiers (row F11; CUDA: fv_viscosity_kernel in gapflow_b200/csrc/fv_kernels.cu)
 # ---------------------------------------------------------------------------------
 def piezoviscosity(p, mu0, piezo):
     """GaPFlow/models/viscosity.py:34-66 -> 144-259.  ``p`` is the pressure field, or the density for
@@ -290,3 +290,33 @@ def shear_rate_avg(dp_dx, dp_dy, h, u1, u2, mu):
     du_pois = h * grad_p / (2 * mu)
     du_carr = (u2 - u1) / h
     return (np.abs(du_pois + du_carr) + np.abs(-du_pois + du_carr)) / 2.
+
+
+def shear_thinning_factor(shear_rate, mu0, thinning):
+    """viscosity.py:69-96 -> 262-318: factor that multiplies the (piezo-)viscosity."""
+    name = thinning.get('name', 'none')
+    if name == 'Eyring':                 # viscosity.py:284-285
+        tau0 = mu0 * shear_rate
+        return thinning['tauE'] / tau0 * np.arcsinh(tau0 / thinning['tauE'])
+    if name == 'Carreau':                # viscosity.py:316-318
+        mu = thinning['mu_inf'] + (mu0 - thinning['mu_inf']) * \
+            (1 + (thinning['lam'] * shear_rate)**thinning['a'])**((thinning['N'] - 1) / thinning['a'])
+        return mu / mu0
+    return np.ones_like(shear_rate)      # viscosity.py:94
+
+
+def shear_viscosity(pressure, dens, h, x, y, U, V, prop):
+    """The viscosity field both stress models build (stress.py:305-326 == 429-450): piezoviscosity of the
+    CURRENT pressure field (density for the Bayada-Chupin EOS), then the thinning factor at the average
+    shear rate, whose pressure gradient is np.gradient over the padded array with the cell-centre
+    coordinates (stress.py:171-192: second-order central, one-sided at the array edges).  Note the
+    reference passes (geo['U'], geo['V']) as (u1, u2) of shear_rate_avg (stress.py:317-318)."""
+    mu0 = prop['shear']
+    if 'piezo' in prop:
+        mu0 = piezoviscosity(pressure if prop['EOS'] != 'Bayada' else dens, prop['shear'], prop['piezo'])
+    if 'thinning' in prop:
+        dp_dx = np.gradient(pressure, x, axis=0)
+        dp_dy = np.gradient(pressure, y, axis=1)
+        rate = shear_rate_avg(dp_dx, dp_dy, h, U, V, mu0)
+        return mu0 * shear_thinning_factor(rate, mu0, prop['thinning'])
+    return mu0

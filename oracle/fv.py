@@ -212,13 +212,14 @@ class FVOracle:
     # -- closures, stress.py --------------------------------------------------
     def closures(self):
         """Pressure.update (:600-622), WallStress.update x2 (:289-362), BulkStress.update
-        (:427-459), fixed-form branch, constant viscosity."""
+        (:427-459), fixed-form branch; viscosity modifiers via viscosity()."""
         g, pr = self.geo, self.prop
         h = self.topo[:3]
         Ls = self.extra[0]
         self.pressure[...] = C.eos_pressure(self.q[0], pr)
-        sb = C.stress_bottom(self.q, h, g['U'], g['V'], pr['shear'], pr['bulk'], Ls)
-        st = C.stress_top(self.q, h, g['U'], g['V'], pr['shear'], pr['bulk'], Ls)
+        eta = self.viscosity()
+        sb = C.stress_bottom(self.q, h, g['U'], g['V'], eta, pr['bulk'], Ls)
+        st = C.stress_top(self.q, h, g['U'], g['V'], eta, pr['bulk'], Ls)
         for f, k in ((self.wall_xz, 4), (self.wall_yz, 3)):
             f[:3] = sb[:3] / 2.
             f[6:9] = st[:3] / 2.
@@ -226,7 +227,16 @@ class FVOracle:
             f[11] = st[-1] / 2.
             f[k] = sb[k]
             f[k + 6] = st[k]
-        self.bulk[...] = C.stress_avg(self.q, h, g['U'], g['V'], pr['shear'], pr['bulk'], Ls)
+        self.bulk[...] = C.stress_avg(self.q, h, g['U'], g['V'], eta, pr['bulk'], Ls)
+
+    def viscosity(self):
+        """Scalar, or the (Nx+2, Ny+2) field of stress.py:305-326 when a piezo / thinning block is present;
+        needs self.pressure of the current q."""
+        if 'piezo' not in self.prop and 'thinning' not in self.prop:
+            return self.prop['shear']
+        xx, yy = midpoint_grid(self.grid)
+        return C.shear_viscosity(self.pressure, self.q[0], self.topo[0], xx[:, 0], yy[0, :],
+                                 self.geo['U'], self.geo['V'], self.prop)
 
     # -- ghost cells, problem.py:676-768 ---------------------------------------
     def ghost_values(self, bc_type, axis, direction):

@@ -42,8 +42,9 @@ class RefDrivenOracle(fv.FVOracle):
         R, g, pr = self.R, self.geo, self.prop
         h = self.topo[:3]
         self.pressure[...] = R['pressure'].eos_pressure(self.q[0], pr)
-        sb = R['viscous'].stress_bottom(self.q, h, g['U'], g['V'], pr['shear'], pr['bulk'], self.extra)
-        st = R['viscous'].stress_top(self.q, h, g['U'], g['V'], pr['shear'], pr['bulk'], self.extra)
+        eta = self.viscosity()
+        sb = R['viscous'].stress_bottom(self.q, h, g['U'], g['V'], eta, pr['bulk'], self.extra)
+        st = R['viscous'].stress_top(self.q, h, g['U'], g['V'], eta, pr['bulk'], self.extra)
         for f, k in ((self.wall_xz, 4), (self.wall_yz, 3)):
             f[:3] = sb[:3] / 2.
             f[6:9] = st[:3] / 2.
@@ -51,7 +52,20 @@ class RefDrivenOracle(fv.FVOracle):
             f[11] = st[-1] / 2.
             f[k] = sb[k]
             f[k + 6] = st[k]
-        self.bulk[...] = R['viscous'].stress_avg(self.q, h, g['U'], g['V'], pr['shear'], pr['bulk'], self.extra)
+        self.bulk[...] = R['viscous'].stress_avg(self.q, h, g['U'], g['V'], eta, pr['bulk'], self.extra)
+
+    def viscosity(self):
+        """stress.py:305-326 with the reference's own viscosity.py functions."""
+        V, g, pr = self.R['viscosity'], self.geo, self.prop
+        mu0 = pr['shear']
+        if 'piezo' in pr:
+            mu0 = V.piezoviscosity(self.pressure if not pr['EOS'] == 'Bayada' else self.q[0], pr['shear'], pr['piezo'])
+        if 'thinning' in pr:
+            xx, yy = fv.midpoint_grid(self.grid)
+            rate = V.shear_rate_avg(np.gradient(self.pressure, xx[:, 0], axis=0),
+                                    np.gradient(self.pressure, yy[0, :], axis=1), self.topo[0], g['U'], g['V'], mu0)
+            return mu0 * V.shear_thinning_factor(rate, mu0, pr['thinning'])
+        return mu0
 
     def one_pass(self, d):
         R = self.R

@@ -79,6 +79,51 @@ STEP_CASES = {
                                   prop=_BWR), extra=True, rel_rho=1e-3),
 }
 
+_BAYADA = """
+properties:
+    EOS: Bayada
+    rho0: 850.
+    shear: 0.039
+    bulk: 0.
+    c_l: 1600.
+    c_v: 352.
+    piezo:
+        name: {name}
+        eta_v: 3.9e-5
+        rho_l: 850.
+        rho_v: 0.019
+"""
+_SLIDER = "geometry:\n    type: parabolic\n    hmin: 2.54e-5\n    hmax: 5.08e-5\n    U: 4.57\n    V: {V}\n"
+_XDN850 = _XDN.replace('877.7007', '850.')
+
+# viscosity modifiers (SURVEY row F11; stress.py:305-326): piezo / thinning blocks make the viscosity a field
+STEP_CASES.update({
+    # examples/config/parabolic_1d_cav_bayada.yaml (density-based mixture viscosity, no pressure gradient needed)
+    'cav1d_dukler': dict(yaml=_yaml("grid:\n    Lx: 0.0762\n    Ly: 1.\n    Nx: 100\n    Ny: 1\n" + _XDN850, _SLIDER.format(V='0.'),
+                                    _ADAPT.format(CFL=0.45, mc=1), prop=_BAYADA.format(name='Dukler')), rel_rho=1e-3),
+    'cav2d_mcadams': dict(yaml=_yaml("grid:\n    Lx: 0.0762\n    Ly: 0.0762\n    Nx: 21\n    Ny: 70\n" + _XDN850, _SLIDER.format(V='0.3'),
+                                     _ADAPT.format(CFL=0.4, mc=0), prop=_BAYADA.format(name='McAdams')), rel_rho=1e-3),
+    # pressure-based laws on the BASELINE config 2 slider: Barus alone; Barus + Eyring; Roelands + Carreau (+ slip
+    # length, bulk viscosity, V != 0); Eyring alone
+    'slider2d_barus': dict(yaml=_yaml("grid:\n    Lx: 0.0762\n    Ly: 0.0762\n    Nx: 33\n    Ny: 65\n" + _XDN, _SLIDER.format(V='0.'),
+                                      _ADAPT.format(CFL=0.45, mc=1),
+                                      prop=_DH.format(bulk=0., C1='3.5e10') + "    piezo:\n        name: Barus\n        aB: 2.e-8\n")),
+    'slider2d_barus_eyring': dict(yaml=_yaml("grid:\n    Lx: 0.0762\n    Ly: 0.0762\n    Nx: 33\n    Ny: 65\n" + _XDN, _SLIDER.format(V='0.'),
+                                             _ADAPT.format(CFL=0.45, mc=1),
+                                             prop=_DH.format(bulk=0., C1='3.5e10') + "    piezo:\n        name: Barus\n        aB: 2.e-8\n"
+                                             "    thinning:\n        name: Eyring\n        tauE: 5.e5\n")),
+    'journal2d_roelands_carreau_slip': dict(yaml=_yaml(_grid(20, 70, '2.e-4', '1.e-4', _PER), _JOURNAL.format(V='-0.03', flip=False),
+                                                       _ADAPT.format(CFL=0.4, mc=-1),
+                                                       prop=_DH.format(bulk=0.013, C1='3.5e10') +
+                                                       "    piezo:\n        name: Roelands\n        mu_inf: 1.e-3\n        p_ref: 1.96e8\n        z: 0.68\n"
+                                                       "    thinning:\n        name: Carreau\n        mu_inf: 1.e-3\n        lam: 0.02\n        a: 2.\n        N: 0.8\n"),
+                                            extra=True),
+    'journal1d_eyring': dict(yaml=_yaml(_grid(100, 1, '1.e-5', '1.', _XDN), _JOURNAL.format(V='0.', flip=False), _FIXED,
+                                        prop=_DH.format(bulk=0., C1='3.5e10') + "    thinning:\n        name: Eyring\n        tauE: 5.e5\n")),
+})
+VISC_CASES = ['cav1d_dukler', 'cav2d_mcadams', 'slider2d_barus', 'slider2d_barus_eyring',
+              'journal2d_roelands_carreau_slip', 'journal1d_eyring']
+
 
 def perturb(q, rho0, U, seed, rel_rho=1e-6):
     """Seeded perturbation of SURVEY 8(d): q0 *= 1 + 1e-6 N(0,1) (1e-4 makes |v| ~ 1e5 m/s with C1=3.5e10); q1, q2 += 1e-3 rho0 U N(0,1)."""

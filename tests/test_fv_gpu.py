@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 torch = pytest.importorskip("torch")
 
-from tests.cases import STEP_CASES, build_case, inputs  # noqa: E402
+from tests.cases import STEP_CASES, VISC_CASES, build_case, inputs  # noqa: E402
 
 REL_STEP = 1e-12
 REL_1000 = 1e-9
@@ -99,7 +99,8 @@ def test_step_vs_reference_golden(gs, name, arith):
     assert np.array_equal(s.get_q(), gs[f'{name}_q0'])
     sc = s.scalars()
     # BWR: pow/exp -> tolerance (see EOS test); fast arithmetic: tolerance by contract
-    exact = STEP_CASES[name]['yaml'].find('EOS: DH') >= 0 and arith == 'exact'
+    # viscosity modifiers: exp / pow / asinh / hypot -> tolerance in both contracts (include/gapflow_b200.h)
+    exact = STEP_CASES[name]['yaml'].find('EOS: DH') >= 0 and arith == 'exact' and name not in VISC_CASES
     dt0 = float(gs[f'{name}_dt0'])
     assert sc.dt == dt0 if exact else abs(sc.dt - dt0) <= 1e-12 * dt0
     for nsteps, tag in ((1, '1'), (2, '3')):
@@ -173,6 +174,118 @@ def test_closure_fields_match_oracle():
     assert np.array_equal(wxz, o.wall_xz)
     assert np.array_equal(wyz, o.wall_yz)
     assert np.array_equal(bulk, o.bulk)
+
+
+# ---- viscosity modifiers (stress.py:305-326, viscosity.py) -----------------------------
+def _maxrel(a, b):
+    return float(np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(b).max(), 1e-300))
+
+
+@pytest.mark.parametrize("arith", ARITH)
+@pytest.mark.parametrize("name", VISC_CASES)
+def test_viscosity_field_and_closures_vs_oracle(name, arith):
+    """The viscosity field the device builds before each pass, and the closure fields evaluated with it,
+    against the oracle (== the reference's piezoviscosity / shear_rate_avg / shear_thinning_factor chain,
+    tests/test_oracle_vs_reference.py).  Transcendentals: 1e-13 relative, every cell incl. ghosts."""
+    s, o = make_solver(name, arith=arith)
+    o.closures()
+    want = o.viscosity()
+    eta = s.viscosity()
+    assert eta.shape == want.shape
+    assert np.allclose(eta, want, rtol=1e-13, atol=0.0), (name, float(np.abs(eta / want - 1).max()))
+    assert np.ptp(want) > 0.0            # the case really has a non-uniform viscosity
+    p, wxz, wyz, bulk = s.closures()
+    assert _maxrel(p, o.pressure) <= 1e-13
+    for got, ref in ((wxz, o.wall_xz), (wyz, o.wall_yz), (bulk, o.bulk)):
+        assert np.array_equal(got == 0.0, ref == 0.0)
+        assert _maxrel(got, ref) <= 1e-12, (name, _maxrel(got, ref))
+
+
+@pytest.mark.parametrize("arith", ARITH)
+@pytest.mark.parametrize("name", VISC_CASES)
+def test_viscosity_cases_ten_steps_vs_oracle(name, arith):
+    """10 steps with the viscosity field against the oracle; the stale closure fields afterwards are those
+    of the last corrector pass's input (problem.py:532-540), viscosity included."""
+    s, o = make_solver(name, arith=arith)
+    for _ in range(10):
+        o.update()
+    s.step(10)
+    q = s.get_q()
+    assert relerr(q, o.q) <= REL_STEP * 10, (name, relerr(q, o.q))
+    assert abs(s.scalars().dt - o.dt) <= 1e-11 * o.dt
+    # ghost cells remain exact functions of the interior
+    ref = type(o).__new__(type(o))
+    ref.__dict__.update(o.__dict__)
+    ref.q = q.copy()
+    ref.fill_ghosts()
+    assert np.array_equal(ref.q, q)
+    # o.pressure / o.bulk are the corrector-pass fields of the last step (refreshed at the start of a pass only)
+    p, wxz, wyz, bulk = s.closures(stale=True)
+    # (the fields of the final q differ from these by ~10 %; 10 steps of 1e-12 in q are amplified by K/p ~ 1e5 in p)
+    assert _maxrel(p, o.pressure) <= 1e-6
+    assert _maxrel(bulk, o.bulk) <= 1e-6
+    assert _maxrel(wxz, o.wall_xz) <= 1e-6
+
+
+def test_viscosity_multi_tile_ragged_grid_vs_oracle():
+    """Barus + Eyring on an 83 x 150 grid (several tiles, ragged edges, D/N x-sides): np.gradient's one-sided
+    edge rows and the tile halos see every position; 4 steps."""
+    import copy
+    from gapflow_b200.fv import FVSolver
+    from oracle.fv import FVOracle
+    from tests.cases import perturb
+    d, _ = inputs('slider2d_barus_eyring')
+    d = copy.deepcopy(d)
+    g = d['grid']
+    g['Nx'], g['Ny'] = 83, 150
+    g['dx'], g['dy'] = g['Lx'] / 83, g['Ly'] / 150
+    o = FVOracle(g, d['geometry'], d['properties'], d['numerics'])
+    perturb(o.q, d['properties']['rho0'], abs(d['geometry']['U']), 4321)
+    o.fill_ghosts()
+    o.dt = d['numerics']['CFL'] * o.dt_crit
+    for arith in ARITH:
+        oo = copy.deepcopy(o)
+        s = FVSolver(g, d['geometry'], d['properties'], d['numerics'], topo=oo.topo, arith=arith)
+        s.set_q(oo.q)
+        s.pre_run(False)
+        oo.closures()
+        assert np.allclose(s.viscosity(), oo.viscosity(), rtol=1e-13, atol=0.0)
+        for k in range(4):
+            oo.update()
+            s.step(1)
+            assert relerr(s.get_q(), oo.q) <= REL_STEP * (k + 1), (arith, k, relerr(s.get_q(), oo.q))
+
+
+def test_viscosity_requires_set_viscosity_and_identity_law():
+    """cfg.visc_field without gpf_fv_set_viscosity is a call-sequence error, not a Newtonian run; a block
+    with an unknown law name is the identity (viscosity.py:64, 94) and reproduces the Newtonian step."""
+    import copy
+    import ctypes as C
+    from gapflow_b200 import _capi
+    from gapflow_b200.fv import FVSolver
+    d, _ = inputs('journal2d_periodic')
+    o = build_case('journal2d_periodic')
+    prop = copy.deepcopy(d['properties'])
+    prop['piezo'] = {'name': 'none'}
+    s = FVSolver(d['grid'], d['geometry'], prop, d['numerics'], topo=o.topo)
+    s.set_q(o.q)
+    s.pre_run(False)
+    s.step(3)
+    s0, _ = make_solver('journal2d_periodic')
+    s0.step(3)
+    assert np.array_equal(s.get_q(), s0.get_q())
+    assert np.array_equal(s.viscosity(), np.full(s.shape, prop['shear']))
+    # raw handle without the set-up call
+    lib = _capi.load()
+    cfg = _capi.make_cfg(d['grid'], d['geometry'], prop, d['numerics'])
+    n = C.c_size_t()
+    _capi.check(lib.gpf_fv_workspace_bytes(C.byref(cfg), C.byref(n)))
+    ws = torch.empty(n.value, dtype=torch.uint8, device='cuda')
+    h = C.c_void_p()
+    _capi.check(lib.gpf_fv_create(C.byref(cfg), C.c_void_p(ws.data_ptr()), n.value, C.byref(h)))
+    assert lib.gpf_fv_step(h, 1, 0, None) == _capi.GPF_E_STATE
+    assert b'gpf_fv_set_viscosity' in lib.gpf_last_error()
+    lib.gpf_fv_destroy(h)
 
 
 def test_fill_ghosts_and_host_update():
