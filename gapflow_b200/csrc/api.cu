@@ -197,6 +197,13 @@ int gpf_fv_reduce_local(gpf_fv* s, int kind, double* rec5, void* stream) {
 int gpf_fv_finish(gpf_fv* s, int mode, const double* recs, int nrec, void* stream) {
     GPF_TRY NEED(s) return s->S.finish(mode, recs, nrec, (cudaStream_t)stream); GPF_CATCH
 }
+int gpf_fv_set_surrogate(gpf_fv* s, const double* pressure, double pressure_scale, const double* shear_xz,
+                         double shear_xz_scale, const double* shear_yz, double shear_yz_scale) {
+    GPF_TRY NEED(s) return s->S.set_surrogate(pressure, pressure_scale, shear_xz, shear_xz_scale, shear_yz, shear_yz_scale); GPF_CATCH
+}
+int gpf_fv_finish_surrogate(gpf_fv* s, int mode, double* rec5, double c2, void* stream) {
+    GPF_TRY NEED(s) return s->S.finish_surrogate(mode, rec5, c2, (cudaStream_t)stream); GPF_CATCH
+}
 int gpf_fv_set_timing(gpf_fv* s, int enable) {
     GPF_TRY NEED(s) s->S.timing = enable != 0; s->S.ev_steps = 0; return GPF_OK; GPF_CATCH
 }
@@ -319,6 +326,9 @@ int gpf_gp_mean_var(gpf_gp* g, const double* Xtest, int64_t N, const double* noi
 }
 int gpf_gp_features(gpf_fv* s, const double* x_scale, const int32_t* active_dims, int D, double* X, void* stream) {
     GPF_TRY NEED(s && x_scale && active_dims && X) return launch_gp_features(s->S, x_scale, active_dims, D, X, (cudaStream_t)stream); GPF_CATCH
+}
+int gpf_gp_features_of(gpf_fv* s, int rel, const double* x_scale, const int32_t* active_dims, int D, double* X, void* stream) {
+    GPF_TRY NEED(s && x_scale && active_dims && X) return launch_gp_features(s->S, x_scale, active_dims, D, X, (cudaStream_t)stream, rel); GPF_CATCH
 }
 
 int gpf_selftest_division(uint64_t n, uint64_t seed, uint64_t mismatches[2], void* stream) {

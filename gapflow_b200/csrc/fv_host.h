@@ -41,6 +41,14 @@ struct FvSolver {
     int set_viscosity(int piezo, const double* pp, int thin, const double* tp, const double* x, const double* y);
     int launch_viscosity(int rel, cudaStream_t s);
     int viscosity(int which, double* out, int on_device, cudaStream_t s);
+    // GP surrogate closures (gpf_fv_set_surrogate): normalised predictive means of the pass's input, dense
+    // over the padded array; null = the fixed-form law
+    const double* sg_p = nullptr;    // (Np)
+    const double* sg_xz = nullptr;   // (2, Np): lower, upper wall
+    const double* sg_yz = nullptr;
+    double sg_scale[3] = {1.0, 1.0, 1.0};
+    int set_surrogate(const double* p, double ps, const double* xz, double xzs, const double* yz, double yzs);
+    int finish_surrogate(int mode, double* rec5, double c2, cudaStream_t s);
     DevState* st;
     Partial* partial;
     int* pflags;
@@ -109,6 +117,11 @@ struct PassArgs {
     int ntiles;                // tiles of this launch (virtual index t -> tile row (t / nty) * bx_mul + bx_off)
     int bx_mul, bx_off;
     int rec0;                  // first record slot of this launch
+    // surrogate variant only (SG): GP means replacing the pressure / the own shear component of the wall stresses
+    const double* sg_p;
+    const double* sg_xz;
+    const double* sg_yz;
+    double sg_scale[3];
 };
 
 // parameter packing shared with the pure-function entry points

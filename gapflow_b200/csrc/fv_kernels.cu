@@ -1099,6 +1099,8 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     }
     A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags; A.redo = S.redo;
     A.until_converged = until_converged;
+    A.sg_p = S.sg_p; A.sg_xz = S.sg_xz; A.sg_yz = S.sg_yz;
+    for (int k = 0; k < 3; ++k) A.sg_scale[k] = S.sg_scale[k];
     // INTERIOR leaves a few CTA slots empty so that the exchange kernels of the side stream (pack,
     // send, receive) find room beside the persistent CTAs (GPF_INTERIOR_SLACK, default 2)
     static const int slack = [] { const char* e = getenv("GPF_INTERIOR_SLACK"); return e ? atoi(e) : 2; }();
@@ -1121,7 +1123,8 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, vf, n, s)
                                                    : launch_pass_exact(A, CORR, ls, dh, xf, vf, n, s);
     if (rc) return rc;
-    g_launches += 2;           // straight-line kernel + general kernel (returns at once unless flagged)
+    // straight-line kernel + general kernel (returns at once unless flagged); surrogate variant: the general kernel alone
+    g_launches += (S.sg_p || S.sg_xz || S.sg_yz) ? 1 : 2;
     return debug_check(CORR ? "fv_pass_kernel<corrector>" : "fv_pass_kernel<predictor>", s);
 }
 
@@ -1145,6 +1148,11 @@ static int launch_reduce(FvSolver& S, cudaStream_t s) {
 
 int FvSolver::step(int n, int until_converged, cudaStream_t s) {
     if (n < 0) { set_error("n < 0"); return GPF_E_INVALID; }
+    if (sg_p || sg_xz || sg_yz) {
+        set_error("gpf_fv_step: surrogate closures are set; the GP means must be refreshed before every pass "
+                  "(drive gpf_fv_pass / gpf_fv_reduce_local / gpf_fv_finish_surrogate)");
+        return GPF_E_INVALID;
+    }
     const int nblk = P.ncta;               // = nrec_corr of an unsplit corrector launch
     if (timing) {
         while ((int)ev.size() < 3 * n + 1) { cudaEvent_t e; GPF_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
@@ -1255,6 +1263,41 @@ int FvSolver::finish(int mode, const double* recs, int nrec, cudaStream_t s) {
     if (mode != FIN_REFRESH) dirty_scalars = false;
     else refresh_valid = true;
     return GPF_OK;
+}
+
+// ---- GP surrogate closures (stress.py:346-356, 614-620) -------------------------------------
+int FvSolver::set_surrogate(const double* p, double ps, const double* xz, double xzs, const double* yz, double yzs) {
+    if ((p || xz || yz) && P.visc_field) {
+        set_error("gpf_fv_set_surrogate: a solver with viscosity modifiers has no surrogate variant");
+        return GPF_E_INVALID;
+    }
+    if ((p || xz || yz) && (P.bc.type[0][0] == GPF_BC_HALO || P.bc.type[1][0] == GPF_BC_HALO)) {
+        set_error("gpf_fv_set_surrogate: slab solvers take the GP means of their own rows only through a "
+                  "single-domain solver (query cells are partitioned, the FV step is not)");
+        return GPF_E_INVALID;
+    }
+    sg_p = p; sg_xz = xz; sg_yz = yz;
+    sg_scale[0] = ps; sg_scale[1] = xzs; sg_scale[2] = yzs;
+    return GPF_OK;
+}
+
+// rec5[2] (max c^2) <- c2 when the pressure is a GP (Pressure.v_sound, stress.py:522-537); the flag of
+// an undefined analytic sound speed is replaced by that of c2
+__global__ void fv_record_c2_kernel(double* rec5, double c2) {
+    rec5[2] = c2;
+    int f = (int)rec5[4] & ~FLAG_CNAN;
+    if (!(c2 >= 0.0)) f |= FLAG_CNAN;       // sqrt of a negative slope is NaN (stress.py:535)
+    rec5[4] = (double)f;
+}
+
+int FvSolver::finish_surrogate(int mode, double* rec5, double c2, cudaStream_t s) {
+    if (!rec5) { set_error("rec5 is NULL"); return GPF_E_INVALID; }
+    if (sg_p) {
+        fv_record_c2_kernel<<<1, 1, 0, s>>>(rec5, c2);
+        g_launches++;
+        GPF_CUDA(cudaGetLastError());
+    }
+    return finish(mode, rec5, 1, s);
 }
 
 // ---- peer-memory exchange (slab_comm.cuh) --------------------------------------------------

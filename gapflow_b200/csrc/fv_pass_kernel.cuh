@@ -123,14 +123,19 @@ __device__ __noinline__ Clos4 phase1_cell_slow(const Cell c, const FvParams& P, 
 
 struct Nb { double q1x, Ax, t2x, q2y, t2y, Cy; };   // neighbour fluxes: Fx = (q1, A, t2), Fy = (q2, t2, C)
 struct Q3 { double v0, v1, v2; };
+// GP surrogate (SG variant): predictive means that replace the own shear component of the wall stresses
+// (stress.py:350-356: field[_out_index] = mean[0], field[_out_index + 6] = mean[1]); mask bit 0: xz model,
+// bit 1: yz model
+struct SgWall { double lo_xz, up_xz, lo_yz, up_yz; unsigned mask; };
 
 // fluxes (integrate.py:65-75), wall stresses (stress.py:328-362), source (integrate.py:118-128)
 // and the update q - dt*(fX/dx + fY/dy - src) (problem.py:558) of one interior cell.
 // flux = -d*(F[nb] - F[own]): the sign flip is exact and done on the integer pipe.  The xz + yz
 // field sums of problem.py:554-555 are u/2 + u/2 == u (exact) and u + 0.
-template <bool LS, bool FAST, bool XF, bool VF = false>
+template <bool LS, bool FAST, bool XF, bool VF = false, bool SG = false>
 __device__ __forceinline__ Q3 phase2_cell(const Cell& c, const Clos4& k, const Nb& n, const FvParams& P,
-                                          unsigned sbit, double dt, double eta = 0.0) {
+                                          unsigned sbit, double dt, double eta = 0.0, const SgWall* sg = nullptr) {
+    static_assert(!SG || !FAST, "the surrogate variant runs the plain-division path");
     static_assert(!VF || LS, "the viscosity-field variants use the general (slip-length) closures");
     Visc Vcell;
     if constexpr (VF) Vcell = cell_visc<true>(P, eta);
@@ -181,6 +186,10 @@ __device__ __forceinline__ Q3 phase2_cell(const Cell& c, const Clos4& k, const N
     double b3, b4, u[6];
     stress_bottom<LS, FAST, XF>(c, V, b3, b4);
     stress_top<LS, false, FAST, XF>(c, V, u);
+    if constexpr (SG) {
+        if (sg->mask & 1u) { b4 = sg->lo_xz; u[4] = sg->up_xz; }
+        if (sg->mask & 2u) { b3 = sg->lo_yz; u[3] = sg->up_yz; }
+    }
     const double rh = rcp_sel<FAST>(c.h);
     double s0, s1, s2;
     if constexpr (XF) {      // hy == 0: the hy terms are exact zeros
@@ -202,6 +211,11 @@ template <bool LS, bool VF = false>
 __device__ __noinline__ Q3 phase2_cell_slow(const Cell c, const Clos4 k, const Nb n, const FvParams& P,
                                             unsigned sbit, double dt, double eta = 0.0) {
     return phase2_cell<LS, false, false, VF>(c, k, n, P, sbit, dt, eta);
+}
+template <bool LS>
+__device__ __noinline__ Q3 phase2_cell_sg(const Cell c, const Clos4 k, const Nb n, const FvParams& P,
+                                          unsigned sbit, double dt, const SgWall sg) {
+    return phase2_cell<LS, false, false, false, true>(c, k, n, P, sbit, dt, 0.0, &sg);
 }
 
 // exact flags of one stored cell, off the hot path (problem.py:320-332)
@@ -226,8 +240,14 @@ __device__ __noinline__ int cell_flags_slow(double a, double b, double c, double
 //                plain IEEE divisions, exact validity flags).  Returns at once unless A.redo[CORR] is
 //                raised, else recomputes the whole pass: a pass reads only buffers it does not write.
 // Each GEN = false launch lowers the other pass's flag; a stale raised flag only costs time.
-template <bool CORR, bool LS, int EOS, bool XF, bool GEN, bool VF = false>
+//
+// SG = true (GP surrogate closures, gpf_fv_set_surrogate): only the general kernel is launched and every
+// tile takes the plain-division path; the pressure of a staged cell and the own shear component of the
+// wall stresses come from the GP means of the pass's input (dense arrays over the padded grid, row
+// i*(Ny+2)+j like gp.py:223-232 orders them) times the model's Yscale (gp.py:362).
+template <bool CORR, bool LS, int EOS, bool XF, bool GEN, bool VF = false, bool SG = false>
 __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kernel(const __grid_constant__ PassArgs A) {
+    static_assert(!SG || (GEN && LS && !XF && !VF && EOS == -1), "surrogate variant: general kernel, general closures");
     constexpr int NST = fv_nstage(CORR);
     using S = Smem<CORR, LS, XF, NST, VF>;
     extern __shared__ __align__(1024) unsigned char smem[];      // no static shared memory: offset 0
@@ -243,7 +263,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     const DevState* st = A.st;
     // run-loop condition (problem.py:401) evaluated on the device; uniform per grid
     if (st->stop || (A.until_converged && st->halt)) return;
-    if (GEN && A.redo[CORR] == 0) return;
+    if (GEN && !SG && A.redo[CORR] == 0) return;
 
     const int tid = threadIdx.x;
     const int cur = st->cur;
@@ -388,7 +408,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         } else {
             const Cell ca = load_cell(o_own), cb = load_cell(o_own + BY);
             const double ea = load_eta(o_own), eb = load_eta(o_own + BY);
-            const bool ok = q_in_fast_range(ca) & q_in_fast_range(cb) & eta_ok(ea) & eta_ok(eb);
+            const bool ok = !SG & q_in_fast_range(ca) & q_in_fast_range(cb) & eta_ok(ea) & eta_ok(eb);
             if (__all_sync(0xffffffffu, ok) && P.static_fast) {   // warp-uniform
                 store_clos(o_own, phase1_cell<LS, EOS, true, XF, VF>(ca, P, ea));
                 store_clos(o_own + BY, phase1_cell<LS, EOS, true, XF, VF>(cb, P, eb));
@@ -401,17 +421,32 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         if (GEN && has_halo) {
             const Cell ch = load_cell(o_halo);
             const double eh = load_eta(o_halo);
-            if (__all_sync(0xffffffffu, q_in_fast_range(ch) & eta_ok(eh)) && P.static_fast) {
+            if (__all_sync(0xffffffffu, !SG & q_in_fast_range(ch) & eta_ok(eh)) && P.static_fast) {
                 store_clos(o_halo, phase1_cell<LS, EOS, true, XF, VF>(ch, P, eh));
             } else {
                 store_clos(o_halo, phase1_cell_slow<LS, EOS, VF>(ch, P, eh));
                 sbad[fl] = 1;
             }
         }
+        if constexpr (SG) {
+            // the GP pressure of every staged cell that lies inside the padded array (the others are
+            // neighbours of cells that are neither stored nor counted)
+            if (A.sg_p) {
+                const int io = 1 + (bx * bx_mul + bx_off) * TX - ox, jo = 1 + by * TY - oy;   // cell of box offset 0
+                auto put = [&](int o) {
+                    const int r = o / BY, i = io + r, j = jo + (o - r * BY);
+                    if (i >= 0 && i <= Nx + 1 && j >= 0 && j <= Ny + 1)
+                        sp[o] = A.sg_p[(size_t)i * (Ny + 2) + j] * A.sg_scale[0];
+                };
+                put(o_own);
+                put(o_own + BY);
+                if (has_halo) put(o_halo);
+            }
+        }
         __syncthreads();
 
         // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
-        const bool fast = !GEN || ((sbad[fl] == 0) && dt_fast);                    // tile-uniform
+        const bool fast = !SG && (!GEN || ((sbad[fl] == 0) && dt_fast));           // tile-uniform
         if (GEN && tid == 0) sbad[fl ^ 1] = 0;                                      // next tile's flag
         const int rbx = bx * bx_mul + bx_off;                                      // tile row in the grid
         const int i0 = 1 + rbx * TX, j0 = 1 + by * TY;
@@ -428,6 +463,18 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             nb.q1x = sq[BOX + o + on_dx]; nb.Ax = sp[o + on_dx] + st0[o + on_dx]; nb.t2x = st2[o + on_dx];
             nb.q2y = sq[2 * BOX + o + on_dy]; nb.t2y = st2[o + on_dy]; nb.Cy = sp[o + on_dy] + st1[o + on_dy];
             const double e = load_eta(o);
+            if constexpr (SG) {
+                SgWall w;
+                w.mask = (A.sg_xz ? 1u : 0u) | (A.sg_yz ? 2u : 0u);
+                w.lo_xz = w.up_xz = w.lo_yz = w.up_yz = 0.0;
+                const int i = 1 + (bx * bx_mul + bx_off) * TX + 2 * g + k, j = 1 + by * TY + ty;
+                if (i <= Nx && j <= Ny) {
+                    const size_t np = (size_t)(Nx + 2) * (Ny + 2), a = (size_t)i * (Ny + 2) + j;
+                    if (A.sg_xz) { w.lo_xz = A.sg_xz[a] * A.sg_scale[1]; w.up_xz = A.sg_xz[np + a] * A.sg_scale[1]; }
+                    if (A.sg_yz) { w.lo_yz = A.sg_yz[a] * A.sg_scale[2]; w.up_yz = A.sg_yz[np + a] * A.sg_scale[2]; }
+                }
+                return phase2_cell_sg<LS>(c, kk, nb, P, sbit, dt, w);
+            } else
             if constexpr (GEN) {
                 return fast ? phase2_cell<LS, true, XF, VF>(c, kk, nb, P, sbit, dt, e)
                             : phase2_cell_slow<LS, VF>(c, kk, nb, P, sbit, dt, e);
@@ -582,9 +629,23 @@ static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
     return GPF_OK;
 }
 
+// surrogate variant: the general kernel alone
+template <bool CORR>
+static int launch_pass_surrogate(const PassArgs& A, int ncta, cudaStream_t s) {
+    using Sm = Smem<CORR, true, false, fv_nstage(CORR), false>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, true, -1, false, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        attr_set = true;
+    }
+    fv_pass_kernel<CORR, true, -1, false, true, false, true><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    return GPF_OK;
+}
+
 // variant dispatch: slip-length field, Dowson-Higginson inlined, x-driven film, viscosity field
 template <bool CORR>
 int launch_pass_dispatch(const PassArgs& A, bool ls, bool dh, bool xf, bool vf, int n, cudaStream_t s) {
+    if (A.sg_p || A.sg_xz || A.sg_yz) return launch_pass_surrogate<CORR>(A, n, s);
     // viscosity field (piezo / thinning): one variant, the general closures with the slip-length plane
     // (zeros when the configuration has none: the LS forms with Ls = 0 round like the reference's)
     if (vf) return launch_pass_variant<CORR, true, -1, false, true>(A, n, s);

@@ -40,6 +40,6 @@ struct GpModel {
                  double* var_out, double* vmax_host, long long* imax_host, cudaStream_t s);
 };
 
-int launch_gp_features(FvSolver& S, const double* x_scale7, const int* dims, int D, double* X, cudaStream_t s);
+int launch_gp_features(FvSolver& S, const double* x_scale7, const int* dims, int D, double* X, cudaStream_t s, int rel = 0);
 
 }  // namespace gpf

@@ -919,8 +919,9 @@ int GpModel::mean_var(const double* Xtest, long long N, const double* noise, dou
     return GPF_OK;
 }
 
-int launch_gp_features(FvSolver& S, const double* x_scale7, const int* dims, int D, double* X, cudaStream_t s) {
+int launch_gp_features(FvSolver& S, const double* x_scale7, const int* dims, int D, double* X, cudaStream_t s, int rel) {
     if (D < 1 || D > GP_MAXD) { set_error("1 <= D <= 8"); return GPF_E_INVALID; }
+    if (rel < 0 || rel > 2) { set_error("rel must be 0, 1 or 2"); return GPF_E_INVALID; }
     FeatArgs fa;
     fa.D = D;
     for (int k = 0; k < D; ++k) {
@@ -933,7 +934,7 @@ int launch_gp_features(FvSolver& S, const double* x_scale7, const int* dims, int
     if (rc) return rc;
     const int Nx2 = S.cfg.Nx + 2, Ny2 = S.cfg.Ny + 2;
     const size_t np = (size_t)Nx2 * Ny2;
-    gp_features_kernel<<<(int)((np + 255) / 256), 256, 0, s>>>(S.qbuf[cur], S.topo, S.extra, S.P.L.plane, S.P.L.pitch, Nx2, Ny2,
+    gp_features_kernel<<<(int)((np + 255) / 256), 256, 0, s>>>(S.qbuf[(cur + rel) % 3], S.topo, S.extra, S.P.L.plane, S.P.L.pitch, Nx2, Ny2,
                                                              fa, X);
     g_launches++;
     GPF_CUDA(cudaGetLastError());

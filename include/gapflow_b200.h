@@ -228,6 +228,31 @@ int gpf_fv_reduce_local(gpf_fv* s, int kind, double* rec5, void* stream);
  * of the current q (GPF_FIN_REFRESH) */
 int gpf_fv_finish(gpf_fv* s, int mode, const double* recs, int nrec, void* stream);
 
+/* --- GP surrogate closures in the FV step (GaPFlow/models/stress.py:346-356, 614-620) ---------
+ * With a GP model the reference replaces, at the start of each pass, the pressure field by the GP
+ * mean (Pressure.update) and the own shear component of both wall-stress fields by the two outputs
+ * of the shear GP (WallStress.update: field[_out_index] = mean[0] lower wall, field[_out_index + 6] =
+ * mean[1] upper wall; _out_index = 4 (xz model), 3 (yz model)); everything else stays fixed-form.
+ * gpf_fv_set_surrogate hands the pass kernels the NORMALISED predictive means (what gpf_gp_mean /
+ * gpf_gp_mean_var write) and the model's Yscale (gp.py:362: mean * Yscale): pressure (Np), shear_xz
+ * and shear_yz (2, Np), device arrays over the padded grid in the row order of gpf_gp_features,
+ * Np = (Nx+2)(Ny+2); NULL keeps the fixed-form law for that quantity; all NULL returns the solver
+ * to its fixed-form kernels.  The arrays are read when a pass RUNS: the caller refreshes them from
+ * the pass's input before each pass (rel = 0 predictor, 1 corrector in gpf_gp_features_of) and
+ * drives one Problem.update() as
+ *   features_of(0) -> gp_mean[_var] -> pass(0);  features_of(1) -> gp_mean -> pass(1);
+ *   reduce_local(0, rec5);  features_of(2) -> gp_mean(..., &g);  finish_surrogate(GPF_FIN_STEP, rec5, c2)
+ * gpf_fv_step is refused while surrogate arrays are set.  The surrogate passes run the general
+ * kernel with plain IEEE divisions (tolerance contract of the GP path: 1e-9). */
+int gpf_fv_set_surrogate(gpf_fv* s, const double* pressure, double pressure_scale,
+                         const double* shear_xz, double shear_xz_scale,
+                         const double* shear_yz, double shear_yz_scale);
+/* gpf_fv_finish for one record (device, in/out) after replacing its max c^2 by `c2` when a pressure
+ * GP is set: Pressure.v_sound's GP branch (stress.py:522-537), c2 = max_i d mean / d x_0 * Yscale /
+ * X_scale[0] with the maximum from gpf_gp_mean(..., dmean_dx0_max).  mode as gpf_fv_finish
+ * (GPF_FIN_PRERUN after reduce_local(1, rec5) reproduces _pre_run's dt = CFL * dt_crit). */
+int gpf_fv_finish_surrogate(gpf_fv* s, int mode, double* rec5, double c2, void* stream);
+
 /* --- pure functions (GaPFlow/models/*.py, GaPFlow/integrate.py); device pointers ---- */
 /* eos_pressure(density, prop) -> pressure.py:35;  eos_sound_velocity -> sound.py:35 */
 int gpf_eos_pressure(const gpf_fv_cfg* cfg, const double* dens, double* out, size_t n, void* stream);
@@ -307,6 +332,11 @@ int gpf_gp_mean_var(gpf_gp* g, const double* Xtest, int64_t N, const double* noi
  * active_dims[k] of [rho, jx, jy, h, dh/dx, dh/dy, extra] divided by x_scale[active_dims[k]].
  * x_scale (7) and active_dims (D) are host arrays. */
 int gpf_gp_features(gpf_fv* s, const double* x_scale, const int32_t* active_dims, int D, double* X, void* stream);
+/* the same of buffer `rel`: 0 the current q, 1 the predictor's output (the corrector pass's input), 2 the
+ * corrector's output before gpf_fv_finish made it current (q = (q + q0)/2, ghosts filled: the field
+ * _post_update evaluates v_sound on, problem.py:571-586) */
+int gpf_gp_features_of(gpf_fv* s, int rel, const double* x_scale, const int32_t* active_dims, int D, double* X,
+                       void* stream);
 
 /* --- instrumentation ------------------------------------------------------------- */
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
