@@ -96,9 +96,14 @@ class _BulkStress(_Closure):
 
 
 class Problem:
-    def __init__(self, options, grid, numerics, prop, geo, gp=None, database=None, extra=None):
-        if gp is not None or database is not None:
-            raise NotImplementedError("GP surrogate orchestration stays on the host (use gapflow_b200.gp.GPModel)")
+    def __init__(self, options, grid, numerics, prop, geo, gp=None, database=None, extra=None, extra_field=None):
+        if extra is None:
+            extra = extra_field                                        # the reference's keyword (problem.py:85)
+        if gp is not None and database is None:
+            raise ValueError("a GP configuration needs a Database (gapflow_b200.surrogate.Database)")
+        if database is not None and not database.has_mock_md:        # problem.py:110-113
+            prop['shear'] = 0.
+            prop['bulk'] = 0.
         if prop.get('elastic', {}).get('enabled', False):
             raise NotImplementedError("elastic deformation (ContactMechanics) stays on the host")
         self.options, self.grid, self.numerics, self.prop, self.geo = options, grid, numerics, prop, geo
@@ -106,6 +111,12 @@ class Problem:
         shape = (grid['Nx'] + 2, grid['Ny'] + 2)
         self._extra = None if extra is None else np.broadcast_to(np.asarray(extra, dtype=float), (1, *shape)).copy()
         self._solver = FVSolver(grid, geo, prop, numerics, topo=self.topo.full, extra=self._extra)
+        self.has_gp_model = gp is not None
+        self._sur = None
+        if gp is not None:
+            from .surrogate import SurrogateDriver
+            self._sur = SurrogateDriver(self._solver, gp, database, grid['dim'], write_freq=options['write_freq'])
+        self.database = database
         self._q_host = np.empty((3, *shape))
         self._q_synced = False       # _q_host equals the device field
         self._q_exposed = False      # user code may have edited _q_host
@@ -140,8 +151,17 @@ class Problem:
 
     @classmethod
     def _from_dict(cls, d):
+        # problem.py:207-249: a db section builds the Database around the mock MD (md section absent) --
+        # LAMMPS runners (md section present) stay with the reference
+        gp, db, database = d.get('gp'), d.get('db'), None
+        if db is not None:
+            if d.get('md') is not None:
+                raise NotImplementedError("LAMMPS MD runners are out of scope (host-side, GaPFlow/md); pass a "
+                                          "Database built around your own runner to Problem(...)")
+            from .surrogate import Database, Mock
+            database = Database(Mock(d['properties'], d['geometry'], gp), db)
         return cls(d['options'], d['grid'], d['numerics'], d['properties'], d['geometry'],
-                   gp=d.get('gp'), database=None)
+                   gp=gp, database=database)
 
     # -- state ------------------------------------------------------------------------------
     @property
@@ -188,6 +208,9 @@ class Problem:
         self._push_dt()
         return self._solver.scalars()
 
+    # GP models of the reference's sub-objects (problem.py:141-146); None for a fixed-form law
+    gp_models = property(lambda self: {} if self._sur is None else self._sur.models)
+
     def _pull(self, sc=None):
         sc = sc or self._solver.scalars()
         self.step, self.simtime, self.residual = int(sc.step), sc.simtime, sc.residual
@@ -201,6 +224,8 @@ class Problem:
         if self._clos_cache is None:
             self._sync_to_device()
             self._clos_cache = self._solver.closures(stale=bool(self.step))
+            if self._sur is not None and self._sur.ready:
+                self._clos_cache = self._sur.closures(self._clos_cache)
         return self._clos_cache
 
     mass = property(lambda self: (self._sync_to_device(), np.float64(self._solver.mass))[1])
@@ -217,7 +242,15 @@ class Problem:
     def _pre_run(self):
         """problem.py:412-443 (fixed-form branch)."""
         self._sync_to_device()
-        self._solver.pre_run(reset_ekin_old=False)
+        if self._sur is not None:
+            if self.outdir is not None:
+                self.database.output_path = self.outdir
+            self._sur.pre_run()
+            if not self.options['silent']:
+                for m in self._sur.models.values():
+                    m.write()
+        else:
+            self._solver.pre_run(reset_ekin_old=False)
         self._pull()
 
     def update(self):
@@ -226,7 +259,10 @@ class Problem:
             self._pre_run()
         self._sync_to_device()
         self._push_dt()
-        self._solver.step(1)
+        if self._sur is not None:
+            self._sur.update(self.step)
+        else:
+            self._solver.step(1)
         self._q_synced, self._clos_cache = False, None
         sc = self._pull()
         if sc.stop and not self.options['silent']:
@@ -251,8 +287,12 @@ class Problem:
             while not self.converged and self.step < self.max_it and not self._stop:
                 self._sync_to_device()
                 self._push_dt()
-                n = wf - self.step % wf                       # up to the next multiple of write_freq
-                self._solver.step(n, until_converged=True)    # loop condition evaluated on the device
+                if self._sur is not None:
+                    # every pass needs fresh GP means (and, with active learning, host decisions)
+                    self._sur.update(self.step)
+                else:
+                    n = wf - self.step % wf                       # up to the next multiple of write_freq
+                    self._solver.step(n, until_converged=True)    # loop condition evaluated on the device
                 self._q_synced, self._clos_cache = False, None
                 self._pull()
                 if self.step % wf == 0 and not silent:
@@ -284,6 +324,14 @@ class Problem:
                 w = csv.writer(f)
                 w.writerow(list(self.history))
                 w.writerows(zip(*self.history.values()))
+            for k, m in self.gp_models.items():               # problem.py:486-503: gp_zz.csv, gp_xz.csv, gp_yz.csv
+                with open(os.path.join(self.outdir, f'gp_{k}.csv'), 'w', newline='') as f:
+                    w = csv.writer(f)
+                    w.writerow(list(m.history))
+                    w.writerows(zip(*m.history.values()))
+                with open(os.path.join(self.outdir, f'gp_{k}.txt'), 'w') as f:
+                    print(f"GaussianProcess(kernel={m.kernel_variance!r} * Linear(scale={m.kernel_lengthscale!r}, "
+                          f"Matern32(L2Distance)), M={m.gp.M}, diag={m.Yerr**2!r})", file=f)
 
     # -- output (problem.py:154-205, 616-637) ---------------------------------------------------
     def _open_output(self):
