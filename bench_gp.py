@@ -54,6 +54,8 @@ def main():
     ap.add_argument("--N", type=int, default=1026 * 1026)
     ap.add_argument("--var-sample", type=int, default=32768)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--coupled-n", type=int, default=1024, help="cells per side of the GP-coupled FV step (0: skip)")
+    ap.add_argument("--coupled-steps", type=int, default=3)
     args = ap.parse_args()
     import numpy as np
     import torch
@@ -114,7 +116,88 @@ def main():
         out["models"][name] = res
         del g
     out["value"] = out["models"]["pressure"]["mean"]["value"]
+    if args.coupled_n > 0:
+        out["coupled_step"] = coupled_step(torch, np, lib, args)
     print(json.dumps(out))
+
+
+COUPLED_YAML = """
+options: {{output: /tmp/gpf_bench, write_freq: 1000000, use_tstamp: False, silent: True}}
+grid: {{Lx: 1470., Ly: 1470., Nx: {n}, Ny: {n}, xE: ['P','P','P'], xW: ['P','P','P'], yS: ['P','P','P'], yN: ['P','P','P']}}
+geometry: {{type: journal, hmin: 10., hmax: 14., U: 0.12, V: 0.02}}
+numerics: {{CFL: 0.4, adaptive: 1, tol: 1e-8, dt: 0.1, max_it: 1000000}}
+properties: {{shear: 2.15, bulk: 0.5, EOS: BWR, T: 1.0, rho0: 0.8}}
+gp:
+  press: {{atol: 1., rtol: 0., obs_stddev: 2.e-2, active_learning: False, active_dims: [0]}}
+  shear: {{atol: 1., rtol: 0., obs_stddev: 4.e-3, active_learning: False, active_dims: {{x: [0, 1, 6], y: [0, 2, 6]}}}}
+db: {{init_size: {M}, init_method: lhc, init_width: 0.02}}
+"""
+
+
+def _coupled_inputs(np, n, M):
+    from gapflow_b200 import config
+    d = config.read_yaml_string(COUPLED_YAML.format(n=n, M=M))
+    i = (np.arange(n + 2) - 0.5) / n
+    extra = (0.5 + 0.4 * np.sin(2 * np.pi * i)[:, None] * np.cos(2 * np.pi * i)[None, :])[None]
+    return d, extra
+
+
+def _fixed_hyper(model):
+    import numpy as np
+    return 0.0, np.log(np.std(np.asarray(model.Xtrain), axis=0))       # params_init (stress.py:281-284)
+
+
+def coupled_step(torch, np, lib, args):
+    """One Problem.update() with all three GP models (slip_2d_lj_mock.py scaled: BASELINE config 4): per pass the
+    feature matrices, three predictive means over every padded cell and the surrogate pass kernel; then the
+    GP sound speed.  Active learning off, hyperparameters = params_init (no optimiser in the timed region)."""
+    from gapflow_b200.fv import FVSolver
+    from gapflow_b200.surrogate import Database, Mock, SurrogateDriver
+    n, M = args.coupled_n, args.M
+    d, extra = _coupled_inputs(np, n, M)
+    from gapflow_b200.topography import make_topography
+    topo = make_topography(d['grid'], d['geometry'])
+    s = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, extra=extra, arith='fast')
+    db = Database(Mock(d['properties'], d['geometry'], d['gp'], draws=(0.3, -0.3, 0.5)), d['db'])
+    drv = SurrogateDriver(s, d['gp'], db, 2, write_freq=10**9, optimizer=_fixed_hyper)
+    t0 = time.perf_counter()
+    drv.pre_run()                                # initial design (M mock-MD rows), 3 factorisations, first inference
+    torch.cuda.synchronize()
+    t_pre = time.perf_counter() - t0
+    l0 = lib.gpf_launch_count()
+    drv.update(0)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(args.coupled_steps):
+        drv.update(1 + k)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.coupled_steps
+    launches = (lib.gpf_launch_count() - l0) // (args.coupled_steps + 1)
+    sc = s.scalars()
+    Np = (n + 2) * (n + 2)
+    res = {"workload": f"2D journal film {n}x{n}, BWR fluid, pressure + shear-x + shear-y GP (D = 1, 3, 3) on M = {db.size} "
+                       "mock-MD points, active learning off",
+           "ms_per_step": ms, "cell_updates_per_s": n * n / (ms * 1e-3),
+           "gp_predictions_per_step": 7 * Np, "gp_predictions_per_s": 7 * Np / (ms * 1e-3),
+           "kernel_evals_per_s": 7.0 * Np * db.size / (ms * 1e-3),
+           "pre_run_s": t_pre, "gpu_launches_per_step": int(launches), "final": {"step": int(sc.step), "dt": sc.dt}}
+    if not args.no_cpu:
+        from oracle import surrogate as OS
+        nc = 104                                      # (nc + 2)^2 >= M: the design picks M distinct cells (db.py:329)
+        dc, ec = _coupled_inputs(np, nc, M)
+        odb = OS.Database(OS.MockMD(dc['properties'], dc['geometry'], dc['gp'], draws=(0.3, -0.3, 0.5)), dc['db'])
+        o = OS.SurrogateFVOracle(dc['grid'], dc['geometry'], dc['properties'], dc['numerics'], dc['gp'], odb, extra=ec,
+                                 write_freq=10**9, optimizer=_fixed_hyper)
+        o.pre_run()
+        t0 = time.perf_counter()
+        o.update()
+        t1 = time.perf_counter()
+        res["cpu_baseline"] = {"kind": "port", "cores": os.cpu_count(), "unit": "cell-updates/s",
+                               "value": nc * nc / (t1 - t0),
+                               "sample": f"one step of the NumPy/SciPy oracle (oracle/surrogate.py) on {nc}x{nc} cells, same M"}
+    return res
 
 
 if __name__ == "__main__":

@@ -288,9 +288,12 @@ __global__ void __launch_bounds__(256) gp_trsv_bwd_kernel(const double* L, int M
 
 // ------------------------------------------------------------------------------------
 // mean (n_out, N) = alpha^T Ks, and d mean_0 / d x_0 (max over the queries of this block).
-// One thread per query, training points staged through shared memory.
+// One thread per query, training points staged through shared memory.  The loop is FP64-issue bound
+// (sqrt ~10 and exp ~20 instructions of ~50 per kernel evaluation), so the variants drop what a call does
+// not need: NOUT = 1 the second output, GRAD = false the slope sum, D = 1 the square root
+// (sqrt(RN(t*t)) == |t| exactly unless t*t leaves the normal range, where both give 0 or inf alike).
 // ------------------------------------------------------------------------------------
-template <int D>
+template <int D, int NOUT, bool GRAD>
 __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const double* alpha, int M, int Mp, int nout,
                                                       GpKern kp, const double* Xtest, long long N, long long off,
                                                       long long cnt, double* mean, double* gmax_part) {
@@ -310,27 +313,33 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
         for (int e = threadIdx.x; e < n * D; e += 256) sx[e] = Xs[(size_t)t0 * D + e];
         for (int e = threadIdx.x; e < n; e += 256) {
             sa[0][e] = alpha[t0 + e];
-            sa[1][e] = nout > 1 ? alpha[(size_t)Mp + t0 + e] : 0.0;
+            if (NOUT > 1) sa[1][e] = alpha[(size_t)Mp + t0 + e];
         }
         __syncthreads();
         for (int j = 0; j < n; ++j) {
-            double d2 = 0.0;
+            double r;
+            if constexpr (D == 1) {
+                r = SQRT3 * fabs(x[0] - sx[j]);
+            } else {
+                double d2 = 0.0;
 #pragma unroll
-            for (int k = 0; k < D; ++k) { const double t = x[k] - sx[j * D + k]; d2 += t * t; }
-            const double r = SQRT3 * sqrt(d2);
+                for (int k = 0; k < D; ++k) { const double t = x[k] - sx[j * D + k]; d2 += t * t; }
+                r = SQRT3 * sqrt(d2);
+            }
             const double e = exp(-r);
             const double kv = (1.0 + r) * e;
             m0 += sa[0][j] * kv;
-            m1 += sa[1][j] * kv;
-            g0 += sa[0][j] * ((x[0] - sx[j * D]) * e);
+            if (NOUT > 1) m1 += sa[1][j] * kv;
+            if (GRAD) g0 += sa[0][j] * ((x[0] - sx[j * D]) * e);
         }
     }
     double g = -INFINITY;
     if (valid) {
         mean[i] = kp.amp * m0;
-        if (nout > 1) mean[N + i] = kp.amp * m1;
+        if (NOUT > 1) mean[N + i] = kp.amp * m1;
         g = -3.0 * kp.amp * kp.s[0] * g0;          // d/dx_0 in the (unscaled) normalised input
     }
+    if (!GRAD) return;
     // block max (NaN-propagating like jnp.max is not needed: a NaN gradient makes the mean NaN too)
 #pragma unroll
     for (int oo = 16; oo > 0; oo >>= 1) g = fmax(g, __shfl_xor_sync(0xffffffffu, g, oo));
@@ -878,14 +887,21 @@ int GpModel::mean(const double* Xtest, long long N, double* mean_out, double* dm
     for (long long off = 0; off < N; off += chunk) {
         const long long cnt = std::min<long long>(chunk, N - off);
         const int nbk = (int)((cnt + 255) / 256);
+        const bool grad = dmax_host != nullptr;
         switch (D) {
-#define GP_MEAN_CASE(DD) case DD: gp_mean_kernel<DD><<<nbk, 256, 0, s>>>(Xs, alpha, M, Mp, nout, kp, Xtest, N, off, cnt, mean_out, gpart); break;
+#define GP_MEAN_LAUNCH(DD, NO, GR) gp_mean_kernel<DD, NO, GR><<<nbk, 256, 0, s>>>(Xs, alpha, M, Mp, nout, kp, Xtest, N, off, cnt, mean_out, gpart)
+#define GP_MEAN_CASE(DD) case DD:                                                     \
+            if (grad) { if (nout > 1) GP_MEAN_LAUNCH(DD, 2, true); else GP_MEAN_LAUNCH(DD, 1, true); }   \
+            else { if (nout > 1) GP_MEAN_LAUNCH(DD, 2, false); else GP_MEAN_LAUNCH(DD, 1, false); }      \
+            break;
             GP_MEAN_CASE(1) GP_MEAN_CASE(2) GP_MEAN_CASE(3) GP_MEAN_CASE(4) GP_MEAN_CASE(5) GP_MEAN_CASE(6) GP_MEAN_CASE(7) GP_MEAN_CASE(8)
 #undef GP_MEAN_CASE
+#undef GP_MEAN_LAUNCH
         }
-        gp_max_reduce_kernel<<<1, 256, 0, s>>>(gpart, nbk, scal);
-        g_launches += 2;
+        g_launches += 1;
         if (dmax_host) {
+            gp_max_reduce_kernel<<<1, 256, 0, s>>>(gpart, nbk, scal);
+            g_launches += 1;
             double g;
             GPF_CUDA(cudaMemcpyAsync(&g, scal, 8, cudaMemcpyDeviceToHost, s));
             GPF_CUDA(cudaStreamSynchronize(s));
