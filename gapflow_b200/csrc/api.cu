@@ -201,8 +201,8 @@ int gpf_fv_set_surrogate(gpf_fv* s, const double* pressure, double pressure_scal
                          double shear_xz_scale, const double* shear_yz, double shear_yz_scale) {
     GPF_TRY NEED(s) return s->S.set_surrogate(pressure, pressure_scale, shear_xz, shear_xz_scale, shear_yz, shear_yz_scale); GPF_CATCH
 }
-int gpf_fv_finish_surrogate(gpf_fv* s, int mode, double* rec5, double c2, void* stream) {
-    GPF_TRY NEED(s) return s->S.finish_surrogate(mode, rec5, c2, (cudaStream_t)stream); GPF_CATCH
+int gpf_fv_finish_surrogate(gpf_fv* s, int mode, double* recs, int nrec, double c2, void* stream) {
+    GPF_TRY NEED(s) return s->S.finish_surrogate(mode, recs, nrec, c2, (cudaStream_t)stream); GPF_CATCH
 }
 int gpf_fv_set_timing(gpf_fv* s, int enable) {
     GPF_TRY NEED(s) s->S.timing = enable != 0; s->S.ev_steps = 0; return GPF_OK; GPF_CATCH

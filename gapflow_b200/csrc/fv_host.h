@@ -48,7 +48,7 @@ struct FvSolver {
     const double* sg_yz = nullptr;
     double sg_scale[3] = {1.0, 1.0, 1.0};
     int set_surrogate(const double* p, double ps, const double* xz, double xzs, const double* yz, double yzs);
-    int finish_surrogate(int mode, double* rec5, double c2, cudaStream_t s);
+    int finish_surrogate(int mode, double* recs, int nrec, double c2, cudaStream_t s);
     DevState* st;
     Partial* partial;
     int* pflags;

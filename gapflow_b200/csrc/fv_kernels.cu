@@ -1271,11 +1271,6 @@ int FvSolver::set_surrogate(const double* p, double ps, const double* xz, double
         set_error("gpf_fv_set_surrogate: a solver with viscosity modifiers has no surrogate variant");
         return GPF_E_INVALID;
     }
-    if ((p || xz || yz) && (P.bc.type[0][0] == GPF_BC_HALO || P.bc.type[1][0] == GPF_BC_HALO)) {
-        set_error("gpf_fv_set_surrogate: slab solvers take the GP means of their own rows only through a "
-                  "single-domain solver (query cells are partitioned, the FV step is not)");
-        return GPF_E_INVALID;
-    }
     sg_p = p; sg_xz = xz; sg_yz = yz;
     sg_scale[0] = ps; sg_scale[1] = xzs; sg_scale[2] = yzs;
     return GPF_OK;
@@ -1283,21 +1278,23 @@ int FvSolver::set_surrogate(const double* p, double ps, const double* xz, double
 
 // rec5[2] (max c^2) <- c2 when the pressure is a GP (Pressure.v_sound, stress.py:522-537); the flag of
 // an undefined analytic sound speed is replaced by that of c2
-__global__ void fv_record_c2_kernel(double* rec5, double c2) {
-    rec5[2] = c2;
-    int f = (int)rec5[4] & ~FLAG_CNAN;
+__global__ void fv_record_c2_kernel(double* recs, int nrec, double c2) {
+    const int r = threadIdx.x;
+    if (r >= nrec) return;
+    recs[r * 5 + 2] = c2;
+    int f = (int)recs[r * 5 + 4] & ~FLAG_CNAN;
     if (!(c2 >= 0.0)) f |= FLAG_CNAN;       // sqrt of a negative slope is NaN (stress.py:535)
-    rec5[4] = (double)f;
+    recs[r * 5 + 4] = (double)f;
 }
 
-int FvSolver::finish_surrogate(int mode, double* rec5, double c2, cudaStream_t s) {
-    if (!rec5) { set_error("rec5 is NULL"); return GPF_E_INVALID; }
+int FvSolver::finish_surrogate(int mode, double* recs, int nrec, double c2, cudaStream_t s) {
+    if (!recs || nrec < 1 || nrec > 1024) { set_error("bad record arguments"); return GPF_E_INVALID; }
     if (sg_p) {
-        fv_record_c2_kernel<<<1, 1, 0, s>>>(rec5, c2);
+        fv_record_c2_kernel<<<1, 1024, 0, s>>>(recs, nrec, c2);
         g_launches++;
         GPF_CUDA(cudaGetLastError());
     }
-    return finish(mode, rec5, 1, s);
+    return finish(mode, recs, nrec, s);
 }
 
 // ---- peer-memory exchange (slab_comm.cuh) --------------------------------------------------

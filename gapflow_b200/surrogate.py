@@ -149,8 +149,10 @@ class SurrogateModel:
     """One GP model of the reference bound to an ``FVSolver``: kind 'zz' (pressure, n_out = 1), 'xz' /
     'yz' (lower and upper wall shear, n_out = 2, one kernel; gp.py:546-552)."""
 
-    def __init__(self, kind, solver, database, cfg, optimizer=None, jitter=TINYGP_JITTER):
+    def __init__(self, kind, solver, database, cfg, optimizer=None, jitter=TINYGP_JITTER, coll=None, row0=0):
         self.kind, self.name, self.solver, self.database = kind, kind, solver, database
+        self.coll = coll or LocalColl()       # slabs: maxima, arg-max and the new sample are folded over the ranks
+        self.row0 = row0                      # first row of this solver's padded array in the global padded array
         if kind == 'zz':
             self.active_dims = [int(d) for d in cfg['active_dims']]
             self._cols = [0]
@@ -181,9 +183,13 @@ class SurrogateModel:
         return _features(self.solver, rel, self.database.X_scale, self.active_dims)
 
     def _Xtest_row(self, i, rel=0):
-        """row i of the un-normalised 7-feature matrix (gp.py:223-232, 425)."""
-        X = _features(self.solver, rel, np.ones(7), list(range(7)))
-        return X[int(i)].cpu().numpy()
+        """row i (GLOBAL cell index) of the un-normalised 7-feature matrix (gp.py:223-232, 425); with slabs the
+        lowest rank that holds the cell supplies it."""
+        loc = int(i) - self.row0 * self.solver.shape[1]
+        row = None
+        if 0 <= loc < self.solver.shape[0] * self.solver.shape[1]:
+            row = _features(self.solver, rel, np.ones(7), list(range(7)))[loc].cpu().numpy()
+        return next(r for r in self.coll.allgather(row) if r is not None)
 
     @property
     def Xtrain(self):
@@ -256,8 +262,17 @@ class SurrogateModel:
             self.mean, v = self.gp.repredict_mean_var(X, noise=self.jitter)
             ys = self.Yscale
             self._var = v.reshape(self.solver.shape) * ys**2
-            self.maximum_variance = self.gp._vmax_norm * ys**2
-            self.argmax = self.gp.argmax
+            # gp.py:406, 424 over the GLOBAL padded array: slab-internal halo rows repeat the neighbour's cells
+            # bit for bit, so the smallest global index among the maxima is the reference's first maximum
+            gidx = self.gp.argmax + self.row0 * self.solver.shape[1]
+            pairs = self.coll.allgather((self.gp._vmax_norm, gidx))
+            v = np.array([a for a, _ in pairs])
+            if np.isnan(v).any():
+                vmax, self.argmax = float('nan'), min(g for a, g in pairs if a != a)
+            else:
+                vmax = float(v.max())
+                self.argmax = min(g for a, g in pairs if a == vmax)
+            self.maximum_variance = vmax * ys**2
             self.variance_tol = max(self.atol * self.Yerr * ys, self.rtol * ys)**2
         else:
             self.mean = self.gp.repredict_mean(X)
@@ -295,7 +310,75 @@ class SurrogateModel:
     def v_sound2(self, rel=0):
         """stress.py:522-537: max_i d mean / d x_0 * Yscale / X_scale[0]."""
         _, g = self.gp.repredict_mean(self.Xtest(rel), with_gradient_max=True)
+        gs = np.array(self.coll.allgather(g))
+        g = float('nan') if np.isnan(gs).any() else float(gs.max())
         return g * self.Yscale / float(self.database.X_scale[0])
+
+
+class LocalColl:
+    """host-level collective of a single domain."""
+    rank, world = 0, 1
+
+    def allgather(self, x):
+        return [x]
+
+
+class DistColl:
+    """the same over torch.distributed (one process per GPU): small Python objects, rank order."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self._dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def allgather(self, x):
+        out = [None] * self.world
+        self._dist.all_gather_object(out, x, group=self.group)
+        return out
+
+
+class ThreadColl:
+    """the same between threads of one process, one thread per rank (all slabs on one GPU): what the
+    single-GPU tests run, with ``exchanger(rank, periodic)`` standing in for dist.HaloExchanger."""
+
+    def __init__(self, world):
+        import threading
+        self.world = world
+        self._barrier = threading.Barrier(world)
+        self._slots = [None] * world
+
+    class _Rank:
+        def __init__(self, parent, rank):
+            self.p, self.rank, self.world = parent, rank, parent.world
+
+        def allgather(self, x):
+            p = self.p
+            p._slots[self.rank] = x
+            p._barrier.wait()
+            out = list(p._slots)
+            p._barrier.wait()
+            return out
+
+    def view(self, rank):
+        return ThreadColl._Rank(self, rank)
+
+    def exchanger(self, rank, periodic):
+        from .dist import HaloExchanger
+        coll = self.view(rank)
+
+        class _Ex(HaloExchanger):
+            def exchange(self, send, recv):           # all ranks share the legacy default stream: enqueue order is enough
+                sends = coll.allgather(send)
+                if self.lo is not None:
+                    recv[0].copy_(sends[self.lo][1])
+                if self.hi is not None:
+                    recv[1].copy_(sends[self.hi][0])
+                coll.allgather(None)
+
+            def gather(self, rec, out):
+                out.copy_(torch.stack(coll.allgather(rec)).reshape(out.shape))
+                coll.allgather(None)
+        return _Ex(rank, self.world, periodic)
 
 
 def _features(solver, rel, X_scale, active_dims):
@@ -313,20 +396,23 @@ class SurrogateDriver:
     """``Problem._pre_run`` / ``Problem.update`` with GP closures (problem.py:412-443, 509-586) on an
     ``FVSolver``.  ``gp``: the sanitised gp dict (io.py:395-427); ``database``: a ``Database``."""
 
-    def __init__(self, solver, gp, database, dim, write_freq=1000, optimizer=None, jitter=TINYGP_JITTER):
+    def __init__(self, solver, gp, database, dim, write_freq=1000, optimizer=None, jitter=TINYGP_JITTER,
+                 coll=None, row0=0):
         if database is None:
             raise ValueError("a GP configuration needs a Database (GaPFlow/problem.py:77-152)")
         if database.num_features != 7:
             raise NotImplementedError("the FV solver carries one extra feature plane (problem.py:131)")
         self.solver, self.database, self.dim, self.write_freq = solver, database, dim, write_freq
+        self.coll, self.row0 = coll or LocalColl(), row0
         self.lib = _capi.load()
         self.models = {}
+        kw = dict(optimizer=optimizer, jitter=jitter, coll=self.coll, row0=row0)
         if gp.get('press_gp'):                                   # problem.py:640-660
-            self.models['zz'] = SurrogateModel('zz', solver, database, gp['press'], optimizer, jitter)
+            self.models['zz'] = SurrogateModel('zz', solver, database, gp['press'], **kw)
         if gp.get('shear_gp'):
-            self.models['xz'] = SurrogateModel('xz', solver, database, gp['shear'], optimizer, jitter)
+            self.models['xz'] = SurrogateModel('xz', solver, database, gp['shear'], **kw)
             if dim == 2:
-                self.models['yz'] = SurrogateModel('yz', solver, database, gp['shear'], optimizer, jitter)
+                self.models['yz'] = SurrogateModel('yz', solver, database, gp['shear'], **kw)
         self._rec = torch.zeros(5, dtype=torch.float64, device=solver.device)
         self.ready = False
 
@@ -344,38 +430,44 @@ class SurrogateDriver:
     def _c2(self, rel):
         return self.models['zz'].v_sound2(rel) if 'zz' in self.models else 0.0
 
-    def pre_run(self):
+    # -- the three device phases a slab driver replaces ---------------------------------------------
+    def _global_features(self):
+        """the un-normalised feature matrix of every cell of the global padded array (gp.py:223-232)."""
+        return _features(self.solver, 0, np.ones(7), list(range(7))).cpu().numpy()
+
+    def _run_pass(self, i):
         s = self.solver
+        _capi.check(self.lib.gpf_fv_pass(s.h, i, s._stream()))
+
+    def _finish(self, kind, mode, c2):
+        s = self.solver
+        _capi.check(self.lib.gpf_fv_reduce_local(s.h, kind, C.c_void_p(self._rec.data_ptr()), s._stream()))
+        _capi.check(self.lib.gpf_fv_finish_surrogate(s.h, mode, C.c_void_p(self._rec.data_ptr()), 1, c2, s._stream()))
+
+    # -- problem.py:412-443, 509-586 -------------------------------------------------------------------
+    def pre_run(self):
+        X = self._global_features()
         for m in self._order():                                   # problem.py:418-420
-            X = _features(s, 0, np.ones(7), list(range(7))).cpu().numpy()
             self.database.initialize(X, self.dim)
         for m in self._order():                                   # problem.py:422-424
             m.init()
         self._bind()
         self.ready = True
-        _capi.check(self.lib.gpf_fv_reduce_local(s.h, 1, C.c_void_p(self._rec.data_ptr()), s._stream()))
-        _capi.check(self.lib.gpf_fv_finish_surrogate(s.h, _capi.FIN_PRERUN_KEEP_EKIN, C.c_void_p(self._rec.data_ptr()),
-                                                     self._c2(0), s._stream()))
+        self._finish(1, _capi.FIN_PRERUN_KEEP_EKIN, self._c2(0))
 
     def refresh_scalars(self):
         """scalars of the current q with the GP sound speed (Problem.dt_crit / cfl between steps)."""
-        s = self.solver
-        _capi.check(self.lib.gpf_fv_reduce_local(s.h, 1, C.c_void_p(self._rec.data_ptr()), s._stream()))
-        _capi.check(self.lib.gpf_fv_finish_surrogate(s.h, _capi.FIN_REFRESH, C.c_void_p(self._rec.data_ptr()),
-                                                     self._c2(0), s._stream()))
+        self._finish(1, _capi.FIN_REFRESH, self._c2(0))
 
     def update(self, step):
         """one Problem.update(); ``step`` = Problem.step before it (problem.py:530)."""
-        s = self.solver
         before_output = (step + 1) % self.write_freq == 0
         for i in (0, 1):
             for m in self._order():                               # problem.py:532-540
                 m.predict(predictor=i == 0, compute_var=m.use_active_learning or before_output, rel=i)
             self._bind()
-            _capi.check(self.lib.gpf_fv_pass(s.h, i, s._stream()))
-        _capi.check(self.lib.gpf_fv_reduce_local(s.h, 0, C.c_void_p(self._rec.data_ptr()), s._stream()))
-        _capi.check(self.lib.gpf_fv_finish_surrogate(s.h, _capi.FIN_STEP, C.c_void_p(self._rec.data_ptr()),
-                                                     self._c2(2), s._stream()))
+            self._run_pass(i)
+        self._finish(0, _capi.FIN_STEP, self._c2(2))
 
     def closures(self, fields):
         """overlay the GP means on the fixed-form closure fields (stress.py:350-356, 619-620); ``fields`` =
@@ -389,3 +481,35 @@ class SurrogateDriver:
                 f, oi = (wxz, 4) if k == 'xz' else (wyz, 3)
                 f[oi], f[oi + 6] = mf[0], mf[1]
         return p, wxz, wyz, bulk
+
+
+class SlabSurrogateDriver(SurrogateDriver):
+    """The same step on one rank's slab (gapflow_b200.dist.SlabSolver): the training set, the factor and the
+    database are replicated on every rank (each rank runs the identical mock-MD call and training), the
+    query cells are partitioned -- a rank evaluates the GP means of its own padded rows, halo rows
+    included, after the halo exchange of the pass's input.  Folded over the ranks: the largest variance
+    and its first cell, the new training sample (from the lowest rank that holds the cell), the largest
+    slope of the pressure mean, the loop records.  ``coll``: DistColl (one process per GPU) or a
+    ThreadColl view (all slabs in one process)."""
+
+    def __init__(self, slab, gp, database, dim, coll, **kw):
+        self.slab = slab
+        super().__init__(slab.fv, gp, database, dim, coll=coll, row0=slab.row0, **kw)
+
+    def _global_features(self):
+        from .dist import owned_rows
+        sl, Ny2 = self.slab, self.solver.shape[1]
+        a, b = owned_rows(sl.grid_global['Nx'], sl.rank, sl.world)
+        X = _features(self.solver, 0, np.ones(7), list(range(7)))
+        own = X[(a - sl.row0) * Ny2:(b - sl.row0) * Ny2].cpu().numpy()
+        return np.vstack(self.coll.allgather(own))
+
+    def _run_pass(self, i):
+        self.slab._pass(i)
+        self.slab._exchange(i + 1)            # halo rows of the pass's output: the next pass's (or step's) input
+
+    def _finish(self, kind, mode, c2):
+        sl = self.slab
+        sl._record(kind)
+        sl.ex.gather(sl.rec, sl.recs)
+        _capi.check(self.lib.gpf_fv_finish_surrogate(sl.h, mode, C.c_void_p(sl.recs.data_ptr()), sl.world, c2, sl._s()))

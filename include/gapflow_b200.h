@@ -247,11 +247,15 @@ int gpf_fv_finish(gpf_fv* s, int mode, const double* recs, int nrec, void* strea
 int gpf_fv_set_surrogate(gpf_fv* s, const double* pressure, double pressure_scale,
                          const double* shear_xz, double shear_xz_scale,
                          const double* shear_yz, double shear_yz_scale);
-/* gpf_fv_finish for one record (device, in/out) after replacing its max c^2 by `c2` when a pressure
- * GP is set: Pressure.v_sound's GP branch (stress.py:522-537), c2 = max_i d mean / d x_0 * Yscale /
- * X_scale[0] with the maximum from gpf_gp_mean(..., dmean_dx0_max).  mode as gpf_fv_finish
- * (GPF_FIN_PRERUN after reduce_local(1, rec5) reproduces _pre_run's dt = CFL * dt_crit). */
-int gpf_fv_finish_surrogate(gpf_fv* s, int mode, double* rec5, double c2, void* stream);
+/* gpf_fv_finish for `nrec` records (device, in/out; 1 for a single domain, the gathered records of all
+ * ranks for slabs) after replacing their max c^2 by `c2` when a pressure GP is set: Pressure.v_sound's
+ * GP branch (stress.py:522-537), c2 = max_i d mean / d x_0 * Yscale / X_scale[0] with the maximum from
+ * gpf_gp_mean(..., dmean_dx0_max), over all ranks for slabs.  mode as gpf_fv_finish (GPF_FIN_PRERUN*
+ * after reduce_local(1, rec5) reproduces _pre_run's dt = CFL * dt_crit).
+ * Slabs: a rank's arrays cover ITS padded rows (halo rows included: they hold the neighbour's cells once
+ * the exchange of the pass's input has run), so query cells are partitioned and the training set is
+ * replicated; gapflow_b200/surrogate.py::SlabSurrogateDriver drives it. */
+int gpf_fv_finish_surrogate(gpf_fv* s, int mode, double* recs, int nrec, double c2, void* stream);
 
 /* --- pure functions (GaPFlow/models/*.py, GaPFlow/integrate.py); device pointers ---- */
 /* eos_pressure(density, prop) -> pressure.py:35;  eos_sound_velocity -> sound.py:35 */

@@ -108,7 +108,7 @@ def test_surrogate_pass_kernels_with_given_means(name, kw, arith):
     rec = torch.zeros(5, dtype=torch.float64, device='cuda')
     _capi.check(lib.gpf_fv_reduce_local(s.h, 0, C.c_void_p(rec.data_ptr()), s._stream()))
     c2 = 2.5
-    _capi.check(lib.gpf_fv_finish_surrogate(s.h, _capi.FIN_STEP, C.c_void_p(rec.data_ptr()), c2, s._stream()))
+    _capi.check(lib.gpf_fv_finish_surrogate(s.h, _capi.FIN_STEP, C.c_void_p(rec.data_ptr()), 1, c2, s._stream()))
     q = s.get_q()
     err = relerr(q, o.q)
     assert err <= 1e-12, err
@@ -234,3 +234,136 @@ def test_surrogate_refusals():
     buf = torch.zeros(o.q.shape[1] * o.q.shape[2], dtype=torch.float64, device='cuda')
     rc = lib.gpf_fv_set_surrogate(s.h, C.c_void_p(buf.data_ptr()), 1.0, None, 1.0, None, 1.0)
     assert rc == _capi.GPF_E_INVALID and b'viscosity' in lib.gpf_last_error()
+
+
+# ---- slabs: training set replicated, query cells partitioned (BASELINE.json north_star) ---------------------
+def _run_thread_slabs(d, q_global, topo, extra, world, steps, optimizer=SC.fixed_optimizer):
+    """all slabs on one GPU, one thread per rank (gapflow_b200.surrogate.ThreadColl stands in for
+    torch.distributed); returns per-rank (slab q, Xtrain, scalars, models)."""
+    import threading
+    from gapflow_b200 import _capi
+    from gapflow_b200.dist import SlabSolver, slab_rows, x_periodic
+    from gapflow_b200.surrogate import Database, Mock, SlabSurrogateDriver, ThreadColl
+    tc = ThreadColl(world)
+    rows = slab_rows(d['grid']['Nx'], world)
+    out, errs = [None] * world, []
+
+    def work(r):
+        try:
+            torch.cuda.set_device(0)
+            sl = SlabSolver.from_global(d, None, topo, extra, rank=r, world=world,
+                                        exchanger=tc.exchanger(r, x_periodic(d['grid'])))
+            sl._fold(1, _capi.FIN_PRERUN)                # kinetic_energy_old of the _initialize state
+            start, n = rows[r]
+            sl.set_q(np.ascontiguousarray(q_global[:, start:start + n + 2]))
+            db = Database(Mock(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS), d['db'])
+            drv = SlabSurrogateDriver(sl, d['gp'], db, d['grid']['dim'], tc.view(r),
+                                      write_freq=d['options']['write_freq'], optimizer=optimizer)
+            drv.pre_run()
+            for k in range(steps):
+                drv.update(k)
+            out[r] = (sl.get_q(), db._Xtrain.copy(), sl.fv.scalars(), drv)
+        except BaseException as e:                       # release the other ranks instead of hanging them
+            errs.append((r, repr(e)))
+            tc._barrier.abort()
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(300)
+    assert not errs, errs
+    return out, rows
+
+
+@pytest.mark.parametrize('name,kw,world,steps', [
+    ('slip2d', dict(nx=24, ny=20, atol=0.8, al_steps=2), 2, 4),
+    ('slip1d', dict(nx=100, atol=0.6, al_steps=3), 3, 6),
+])
+def test_slab_coupled_steps_match_single_domain_and_oracle(name, kw, world, steps):
+    """N slabs == one domain bit for bit (same cells, same arithmetic, folds in rank order), and both within the
+    GP tolerance of the oracle; the database grows by the same samples on every rank."""
+    d, o, s, drv = build(name, **kw)
+    q0 = o.q.copy()
+    o.pre_run()
+    drv.pre_run()
+    for k in range(steps):
+        o.update()
+        drv.update(k)
+    q1 = s.get_q()
+    out, rows = _run_thread_slabs(d, q0, o.topo, o.extra, world, steps)
+    for r, (start, n) in enumerate(rows):
+        q, X, sc, sd = out[r]
+        assert np.array_equal(q[:, 1:-1], q1[:, start + 1:start + n + 1]), (r, relerr(q[:, 1:-1], q1[:, start + 1:start + n + 1]))
+        assert np.array_equal(X, drv.database._Xtrain), r
+        s1 = s.scalars()
+        assert sc.dt == s1.dt and sc.step == s1.step == steps, r
+        assert np.isclose(sc.residual, s1.residual, rtol=1e-10), r      # the kinetic-energy sum is folded rank by rank
+        for k, m in sd.models.items():
+            assert m.n_train == drv.models[k].n_train and m.argmax == drv.models[k].argmax, (r, k)
+            assert m.maximum_variance == drv.models[k].maximum_variance, (r, k)
+    assert drv.database.size == o.database.size > d['db']['init_size']
+    assert relerr(q1, o.q) <= 1e-8
+
+
+NCCL_WORKER = r"""
+import os, sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np, torch, torch.distributed as dist
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+rank, world = dist.get_rank(), dist.get_world_size()
+from oracle import surrogate as OS
+from tests import surrogate_cases as SC
+from tests.test_fv_gpu import relerr
+from gapflow_b200.dist import SlabSolver, slab_rows
+from gapflow_b200.surrogate import Database, Mock, SlabSurrogateDriver, DistColl
+d, _ = SC.inputs('slip2d', nx=48, ny=20, atol=0.8, al_steps=2)
+g = d['grid']
+extra = SC.slip_length(g['Nx'], g['Ny'])
+odb = OS.Database(OS.MockMD(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS), d['db'])
+o = OS.SurrogateFVOracle(g, d['geometry'], d['properties'], d['numerics'], d['gp'], odb, extra=extra,
+                         write_freq=d['options']['write_freq'], optimizer=SC.fixed_optimizer)
+o.q[...] = SC.perturb(o.q)
+o.fill_ghosts()
+sl = SlabSolver.from_global(d, o.q, o.topo, extra)
+db = Database(Mock(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS), d['db'])
+drv = SlabSurrogateDriver(sl, d['gp'], db, g['dim'], DistColl(), write_freq=d['options']['write_freq'],
+                          optimizer=SC.fixed_optimizer)
+o.pre_run()
+drv.pre_run()
+for k in range(4):
+    o.update()
+    drv.update(k)
+q = sl.gather_q()
+sc = sl.fv.scalars()
+assert db.size == odb.size > d['db']['init_size'], (db.size, odb.size)
+assert np.allclose(db._Xtrain, odb._Xtrain, rtol=1e-8, atol=1e-12)
+assert relerr(q, o.q) <= 1e-8, relerr(q, o.q)
+assert sc.step == o.step and abs(sc.dt - o.dt) <= 1e-8 * o.dt
+dist.barrier()
+if rank == 0:
+    print("NCCL_SURROGATE_OK")
+dist.destroy_process_group()
+"""
+
+
+def test_nccl_slab_coupled_steps_vs_oracle(tmp_path):
+    import socket
+    import subprocess
+    import sys
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(n, 4)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "worker.py"
+    script.write_text(NCCL_WORKER)
+    sock = socket.socket()
+    sock.bind(("127.0.0.1", 0))
+    port = sock.getsockname()[1]
+    sock.close()
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), root],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0 and "NCCL_SURROGATE_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

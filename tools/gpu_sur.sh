@@ -1,7 +1,7 @@
 #!/bin/bash
 # GP-coupled step: new GPU tests, then (optionally) the whole GPU suite and a bench line.  usage: tools/gpu_sur.sh <tag> [full]
 tag=${1:-rS}; out=gpurun_out/$tag; mkdir -p $out
-timeout 400 python -m pytest tests/test_surrogate_gpu.py -m gpu -q --timeout 200 -x > $out/sur.log 2>&1; echo "sur exit $?" | tee -a $out/sur.log
+timeout 400 python -m pytest tests/test_surrogate_gpu.py -m gpu -q --timeout 200 > $out/sur.log 2>&1; echo "sur exit $?" | tee -a $out/sur.log
 tail -60 $out/sur.log
 if [ "$2" = "full" ]; then
   timeout 420 python -m pytest tests -m gpu -q --timeout 200 > $out/pytest.log 2>&1; echo "pytest exit $?" | tee -a $out/pytest.log
