@@ -60,6 +60,21 @@ def main():
     import numpy as np
     import torch
     from gapflow_b200 import _capi
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        # torchrun: the GP-coupled step on `world` slabs (training set replicated, query cells partitioned)
+        import torch.distributed as dist
+        torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+        args.no_cpu = True
+        res = coupled_step(torch, np, _capi.load(), args, world=world)
+        if dist.get_rank() == 0:
+            print(json.dumps({"metric": "GP-coupled FV cell-updates/s", "unit": "cell-updates/s", "n_gpus": world,
+                              "value": res["cell_updates_per_s"], "scaling": "strong", "dtype": "f64", "data": "synthetic",
+                              "coupled_step": res}))
+        dist.barrier()
+        dist.destroy_process_group()
+        return
     from gapflow_b200.gp import GPModel
     from tests.gp_cases import query_set, training_set
     assert torch.cuda.is_available(), "needs a CUDA device: there is no CPU path"
@@ -147,7 +162,7 @@ def _fixed_hyper(model):
     return 0.0, np.log(np.std(np.asarray(model.Xtrain), axis=0))       # params_init (stress.py:281-284)
 
 
-def coupled_step(torch, np, lib, args):
+def coupled_step(torch, np, lib, args, world=1):
     """One Problem.update() with all three GP models (slip_2d_lj_mock.py scaled: BASELINE config 4): per pass the
     feature matrices, three predictive means over every padded cell and the surrogate pass kernel; then the
     GP sound speed.  Active learning off, hyperparameters = params_init (no optimiser in the timed region)."""
@@ -157,9 +172,17 @@ def coupled_step(torch, np, lib, args):
     d, extra = _coupled_inputs(np, n, M)
     from gapflow_b200.topography import make_topography
     topo = make_topography(d['grid'], d['geometry'])
-    s = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, extra=extra, arith='fast')
     db = Database(Mock(d['properties'], d['geometry'], d['gp'], draws=(0.3, -0.3, 0.5)), d['db'])
-    drv = SurrogateDriver(s, d['gp'], db, 2, write_freq=10**9, optimizer=_fixed_hyper)
+    if world > 1:
+        import torch.distributed as dist
+        from gapflow_b200.dist import SlabSolver
+        from gapflow_b200.surrogate import DistColl, SlabSurrogateDriver
+        sl = SlabSolver.from_global(d, None, topo, extra, arith='fast')
+        s = sl.fv
+        drv = SlabSurrogateDriver(sl, d['gp'], db, 2, DistColl(), write_freq=10**9, optimizer=_fixed_hyper)
+    else:
+        s = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, extra=extra, arith='fast')
+        drv = SurrogateDriver(s, d['gp'], db, 2, write_freq=10**9, optimizer=_fixed_hyper)
     t0 = time.perf_counter()
     drv.pre_run()                                # initial design (M mock-MD rows), 3 factorisations, first inference
     torch.cuda.synchronize()
@@ -167,6 +190,9 @@ def coupled_step(torch, np, lib, args):
     l0 = lib.gpf_launch_count()
     drv.update(0)
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for k in range(args.coupled_steps):
@@ -174,6 +200,10 @@ def coupled_step(torch, np, lib, args):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / args.coupled_steps
+    if world > 1:                                  # device time, max over ranks
+        t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
     launches = (lib.gpf_launch_count() - l0) // (args.coupled_steps + 1)
     sc = s.scalars()
     Np = (n + 2) * (n + 2)
@@ -182,7 +212,9 @@ def coupled_step(torch, np, lib, args):
            "ms_per_step": ms, "cell_updates_per_s": n * n / (ms * 1e-3),
            "gp_predictions_per_step": 7 * Np, "gp_predictions_per_s": 7 * Np / (ms * 1e-3),
            "kernel_evals_per_s": 7.0 * Np * db.size / (ms * 1e-3),
-           "pre_run_s": t_pre, "gpu_launches_per_step": int(launches), "final": {"step": int(sc.step), "dt": sc.dt}}
+           "pre_run_s": t_pre, "gpu_launches_per_step": int(launches), "final": {"step": int(sc.step), "dt": sc.dt},
+           "n_gpus": world, "parallelism": "single GPU" if world == 1 else
+           f"{world} x-slabs: query cells partitioned, training set / factor replicated, halo rows over peer memory"}
     if not args.no_cpu:
         from oracle import surrogate as OS
         nc = 104                                      # (nc + 2)^2 >= M: the design picks M distinct cells (db.py:329)

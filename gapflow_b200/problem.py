@@ -14,8 +14,13 @@ Device residency: ``q`` lives on the GPU.  Reading ``problem.q`` copies it to a 
 a ``run()`` never exposes it, so the loop runs without host traffic: ``write_freq`` updates are enqueued
 at once and the loop condition (problem.py:401) is evaluated on the device.
 
-Not here (host-side): GP surrogate orchestration (database, MD, hyperparameter
-fit), elastic deformation, plotting.  NetCDF: muGrid's ``FileIONetCDF`` is not available; ``sol.nc`` /
+GP models (``gp`` + ``database`` arguments, or ``gp`` / ``db`` sections of the YAML with the mock MD): the step
+is driven pass by pass by ``gapflow_b200.surrogate.SurrogateDriver`` (GP means on the device, active learning
+and the optimiser iteration on the host); outputs ``gp_zz.csv`` / ``gp_xz.csv`` / ``gp_yz.csv`` / ``gp_*.txt`` and
+``Xtrain.npy`` / ``Ytrain.npy`` / ``Ytrain_err.npy`` as the reference writes them (problem.py:486-503, db.py:268-276).
+
+Not here (host-side): LAMMPS MD runners, dtool storage, elastic deformation, plotting.
+NetCDF: muGrid's ``FileIONetCDF`` is not available; ``sol.nc`` /
 ``topo.nc`` are written as NetCDF-3 with ``scipy.io.netcdf_file`` using the reference's field names
 (the exact dimension names of muGrid's files are unverified).
 """
