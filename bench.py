@@ -322,7 +322,7 @@ def run_gpu(args):
     nbytes = qh.numel() * 8 * world
     e2e = {"value": cells_per_step * k2 / t_e2e, "unit": "cell-updates/s", "h2d_bytes_per_step": nbytes,
            "d2h_bytes_per_step": nbytes + (160 if world == 1 else 0), "steps": k2,
-           "api": ("gpf_fv_update_host (C ABI) via FVSolver.update_host" if world == 1 else
+           "api": ("gpf_fv_update_host (C ABI; H2D / passes / D2H pipelined over 16 row chunks) via FVSolver.update_host" if world == 1 else
                    "SlabSolver.update_host (gpf_fv_upload / slab step / gpf_fv_download per rank)")
                   + ", pinned host q, all ranks' bytes"}
 

@@ -170,6 +170,16 @@ int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, vo
     NEED(s && q_host)
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
+    if (n == 1) {
+        // copies overlapped with the passes chunk by chunk; GPF_E_STATE: configuration not eligible
+        rc = s->S.update_host_pipelined(q_host, st);
+        if (rc == GPF_OK) {
+            if (out) return s->S.get_scalars(out, st);
+            GPF_CUDA(cudaStreamSynchronize(st));
+            return GPF_OK;
+        }
+        if (rc != GPF_E_STATE) return rc;
+    }
     if ((rc = s->S.upload(GPF_F_Q, q_host, 3, 0, st))) return rc;
     s->S.dirty_scalars = false;    // loop scalars (dt, ekin_old) are kept; only q is replaced
     if ((rc = s->S.step(n, 0, st))) return rc;

@@ -94,6 +94,10 @@ struct FvSolver {
     bool graph_stale = false;
     int slab_launches = 0;
     int finish(int mode, const double* recs, int nrec, cudaStream_t s);
+    // host-buffer step with the copies overlapped chunk by chunk (gpf_fv_update_host, n == 1)
+    cudaStream_t cp_stream[2] = {nullptr, nullptr};
+    std::vector<cudaEvent_t> cp_event;
+    int update_host_pipelined(double* q_host, cudaStream_t s);
     int get_timing(double* ms_pred, double* ms_corr, long long* launches);
     double* field_ptr(int field, int* ncomp_max);
     int read_cur(cudaStream_t s, int* cur);

@@ -892,6 +892,10 @@ void FvSolver::drop_graphs() {
 int FvSolver::destroy() {
     for (auto e : ev) cudaEventDestroy(e);
     ev.clear();
+    for (auto e : cp_event) cudaEventDestroy(e);
+    cp_event.clear();
+    for (int k = 0; k < 2; ++k)
+        if (cp_stream[k]) { cudaStreamDestroy(cp_stream[k]); cp_stream[k] = nullptr; }
     drop_graphs();
     return GPF_OK;
 }
@@ -1074,11 +1078,15 @@ int FvSolver::viscosity(int which, double* out, int on_device, cudaStream_t s) {
 // slab neighbours need); GPF_PART_INTERIOR the rest -- so that a slab driver can exchange the edge
 // rows while the interior is being computed.  Grids of fewer than 3 tile rows are not split
 // (EDGE = everything, INTERIOR = nothing).
+// PART_ROWS (internal): tile rows [row0, row0 + nrows), records from slot rec0, at most max_cta CTAs --
+// the row chunks of the pipelined host-buffer step (FvSolver::update_host_pipelined)
+constexpr int PART_ROWS = 100;
 template <bool CORR>
-static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int part = GPF_PART_ALL) {
+static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int part = GPF_PART_ALL, int row0 = 0,
+                       int nrows = 0, int rec0 = 0, int max_cta = 0, int* used_cta = nullptr) {
     const int nty = S.P.nblk_x, nbx = S.P.nblk_y;          // tiles along y, tile rows along x
-    if (part < GPF_PART_ALL || part > GPF_PART_INTERIOR) { set_error("bad pass part"); return GPF_E_INVALID; }
-    if (nbx < 3) {
+    if (part != PART_ROWS && (part < GPF_PART_ALL || part > GPF_PART_INTERIOR)) { set_error("bad pass part"); return GPF_E_INVALID; }
+    if (part != PART_ROWS && nbx < 3) {
         if (part == GPF_PART_INTERIOR) return GPF_OK;
         part = GPF_PART_ALL;
     }
@@ -1106,7 +1114,13 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     static const int slack = [] { const char* e = getenv("GPF_INTERIOR_SLACK"); return e ? atoi(e) : 2; }();
     const int n_edge = pass_ctas(2 * nty, CORR, nty);
     const int n_int = pass_ctas((nbx - 2) * nty, CORR, nty, slack);
-    if (part == GPF_PART_ALL) {
+    int n_rows = 0;
+    if (part == PART_ROWS) {
+        A.ntiles = nrows * nty; A.bx_mul = 1; A.bx_off = row0; A.rec0 = rec0;
+        n_rows = std::min(pass_ctas(A.ntiles, CORR, nty), max_cta);
+        if (used_cta) *used_cta = n_rows;
+        if (CORR) S.nrec_corr = rec0 + n_rows;
+    } else if (part == GPF_PART_ALL) {
         A.ntiles = nbx * nty; A.bx_mul = 1; A.bx_off = 0; A.rec0 = 0;
         if (CORR) S.nrec_corr = pass_ctas(A.ntiles, true, nty);
     } else if (part == GPF_PART_EDGE) {
@@ -1119,7 +1133,7 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     const bool ls = S.P.has_extra != 0;
     const bool dh = S.P.eos.kind == GPF_EOS_DH;
     const bool xf = S.P.xflow != 0;
-    const int n = (part == GPF_PART_INTERIOR) ? n_int : pass_ctas(A.ntiles, CORR, nty);
+    const int n = (part == PART_ROWS) ? n_rows : (part == GPF_PART_INTERIOR) ? n_int : pass_ctas(A.ntiles, CORR, nty);
     const int rc = (S.cfg.arith == GPF_ARITH_FAST) ? launch_pass_fast(A, CORR, ls, dh, xf, vf, n, s)
                                                    : launch_pass_exact(A, CORR, ls, dh, xf, vf, n, s);
     if (rc) return rc;
@@ -1209,6 +1223,96 @@ int FvSolver::step(int n, int until_converged, cudaStream_t s) {
         if (timing) GPF_CUDA(cudaEventRecord(ev[3 * it + 3], s));
     }
     dirty_scalars = false;     // the corrector's reductions describe the new q
+    return GPF_OK;
+}
+
+// ---- one step on a host-resident field, copies overlapped with the passes -------------------
+// upload -> predictor -> corrector -> download of a whole field leaves the PCIe link idle in one direction
+// at any time and the GPU idle during both copies.  Here the field moves in chunks of tile rows on two
+// copy streams while the pass kernels follow chunk by chunk on the caller's stream.  For the MacCormack
+// order predictor d = +1 / corrector d = -1 (switch = +1, problem.py:521-522) the dependencies are
+//   P(k) reads input rows [a_k - 1, b_k]                  -> after upload(0..k)
+//   C(k) reads predictor rows [a_k, b_k + 1], q0 [a_k, b_k] -> after P(k + 1)   (the last chunk: the ghost row
+//        Nx+1, written by the predictor's own boundary tiles: P(0) for a periodic x side, P(K-1) otherwise)
+//   download(k)                                            -> after C(k); the two x ghost rows after the last C
+// so the launch order P(0) P(1) C(0) P(2) C(1) ... C(K-1) on one stream satisfies all of them, and a chunk
+// launch is the same kernel with a tile-row range: the result is bit-identical to gpf_fv_step.
+// Returns GPF_E_STATE when the configuration is not eligible (the caller then takes the plain path).
+int FvSolver::update_host_pipelined(double* q_host, cudaStream_t s) {
+    const int nbx = P.nblk_y;
+    if (P.mc_order != 1 || P.visc_field || sg_p || sg_xz || sg_yz || timing || nbx < 8 ||
+        P.bc.type[0][0] == GPF_BC_HALO || P.bc.type[1][0] == GPF_BC_HALO)
+        return GPF_E_STATE;
+    static const int want = [] { const char* e = getenv("GPF_HOST_CHUNKS"); return e ? atoi(e) : 16; }();
+    if (want < 2) return GPF_E_STATE;
+    const int K = std::min(want, nbx / 4);
+    int cur, rc;
+    if ((rc = read_cur(s, &cur))) return rc;                 // synchronises s
+    if (!cp_stream[0]) {
+        for (int k = 0; k < 2; ++k) GPF_CUDA(cudaStreamCreateWithFlags(&cp_stream[k], cudaStreamNonBlocking));
+        cp_event.resize(2 * 64 + 2);
+        for (auto& e : cp_event) GPF_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    if (K > 64) return GPF_E_STATE;
+    const size_t Ny2 = cfg.Ny + 2, Nx2 = cfg.Nx + 2, pitch = P.L.pitch;
+    double* qin = qbuf[cur];
+    const double* qout = qbuf[(cur + 2) % 3];
+    // chunk k: tile rows [t0, t1); padded-array rows uploaded with it: the interior rows of its tiles, chunk 0
+    // also ghost row 0, the last chunk also ghost row Nx+1
+    auto trow = [&](int k) { return (int)((long long)nbx * k / K); };
+    auto rows = [&](int k, size_t* r0, size_t* r1, bool with_ghost) {
+        *r0 = (size_t)trow(k) * TX + 1;
+        *r1 = std::min<size_t>((size_t)trow(k + 1) * TX + 1, (size_t)cfg.Nx + 1);
+        if (with_ghost && k == 0) *r0 = 0;
+        if (with_ghost && k == K - 1) *r1 = Nx2;
+    };
+    cudaEvent_t ev_start = cp_event[2 * 64];
+    GPF_CUDA(cudaEventRecord(ev_start, s));
+    GPF_CUDA(cudaStreamWaitEvent(cp_stream[0], ev_start, 0));
+    GPF_CUDA(cudaStreamWaitEvent(cp_stream[1], ev_start, 0));
+    for (int k = 0; k < K; ++k) {
+        size_t r0, r1;
+        rows(k, &r0, &r1, true);
+        for (int c = 0; c < 3; ++c)
+            GPF_CUDA(cudaMemcpy2DAsync(qin + c * P.L.plane + r0 * pitch + 1, pitch * 8, q_host + (size_t)c * Nx2 * Ny2 + r0 * Ny2,
+                                       Ny2 * 8, Ny2 * 8, r1 - r0, cudaMemcpyHostToDevice, cp_stream[0]));
+        GPF_CUDA(cudaEventRecord(cp_event[k], cp_stream[0]));
+    }
+    const int per = std::max(1, (npartial - 1) / K);         // record slots of one corrector chunk
+    int rec0 = 0;
+    auto corr_chunk = [&](int k) -> int {
+        int used = 0;
+        int r = launch_pass<true>(*this, 0, s, PART_ROWS, trow(k), trow(k + 1) - trow(k), rec0, per, &used);
+        if (r) return r;
+        rec0 += used;
+        GPF_CUDA(cudaEventRecord(cp_event[64 + k], s));
+        GPF_CUDA(cudaStreamWaitEvent(cp_stream[1], cp_event[64 + k], 0));
+        size_t r0, r1;
+        rows(k, &r0, &r1, false);
+        for (int c = 0; c < 3; ++c)
+            GPF_CUDA(cudaMemcpy2DAsync(q_host + (size_t)c * Nx2 * Ny2 + r0 * Ny2, Ny2 * 8, qout + c * P.L.plane + r0 * pitch + 1,
+                                       pitch * 8, Ny2 * 8, r1 - r0, cudaMemcpyDeviceToHost, cp_stream[1]));
+        return GPF_OK;
+    };
+    for (int k = 0; k < K; ++k) {
+        GPF_CUDA(cudaStreamWaitEvent(s, cp_event[k], 0));
+        if ((rc = launch_pass<false>(*this, 0, s, PART_ROWS, trow(k), trow(k + 1) - trow(k), 0, 1 << 30))) return rc;
+        if (k >= 1 && (rc = corr_chunk(k - 1))) return rc;
+    }
+    if ((rc = corr_chunk(K - 1))) return rc;
+    // the two x ghost rows of the new field (written by the first and the last chunk's boundary tiles)
+    cudaEvent_t ev_c = cp_event[2 * 64 + 1];
+    GPF_CUDA(cudaEventRecord(ev_c, s));
+    GPF_CUDA(cudaStreamWaitEvent(cp_stream[1], ev_c, 0));
+    for (int c = 0; c < 3; ++c)
+        for (size_t r : {(size_t)0, Nx2 - 1})
+            GPF_CUDA(cudaMemcpyAsync(q_host + (size_t)c * Nx2 * Ny2 + r * Ny2, qout + c * P.L.plane + r * pitch + 1, Ny2 * 8,
+                                     cudaMemcpyDeviceToHost, cp_stream[1]));
+    if ((rc = launch_finish(*this, nrec_corr, FIN_STEP, 0, s))) return rc;
+    dirty_scalars = false;
+    refresh_valid = false;
+    GPF_CUDA(cudaEventRecord(ev_start, cp_stream[1]));
+    GPF_CUDA(cudaStreamWaitEvent(s, ev_start, 0));           // the caller's stream owns the completed download
     return GPF_OK;
 }
 

@@ -192,7 +192,10 @@ int gpf_fv_closures_of(gpf_fv* s, int which, double* pressure, double* wall_xz, 
                        double* bulk, int on_device, void* stream);
 
 /* One-call host-buffer step for reference-side bindings: uploads q_host (dense, host),
- * runs n x update(), downloads q back, returns the scalars.  Synchronises. */
+ * runs n x update(), downloads q back, returns the scalars.  Synchronises.  For n == 1 (and
+ * MC_order = +1, no viscosity field / surrogate / slab) upload, passes and download are pipelined
+ * over chunks of tile rows on two internal copy streams; same result bit for bit.  Pinned host
+ * memory makes the copies asynchronous (pageable memory works, staged by the driver). */
 int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, void* stream);
 
 /* --- slab decomposition along x (multi-GPU) ---------------------------------------

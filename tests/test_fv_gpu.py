@@ -396,3 +396,51 @@ def test_branch_free_division_equals_ieee():
     _capi.check(lib.gpf_selftest_division(1 << 31, 20251104, out, None))
     assert out[1] == 0, f"{out[1]} quotient mismatches"
     assert out[0] == 0, f"{out[0]} reciprocal mismatches"
+
+
+# ---- host-buffer step with the copies overlapped chunk by chunk (gpf_fv_update_host, n = 1) ---------------
+@pytest.mark.parametrize("arith", ARITH)
+@pytest.mark.parametrize("name,nx,ny", [('journal2d_periodic', 150, 70), ('slider2d_xDN', 130, 65),
+                                        ('slider2d_allDN_slip', 97, 21), ('journal1d_periodic', 100, 1)])
+def test_pipelined_host_step_equals_device_step(name, nx, ny, arith):
+    """gpf_fv_update_host(n = 1) moves the field in chunks of tile rows on two copy streams while the pass
+    kernels follow chunk by chunk (P(0) P(1) C(0) P(2) C(1) ...): bit-identical to gpf_fv_step, ghost rows
+    included, for periodic and Dirichlet / Neumann x sides, ragged last tile rows, and against the oracle."""
+    from gapflow_b200.fv import FVSolver
+    from oracle.fv import FVOracle
+    from tests.cases import perturb, slip_field
+    d, _ = inputs(name)
+    g = d['grid']
+    g['Nx'], g['Ny'] = nx, ny
+    g['Lx'], g['Ly'] = g['dx'] * nx, g['dy'] * ny
+    extra = slip_field((nx + 2, ny + 2), 1e-6) if STEP_CASES[name].get('extra') else None
+    o = FVOracle(g, d['geometry'], d['properties'], d['numerics'], extra=extra)
+    perturb(o.q, d['properties']['rho0'], max(abs(d['geometry']['U']), abs(d['geometry']['V'])), 99)
+    o.fill_ghosts()
+    if d['numerics']['adaptive']:
+        o.dt = d['numerics']['CFL'] * o.dt_crit
+    assert (nx + 7) // 8 >= 8                     # enough tile rows for the chunked path
+    sol = []
+    for _ in range(2):
+        s = FVSolver(g, d['geometry'], d['properties'], d['numerics'], topo=o.topo, extra=extra, arith=arith)
+        s.set_q(o.q)
+        s.pre_run(reset_ekin_old=False)
+        sol.append(s)
+    qh = torch.from_numpy(o.q.copy()).pin_memory().numpy()
+    for n in range(3):
+        sol[0].step(1)
+        sc = sol[1].update_host(qh, 1)
+        assert np.array_equal(qh, sol[0].get_q()), (n, int((qh != sol[0].get_q()).sum()))
+        s0 = sol[0].scalars()
+        assert sc.dt == s0.dt and sc.step == s0.step == n + 1
+        # the kinetic-energy sum is folded chunk by chunk: same value up to the summation order
+        assert np.isclose(sc.ekin, s0.ekin, rtol=1e-13) and np.isclose(sc.residual, s0.residual, rtol=1e-6, atol=1e-14)
+        o.update()
+    assert relerr(qh, o.q) <= 10 * REL_STEP          # three steps of the contracted arithmetic; exact: identical
+    if arith == 'exact':
+        assert np.array_equal(qh, o.q)
+    # pageable host memory takes the same path (the copies are then staged by the driver)
+    qp = sol[0].get_q().copy()
+    sol[0].step(1)
+    sol[1].update_host(qp, 1)
+    assert np.array_equal(qp, sol[0].get_q())
