@@ -56,6 +56,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--coupled-n", type=int, default=1024, help="cells per side of the GP-coupled FV step (0: skip)")
     ap.add_argument("--coupled-steps", type=int, default=3)
+    ap.add_argument("--coupled-only", action="store_true", help="only the GP-coupled step (profiling runs)")
     args = ap.parse_args()
     import numpy as np
     import torch
@@ -74,6 +75,9 @@ def main():
                               "coupled_step": res}))
         dist.barrier()
         dist.destroy_process_group()
+        return
+    if args.coupled_only:
+        print(json.dumps({"metric": "GP-coupled FV cell-updates/s", "coupled_step": coupled_step(torch, np, _capi.load(), args)}))
         return
     from gapflow_b200.gp import GPModel
     from tests.gp_cases import query_set, training_set
