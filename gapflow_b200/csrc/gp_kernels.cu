@@ -293,20 +293,29 @@ __global__ void __launch_bounds__(256) gp_trsv_bwd_kernel(const double* L, int M
 // not need: NOUT = 1 the second output, GRAD = false the slope sum, D = 1 the square root
 // (sqrt(RN(t*t)) == |t| exactly unless t*t leaves the normal range, where both give 0 or inf alike).
 // ------------------------------------------------------------------------------------
+// Two queries per thread (Q = 2: cells i and i + 256 of the block's 512): every shared-memory load of a
+// training point and of its alpha serves two kernel evaluations, which gives the ~13 % of issue slots
+// the loads took (profiles/r1C_ncu_coupled_summary.csv) back to the FP64 pipe.
 template <int D, int NOUT, bool GRAD>
 __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const double* alpha, int M, int Mp, int nout,
                                                       GpKern kp, const double* Xtest, long long N, long long off,
                                                       long long cnt, double* mean, double* gmax_part) {
-    constexpr int TM = 256;
+    constexpr int TM = 256, Q = 2;
     __shared__ double sx[TM * D];
     __shared__ double sa[2][TM];
     __shared__ double sred[8];
-    const long long i = off + (long long)blockIdx.x * 256 + threadIdx.x;
-    const bool valid = i < off + cnt;
-    double x[D];
+    long long i[Q];
+    bool valid[Q];
+    double x[Q][D];
+    double m0[Q], m1[Q], g0[Q];
 #pragma unroll
-    for (int k = 0; k < D; ++k) x[k] = valid ? Xtest[i * D + k] * kp.s[k] : 0.0;
-    double m0 = 0.0, m1 = 0.0, g0 = 0.0;
+    for (int q = 0; q < Q; ++q) {
+        i[q] = off + (long long)blockIdx.x * (256 * Q) + q * 256 + threadIdx.x;
+        valid[q] = i[q] < off + cnt;
+#pragma unroll
+        for (int k = 0; k < D; ++k) x[q][k] = valid[q] ? Xtest[i[q] * D + k] * kp.s[k] : 0.0;
+        m0[q] = m1[q] = g0[q] = 0.0;
+    }
     for (int t0 = 0; t0 < M; t0 += TM) {
         const int n = min(TM, M - t0);
         __syncthreads();
@@ -317,28 +326,38 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
         }
         __syncthreads();
         for (int j = 0; j < n; ++j) {
-            double r;
-            if constexpr (D == 1) {
-                r = SQRT3 * fabs(x[0] - sx[j]);
-            } else {
-                double d2 = 0.0;
+            double xt[D];
 #pragma unroll
-                for (int k = 0; k < D; ++k) { const double t = x[k] - sx[j * D + k]; d2 += t * t; }
-                r = SQRT3 * sqrt(d2);
+            for (int k = 0; k < D; ++k) xt[k] = sx[j * D + k];
+            const double a0 = sa[0][j];
+            const double a1 = NOUT > 1 ? sa[1][j] : 0.0;
+#pragma unroll
+            for (int q = 0; q < Q; ++q) {
+                double r;
+                if constexpr (D == 1) {
+                    r = SQRT3 * fabs(x[q][0] - xt[0]);
+                } else {
+                    double d2 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < D; ++k) { const double t = x[q][k] - xt[k]; d2 += t * t; }
+                    r = SQRT3 * sqrt(d2);
+                }
+                const double e = exp(-r);
+                const double kv = (1.0 + r) * e;
+                m0[q] += a0 * kv;
+                if (NOUT > 1) m1[q] += a1 * kv;
+                if (GRAD) g0[q] += a0 * ((x[q][0] - xt[0]) * e);
             }
-            const double e = exp(-r);
-            const double kv = (1.0 + r) * e;
-            m0 += sa[0][j] * kv;
-            if (NOUT > 1) m1 += sa[1][j] * kv;
-            if (GRAD) g0 += sa[0][j] * ((x[0] - sx[j * D]) * e);
         }
     }
     double g = -INFINITY;
-    if (valid) {
-        mean[i] = kp.amp * m0;
-        if (NOUT > 1) mean[N + i] = kp.amp * m1;
-        g = -3.0 * kp.amp * kp.s[0] * g0;          // d/dx_0 in the (unscaled) normalised input
-    }
+#pragma unroll
+    for (int q = 0; q < Q; ++q)
+        if (valid[q]) {
+            mean[i[q]] = kp.amp * m0[q];
+            if (NOUT > 1) mean[N + i[q]] = kp.amp * m1[q];
+            g = fmax(g, -3.0 * kp.amp * kp.s[0] * g0[q]);      // d/dx_0 in the (unscaled) normalised input
+        }
     if (!GRAD) return;
     // block max (NaN-propagating like jnp.max is not needed: a NaN gradient makes the mean NaN too)
 #pragma unroll
@@ -883,10 +902,10 @@ int GpModel::mean(const double* Xtest, long long N, double* mean_out, double* dm
     if (N < 1) return GPF_OK;
     // at most 65536 partial maxima per launch
     double gmax = -INFINITY;
-    const long long chunk = 65536LL * 256;
+    const long long chunk = 65536LL * 512;                  // 512 queries per block (two per thread)
     for (long long off = 0; off < N; off += chunk) {
         const long long cnt = std::min<long long>(chunk, N - off);
-        const int nbk = (int)((cnt + 255) / 256);
+        const int nbk = (int)((cnt + 511) / 512);
         const bool grad = dmax_host != nullptr;
         switch (D) {
 #define GP_MEAN_LAUNCH(DD, NO, GR) gp_mean_kernel<DD, NO, GR><<<nbk, 256, 0, s>>>(Xs, alpha, M, Mp, nout, kp, Xtest, N, off, cnt, mean_out, gpart)

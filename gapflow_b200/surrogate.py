@@ -265,13 +265,7 @@ class SurrogateModel:
             # gp.py:406, 424 over the GLOBAL padded array: slab-internal halo rows repeat the neighbour's cells
             # bit for bit, so the smallest global index among the maxima is the reference's first maximum
             gidx = self.gp.argmax + self.row0 * self.solver.shape[1]
-            pairs = self.coll.allgather((self.gp._vmax_norm, gidx))
-            v = np.array([a for a, _ in pairs])
-            if np.isnan(v).any():
-                vmax, self.argmax = float('nan'), min(g for a, g in pairs if a != a)
-            else:
-                vmax = float(v.max())
-                self.argmax = min(g for a, g in pairs if a == vmax)
+            vmax, self.argmax = fold_first_maximum(self.coll.allgather((self.gp._vmax_norm, gidx)))
             self.maximum_variance = vmax * ys**2
             self.variance_tol = max(self.atol * self.Yerr * ys, self.rtol * ys)**2
         else:
@@ -313,6 +307,17 @@ class SurrogateModel:
         gs = np.array(self.coll.allgather(g))
         g = float('nan') if np.isnan(gs).any() else float(gs.max())
         return g * self.Yscale / float(self.database.X_scale[0])
+
+
+def fold_first_maximum(pairs):
+    """(value, global index) of the first maximum from every rank's (local maximum, its global index): what
+    jnp.max / np.argmax return on the whole array (gp.py:406, 424) -- NaN propagates and wins, ties go to the
+    smallest index (cells that several ranks hold carry the same value bit for bit)."""
+    v = np.array([a for a, _ in pairs], dtype=float)
+    if np.isnan(v).any():
+        return float('nan'), min(int(g) for a, g in pairs if a != a)
+    vmax = float(v.max())
+    return vmax, min(int(g) for a, g in pairs if a == vmax)
 
 
 class LocalColl:

@@ -125,3 +125,86 @@ def test_owned_rows_partition_every_row_once():
             rows = [owned_rows(Nx, r, w) for r in range(w)]
             assert rows[0][0] == 0 and rows[-1][1] == Nx + 2
             assert all(rows[r][1] == rows[r + 1][0] for r in range(w - 1))
+
+
+# ---- host-level folds of the slab-decomposed GP-coupled step (gapflow_b200/surrogate.py) -------------------
+def test_fold_first_maximum_matches_numpy_argmax():
+    """(max, argmax) of a global array from per-rank (local max, global index of its first occurrence), with
+    overlapping (halo) rows, ties and NaN -- jnp.max / np.argmax semantics (gp.py:406, 424)."""
+    from gapflow_b200.surrogate import fold_first_maximum
+    rng = np.random.default_rng(5)
+    for trial in range(50):
+        n, w = 40, 4
+        v = np.round(rng.random(n), 1)                       # many ties
+        if trial % 7 == 0:
+            v[rng.integers(n)] = np.nan
+        bounds = [(max(0, r * 10 - 1), min(n, (r + 1) * 10 + 1)) for r in range(w)]     # one overlapping cell per side
+        pairs = []
+        for a, b in bounds:
+            loc = v[a:b]
+            k = int(np.argmax(loc))                          # np.argmax: first maximum, NaN wins
+            pairs.append((float(loc[k]), a + k))
+        vmax, imax = fold_first_maximum(pairs)
+        assert imax == int(np.argmax(v)), (trial, pairs)
+        assert (np.isnan(vmax) and np.isnan(np.max(v))) or vmax == np.max(v)
+
+
+def test_thread_collective_allgather_and_exchanger():
+    """ThreadColl: rank-ordered all-gather between threads and the halo / record exchange built on it (CPU tensors)."""
+    import threading
+    import torch
+    from gapflow_b200.surrogate import ThreadColl
+    world = 3
+    tc = ThreadColl(world)
+    out = [None] * world
+
+    def work(r):
+        c = tc.view(r)
+        got = [c.allgather((r, k)) for k in range(5)]
+        ex = tc.exchanger(r, periodic=True)
+        send = torch.full((2, 3, 4), float(r), dtype=torch.float64)
+        send[1] += 0.5                                       # [0] goes down, [1] goes up
+        recv = torch.zeros_like(send)
+        ex.exchange(send, recv)
+        recs = torch.zeros((world, 5), dtype=torch.float64)
+        ex.gather(torch.full((5,), float(r), dtype=torch.float64), recs)
+        out[r] = (got, recv, recs)
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join(60) for t in th]
+    for r in range(world):
+        got, recv, recs = out[r]
+        assert got == [[(q, k) for q in range(world)] for k in range(5)]
+        lo, hi = (r - 1) % world, (r + 1) % world
+        assert torch.all(recv[0] == lo + 0.5) and torch.all(recv[1] == float(hi))      # lower neighbour's last row, upper's first
+        assert torch.equal(recs, torch.arange(world, dtype=torch.float64)[:, None].expand(world, 5))
+
+
+def _gloo_coll_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from gapflow_b200.surrogate import DistColl, fold_first_maximum
+    c = DistColl()
+    pairs = c.allgather((float(rank % 2), 10 * rank))
+    rows = c.allgather(None if rank == 0 else np.full(7, float(rank)))
+    q.put((rank, fold_first_maximum(pairs), next(r for r in rows if r is not None)[0]))
+    dist.destroy_process_group()
+
+
+def test_dist_collective_over_gloo():
+    """DistColl (torch.distributed all_gather_object) gives every rank the same fold: world_size 2, gloo."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_gloo_coll_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = sorted(q.get(timeout=120) for _ in ps)
+    [p.join(60) for p in ps]
+    assert res == [(0, (1.0, 10), 1.0), (1, (1.0, 10), 1.0)]
