@@ -1,6 +1,8 @@
 // extern "C" boundary of libgapflow_b200.so (see include/gapflow_b200.h).
+#include <cmath>
 #include <cstring>
 #include <new>
+#include <vector>
 #include <string>
 #include "fv_host.h"
 #include "gp_host.h"
@@ -332,6 +334,25 @@ int gpf_gp_mean_var(gpf_gp* g, const double* Xtest, int64_t N, const double* noi
     int rc = g->G.mean_var(Xtest, N, noise, noise_scalar, mean, var, var_max, arg_max ? &im : nullptr, (cudaStream_t)stream);
     if (arg_max) *arg_max = im;
     return rc;
+    GPF_CATCH
+}
+int gpf_selftest_mean1d_host(const double* Xtrain, int M, double log_amp, double log_scale, const double* alpha,
+                             const double* Xtest, int64_t N, double* mean, double* dmean_dx0) {
+    GPF_TRY
+    if (!Xtrain || !alpha || !Xtest || !mean || M < 1 || N < 0) { set_error("bad arguments"); return GPF_E_INVALID; }
+    const double s = exp(-log_scale), amp = exp(log_amp);
+    std::vector<double> u(M);
+    for (int j = 0; j < M; ++j) u[j] = Xtrain[j] * s;
+    Mean1DHost H;
+    H.build(u.data(), alpha, M);
+    const Mean1D T = H.view();
+    for (int64_t i = 0; i < N; ++i) {
+        double m, g;
+        mean1d_eval(T, Xtest[i] * s, &m, &g);
+        mean[i] = amp * m;
+        if (dmean_dx0) dmean_dx0[i] = -3.0 * amp * s * g;
+    }
+    return GPF_OK;
     GPF_CATCH
 }
 int gpf_gp_features(gpf_fv* s, const double* x_scale, const int32_t* active_dims, int D, double* X, void* stream) {

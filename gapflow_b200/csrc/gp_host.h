@@ -1,7 +1,9 @@
 // Host-side GP model object behind the opaque gpf_gp handle.
 #pragma once
 #include <cuda_runtime.h>
+#include <vector>
 #include "gpf_types.h"
+#include "gp_mean1d.h"
 
 namespace gpf {
 
@@ -27,6 +29,13 @@ struct GpModel {
     double* vpart;       // per-CTA variance maxima
     long long* ipart;    // per-CTA arg-maxima
     double* scal;        // result scalars
+    // one-input, one-output models (the pressure GP on the density): O(log M) mean (gp_mean1d.h)
+    double* t1d;         // 5 Mp doubles: u, A, B, C, D
+    int* t1d_i;          // Mp + Mp + 1 ints: blk, bstart
+    std::vector<double> u_host;      // scaled training inputs of the last factorisation (D == 1)
+    bool t1d_valid = false;          // tables match the last factorisation
+    Mean1D t1d_view;
+    int build_mean1d(cudaStream_t s);
 
     static size_t workspace_bytes(int Mmax, int D, int nout, int nslots);
     int init(int Mmax, int D, int nout, void* ws, size_t bytes);

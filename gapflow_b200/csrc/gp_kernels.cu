@@ -759,6 +759,7 @@ size_t GpModel::workspace_bytes(int Mmax, int D, int nout, int nslots) {
     b += al(Mp * 2 * 8);                 // copy of the right-hand sides (training loss)
     b += al((size_t)nslots * Mp * NQ * 8);   // v panels of the variance kernel
     b += al(65536 * 8) + al(4096 * 8) + al(4096 * 8) + 256;   // partial maxima, argmax parts, scalars
+    b += al(Mp * 5 * 8) + al((2 * Mp + 1) * 4);               // tables of the one-input mean (gp_mean1d.h)
     (void)nout;
     return b;
 }
@@ -782,7 +783,10 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
     gpart = reinterpret_cast<double*>(p); p += al(65536 * 8);
     vpart = reinterpret_cast<double*>(p); p += al(4096 * 8);
     ipart = reinterpret_cast<long long*>(p); p += al(4096 * 8);
-    scal = reinterpret_cast<double*>(p);
+    scal = reinterpret_cast<double*>(p); p += 256;
+    t1d = reinterpret_cast<double*>(p); p += al(Mpm * 5 * 8);
+    t1d_i = reinterpret_cast<int*>(p);
+    t1d_valid = false;
     return GPF_OK;
 }
 
@@ -800,6 +804,8 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
         for (int k = 0; k < D; ++k) xs[(size_t)i * D + k] = Xtrain[(size_t)i * D + k] * kp.s[k];
     for (int i = 0; i < M; ++i)
         for (int o = 0; o < nout; ++o) y[(size_t)o * Mp + i] = Y[(size_t)i * nout + o];
+    t1d_valid = false;
+    if (D == 1) u_host.assign(xs.begin(), xs.begin() + M);
     GPF_CUDA(cudaMemcpyAsync(Xs, xs.data(), xs.size() * 8, cudaMemcpyHostToDevice, s));
     GPF_CUDA(cudaMemcpyAsync(alpha, y.data(), (size_t)Mp * 2 * 8, cudaMemcpyHostToDevice, s));
     GPF_CUDA(cudaMemcpyAsync(ycopy, y.data(), (size_t)Mp * 2 * 8, cudaMemcpyHostToDevice, s));
@@ -897,9 +903,79 @@ int GpModel::get_factor(double* L_out, double* alpha_out, cudaStream_t s) {
     return GPF_OK;
 }
 
+// ---- one-input models: O(log M) mean per query (gp_mean1d.h) ---------------------------------------------
+template <bool GRAD>
+__global__ void __launch_bounds__(256) gp_mean1d_kernel(Mean1D T, GpKern kp, const double* Xtest, long long N, long long off,
+                                                        long long cnt, double* mean, double* gmax_part) {
+    __shared__ double sred[8];
+    const long long i = off + (long long)blockIdx.x * 256 + threadIdx.x;
+    double g = -INFINITY;
+    if (i < off + cnt) {
+        double m, gs;
+        mean1d_eval(T, Xtest[i] * kp.s[0], &m, &gs);
+        mean[i] = kp.amp * m;
+        g = -3.0 * kp.amp * kp.s[0] * gs;
+    }
+    if (!GRAD) return;
+#pragma unroll
+    for (int oo = 16; oo > 0; oo >>= 1) g = fmax(g, __shfl_xor_sync(0xffffffffu, g, oo));
+    if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = g;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int ww = 1; ww < 8; ++ww) g = fmax(g, sred[ww]);
+        gmax_part[blockIdx.x] = g;
+    }
+}
+
+// tables of the last factorisation: alpha comes back from the device (M doubles), the running sums are built on
+// the host (M log M, long double) and go up again (5 M doubles)
+int GpModel::build_mean1d(cudaStream_t s) {
+    std::vector<double> a(M);
+    GPF_CUDA(cudaMemcpyAsync(a.data(), alpha, (size_t)M * 8, cudaMemcpyDeviceToHost, s));
+    GPF_CUDA(cudaStreamSynchronize(s));
+    Mean1DHost H;
+    H.build(u_host.data(), a.data(), M);
+    const size_t Mpm = (size_t)(Mmax + NB - 1) / NB * NB;
+    double* d[5] = {t1d, t1d + Mpm, t1d + 2 * Mpm, t1d + 3 * Mpm, t1d + 4 * Mpm};
+    const std::vector<double>* h[5] = {&H.u, &H.A, &H.B, &H.C, &H.D};
+    for (int k = 0; k < 5; ++k) GPF_CUDA(cudaMemcpyAsync(d[k], h[k]->data(), (size_t)M * 8, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaMemcpyAsync(t1d_i, H.blk.data(), (size_t)M * 4, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaMemcpyAsync(t1d_i + Mpm, H.bstart.data(), H.bstart.size() * 4, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaStreamSynchronize(s));                  // the host vectors go out of scope
+    t1d_view.M = M; t1d_view.nb = (int)H.bstart.size() - 1;
+    t1d_view.u = d[0]; t1d_view.A = d[1]; t1d_view.B = d[2]; t1d_view.C = d[3]; t1d_view.D = d[4];
+    t1d_view.blk = t1d_i; t1d_view.bstart = t1d_i + Mpm;
+    t1d_valid = true;
+    return GPF_OK;
+}
+
 int GpModel::mean(const double* Xtest, long long N, double* mean_out, double* dmax_host, cudaStream_t s) {
     if (M < 1) { set_error("no factorisation"); return GPF_E_STATE; }
     if (N < 1) return GPF_OK;
+    static const bool use1d = [] { const char* e = getenv("GPF_GP_MEAN1D"); return !e || atoi(e) != 0; }();
+    if (D == 1 && nout == 1 && use1d) {
+        if (!t1d_valid) { const int rc = build_mean1d(s); if (rc) return rc; }
+        double gmax = -INFINITY;
+        const long long chunk = 65536LL * 256;
+        for (long long off = 0; off < N; off += chunk) {
+            const long long cnt = std::min<long long>(chunk, N - off);
+            const int nbk = (int)((cnt + 255) / 256);
+            if (dmax_host) gp_mean1d_kernel<true><<<nbk, 256, 0, s>>>(t1d_view, kp, Xtest, N, off, cnt, mean_out, gpart);
+            else gp_mean1d_kernel<false><<<nbk, 256, 0, s>>>(t1d_view, kp, Xtest, N, off, cnt, mean_out, gpart);
+            g_launches += 1;
+            if (dmax_host) {
+                gp_max_reduce_kernel<<<1, 256, 0, s>>>(gpart, nbk, scal);
+                g_launches += 1;
+                double g;
+                GPF_CUDA(cudaMemcpyAsync(&g, scal, 8, cudaMemcpyDeviceToHost, s));
+                GPF_CUDA(cudaStreamSynchronize(s));
+                gmax = std::fmax(gmax, g);
+            }
+        }
+        GPF_CUDA(cudaGetLastError());
+        if (dmax_host) *dmax_host = gmax;
+        return GPF_OK;
+    }
     // at most 65536 partial maxima per launch
     double gmax = -INFINITY;
     const long long chunk = 65536LL * 512;                  // 512 queries per block (two per thread)

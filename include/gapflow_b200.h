@@ -358,6 +358,14 @@ int gpf_fv_get_timing(gpf_fv* s, double* ms_predictor, double* ms_corrector, int
  * (__drcp_rn, __ddiv_rn).  mismatches[0]: reciprocal, [1]: quotient.  Synchronises. */
 int gpf_selftest_division(uint64_t n, uint64_t seed, uint64_t mismatches[2], void* stream);
 
+/* Self-test, HOST arithmetic only (no device call): the O(log M) mean of a one-input, one-output model
+ * (csrc/gp_mean1d.h: sorted training points, blockwise running sums, bisection per query) evaluated by
+ * the same inline routine the device kernel calls.  gpf_gp_mean takes this route whenever D = 1 and
+ * n_out = 1 (GPF_GP_MEAN1D=0 restores the O(M) kernel).  Xtrain (M), alpha (M), Xtest (N): normalised,
+ * unscaled inputs as for gpf_gp_factor / gpf_gp_mean; mean (N), dmean_dx0 (N) or NULL. */
+int gpf_selftest_mean1d_host(const double* Xtrain, int M, double log_amp, double log_scale, const double* alpha,
+                             const double* Xtest, int64_t N, double* mean, double* dmean_dx0);
+
 #ifdef __cplusplus
 }
 #endif
