@@ -22,7 +22,6 @@ seeded design in ``Database.initialize``); tinygp's conditioned-GP jitter is ``T
 oracle/surrogate.py, which restates the same step in NumPy for the tests.
 """
 import ctypes as C
-from collections import deque
 
 import numpy as np
 import torch

@@ -223,11 +223,9 @@ def test_surrogate_refusals():
     """viscosity-field solvers and slab solvers have no surrogate variant: loud errors, not silent fixed-form."""
     from gapflow_b200 import _capi
     from gapflow_b200.fv import FVSolver
-    from tests.cases import build_case, inputs
+    from tests.cases import VISC_CASES, build_case, inputs
     lib = _capi.load()
-    name = 'visc_barus' if 'visc_barus' in __import__('tests.cases', fromlist=['VISC_CASES']).VISC_CASES else None
-    if name is None:
-        name = next(iter(__import__('tests.cases', fromlist=['VISC_CASES']).VISC_CASES))
+    name = VISC_CASES[0]
     d, extra = inputs(name)
     o = build_case(name)
     s = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=o.topo, extra=extra)
