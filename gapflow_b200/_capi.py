@@ -119,6 +119,7 @@ SIGNATURES = {
     "gpf_fv_set_surrogate": (_i, [_vp, _dp, C.c_double, _dp, C.c_double, _dp, C.c_double]),
     "gpf_fv_finish_surrogate": (_i, [_vp, _i, _dp, _i, C.c_double, _vp]),
     "gpf_selftest_mean1d_host": (_i, [_dp, _i, C.c_double, C.c_double, _dp, _dp, C.c_int64, _dp, _dp]),
+    "gpf_selftest_var1d_host": (_i, [_dp, _i, C.c_double, C.c_double, C.c_double, _dp, C.c_int64, C.c_double, _dp]),
     "gpf_selftest_division": (_i, [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), _vp]),
 }
 

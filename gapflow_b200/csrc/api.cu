@@ -355,6 +355,20 @@ int gpf_selftest_mean1d_host(const double* Xtrain, int M, double log_amp, double
     return GPF_OK;
     GPF_CATCH
 }
+int gpf_selftest_var1d_host(const double* Xtrain, int M, double log_amp, double log_scale, double yerr,
+                            const double* Xtest, int64_t N, double noise, double* var) {
+    GPF_TRY
+    if (!Xtrain || !Xtest || !var || M < 1 || N < 0) { set_error("bad arguments"); return GPF_E_INVALID; }
+    const double s = exp(-log_scale);
+    std::vector<double> u(M);
+    for (int j = 0; j < M; ++j) u[j] = Xtrain[j] * s;
+    Var1DHost H;
+    H.build(u.data(), M, exp(log_amp), yerr);
+    const Var1D T = H.view();
+    for (int64_t i = 0; i < N; ++i) var[i] = var1d_eval(T, Xtest[i] * s) + noise;
+    return GPF_OK;
+    GPF_CATCH
+}
 int gpf_gp_features(gpf_fv* s, const double* x_scale, const int32_t* active_dims, int D, double* X, void* stream) {
     GPF_TRY NEED(s && x_scale && active_dims && X) return launch_gp_features(s->S, x_scale, active_dims, D, X, (cudaStream_t)stream); GPF_CATCH
 }

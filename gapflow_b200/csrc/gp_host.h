@@ -4,6 +4,7 @@
 #include <vector>
 #include "gpf_types.h"
 #include "gp_mean1d.h"
+#include "gp_var1d.h"
 
 namespace gpf {
 

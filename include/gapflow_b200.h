@@ -366,6 +366,14 @@ int gpf_selftest_division(uint64_t n, uint64_t seed, uint64_t mismatches[2], voi
 int gpf_selftest_mean1d_host(const double* Xtrain, int M, double log_amp, double log_scale, const double* alpha,
                              const double* Xtest, int64_t N, double* mean, double* dmean_dx0);
 
+/* Self-test, HOST arithmetic only: the O(log M) predictive variance of a one-input model (csrc/gp_var1d.h:
+ * the one-dimensional Matern-3/2 process as a two-state Markov process, Kalman sweeps from both ends of the
+ * sorted training points, two-filter combination per query), by the same inline routine as the device kernel
+ * that gpf_gp_mean_var uses for D = 1 when GPF_GP_VAR1D=1 is set (opt-in until it has been run on a B200).
+ * var (N) = posterior variance + noise, i.e. gp.py:509-522's `Kss - sum(v**2)`. */
+int gpf_selftest_var1d_host(const double* Xtrain, int M, double log_amp, double log_scale, double yerr,
+                            const double* Xtest, int64_t N, double noise, double* var);
+
 #ifdef __cplusplus
 }
 #endif
