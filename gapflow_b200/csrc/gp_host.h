@@ -37,6 +37,12 @@ struct GpModel {
     bool t1d_valid = false;          // tables match the last factorisation
     Mean1D t1d_view;
     int build_mean1d(cudaStream_t s);
+    // O(log M) variance of one-input models (gp_var1d.h); opt-in (GPF_GP_VAR1D=1)
+    double* v1d;         // 7 Mp doubles: u, Pf (3), Pb (3)
+    double yerr_last = 0.0;
+    bool v1d_valid = false;
+    Var1D v1d_view;
+    int build_var1d(cudaStream_t s);
 
     static size_t workspace_bytes(int Mmax, int D, int nout, int nslots);
     int init(int Mmax, int D, int nout, void* ws, size_t bytes);

@@ -760,6 +760,7 @@ size_t GpModel::workspace_bytes(int Mmax, int D, int nout, int nslots) {
     b += al((size_t)nslots * Mp * NQ * 8);   // v panels of the variance kernel
     b += al(65536 * 8) + al(4096 * 8) + al(4096 * 8) + 256;   // partial maxima, argmax parts, scalars
     b += al(Mp * 5 * 8) + al((2 * Mp + 1) * 4);               // tables of the one-input mean (gp_mean1d.h)
+    b += al(Mp * 7 * 8);                                      // tables of the one-input variance (gp_var1d.h)
     (void)nout;
     return b;
 }
@@ -785,8 +786,10 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
     ipart = reinterpret_cast<long long*>(p); p += al(4096 * 8);
     scal = reinterpret_cast<double*>(p); p += 256;
     t1d = reinterpret_cast<double*>(p); p += al(Mpm * 5 * 8);
-    t1d_i = reinterpret_cast<int*>(p);
+    t1d_i = reinterpret_cast<int*>(p); p += al((2 * Mpm + 1) * 4);
+    v1d = reinterpret_cast<double*>(p);
     t1d_valid = false;
+    v1d_valid = false;
     return GPF_OK;
 }
 
@@ -805,6 +808,8 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
     for (int i = 0; i < M; ++i)
         for (int o = 0; o < nout; ++o) y[(size_t)o * Mp + i] = Y[(size_t)i * nout + o];
     t1d_valid = false;
+    v1d_valid = false;
+    yerr_last = yerr;
     if (D == 1) u_host.assign(xs.begin(), xs.begin() + M);
     GPF_CUDA(cudaMemcpyAsync(Xs, xs.data(), xs.size() * 8, cudaMemcpyHostToDevice, s));
     GPF_CUDA(cudaMemcpyAsync(alpha, y.data(), (size_t)Mp * 2 * 8, cudaMemcpyHostToDevice, s));
@@ -1008,15 +1013,70 @@ int GpModel::mean(const double* Xtest, long long N, double* mean_out, double* dm
     return GPF_OK;
 }
 
+// ---- one-input models: O(log M) variance per query (gp_var1d.h), opt-in ----------------------------------
+// grid-stride over the queries; per block the largest variance and the index of its first occurrence (NaN wins,
+// like np.argmax), folded by gp_argmax_reduce_kernel exactly as the dense kernel's per-CTA records are
+__global__ void __launch_bounds__(256) gp_var1d_kernel(Var1D T, GpKern kp, const double* Xtest, long long N,
+                                                       const double* noise, double noise_scalar, double* var,
+                                                       double* vpart, long long* ipart) {
+    __shared__ double sv[256];
+    __shared__ long long si[256];
+    double b = -INFINITY;
+    long long bi = 0x7fffffffffffffffLL;
+    bool nanv = false;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < N; i += (long long)gridDim.x * 256) {
+        const double v = var1d_eval(T, Xtest[i] * kp.s[0]) + (noise ? noise[i] : noise_scalar);
+        var[i] = v;
+        if (v != v) { if (!nanv) { nanv = true; b = v; bi = i; } continue; }     // i ascends: the first NaN stays
+        if (!nanv && v > b) { b = v; bi = i; }                                   // strict: the first maximum stays
+    }
+    sv[threadIdx.x] = b;
+    si[threadIdx.x] = bi;
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    nanv = false; b = -INFINITY; bi = 0x7fffffffffffffffLL;
+    for (int t = 0; t < 256; ++t) {
+        const double v = sv[t];
+        if (v != v) { if (!nanv || si[t] < bi) { nanv = true; b = v; bi = si[t]; } continue; }
+        if (nanv) continue;
+        if (v > b || (v == b && si[t] < bi)) { b = v; bi = si[t]; }
+    }
+    vpart[blockIdx.x] = b;
+    ipart[blockIdx.x] = bi;
+}
+
+int GpModel::build_var1d(cudaStream_t s) {
+    Var1DHost H;
+    H.build(u_host.data(), M, kp.amp, yerr_last);
+    const size_t Mpm = (size_t)(Mmax + NB - 1) / NB * NB;
+    GPF_CUDA(cudaMemcpyAsync(v1d, H.u.data(), (size_t)M * 8, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaMemcpyAsync(v1d + Mpm, H.Pf.data(), (size_t)3 * M * 8, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaMemcpyAsync(v1d + 4 * Mpm, H.Pb.data(), (size_t)3 * M * 8, cudaMemcpyHostToDevice, s));
+    GPF_CUDA(cudaStreamSynchronize(s));                  // the host vectors go out of scope
+    v1d_view.M = M; v1d_view.amp = kp.amp;
+    v1d_view.u = v1d; v1d_view.Pf = v1d + Mpm; v1d_view.Pb = v1d + 4 * Mpm;
+    v1d_valid = true;
+    return GPF_OK;
+}
+
 int GpModel::mean_var(const double* Xtest, long long N, const double* noise, double noise_scalar, double* mean_out,
                       double* var_out, double* vmax_host, long long* imax_host, cudaStream_t s) {
     int rc = mean(Xtest, N, mean_out, nullptr, s);
     if (rc) return rc;
     if (N < 1) return GPF_OK;
-    const long long ntiles = (N + NQ - 1) / NQ;
-    const int grid = (int)std::min<long long>(ntiles, nslots);
-    gp_var_kernel<<<grid, 256, VAR_SMEM, s>>>(L, Dinv, Xs, M, Mp, kp, Xtest, N, noise, noise_scalar, var_out, scratch, vpart,
-                                              ipart);
+    // opt-in until it has been run on a B200 (the host instantiation of the routine is tested on the CPU)
+    static const bool use1d = [] { const char* e = getenv("GPF_GP_VAR1D"); return e && atoi(e) != 0; }();
+    int grid;
+    if (D == 1 && use1d) {
+        if (!v1d_valid && (rc = build_var1d(s))) return rc;
+        grid = (int)std::min<long long>((N + 255) / 256, 4096);
+        gp_var1d_kernel<<<grid, 256, 0, s>>>(v1d_view, kp, Xtest, N, noise, noise_scalar, var_out, vpart, ipart);
+    } else {
+        const long long ntiles = (N + NQ - 1) / NQ;
+        grid = (int)std::min<long long>(ntiles, nslots);
+        gp_var_kernel<<<grid, 256, VAR_SMEM, s>>>(L, Dinv, Xs, M, Mp, kp, Xtest, N, noise, noise_scalar, var_out, scratch, vpart,
+                                                  ipart);
+    }
     gp_argmax_reduce_kernel<<<1, 32, 0, s>>>(vpart, ipart, grid, scal + 1, reinterpret_cast<long long*>(scal + 2));
     g_launches += 2;
     GPF_CUDA(cudaGetLastError());
