@@ -142,3 +142,16 @@ def test_train_reaches_the_oracle_optimum():
     L, a = gp.get_factor()
     Lr = G.build(c['X'], c['Yerr'], la, ls)
     assert np.abs(L - Lr).max() <= 1e-9 * np.abs(Lr).max()
+
+
+def test_optin_one_input_variance_kernel_vs_oracle():
+    """GPF_GP_VAR1D=1 (read once per process, hence the subprocess): the O(log M) two-filter variance of one-input
+    models (csrc/gp_var1d.h) on the device against the oracle's dense solve -- 1e-10 of the amplitude, same arg-max."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, GPF_GP_VAR1D="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "var1d_check.py")], capture_output=True, text=True,
+                       timeout=300, env=env, cwd=root)
+    assert r.returncode == 0 and "VAR1D_CHECK_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

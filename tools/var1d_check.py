@@ -23,3 +23,5 @@ for M, model in ((300, 'press_wide'), (2000, 'press')):
     print(f"VAR1D={os.environ.get('GPF_GP_VAR1D', '0')} M={M}: max|var-oracle|/amp {np.abs(v - vr).max():.3e}, "
           f"mean err {np.abs(m.cpu().numpy() - mr).max() / np.abs(mr).max():.3e}, "
           f"argmax {g.argmax} vs {int(np.argmax(vr))}, vmax {g._vmax_norm:.6e} vs {vr.max():.6e}")
+    assert np.abs(v - vr).max() <= 1e-10 * np.exp(c['log_amp']) and g.argmax == int(np.argmax(vr))
+print("VAR1D_CHECK_OK")
