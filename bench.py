@@ -1,18 +1,30 @@
 #!/usr/bin/env python
-"""Benchmark of the FV hot path (BASELINE.json metric: FV cell-updates/s, % HBM roofline).
+"""Benchmark of the hot path (BASELINE.json metric: FV cell-updates/s as a fraction of the HBM
+roofline at 1/2/4/8 B200; GP predictions/s).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-Workload at N=1: BASELINE config 2, the 2D parabolic slider bearing on 4096 x 4096 cells,
-FP64, Dowson-Higginson EOS, fixed-form stresses, x: Dirichlet(rho)/Neumann(jx, jy), y
-periodic, adaptive time step.  N>1: the same slider slab-decomposed
-along x with 4096 x 4096 cells per GPU (weak scaling).
+Headline workload (every N, also N = 1): BASELINE config 5, the north_star target grid -- the
+periodic 2D journal bearing of tests/test_flip_axes.py:30-65 scaled to 8192 x 8192 cells PER
+GPU (dx = dy = 1e-5, DH EOS with C1 = 3.5e10, adaptive CFL = 0.5), slab-decomposed along x
+into a ring for N > 1 (weak scaling).
 
 One "step" = one Problem.update(): predictor pass + corrector pass (+ temporal average,
 validity test, reductions) + the scalar bookkeeping kernel.  `value` times K steps with the
-fields resident in HBM; `e2e` times the host-buffer entry point (pinned host q uploaded
-and downloaded every step).  The oracle is used only for the cpu_baseline / --impl
-reference legs.
+fields resident in HBM; `e2e` times the host-buffer entry point (pinned host q uploaded and
+downloaded every step).  Extra blocks of the same JSON line:
+
+  slab_parity   N > 1: before the timed region, 3 steps of a 2048*N x 2048 journal on the N slabs
+                (real processes, peer memory over NVLink) against the single-domain run of rank 0,
+                compared bit for bit on the device
+  slider4096    N = 1: BASELINE config 2 (round 1's headline workload), same measurement
+  variants      N = 1: the general kernel (dh/dy != 0), the slip-length (LS) and the
+                viscosity-field (VF) variants at 4096^2
+  other_arith   N = 1: the other arithmetic contract on the headline workload
+  gp            N = 1: BASELINE config 4 -- GP predictions/s (mean; mean + variance), Cholesky
+                factorisation, training objective, against a same-run cuBLAS DGEMM rate
+
+The oracle is used only for the cpu_baseline / --impl reference legs.
 """
 import argparse
 import json
@@ -25,9 +37,52 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-N_CELLS_1D = 4096            # cells per GPU per axis
+N_CELLS_1D = 8192            # cells per GPU per axis of the headline workload (BASELINE config 5)
+N_SLIDER = 4096              # BASELINE config 2
 BYTES_PER_CELL_UPDATE = 168  # 21 doubles (pass 1: 9, pass 2: 12)
 BYTES_PRED, BYTES_CORR = 72, 96
+PERTURBATION = ("rho *= 1 + 1e-6 N(0,1), jx, jy += 1e-3 rho0 |U| N(0,1), one generator per 256 global rows, seed 1234 "
+                "(SURVEY 8(d) writes 1e-4 for rho; with C1 = 3.5e10 that is |v| ~ 1e5 m/s and an invalid first step)")
+
+_DH = """
+properties:
+    shear: 0.0794
+    bulk: 0.
+    EOS: DH
+    P0: 101325.
+    rho0: 877.7007
+    C1: 3.5e10
+    C2: 1.23
+"""
+
+JOURNAL_YAML = """
+options:
+    output: data/bench
+    write_freq: 1000000
+    silent: True
+grid:
+    dx: 1.e-5
+    dy: 1.e-5
+    Nx: {Nx}
+    Ny: {Ny}
+    xE: ['P', 'P', 'P']
+    xW: ['P', 'P', 'P']
+    yS: ['P', 'P', 'P']
+    yN: ['P', 'P', 'P']
+geometry:
+    type: journal
+    CR: 1.e-2
+    eps: 0.7
+    U: {U}
+    V: {V}
+    flip: {flip}
+numerics:
+    CFL: 0.5
+    adaptive: 1
+    tol: 1e-30
+    dt: 1e-10
+    max_it: 100000000
+""" + _DH
 
 SLIDER_YAML = """
 options:
@@ -54,36 +109,36 @@ geometry:
 numerics:
     CFL: 0.45
     adaptive: 1
-    tol: 1e-12
+    tol: 1e-30
     dt: 1e-10
     max_it: 100000000
-properties:
-    shear: 0.0794
-    bulk: 0.
-    EOS: DH
-    P0: 101325.
-    rho0: 877.7007
-    C1: 3.5e10
-    C2: 1.23
-"""
+""" + _DH
 
 
-def slider_inputs(Nx, Ny):
+def journal_inputs(Nx, Ny, flip=False):
+    """tests/test_flip_axes.py:30-65 scaled; ``flip``: the test's second problem (axes swapped, dh/dy != 0)."""
     from gapflow_b200 import config
-    return config.read_yaml_string(SLIDER_YAML.format(Nx=Nx, Ny=Ny, Lx=0.0762 * Nx / Ny))
+    u, v = ("0.", "0.1") if flip else ("0.1", "0.")
+    return config.read_yaml_string(JOURNAL_YAML.format(Nx=Nx, Ny=Ny, U=u, V=v, flip=bool(flip)))
+
+
+def slider_inputs(Nx, Ny, extra_prop=""):
+    from gapflow_b200 import config
+    return config.read_yaml_string(SLIDER_YAML.format(Nx=Nx, Ny=Ny, Lx=0.0762 * Nx / Ny) + extra_prop)
 
 
 def initial_fields(d, seed=1234, rows=None):
     """_initialize + the seeded perturbation + topography, host NumPy.
 
     ``rows=(a, b)``: padded x-rows a..b-1 of the global field only (one rank's slab).  The
-    perturbation is drawn per global row from its own generator, so every decomposition sees
+    perturbation is drawn per global row block from its own generator, so every decomposition sees
     the same global field; ghost cells are filled by the solver afterwards."""
     import numpy as np
     from gapflow_b200.topography import make_topography
     g, geo, prop = d['grid'], d['geometry'], d['properties']
     a, b = rows if rows is not None else (0, g['Nx'] + 2)
     shape = (b - a, g['Ny'] + 2)
+    umag = max(abs(geo['U']), abs(geo['V']))
     q = np.empty((3, *shape))
     q[0] = prop['rho0']
     q[1] = prop['rho0'] * geo['U'] / 2.0
@@ -95,8 +150,8 @@ def initial_fields(d, seed=1234, rows=None):
         lo, hi = max(a, b0), min(b, b0 + blk)
         sl, ns = slice(lo - a, hi - a), slice(lo - b0, hi - b0)
         q[0, sl] *= 1 + 1e-6 * n[0, ns]
-        q[1, sl] += 1e-3 * prop['rho0'] * geo['U'] * n[1, ns]
-        q[2, sl] += 1e-3 * prop['rho0'] * geo['U'] * n[2, ns]
+        q[1, sl] += 1e-3 * prop['rho0'] * umag * n[1, ns]
+        q[2, sl] += 1e-3 * prop['rho0'] * umag * n[2, ns]
     return q, make_topography(g, geo, rows=rows)
 
 
@@ -153,10 +208,10 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 def cpu_steps(n_side, steps, warmup):
     """Times the NumPy oracle (port of the reference's update loop, 1 core: NumPy ufuncs are
-    single-threaded and so is the reference) on an n_side^2 sample of the slider workload."""
+    single-threaded and so is the reference) on an n_side^2 sample of the headline journal."""
     import numpy as np
     from oracle.fv import FVOracle
-    d = slider_inputs(n_side, n_side)
+    d = journal_inputs(n_side, n_side)
     q, topo = initial_fields(d)
     o = FVOracle(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo)
     o.q[...] = q
@@ -181,6 +236,11 @@ def pick_cpu_sample(budget_s, steps):
     return n
 
 
+def workload_text(n, world):
+    return (f"2D periodic journal bearing {n * world}x{n} ({n}x{n} per GPU), FP64, DH EOS (C1 = 3.5e10), fixed-form "
+            "stress, periodic in x and y, adaptive dt CFL = 0.5 (BASELINE config 5: tests/test_flip_axes.py:30-65 scaled)")
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path (NumPy, host cores)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -193,9 +253,8 @@ def run_reference(args):
         "impl": "reference", "metric": "FV cell-updates/s", "value": rate, "unit": "cell-updates/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * s_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "2D parabolic slider bearing, DH EOS, fixed-form stress, FP64 "
-                               f"(BASELINE config 2: 4096x4096 per GPU); CPU sample {n}x{n} of the same problem",
-                   "l2": "n/a (CPU)"},
+        "config": {"workload": workload_text(args.cells, args.gpus) + f"; CPU sample {n}x{n} of the same problem",
+                   "perturbation": PERTURBATION, "l2": "n/a (CPU)"},
         "cpu_baseline": {"value": rate, "unit": "cell-updates/s", "cores": 1, "kind": "port",
                          "sample": f"{n}x{n} cells, {steps} steps after {warmup} warm-up; NumPy restatement of "
                                    "the reference's update loop (its ufuncs are single-threaded); "
@@ -217,6 +276,206 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the pass kernels for workload `key`,
+    from the committed `ncu --set full` capture (profiles/traffic.json, written by tools/ncu_traffic.py from
+    the round's .ncu-rep); None where no capture exists."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f).get(key)
+
+
+def _events(torch):
+    return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+
+def time_single(torch, d, q0, topo, arith, steps, warmup, extra=None, per_kernel=False):
+    """ms/step of a single-GPU FVSolver (device-resident), optionally the per-kernel event times too."""
+    from gapflow_b200.fv import FVSolver
+    s = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, extra=extra, arith=arith)
+    s.set_q(q0)
+    s.fill_ghosts()
+    s.pre_run(False)
+    s.step(warmup)
+    torch.cuda.synchronize()
+    e0, e1 = _events(torch)
+    e0.record()
+    s.step(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    sc = s.scalars()
+    assert sc.step == warmup + steps and not sc.stop, "benchmark run went invalid"
+    out = {"ms_per_step": ms, "final_dt": sc.dt}
+    if per_kernel:
+        s.set_timing(True)
+        s.step(min(steps, 20))
+        out["ms_pred"], out["ms_corr"], _ = s.timing()
+        s.set_timing(False)
+    del s
+    torch.cuda.empty_cache()
+    return out
+
+
+def slab_parity(torch, dist, world, rank, ariths=("fast", "exact"), steps=3, n=2048):
+    """the 2048*G x 2048 journal on G slabs (this job's processes: CUDA-IPC peer memory,
+    system-scope flags, graph replay) against the single-domain run, bit for bit.  Rank 0 runs the single
+    domain and broadcasts its padded field; every rank compares its own padded slab on the device."""
+    import numpy as np
+    from gapflow_b200.dist import SlabSolver, slab_rows
+    from gapflow_b200.fv import FVSolver
+    d = journal_inputs(n * world, n)
+    start, nloc = slab_rows(d['grid']['Nx'], world)[rank]
+    out = {"grid": f"{n * world}x{n} periodic journal on {world} x-slabs vs one domain (rank 0)", "steps": steps,
+           "bit_exact": True, "mismatched_values": 0, "dt_equal": True, "ekin_rel_diff": 0.0, "comm_error": False,
+           "arith": list(ariths)}
+    for arith in ariths:
+        ql, tl = initial_fields(d, rows=(start, start + nloc + 2))
+        sl = SlabSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=tl, q=ql, rank=rank,
+                        world=world, arith=arith)
+        sl.fill_ghosts()
+        sl.pre_run(False)
+        sl.step(steps)
+        sc = sl.scalars()
+        mine = torch.empty((3, nloc + 2, n + 2), dtype=torch.float64, device='cuda')
+        sl.fv.get_q(out=mine)
+        ref = torch.empty((3, n * world + 2, n + 2), dtype=torch.float64, device='cuda')
+        scal = torch.zeros(3, dtype=torch.float64, device='cuda')
+        if rank == 0:
+            qg, tg = initial_fields(d)
+            one = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=tg, arith=arith)
+            one.set_q(qg)
+            one.fill_ghosts()
+            one.pre_run(False)
+            one.step(steps)
+            s1 = one.scalars()
+            one.get_q(out=ref)
+            scal[0], scal[1], scal[2] = s1.dt, s1.ekin, float(s1.step)
+            del one, qg, tg
+        dist.broadcast(ref, 0)
+        dist.broadcast(scal, 0)
+        bad = (mine != ref[:, start:start + nloc + 2]).sum().to(torch.float64)
+        flags = torch.stack([bad, torch.tensor(float(sc.dt != float(scal[0])), device='cuda', dtype=torch.float64),
+                             torch.tensor(float(sl.comm_error()), device='cuda', dtype=torch.float64)])
+        dist.all_reduce(flags, op=dist.ReduceOp.SUM)
+        out["mismatched_values"] += int(flags[0].item())
+        out["dt_equal"] = out["dt_equal"] and flags[1].item() == 0 and sc.step == int(scal[2])
+        out["comm_error"] = out["comm_error"] or flags[2].item() != 0
+        out["ekin_rel_diff"] = max(out["ekin_rel_diff"], abs(sc.ekin - float(scal[1])) / abs(float(scal[1])))
+        sl.close()
+        del sl, mine, ref
+        torch.cuda.empty_cache()
+    out["bit_exact"] = out["mismatched_values"] == 0 and out["dt_equal"] and not out["comm_error"]
+    assert np.isfinite(out["ekin_rel_diff"])
+    return out
+
+
+def gp_block(torch, lib, args, clock_index):
+    """BASELINE config 4: N = 1026^2 query cells x M = 10^4 training points, pressure (D = 1, one output) and
+    wall-shear (D = 3, two outputs) models of examples/slip_2d_lj_mock.py.  Training targets from the device
+    mock MD (gapflow_b200.surrogate.Mock: the BWR / slip-top closures) + seeded noise; hyperparameters =
+    params_init (stress.py:281-284).  FP64 roofline = cuBLAS DGEMM measured in this run."""
+    import numpy as np
+    import bench_gp as BG
+    from gapflow_b200.gp import GPModel
+    from gapflow_b200.surrogate import Mock, _normalizer
+    M, N, ns = args.gp_M, 1026 * 1026, args.gp_var_sample
+    prop = dict(EOS='BWR', T=1.0, gamma=3.0, rho0=0.8, shear=2.15, bulk=0.)
+    geo = dict(U=0.12, V=0.)
+    gpcfg = dict(press_gp=True, shear_gp=True, press=dict(obs_stddev=2e-2), shear=dict(obs_stddev=4e-3))
+    rng = np.random.default_rng(2025)
+    X = np.zeros((M, 7))
+    X[:, 0] = rng.uniform(0.8 * 0.99, 0.8 * 1.01, M)
+    X[:, 1] = rng.uniform(0.5, 1.5, M) * 0.8 * 0.12 / 2
+    X[:, 2] = rng.uniform(-0.5, 0.5, M) * 0.8 * 0.12 / 2
+    X[:, 3] = 10.0
+    X[:, 6] = rng.uniform(0., 1., M)
+    Y, _ = Mock(prop, geo, gpcfg).run_batch(X)                        # (M, 13), device closures, no noise draws
+    xs, ys = _normalizer(X), _normalizer(Y)
+    with ClockSampler(clock_index) as clk:
+        peak = BG.dgemm_peak(torch)
+        out = {"workload": f"2D GP surrogate, N = {N} query cells (1026^2, ghosts included) x M = {M} training points "
+                           "(BASELINE config 4), Matern-3/2, mock LJ training data (seed 2025)",
+               "unit": "predictions/s (one query cell evaluated by one model)",
+               "fp64_peak_tflops": peak, "fp64_peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, best of 5, same run",
+               "models": {}}
+        cases = {}
+        for name, dims, cols, sd in (("pressure", [0], [0], 2e-2), ("shear_x", [0, 1, 6], [5, 11], 4e-3)):
+            Yn = Y[:, cols] + sd * rng.standard_normal((M, len(cols)))
+            Yscale = ys[cols].max()
+            Xn = (X / xs)[:, dims]
+            std = np.std(Xn, axis=0)
+            c = dict(X=Xn, Y=Yn / Yscale, Yerr=float(sd / Yscale), log_amp=0.0,
+                     log_scale=np.log(np.where(std > 0, std, 1.0)), dims=dims, n_out=len(cols))
+            cases[name] = c
+            D, nout = len(dims), len(cols)
+            g = GPModel(M, D, nout)
+            l0 = lib.gpf_launch_count()
+            t_fac = BG.timed(torch, lambda: g.factor(c['X'], c['Y'], c['log_amp'], c['log_scale'], c['Yerr']))
+            lo, hi = Xn.min(0), Xn.max(0)
+            xt = torch.as_tensor(np.random.default_rng(7).uniform(lo - 0.05 * (hi - lo), hi + 0.05 * (hi - lo), (N, D)),
+                                 device='cuda')
+            c['xt'] = xt
+            t_mean = BG.timed(torch, lambda: g.repredict_mean(xt), reps=3)
+            xv = xt[:ns].contiguous()
+            t_mv = BG.timed(torch, lambda: g.repredict_mean_var(xv, 1.5e-8))
+            t_m_s = BG.timed(torch, lambda: g.repredict_mean(xv), reps=3)
+            t_nlml = BG.timed(torch, lambda: g.nlml())
+            Mp = (M + 63) // 64 * 64
+            flop_var, flop_fac = float(Mp) * Mp * ns, M**3 / 3.0
+            dense_var = not (D == 1 and os.environ.get("GPF_GP_VAR1D", "1") != "0")
+            res = {"D": D, "n_out": nout, "factor_ms": t_fac, "factor_tflops": flop_fac / (t_fac * 1e-3) / 1e12,
+                   "factor_frac_of_dgemm_peak": flop_fac / (t_fac * 1e-3) / 1e12 / peak,
+                   "nlml_grad_ms": t_nlml, "nlml_grad_tflops": 2.0 * flop_fac / (t_nlml * 1e-3) / 1e12,
+                   "mean": {"value": N / (t_mean * 1e-3), "ms": t_mean, "N": N,
+                            "equivalent_kernel_evals_per_s": N * M / (t_mean * 1e-3)},
+                   "mean_var": {"value": ns / (t_mv * 1e-3), "ms": t_mv, "N": ns,
+                                "sample": f"first {ns} of the {N} query cells"},
+                   "gpu_launches": int(lib.gpf_launch_count() - l0)}
+            if dense_var:
+                tf = flop_var / (max(t_mv - t_m_s, 1e-6) * 1e-3) / 1e12
+                res["mean_var"].update({"algorithm": "dense forward substitution on the FP64 tensor pipe (DMMA), M^2 flops per cell",
+                                        "var_kernel_tflops": tf, "frac_of_dgemm_peak": tf / peak})
+            else:
+                res["mean_var"]["algorithm"] = "O(log M) per query: two-filter Kalman form of the 1-D Matern-3/2 process (csrc/gp_var1d.h)"
+            c['g'] = g
+            out["models"][name] = res
+    out["clocks"] = clk.summary()
+    out["value"] = out["models"]["shear_x"]["mean"]["value"]
+    out["roofline"] = {"bound": "tensor", "kernel": "gp_var_kernel (FP64 DMMA forward substitution)",
+                       "achieved": out["models"]["shear_x"]["mean_var"].get("var_kernel_tflops"), "peak": peak,
+                       "unit": "TFLOP/s", "frac": out["models"]["shear_x"]["mean_var"].get("frac_of_dgemm_peak"),
+                       "peak_source": "cuBLAS DGEMM, same run (MEASURED_PEAKS.json has no FP64 figure)"}
+    if not args.no_cpu:
+        from oracle import gp as G
+        c = cases["shear_x"]
+        nc = 2048
+        xh = c['xt'][:nc].cpu().numpy()
+        t0 = time.perf_counter()
+        L = G.build(c['X'], c['Yerr'], c['log_amp'], c['log_scale'])
+        a = G.alpha(L, c['Y'])
+        t1 = time.perf_counter()
+        mref = G.repredict_mean(c['X'], c['log_amp'], c['log_scale'], a, xh)
+        t2 = time.perf_counter()
+        _, vref = G.repredict_mean_var(c['X'], c['log_amp'], c['log_scale'], L, a, 1.5e-8, xh)
+        t3 = time.perf_counter()
+        m, v = c['g'].repredict_mean_var(c['xt'][:nc].contiguous(), 1.5e-8)
+        out["cpu_baseline"] = {"kind": "port", "cores": os.cpu_count(), "unit": "predictions/s",
+                               "sample": f"shear_x model, {nc} query cells, SciPy restatement of gp.py:509-535 (OpenBLAS, all host cores)",
+                               "factor_s": t1 - t0, "mean": nc / (t2 - t1), "mean_var": nc / (t3 - t2)}
+        out["parity_vs_cpu_port"] = {"mean_max_rel": float(np.abs(m.cpu().numpy() - mref).max() / np.abs(mref).max()),
+                                     "var_max_abs_over_amp": float(np.abs(v.cpu().numpy() - vref).max())}
+    for c in cases.values():
+        del c['g'], c['xt']
+    torch.cuda.empty_cache()
+    if args.gp_coupled_steps > 0:
+        ca = argparse.Namespace(coupled_n=1024, M=M, coupled_steps=args.gp_coupled_steps, no_cpu=True)
+        out["coupled_step"] = BG.coupled_step(torch, np, lib, ca)
+    return out
+
+
 def run_gpu(args):
     import numpy as np
     import torch
@@ -232,9 +491,28 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = _capi.load()
+    notes = []
 
-    n = N_CELLS_1D
-    d = slider_inputs(n * world, n)
+    def guarded(name, fn):
+        """extra blocks never take the headline down: a failure is recorded in the line"""
+        try:
+            return fn()
+        except Exception as e:          # noqa: BLE001
+            notes.append(f"{name}: {type(e).__name__}: {e}")
+            return None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = slab_parity(torch, dist, world, rank)
+        barrier()
+
+    n = args.cells
+    d = journal_inputs(n * world, n)
     if world == 1:
         from gapflow_b200.fv import FVSolver
         q0, topo = initial_fields(d)
@@ -242,7 +520,6 @@ def run_gpu(args):
         solver.set_q(q0)
         solver.fill_ghosts()
         solver.pre_run(False)
-        step = solver.step
     else:
         from gapflow_b200.dist import SlabSolver, slab_rows
         start, nloc = slab_rows(d['grid']['Nx'], world)[rank]
@@ -252,19 +529,14 @@ def run_gpu(args):
                             overlap=os.environ.get('GPF_SLAB_OVERLAP', '1') != '0')
         solver.fill_ghosts()
         solver.pre_run(False)
-        step = solver.step
         q0 = None
+    step = solver.step
     cells_per_step = n * n * world
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     # ---- device-resident throughput --------------------------------------------------------
     step(args.warmup)
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0, e1 = _events(torch)
     l0 = lib.gpf_launch_count()
     with ClockSampler(local) as clk:
         barrier()
@@ -282,6 +554,8 @@ def run_gpu(args):
         ms = float(t.item())
     sc = solver.scalars()
     assert sc.step == args.warmup + args.steps and not sc.stop, "benchmark run went invalid"
+    if world > 1:
+        assert not solver.comm_error(), "a wait on a peer timed out during the timed region"
     value = cells_per_step * args.steps / (ms * 1e-3)
 
     # ---- per-kernel durations (CUDA events on the launching stream, separate batch) --------
@@ -294,18 +568,30 @@ def run_gpu(args):
     per_gpu_cells = n * n
     ach_corr = per_gpu_cells * BYTES_CORR / (t_corr * 1e-3) / 1e9
     ach_pred = per_gpu_cells * BYTES_PRED / (t_pred * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "fv_pass_kernel<corrector> (timed: the straight-line launch + the general launch that returns at once)", "achieved": ach_corr, "peak": peak,
-                "unit": "GB/s", "frac": ach_corr / peak, "traffic": TRAFFIC_CORR_BYTES,
+    traffic = ncu_traffic(f"journal{n}") or {}
+    tr_corr, tr_pred = traffic.get("corrector"), traffic.get("predictor")
+    roofline = {"bound": "hbm", "kernel": "fv_pass_kernel<corrector> (timed: the straight-line launch + the general launch that returns at once)",
+                "achieved": ach_corr, "peak": peak, "unit": "GB/s", "frac": ach_corr / peak, "traffic": tr_corr,
+                "dram_frac": (tr_corr / (t_corr * 1e-3) / 1e9 / peak) if tr_corr else None,
+                "traffic_source": traffic.get("source"),
+                "note": ("frac counts SURVEY 8(d)'s 96 B per cell; this workload has dh/dy == 0, so the kernel's x-driven-film "
+                         "variant loads 2 of the 3 topography planes (88 B per cell really requested); dram_frac = ncu DRAM bytes / time "
+                         "/ peak; the general kernel is in `variants`"),
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": per_gpu_cells * BYTES_CORR,
                 "ms_per_launch": t_corr,
                 "predictor": {"achieved": ach_pred, "frac": ach_pred / peak, "ms_per_launch": t_pred,
-                              "algorithmic_bytes_per_launch": per_gpu_cells * BYTES_PRED},
-                "step_frac_of_hbm_roofline": (value / world) * BYTES_PER_CELL_UPDATE / 1e9 / peak}
+                              "algorithmic_bytes_per_launch": per_gpu_cells * BYTES_PRED, "traffic": tr_pred,
+                              "dram_frac": (tr_pred / (t_pred * 1e-3) / 1e9 / peak) if tr_pred else None},
+                "step_frac_of_hbm_roofline": (value / world) * BYTES_PER_CELL_UPDATE / 1e9 / peak,
+                "step_dram_frac": ((tr_corr + tr_pred) / (ms / args.steps * 1e-3) / 1e9 / peak) if (tr_corr and tr_pred and world == 1) else None}
 
     # ---- end to end through the host-buffer entry point ---------------------------------------
     # every step: H2D of this rank's q from pinned host memory, update(), D2H of q (+ scalars)
     qh = torch.empty((3, n + 2, n + 2), dtype=torch.float64, pin_memory=True)
-    qh.copy_(torch.from_numpy(solver.get_q()))
+    if world == 1:
+        solver.get_q(out=qh.numpy())
+    else:
+        qh.copy_(torch.from_numpy(solver.get_q()))
     k2 = max(3, min(args.steps, 10))
     solver.update_host(qh, 1)
     barrier()
@@ -325,30 +611,69 @@ def run_gpu(args):
            "api": ("gpf_fv_update_host (C ABI; H2D / passes / D2H pipelined over 16 row chunks) via FVSolver.update_host" if world == 1 else
                    "SlabSolver.update_host (gpf_fv_upload / slab step / gpf_fv_download per rank)")
                   + ", pinned host q, all ranks' bytes"}
+    del qh
 
-    # ---- the other arithmetic contract, same workload (N=1 only) -------------------------------
-    other = None
+    # ---- single-GPU extras: the other contract, config 2, kernel variants, GP ---------------------
+    other = slider = variants = gp = None
     if world == 1:
-        mode = "exact" if args.arith == "fast" else "fast"
         del solver
         torch.cuda.empty_cache()
-        from gapflow_b200.fv import FVSolver
-        s2 = FVSolver(d['grid'], d['geometry'], d['properties'], d['numerics'], topo=topo, arith=mode)
-        s2.set_q(q0)
-        s2.fill_ghosts()
-        s2.pre_run(False)
-        s2.step(args.warmup)
-        torch.cuda.synchronize()
-        k3 = max(3, args.steps // 2)
-        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        f0.record()
-        s2.step(k3)
-        f1.record()
-        torch.cuda.synchronize()
-        ms2 = f0.elapsed_time(f1) / k3
-        other = {"arith": mode, "value": n * n / (ms2 * 1e-3), "ms_per_step": ms2, "steps": k3,
-                 "step_frac_of_hbm_roofline": n * n / (ms2 * 1e-3) * BYTES_PER_CELL_UPDATE / 1e9 / peak}
-        del s2
+        kx, wx = max(3, min(args.steps, 40)), 5
+
+        def frac(ms_step, cells, nbytes=BYTES_PER_CELL_UPDATE):
+            return cells / (ms_step * 1e-3) * nbytes / 1e9 / peak
+
+        def other_contract():
+            mode = "exact" if args.arith == "fast" else "fast"
+            r = time_single(torch, d, q0, topo, mode, kx, wx)
+            return {"arith": mode, "value": n * n / (r["ms_per_step"] * 1e-3), "ms_per_step": r["ms_per_step"], "steps": kx,
+                    "step_frac_of_hbm_roofline": frac(r["ms_per_step"], n * n)}
+        other = guarded("other_arith", other_contract)
+        q0 = topo = None
+        if not args.no_extras:
+            ns_ = N_SLIDER
+            ds = slider_inputs(ns_, ns_)
+            qs, ts = initial_fields(ds)
+
+            def slider_block():
+                out = {"workload": f"2D parabolic slider bearing {ns_}x{ns_}, x: D/N/N, y periodic, adaptive dt (BASELINE config 2; "
+                                   "round 1's headline workload)"}
+                for mode in (args.arith, "exact" if args.arith == "fast" else "fast"):
+                    r = time_single(torch, ds, qs, ts, mode, kx, wx, per_kernel=(mode == args.arith))
+                    out[mode] = {"value": ns_ * ns_ / (r["ms_per_step"] * 1e-3), "ms_per_step": r["ms_per_step"], "steps": kx,
+                                 "step_frac_of_hbm_roofline": frac(r["ms_per_step"], ns_ * ns_)}
+                    if "ms_corr" in r:
+                        out[mode]["corrector_frac"] = ns_ * ns_ * BYTES_CORR / (r["ms_corr"] * 1e-3) / 1e9 / peak
+                        out[mode]["predictor_frac"] = ns_ * ns_ * BYTES_PRED / (r["ms_pred"] * 1e-3) / 1e9 / peak
+                return out
+            slider = guarded("slider4096", slider_block)
+
+            def variants_block():
+                out = {"grid": f"{ns_}x{ns_}", "arith": args.arith, "steps": kx}
+                # general kernel: the flipped journal of tests/test_flip_axes.py (U = 0, V = 0.1, dh/dy != 0): all 3 topography planes
+                df = journal_inputs(ns_, ns_, flip=True)
+                qf, tf = initial_fields(df)
+                r = time_single(torch, df, qf, tf, args.arith, kx, wx)
+                out["general_XF0"] = {"workload": "periodic journal, flip: True (dh/dy != 0, V != 0)", "bytes_per_cell_update": 168,
+                                      "ms_per_step": r["ms_per_step"], "step_frac_of_hbm_roofline": frac(r["ms_per_step"], ns_ * ns_)}
+                del qf, tf
+                # slip-length field (LS): + 1 plane per pass
+                ls = 1e-6 * np.random.default_rng(7).random((1, ns_ + 2, ns_ + 2))
+                r = time_single(torch, ds, qs, ts, args.arith, kx, wx, extra=ls)
+                out["slip_length_LS"] = {"workload": "config 2 slider + random slip-length field (<= 1e-6 m)", "bytes_per_cell_update": 184,
+                                         "ms_per_step": r["ms_per_step"], "step_frac_of_hbm_roofline": frac(r["ms_per_step"], ns_ * ns_, 184)}
+                del ls
+                # viscosity field (VF): Barus piezoviscosity; per pass + 1 viscosity plane written and read, + the slip plane
+                dv = slider_inputs(ns_, ns_, "    piezo:\n        name: Barus\n        aB: 2.e-8\n")
+                r = time_single(torch, dv, qs, ts, args.arith, kx, wx)
+                out["viscosity_field_VF"] = {"workload": "config 2 slider + Barus piezoviscosity (viscosity kernel + VF pass variant per pass)",
+                                             "bytes_per_cell_update": 232,
+                                             "ms_per_step": r["ms_per_step"], "step_frac_of_hbm_roofline": frac(r["ms_per_step"], ns_ * ns_, 232)}
+                return out
+            variants = guarded("variants", variants_block)
+            del qs, ts
+        if not args.no_gp:
+            gp = guarded("gp", lambda: gp_block(torch, lib, args, local))
 
     if rank == 0:
         cpu = None
@@ -356,31 +681,32 @@ def run_gpu(args):
             ncpu = 1024
             rate, _ = cpu_steps(ncpu, 3, 1)
             cpu = {"value": rate, "unit": "cell-updates/s", "cores": 1, "kind": "port",
-                   "sample": f"{ncpu}x{ncpu} sample of the same slider, 3 steps after 1 warm-up, NumPy oracle "
+                   "sample": f"{ncpu}x{ncpu} sample of the same journal, 3 steps after 1 warm-up, NumPy oracle "
                              f"(single-threaded like the reference); host has {os.cpu_count()} logical cores"}
         line = {
             "metric": "FV cell-updates/s", "value": value, "unit": "cell-updates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"2D parabolic slider bearing {n * world}x{n} ({n}x{n} per GPU), FP64, DH EOS, "
-                                   "fixed-form stress, x: D/N/N, y periodic, adaptive dt (BASELINE config 2)",
-                       "parallelism": f"x-slabs x{world}" if world > 1 else "single GPU",
-                       "arith": args.arith + (" (FMA contraction, a*rcp(b) quotients; parity 1e-12/step, 1e-9/1000 steps)"
+            "config": {"workload": workload_text(n, world),
+                       "parallelism": (f"x-slabs x{world} (ring), edge rows and loop records over CUDA-IPC peer memory "
+                                       "(NVLink), one CUDA graph per step") if world > 1 else "single GPU",
+                       "arith": args.arith + (" (FMA contraction, a*rcp(b) quotients; parity 1e-12/step, 1e-9/1000 steps; "
+                                              "Problem / the C ABI default to `exact`, reported in other_arith)"
                                               if args.arith == "fast" else " (bit-identical to the reference's NumPy path)"),
-                       "l2": "inputs larger than L2: 1.2 GB of fields streamed per step vs 126 MB L2"},
+                       "perturbation": PERTURBATION,
+                       "steps_note": "SURVEY 8(d) specifies 200 timed steps after 20 warm-up: the defaults of this script; "
+                                     "the line states what was run",
+                       "l2": f"inputs larger than L2: {n * n * 168 / 1e9:.1f} GB of fields streamed per step vs 126 MB L2"},
             "clocks": clk.summary(), "host_enqueue_ms_per_step": 1e3 * t_host / args.steps,
             "gpu_launches": int(launches), "roofline": roofline,
-            "e2e": e2e, "cpu_baseline": cpu, "other_arith": other,
+            "e2e": e2e, "cpu_baseline": cpu, "other_arith": other, "slider4096": slider, "variants": variants,
+            "slab_parity": parity, "gp": gp, "notes": notes,
             "final": {"step": int(sc.step), "dt": sc.dt, "residual": sc.residual},
         }
         emit(line)
     if world > 1:
+        solver.close()
         dist.destroy_process_group()
-
-
-# dram__bytes_read.sum + dram__bytes_write.sum of one corrector launch at 4096^2 from the
-# committed `ncu --set full` capture (profiles/); None until a capture exists.
-TRAFFIC_CORR_BYTES = 1486998624  # profiles/r1s_ncu_fv_pass_summary.csv: 1.105212 GB read + 381.787 MB written
 
 
 _RESULT_FD = None
@@ -408,10 +734,17 @@ def main():
     os.environ.setdefault("NCCL_P2P_USE_CUDA_MEMCPY", "1")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="gapflow_b200")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cells", type=int, default=N_CELLS_1D, help="cells per GPU per axis of the headline journal")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
+    ap.add_argument("--no-extras", action="store_true", help="skip slider4096 / variants (N = 1)")
+    ap.add_argument("--no-gp", action="store_true", help="skip the GP block (N = 1)")
+    ap.add_argument("--no-parity", action="store_true", help="skip slab_parity (N > 1)")
+    ap.add_argument("--gp-M", type=int, default=10000)
+    ap.add_argument("--gp-var-sample", type=int, default=32768)
+    ap.add_argument("--gp-coupled-steps", type=int, default=2)
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"],
                     help="arithmetic contract of the pass kernels (include/gapflow_b200.h: gpf_fv_cfg.arith)")
     args = ap.parse_args()

@@ -88,6 +88,7 @@ SIGNATURES = {
     "gpf_comm_connect": (_i, [_vp, _vp]),
     "gpf_comm_destroy": (_i, [_vp]),
     "gpf_comm_error": (_i, [_vp, C.POINTER(C.c_int)]),
+    "gpf_comm_set_timeout": (_i, [_vp, C.c_double]),
     "gpf_fv_halo_send": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "gpf_fv_halo_recv": (_i, [_vp, _vp, _i, _vp]),
     "gpf_fv_record_send": (_i, [_vp, _vp, _i, _vp]),

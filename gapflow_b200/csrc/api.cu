@@ -303,6 +303,9 @@ int gpf_comm_error(gpf_comm* c, int* err) {
     return GPF_OK;
     GPF_CATCH
 }
+int gpf_comm_set_timeout(gpf_comm* c, double seconds) {
+    GPF_TRY NEED(c) return c->C.set_timeout(seconds); GPF_CATCH
+}
 int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, void* stream) {
     GPF_TRY NEED(s && c) return s->S.halo_send(c->C, rel, lo, hi, (cudaStream_t)stream); GPF_CATCH
 }

@@ -23,7 +23,6 @@ enum { FIN_STEP = 0, FIN_PRERUN = 1, FIN_PRERUN_KEEP_EKIN = 2, FIN_REFRESH = 3 }
 // records, so every rank folds the same numbers in the same order and advances identically.
 // `rec_out` != nullptr: only fold this rank's per-block records into one Rec5 and return.
 // ---- system-scope flag protocol of the peer-memory exchange (slab_comm.cuh) ----------------
-constexpr unsigned long long SPIN_NS = 5ull * 1000 * 1000 * 1000;
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -37,12 +36,19 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-// waits until *flag >= seq; gives up after SPIN_NS (a peer died) and raises *err instead of hanging the GPU
+// Waits until *flag >= seq.  `err` is the communicator's error block: err[0] the error flag, the 64-bit word at
+// err + 2 the wait bound in ns (gpf_comm_set_timeout).  A wait that exceeds the bound (a peer died) raises the
+// flag instead of hanging the GPU; once it is up every later wait falls through at once, the records carry
+// FLAG_COMM to every rank and fv_finish_kernel stops the run (DevState::comm_err).
 __device__ __forceinline__ void spin_until(const unsigned long long* flag, unsigned long long seq, int* err) {
+    if (ld_acquire_sys(flag) >= seq) return;
+    if (*reinterpret_cast<volatile int*>(err)) return;
+    const unsigned long long limit = *reinterpret_cast<const volatile unsigned long long*>(err + 2);
     const unsigned long long t0 = global_ns();
     while (ld_acquire_sys(flag) < seq) {
-        if (global_ns() - t0 > SPIN_NS) {
-            if (err) *err = 1;
+        if (global_ns() - t0 > limit) {
+            *reinterpret_cast<volatile int*>(err) = 1;
+            __threadfence();
             return;
         }
         __nanosleep(64);
@@ -67,6 +73,7 @@ __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ 
             for (int k = 0; k < 5; ++k) recs_copy[tid * 5 + k] = __ldcg(reinterpret_cast<const double*>(recs) + (size_t)tid * rec_stride + k);
     }
     if (mode == FIN_STEP && (st->stop || (until_converged && st->halt))) return;
+    const int cerr = (werr && *reinterpret_cast<volatile int*>(werr)) ? FLAG_COMM : 0;   // a wait of this rank timed out
     __shared__ double sE[256], sV[256], sC[256], sM[256];
     __shared__ int sF[256];
     double E = 0.0, VM = -INFINITY, CM = -INFINITY, M = 0.0;
@@ -110,9 +117,17 @@ __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ 
         __syncthreads();
     }
     if (tid != 0) return;
-    E = sE[0]; VM = sV[0]; CM = sC[0]; M = sM[0]; F = sF[0];
+    E = sE[0]; VM = sV[0]; CM = sC[0]; M = sM[0]; F = sF[0] | cerr;
     if (rec_out) {
         rec_out->ekin = E; rec_out->vmax2 = VM; rec_out->cs2 = CM; rec_out->mass = M; rec_out->flags = (double)F;
+        return;
+    }
+    if (F & FLAG_COMM) {
+        // some rank's wait on a peer timed out: the exchanged rows / records of this step are not trustworthy.
+        // Every rank sees the flag in the same fold and stops; gpf_fv_get_scalars reports it.
+        st->comm_err = 1;
+        st->stop = 1;
+        st->halt = 1;
         return;
     }
     const double qnan = nan("");
@@ -325,7 +340,7 @@ __global__ void __launch_bounds__(256) fv_halo_recv_kernel(const __grid_constant
 // stored into every rank's record table, each followed by its sequence number
 __global__ void __launch_bounds__(256) fv_record_send_kernel(const Partial* part, const int* pflags, int nblk, int xslot,
                                                              unsigned char* const* peers, size_t off_recs, size_t off_rflag,
-                                                             int world, int rank, const unsigned long long* seqp) {
+                                                             int world, int rank, const unsigned long long* seqp, const int* err) {
     const unsigned long long seq = *seqp + 1;             // this fold; fv_finish_kernel advances *seqp
     const int parity = (int)(seq & 1ull);
     __shared__ double sE[256], sV[256], sC[256], sM[256];
@@ -361,7 +376,8 @@ __global__ void __launch_bounds__(256) fv_record_send_kernel(const Partial* part
     }
     if (tid < world) {
         double* dst = reinterpret_cast<double*>(peers[tid] + off_recs) + ((size_t)parity * world + rank) * 8;
-        dst[0] = sE[0]; dst[1] = sV[0]; dst[2] = sC[0]; dst[3] = sM[0]; dst[4] = (double)sF[0];
+        const int cf = *reinterpret_cast<const volatile int*>(err) ? FLAG_COMM : 0;   // tell every rank
+        dst[0] = sE[0]; dst[1] = sV[0]; dst[2] = sC[0]; dst[3] = sM[0]; dst[4] = (double)(sF[0] | cf);
         __threadfence_system();
         st_release_sys(reinterpret_cast<unsigned long long*>(peers[tid] + off_rflag) + rank, seq);
     }
@@ -1422,11 +1438,24 @@ int SlabComm::create(int world, int rank, int Ny) {
     lay = layout(world, rank, Ny + 2);
     GPF_CUDA(cudaMalloc(&local, lay.bytes));
     GPF_CUDA(cudaMemset(local, 0, lay.bytes));
+    {
+        const char* e = getenv("GPF_COMM_TIMEOUT_S");
+        const double sec = (e && atof(e) > 0.0) ? atof(e) : 30.0;
+        int rc = set_timeout(sec);
+        if (rc) return rc;
+    }
     GPF_CUDA(cudaDeviceSynchronize());
     GPF_CUDA(cudaIpcGetMemHandle(&handle, local));
     peer.assign(world, nullptr);
     peer[rank] = local;
     d_peer = reinterpret_cast<unsigned char**>(local + lay.off_ptrs);
+    return GPF_OK;
+}
+
+int SlabComm::set_timeout(double seconds) {
+    if (!local || !(seconds > 0.0) || seconds > 3600.0) { set_error("gpf_comm_set_timeout: 0 < seconds <= 3600"); return GPF_E_INVALID; }
+    const unsigned long long ns = (unsigned long long)(seconds * 1e9);
+    GPF_CUDA(cudaMemcpy(local + lay.off_err + 8, &ns, sizeof(ns), cudaMemcpyHostToDevice));
     return GPF_OK;
 }
 
@@ -1506,7 +1535,7 @@ int FvSolver::record_send(SlabComm& c, int kind, cudaStream_t s) {
         xslot = -1;
     }
     fv_record_send_kernel<<<1, 256, 0, s>>>(partial, pflags, nblk, xslot, c.d_peer, c.lay.off_recs, c.lay.off_rflag,
-                                            c.lay.world, c.lay.rank, c.seq(1));
+                                            c.lay.world, c.lay.rank, c.seq(1), c.err());
     g_launches++;
     return debug_check("fv_record_send_kernel", s);
 }
@@ -1641,6 +1670,11 @@ int FvSolver::get_scalars(gpf_fv_scalars* o, cudaStream_t s) {
     }
     GPF_CUDA(cudaMemcpyAsync(&h, st, sizeof(h), cudaMemcpyDeviceToHost, s));
     GPF_CUDA(cudaStreamSynchronize(s));
+    if (h.comm_err) {
+        set_error("slab exchange: a wait on a peer rank timed out (a peer died or lagged beyond gpf_comm_set_timeout); "
+                  "the run was stopped on every rank and the fields of the last step are not valid");
+        return GPF_E_STATE;
+    }
     memset(o, 0, sizeof(*o));
     o->step = h.step; o->simtime = h.simtime; o->dt = h.dt; o->residual = h.residual;
     for (int k = 0; k < 5; ++k) o->residual_buffer[k] = h.resbuf[k];

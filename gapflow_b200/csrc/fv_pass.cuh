@@ -127,6 +127,7 @@ struct Red {
     int flags;      // 1: NaN in q, 2: rho < 0, 4 / 8: sqrt argument of v_max / v_sound NaN or negative
 };
 constexpr int FLAG_NAN = 1, FLAG_NEG = 2, FLAG_VNAN = 4, FLAG_CNAN = 8;
+constexpr int FLAG_COMM = 16;   // slab exchange: a wait on a peer timed out somewhere (fv_kernels.cu: spin_until)
 
 // kinetic energy and speed of one cell (problem.py:342, 347)
 __device__ __forceinline__ void red_accum_v(Red& r, const double v[3]) {

@@ -618,11 +618,14 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
 template <bool CORR, bool LS, int EOS, bool XF, bool VF = false>
 static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
     using Sm = Smem<CORR, LS, XF, fv_nstage(CORR), VF>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in to > 48 KB of dynamic shared memory is a per-device attribute of the function
+    static bool attr_set[64] = {};
+    int dev = 0;
+    GPF_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, false, VF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
         GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, true, VF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     fv_pass_kernel<CORR, LS, EOS, XF, false, VF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
     fv_pass_kernel<CORR, LS, EOS, XF, true, VF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
@@ -633,10 +636,12 @@ static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
 template <bool CORR>
 static int launch_pass_surrogate(const PassArgs& A, int ncta, cudaStream_t s) {
     using Sm = Smem<CORR, true, false, fv_nstage(CORR), false>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};
+    int dev = 0;
+    GPF_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, true, -1, false, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     fv_pass_kernel<CORR, true, -1, false, true, false, true><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
     return GPF_OK;

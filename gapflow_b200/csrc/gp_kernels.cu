@@ -772,6 +772,17 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
     GPF_CUDA(cudaGetDevice(&dev));
     GPF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     nslots = sms;
+    {
+        // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: set it for the device
+        // of every model (cheap), not once per process
+        const int sm2 = (int)((size_t)2 * NB * LDT * 8), sm3 = (int)((size_t)3 * NB * LDT * 8);
+        GPF_CUDA(cudaFuncSetAttribute(gp_potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)2 * NB * (NB + 1) * 8)));
+        GPF_CUDA(cudaFuncSetAttribute(gp_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
+        GPF_CUDA(cudaFuncSetAttribute(gp_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
+        GPF_CUDA(cudaFuncSetAttribute(gp_var_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)VAR_SMEM));
+        GPF_CUDA(cudaFuncSetAttribute(gp_trtri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm3));
+        GPF_CUDA(cudaFuncSetAttribute(gp_lauum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
+    }
     if (bytes < workspace_bytes(Mmax, D, nout, nslots)) { set_error("GP workspace too small"); return GPF_E_INVALID; }
     const size_t Mpm = (size_t)(Mmax + NB - 1) / NB * NB;
     unsigned char* p = reinterpret_cast<unsigned char*>(al(reinterpret_cast<size_t>(ws)));
@@ -822,14 +833,6 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
     const int nb = Mp / NB;
     const size_t sm2 = (size_t)2 * NB * LDT * 8;
     const size_t smp = (size_t)2 * NB * (NB + 1) * 8;
-    static bool attr = false;
-    if (!attr) {
-        GPF_CUDA(cudaFuncSetAttribute(gp_potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp));
-        GPF_CUDA(cudaFuncSetAttribute(gp_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-        GPF_CUDA(cudaFuncSetAttribute(gp_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-        GPF_CUDA(cudaFuncSetAttribute(gp_var_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)VAR_SMEM));
-        attr = true;
-    }
     for (int k = 0; k < nb; ++k) {
         gp_potrf_diag_kernel<<<1, 256, smp, s>>>(L, Mp, k, Dinv, info);
         g_launches++;
@@ -868,12 +871,6 @@ int GpModel::nlml(void* work, size_t bytes, double* loss, double* grad, cudaStre
     double* part = reinterpret_cast<double*>(p); p += al((size_t)ntile * (1 + GP_MAXD) * 8);
     double* out = reinterpret_cast<double*>(p);
     const size_t sm3 = (size_t)3 * NB * LDT * 8, sm2 = (size_t)2 * NB * LDT * 8;
-    static bool attr = false;
-    if (!attr) {
-        GPF_CUDA(cudaFuncSetAttribute(gp_trtri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm3));
-        GPF_CUDA(cudaFuncSetAttribute(gp_lauum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-        attr = true;
-    }
     gp_trtri_kernel<<<nb, 128, sm3, s>>>(L, Dinv, Mp, X);
     gp_lauum_kernel<<<ntile, 128, sm2, s>>>(X, Mp, Kinv);
     gp_grad_kernel<<<ntile, 256, 0, s>>>(Kinv, alpha, Xs, M, Mp, D, nout, kp, part);
@@ -1013,7 +1010,7 @@ int GpModel::mean(const double* Xtest, long long N, double* mean_out, double* dm
     return GPF_OK;
 }
 
-// ---- one-input models: O(log M) variance per query (gp_var1d.h), opt-in ----------------------------------
+// ---- one-input models: O(log M) variance per query (gp_var1d.h) ------------------------------------------
 // grid-stride over the queries; per block the largest variance and the index of its first occurrence (NaN wins,
 // like np.argmax), folded by gp_argmax_reduce_kernel exactly as the dense kernel's per-CTA records are
 __global__ void __launch_bounds__(256) gp_var1d_kernel(Var1D T, GpKern kp, const double* Xtest, long long N,
@@ -1064,8 +1061,8 @@ int GpModel::mean_var(const double* Xtest, long long N, const double* noise, dou
     int rc = mean(Xtest, N, mean_out, nullptr, s);
     if (rc) return rc;
     if (N < 1) return GPF_OK;
-    // opt-in until it has been run on a B200 (the host instantiation of the routine is tested on the CPU)
-    static const bool use1d = [] { const char* e = getenv("GPF_GP_VAR1D"); return e && atoi(e) != 0; }();
+    // one-input models: the O(log M) two-filter form (GPF_GP_VAR1D=0 restores the dense solve)
+    static const bool use1d = [] { const char* e = getenv("GPF_GP_VAR1D"); return !e || atoi(e) != 0; }();
     int grid;
     if (D == 1 && use1d) {
         if (!v1d_valid && (rc = build_var1d(s))) return rc;

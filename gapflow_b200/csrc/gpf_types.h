@@ -89,7 +89,7 @@ struct DevState {
     int has_nan, has_neg, stop, converged;
     int halt;           // run-loop condition false: later steps are no-ops
     int cur;            // index of the buffer holding the current q (0..2)
-    int pad;
+    int comm_err;       // slab exchange: some rank's wait on a peer timed out; the run is stopped (see spin_until)
 };
 
 // per-block partial record written by reducing kernels, consumed by fv_finish_kernel

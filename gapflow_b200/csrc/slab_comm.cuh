@@ -6,7 +6,8 @@
 //   hflag[2 sides]                         sequence number of the last completed halo write per side
 //   recs [2 parities][world][8]            one folded record (Rec5, padded) per rank
 //   rflag[world]                           sequence number of the last record written by rank w
-//   err                                    set when a wait timed out (a peer died): results are garbage
+//   err                                    [0] set when a wait timed out (a peer died or lagged): carried to every rank with the
+//                                          records, the run stops (DevState::comm_err);  +8 bytes: the wait bound in ns
 //   seq  [2]                               exchanges / folds this rank has completed (device-resident, so that
 //                                          a captured step can be replayed: no sequence number is a kernel argument)
 // A sender stores the data into the receiver's buffer, fences at system scope and then publishes the
@@ -36,6 +37,7 @@ struct SlabComm {
     int create(int world, int rank, int Ny);
     int connect(const unsigned char* handles);     // [world][sizeof(cudaIpcMemHandle_t)]
     int destroy();
+    int set_timeout(double seconds);                // bound of every device-side wait on a peer (default 30 s)
     cudaGraphExec_t step_graph = nullptr;  // one captured slab step (FvSolver::slab_step)
     int graph_lo = -2, graph_hi = -2;
     const void* graph_owner = nullptr;

@@ -142,11 +142,13 @@ class SlabSolver:
         mine = (C.c_ubyte * n)()
         comm = C.c_void_p()
         _capi.check(self.lib.gpf_comm_create(self.world, self.rank, int(Ny), mine, C.byref(comm)))
-        dev = self.fv.device
+        # the handles travel by whatever backend the group has (device tensors for nccl, host tensors for gloo:
+        # CUDA IPC itself only needs the ranks to be processes of one node, also two processes on one GPU)
+        dev = self.fv.device if dist.get_backend(group) == 'nccl' else torch.device('cpu')
         local = torch.tensor(list(mine), dtype=torch.uint8, device=dev)
-        allh = torch.zeros(self.world * n, dtype=torch.uint8, device=dev)
-        dist.all_gather_into_tensor(allh, local, group=group)
-        buf = (C.c_ubyte * (self.world * n)).from_buffer_copy(allh.cpu().numpy().tobytes())
+        parts = [torch.zeros(n, dtype=torch.uint8, device=dev) for _ in range(self.world)]
+        dist.all_gather(parts, local, group=group)
+        buf = (C.c_ubyte * (self.world * n)).from_buffer_copy(torch.cat(parts).cpu().numpy().tobytes())
         _capi.check(self.lib.gpf_comm_connect(comm, buf))
         dist.barrier(group=group)            # nobody writes into a buffer that is still being zeroed
         self._comm = comm
@@ -160,12 +162,25 @@ class SlabSolver:
             self._comm = None
 
     def comm_error(self):
-        """True if a wait on a peer timed out (a peer process died): the fields are then garbage."""
+        """True if a device-side wait of THIS rank on a peer timed out (synchronises).  The flag also travels to
+        every rank with the next record fold, where it stops the run (gpf_fv_scalars.stop, GPF_E_STATE)."""
         if self._comm is None:
             return False
         e = C.c_int()
         _capi.check(self.lib.gpf_comm_error(self._comm, C.byref(e)))
         return bool(e.value)
+
+    def set_comm_timeout(self, seconds):
+        """Bound of the device-side waits on a peer (default 30 s): longer than the largest host-side skew
+        between ranks (output, GP training on one rank)."""
+        if self._comm is not None:
+            _capi.check(self.lib.gpf_comm_set_timeout(self._comm, float(seconds)))
+
+    def _check_comm(self):
+        """Called at every host synchronisation point: stale halo rows must never reach a result silently."""
+        if self.comm_error():
+            raise _capi.GapflowError(_capi.GPF_E_STATE, f"rank {self.rank}: a wait on a neighbour rank timed out "
+                                     "(a peer died or lagged beyond the communicator's timeout); fields are invalid")
 
     def set_q(self, q):
         """this rank's padded slab (3, n+2, Ny+2) of the global padded q"""
@@ -257,7 +272,9 @@ class SlabSolver:
 
     def scalars(self):
         self._fold(1, _capi.FIN_REFRESH)
-        return self.fv.scalars()
+        sc = self.fv.scalars()              # GPF_E_STATE if any rank's wait timed out (record fold carries it)
+        self._check_comm()
+        return sc
 
     def update_host(self, q_host, n=1):
         """Host-buffer step of this rank's slab: upload q_host (padded slab, pinned), n x update(),
@@ -268,16 +285,20 @@ class SlabSolver:
         self.step(n)
         _capi.check(self.lib.gpf_fv_download(self.h, _capi.F_Q, p, 3, dev, self._s()))
         torch.cuda.current_stream(self.fv.device).synchronize()
+        self._check_comm()
 
     @property
     def mass(self):
         self._fold(1, _capi.FIN_REFRESH)
         torch.cuda.current_stream(self.fv.device).synchronize()
+        self._check_comm()
         return float(self.recs[:, 3].sum().item())
 
     def get_q(self):
         """this rank's padded slab (3, n+2, Ny+2)"""
-        return self.fv.get_q()
+        q = self.fv.get_q()
+        self._check_comm()
+        return q
 
     def gather_q(self):
         """Global padded q on every rank (tests / output staging; host arrays)."""

@@ -276,8 +276,8 @@ int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
 /* The same two exchanges over peer memory instead of a communication library: every rank owns a
  * small buffer that its peers map through CUDA IPC (one node, NVLink / NVSwitch).  The sending
  * kernel stores the edge rows (the folded record) straight into the receivers' buffers and then
- * publishes a sequence number; the receiving kernel waits for it (bounded: a dead peer raises the
- * error flag after 5 s instead of hanging the GPU) and fills the ghost rows (folds the records and
+ * publishes a sequence number; the receiving kernel waits for it (bounded, gpf_comm_set_timeout:
+ * a dead peer raises the error flag and stops every rank instead of hanging the GPU) and fills the ghost rows (folds the records and
  * advances the loop state).  No reference counterpart (problem.py:676-707 is a local copy).
  *   create on every rank -> all-gather the GPF_IPC_HANDLE_BYTES handles by any means -> connect ->
  *   barrier; then, in the same order on every rank,
@@ -292,6 +292,11 @@ int gpf_comm_create(int world, int rank, int Ny, unsigned char* handle_out, gpf_
 int gpf_comm_connect(gpf_comm* c, const unsigned char* handles /* [world][GPF_IPC_HANDLE_BYTES] */);
 int gpf_comm_destroy(gpf_comm* c);
 int gpf_comm_error(gpf_comm* c, int* err);       /* synchronises; 1 = a wait timed out */
+/* Bound of every device-side wait on a peer (default 30 s, or GPF_COMM_TIMEOUT_S at creation).  A wait that
+ * exceeds it raises the error flag; the flag travels to every rank with the next record fold, every rank
+ * stops (gpf_fv_scalars.stop) and gpf_fv_get_scalars returns GPF_E_STATE, so stale halo rows never reach
+ * a result silently.  Choose it longer than the largest host-side skew between ranks (output, training). */
+int gpf_comm_set_timeout(gpf_comm* c, double seconds);
 int gpf_fv_halo_send(gpf_fv* s, gpf_comm* c, int rel, int lo, int hi, void* stream);
 int gpf_fv_halo_recv(gpf_fv* s, gpf_comm* c, int rel, void* stream);
 int gpf_fv_record_send(gpf_fv* s, gpf_comm* c, int kind, void* stream);
@@ -369,7 +374,7 @@ int gpf_selftest_mean1d_host(const double* Xtrain, int M, double log_amp, double
 /* Self-test, HOST arithmetic only: the O(log M) predictive variance of a one-input model (csrc/gp_var1d.h:
  * the one-dimensional Matern-3/2 process as a two-state Markov process, Kalman sweeps from both ends of the
  * sorted training points, two-filter combination per query), by the same inline routine as the device kernel
- * that gpf_gp_mean_var uses for D = 1 when GPF_GP_VAR1D=1 is set (opt-in until it has been run on a B200).
+ * that gpf_gp_mean_var uses for D = 1 (GPF_GP_VAR1D=0 restores the dense solve).
  * var (N) = posterior variance + noise, i.e. gp.py:509-522's `Kss - sum(v**2)`. */
 int gpf_selftest_var1d_host(const double* Xtrain, int M, double log_amp, double log_scale, double yerr,
                             const double* Xtest, int64_t N, double noise, double* var);

@@ -166,3 +166,89 @@ def test_config4_gp_inference_vs_oracle_on_a_subsample():
     _, vref = G.repredict_mean_var(c['X'], c['log_amp'], c['log_scale'], L, a, 1.5e-8, xt[blk][sub])
     assert np.abs(var[sub] - vref).max() <= 1e-9 * np.abs(vref).max()
     assert gp.argmax == int(np.argmax(var)) and abs(gp._vmax_norm - var.max()) == 0.0
+
+
+# ---- BASELINE config 5 / north_star target grid: the periodic journal at 8192 x 8192 -----------------------
+N5 = 8192
+
+
+@pytest.fixture(scope="module")
+def journal8192():
+    d = bench.journal_inputs(N5, N5)
+    q, topo = bench.initial_fields(d)
+    # exactly periodic gap field: the generator's ghost rows (x = -dx/2, Lx + dx/2) equal the periodic images only
+    # to rounding, and the seam tests below compare bit for bit with runs that see the image itself
+    topo[:, 0], topo[:, -1] = topo[:, -2], topo[:, 1]
+    topo[:, :, 0], topo[:, :, -1] = topo[:, :, -2], topo[:, :, 1]
+    return d, q, topo
+
+
+def test_config5_windows_match_the_oracle_bit_for_bit(journal8192):
+    """Locality at 8192^2, fixed dt, exact contract: windows across tile corners, across the periodic x seam
+    (rows Nx-k .. Nx, 1 .. k: what the ring exchange carries on slabs), across the periodic y seam and across
+    both seams at once (the corner ghosts)."""
+    from oracle.fv import FVOracle
+    d, q, topo = journal8192
+    d = copy.deepcopy(d)
+    d['numerics']['adaptive'] = 0
+    d['numerics']['dt'] = 2e-10
+    s = _solver(d, q, topo)
+    q0 = s.get_q()
+    steps, m = 3, 8
+    s.step(steps)
+    sc = s.scalars()
+    assert sc.step == steps and not sc.stop and sc.dt == 2e-10
+    q1 = s.get_q()
+    del s
+    torch.cuda.empty_cache()
+
+    def rng(a, b):
+        return list(range(a, b))
+    seam_x = rng(N5 + 1 - 30 - m, N5 + 1) + rng(1, 31 + m)       # interior rows Nx-37 .. Nx, 1 .. 38
+    seam_y = rng(N5 + 1 - 40 - m, N5 + 1) + rng(1, 41 + m)
+    windows = [(rng(4090 - m, 4170 + m), rng(4060 - m, 4200 + m)),          # tile corners in the middle
+               (seam_x, rng(5000 - m, 5100 + m)),                            # periodic x seam
+               (rng(6001 - m, 6041 + m), seam_y),                            # periodic y seam
+               (seam_x, seam_y)]                                             # both: the corner ghost cells
+    for rows, cols in windows:
+        ix = np.ix_(range(3), rows, cols)
+        g = dict(d['grid'])
+        g['Nx'], g['Ny'] = len(rows) - 2, len(cols) - 2
+        g['Lx'], g['Ly'] = g['dx'] * g['Nx'], g['dy'] * g['Ny']
+        o = FVOracle(g, d['geometry'], d['properties'], d['numerics'], topo=topo[np.ix_(range(topo.shape[0]), rows, cols)].copy())
+        o.q[...] = q0[ix]
+        o.dt = 2e-10
+        for _ in range(steps):
+            o.update()
+        inner = (slice(None), slice(m, len(rows) - m), slice(m, len(cols) - m))
+        got, ref = q1[ix][inner], o.q[inner]
+        assert np.array_equal(got, ref), (rows[0], cols[0], int((got != ref).sum()))
+    # the ghost layers of the full field are the periodic images of the interior (problem.py:681-707)
+    assert np.array_equal(q1[:, 0, 1:-1], q1[:, N5, 1:-1]) and np.array_equal(q1[:, N5 + 1, 1:-1], q1[:, 1, 1:-1])
+    assert np.array_equal(q1[:, :, 0], q1[:, :, N5]) and np.array_equal(q1[:, :, N5 + 1], q1[:, :, 1])
+
+
+@pytest.mark.parametrize("arith", ['exact', 'fast'])
+def test_config5_shift_invariance_in_x_and_y(journal8192, arith):
+    """The fully periodic problem commutes with cyclic shifts of the interior (solution AND gap field) in x and
+    in y, bit for bit: tiles, halos, the persistent-CTA walk and the seam index arithmetic at 8192^2."""
+    d, q, t1 = journal8192
+    kx, ky = 3001, 1234
+    s1 = _solver(d, q, t1, arith)
+    s1.step(4)
+    a = s1.get_q()
+    dt1 = s1.scalars().dt
+    del s1
+    torch.cuda.empty_cache()
+
+    def shifted(f):
+        out = f.copy()
+        out[:, 1:-1, 1:-1] = np.roll(f[:, 1:-1, 1:-1], (kx, ky), axis=(1, 2))
+        out[:, 0], out[:, -1] = out[:, -2], out[:, 1]
+        out[:, :, 0], out[:, :, -1] = out[:, :, -2], out[:, :, 1]
+        return out
+    s2 = _solver(d, shifted(q), shifted(t1), arith)
+    s2.step(4)
+    b = s2.get_q()
+    assert s2.scalars().dt == dt1
+    assert np.array_equal(np.roll(a[:, 1:-1, 1:-1], (kx, ky), axis=(1, 2)), b[:, 1:-1, 1:-1])

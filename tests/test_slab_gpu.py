@@ -165,13 +165,92 @@ def test_nccl_slabs_match_oracle(tmp_path):
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
     world = min(n, 4)
+    r = _run_workers(tmp_path, NCCL_WORKER, world)
+    assert r.returncode == 0 and "NCCL_SLABS_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+# Two (three) real processes whose slabs live on whatever GPUs the box has -- on a 1-GPU box all on the same
+# device: CUDA IPC maps a peer process's buffer regardless of which device it is on, so the IPC mapping, the
+# system-scope release / acquire flags, the slot parity and the graph replay of gpf_fv_slab_step run exactly
+# as they do across NVLink (the processes time-slice the GPU; a waiting kernel is preempted for its peer's).
+# NCCL refuses two ranks on one device, so the handles travel over gloo; no data-path call uses the backend.
+IPC_WORKER = r"""
+import os, sys, time, numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+mode = sys.argv[2]
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank % torch.cuda.device_count())
+dist.init_process_group("gloo")
+from tests.cases import build_case, inputs
+from gapflow_b200 import _capi
+from gapflow_b200.dist import SlabSolver
+if mode == "parity":
+    for name, arith in (("journal2d_periodic", "exact"), ("slider2d_xDN", "exact"), ("slider2d_allDN_slip", "exact"),
+                        ("journal2d_mcm1_bulk", "exact"), ("journal2d_periodic", "fast")):
+        d, extra = inputs(name)
+        o = build_case(name)
+        s = SlabSolver.from_global(d, o.q, o.topo, extra, peer=True, arith=arith)
+        assert s._comm is not None
+        for k in range(7):
+            o.update()
+        s.step(3)                       # first call: plain launches + graph capture
+        s.step(4)                       # replays
+        q = s.gather_q()
+        sc = s.scalars()
+        if arith == "exact":
+            assert np.array_equal(q, o.q), (name, rank, int((q != o.q).sum()))
+            assert sc.dt == o.dt and sc.step == o.step, (name, sc.dt, o.dt)
+        else:
+            assert np.abs(q - o.q).max() <= 1e-11 * np.abs(o.q).max(), name
+        assert abs(sc.ekin - o.kinetic_energy) <= 1e-11 * abs(o.kinetic_energy)
+        assert abs(s.mass - o.mass) <= 1e-12 * abs(o.mass)
+        assert not s.comm_error()
+        s.close()
+    dist.barrier()
+    if rank == 0:
+        print("IPC_SLABS_OK")
+else:
+    # a lagging peer: rank 1 does not step; rank 0's waits exceed the bound, the run stops and the host is told
+    name = "journal2d_periodic"
+    d, extra = inputs(name)
+    o = build_case(name)
+    s = SlabSolver.from_global(d, o.q, o.topo, extra, peer=True)
+    s.set_comm_timeout(1.0)
+    dist.barrier()
+    if rank == 0:
+        s.step(2)
+        try:
+            s.scalars()
+            print("NO_ERROR_RAISED")
+        except _capi.GapflowError as e:
+            assert e.code == _capi.GPF_E_STATE, e
+            assert s.fv.lib.gpf_last_error()
+            print("LAG_REPORTED")
+    dist.barrier()
+    torch.cuda.synchronize()
+sys.stdout.flush()
+os._exit(0)
+"""
+
+
+def _run_workers(tmp_path, source, world, *args, timeout=600):
     script = tmp_path / "worker.py"
-    script.write_text(NCCL_WORKER)
+    script.write_text(source)
     sock = socket.socket()
     sock.bind(("127.0.0.1", 0))
     port = sock.getsockname()[1]
     sock.close()
-    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), ROOT],
-                       capture_output=True, text=True, timeout=600, cwd=ROOT)
-    assert r.returncode == 0 and "NCCL_SLABS_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    return subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                           "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), ROOT, *args],
+                          capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_ipc_slabs_in_real_processes_match_oracle(tmp_path, world):
+    r = _run_workers(tmp_path, IPC_WORKER, world, "parity")
+    assert r.returncode == 0 and "IPC_SLABS_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_ipc_lagging_peer_is_reported_not_silent(tmp_path):
+    r = _run_workers(tmp_path, IPC_WORKER, 2, "lag")
+    assert r.returncode == 0 and "LAG_REPORTED" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
