@@ -67,9 +67,8 @@ int gpf_fv_cfg_set_bc(gpf_fv_cfg* cfg, const uint8_t masks[4][3][3], const doubl
         for (int k = 1; k <= 2; ++k) {       // D then N, as the reference assigns them
             int dst[3], nd = 0, src[3], ns = 0;
             for (int c = 0; c < 3; ++c) { if (masks[A][k][c]) dst[nd++] = c; if (masks[Vv][k][c]) src[ns++] = c; }
-            if (nd == 0 && ns == 0) continue;
-            if (nd == 0) continue;           // nothing selected on the left-hand side: no-op in NumPy
-            if (!(ns == nd || ns == 1)) {
+            if (nd == 0 && ns <= 1) continue; // empty selection on the left: a (0|1, 1, n) value broadcasts into it, a no-op
+            if (!(ns == nd || ns == 1)) {     // includes nd == 0 with ns >= 2: NumPy cannot broadcast (2, 1, n) into (0, 1, n)
                 set_error("boundary masks: the reference's ghost-cell assignment would raise (shape mismatch between E/W or S/N masks)");
                 return GPF_E_INVALID;
             }

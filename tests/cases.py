@@ -79,6 +79,44 @@ STEP_CASES = {
                                   prop=_BWR), extra=True, rel_rho=1e-3),
 }
 
+# Different masks on OPPOSITE sides: the reference assigns ghost row 0 through the E masks but
+# values it through the W masks and the W target, ghost row -1 the other way round, likewise S / N
+# (problem.py:682-707 vs :736-754), so the ghost value of one component is built from ANOTHER component of the
+# adjacent cell.  Such conditions are not physical: U = V = 2 m/s puts rho, jx and jy on the same scale and a soft
+# fluid (C1 = 3.5e4) with 1e-6 perturbations keeps the runs valid for the compared steps.  Legal
+# combinations have the same number of D components on opposite sides (anything else raises in NumPy).
+def _asym(xE, xW, yS, yN, vals):
+    bc = f"    xE: {xE}\n    xW: {xW}\n    yS: {yS}\n    yN: {yN}\n"
+    return bc + "".join(f"    {k}: {v}\n" for k, v in vals.items())
+
+
+_P3, _SLIDER_U2 = "['P', 'P', 'P']", "geometry:\n    type: inclined\n    hmin: 1.e-5\n    hmax: 2.e-5\n    U: {U}\n    V: {V}\n"
+STEP_CASES.update({
+    # x: E = D,N,N / W = N,D,N  -> ghost row 0: rho <- 2 xW_D - jx, jx <- rho, jy <- jy; ghost row -1: rho <- jx, jx <- 2 xE_D - rho
+    'asym_x_mc1': dict(yaml=_yaml(_grid(19, 23, '2.e-5', '1.e-5', _asym("['D', 'N', 'N']", "['N', 'D', 'N']", _P3, _P3,
+                                                                       dict(xE_D=877.7007, xW_D=877.7107))),
+                                  _SLIDER_U2.format(U=2.0, V=2.0), _ADAPT.format(CFL=0.3, mc=1), C1='3.5e4'), rel_j=1e-6),
+    # y: S = N,N,D / N = D,N,N with MacCormack order -1 and a slip-length field
+    'asym_y_mcm1_slip': dict(yaml=_yaml(_grid(17, 70, '2.e-5', '1.e-5', _asym(_P3, _P3, "['N', 'N', 'D']", "['D', 'N', 'N']",
+                                                                             dict(yS_D=877.6907, yN_D=877.7057))),
+                                        _SLIDER_U2.format(U=2.0, V=2.0), _ADAPT.format(CFL=0.3, mc=-1), bulk=0.01, C1='3.5e4'), extra=True, rel_j=1e-6),
+    # both axes asymmetric (corner ghosts chain two cross-lookups), two D components per side, alternating order
+    'asym_xy_mc0': dict(yaml=_yaml(_grid(21, 18, '2.e-5', '2.e-5', _asym("['D', 'D', 'N']", "['N', 'D', 'D']", "['D', 'N', 'D']", "['D', 'D', 'N']",
+                                                                        dict(xE_D=877.7007, xW_D=877.7107, yS_D=877.6957, yN_D=877.7057))),
+                                   _SLIDER_U2.format(U=2.0, V=2.0), _ADAPT.format(CFL=0.25, mc=0), C1='3.5e4'), rel_j=1e-6),
+    # symmetric masks, non-periodic on both axes, with the two other MacCormack orders (so far only periodic cases used them)
+    'slider2d_allDN_mcm1': dict(yaml=_yaml(_grid(18, 21, '2.e-5', '1.e-5',
+                                                 "    xE: ['D', 'N', 'N']\n    xW: ['D', 'N', 'N']\n    yS: ['N', 'D', 'N']\n    yN: ['N', 'D', 'N']\n"
+                                                 "    xE_D: 880.\n    xW_D: 875.\n    yS_D: 40.\n    yN_D: 45.\n"),
+                                           "geometry:\n    type: inclined\n    hmin: 1.e-5\n    hmax: 2.e-5\n    U: 0.1\n    V: 0.02\n",
+                                           _ADAPT.format(CFL=0.3, mc=-1), bulk=0.02)),
+    'slider2d_xDN_mc0': dict(yaml=_yaml("grid:\n    Lx: 0.0762\n    Ly: 0.0762\n    Nx: 33\n    Ny: 65\n" + _XDN,
+                                        "geometry:\n    type: parabolic\n    hmin: 2.54e-5\n    hmax: 5.08e-5\n    U: 4.57\n    V: 0.\n",
+                                        _ADAPT.format(CFL=0.45, mc=0))),
+})
+ASYM_CASES = ['asym_x_mc1', 'asym_y_mcm1_slip', 'asym_xy_mc0']
+
+
 _BAYADA = """
 properties:
     EOS: Bayada
@@ -125,13 +163,13 @@ VISC_CASES = ['cav1d_dukler', 'cav2d_mcadams', 'slider2d_barus', 'slider2d_barus
               'journal2d_roelands_carreau_slip', 'journal1d_eyring']
 
 
-def perturb(q, rho0, U, seed, rel_rho=1e-6):
+def perturb(q, rho0, U, seed, rel_rho=1e-6, rel_j=1e-3):
     """Seeded perturbation of SURVEY 8(d): q0 *= 1 + 1e-6 N(0,1) (1e-4 makes |v| ~ 1e5 m/s with C1=3.5e10); q1, q2 += 1e-3 rho0 U N(0,1)."""
     rng = np.random.default_rng(seed)
     shape = q.shape[1:]
     q[0] *= 1 + rel_rho * rng.standard_normal(shape)
-    q[1] += 1e-3 * rho0 * U * rng.standard_normal(shape)
-    q[2] += 1e-3 * rho0 * U * rng.standard_normal(shape)
+    q[1] += rel_j * rho0 * U * rng.standard_normal(shape)
+    q[2] += rel_j * rho0 * U * rng.standard_normal(shape)
 
 
 def slip_field(shape, scale, seed=7):
@@ -159,7 +197,7 @@ def build_case(name, cls=None, seed=1234):
     d, extra = inputs(name)
     o = cls(d['grid'], d['geometry'], d['properties'], d['numerics'], extra=extra)
     Umag = max(abs(d['geometry']['U']), abs(d['geometry']['V']))
-    perturb(o.q, d['properties']['rho0'], Umag, seed, STEP_CASES[name].get('rel_rho', 1e-6))
+    perturb(o.q, d['properties']['rho0'], Umag, seed, STEP_CASES[name].get('rel_rho', 1e-6), STEP_CASES[name].get('rel_j', 1e-3))
     o.fill_ghosts()
     if d['numerics']['adaptive']:
         o.dt = d['numerics']['CFL'] * o.dt_crit

@@ -74,3 +74,73 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(_capi, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(_capi.GapflowLibraryError):
         _capi.load()
+
+
+def _table_fill(q, c):
+    """Ghost cells from the (type, source component, target) table of gpf_fv_cfg_set_bc, applied the way the
+    kernels do (x sides, then y sides over the full x range): NumPy emulation of for_each_ghost / ghost_val."""
+    import numpy as np
+    q = q.copy()
+    sides = [(lambda a: a[:, 0, :], lambda a: a[:, 1, :], lambda a: a[:, -2, :]),
+             (lambda a: a[:, -1, :], lambda a: a[:, -2, :], lambda a: a[:, 1, :]),
+             (lambda a: a[:, :, 0], lambda a: a[:, :, 1], lambda a: a[:, :, -2]),
+             (lambda a: a[:, :, -1], lambda a: a[:, :, -2], lambda a: a[:, :, 1])]
+    for s, (ghost, adj, image) in enumerate(sides):
+        new = np.empty_like(ghost(q))
+        for comp in range(3):
+            t, src = c.bc_type[s][comp], c.bc_src[s][comp]
+            if t == _capi.BC_P:
+                new[comp] = image(q)[comp]
+            elif t == _capi.BC_D:
+                new[comp] = (c.bc_val[s] - 0.5 * adj(q)[src] + 0.0 * 0.0) / (0.5 - 0.0)
+            else:
+                new[comp] = ((1.0 - 0.5) * adj(q)[src] + 0.0 * 0.0) / (0.5 - 0.0)
+        ghost(q)[...] = new
+    return q
+
+
+def test_bc_table_equals_reference_ghost_fill_for_every_mask_combination(lib):
+    """All 8 x 8 D/N mask pairs on opposite sides (+ periodic), on x and on y: gpf_fv_cfg_set_bc accepts exactly the
+    combinations on which the reference's NumPy assignment (problem.py:682-707, 736-768; restated in
+    oracle/fv.py::fill_ghosts and pinned to the reference by the golden asym_* cases) does not raise, and its
+    table reproduces the reference's ghost cells bit for bit, cross-lookups and corner chaining included."""
+    import itertools
+    import numpy as np
+    from gapflow_b200 import config
+    from oracle.fv import FVOracle
+    from tests.cases import STEP_CASES
+    d = config.read_yaml_string(STEP_CASES['slider2d_allDN_slip']['yaml'])
+    rng = np.random.default_rng(3)
+    combos = [''.join(t) for t in itertools.product('DN', repeat=3)]
+    n_ok = n_bad = n_cross = 0
+    for axis, (a, b) in enumerate((('xE', 'xW'), ('yS', 'yN'))):
+        for ma, mb in itertools.product(combos + ['PPP'], repeat=2):
+            if (ma == 'PPP') != (mb == 'PPP'):
+                continue                      # io.py:203 asserts equal P masks on opposite sides
+            g = dict(d['grid'])
+            for side, m in ((a, ma), (b, mb)):
+                for kind in 'PDN':
+                    g[f'bc_{side}_{kind}'] = [ch == kind for ch in m]
+                g[f'bc_{side}_D_val'] = 870.0 + 3.0 * rng.random()
+            o = FVOracle(g, d['geometry'], d['properties'], d['numerics'])
+            o.q[...] = rng.random(o.q.shape) + np.array([877., 40., 5.])[:, None, None]
+            q0 = o.q.copy()
+            try:
+                o.fill_ghosts()
+                ref_ok = True
+            except ValueError:
+                ref_ok = False
+            try:
+                c = _capi.make_cfg(g, d['geometry'], d['properties'], d['numerics'])
+                ok = True
+            except _capi.GapflowError as e:
+                assert e.code == _capi.GPF_E_INVALID
+                ok = False
+            assert ok == ref_ok, (axis, ma, mb, ok, ref_ok)
+            if ok:
+                assert np.array_equal(_table_fill(q0, c), o.q), (axis, ma, mb)
+                n_ok += 1
+                n_cross += any(c.bc_src[s][k] != k for s in range(4) for k in range(3))
+            else:
+                n_bad += 1
+    assert n_ok > 40 and n_bad > 40 and n_cross > 20, (n_ok, n_bad, n_cross)

@@ -26,7 +26,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 @pytest.mark.parametrize("name,world", [("journal2d_periodic", 2), ("journal2d_periodic", 3), ("slider2d_xDN", 2),
                                         ("slider2d_allDN_slip", 3), ("journal2d_flip_mc0", 4),
-                                        ("journal2d_mcm1_bulk", 2)])
+                                        ("journal2d_mcm1_bulk", 2), ("asym_x_mc1", 2), ("asym_y_mcm1_slip", 3),
+                                        ("asym_xy_mc0", 2), ("slider2d_allDN_mcm1", 3), ("slider2d_xDN_mc0", 2)])
 def test_in_process_slabs_match_single_domain(name, world):
     from gapflow_b200.dist import InProcessSlabs
     d, extra = inputs(name)
