@@ -82,6 +82,7 @@ SIGNATURES = {
     "gpf_fv_set_viscosity": (_i, [_vp, _i, C.POINTER(C.c_double), _i, C.POINTER(C.c_double), _dp, _dp]),
     "gpf_fv_viscosity": (_i, [_vp, _i, _dp, _i, _vp]),
     "gpf_fv_update_host": (_i, [_vp, _dp, _i, C.POINTER(FvScalars), _vp]),
+    "gpf_fv_set_run_mode": (_i, [_vp, _i]),
     "gpf_fv_pass": (_i, [_vp, _i, _vp]),
     "gpf_fv_pass_part": (_i, [_vp, _i, _i, _vp]),
     "gpf_comm_create": (_i, [_i, _i, _i, _vp, C.POINTER(C.c_void_p)]),

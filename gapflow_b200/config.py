@@ -122,9 +122,16 @@ def sanitize_properties(d):
 
 
 def sanitize_numerics(d):
-    return {'tol': float(d.get('tol', 1e-6)), 'max_it': int(d.get('max_it', 1000)),
-            'dt': float(d.get('dt', 3e-10)), 'adaptive': bool(d.get('adaptive', False)),
-            'CFL': float(d.get('CFL', 0.5)), 'MC_order': int(d.get('MC_order', 1))}
+    out = {'tol': float(d.get('tol', 1e-6)), 'max_it': int(d.get('max_it', 1000)),
+           'dt': float(d.get('dt', 3e-10)), 'adaptive': bool(d.get('adaptive', False)),
+           'CFL': float(d.get('CFL', 0.5)), 'MC_order': int(d.get('MC_order', 1))}
+    # the one key the reference does not have: the arithmetic contract of the pass kernels (include/gapflow_b200.h:
+    # gpf_fv_cfg.arith).  Absent = 'exact' = the reference's NumPy roundings; 'fast' = FMA contraction, 1e-12 per step
+    if 'arith' in d:
+        out['arith'] = str(d['arith'])
+        if out['arith'] not in ('exact', 'fast'):
+            raise IOError("numerics.arith must be 'exact' or 'fast'")
+    return out
 
 
 def sanitize_gp(d):

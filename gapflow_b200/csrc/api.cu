@@ -196,6 +196,13 @@ int gpf_fv_pass(gpf_fv* s, int corrector, void* stream) {
 int gpf_fv_pass_part(gpf_fv* s, int corrector, int part, void* stream) {
     GPF_TRY NEED(s) return s->S.pass(corrector, part, (cudaStream_t)stream); GPF_CATCH
 }
+int gpf_fv_set_run_mode(gpf_fv* s, int until_converged) {
+    GPF_TRY NEED(s)
+    const int uc = until_converged ? 1 : 0;
+    if (s->S.run_mode_uc != uc) { s->S.run_mode_uc = uc; s->S.drop_graphs(); }
+    return GPF_OK;
+    GPF_CATCH
+}
 int gpf_fv_halo_pack(gpf_fv* s, int rel, double* sendbuf, void* stream) {
     GPF_TRY NEED(s && sendbuf) return s->S.halo_pack(rel, sendbuf, (cudaStream_t)stream); GPF_CATCH
 }
@@ -253,7 +260,7 @@ int gpf_gp_workspace_bytes(int M_max, int D, int n_out, size_t* bytes) {
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaGetLastError();
     if (sms <= 0) sms = 148;
-    *bytes = GpModel::workspace_bytes(M_max, D, n_out, sms);
+    *bytes = GpModel::workspace_bytes(M_max, D, n_out, GpModel::var_slots(sms));
     return GPF_OK;
     GPF_CATCH
 }

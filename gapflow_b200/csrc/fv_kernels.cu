@@ -866,6 +866,7 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     pflags = reinterpret_cast<int*>(p); p += align_up((size_t)npartial * sizeof(int), 256);
     qtable = reinterpret_cast<double**>(p);
     redo = reinterpret_cast<int*>(p + 128);         // zeroed with the workspace
+    prog = reinterpret_cast<unsigned*>(p + 144);    // 24 counters (96 bytes), zeroed with the workspace
     p += 256;
     // planes are allocated with stride plane_b; the layout's plane stride must match
     P.L.plane = plane_b / 8;
@@ -1123,6 +1124,11 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     }
     A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags; A.redo = S.redo;
     A.until_converged = until_converged;
+    // wave throttle (fv_pass_kernel.cuh): launches that may run concurrently (EDGE on a side stream beside
+    // INTERIOR) count in separate slots
+    static const int window = [] { const char* e = getenv("GPF_WAVE_WINDOW"); return e ? atoi(e) : 3; }();
+    A.wave_window = window;
+    A.prog = S.prog + 8 * (part == GPF_PART_EDGE ? 1 : part == GPF_PART_INTERIOR ? 2 : 0);
     A.sg_p = S.sg_p; A.sg_xz = S.sg_xz; A.sg_yz = S.sg_yz;
     for (int k = 0; k < 3; ++k) A.sg_scale[k] = S.sg_scale[k];
     // INTERIOR leaves a few CTA slots empty so that the exchange kernels of the side stream (pack,
@@ -1334,7 +1340,7 @@ int FvSolver::update_host_pipelined(double* q_host, cudaStream_t s) {
 
 // ---- slab decomposition building blocks (gapflow_b200/dist.py drives them) ---------------
 int FvSolver::pass(int corrector, int part, cudaStream_t s) {
-    return corrector ? launch_pass<true>(*this, 0, s, part) : launch_pass<false>(*this, 0, s, part);
+    return corrector ? launch_pass<true>(*this, run_mode_uc, s, part) : launch_pass<false>(*this, run_mode_uc, s, part);
 }
 
 int FvSolver::halo_pack(int rel, double* send, cudaStream_t s) {
@@ -1378,7 +1384,7 @@ int FvSolver::reduce_local(int kind, double* rec5, cudaStream_t s) {
 
 int FvSolver::finish(int mode, const double* recs, int nrec, cudaStream_t s) {
     if (mode < FIN_STEP || mode > FIN_REFRESH || !recs || nrec < 1) { set_error("bad finish arguments"); return GPF_E_INVALID; }
-    int rc = launch_finish(*this, 0, mode, 0, s, reinterpret_cast<const Rec5*>(recs), nrec);
+    int rc = launch_finish(*this, 0, mode, run_mode_uc, s, reinterpret_cast<const Rec5*>(recs), nrec);
     if (rc) return rc;
     if (mode != FIN_REFRESH) dirty_scalars = false;
     else refresh_valid = true;
@@ -1559,14 +1565,14 @@ int FvSolver::finish_recv(SlabComm& c, int mode, double* recs_out, cudaStream_t 
 // captured once as a CUDA graph (10 kernels) and replayed.
 int FvSolver::slab_step_once(SlabComm& c, int lo, int hi, double* recs_out, cudaStream_t s) {
     int rc;
-    if ((rc = launch_pass<false>(*this, 0, s))) return rc;
+    if ((rc = launch_pass<false>(*this, run_mode_uc, s))) return rc;
     if ((rc = halo_send(c, 1, lo, hi, s))) return rc;
     if ((rc = halo_recv(c, 1, s))) return rc;
-    if ((rc = launch_pass<true>(*this, 0, s))) return rc;
+    if ((rc = launch_pass<true>(*this, run_mode_uc, s))) return rc;
     if ((rc = halo_send(c, 2, lo, hi, s))) return rc;
     if ((rc = halo_recv(c, 2, s))) return rc;
     if ((rc = record_send(c, 0, s))) return rc;
-    return finish_recv(c, FIN_STEP, recs_out, s, 0);
+    return finish_recv(c, FIN_STEP, recs_out, s, run_mode_uc);
 }
 
 int FvSolver::slab_step(SlabComm& c, int lo, int hi, int n, double* recs_out, cudaStream_t s) {

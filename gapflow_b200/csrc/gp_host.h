@@ -45,6 +45,7 @@ struct GpModel {
     int build_var1d(cudaStream_t s);
 
     static size_t workspace_bytes(int Mmax, int D, int nout, int nslots);
+    static int var_slots(int sms);           // resident CTAs of the variance kernel = v panels in the workspace
     int init(int Mmax, int D, int nout, void* ws, size_t bytes);
     int factor(const double* Xtrain, int M, double log_amp, const double* log_scale, double yerr, const double* Y,
                cudaStream_t s);

@@ -107,46 +107,54 @@ __global__ void gp_build_K_kernel(const double* Xs, int M, int Mp, int D, double
 // ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, int k, double* Dinv, int* info) {
     extern __shared__ double potrf_sm[];
-    double (*S)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);
-    double (*X)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm + NB * (NB + 1));
+    double (*S)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);                  // working copy, then inv(L_kk)
+    double (*Lm)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm + NB * (NB + 1));  // L_kk
     const int tid = threadIdx.x;
     double* Akk = A + (size_t)k * NB * Mp + (size_t)k * NB;
     for (int e = tid; e < NB * NB; e += 256) S[e / NB][e % NB] = Akk[(size_t)(e / NB) * Mp + e % NB];
     __syncthreads();
+    // right-looking, one barrier per column: every thread forms 1 / sqrt(d_jj) itself and scales the two column
+    // entries of its update on the fly (column j of S is never written by the update of step j), the scaled column
+    // goes to Lm.  16 x 16 threads sweep the trailing triangle only.  (r2a: the version with three barriers per
+    // column and a one-thread-per-column inverse took 92 us per block, 14 of the 41 ms of a factorisation.)
+    const int ty = tid >> 4, tx = tid & 15;
     for (int j = 0; j < NB; ++j) {
-        if (tid == 0) {
-            const double d = S[j][j];
-            if (!(d > 0.0)) atomicExch(info, k * NB + j + 1);
-            S[j][j] = sqrt(d);
-        }
-        __syncthreads();
-        const double djj = S[j][j];
-        if (tid > j && tid < NB) S[tid][j] /= djj;
-        __syncthreads();
-        // trailing update of the lower triangle: rows i > j, cols j < c <= i
-        for (int e = tid; e < NB * NB; e += 256) {
-            const int i = e / NB, c = e % NB;
-            if (i > j && c > j && c <= i) S[i][c] -= S[i][j] * S[c][j];
+        const double d = S[j][j];
+        if (tid == 0 && !(d > 0.0)) atomicExch(info, k * NB + j + 1);
+        const double djj = sqrt(d), inv = 1.0 / djj;
+        if (tid >= j && tid < NB) Lm[tid][j] = (tid == j) ? djj : S[tid][j] * inv;
+        if (tid < j) Lm[tid][j] = 0.0;
+        for (int i = j + 1 + ty; i < NB; i += 16) {
+            const double lij = S[i][j] * inv;
+            for (int c = j + 1 + tx; c <= i; c += 16) S[i][c] -= lij * (S[c][j] * inv);
         }
         __syncthreads();
     }
-    // inverse of the lower-triangular block: thread c solves column c
-    if (tid < NB) {
-        const int c = tid;
-        for (int i = 0; i < c; ++i) X[i][c] = 0.0;
-        X[c][c] = 1.0 / S[c][c];
-        for (int i = c + 1; i < NB; ++i) {
+    // X = inv(L_kk) into S, four threads per column: X_cc = 1 / L_cc, X_ic = -(sum_{j=c}^{i-1} L_ij X_jc) / L_ii with
+    // the sum split over the four threads (j = c + p, c + p + 4, ...) and folded by two shuffles; the four threads
+    // of a column sit in one warp, rows advance in lock step
+    {
+        const int c = tid >> 2, p = tid & 3;
+        const int c_first = (tid >> 5) * 8;               // first of the warp's 8 columns: the warp walks rows c_first + 1 ..
+        for (int i = 0; i < c; ++i) if (p == 0) S[i][c] = 0.0;
+        if (p == 0) S[c][c] = 1.0 / Lm[c][c];
+        __syncwarp();
+        for (int i = c_first + 1; i < NB; ++i) {          // warp-uniform trip count (full-mask shuffles)
+            const bool act = i > c;
             double s = 0.0;
-            for (int j = c; j < i; ++j) s += S[i][j] * X[j][c];
-            X[i][c] = -s / S[i][i];
+            if (act) for (int j = c + p; j < i; j += 4) s += Lm[i][j] * S[j][c];
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            if (act && p == 0) S[i][c] = -s / Lm[i][i];
+            __syncwarp();
         }
     }
     __syncthreads();
     double* Dk = Dinv + (size_t)k * NB * NB;
     for (int e = tid; e < NB * NB; e += 256) {
         const int i = e / NB, c = e % NB;
-        Akk[(size_t)i * Mp + c] = (c <= i) ? S[i][c] : 0.0;
-        Dk[e] = X[i][c];
+        Akk[(size_t)i * Mp + c] = Lm[i][c];
+        Dk[e] = S[i][c];
     }
 }
 
@@ -389,14 +397,37 @@ __global__ void gp_max_reduce_kernel(const double* part, int n, double* out) {
 // ------------------------------------------------------------------------------------
 constexpr int VBK = 16;                       // k-depth of one pipeline stage
 constexpr int VST = 3;                        // cp.async stages
-constexpr int LDA_V = VBK + 2;                // stride of the staged L sub-tile rows
+constexpr int LDA_V = VBK + 4;                // row stride of the staged L sub-tile: = 4 mod 16 doubles, so the 16 lanes of a
+                                              // half-warp (4 rows x 4 k) hit 16 different 8-byte banks (r2a: VBK + 2 gave 2-way
+                                              // conflicts on every A-fragment load, 29 % of the kernel's shared-memory wavefronts)
 constexpr size_t VAR_STAGE = (size_t)(NB * LDA_V + VBK * LDQ) * 8;
-constexpr size_t VAR_SOLVE = (size_t)(NB * LDQ + NB * LDT) * 8;
+constexpr size_t VAR_SOLVE = (size_t)(NB * LDQ) * 8;                          // R = Ks - acc, the B operand of the block solve
 constexpr size_t VAR_MAIN = (VST * VAR_STAGE > VAR_SOLVE) ? VST * VAR_STAGE : VAR_SOLVE;
 constexpr int GP_MAXD = 8;
 constexpr size_t VAR_SMEM = VAR_MAIN + (size_t)(NQ * GP_MAXD + NB * GP_MAXD + NQ * 2) * 8;
+constexpr int VAR_CTAS_PER_SM = 2;            // 95 KB and <= 128 registers per CTA: two CTAs share an SM, so the tensor pipe has
+                                              // work while the other CTA sits at a barrier or in its block solve (r2a, one CTA per
+                                              // SM: DMMA pipe 72 % busy, stalls = barrier + cp.async wait)
 
-__global__ void __launch_bounds__(256, 1) gp_var_kernel(const double* L, const double* Dinv, const double* Xs, int M, int Mp,
+// A-fragment loads of the 64 x 64 block solve straight from global memory (inv(L_kk), 32 KB, L2-resident: every CTA
+// is at a similar block row); keeps the solve's A operand out of shared memory
+__device__ __forceinline__ void warp_mma_gA(double (&acc)[4][4][2], const double* Ag, int lda, const double* Bs, int ldb, int lane) {
+    const int r = lane >> 2, c = lane & 3;
+#pragma unroll 4
+    for (int kk = 0; kk < NB / 4; ++kk) {
+        double a[4], b[4];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi) a[mi] = __ldg(Ag + (size_t)(mi * 8 + r) * lda + kk * 4 + c);
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[(kk * 4 + c) * ldb + ni * 8 + r];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) dmma(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+    }
+}
+
+__global__ void __launch_bounds__(256, VAR_CTAS_PER_SM) gp_var_kernel(const double* L, const double* Dinv, const double* Xs, int M, int Mp,
                                                         GpKern kp, const double* Xtest, long long N, const double* noise,
                                                         double noise_scalar, double* var, double* scratch,
                                                         double* vmax_part, long long* imax_part) {
@@ -427,20 +458,19 @@ __global__ void __launch_bounds__(256, 1) gp_var_kernel(const double* L, const d
             double acc[4][4][2] = {};
             const int nk = kb * NB / VBK;
             const double* Lrow = L + (size_t)kb * NB * Mp;
+            // L sub-tile: 64 rows x 16 doubles = 512 16-byte chunks (2 per thread); V sub-tile: 16 rows x 128 = 1024 chunks (4)
+            const int lrow = tid >> 3, lch = tid & 7, vrow = tid >> 6, vch = tid & 63;
             auto stage_load = [&](int s, int kt) {
                 double* As = sm + (size_t)s * (VAR_STAGE / 8);
                 double* Bs = As + NB * LDA_V;
-                // L sub-tile: 64 rows x 16 doubles = 512 16-byte chunks; V sub-tile: 16 rows x 128 = 1024 chunks
-                for (int e = tid; e < 512; e += 256) {
-                    const int row = e >> 3, ch = e & 7;
-                    cp_async16(As + row * LDA_V + ch * 2, Lrow + (size_t)row * Mp + (size_t)kt * VBK + ch * 2);
-                }
-                for (int e = tid; e < 1024; e += 256) {
-                    const int row = e >> 6, ch = e & 63;
-                    cp_async16(Bs + row * LDQ + ch * 2, V + (size_t)(kt * VBK + row) * NQ + ch * 2);
-                }
+                const double* lg = Lrow + (size_t)kt * VBK + lch * 2;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) cp_async16(As + (lrow + 32 * h) * LDA_V + lch * 2, lg + (size_t)(lrow + 32 * h) * Mp);
+                const double* vg = V + (size_t)(kt * VBK) * NQ + vch * 2;
+#pragma unroll
+                for (int h = 0; h < 4; ++h) cp_async16(Bs + (vrow + 4 * h) * LDQ + vch * 2, vg + (size_t)(vrow + 4 * h) * NQ);
             };
-            __syncthreads();                      // previous block's solve buffers / V stores are done
+            __syncthreads();                      // previous block's solve buffer / V stores are done
             for (int s = 0; s < VST - 1; ++s) {
                 if (s < nk) stage_load(s, s);
                 cp_async_commit();
@@ -457,33 +487,37 @@ __global__ void __launch_bounds__(256, 1) gp_var_kernel(const double* L, const d
             }
             cp_async_wait<0>();
             __syncthreads();
-            // ---- R = Ks[kb] - acc, evaluated in the accumulator layout; staged as the B operand ----
+            // ---- R = Ks[kb] - acc in the accumulator layout, staged as the B operand of the block solve.  The sums go
+            //      first so that the accumulators are dead while the kernel function is evaluated ----
             for (int e = tid; e < NB * D; e += 256) {
                 const int m = kb * NB + e / D;
                 sxt[(e / D) * GP_MAXD + e % D] = (m < M) ? Xs[(size_t)m * D + e % D] : 0.0;
             }
             double* Rs = sm;                              // [NB][LDQ]
-            double* Ds = sm + NB * LDQ;                   // [NB][LDT]
-            const double* Dk = Dinv + (size_t)kb * NB * NB;
-            for (int e = tid; e < NB * NB; e += 256) Ds[(e / NB) * LDT + e % NB] = Dk[e];
-            __syncthreads();
 #pragma unroll
+            for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) {
+                    const int m = wm * 32 + mi * 8 + r, n = wn * 32 + ni * 8 + c * 2;
+                    *reinterpret_cast<double2*>(Rs + m * LDQ + n) = make_double2(-acc[mi][ni][0], -acc[mi][ni][1]);
+                }
+            __syncthreads();                              // sxt complete (the Rs elements are this thread's own)
+#pragma unroll 1
             for (int mi = 0; mi < 4; ++mi) {
                 const int m = wm * 32 + mi * 8 + r;
-                const bool real = kb * NB + m < M;
-#pragma unroll
+                if (kb * NB + m >= M) continue;           // padding rows: R = -acc
+#pragma unroll 2
                 for (int ni = 0; ni < 4; ++ni)
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         const int n = wn * 32 + ni * 8 + c * 2 + h;
-                        const double kv = real ? m32_rt(sxt + m * GP_MAXD, sxq + n * GP_MAXD, D, kp.amp) : 0.0;
-                        Rs[m * LDQ + n] = kv - acc[mi][ni][h];
+                        Rs[m * LDQ + n] += m32_rt(sxt + m * GP_MAXD, sxq + n * GP_MAXD, D, kp.amp);
                     }
             }
             __syncthreads();
             // ---- V[kb] = inv(L_kk) R ----
             double vv[4][4][2] = {};
-            warp_mma<false, NB / 4>(vv, Ds + wm * 32 * LDT, LDT, Rs + wn * 32, LDQ, lane);
+            warp_mma_gA(vv, Dinv + (size_t)kb * NB * NB + (size_t)wm * 32 * NB, NB, Rs + wn * 32, LDQ, lane);
 #pragma unroll
             for (int mi = 0; mi < 4; ++mi)
 #pragma unroll
@@ -749,6 +783,8 @@ __global__ void __launch_bounds__(256) gp_nlml_finish_kernel(const double* L, co
 // =====================================================================================
 static size_t al(size_t x) { return (x + 255) / 256 * 256; }
 
+int GpModel::var_slots(int sms) { return VAR_CTAS_PER_SM * sms; }
+
 size_t GpModel::workspace_bytes(int Mmax, int D, int nout, int nslots) {
     const size_t Mp = (size_t)(Mmax + NB - 1) / NB * NB;
     size_t b = 256;
@@ -771,7 +807,7 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
     int dev = 0, sms = 148;
     GPF_CUDA(cudaGetDevice(&dev));
     GPF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    nslots = sms;
+    nslots = VAR_CTAS_PER_SM * sms;     // one v panel per resident CTA of the variance kernel
     {
         // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: set it for the device
         // of every model (cheap), not once per process

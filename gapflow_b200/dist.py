@@ -113,6 +113,7 @@ class SlabSolver:
         self.rec = torch.zeros(5, dtype=torch.float64, device=dev)
         self.recs = torch.zeros((self.world, 5), dtype=torch.float64, device=dev)
         self._timing, self._ev = False, []
+        self._run_mode = 0
         # edge tile rows first, their exchange on a side stream under the interior launch
         self.overlap = overlap and self.world > 1
         self._side = torch.cuda.Stream(device=dev, priority=-1) if self.overlap else None
@@ -244,8 +245,13 @@ class SlabSolver:
         self.fv.fill_ghosts()
         self._exchange(0)
 
-    def step(self, n=1):
-        """n x Problem.update() (problem.py:509-569); enqueues only."""
+    def step(self, n=1, until_converged=False):
+        """n x Problem.update() (problem.py:509-569); enqueues only.  ``until_converged``: steps become no-ops on
+        the device once the run-loop condition (problem.py:401) is false -- on every rank at the same step."""
+        uc = 1 if until_converged else 0
+        if uc != self._run_mode:
+            _capi.check(self.lib.gpf_fv_set_run_mode(self.h, uc))
+            self._run_mode = uc
         if self._comm is not None and not self._timing:
             # peer memory: the whole step is the library's own kernels, replayed as one CUDA graph
             lo, hi = self._neighbours()
@@ -477,3 +483,117 @@ def owned_rows(Nx, rank, world):
     a = start + (0 if rank == 0 else 1)
     b = start + n + (2 if rank == world - 1 else 1)
     return a, b
+
+
+# -------------------------------------------------------------------------------------------
+# Problem-level view of a slab-decomposed run (gapflow_b200.problem.Problem under torchrun)
+# -------------------------------------------------------------------------------------------
+class Parallel:
+    """Where this process stands in a slab-decomposed ``Problem``: rank, world, the host-level collective
+    (``allgather`` of small Python objects, rank order) and -- for ranks that are threads of one process --
+    the tensor exchanger that stands in for the device-side exchange.  ``Parallel.auto()`` is what ``Problem``
+    uses when none is given: the initialised ``torch.distributed`` group, else ``RANK`` / ``WORLD_SIZE`` /
+    ``LOCAL_RANK`` of a torchrun launch (NCCL, one GPU per rank), else a single domain."""
+
+    def __init__(self, rank=0, world=1, coll=None, exchanger=None, group=None):
+        from .surrogate import LocalColl
+        self.rank, self.world, self.group = rank, world, group
+        self.coll = coll or LocalColl()
+        self._exchanger = exchanger
+
+    def exchanger(self, periodic):
+        return None if self._exchanger is None else self._exchanger(self.rank, periodic)
+
+    @classmethod
+    def auto(cls):
+        if not dist.is_available():
+            return cls()
+        if not dist.is_initialized():
+            if int(os.environ.get('WORLD_SIZE', '1')) <= 1 or 'RANK' not in os.environ:
+                return cls()
+            local = int(os.environ.get('LOCAL_RANK', os.environ['RANK']))
+            torch.cuda.set_device(local)
+            dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+        if dist.get_world_size() == 1:
+            return cls()
+        from .surrogate import DistColl
+        return cls(dist.get_rank(), dist.get_world_size(), DistColl())
+
+    @classmethod
+    def threads(cls, tc, rank):
+        """rank ``rank`` of a ``ThreadColl`` (all slabs in one process, one thread per rank, one GPU)."""
+        return cls(rank, tc.world, tc.view(rank), exchanger=tc.exchanger)
+
+
+class SlabField:
+    """The ``FVSolver`` interface ``Problem`` drives, on one rank's slab of the global problem: ``q``, the closure
+    fields and the scalars are those of the GLOBAL padded arrays (gathered over the ranks on access: output and
+    host edits only, never inside the time loop), so ``Problem`` keeps the reference's semantics
+    (problem.py:314-362, 616-637) for any number of ranks."""
+
+    def __init__(self, grid, geo, prop, numerics, topo_global, extra_global, par, arith='exact'):
+        self.par, self.grid = par, grid
+        self.start, self.n = slab_rows(grid['Nx'], par.world)[par.rank]
+        sl = slice(self.start, self.start + self.n + 2)
+        ex = None if extra_global is None else np.ascontiguousarray(np.asarray(extra_global)[..., sl, :])
+        xch = par.exchanger(x_periodic(grid))
+        self.slab = SlabSolver(grid, geo, prop, numerics, topo=np.ascontiguousarray(topo_global[:, sl]), extra=ex,
+                               rank=par.rank, world=par.world, group=par.group, exchanger=xch, arith=arith)
+        if xch is not None:                       # SlabSolver leaves the first fold to a caller that brings its own exchanger
+            self.slab.pre_run(reset_ekin_old=True)
+        self.fv = self.slab.fv
+        self.device, self.lib, self.h = self.fv.device, self.fv.lib, self.fv.h
+        self.shape = (grid['Nx'] + 2, grid['Ny'] + 2)           # of the GLOBAL padded arrays
+        self.local_shape = self.fv.shape
+
+    # rows of the global padded array this rank contributes when a field is assembled (every row exactly once)
+    def _own(self):
+        a, b = owned_rows(self.grid['Nx'], self.par.rank, self.par.world)
+        return a - self.start, b - self.start
+
+    def gather_rows(self, local):
+        """global (..., Nx+2, Ny+2) host array from every rank's local (..., n+2, Ny+2) array (host or device)."""
+        if isinstance(local, torch.Tensor):
+            local = local.cpu().numpy()
+        lo, hi = self._own()
+        parts = self.par.coll.allgather(np.ascontiguousarray(local[..., lo:hi, :]))
+        return np.concatenate(parts, axis=-2)
+
+    def get_q(self, out=None):
+        q = self.gather_rows(self.slab.get_q())
+        if out is None:
+            return q
+        out[...] = q
+        return out
+
+    def set_q(self, q):
+        self.slab.set_q(np.ascontiguousarray(np.asarray(q)[:, self.start:self.start + self.n + 2]))
+
+    def closures_local(self, stale=False):
+        return self.fv.closures(stale=stale)
+
+    def gather_fields(self, fields):
+        return tuple(self.gather_rows(f) for f in fields)
+
+    def closures(self, on_device=False, stale=False):
+        return self.gather_fields(self.closures_local(stale))
+
+    def pre_run(self, reset_ekin_old=False):
+        self.slab.pre_run(reset_ekin_old)
+
+    def step(self, n=1, until_converged=False):
+        self.slab.step(n, until_converged)
+
+    def fill_ghosts(self):
+        self.slab.fill_ghosts()
+
+    def scalars(self):
+        return self.slab.scalars()
+
+    def set_scalars(self, **kw):
+        self.fv.set_scalars(**kw)          # the loop state is replicated: every rank applies the same edit
+
+    mass = property(lambda self: self.slab.mass)
+
+    def close(self):
+        self.slab.close()

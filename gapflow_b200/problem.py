@@ -101,7 +101,13 @@ class _BulkStress(_Closure):
 
 
 class Problem:
-    def __init__(self, options, grid, numerics, prop, geo, gp=None, database=None, extra=None, extra_field=None):
+    def __init__(self, options, grid, numerics, prop, geo, gp=None, database=None, extra=None, extra_field=None,
+                 parallel=None, arith=None):
+        """``parallel``: a ``gapflow_b200.dist.Parallel`` (default ``Parallel.auto()``: the torch.distributed group or
+        torchrun's RANK / WORLD_SIZE; one process per GPU).  With more than one rank the grid is slab-decomposed
+        along x; every attribute below keeps its GLOBAL meaning and rank 0 writes the files.
+        ``arith``: 'exact' (default; bit-identical to the reference's NumPy expressions) or 'fast' (FMA contraction,
+        1e-12 per step); also ``numerics['arith']`` of the YAML."""
         if extra is None:
             extra = extra_field                                        # the reference's keyword (problem.py:85)
         if gp is not None and database is None:
@@ -115,12 +121,24 @@ class Problem:
         self.topo = _Topo(grid, geo)
         shape = (grid['Nx'] + 2, grid['Ny'] + 2)
         self._extra = None if extra is None else np.broadcast_to(np.asarray(extra, dtype=float), (1, *shape)).copy()
-        self._solver = FVSolver(grid, geo, prop, numerics, topo=self.topo.full, extra=self._extra)
+        from .dist import Parallel, SlabField
+        self._par = parallel if parallel is not None else Parallel.auto()
+        self._root = self._par.rank == 0
+        arith = arith or numerics.get('arith', 'exact')
         self.has_gp_model = gp is not None
         self._sur = None
-        if gp is not None:
-            from .surrogate import SurrogateDriver
-            self._sur = SurrogateDriver(self._solver, gp, database, grid['dim'], write_freq=options['write_freq'])
+        if self._par.world == 1:
+            self._solver = FVSolver(grid, geo, prop, numerics, topo=self.topo.full, extra=self._extra, arith=arith)
+            if gp is not None:
+                from .surrogate import SurrogateDriver
+                self._sur = SurrogateDriver(self._solver, gp, database, grid['dim'], write_freq=options['write_freq'])
+        else:
+            # x-slabs, one per rank (problem.py has no counterpart: the reference is single-process)
+            self._solver = SlabField(grid, geo, prop, numerics, self.topo.full, self._extra, self._par, arith=arith)
+            if gp is not None:
+                from .surrogate import SlabSurrogateDriver
+                self._sur = SlabSurrogateDriver(self._solver.slab, gp, database, grid['dim'], self._par.coll,
+                                                write_freq=options['write_freq'])
         self.database = database
         self._q_host = np.empty((3, *shape))
         self._q_synced = False       # _q_host equals the device field
@@ -141,7 +159,9 @@ class Problem:
         self.history = {"step": [], "time": [], "ekin": [], "residual": [], "vsound": []}
         self.outdir, self._sol, self._frames = None, None, 0
         if not options['silent']:
-            self._open_output()
+            if self._root:
+                self._open_output()
+            self.outdir = self._par.coll.allgather(self.outdir)[0]       # every rank knows where rank 0 writes
 
     # -- constructors (problem.py:251-308) --------------------------------------------------
     @classmethod
@@ -228,9 +248,15 @@ class Problem:
     def _closures(self):
         if self._clos_cache is None:
             self._sync_to_device()
-            self._clos_cache = self._solver.closures(stale=bool(self.step))
-            if self._sur is not None and self._sur.ready:
-                self._clos_cache = self._sur.closures(self._clos_cache)
+            if self._par.world == 1:
+                self._clos_cache = self._solver.closures(stale=bool(self.step))
+                if self._sur is not None and self._sur.ready:
+                    self._clos_cache = self._sur.closures(self._clos_cache)
+            else:                                   # overlay the GP means on this rank's rows, then assemble the global fields
+                loc = self._solver.closures_local(stale=bool(self.step))
+                if self._sur is not None and self._sur.ready:
+                    loc = self._sur.closures(loc)
+                self._clos_cache = self._solver.gather_fields(loc)
         return self._clos_cache
 
     mass = property(lambda self: (self._sync_to_device(), np.float64(self._solver.mass))[1])
@@ -248,7 +274,7 @@ class Problem:
         """problem.py:412-443 (fixed-form branch)."""
         self._sync_to_device()
         if self._sur is not None:
-            if self.outdir is not None:
+            if self.outdir is not None and self._root:
                 self.database.output_path = self.outdir
             self._sur.pre_run()
             if not self.options['silent']:
@@ -270,7 +296,7 @@ class Problem:
             self._solver.step(1)
         self._q_synced, self._clos_cache = False, None
         sc = self._pull()
-        if sc.stop and not self.options['silent']:
+        if sc.stop and not self.options['silent'] and self._root:
             print("Stopping: NaN or negative density detected (state of the previous step restored).")
 
     def run(self, keep_open=False):
@@ -281,9 +307,10 @@ class Problem:
         self.history = {"step": [], "time": [], "ekin": [], "residual": [], "vsound": []}
         silent = self.options['silent']
         if not silent:
-            print(61 * '-')
-            print(f"{'Step':6s} {'Timestep':10s} {'Time':10s} {'CFL':10s} {'Residual':10s}")
-            print(61 * '-')
+            if self._root:
+                print(61 * '-')
+                print(f"{'Step':6s} {'Timestep':10s} {'Time':10s} {'CFL':10s} {'Residual':10s}")
+                print(61 * '-')
             self.write(params=False)
         old = {s: signal.signal(s, self._receive_signal) for s in (signal.SIGINT, signal.SIGTERM)}
         self._tic = datetime.now()
@@ -300,6 +327,8 @@ class Problem:
                     self._solver.step(n, until_converged=True)    # loop condition evaluated on the device
                 self._q_synced, self._clos_cache = False, None
                 self._pull()
+                if self._par.world > 1:              # a termination signal reaches one rank: all ranks leave together
+                    self._stop = any(self._par.coll.allgather(bool(self._stop)))
                 if self.step % wf == 0 and not silent:
                     self.write()
         finally:
@@ -320,11 +349,12 @@ class Problem:
             self._sol.close()
             self._sol = None
         speed = self.step / max(walltime.total_seconds(), 1e-12)
-        print(33 * '=')
-        print("Total walltime   : ", str(walltime).split('.')[0])
-        print(f"({speed:.2f} steps/s)")
-        print(33 * '=')
-        if not silent:
+        if self._root:
+            print(33 * '=')
+            print("Total walltime   : ", str(walltime).split('.')[0])
+            print(f"({speed:.2f} steps/s)")
+            print(33 * '=')
+        if not silent and self._root:
             with open(os.path.join(self.outdir, 'history.csv'), 'w', newline='') as f:
                 w = csv.writer(f)
                 w.writerow(list(self.history))
@@ -351,37 +381,73 @@ class Problem:
         with open(os.path.join(self.outdir, 'config.yml'), 'w') as f:
             yaml.dump(dict(version='gapflow_b200', options=self.options, grid=self.grid, numerics=self.numerics,
                            geo=self.geo, prop=self.prop), f)
+        # Layout as muGrid's FileIONetCDF leaves it for the reference's readers (GaPFlow/viz/plotting.py:235-240,
+        # 307-312, 331-349 index the arrays by position): multi-component fields (frame, component, sub-point = 1,
+        # x, y), scalar fields (frame, x, y).  Variable names are the reference's (problem.py:185-205); the
+        # dimension NAMES are this writer's (muGrid's are unverified here: INTEGRATION.md).
         nx, ny = self.grid['Nx'] + 2, self.grid['Ny'] + 2
         with netcdf_file(os.path.join(self.outdir, 'topo.nc'), 'w') as t:
-            for d, n in (('frame', None), ('comp4', 4), ('nx', nx), ('ny', ny)):
+            for d, n in (('frame', None), ('comp4', 4), ('subpt', 1), ('nx', nx), ('ny', ny)):
                 t.createDimension(d, n)
-            v = t.createVariable('topography', 'f8', ('frame', 'comp4', 'nx', 'ny'))
-            v[0] = self.topo.full
+            v = t.createVariable('topography', 'f8', ('frame', 'comp4', 'subpt', 'nx', 'ny'))
+            v[0, :, 0] = self.topo.full
         self._sol = netcdf_file(os.path.join(self.outdir, 'sol.nc'), 'w')
-        for d, n in (('frame', None), ('comp3', 3), ('comp12', 12), ('nx', nx), ('ny', ny)):
+        for d, n in (('frame', None), ('comp3', 3), ('comp12', 12), ('subpt', 1), ('nx', nx), ('ny', ny)):
             self._sol.createDimension(d, n)
-        self._sol.createVariable('solution', 'f8', ('frame', 'comp3', 'nx', 'ny'))
+        self._sol.createVariable('solution', 'f8', ('frame', 'comp3', 'subpt', 'nx', 'ny'))
         self._sol.createVariable('pressure', 'f8', ('frame', 'nx', 'ny'))
-        self._sol.createVariable('wall_stress_xz', 'f8', ('frame', 'comp12', 'nx', 'ny'))
-        self._sol.createVariable('wall_stress_yz', 'f8', ('frame', 'comp12', 'nx', 'ny'))
+        self._sol.createVariable('wall_stress_xz', 'f8', ('frame', 'comp12', 'subpt', 'nx', 'ny'))
+        self._sol.createVariable('wall_stress_yz', 'f8', ('frame', 'comp12', 'subpt', 'nx', 'ny'))
+        # predictive-variance fields of the GP models, in the reference's order (problem.py:195-203)
+        for key, name in (('xz', 'wall_stress_xz_var'), ('yz', 'wall_stress_yz_var'), ('zz', 'pressure_var')):
+            if key in self.gp_models:
+                self._sol.createVariable(name, 'f8', ('frame', 'nx', 'ny'))
+
+    def _variance_fields(self):
+        """{name: (Nx+2, Ny+2) host array} of the GP models' variance fields as the reference's muGrid fields hold
+        them at write time: the variance of the last inference that computed one (stress.py:353-354, 617-618),
+        zeros before the first."""
+        out = {}
+        for key, name in (('xz', 'wall_stress_xz_var'), ('yz', 'wall_stress_yz_var'), ('zz', 'pressure_var')):
+            m = self.gp_models.get(key)
+            if m is not None:
+                v = m.variance
+                out[name] = np.zeros((self.grid['Nx'] + 2, self.grid['Ny'] + 2)) if v is None else self._gather_field(v)
+        return out
+
+    def _gather_field(self, dev_field):
+        """a device field over this rank's padded rows -> the global host array"""
+        return dev_field.cpu().numpy() if self._par.world == 1 else self._solver.gather_rows(dev_field)
 
     def write(self, scalars=True, fields=True, params=True):
+        """problem.py:616-637."""
         if self.step is None:
             self._pre_run()
         if scalars:
             sc = self._scalars()
-            print(f"{self.step:<6d} {sc.dt:.4e} {self.simtime:.4e} {sc.cfl:.4e} {self.residual:.4e}")
+            if self._root:
+                print(f"{self.step:<6d} {sc.dt:.4e} {self.simtime:.4e} {sc.cfl:.4e} {self.residual:.4e}")
             for k, v in zip(self.history, (self.step, self.simtime, sc.ekin, self.residual, sc.v_sound)):
                 self.history[k].append(v)
-        if fields and self._sol is not None:
-            p, wxz, wyz, _ = self._closures()
+        if fields and (self._sol is not None or (self._par.world > 1 and not self.options['silent'])):
+            p, wxz, wyz, _ = self._closures()             # slabs: gathers, every rank takes part
             if not self._q_synced:
                 self._solver.get_q(self._q_host)
                 self._q_synced = True
+            var = self._variance_fields()
+        if fields and self._sol is not None:
             f = self._frames
-            self._sol.variables['solution'][f] = self._q_host
+            self._sol.variables['solution'][f, :, 0] = self._q_host
             self._sol.variables['pressure'][f] = p
-            self._sol.variables['wall_stress_xz'][f] = wxz
-            self._sol.variables['wall_stress_yz'][f] = wyz
+            self._sol.variables['wall_stress_xz'][f, :, 0] = wxz
+            self._sol.variables['wall_stress_yz'][f, :, 0] = wyz
+            for name, v in var.items():
+                self._sol.variables[name][f] = v
             self._frames += 1
             self._sol.flush()
+        if params:
+            # Pressure.write / WallStress.write (gp.py:242-253): one row of hyper-parameter history per GP model
+            for key in ('zz', 'xz', 'yz'):
+                m = self.gp_models.get(key)
+                if m is not None:
+                    m.write()

@@ -208,6 +208,11 @@ int gpf_fv_update_host(gpf_fv* s, double* q_host, int n, gpf_fv_scalars* out, vo
  *   reduce_local(0); <all-gather of the 5-double records>; finish(GPF_FIN_STEP).
  * All calls enqueue on `stream` and never synchronise. */
 enum { GPF_FIN_STEP = 0, GPF_FIN_PRERUN = 1, GPF_FIN_PRERUN_KEEP_EKIN = 2, GPF_FIN_REFRESH = 3 };
+/* until_converged != 0: the steps driven through gpf_fv_pass / gpf_fv_finish / gpf_fv_finish_recv / gpf_fv_slab_step
+ * honour the loop condition of Problem.run (problem.py:401) on the device, like gpf_fv_step(until_converged = 1):
+ * once converged, at max_it or stopped they are no-ops (the exchanges still run, identically on every rank).
+ * Set it identically on every rank. */
+int gpf_fv_set_run_mode(gpf_fv* s, int until_converged);
 /* one MacCormack pass (predictor: corrector = 0), problem.py:524-560 */
 int gpf_fv_pass(gpf_fv* s, int corrector, void* stream);
 /* the same pass in two launches, so that the exchange of the edge rows runs under the interior:

@@ -140,9 +140,16 @@ def test_run_writes_the_reference_files(tmp_path, capsys):
     assert rows[0] == 'step,time,ekin,residual,vsound'
     assert [int(r.split(',')[0]) for r in rows[1:]] == [0, 100, 200, 250]
     with netcdf_file(str(out / 'sol.nc'), 'r', mmap=False) as f:
-        assert f.variables['solution'].shape == (4, 3, 102, 3)
-        assert f.variables['wall_stress_xz'].shape == (4, 12, 102, 3)
-        assert np.array_equal(f.variables['solution'][3], problem.q)
+        # muGrid's layout as the reference's readers index it (viz/plotting.py:331-349): (frame, comp, sub-point, x, y)
+        assert f.variables['solution'].shape == (4, 3, 1, 102, 3)
+        assert f.variables['wall_stress_xz'].shape == (4, 12, 1, 102, 3)
+        assert f.variables['pressure'].shape == (4, 102, 3)
+        q_nc = np.asarray(f.variables['solution'][:])[-1]
+        assert np.array_equal(q_nc[:, 0], problem.q)
+        assert 'pressure_var' not in f.variables
+    with netcdf_file(str(out / 'topo.nc'), 'r', mmap=False) as f:
+        topo = np.asarray(f.variables['topography'][:])
+        assert np.array_equal(topo[0, 0, 0, 1:-1, 1], problem.topo.h[1:-1, 1])      # plotting.py:235
     assert "steps/s" in capsys.readouterr().out
 
 
@@ -207,3 +214,71 @@ def test_sound_wave_decay(n):
             isT = np.sqrt((1 / tau / kn)**2 - cT**2)
             env = np.exp(-t / tau) * (np.cosh(isT * kn * t) - np.sinh(isT * kn * t) / (tau * isT * kn))
         np.testing.assert_almost_equal(problem.q[1, 1:-1, 1], np.sin(kn * x) * env, decimal=3)
+
+
+# ---------------------------------------------------------------------------------------------
+# Problem.run() on x-slabs (gapflow_b200.dist.Parallel): same files as the single-domain run
+# ---------------------------------------------------------------------------------------------
+def _run_problem_threads(make, world):
+    """one Problem per rank, ranks = threads of this process on one GPU (ThreadColl stands in for torch.distributed;
+    the launches of all ranks go down one stream in lock step, so no kernel ever waits for a peer)"""
+    import threading
+    from gapflow_b200.dist import Parallel
+    from gapflow_b200.surrogate import ThreadColl
+    tc = ThreadColl(world)
+    out, errs = [None] * world, []
+
+    def work(r):
+        try:
+            torch.cuda.set_device(0)
+            p = make(Parallel.threads(tc, r))
+            p.run()
+            out[r] = p
+        except BaseException as e:
+            import traceback
+            errs.append((r, traceback.format_exc()))
+            tc._barrier.abort()
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(600)
+    assert not errs, errs
+    return out
+
+
+def _read_nc(path):
+    from scipy.io import netcdf_file
+    with netcdf_file(path, 'r', mmap=False) as f:
+        return {k: np.array(v[:]) for k, v in f.variables.items()}
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_problem_run_on_slabs_writes_the_same_files(tmp_path, world, capsys):
+    from gapflow_b200.problem import Problem
+    text = SOMMERFELD.replace('C1: 3.5e12', 'C1: 3.5e10')
+
+    def make(par, tag):
+        d = config.read_yaml_string(text)
+        d['options'].update(output=str(tmp_path / tag), silent=False, use_tstamp=False, write_freq=50)
+        d['numerics']['max_it'] = 120
+        return Problem(d['options'], d['grid'], d['numerics'], d['properties'], d['geometry'], parallel=par)
+    one = make(None, 'one')
+    one.run()
+    ranks = _run_problem_threads(lambda par: make(par, f'slabs{world}'), world)
+    assert all(p.step == one.step == 120 for p in ranks)
+    assert all(p.dt == one.dt and np.array_equal(p.q, one.q) for p in ranks)        # q, dt: global and bit-identical
+    assert all(abs(p.mass - one.mass) <= 1e-12 * one.mass for p in ranks)
+    a, b = _read_nc(str(tmp_path / 'one' / 'sol.nc')), _read_nc(str(tmp_path / f'slabs{world}' / 'sol.nc'))
+    assert sorted(a) == sorted(b)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(_read_nc(str(tmp_path / 'one' / 'topo.nc'))['topography'],
+                          _read_nc(str(tmp_path / f'slabs{world}' / 'topo.nc'))['topography'])
+    ha = np.loadtxt(str(tmp_path / 'one' / 'history.csv'), delimiter=',', skiprows=1)
+    hb = np.loadtxt(str(tmp_path / f'slabs{world}' / 'history.csv'), delimiter=',', skiprows=1)
+    assert ha.shape == hb.shape and np.array_equal(ha[:, :2], hb[:, :2]) and np.array_equal(ha[:, 4], hb[:, 4])
+    assert np.allclose(ha[:, 2:4], hb[:, 2:4], rtol=1e-9, atol=0)      # the kinetic-energy sum is folded rank by rank
+    assert sorted(os.listdir(tmp_path / f'slabs{world}')) == ['config.yml', 'history.csv', 'sol.nc', 'topo.nc']
+    capsys.readouterr()

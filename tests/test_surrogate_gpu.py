@@ -365,3 +365,33 @@ def test_nccl_slab_coupled_steps_vs_oracle(tmp_path):
                         "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), root],
                        capture_output=True, text=True, timeout=600, cwd=root)
     assert r.returncode == 0 and "NCCL_SURROGATE_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world", [2])
+def test_problem_with_gp_on_slabs_writes_the_same_files(tmp_path, world):
+    """Problem.run() with GP closures on x-slabs (ranks = threads on one GPU): same sol.nc (variance fields
+    included), same training database and hyper-parameter history as the single-domain run."""
+    from gapflow_b200.problem import Problem
+    from gapflow_b200.surrogate import Database, Mock
+    from tests.test_problem_gpu import _read_nc, _run_problem_threads
+
+    def make(par, tag):
+        d, _ = SC.inputs('slip1d', nx=64, max_it=10, wf=5, out=str(tmp_path / tag), silent=False, atol=0.8, al_steps=2)
+        database = Database(Mock(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS), d['db'])
+        return Problem(d['options'], d['grid'], d['numerics'], d['properties'], d['geometry'], d['gp'], database,
+                       extra_field=SC.slip_length(64, 1), parallel=par)
+    one = make(None, 'one')
+    one.run()
+    ranks = _run_problem_threads(lambda par: make(par, 'slabs'), world)
+    a, b = _read_nc(os.path.join(one.outdir, 'sol.nc')), _read_nc(os.path.join(ranks[0].outdir, 'sol.nc'))
+    assert {'pressure_var', 'wall_stress_xz_var'} <= set(a) and sorted(a) == sorted(b)
+    assert a['pressure_var'].shape == a['pressure'].shape and np.isfinite(a['pressure_var']).all()
+    assert a['pressure_var'].max() > 0.0                       # a variance was computed before the first frame (gp.py:468)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
+    for p in ranks:
+        assert p.step == one.step and p.database.size == one.database.size
+        assert np.array_equal(p.database._Xtrain, one.database._Xtrain)
+        assert np.array_equal(p.q, one.q)
+    for name in ('gp_zz.csv', 'gp_xz.csv', 'Xtrain.npy'):
+        assert open(os.path.join(one.outdir, name), 'rb').read() == open(os.path.join(ranks[0].outdir, name), 'rb').read(), name
