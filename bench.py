@@ -743,7 +743,8 @@ def main():
     ap.add_argument("--no-gp", action="store_true", help="skip the GP block (N = 1)")
     ap.add_argument("--no-parity", action="store_true", help="skip slab_parity (N > 1)")
     ap.add_argument("--gp-M", type=int, default=10000)
-    ap.add_argument("--gp-var-sample", type=int, default=32768)
+    ap.add_argument("--gp-var-sample", type=int, default=75776,
+                    help="query cells of the timed variance call: 2 x 296 x 128 = two full waves of the variance kernel")
     ap.add_argument("--gp-coupled-steps", type=int, default=2)
     ap.add_argument("--arith", default="fast", choices=["fast", "exact"],
                     help="arithmetic contract of the pass kernels (include/gapflow_b200.h: gpf_fv_cfg.arith)")

@@ -52,7 +52,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--M", type=int, default=10000)
     ap.add_argument("--N", type=int, default=1026 * 1026)
-    ap.add_argument("--var-sample", type=int, default=32768)
+    ap.add_argument("--var-sample", type=int, default=75776)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--coupled-n", type=int, default=1024, help="cells per side of the GP-coupled FV step (0: skip)")
     ap.add_argument("--coupled-steps", type=int, default=3)

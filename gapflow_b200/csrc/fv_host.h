@@ -55,7 +55,6 @@ struct FvSolver {
     RefreshOut* refresh;
     int npartial;      // capacity of partial/pflags
     int* redo;         // [2] device flags, see fv_pass_kernel
-    unsigned* prog;    // [3 launch kinds][2 passes][2 GEN][2] wave-throttle counters of the pass kernels (self-clearing)
     int nrec_corr = 0; // record slots written by the last corrector pass (all its launches)
     cudaGraphExec_t step_graph[2] = {nullptr, nullptr};   // one captured step, [until_converged]
     void drop_graphs();
@@ -123,8 +122,6 @@ struct PassArgs {
     int ntiles;                // tiles of this launch (virtual index t -> tile row (t / nty) * bx_mul + bx_off)
     int bx_mul, bx_off;
     int rec0;                  // first record slot of this launch
-    unsigned* prog;            // wave-throttle counters of this launch kind: [CORR][GEN]{tiles completed, CTAs gone}
-    int wave_window;           // a CTA runs at most this many waves ahead of the grid's completed-tile count (0: off)
     // surrogate variant only (SG): GP means replacing the pressure / the own shear component of the wall stresses
     const double* sg_p;
     const double* sg_xz;

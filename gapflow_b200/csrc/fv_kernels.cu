@@ -866,7 +866,6 @@ int FvSolver::init(const gpf_fv_cfg& c, void* ws, size_t bytes) {
     pflags = reinterpret_cast<int*>(p); p += align_up((size_t)npartial * sizeof(int), 256);
     qtable = reinterpret_cast<double**>(p);
     redo = reinterpret_cast<int*>(p + 128);         // zeroed with the workspace
-    prog = reinterpret_cast<unsigned*>(p + 144);    // 24 counters (96 bytes), zeroed with the workspace
     p += 256;
     // planes are allocated with stride plane_b; the layout's plane stride must match
     P.L.plane = plane_b / 8;
@@ -1124,11 +1123,6 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     }
     A.P = S.P; A.st = S.st; A.partial = S.partial; A.pflags = S.pflags; A.redo = S.redo;
     A.until_converged = until_converged;
-    // wave throttle (fv_pass_kernel.cuh): launches that may run concurrently (EDGE on a side stream beside
-    // INTERIOR) count in separate slots
-    static const int window = [] { const char* e = getenv("GPF_WAVE_WINDOW"); return e ? atoi(e) : 3; }();
-    A.wave_window = window;
-    A.prog = S.prog + 8 * (part == GPF_PART_EDGE ? 1 : part == GPF_PART_INTERIOR ? 2 : 0);
     A.sg_p = S.sg_p; A.sg_xz = S.sg_xz; A.sg_yz = S.sg_yz;
     for (int k = 0; k < 3; ++k) A.sg_scale[k] = S.sg_scale[k];
     // INTERIOR leaves a few CTA slots empty so that the exchange kernels of the side stream (pack,

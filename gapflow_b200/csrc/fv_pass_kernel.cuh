@@ -25,7 +25,6 @@ constexpr size_t BOX3_BYTES = al128((size_t)3 * BOX * 8);
 constexpr size_t BOX2_BYTES = al128((size_t)2 * BOX * 8);
 constexpr size_t BOX1_BYTES = al128((size_t)BOX * 8);
 constexpr size_t OWN3_BYTES = (size_t)3 * TX * TY * 8;          // q0 of the tile's own cells (corrector)
-constexpr long long THROTTLE_CLOCKS = 200000;                   // ~0.1 ms: bound of one wave-throttle wait
 
 // NST: depth of the TMA ring (tiles in flight ahead of the one being computed: NST - 1)
 template <bool CORR, bool LS, bool XF, int NST, bool VF = false>
@@ -288,29 +287,6 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     // a launch covers all tile rows (mul 1, off 0), the interior ones (mul 1, off 1) or the first
     // and the last one (mul = rows - 1, off 0): see FvSolver::pass
     const int bx_mul = A.bx_mul, bx_off = A.bx_off;
-    // Wave throttle.  CTA b owns tiles b, b + G, b + 2G, ... (static: the per-CTA records stay deterministic), and
-    // the halo row / columns a tile stages were fetched a moment earlier by the CTAs of the neighbouring tiles --
-    // an L2 hit as long as the CTAs stay within a few tiles of each other.  Nothing keeps them there: over the
-    // ~300 tiles a CTA walks at 8192^2 the fast CTAs run tens of waves ahead, the reuse distance outgrows the
-    // L2 and the halo cells come from DRAM a second time (ncu r2a: 3.17 GB read per predictor launch where 2.68
-    // are needed, 4.78 / 4.30 for the corrector).  So a CTA does not issue the loads of its j-th tile before
-    // (j - W) G tiles of the grid are complete.  The count only ever delays work: a wait that outlasts
-    // THROTTLE_CLOCKS (CTAs not co-resident) switches the throttle off for that CTA.  prog[0]: tiles completed,
-    // prog[1]: CTAs that have left; the last one out clears both for the next launch.
-    unsigned* const prog = A.prog + (CORR ? 4 : 0) + (GEN ? 2 : 0);
-    int wave_window = A.wave_window;
-    auto throttle = [&](int j) {                            // thread 0 only
-        if (wave_window <= 0 || j <= wave_window) return;
-        // tile t = b + j G may start once t - W G tiles are complete: thresholds differ from CTA to CTA, so the
-        // waiting CTAs are released one by one, not all in the same instant (which phase-locked the grid: r2b)
-        const unsigned need = (unsigned)(j - wave_window) * gridDim.x + blockIdx.x;
-        if (*reinterpret_cast<volatile unsigned*>(prog) >= need) return;
-        const long long t0 = clock64();
-        while (*reinterpret_cast<volatile unsigned*>(prog) < need) {
-            if (clock64() - t0 > THROTTLE_CLOCKS) { wave_window = 0; return; }
-            __nanosleep(100);
-        }
-    };
     auto issue = [&](int vbx, int by, int stage) {         // thread 0 only
         const int i0 = 1 + (vbx * bx_mul + bx_off) * TX, j0 = 1 + by * TY;
         unsigned char* base = smem + (size_t)stage * S::STAGE;
@@ -390,10 +366,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         // the stage read by tile it-1 was released by that tile's closing CTA barrier: refill it
         {
             const int is = (stage == 0) ? NST - 1 : stage - 1;
-            if (tid == 0 && itile < A.ntiles) {
-                throttle(it + NST - 1);
-                issue(ibx, iby, is);
-            }
+            if (tid == 0 && itile < A.ntiles) issue(ibx, iby, is);
             advance(itile, ibx, iby);
         }
         const unsigned char* base = smem + (size_t)stage * S::STAGE;
@@ -602,16 +575,11 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             }
         }
         __syncthreads();          // closures and this stage's boxes are free again
-        if (tid == 0 && A.wave_window > 0) atomicAdd(prog, 1u);
         advance(tile, bx, by);
         if (++stage == NST) { stage = 0; phase ^= 1u; }
     }
 
     if (!GEN && bad) A.redo[CORR] = 1;
-    if (tid == 0 && A.wave_window > 0) {
-        __threadfence();                                           // this CTA's tile counts land before its exit count
-        if (atomicAdd(prog + 1, 1u) == gridDim.x - 1) { prog[0] = 0u; prog[1] = 0u; }
-    }
     if (CORR) {
         // warp shuffles, then one record per CTA (fixed order: deterministic)
         double e = warp_sum(red.ekin);

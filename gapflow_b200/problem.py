@@ -312,7 +312,10 @@ class Problem:
                 print(f"{'Step':6s} {'Timestep':10s} {'Time':10s} {'CFL':10s} {'Residual':10s}")
                 print(61 * '-')
             self.write(params=False)
-        old = {s: signal.signal(s, self._receive_signal) for s in (signal.SIGINT, signal.SIGTERM)}
+        import threading
+        old = {}
+        if threading.current_thread() is threading.main_thread():     # signal handlers belong to the main thread
+            old = {s: signal.signal(s, self._receive_signal) for s in (signal.SIGINT, signal.SIGTERM)}
         self._tic = datetime.now()
         wf = max(1, int(self.options['write_freq']))
         try:
