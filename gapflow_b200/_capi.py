@@ -30,6 +30,7 @@ BC_P, BC_D, BC_N, BC_HALO = 0, 1, 2, 3
 F_Q, F_TOPO, F_EXTRA = 0, 1, 2
 PART_ALL, PART_EDGE, PART_INTERIOR = 0, 1, 2
 IPC_HANDLE_BYTES = 64
+PEER_BLOB_BYTES = 96
 PIEZO_IDS = {'Barus': 2, 'Roelands': 3, 'Dukler': 4, 'McAdams': 5}       # GPF_PIEZO_*; any other name: 1 (identity)
 PIEZO_KEYS = {'Barus': ['aB'], 'Roelands': ['mu_inf', 'p_ref', 'z'], 'Dukler': ['eta_v', 'rho_l', 'rho_v'],
               'McAdams': ['eta_v', 'rho_l', 'rho_v']}
@@ -90,6 +91,11 @@ SIGNATURES = {
     "gpf_comm_destroy": (_i, [_vp]),
     "gpf_comm_error": (_i, [_vp, C.POINTER(C.c_int)]),
     "gpf_comm_set_timeout": (_i, [_vp, C.c_double]),
+    "gpf_fv_peer_export": (_i, [_vp, _vp]),
+    "gpf_comm_attach": (_i, [_vp, _vp, _vp, _i, _i]),
+    "gpf_comm_connect_local": (_i, [_vp, C.POINTER(C.c_void_p)]),
+    "gpf_comm_attach_local": (_i, [_vp, _vp, _vp, _i, _vp, _i]),
+    "gpf_fv_slab_pass": (_i, [_vp, _vp, _i, _vp]),
     "gpf_fv_halo_send": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "gpf_fv_halo_recv": (_i, [_vp, _vp, _i, _vp]),
     "gpf_fv_record_send": (_i, [_vp, _vp, _i, _vp]),

@@ -309,6 +309,25 @@ int gpf_comm_error(gpf_comm* c, int* err) {
     return GPF_OK;
     GPF_CATCH
 }
+int gpf_fv_peer_export(gpf_fv* s, unsigned char* blob) {
+    GPF_TRY NEED(s && blob) return s->S.peer_export(blob); GPF_CATCH
+}
+int gpf_comm_attach(gpf_comm* c, gpf_fv* s, const unsigned char* blobs, int lo, int hi) {
+    GPF_TRY NEED(c && s && blobs) return c->C.attach(s->S, blobs, lo, hi); GPF_CATCH
+}
+int gpf_comm_connect_local(gpf_comm* c, gpf_comm* const* all) {
+    GPF_TRY NEED(c && all)
+    std::vector<SlabComm*> v(c->C.lay.world);
+    for (int r = 0; r < c->C.lay.world; ++r) { NEED(all[r]) v[r] = &all[r]->C; }
+    return c->C.connect_local(v.data());
+    GPF_CATCH
+}
+int gpf_comm_attach_local(gpf_comm* c, gpf_fv* s, gpf_fv* lo_solver, int lo, gpf_fv* hi_solver, int hi) {
+    GPF_TRY NEED(c && s) return c->C.attach_local(s->S, lo_solver ? &lo_solver->S : nullptr, lo, hi_solver ? &hi_solver->S : nullptr, hi); GPF_CATCH
+}
+int gpf_fv_slab_pass(gpf_fv* s, gpf_comm* c, int corrector, void* stream) {
+    GPF_TRY NEED(s && c) return s->S.slab_pass(c->C, corrector, (cudaStream_t)stream); GPF_CATCH
+}
 int gpf_comm_set_timeout(gpf_comm* c, double seconds) {
     GPF_TRY NEED(c) return c->C.set_timeout(seconds); GPF_CATCH
 }

@@ -90,6 +90,8 @@ struct FvSolver {
     int record_send(struct SlabComm& c, int kind, cudaStream_t s);
     int finish_recv(struct SlabComm& c, int mode, double* recs_out, cudaStream_t s, int until_converged = 0);
     int slab_step_once(struct SlabComm& c, int lo, int hi, double* recs_out, cudaStream_t s);
+    int slab_pass(struct SlabComm& c, int corrector, cudaStream_t s);      // one pass with the exchange fused in
+    int peer_export(unsigned char* blob);                                  // GPF_PEER_BLOB_BYTES describing the q buffers
     int slab_step(struct SlabComm& c, int lo, int hi, int n, double* recs_out, cudaStream_t s);
     bool graph_stale = false;
     int run_mode_uc = 0;     // gpf_fv_set_run_mode: pass / finish / slab-step launches honour the run-loop condition on the device
@@ -122,6 +124,7 @@ struct PassArgs {
     int ntiles;                // tiles of this launch (virtual index t -> tile row (t / nty) * bx_mul + bx_off)
     int bx_mul, bx_off;
     int rec0;                  // first record slot of this launch
+    SlabX X;                   // fused slab exchange (X.on = 0: plain pass)
     // surrogate variant only (SG): GP means replacing the pressure / the own shear component of the wall stresses
     const double* sg_p;
     const double* sg_xz;

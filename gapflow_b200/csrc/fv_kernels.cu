@@ -23,38 +23,6 @@ enum { FIN_STEP = 0, FIN_PRERUN = 1, FIN_PRERUN_KEEP_EKIN = 2, FIN_REFRESH = 3 }
 // records, so every rank folds the same numbers in the same order and advances identically.
 // `rec_out` != nullptr: only fold this rank's per-block records into one Rec5 and return.
 // ---- system-scope flag protocol of the peer-memory exchange (slab_comm.cuh) ----------------
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-// Waits until *flag >= seq.  `err` is the communicator's error block: err[0] the error flag, the 64-bit word at
-// err + 2 the wait bound in ns (gpf_comm_set_timeout).  A wait that exceeds the bound (a peer died) raises the
-// flag instead of hanging the GPU; once it is up every later wait falls through at once, the records carry
-// FLAG_COMM to every rank and fv_finish_kernel stops the run (DevState::comm_err).
-__device__ __forceinline__ void spin_until(const unsigned long long* flag, unsigned long long seq, int* err) {
-    if (ld_acquire_sys(flag) >= seq) return;
-    if (*reinterpret_cast<volatile int*>(err)) return;
-    const unsigned long long limit = *reinterpret_cast<const volatile unsigned long long*>(err + 2);
-    const unsigned long long t0 = global_ns();
-    while (ld_acquire_sys(flag) < seq) {
-        if (global_ns() - t0 > limit) {
-            *reinterpret_cast<volatile int*>(err) = 1;
-            __threadfence();
-            return;
-        }
-        __nanosleep(64);
-    }
-}
-
 __global__ void __launch_bounds__(256) fv_finish_kernel(const __grid_constant__ FvParams P, DevState* st,
                                                         const Partial* part, const int* pflags, int nblk,
                                                         int mode, int until_converged, RefreshOut* ro,
@@ -1099,7 +1067,7 @@ int FvSolver::viscosity(int which, double* out, int on_device, cudaStream_t s) {
 constexpr int PART_ROWS = 100;
 template <bool CORR>
 static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int part = GPF_PART_ALL, int row0 = 0,
-                       int nrows = 0, int rec0 = 0, int max_cta = 0, int* used_cta = nullptr) {
+                       int nrows = 0, int rec0 = 0, int max_cta = 0, int* used_cta = nullptr, SlabComm* xc = nullptr) {
     const int nty = S.P.nblk_x, nbx = S.P.nblk_y;          // tiles along y, tile rows along x
     if (part != PART_ROWS && (part < GPF_PART_ALL || part > GPF_PART_INTERIOR)) { set_error("bad pass part"); return GPF_E_INVALID; }
     if (part != PART_ROWS && nbx < 3) {
@@ -1125,6 +1093,25 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     A.until_converged = until_converged;
     A.sg_p = S.sg_p; A.sg_xz = S.sg_xz; A.sg_yz = S.sg_yz;
     for (int k = 0; k < 3; ++k) A.sg_scale[k] = S.sg_scale[k];
+    memset(&A.X, 0, sizeof(A.X));
+    if (xc) {
+        // fused exchange (slab_comm.cuh): whole-pass launches only
+        if (!xc->attached || part != GPF_PART_ALL) { set_error("fused slab pass needs an attached communicator and a whole-pass launch"); return GPF_E_STATE; }
+        SlabX& X = A.X;
+        X.on = 1;
+        for (int sd = 0; sd < 2; ++sd) {
+            for (int k = 0; k < 3; ++k) X.peer_q[sd][k] = xc->peer_q[sd][k];
+            X.peer_plane[sd] = xc->peer_plane[sd];
+            X.peer_row[sd] = xc->peer_row[sd];
+            // my row 1 completes the lower neighbour's upper ghost row (its side 1), my row Nx the upper neighbour's side 0
+            X.peer_flag[sd] = xc->nbr[sd] >= 0 ? xc->hflag2(xc->nbr[sd], sd == 0 ? 1 : 0) : nullptr;
+            X.edge_dup[sd] = S.P.bc.edge[sd];
+        }
+        X.my_flag = xc->hflag2(xc->lay.rank, 0);
+        X.xseq = xc->xseq(); X.xdone = xc->xdone(); X.err = xc->err();
+        X.peers = xc->d_peer; X.off_recs = xc->lay.off_recs; X.off_rflag = xc->lay.off_rflag;
+        X.world = xc->lay.world; X.rank = xc->lay.rank; X.rseq = xc->seq(1);
+    }
     // INTERIOR leaves a few CTA slots empty so that the exchange kernels of the side stream (pack,
     // send, receive) find room beside the persistent CTAs (GPF_INTERIOR_SLACK, default 2)
     static const int slack = [] { const char* e = getenv("GPF_INTERIOR_SLACK"); return e ? atoi(e) : 2; }();
@@ -1139,6 +1126,7 @@ static int launch_pass(FvSolver& S, int until_converged, cudaStream_t s, int par
     } else if (part == GPF_PART_ALL) {
         A.ntiles = nbx * nty; A.bx_mul = 1; A.bx_off = 0; A.rec0 = 0;
         if (CORR) S.nrec_corr = pass_ctas(A.ntiles, true, nty);
+        if (CORR) A.X.nrec = S.nrec_corr;
     } else if (part == GPF_PART_EDGE) {
         A.ntiles = 2 * nty; A.bx_mul = nbx - 1; A.bx_off = 0; A.rec0 = 0;
         if (CORR) S.nrec_corr = n_edge + n_int;
@@ -1429,6 +1417,7 @@ SlabCommLayout SlabComm::layout(int world, int rank, int Ny2) {
     l.off_err = o; o += 256;
     l.off_seq = o; o += 256;
     l.off_ptrs = o; o += align_up((size_t)world * sizeof(void*), 256);
+    l.off_x = o; o += 256;
     l.bytes = o;
     return l;
 }
@@ -1473,8 +1462,110 @@ int SlabComm::connect(const unsigned char* handles) {
     return GPF_OK;
 }
 
+// ---- fused exchange: the neighbours' q buffers ---------------------------------------------------------
+struct PeerBlob {                      // what a rank tells the others about its rotating q buffers
+    cudaIpcMemHandle_t handle;         // of the allocation that holds the solver's workspace
+    unsigned long long offset;         // of qbuf[0] inside it (bytes)
+    unsigned long long plane;          // plane stride (doubles); buffer k starts 3 k planes on
+    int pitch, Nx, Ny, pad;
+};
+static_assert(sizeof(PeerBlob) == GPF_PEER_BLOB_BYTES, "peer blob size");
+
+typedef CUresult (*AddrRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+
+int FvSolver::peer_export(unsigned char* blob) {
+    static AddrRangeFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            set_error("cuMemGetAddressRange not available from the driver"); return GPF_E_CUDA;
+        }
+        fn = reinterpret_cast<AddrRangeFn>(p);
+    }
+    CUdeviceptr base = 0; size_t size = 0;
+    if (fn(&base, &size, reinterpret_cast<CUdeviceptr>(qbuf[0])) != CUDA_SUCCESS) { set_error("cuMemGetAddressRange failed on the workspace"); return GPF_E_CUDA; }
+    PeerBlob b;
+    memset(&b, 0, sizeof(b));
+    // a workspace from a stream-ordered or virtual-memory allocator has no legacy IPC handle: the caller then keeps
+    // the exchange kernels (gpf_comm_attach reports it)
+    cudaError_t e = cudaIpcGetMemHandle(&b.handle, reinterpret_cast<void*>(base));
+    if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "cudaIpcGetMemHandle(workspace)"); }
+    b.offset = reinterpret_cast<unsigned long long>(qbuf[0]) - (unsigned long long)base;
+    b.plane = P.L.plane; b.pitch = P.L.pitch; b.Nx = cfg.Nx; b.Ny = cfg.Ny;
+    memcpy(blob, &b, sizeof(b));
+    return GPF_OK;
+}
+
+static int attach_checks(const FvSolver& S, const SlabComm& c, int lo, int hi) {
+    if (!c.connected) { set_error("communicator not connected"); return GPF_E_STATE; }
+    if (lo >= c.lay.world || hi >= c.lay.world) { set_error("bad neighbour rank"); return GPF_E_INVALID; }
+    if ((lo >= 0) != (S.P.bc.type[0][0] == GPF_BC_HALO) || (hi >= 0) != (S.P.bc.type[1][0] == GPF_BC_HALO)) {
+        set_error("gpf_comm_attach: neighbours do not match the solver's HALO sides"); return GPF_E_INVALID;
+    }
+    return GPF_OK;
+}
+
+int SlabComm::attach(const FvSolver& S, const unsigned char* blobs, int lo, int hi) {
+    int rc = attach_checks(S, *this, lo, hi);
+    if (rc) return rc;
+    const int nb[2] = {lo, hi};
+    for (int sd = 0; sd < 2; ++sd) {
+        nbr[sd] = nb[sd];
+        if (nb[sd] < 0) continue;
+        PeerBlob b;
+        memcpy(&b, blobs + (size_t)nb[sd] * sizeof(b), sizeof(b));
+        if (b.pitch != S.P.L.pitch || b.Ny != S.cfg.Ny) { set_error("gpf_comm_attach: the neighbour's rows have another length"); return GPF_E_INVALID; }
+        void* p = nullptr;
+        if (sd == 1 && nb[1] == nb[0]) p = peer_map[0];           // two ranks on a ring: one peer on both sides
+        else GPF_CUDA(cudaIpcOpenMemHandle(&p, b.handle, cudaIpcMemLazyEnablePeerAccess));
+        peer_map[sd] = p;
+        double* q0 = reinterpret_cast<double*>(static_cast<unsigned char*>(p) + b.offset);
+        for (int k = 0; k < 3; ++k) peer_q[sd][k] = q0 + (size_t)k * 3 * b.plane;
+        peer_plane[sd] = b.plane;
+        peer_row[sd] = (sd == 0) ? b.Nx + 1 : 0;
+    }
+    attached = true;
+    return GPF_OK;
+}
+
+int SlabComm::attach_local(const FvSolver& S, const FvSolver* lo_s, int lo, const FvSolver* hi_s, int hi) {
+    int rc = attach_checks(S, *this, lo, hi);
+    if (rc) return rc;
+    const FvSolver* ns[2] = {lo_s, hi_s};
+    const int nb[2] = {lo, hi};
+    for (int sd = 0; sd < 2; ++sd) {
+        nbr[sd] = nb[sd];
+        if (nb[sd] < 0) continue;
+        if (!ns[sd] || ns[sd]->P.L.pitch != S.P.L.pitch) { set_error("gpf_comm_attach_local: bad neighbour solver"); return GPF_E_INVALID; }
+        for (int k = 0; k < 3; ++k) peer_q[sd][k] = ns[sd]->qbuf[k];
+        peer_plane[sd] = ns[sd]->P.L.plane;
+        peer_row[sd] = (sd == 0) ? ns[sd]->cfg.Nx + 1 : 0;
+    }
+    attached = true;
+    return GPF_OK;
+}
+
+int SlabComm::connect_local(SlabComm* const* all) {
+    for (int r = 0; r < lay.world; ++r) {
+        if (!all[r] || !all[r]->local || all[r]->lay.world != lay.world || all[r]->lay.Ny2 != lay.Ny2) { set_error("gpf_comm_connect_local: bad communicator table"); return GPF_E_INVALID; }
+        peer[r] = all[r]->local;
+    }
+    GPF_CUDA(cudaMemcpy(d_peer, peer.data(), (size_t)lay.world * sizeof(void*), cudaMemcpyHostToDevice));
+    connected = true;
+    local_only = true;
+    return GPF_OK;
+}
+
 int SlabComm::destroy() {
     if (step_graph) { cudaGraphExecDestroy(step_graph); step_graph = nullptr; }
+    if (!local_only) {
+        if (peer_map[0]) cudaIpcCloseMemHandle(peer_map[0]);
+        if (peer_map[1] && peer_map[1] != peer_map[0]) cudaIpcCloseMemHandle(peer_map[1]);
+    }
+    peer_map[0] = peer_map[1] = nullptr;
+    if (local_only) peer.clear();
     for (int r = 0; r < (int)peer.size(); ++r)
         if (r != lay.rank && peer[r]) cudaIpcCloseMemHandle(peer[r]);
     peer.clear();
@@ -1557,8 +1648,24 @@ int FvSolver::finish_recv(SlabComm& c, int mode, double* recs_out, cudaStream_t 
 // n x Problem.update() of this rank's slab: pass, edge rows to the neighbours, ghost rows from them
 // (twice), records to every rank, fold.  All sequence numbers live on the device, so one step is
 // captured once as a CUDA graph (10 kernels) and replayed.
+int FvSolver::slab_pass(SlabComm& c, int corrector, cudaStream_t s) {
+    int rc = comm_ok(*this, c);
+    if (rc) return rc;
+    return corrector ? launch_pass<true>(*this, run_mode_uc, s, GPF_PART_ALL, 0, 0, 0, 0, nullptr, &c)
+                     : launch_pass<false>(*this, run_mode_uc, s, GPF_PART_ALL, 0, 0, 0, 0, nullptr, &c);
+}
+
 int FvSolver::slab_step_once(SlabComm& c, int lo, int hi, double* recs_out, cudaStream_t s) {
     int rc;
+    // fused: the boundary tiles of the pass kernels store the edge rows into the neighbours' ghost rows, the general
+    // launch of each pass raises the flags and (corrector) publishes the folded record: 5 kernels per step like a
+    // single domain, none of them an exchange kernel (GPF_SLAB_FUSED=0: the send / receive / record kernels below)
+    static const bool fused = [] { const char* e = getenv("GPF_SLAB_FUSED"); return !e || atoi(e) != 0; }();
+    if (fused && c.attached && c.nbr[0] == lo && c.nbr[1] == hi && !P.visc_field && !(sg_p || sg_xz || sg_yz)) {
+        if ((rc = slab_pass(c, 0, s))) return rc;
+        if ((rc = slab_pass(c, 1, s))) return rc;
+        return finish_recv(c, FIN_STEP, recs_out, s, run_mode_uc);
+    }
     if ((rc = launch_pass<false>(*this, run_mode_uc, s))) return rc;
     if ((rc = halo_send(c, 1, lo, hi, s))) return rc;
     if ((rc = halo_recv(c, 1, s))) return rc;

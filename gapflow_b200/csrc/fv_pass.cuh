@@ -66,6 +66,39 @@ __device__ __forceinline__ double flip(double x, unsigned sbit) {
     return __hiloint2double(__double2hiint(x) ^ (int)sbit, __double2loint(x));
 }
 
+// ------------------------------ system-scope flags (slab exchange over peer memory) --------
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Waits until *flag >= seq.  `err` is the communicator's error block: err[0] the error flag, the 64-bit word at
+// err + 2 the wait bound in ns (gpf_comm_set_timeout).  A wait that exceeds the bound (a peer died) raises the
+// flag instead of hanging the GPU; once it is up every later wait falls through at once, the records carry
+// FLAG_COMM to every rank and fv_finish_kernel stops the run (DevState::comm_err).
+__device__ __forceinline__ void spin_until(const unsigned long long* flag, unsigned long long seq, int* err) {
+    if (ld_acquire_sys(flag) >= seq) return;
+    if (*reinterpret_cast<volatile int*>(err)) return;
+    const unsigned long long limit = *reinterpret_cast<const volatile unsigned long long*>(err + 2);
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys(flag) < seq) {
+        if (global_ns() - t0 > limit) {
+            *reinterpret_cast<volatile int*>(err) = 1;
+            __threadfence();
+            return;
+        }
+        __nanosleep(64);
+    }
+}
+
 // ------------------------------ ghost cells ---------------------------------------
 // Ghost value of one side from the adjacent (or periodic image) cell's 3 components.
 // problem.py:761-768:  D: (target - 0.5*q + 0.0*0.0)/(0.5 - 0.0);  N: ((1-0.5)*q + 0.0*0.0)/(0.5-0.0)
@@ -154,9 +187,13 @@ __device__ __forceinline__ void red_accum(Red& r, const double v[3], const EosPa
 //   qs[3]: value after this pass (before averaging), qn[3]: value stored for the cell.
 // Corrector: validity is tested on the averaged array INCLUDING its averaged ghost cells
 // (problem.py:563-565): ghost = (fill(q**) + ghost(q0)) / 2.
+// X != nullptr (fused slab exchange, SlabX in fv_host.h): a cell of row 1 (row Nx) and its y-ghost images are also
+// stored into the lower (upper) neighbour's ghost row of the same rotating buffer, over NVLink -- a neighbour's
+// interior row with its y ghosts filled is exactly what the reference's x-then-y fill order leaves in an x-ghost row.
 template <bool CORR, int EOS>
 __device__ __noinline__ Red boundary_cell(const FvParams& P, int i, int j, double s0, double s1, double s2,
-                                          double n0, double n1, double n2, double* qout, const double* q0b) {
+                                          double n0, double n1, double n2, double* qout, const double* q0b,
+                                          const SlabX* X = nullptr, int out_idx = 0) {
     Red r;
     r.ekin = 0.0; r.vmax2 = -INFINITY; r.cs2 = -INFINITY; r.flags = 0;
     const size_t plane = P.L.plane;
@@ -174,12 +211,26 @@ __device__ __noinline__ Red boundary_cell(const FvParams& P, int i, int j, doubl
         });
     }
     const double qn[3] = {n0, n1, n2};
+    auto remote = [&](int gj, const double* v) {          // (i, gj) of this slab -> the neighbours' ghost rows
+#pragma unroll
+        for (int sd = 0; sd < 2; ++sd) {
+            double* pq = X->peer_q[sd][out_idx];
+            if (pq && i == (sd == 0 ? 1 : P.L.Nx)) {
+                const size_t a = (size_t)X->peer_row[sd] * pitch + (gj + 1);
+                pq[a] = v[0];
+                pq[X->peer_plane[sd] + a] = v[1];
+                pq[2 * X->peer_plane[sd] + a] = v[2];
+            }
+        }
+    };
+    if (X) remote(j, qn);
     for_each_ghost(P, i, j, qn, [&](int gi, int gj, const double* gv) {
         const size_t ga = (size_t)gi * pitch + (gj + 1);
         qout[ga] = gv[0];
         qout[plane + ga] = gv[1];
         qout[2 * plane + ga] = gv[2];
         if (CORR) red_accum<EOS>(r, gv, P.eos);
+        if (X && gi == i) remote(gj, gv);                 // y-ghost image of an edge-row cell
     });
     return r;
 }

@@ -227,6 +227,56 @@ __device__ __noinline__ int cell_flags_slow(double a, double b, double c, double
     return f;
 }
 
+// ---- fused slab exchange: what the general launch of a pass does for its rank (one CTA, all threads) -------------
+// Raises the neighbours' flags for this pass's edge rows (stored remotely by the boundary tiles, see
+// boundary_cell) and -- corrector -- folds this rank's per-CTA records in a fixed order and stores the result, with
+// its sequence number, into every rank's record table: the jobs of fv_halo_send_kernel and fv_record_send_kernel
+// without their launches.  `scratch`: >= 5 * FV_THREADS doubles of shared memory.
+__device__ __forceinline__ void slab_publish(const PassArgs& A, bool corr, double* scratch) {
+    const SlabX& X = A.X;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        __threadfence_system();                      // the edge rows (this kernel's or the straight-line launch's) first
+        const unsigned long long seq = *X.xseq + 1;
+        if (X.peer_flag[0]) st_release_sys(X.peer_flag[0], seq);
+        if (X.peer_flag[1]) st_release_sys(X.peer_flag[1], seq);
+        *X.xseq = seq;
+    }
+    if (!corr) return;
+    double* sE = scratch; double* sV = sE + FV_THREADS; double* sC = sV + FV_THREADS; double* sM = sC + FV_THREADS;
+    int* sF = reinterpret_cast<int*>(sM + FV_THREADS);
+    double E = 0.0, VM = -INFINITY, CM = -INFINITY, M = 0.0;
+    int F = 0;
+    for (int b = tid; b < X.nrec; b += FV_THREADS) {
+        E += __ldcg(&A.partial[b].ekin);
+        M += __ldcg(&A.partial[b].mass);
+        VM = fmax(VM, __ldcg(&A.partial[b].vmax2));
+        CM = fmax(CM, __ldcg(&A.partial[b].cs2));
+        F |= __ldcg(&A.pflags[b]);
+    }
+    sE[tid] = E; sV[tid] = VM; sC[tid] = CM; sM[tid] = M; sF[tid] = F;
+    __syncthreads();
+    for (int st = FV_THREADS / 2; st > 0; st >>= 1) {
+        if (tid < st) {
+            sE[tid] += sE[tid + st];
+            sM[tid] += sM[tid + st];
+            sV[tid] = fmax(sV[tid], sV[tid + st]);
+            sC[tid] = fmax(sC[tid], sC[tid + st]);
+            sF[tid] |= sF[tid + st];
+        }
+        __syncthreads();
+    }
+    if (tid < X.world) {
+        const unsigned long long seq = *X.rseq + 1;            // this fold; fv_finish_kernel advances *rseq
+        const int parity = (int)(seq & 1ull);
+        double* dst = reinterpret_cast<double*>(X.peers[tid] + X.off_recs) + ((size_t)parity * X.world + X.rank) * 8;
+        const int cf = *reinterpret_cast<const volatile int*>(X.err) ? FLAG_COMM : 0;
+        dst[0] = sE[0]; dst[1] = sV[0]; dst[2] = sC[0]; dst[3] = sM[0]; dst[4] = (double)(sF[0] | cf);
+        __threadfence_system();
+        st_release_sys(reinterpret_cast<unsigned long long*>(X.peers[tid] + X.off_rflag) + X.rank, seq);
+    }
+}
+
 // Persistent kernel: fv_ctas_per_sm(CORR) CTAs per SM walk the tiles round-robin.  A 2-deep ring of
 // TMA-staged boxes keeps the loads of tile n+1 in flight under the arithmetic of tile n.
 //
@@ -262,8 +312,16 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     const FvParams& P = A.P;
     const DevState* st = A.st;
     // run-loop condition (problem.py:401) evaluated on the device; uniform per grid
-    if (st->stop || (A.until_converged && st->halt)) return;
-    if (GEN && !SG && A.redo[CORR] == 0) return;
+    // fused slab exchange: the general launch closes the pass for its rank (flags, record) also when it has nothing
+    // to recompute, and when the run has halted (every rank halts in the same step; the fold still runs)
+    if (st->stop || (A.until_converged && st->halt)) {
+        if (GEN && A.X.on && blockIdx.x == 0) slab_publish(A, CORR, reinterpret_cast<double*>(smem));
+        return;
+    }
+    if (GEN && !SG && A.redo[CORR] == 0) {
+        if (A.X.on && blockIdx.x == 0) slab_publish(A, CORR, reinterpret_cast<double*>(smem));
+        return;
+    }
 
     const int tid = threadIdx.x;
     const int cur = st->cur;
@@ -287,7 +345,17 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     // a launch covers all tile rows (mul 1, off 0), the interior ones (mul 1, off 1) or the first
     // and the last one (mul = rows - 1, off 0): see FvSolver::pass
     const int bx_mul = A.bx_mul, bx_off = A.bx_off;
+    // fused slab exchange: the ghost row a first / last tile row stages was stored by the neighbour's previous pass;
+    // its flag carries the number of that exchange = the exchanges this rank has published so far
+    const unsigned long long xneed = (A.X.on && tid == 0) ? *A.X.xseq : 0ull;
     auto issue = [&](int vbx, int by, int stage) {         // thread 0 only
+        if (A.X.on) {
+            const int trow = vbx * bx_mul + bx_off;
+            bool waited = false;
+            if (ox == 1 && trow == 0 && P.bc.type[0][0] == GPF_BC_HALO) { spin_until(A.X.my_flag + 0, xneed, A.X.err); waited = true; }
+            if (ox == 0 && trow == P.nblk_y - 1 && P.bc.type[1][0] == GPF_BC_HALO) { spin_until(A.X.my_flag + 1, xneed, A.X.err); waited = true; }
+            if (waited) asm volatile("fence.proxy.async;" ::: "memory");     // peer-written rows, read next by the TMA unit
+        }
         const int i0 = 1 + (vbx * bx_mul + bx_off) * TX, j0 = 1 + by * TY;
         unsigned char* base = smem + (size_t)stage * S::STAGE;
         uint64_t* b = bar + stage;
@@ -497,6 +565,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             const bool act = full || ((i0 + 2 * g + k <= Nx) && (j0 + ty <= Ny));
             const Q3 qq = ILP2 ? q2c[k] : update_cell(k);
             double qn0 = qq.v0, qn1 = qq.v1, qn2 = qq.v2;
+            double w = 0.0;                                        // (jx^2 + jy^2) / rho of the stored cell (corrector)
             if (CORR) {
                 const int oo = (2 * g + k) * TY + ty;
                 qn0 = (qn0 + sq0[oo]) * 0.5;                       // problem.py:563 ((q + q0)/2.0, exact)
@@ -504,7 +573,6 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
                 qn2 = (qn2 + sq0[2 * TX * TY + oo]) * 0.5;
                 // kinetic energy and speed (problem.py:342, 347): w = (jx^2 + jy^2)/rho
                 const double num = qn1 * qn1 + qn2 * qn2;
-                double w;
                 if constexpr (GEN) {
                     const bool wok = fast & in_fast_range_nz(qn0) & in_fast_range(num);
                     if (__all_sync(0xffffffffu, wok)) w = div_sel<true>(num, qn0, rcp_exact(qn0));
@@ -538,8 +606,12 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             if (btile) {
                 const int i = i0 + 2 * g + k, j = j0 + ty;
                 if (act && ((i == 1) | (i == Nx) | (j == 1) | (j == Ny))) {
-                    const Red br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b);
+                    const Red br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b,
+                                                            A.X.on ? &A.X : nullptr, out_idx);
                     if (CORR) {
+                        // periodic ring, fused exchange: this row is also the global ghost row of the reference's padded
+                        // array (it lives in the neighbour's memory): the cell and its y-ghost images count once more
+                        if (A.X.on && ((A.X.edge_dup[0] && i == 1) || (A.X.edge_dup[1] && i == Nx))) red.ekin += w * 0.5 + br.ekin;
                         red.ekin += br.ekin;
                         red.vmax2 = fmax(red.vmax2, br.vmax2);
                         red.cs2 = fmax(red.cs2, br.cs2);
@@ -612,6 +684,17 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             A.partial[slot].mass = 0.0;
             A.pflags[slot] = F;
         }
+    }
+    if (GEN && A.X.on) {
+        // the general kernel ran the pass in full (redo, or the surrogate variant): the last CTA out closes it
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence_system();                                // this CTA's record and (remote) edge rows before its exit count
+            sbad[0] = (atomicAdd(A.X.xdone, 1u) == gridDim.x - 1) ? 1 : 0;
+            if (sbad[0]) { *A.X.xdone = 0u; __threadfence(); }
+        }
+        __syncthreads();
+        if (sbad[0]) slab_publish(A, CORR, reinterpret_cast<double*>(smem));
     }
 }
 

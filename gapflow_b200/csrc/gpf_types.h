@@ -102,6 +102,30 @@ struct Rec5 {
     double ekin, vmax2, cs2, mass, flags;
 };
 
+// Fused slab exchange (slab_comm.cuh): what a pass kernel needs to store its edge rows straight into the
+// neighbours' ghost rows, to wait for theirs, and -- corrector -- to fold and publish this rank's record.
+// Side 0 = the lower neighbour (it receives my row 1 into its row Nx_peer + 1), side 1 = the upper one (my row Nx
+// into its row 0).
+struct SlabX {
+    int on;                               // 0: plain pass
+    double* peer_q[2][3];                 // [side][rotating buffer]: the neighbour's q buffers (peer-mapped); null = no neighbour
+    unsigned long long peer_plane[2];     // the neighbour's plane stride (doubles)
+    int peer_row[2];                      // the ghost row of the neighbour that my edge row fills
+    unsigned long long* peer_flag[2];     // the neighbour's flag that I raise when my edge row is complete
+    const unsigned long long* my_flag;    // [2]: raised by my lower / upper neighbour
+    unsigned long long* xseq;             // exchanges this rank has published (device-resident: graph replay)
+    unsigned int* xdone;                  // CTA exit counter of a pass that the general kernel runs in full
+    int* err;                             // communicator error block (spin_until)
+    int edge_dup[2];                      // periodic ring: my row 1 (Nx) is also the global ghost row Nx_g + 1 (0) of the
+                                          // reference's padded array; its cells count twice in the kinetic-energy sum
+    // record fold (corrector): fv_record_send_kernel's job, done by the general launch
+    unsigned char* const* peers;          // device table of every rank's communicator buffer
+    unsigned long long off_recs, off_rflag;
+    int world, rank;
+    const unsigned long long* rseq;       // folds completed (advanced by fv_finish_kernel)
+    int nrec;                             // per-CTA records of this rank's corrector
+};
+
 struct FvParams {
     Layout L;
     double dx, dy, rdx, rdy;

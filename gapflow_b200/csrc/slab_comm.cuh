@@ -8,6 +8,7 @@
 //   rflag[world]                           sequence number of the last record written by rank w
 //   err                                    [0] set when a wait timed out (a peer died or lagged): carried to every rank with the
 //                                          records, the run stops (DevState::comm_err);  +8 bytes: the wait bound in ns
+//   x                                      fused exchange: hflag2[2], xseq, xdone (see below)
 //   seq  [2]                               exchanges / folds this rank has completed (device-resident, so that
 //                                          a captured step can be replayed: no sequence number is a kernel argument)
 // A sender stores the data into the receiver's buffer, fences at system scope and then publishes the
@@ -23,7 +24,7 @@ namespace gpf {
 
 struct SlabCommLayout {
     int world, rank, Ny2;
-    size_t off_halo, off_hflag, off_recs, off_rflag, off_err, off_seq, off_ptrs, bytes;
+    size_t off_halo, off_hflag, off_recs, off_rflag, off_err, off_seq, off_ptrs, off_x, bytes;
 };
 
 struct SlabComm {
@@ -52,6 +53,21 @@ struct SlabComm {
     unsigned long long* seq(int which) const { return reinterpret_cast<unsigned long long*>(local + lay.off_seq) + which; }
     unsigned int* done(int which) const { return reinterpret_cast<unsigned int*>(local + lay.off_seq + 64) + which; }   // block counters
     size_t halo_par_stride() const { return (size_t)2 * 3 * lay.Ny2; }       // doubles between the two parities
+    // ---- fused exchange: the pass kernels store edge rows straight into the neighbours' q buffers ----------------
+    //   x block of the buffer: hflag2[2] (raised by the lower / upper neighbour), xseq (exchanges published), xdone
+    unsigned long long* hflag2(int r, int side) const { return reinterpret_cast<unsigned long long*>(peer[r] + lay.off_x) + side; }
+    unsigned long long* xseq() const { return reinterpret_cast<unsigned long long*>(local + lay.off_x) + 2; }
+    unsigned int* xdone() const { return reinterpret_cast<unsigned int*>(local + lay.off_x + 24); }
+    bool attached = false;
+    bool local_only = false;               // peers are communicators of this process (connect_local): nothing to unmap
+    double* peer_q[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+    unsigned long long peer_plane[2] = {0, 0};
+    int peer_row[2] = {0, 0};
+    int nbr[2] = {-1, -1};                 // neighbour ranks (lo, hi)
+    void* peer_map[2] = {nullptr, nullptr};   // IPC mappings of the neighbours' workspaces (closed in destroy)
+    int attach(const struct FvSolver& S, const unsigned char* blobs, int lo, int hi);   // [world][GPF_PEER_BLOB_BYTES]
+    int attach_local(const struct FvSolver& S, const struct FvSolver* lo_s, int lo, const struct FvSolver* hi_s, int hi);
+    int connect_local(SlabComm* const* all);
 };
 
 }  // namespace gpf

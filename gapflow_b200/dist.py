@@ -151,6 +151,28 @@ class SlabSolver:
         dist.all_gather(parts, local, group=group)
         buf = (C.c_ubyte * (self.world * n)).from_buffer_copy(torch.cat(parts).cpu().numpy().tobytes())
         _capi.check(self.lib.gpf_comm_connect(comm, buf))
+        self.fused = False
+        if os.environ.get('GPF_SLAB_FUSED', '1') != '0' and not self.fv.cfg.visc_field:
+            # fused exchange: every rank exports its q buffers (CUDA IPC of the workspace allocation), the neighbours map
+            # them, and the pass kernels store their edge rows straight into the neighbours' ghost rows
+            nb = _capi.PEER_BLOB_BYTES
+            blob = (C.c_ubyte * nb)()
+            rc = self.lib.gpf_fv_peer_export(self.h, blob)
+            ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=dev)
+            oks = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(self.world)]
+            dist.all_gather(oks, ok, group=group)
+            if all(int(o.item()) for o in oks):          # all ranks or none: the step graphs must match
+                mine_b = torch.tensor(list(blob), dtype=torch.uint8, device=dev)
+                parts = [torch.zeros(nb, dtype=torch.uint8, device=dev) for _ in range(self.world)]
+                dist.all_gather(parts, mine_b, group=group)
+                blobs = (C.c_ubyte * (self.world * nb)).from_buffer_copy(torch.cat(parts).cpu().numpy().tobytes())
+                lo, hi = self._neighbours()
+                _capi.check(self.lib.gpf_comm_attach(comm, self.h, blobs, lo, hi))
+                self.fused = True
+            elif rc != 0 and self.rank == 0:
+                import warnings
+                warnings.warn("gapflow_b200: the solver workspace cannot be exported over CUDA IPC ("
+                              + self.lib.gpf_last_error().decode() + "); the slab step keeps its exchange kernels")
         dist.barrier(group=group)            # nobody writes into a buffer that is still being zeroed
         self._comm = comm
 
@@ -357,21 +379,53 @@ class InProcessSlabs:
         lo = hi = None
         group = None
 
-    def __init__(self, d, q_global, topo_global, world, extra_global=None, split=True):
+    def __init__(self, d, q_global, topo_global, world, extra_global=None, split=True, fused=False, arith='exact'):
         per = x_periodic(d['grid'])
         self.world = world
         self.split = split             # passes as EDGE + INTERIOR launches, like SlabSolver's overlapped step
+        self.fused = fused             # the fused exchange of gpf_fv_slab_pass over communicators of this process
         self.s = []
         rows = slab_rows(d['grid']['Nx'], world)
         for r in range(world):
             ex = HaloExchanger(r, world, per)          # neighbour table only; never communicates
             self.s.append(SlabSolver.from_global(d, None, topo_global, extra_global, rank=r, world=world,
-                                                 exchanger=ex))
+                                                 exchanger=ex, arith=arith))
         self.d = d
+        if fused:
+            self._connect_local(d['grid']['Ny'])
         self._fold(1, _capi.FIN_PRERUN)                # kinetic_energy_old of the _initialize state
         for r, (start, n) in enumerate(rows):
             self.s[r].set_q(np.ascontiguousarray(q_global[:, start:start + n + 2]))
         self._fold(1, _capi.FIN_PRERUN_KEEP_EKIN)
+
+    def _connect_local(self, Ny):
+        """one communicator per rank, wired to each other and to the neighbours' q buffers inside this process"""
+        lib = self.s[0].lib
+        self.comms = []
+        for r in range(self.world):
+            h = (C.c_ubyte * _capi.IPC_HANDLE_BYTES)()
+            c = C.c_void_p()
+            _capi.check(lib.gpf_comm_create(self.world, r, int(Ny), h, C.byref(c)))
+            self.comms.append(c)
+        table = (C.c_void_p * self.world)(*[c.value for c in self.comms])
+        for r, s in enumerate(self.s):
+            _capi.check(lib.gpf_comm_connect_local(self.comms[r], table))
+            lo, hi = s._neighbours()
+            _capi.check(lib.gpf_comm_attach_local(self.comms[r], s.h, self.s[lo].h if lo >= 0 else None, lo,
+                                                  self.s[hi].h if hi >= 0 else None, hi))
+
+    def close(self):
+        if self.fused:
+            torch.cuda.synchronize()
+            for c in self.comms:
+                self.s[0].lib.gpf_comm_destroy(c)
+            self.comms, self.fused = [], False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def _exchange(self, rel):
         for s in self.s:
@@ -393,6 +447,16 @@ class InProcessSlabs:
             s._finish(mode)
 
     def step(self, n=1):
+        if self.fused:
+            # lock step, pass by pass: every flag a kernel waits for was raised by a kernel launched before it
+            lib = self.s[0].lib
+            for _ in range(n):
+                for c in (0, 1):
+                    for r, s in enumerate(self.s):
+                        _capi.check(lib.gpf_fv_slab_pass(s.h, self.comms[r], c, s._s()))
+                for r, s in enumerate(self.s):
+                    _capi.check(lib.gpf_fv_finish_recv(s.h, self.comms[r], _capi.FIN_STEP, C.c_void_p(s.recs.data_ptr()), s._s()))
+            return
         for _ in range(n):
             for c, rel in ((0, 1), (1, 2)):
                 for s in self.s:

@@ -309,6 +309,29 @@ int gpf_fv_finish_recv(gpf_fv* s, gpf_comm* c, int mode, double* recs_out, void*
 /* n x Problem.update() of this rank's slab (problem.py:509-569) */
 int gpf_fv_slab_step(gpf_fv* s, gpf_comm* c, int lo, int hi, int n, double* recs_out, void* stream);
 
+/* Fused exchange: with the neighbours' q buffers mapped (gpf_comm_attach), the pass kernels do the exchange
+ * themselves.  The boundary tiles store the cells of row 1 / row Nx (and their y-ghost images) straight into the
+ * lower / upper neighbour's ghost row of the same rotating buffer; the general launch of the pass (the second of
+ * its two launches, which otherwise returns at once) raises the neighbours' flags and, in the corrector, folds this
+ * rank's records and stores them into every rank's table; the thread that issues the TMA loads of a first / last
+ * tile row waits for the neighbour's flag of the previous pass.  gpf_fv_slab_step then replays 5 kernels per step
+ * (2 + 2 + the fold), none of them an exchange kernel.  On a periodic ring the ranks at the seam count their edge row
+ * twice in the kinetic-energy sum (it is also the global ghost row of the reference's padded array, which lives in
+ * the neighbour's memory) instead of reducing the received row with one more kernel.
+ *   every rank: gpf_fv_peer_export(s, blob) -> all-gather the GPF_PEER_BLOB_BYTES blobs -> gpf_comm_attach(c, s, blobs, lo, hi)
+ * The workspace must come from cudaMalloc (a torch tensor of the default caching allocator does): legacy CUDA IPC
+ * cannot export stream-ordered or virtual-memory allocations; gpf_fv_peer_export then fails with GPF_E_CUDA and
+ * the caller keeps the exchange kernels above.  GPF_SLAB_FUSED=0 keeps them too.
+ * gpf_comm_connect_local / gpf_comm_attach_local: the same wiring between communicators and solvers of ONE process
+ * (all ranks' slabs on one GPU, driven in lock step pass by pass with gpf_fv_slab_pass: what the single-GPU tests run). */
+#define GPF_PEER_BLOB_BYTES 96
+int gpf_fv_peer_export(gpf_fv* s, unsigned char* blob);
+int gpf_comm_attach(gpf_comm* c, gpf_fv* s, const unsigned char* blobs /* [world][GPF_PEER_BLOB_BYTES] */, int lo, int hi);
+int gpf_comm_connect_local(gpf_comm* c, gpf_comm* const* all /* [world] */);
+int gpf_comm_attach_local(gpf_comm* c, gpf_fv* s, gpf_fv* lo_solver, int lo, gpf_fv* hi_solver, int hi);
+/* one pass (0 predictor, 1 corrector) with the exchange fused in; the step ends with gpf_fv_finish_recv */
+int gpf_fv_slab_pass(gpf_fv* s, gpf_comm* c, int corrector, void* stream);
+
 /* --- GP surrogate inference (GaPFlow/models/gp.py) -------------------------------------
  * One handle per GP model (pressure: n_out = 1; wall shear: n_out = 2 outputs sharing one
  * kernel, gp.py:546-552).  Kernel: exp(log_amp) * Matern32(|| exp(-log_scale) . (x - x') ||)

@@ -88,6 +88,66 @@ def test_edge_plus_interior_launches_equal_one_pass(name, world):
             assert abs(sc.ekin - ref.ekin) <= 1e-13 * abs(ref.ekin)
 
 
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+@pytest.mark.parametrize("name,world", [("journal2d_periodic", 2), ("journal2d_periodic", 3), ("slider2d_xDN", 2),
+                                        ("slider2d_allDN_slip", 3), ("journal2d_flip_mc0", 4), ("journal2d_mcm1_bulk", 2),
+                                        ("asym_xy_mc0", 3), ("slider2d_allDN_mcm1", 2), ("journal1d_periodic", 5)])
+def test_fused_exchange_matches_single_domain(name, world, arith):
+    """gpf_fv_slab_pass: edge rows stored into the neighbours' ghost rows by the pass kernels' boundary tiles, flags and
+    record fold by the general launch -- all ranks in one process, driven pass by pass in lock step.  q and dt bit for bit
+    equal to the single-domain solver (ring seams, physical x sides, every MacCormack order, ragged slabs)."""
+    from gapflow_b200.dist import InProcessSlabs
+    d, extra = inputs(name)
+    o = build_case(name)
+    single, _ = make_solver(name, oracle=o, arith=arith)
+    slabs = InProcessSlabs(d, o.q, o.topo, world, extra_global=extra, fused=True, arith=arith)
+    assert all(s.dt == single.scalars().dt for s in slabs.scalars())
+    for k in range(6):
+        single.step(1)
+        slabs.step(1)
+        q, q1 = slabs.gather_q(), single.get_q()
+        assert np.array_equal(q, q1), (name, world, k, int((q != q1).sum()))
+        ref = single.scalars()
+        for s in slabs.scalars():
+            assert s.dt == ref.dt and s.step == ref.step == k + 1
+            assert s.v_max == ref.v_max and s.v_sound == ref.v_sound
+            assert abs(s.ekin - ref.ekin) <= 1e-13 * abs(ref.ekin)
+            assert abs(s.residual - ref.residual) <= 1e-9 * abs(ref.residual) + 1e-14
+    slabs.close()
+
+
+def test_fused_exchange_invalid_step_and_general_kernel_redo():
+    """a step that goes invalid stops every rank with the previous field in place; operands outside the straight-line
+    range make the general launch recompute the pass -- it then re-sends the edge rows and closes the pass itself"""
+    from gapflow_b200.dist import InProcessSlabs
+    name = "journal2d_periodic"
+    d, extra = inputs(name)
+    o = build_case(name)
+    slabs = InProcessSlabs(d, o.q, o.topo, 3, fused=True)
+    slabs.step(1)
+    q1 = slabs.gather_q()
+    for s in slabs.s:
+        s.fv.set_scalars(dt=1e-3)
+    slabs.step(1)
+    for s in slabs.s:
+        sc = s.fv.scalars()
+        assert sc.stop == 1 and sc.step == 1
+    assert np.array_equal(slabs.gather_q(), q1)
+    slabs.step(2)                                   # halted: the exchanges and folds still run, nothing moves
+    assert np.array_equal(slabs.gather_q(), q1)
+    slabs.close()
+    # tiny momenta (outside [2^-100, 2^100]) in one slab: the straight-line launch flags the pass, the general one redoes it
+    o = build_case(name)
+    o.q[1, 5:9, 3:7] = 1e-40
+    single, _ = make_solver(name, oracle=o)
+    slabs = InProcessSlabs(d, o.q, o.topo, 2, fused=True)
+    for k in range(3):
+        single.step(1)
+        slabs.step(1)
+        assert np.array_equal(slabs.gather_q(), single.get_q()), k
+    slabs.close()
+
+
 def test_in_process_slabs_invalid_step_stops_every_rank():
     from gapflow_b200.dist import InProcessSlabs
     name = "journal2d_periodic"
