@@ -219,9 +219,11 @@ def test_sound_wave_decay(n):
 # ---------------------------------------------------------------------------------------------
 # Problem.run() on x-slabs (gapflow_b200.dist.Parallel): same files as the single-domain run
 # ---------------------------------------------------------------------------------------------
-def _run_problem_threads(make, world):
+def _run_problem_threads(make, world, collect=None):
     """one Problem per rank, ranks = threads of this process on one GPU (ThreadColl stands in for torch.distributed;
-    the launches of all ranks go down one stream in lock step, so no kernel ever waits for a peer)"""
+    the launches of all ranks go down one stream in lock step, so no kernel ever waits for a peer).  ``collect(p)``
+    runs on every rank's thread after run(): q, mass, ... of a slab-decomposed Problem are GLOBAL quantities whose
+    access is a collective of all ranks."""
     import threading
     from gapflow_b200.dist import Parallel
     from gapflow_b200.surrogate import ThreadColl
@@ -233,7 +235,7 @@ def _run_problem_threads(make, world):
             torch.cuda.set_device(0)
             p = make(Parallel.threads(tc, r))
             p.run()
-            out[r] = p
+            out[r] = collect(p) if collect else p
         except BaseException as e:
             import traceback
             errs.append((r, traceback.format_exc()))
@@ -266,10 +268,12 @@ def test_problem_run_on_slabs_writes_the_same_files(tmp_path, world, capsys):
         return Problem(d['options'], d['grid'], d['numerics'], d['properties'], d['geometry'], parallel=par)
     one = make(None, 'one')
     one.run()
-    ranks = _run_problem_threads(lambda par: make(par, f'slabs{world}'), world)
-    assert all(p.step == one.step == 120 for p in ranks)
-    assert all(p.dt == one.dt and np.array_equal(p.q, one.q) for p in ranks)        # q, dt: global and bit-identical
-    assert all(abs(p.mass - one.mass) <= 1e-12 * one.mass for p in ranks)
+    ranks = _run_problem_threads(lambda par: make(par, f'slabs{world}'), world,
+                                 collect=lambda p: (p.step, p.dt, p.q.copy(), p.mass, p.kinetic_energy))
+    assert all(st == one.step == 120 for st, *_ in ranks)
+    assert all(dt == one.dt and np.array_equal(q, one.q) for _, dt, q, _, _ in ranks)      # q, dt: global and bit-identical
+    assert all(abs(m - one.mass) <= 1e-12 * one.mass for *_, m, _ in ranks)
+    assert all(abs(e - one.kinetic_energy) <= 1e-12 * one.kinetic_energy for *_, e in ranks)
     a, b = _read_nc(str(tmp_path / 'one' / 'sol.nc')), _read_nc(str(tmp_path / f'slabs{world}' / 'sol.nc'))
     assert sorted(a) == sorted(b)
     for k in a:

@@ -1,4 +1,7 @@
 #!/bin/bash
-# run one test file on the GPU: tools/gpu_t.sh <tag> <pytest args...>
-tag=$1; shift; out=gpurun_out/$tag; mkdir -p $out
-timeout 600 python -m pytest "$@" -x -q --timeout 300 > $out/pytest.log 2>&1; echo "pytest exit $?"; tail -40 $out/pytest.log
+# GPU tests with the log kept: tools/gpu_t.sh <tag> [pytest args...]
+tag=$1; shift
+out=gpurun_out/$tag
+mkdir -p $out
+timeout 1200 python -m pytest "$@" -m gpu -q --timeout 120 --durations=10 > $out/pytest.log 2>&1; echo "pytest exit $?" | tee -a $out/pytest.log
+tail -25 $out/pytest.log
