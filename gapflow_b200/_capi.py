@@ -115,6 +115,7 @@ SIGNATURES = {
     "gpf_gp_workspace_bytes": (_i, [_i, _i, _i, C.POINTER(C.c_size_t)]),
     "gpf_gp_create": (_i, [_i, _i, _i, _vp, _sz, C.POINTER(_vp)]),
     "gpf_gp_destroy": (_i, [_vp]),
+    "gpf_gp_set_arith": (_i, [_vp, _i]),
     "gpf_gp_factor": (_i, [_vp, _dp, _i, C.c_double, _dp, C.c_double, _dp, _vp]),
     "gpf_gp_get_factor": (_i, [_vp, _dp, _dp, _vp]),
     "gpf_gp_train_workspace_bytes": (_i, [_i, C.POINTER(C.c_size_t)]),

@@ -274,6 +274,13 @@ int gpf_gp_create(int M_max, int D, int n_out, void* workspace, size_t bytes, gp
     return GPF_OK;
     GPF_CATCH
 }
+int gpf_gp_set_arith(gpf_gp* g, int arith) {
+    GPF_TRY NEED(g)
+    if (arith != GPF_ARITH_EXACT && arith != GPF_ARITH_FAST) { set_error("arith must be GPF_ARITH_EXACT or GPF_ARITH_FAST"); return GPF_E_INVALID; }
+    g->G.fast_arith = arith == GPF_ARITH_FAST;
+    return GPF_OK;
+    GPF_CATCH
+}
 int gpf_gp_destroy(gpf_gp* g) {
     GPF_TRY delete g; return GPF_OK; GPF_CATCH
 }

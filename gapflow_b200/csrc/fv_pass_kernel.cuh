@@ -345,18 +345,24 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     // a launch covers all tile rows (mul 1, off 0), the interior ones (mul 1, off 1) or the first
     // and the last one (mul = rows - 1, off 0): see FvSolver::pass
     const int bx_mul = A.bx_mul, bx_off = A.bx_off;
+    // Fused slab exchange: a pass with d > 0 needs the lower neighbour's edge row in its FIRST tile row, one with d < 0
+    // the upper neighbour's in its LAST.  The rows arrive when the neighbour's previous pass ends, so the tile rows are
+    // walked such that the one that needs them comes last (d > 0: top to bottom reversed): every wait then has a
+    // whole pass of slack and ranks may drift apart by up to a pass without stalling each other.
+    const bool flip_rows = A.X.on && d > 0;
+    auto tile_row = [&](int vbx) { const int r = vbx * bx_mul + bx_off; return flip_rows ? P.nblk_y - 1 - r : r; };
     // fused slab exchange: the ghost row a first / last tile row stages was stored by the neighbour's previous pass;
     // its flag carries the number of that exchange = the exchanges this rank has published so far
     const unsigned long long xneed = (A.X.on && tid == 0) ? *A.X.xseq : 0ull;
     auto issue = [&](int vbx, int by, int stage) {         // thread 0 only
         if (A.X.on) {
-            const int trow = vbx * bx_mul + bx_off;
+            const int trow = tile_row(vbx);
             bool waited = false;
             if (ox == 1 && trow == 0 && P.bc.type[0][0] == GPF_BC_HALO) { spin_until(A.X.my_flag + 0, xneed, A.X.err); waited = true; }
             if (ox == 0 && trow == P.nblk_y - 1 && P.bc.type[1][0] == GPF_BC_HALO) { spin_until(A.X.my_flag + 1, xneed, A.X.err); waited = true; }
             if (waited) asm volatile("fence.proxy.async;" ::: "memory");     // peer-written rows, read next by the TMA unit
         }
-        const int i0 = 1 + (vbx * bx_mul + bx_off) * TX, j0 = 1 + by * TY;
+        const int i0 = 1 + tile_row(vbx) * TX, j0 = 1 + by * TY;
         unsigned char* base = smem + (size_t)stage * S::STAGE;
         uint64_t* b = bar + stage;
         mbar_expect_tx(b, S::TX_BYTES);
@@ -500,7 +506,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             // the GP pressure of every staged cell that lies inside the padded array (the others are
             // neighbours of cells that are neither stored nor counted)
             if (A.sg_p) {
-                const int io = 1 + (bx * bx_mul + bx_off) * TX - ox, jo = 1 + by * TY - oy;   // cell of box offset 0
+                const int io = 1 + tile_row(bx) * TX - ox, jo = 1 + by * TY - oy;   // cell of box offset 0
                 auto put = [&](int o) {
                     const int r = o / BY, i = io + r, j = jo + (o - r * BY);
                     if (i >= 0 && i <= Nx + 1 && j >= 0 && j <= Ny + 1)
@@ -516,7 +522,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
         // ---- phase 2: wall stresses, fluxes, source, update, ghosts, reductions ----------
         const bool fast = !SG && (!GEN || ((sbad[fl] == 0) && dt_fast));           // tile-uniform
         if (GEN && tid == 0) sbad[fl ^ 1] = 0;                                      // next tile's flag
-        const int rbx = bx * bx_mul + bx_off;                                      // tile row in the grid
+        const int rbx = tile_row(bx);                                              // tile row in the grid
         const int i0 = 1 + rbx * TX, j0 = 1 + by * TY;
         const bool full = (i0 + TX - 1 <= Nx) && (j0 + TY - 1 <= Ny);
         const bool btile = (rbx == 0) | (i0 + TX - 1 >= Nx) | (by == 0) | (j0 + TY - 1 >= Ny);
@@ -535,7 +541,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
                 SgWall w;
                 w.mask = (A.sg_xz ? 1u : 0u) | (A.sg_yz ? 2u : 0u);
                 w.lo_xz = w.up_xz = w.lo_yz = w.up_yz = 0.0;
-                const int i = 1 + (bx * bx_mul + bx_off) * TX + 2 * g + k, j = 1 + by * TY + ty;
+                const int i = 1 + tile_row(bx) * TX + 2 * g + k, j = 1 + by * TY + ty;
                 if (i <= Nx && j <= Ny) {
                     const size_t np = (size_t)(Nx + 2) * (Ny + 2), a = (size_t)i * (Ny + 2) + j;
                     if (A.sg_xz) { w.lo_xz = A.sg_xz[a] * A.sg_scale[1]; w.up_xz = A.sg_xz[np + a] * A.sg_scale[1]; }

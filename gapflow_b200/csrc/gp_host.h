@@ -18,6 +18,7 @@ struct FvSolver;
 
 struct GpModel {
     int Mmax, D, nout, M, Mp, nslots;
+    bool fast_arith = true;   // gpf_gp_set_arith: contracted exp / sqrt in the mean kernel (1e-12; the GP tolerance is 1e-9)
     GpKern kp;
     // carved from the caller's workspace
     double* Xs;          // (Mp, D) pre-scaled training inputs
@@ -37,7 +38,7 @@ struct GpModel {
     bool t1d_valid = false;          // tables match the last factorisation
     Mean1D t1d_view;
     int build_mean1d(cudaStream_t s);
-    // O(log M) variance of one-input models (gp_var1d.h); opt-in (GPF_GP_VAR1D=1)
+    // O(log M) variance of one-input models (gp_var1d.h); GPF_GP_VAR1D=0 restores the dense solve
     double* v1d;         // 7 Mp doubles: u, Pf (3), Pb (3)
     double yerr_last = 0.0;
     bool v1d_valid = false;

@@ -65,6 +65,34 @@ __device__ __forceinline__ double m32_rt(const double* a, const double* b, int D
     return amp * (1.0 + r) * exp(-r);
 }
 
+// ---- contracted arithmetic of the mean kernel (GPF_ARITH_FAST; north_star's GP tolerance is 1e-9 relative) --------
+// exp(x), -700 <= x <= 0:  x = (32 n + j) ln2/32 + f, |f| <= ln2/64;  exp(x) = 2^n T[j] (1 + f + ... + f^5/120), T[j] =
+// 2^(j/32) from a 32-entry table in shared memory.  Truncation f^6/720 <= 2.3e-15; 11 FP64 instructions against ~20
+// of the correctly rounded libm routine.
+__device__ __forceinline__ double exp_neg_fast(double x, const double* T) {
+    x = fmax(x, -700.0);
+    const double kd = fma(x, 46.16624130844683, 6755399441055744.0);      // 32 / ln 2; 1.5 * 2^52: k = rint(...) in the low word
+    const int k = __double2loint(kd);
+    const double kf = kd - 6755399441055744.0;
+    double f = fma(kf, -0.021660849392496573, x);                             // ln2/32 = hi + lo (the fma forms x - k hi exactly)
+    f = fma(kf, -1.718100943346366e-15, f);
+    double p = fma(f, 8.33333333333333322e-03, 4.16666666666666644e-02);
+    p = fma(p, f, 1.66666666666666657e-01);
+    p = fma(p, f, 0.5);
+    p = fma(p, f, 1.0);
+    p = fma(p, f, 1.0);
+    const double t = T[k & 31] * p;
+    return __hiloint2double(__double2hiint(t) + ((k >> 5) << 20), __double2loint(t));
+}
+// sqrt(d), d >= 0: one correction of d * rsqrt.approx(d) (2^-22 seed): relative error ~1e-13
+__device__ __forceinline__ double sqrt_fast(double d) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(fmax(d, 1e-290)));
+    const double g = d * y;
+    const double e = fma(-g, g, d);
+    return fma(e, 0.5 * y, g);
+}
+
 // warp tile 32 x 32 of a CTA tile: acc[mi][ni][2] += A(32 x 4*KK, row-major in smem) x B
 //   BT = true : B given as rows n with k contiguous (C += A B^T),   Bs[n][k]
 //   BT = false: B given as rows k with n contiguous (C += A B),     Bs[k][n]
@@ -304,7 +332,7 @@ __global__ void __launch_bounds__(256) gp_trsv_bwd_kernel(const double* L, int M
 // Two queries per thread (Q = 2: cells i and i + 256 of the block's 512): every shared-memory load of a
 // training point and of its alpha serves two kernel evaluations, which gives the ~13 % of issue slots
 // the loads took (profiles/r1C_ncu_coupled_summary.csv) back to the FP64 pipe.
-template <int D, int NOUT, bool GRAD>
+template <int D, int NOUT, bool GRAD, bool FASTM>
 __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const double* alpha, int M, int Mp, int nout,
                                                       GpKern kp, const double* Xtest, long long N, long long off,
                                                       long long cnt, double* mean, double* gmax_part) {
@@ -312,6 +340,10 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
     __shared__ double sx[TM * D];
     __shared__ double sa[2][TM];
     __shared__ double sred[8];
+    __shared__ double sT[32];
+    // contracted variant: inputs carry the factor sqrt(3), so r = sqrt(sum t^2) needs no multiplication
+    constexpr double PRE = FASTM ? SQRT3 : 1.0;
+    if (FASTM && threadIdx.x < 32) sT[threadIdx.x] = exp2((double)threadIdx.x / 32.0);
     long long i[Q];
     bool valid[Q];
     double x[Q][D];
@@ -321,13 +353,13 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
         i[q] = off + (long long)blockIdx.x * (256 * Q) + q * 256 + threadIdx.x;
         valid[q] = i[q] < off + cnt;
 #pragma unroll
-        for (int k = 0; k < D; ++k) x[q][k] = valid[q] ? Xtest[i[q] * D + k] * kp.s[k] : 0.0;
+        for (int k = 0; k < D; ++k) x[q][k] = valid[q] ? Xtest[i[q] * D + k] * kp.s[k] * PRE : 0.0;
         m0[q] = m1[q] = g0[q] = 0.0;
     }
     for (int t0 = 0; t0 < M; t0 += TM) {
         const int n = min(TM, M - t0);
         __syncthreads();
-        for (int e = threadIdx.x; e < n * D; e += 256) sx[e] = Xs[(size_t)t0 * D + e];
+        for (int e = threadIdx.x; e < n * D; e += 256) sx[e] = Xs[(size_t)t0 * D + e] * PRE;
         for (int e = threadIdx.x; e < n; e += 256) {
             sa[0][e] = alpha[t0 + e];
             if (NOUT > 1) sa[1][e] = alpha[(size_t)Mp + t0 + e];
@@ -343,14 +375,14 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
             for (int q = 0; q < Q; ++q) {
                 double r;
                 if constexpr (D == 1) {
-                    r = SQRT3 * fabs(x[q][0] - xt[0]);
+                    r = PRE == 1.0 ? SQRT3 * fabs(x[q][0] - xt[0]) : fabs(x[q][0] - xt[0]);
                 } else {
                     double d2 = 0.0;
 #pragma unroll
                     for (int k = 0; k < D; ++k) { const double t = x[q][k] - xt[k]; d2 += t * t; }
-                    r = SQRT3 * sqrt(d2);
+                    r = FASTM ? sqrt_fast(d2) : SQRT3 * sqrt(d2);
                 }
-                const double e = exp(-r);
+                const double e = FASTM ? exp_neg_fast(-r, sT) : exp(-r);
                 const double kv = (1.0 + r) * e;
                 m0[q] += a0 * kv;
                 if (NOUT > 1) m1[q] += a1 * kv;
@@ -364,7 +396,8 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
         if (valid[q]) {
             mean[i[q]] = kp.amp * m0[q];
             if (NOUT > 1) mean[N + i[q]] = kp.amp * m1[q];
-            g = fmax(g, -3.0 * kp.amp * kp.s[0] * g0[q]);      // d/dx_0 in the (unscaled) normalised input
+            // d/dx_0 in the (unscaled) normalised input; the contracted variant's differences carry sqrt(3)
+            g = fmax(g, (FASTM ? -SQRT3 : -3.0) * kp.amp * kp.s[0] * g0[q]);
         }
     if (!GRAD) return;
     // block max (NaN-propagating like jnp.max is not needed: a NaN gradient makes the mean NaN too)
@@ -1022,7 +1055,8 @@ int GpModel::mean(const double* Xtest, long long N, double* mean_out, double* dm
         const int nbk = (int)((cnt + 511) / 512);
         const bool grad = dmax_host != nullptr;
         switch (D) {
-#define GP_MEAN_LAUNCH(DD, NO, GR) gp_mean_kernel<DD, NO, GR><<<nbk, 256, 0, s>>>(Xs, alpha, M, Mp, nout, kp, Xtest, N, off, cnt, mean_out, gpart)
+#define GP_MEAN_LAUNCH(DD, NO, GR) do { if (fast_arith) gp_mean_kernel<DD, NO, GR, true><<<nbk, 256, 0, s>>>(Xs, alpha, M, Mp, nout, kp, Xtest, N, off, cnt, mean_out, gpart); \
+                                        else gp_mean_kernel<DD, NO, GR, false><<<nbk, 256, 0, s>>>(Xs, alpha, M, Mp, nout, kp, Xtest, N, off, cnt, mean_out, gpart); } while (0)
 #define GP_MEAN_CASE(DD) case DD:                                                     \
             if (grad) { if (nout > 1) GP_MEAN_LAUNCH(DD, 2, true); else GP_MEAN_LAUNCH(DD, 1, true); }   \
             else { if (nout > 1) GP_MEAN_LAUNCH(DD, 2, false); else GP_MEAN_LAUNCH(DD, 1, false); }      \

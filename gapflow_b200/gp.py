@@ -17,7 +17,7 @@ from . import _capi
 
 
 class GPModel:
-    def __init__(self, M_max, D, n_out=1, device=None):
+    def __init__(self, M_max, D, n_out=1, device=None, arith=None):
         if not torch.cuda.is_available():
             raise _capi.GapflowLibraryError("gapflow_b200 needs a CUDA device; there is no CPU path")
         self.lib = _capi.load()
@@ -31,6 +31,8 @@ class GPModel:
         _capi.check(self.lib.gpf_gp_create(self.M_max, self.D, self.n_out, C.c_void_p(self.workspace.data_ptr()),
                                            nbytes.value, C.byref(h)))
         self.h = h
+        if arith is not None:                 # 'fast' (library default) | 'exact': include/gapflow_b200.h gpf_gp_set_arith
+            _capi.check(self.lib.gpf_gp_set_arith(self.h, _capi.ARITH[arith]))
         self.M = 0
         self.log_amp, self.log_scale, self.yerr = None, None, None
         self.maximum_variance, self.variance_tol, self.argmax = None, None, None

@@ -342,6 +342,12 @@ typedef struct gpf_gp gpf_gp;
 int gpf_gp_workspace_bytes(int M_max, int D, int n_out, size_t* bytes);
 int gpf_gp_create(int M_max, int D, int n_out, void* workspace, size_t bytes, gpf_gp** out);
 int gpf_gp_destroy(gpf_gp* g);
+/* Arithmetic of the O(M)-per-query mean kernel (gpf_gp_mean; the mean part of gpf_gp_mean_var).  GPF_ARITH_FAST (the
+ * default; GPF_GP_ARITH=exact in the environment changes the default): exp(-r) by a 32-entry table and a degree-5
+ * polynomial, sqrt by one correction of the hardware reciprocal square root -- <= 1e-12 relative on the mean, half the
+ * FP64 instructions per kernel evaluation.  GPF_ARITH_EXACT: correctly rounded exp and sqrt.  There is no
+ * bit-exact reference for this path (tinygp / JAX's XLA kernels round differently again): its tolerance is 1e-9. */
+int gpf_gp_set_arith(gpf_gp* g, int arith);
 /* build_gp + the solves of gp.condition (gp.py:268-288, 546-568): K + yerr^2 I, its Cholesky
  * factor, alpha = K^-1 Y.  Xtrain (M, D), Y (M, n_out), log_scale (D): HOST arrays (they come
  * from the host-side database and optimiser).  This is the refactorisation that follows every
