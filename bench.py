@@ -675,6 +675,16 @@ def run_gpu(args):
         if not args.no_gp:
             gp = guarded("gp", lambda: gp_block(torch, lib, args, local))
 
+    if world > 1 and not args.no_gp and args.gp_coupled_steps > 0:
+        # GP half of the metric at N > 1: the GP-coupled step of BASELINE config 4 on N slabs (training set and factor
+        # replicated, query cells partitioned with the slabs): strong scaling of a fixed 1024^2 x 10^4 problem
+        def gp_slabs():
+            import bench_gp as BG
+            ca = argparse.Namespace(coupled_n=1024, M=args.gp_M, coupled_steps=args.gp_coupled_steps, no_cpu=True)
+            return {"coupled_step": BG.coupled_step(torch, np, lib, ca, world=world), "scaling": "strong"}
+        gp = guarded("gp", gp_slabs)
+        barrier()
+
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:

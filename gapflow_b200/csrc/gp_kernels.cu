@@ -66,31 +66,49 @@ __device__ __forceinline__ double m32_rt(const double* a, const double* b, int D
 }
 
 // ---- contracted arithmetic of the mean kernel (GPF_ARITH_FAST; north_star's GP tolerance is 1e-9 relative) --------
-// exp(x), -700 <= x <= 0:  x = (32 n + j) ln2/32 + f, |f| <= ln2/64;  exp(x) = 2^n T[j] (1 + f + ... + f^5/120), T[j] =
-// 2^(j/32) from a 32-entry table in shared memory.  Truncation f^6/720 <= 2.3e-15; 11 FP64 instructions against ~20
-// of the correctly rounded libm routine.
-__device__ __forceinline__ double exp_neg_fast(double x, const double* T) {
-    x = fmax(x, -700.0);
-    const double kd = fma(x, 46.16624130844683, 6755399441055744.0);      // 32 / ln 2; 1.5 * 2^52: k = rint(...) in the low word
+// exp(x), x <= 0:  x = (32 n + j) ln2/32 + f, |f| <= ln2/64;  exp(x) = 2^n T[j] (1 + f + ... + f^5/120), T[j] = 2^(j/32)
+// from a 32-entry table in shared memory.  Truncation f^6/720 <= 2.3e-15; 10 FP64 instructions against ~20 of the
+// correctly rounded libm routine.  The constants come from constant memory (FastK): written as literals the assembler
+// re-materialises every 64-bit constant with two moves inside the loop, and this loop is bound by issue slots (r2f:
+// 26 IMAD.MOV + 15 UMOV next to 48 FP64 instructions per training point).
+__constant__ double GP_FASTK[10] = {
+    46.16624130844683,                            // 32 / ln 2
+    6755399441055744.0,                           // 1.5 * 2^52: the low word of x * rl + magic is rint(x * rl)
+    -0.021660849392496573, -1.718100943346366e-15,   // -(ln 2 / 32), high and low part
+    8.33333333333333322e-03, 4.16666666666666644e-02, 1.66666666666666657e-01, 0.5, 1.0, 1e-300};
+struct FastK {                                    // read from constant memory: values the assembler cannot see through, so
+    double rl, magic, l_hi, l_lo, c5, c4, c3, half, one, tiny;   // they are constant-bank operands or stay in registers
+    __device__ __forceinline__ void init() {
+        rl = GP_FASTK[0]; magic = GP_FASTK[1]; l_hi = GP_FASTK[2]; l_lo = GP_FASTK[3]; c5 = GP_FASTK[4];
+        c4 = GP_FASTK[5]; c3 = GP_FASTK[6]; half = GP_FASTK[7]; one = GP_FASTK[8]; tiny = GP_FASTK[9];
+    }
+};
+__device__ __forceinline__ double exp_neg_fast(double x, const double* T, const FastK& K) {
+    // x <= 0 here; below -700 the result is 0 to every accuracy that matters: clamp on the integer pipe (for
+    // negative doubles a larger magnitude is a larger high word)
+    const unsigned hx = (unsigned)__double2hiint(x);
+    if (hx > 0xC085E000u) x = -700.0;
+    const double kd = fma(x, K.rl, K.magic);
     const int k = __double2loint(kd);
-    const double kf = kd - 6755399441055744.0;
-    double f = fma(kf, -0.021660849392496573, x);                             // ln2/32 = hi + lo (the fma forms x - k hi exactly)
-    f = fma(kf, -1.718100943346366e-15, f);
-    double p = fma(f, 8.33333333333333322e-03, 4.16666666666666644e-02);
-    p = fma(p, f, 1.66666666666666657e-01);
-    p = fma(p, f, 0.5);
-    p = fma(p, f, 1.0);
-    p = fma(p, f, 1.0);
+    const double kf = kd - K.magic;
+    double f = fma(kf, K.l_hi, x);                // the fma forms x - k ln2/32 without intermediate rounding
+    f = fma(kf, K.l_lo, f);
+    double p = fma(f, K.c5, K.c4);
+    p = fma(p, f, K.c3);
+    p = fma(p, f, K.half);
+    p = fma(p, f, K.one);
+    p = fma(p, f, K.one);
     const double t = T[k & 31] * p;
     return __hiloint2double(__double2hiint(t) + ((k >> 5) << 20), __double2loint(t));
 }
-// sqrt(d), d >= 0: one correction of d * rsqrt.approx(d) (2^-22 seed): relative error ~1e-13
-__device__ __forceinline__ double sqrt_fast(double d) {
+// sqrt(d), d > 0 (the caller starts its sum of squares at 1e-300): one correction of d * rsqrt.approx(d)
+// (2^-22 seed): relative error ~1e-13
+__device__ __forceinline__ double sqrt_fast(double d, const FastK& K) {
     double y;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(fmax(d, 1e-290)));
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
     const double g = d * y;
     const double e = fma(-g, g, d);
-    return fma(e, 0.5 * y, g);
+    return fma(e, K.half * y, g);
 }
 
 // warp tile 32 x 32 of a CTA tile: acc[mi][ni][2] += A(32 x 4*KK, row-major in smem) x B
@@ -344,6 +362,8 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
     // contracted variant: inputs carry the factor sqrt(3), so r = sqrt(sum t^2) needs no multiplication
     constexpr double PRE = FASTM ? SQRT3 : 1.0;
     if (FASTM && threadIdx.x < 32) sT[threadIdx.x] = exp2((double)threadIdx.x / 32.0);
+    FastK K;
+    if (FASTM) K.init();
     long long i[Q];
     bool valid[Q];
     double x[Q][D];
@@ -377,13 +397,13 @@ __global__ void __launch_bounds__(256) gp_mean_kernel(const double* Xs, const do
                 if constexpr (D == 1) {
                     r = PRE == 1.0 ? SQRT3 * fabs(x[q][0] - xt[0]) : fabs(x[q][0] - xt[0]);
                 } else {
-                    double d2 = 0.0;
+                    double d2 = FASTM ? K.tiny : 0.0;
 #pragma unroll
                     for (int k = 0; k < D; ++k) { const double t = x[q][k] - xt[k]; d2 += t * t; }
-                    r = FASTM ? sqrt_fast(d2) : SQRT3 * sqrt(d2);
+                    r = FASTM ? sqrt_fast(d2, K) : SQRT3 * sqrt(d2);
                 }
-                const double e = FASTM ? exp_neg_fast(-r, sT) : exp(-r);
-                const double kv = (1.0 + r) * e;
+                const double e = FASTM ? exp_neg_fast(-r, sT, K) : exp(-r);
+                const double kv = FASTM ? fma(r, e, e) : (1.0 + r) * e;
                 m0[q] += a0 * kv;
                 if (NOUT > 1) m1[q] += a1 * kv;
                 if (GRAD) g0[q] += a0 * ((x[q][0] - xt[0]) * e);

@@ -203,6 +203,7 @@ class Problem:
             self._solver.set_q(self._q_host)
             self._q_exposed = False
             self._clos_cache = None
+            self._scal_stale = True          # dt_crit / cfl / v_sound of an edited q: see _scalars
 
     @property
     def dt(self):
@@ -231,6 +232,11 @@ class Problem:
     def _scalars(self):
         self._sync_to_device()
         self._push_dt()
+        if getattr(self, '_scal_stale', False) and self._sur is not None and self._sur.ready and 'zz' in self._sur.models:
+            # a pressure GP defines the sound speed (stress.py:522-537): after a host edit of q the scalars of the
+            # current field are folded with the slope of the GP mean, not with the fixed-form law
+            self._sur.refresh_scalars()
+        self._scal_stale = False
         return self._solver.scalars()
 
     # GP models of the reference's sub-objects (problem.py:141-146); None for a fixed-form law
@@ -294,7 +300,7 @@ class Problem:
             self._sur.update(self.step)
         else:
             self._solver.step(1)
-        self._q_synced, self._clos_cache = False, None
+        self._q_synced, self._clos_cache, self._scal_stale = False, None, False
         sc = self._pull()
         if sc.stop and not self.options['silent'] and self._root:
             print("Stopping: NaN or negative density detected (state of the previous step restored).")

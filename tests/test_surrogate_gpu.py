@@ -212,6 +212,15 @@ def test_problem_with_gp_from_yaml_runs_and_writes_outputs(tmp_path):
     rows = open(os.path.join(problem.outdir, 'gp_zz.csv')).read().strip().splitlines()
     assert rows[0].split(',')[:3] == ['step', 'database_size', 'variance'] and len(rows) >= 2
     assert problem.database.size >= 10
+    # host edit of q between steps: dt_crit / cfl / v_sound of the edited field take the GP sound speed (stress.py:522-537),
+    # as the reference's properties would (problem.py:349-358), not the fixed-form law
+    sc0 = problem._solver.scalars()
+    problem.q[0] *= 1.0 + 1e-3
+    vs = problem.pressure.v_sound
+    zz = problem.gp_models['zz']
+    want = np.sqrt(zz.v_sound2(0))
+    assert np.isclose(vs, want, rtol=1e-12) and vs != sc0.v_sound
+    assert np.isclose(problem.dt_crit, min(d['grid']['dx'], d['grid']['dy']) / (problem.v_max + vs), rtol=1e-12)
     # the YAML-only route (no slip-length field: the shear model takes density and flux)
     _, text2 = SC.inputs('slip1d', nx=48, max_it=4, wf=2, out=str(tmp_path / 'yaml'), silent=True, sx='[0, 1]')
     p2 = Problem.from_string(text2)
