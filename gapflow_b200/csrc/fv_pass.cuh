@@ -190,7 +190,7 @@ __device__ __forceinline__ void red_accum(Red& r, const double v[3], const EosPa
 // X != nullptr (fused slab exchange, SlabX in fv_host.h): a cell of row 1 (row Nx) and its y-ghost images are also
 // stored into the lower (upper) neighbour's ghost row of the same rotating buffer, over NVLink -- a neighbour's
 // interior row with its y ghosts filled is exactly what the reference's x-then-y fill order leaves in an x-ghost row.
-template <bool CORR, int EOS>
+template <bool CORR, int EOS, bool SX = false>
 __device__ __noinline__ Red boundary_cell(const FvParams& P, int i, int j, double s0, double s1, double s2,
                                           double n0, double n1, double n2, double* qout, const double* q0b,
                                           const SlabX* X = nullptr, int out_idx = 0) {
@@ -223,14 +223,14 @@ __device__ __noinline__ Red boundary_cell(const FvParams& P, int i, int j, doubl
             }
         }
     };
-    if (X) remote(j, qn);
+    if constexpr (SX) remote(j, qn);
     for_each_ghost(P, i, j, qn, [&](int gi, int gj, const double* gv) {
         const size_t ga = (size_t)gi * pitch + (gj + 1);
         qout[ga] = gv[0];
         qout[plane + ga] = gv[1];
         qout[2 * plane + ga] = gv[2];
         if (CORR) red_accum<EOS>(r, gv, P.eos);
-        if (X && gi == i) remote(gj, gv);                 // y-ghost image of an edge-row cell
+        if constexpr (SX) { if (gi == i) remote(gj, gv); }   // y-ghost image of an edge-row cell
     });
     return r;
 }

@@ -295,9 +295,12 @@ __device__ __forceinline__ void slab_publish(const PassArgs& A, bool corr, doubl
 // tile takes the plain-division path; the pressure of a staged cell and the own shear component of the
 // wall stresses come from the GP means of the pass's input (dense arrays over the padded grid, row
 // i*(Ny+2)+j like gp.py:223-232 orders them) times the model's Yscale (gp.py:362).
-template <bool CORR, bool LS, int EOS, bool XF, bool GEN, bool VF = false, bool SG = false>
+// SX = true: the fused slab exchange (SlabX).  A separate instantiation: folded into the plain kernels as a run-time
+// switch it cost them 10 registers and 1.3 % (contracted) to 5 % (exact arithmetic) of a single-GPU step (r2g).
+template <bool CORR, bool LS, int EOS, bool XF, bool GEN, bool VF = false, bool SG = false, bool SX = false>
 __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kernel(const __grid_constant__ PassArgs A) {
     static_assert(!SG || (GEN && LS && !XF && !VF && EOS == -1), "surrogate variant: general kernel, general closures");
+    static_assert(!SX || (!VF && !SG), "fused exchange: fixed-form variants only");
     constexpr int NST = fv_nstage(CORR);
     using S = Smem<CORR, LS, XF, NST, VF>;
     extern __shared__ __align__(1024) unsigned char smem[];      // no static shared memory: offset 0
@@ -315,11 +318,11 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     // fused slab exchange: the general launch closes the pass for its rank (flags, record) also when it has nothing
     // to recompute, and when the run has halted (every rank halts in the same step; the fold still runs)
     if (st->stop || (A.until_converged && st->halt)) {
-        if (GEN && A.X.on && blockIdx.x == 0) slab_publish(A, CORR, reinterpret_cast<double*>(smem));
+        if (GEN && SX && blockIdx.x == 0) slab_publish(A, CORR, reinterpret_cast<double*>(smem));
         return;
     }
     if (GEN && !SG && A.redo[CORR] == 0) {
-        if (A.X.on && blockIdx.x == 0) slab_publish(A, CORR, reinterpret_cast<double*>(smem));
+        if (SX && blockIdx.x == 0) slab_publish(A, CORR, reinterpret_cast<double*>(smem));
         return;
     }
 
@@ -349,13 +352,13 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     // the upper neighbour's in its LAST.  The rows arrive when the neighbour's previous pass ends, so the tile rows are
     // walked such that the one that needs them comes last (d > 0: top to bottom reversed): every wait then has a
     // whole pass of slack and ranks may drift apart by up to a pass without stalling each other.
-    const bool flip_rows = A.X.on && d > 0;
+    const bool flip_rows = SX && d > 0;
     auto tile_row = [&](int vbx) { const int r = vbx * bx_mul + bx_off; return flip_rows ? P.nblk_y - 1 - r : r; };
     // fused slab exchange: the ghost row a first / last tile row stages was stored by the neighbour's previous pass;
     // its flag carries the number of that exchange = the exchanges this rank has published so far
-    const unsigned long long xneed = (A.X.on && tid == 0) ? *A.X.xseq : 0ull;
+    const unsigned long long xneed = (SX && tid == 0) ? *A.X.xseq : 0ull;
     auto issue = [&](int vbx, int by, int stage) {         // thread 0 only
-        if (A.X.on) {
+        if constexpr (SX) {
             const int trow = tile_row(vbx);
             bool waited = false;
             if (ox == 1 && trow == 0 && P.bc.type[0][0] == GPF_BC_HALO) { spin_until(A.X.my_flag + 0, xneed, A.X.err); waited = true; }
@@ -612,12 +615,13 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             if (btile) {
                 const int i = i0 + 2 * g + k, j = j0 + ty;
                 if (act && ((i == 1) | (i == Nx) | (j == 1) | (j == Ny))) {
-                    const Red br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b,
-                                                            A.X.on ? &A.X : nullptr, out_idx);
+                    Red br;
+                    if constexpr (SX) br = boundary_cell<CORR, EOS, true>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b, &A.X, out_idx);
+                    else br = boundary_cell<CORR, EOS>(P, i, j, qq.v0, qq.v1, qq.v2, qn0, qn1, qn2, qout, q0b);
                     if (CORR) {
                         // periodic ring, fused exchange: this row is also the global ghost row of the reference's padded
                         // array (it lives in the neighbour's memory): the cell and its y-ghost images count once more
-                        if (A.X.on && ((A.X.edge_dup[0] && i == 1) || (A.X.edge_dup[1] && i == Nx))) red.ekin += w * 0.5 + br.ekin;
+                        if (SX && ((A.X.edge_dup[0] && i == 1) || (A.X.edge_dup[1] && i == Nx))) red.ekin += w * 0.5 + br.ekin;
                         red.ekin += br.ekin;
                         red.vmax2 = fmax(red.vmax2, br.vmax2);
                         red.cs2 = fmax(red.cs2, br.cs2);
@@ -691,7 +695,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
             A.pflags[slot] = F;
         }
     }
-    if (GEN && A.X.on) {
+    if (GEN && SX) {
         // the general kernel ran the pass in full (redo, or the surrogate variant): the last CTA out closes it
         __syncthreads();
         if (tid == 0) {
@@ -704,7 +708,7 @@ __global__ void __launch_bounds__(FV_THREADS, fv_ctas_per_sm(CORR)) fv_pass_kern
     }
 }
 
-template <bool CORR, bool LS, int EOS, bool XF, bool VF = false>
+template <bool CORR, bool LS, int EOS, bool XF, bool VF = false, bool SX = false>
 static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
     using Sm = Smem<CORR, LS, XF, fv_nstage(CORR), VF>;
     // the opt-in to > 48 KB of dynamic shared memory is a per-device attribute of the function
@@ -712,12 +716,12 @@ static int launch_pass_variant(const PassArgs& A, int ncta, cudaStream_t s) {
     int dev = 0;
     GPF_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, false, VF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
-        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, true, VF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, false, VF, false, SX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
+        GPF_CUDA(cudaFuncSetAttribute(fv_pass_kernel<CORR, LS, EOS, XF, true, VF, false, SX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Sm::TOTAL));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    fv_pass_kernel<CORR, LS, EOS, XF, false, VF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
-    fv_pass_kernel<CORR, LS, EOS, XF, true, VF><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    fv_pass_kernel<CORR, LS, EOS, XF, false, VF, false, SX><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
+    fv_pass_kernel<CORR, LS, EOS, XF, true, VF, false, SX><<<ncta, FV_THREADS, Sm::TOTAL, s>>>(A);
     return GPF_OK;
 }
 
@@ -743,6 +747,18 @@ int launch_pass_dispatch(const PassArgs& A, bool ls, bool dh, bool xf, bool vf, 
     // viscosity field (piezo / thinning): one variant, the general closures with the slip-length plane
     // (zeros when the configuration has none: the LS forms with Ls = 0 round like the reference's)
     if (vf) return launch_pass_variant<CORR, true, -1, false, true>(A, n, s);
+    if (A.X.on) {          // fused slab exchange: the SX instantiations
+        switch ((ls ? 4 : 0) + (dh ? 2 : 0) + (xf ? 1 : 0)) {
+        case 0: return launch_pass_variant<CORR, false, -1, false, false, true>(A, n, s);
+        case 1: return launch_pass_variant<CORR, false, -1, true, false, true>(A, n, s);
+        case 2: return launch_pass_variant<CORR, false, GPF_EOS_DH, false, false, true>(A, n, s);
+        case 3: return launch_pass_variant<CORR, false, GPF_EOS_DH, true, false, true>(A, n, s);
+        case 4: return launch_pass_variant<CORR, true, -1, false, false, true>(A, n, s);
+        case 5: return launch_pass_variant<CORR, true, -1, true, false, true>(A, n, s);
+        case 6: return launch_pass_variant<CORR, true, GPF_EOS_DH, false, false, true>(A, n, s);
+        default: return launch_pass_variant<CORR, true, GPF_EOS_DH, true, false, true>(A, n, s);
+        }
+    }
     switch ((ls ? 4 : 0) + (dh ? 2 : 0) + (xf ? 1 : 0)) {
     case 0: return launch_pass_variant<CORR, false, -1, false>(A, n, s);
     case 1: return launch_pass_variant<CORR, false, -1, true>(A, n, s);

@@ -33,6 +33,8 @@
 namespace gpf {
 
 constexpr int NB = 64;          // block size of the factorisation and of the substitutions
+constexpr int MPAD = 128;       // the matrices are padded to a multiple of 128 (= the column width of the GEMM tiles): identity there
+__host__ __device__ constexpr size_t pad_m(size_t m) { return (m + MPAD - 1) / MPAD * MPAD; }
 constexpr int NQ = 128;         // query columns per CTA of the variance kernel
 constexpr int LDT = NB + 4;     // shared-memory row stride of a 64-wide FP64 tile (2 wavefronts per fragment load)
 constexpr int LDQ = NQ + 4;
@@ -114,7 +116,8 @@ __device__ __forceinline__ double sqrt_fast(double d, const FastK& K) {
 // warp tile 32 x 32 of a CTA tile: acc[mi][ni][2] += A(32 x 4*KK, row-major in smem) x B
 //   BT = true : B given as rows n with k contiguous (C += A B^T),   Bs[n][k]
 //   BT = false: B given as rows k with n contiguous (C += A B),     Bs[k][n]
-template <bool BT, int KK>
+//   AT = true : A given as rows k with m contiguous (C += A^T B),   As[k][m]
+template <bool BT, int KK, bool AT = false>
 __device__ __forceinline__ void warp_mma(double (&acc)[4][4][2], const double* As, int lda, const double* Bs, int ldb,
                                          int lane) {
     const int r = lane >> 2, c = lane & 3;
@@ -122,7 +125,7 @@ __device__ __forceinline__ void warp_mma(double (&acc)[4][4][2], const double* A
     for (int kk = 0; kk < KK; ++kk) {
         double a[4], b[4];
 #pragma unroll
-        for (int mi = 0; mi < 4; ++mi) a[mi] = As[(mi * 8 + r) * lda + kk * 4 + c];
+        for (int mi = 0; mi < 4; ++mi) a[mi] = AT ? As[(kk * 4 + c) * lda + mi * 8 + r] : As[(mi * 8 + r) * lda + kk * 4 + c];
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) b[ni] = BT ? Bs[(ni * 8 + r) * ldb + kk * 4 + c] : Bs[(kk * 4 + c) * ldb + ni * 8 + r];
 #pragma unroll
@@ -671,83 +674,161 @@ __device__ __forceinline__ void load_tile_t(double* dst, const double* src, int 
     for (int e = tid; e < NB * NB; e += nthr) dst[(e % NB) * LDT + e / NB] = src[(size_t)(e / NB) * ld + e % NB];
 }
 
-// X = L^-1 (lower triangular, Mp x Mp, blocks above the diagonal are not written).  One CTA per
-// block column j:  X_jj = Dinv_j;  X_ij = -Dinv_i sum_{k=j}^{i-1} L_ik X_kj  for i = j+1 .. nb-1.
-__global__ void __launch_bounds__(128) gp_trtri_kernel(const double* L, const double* Dinv, int Mp, double* X) {
+// ------------------------------------------------------------------------------------
+// One DMMA GEMM engine for the dense level-3 work of training: a CTA (256 threads, 2 x 4 warps of 32 x 32) forms a
+// 64 x 128 tile  sum_{k0 <= k < k1} A(m, k) B(k, n)  through a 3-stage cp.async pipeline of 16-deep slices -- the
+// main loop of the variance kernel with the operand layouts as template parameters:
+//   AT: A stored as [k][m] (the product uses A^T),  BT: B stored as [n][k] (the product uses B^T).
+// Two CTAs share an SM.  What the tile is, which k range is non-zero and what happens to the result depends on
+// the job (tile coordinates from blockIdx, no tile list in memory):
+//   GEMM_TRTRI_T   T = L21 X11        one level of the recursive inverse, first product   (NN)  -> T
+//   GEMM_TRTRI_X   X21 = -X22 T       second product                                      (NN)  -> X
+//   GEMM_LAUUM     Kinv = X^T X       lower triangle                                      (TN)  -> Kinv
+// ------------------------------------------------------------------------------------
+enum { GEMM_TRTRI_T = 0, GEMM_TRTRI_X = 1, GEMM_LAUUM = 2 };
+constexpr int GK = 16;                                   // k-depth of a pipeline slice
+constexpr int GST = 3;
+constexpr int G_LDA = GK + 4, G_LDAT = NB + 4, G_LDB = NQ + 4, G_LDBT = GK + 4;
+constexpr size_t GEMM_STAGE = (size_t)(NB * G_LDA + NQ * G_LDBT) * 8;      // the larger of the layouts: 30 720 bytes
+constexpr size_t GEMM_SMEM = GST * GEMM_STAGE;
+static_assert((size_t)(GK * G_LDAT + GK * G_LDB) * 8 <= GEMM_STAGE, "stage size");
+
+struct GemmJob {
+    int mode;
+    int Mp;              // leading dimension of every matrix
+    int h;               // TRTRI: blocks (of 64) in the left part of a group at this level
+    const double* L;     // TRTRI_T: the Cholesky factor
+    double* X;           // the inverse under construction (TRTRI), its input (LAUUM)
+    double* T;           // TRTRI: scratch with the layout of X;  LAUUM: Kinv
+};
+
+template <bool AT, bool BT>
+__global__ void __launch_bounds__(256, 2) gp_gemm_kernel(const GemmJob J) {
+    extern __shared__ __align__(16) unsigned char gsm[];
+    double* sm = reinterpret_cast<double*>(gsm);
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 2, wn = w & 3;
+    const int r = lane >> 2, c = lane & 3;
+    const int ld = J.Mp, nb = J.Mp / NB;
+    // ---- the tile: rows m0 .. m0+63, columns n0 .. n0+127, k in [k0, k1) of A (lda) and B (ldb) -> C ----
+    int m0, n0, k0, k1;
+    const double *A, *B;
+    double* C;
+    bool negate = false;
+    if (J.mode == GEMM_LAUUM) {
+        // Kinv[m, n] = sum_{k >= m} X[k, m] X[k, n] for n0 <= m0 + 63 (X is lower triangular: X[k, .] = 0 left of k)
+        m0 = blockIdx.x * NB; n0 = blockIdx.y * NQ;
+        if (n0 > m0 + NB - 1) return;
+        k0 = m0; k1 = J.Mp;
+        A = J.X; B = J.X; C = J.T;
+    } else {
+        // group g of this level: blocks [a, a + h) left, [a + h, min(a + 2h, nb)) right; the tile lies in the block
+        // (right rows, left columns)
+        const int a = blockIdx.z * 2 * J.h, mid = a + J.h, end = min(a + 2 * J.h, nb);
+        if (mid >= nb) return;
+        m0 = (mid + blockIdx.x) * NB; n0 = a * NB + blockIdx.y * NQ;
+        if (m0 >= end * NB || n0 >= mid * NB) return;
+        if (J.mode == GEMM_TRTRI_T) {          // T[m, n] = sum_{k in left, k >= n0} L[m, k] X[k, n]
+            A = J.L; B = J.X; C = J.T;
+            k0 = n0; k1 = mid * NB;
+        } else {                               // X[m, n] = -sum_{k in right, k <= m0 + 63} X[m, k] T[k, n]
+            A = J.X; B = J.T; C = J.X;
+            k0 = mid * NB; k1 = m0 + NB;
+            negate = true;
+        }
+    }
+    const int nk = (k1 - k0) / GK;
+    const int lrow = tid >> 3, lch = tid & 7, vrow = tid >> 6, vch = tid & 63, trow = tid >> 5, tch = tid & 31;
+    auto stage_load = [&](int s, int kt) {
+        double* As = sm + (size_t)s * (GEMM_STAGE / 8);
+        const int k = k0 + kt * GK;
+        double* Bs;
+        if (AT) {        // A^T: 16 rows (k) x 64 doubles (m): 512 chunks
+            Bs = As + GK * G_LDAT;
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) cp_async16(As + (trow + 8 * hh) * G_LDAT + tch * 2, A + (size_t)(k + trow + 8 * hh) * ld + m0 + tch * 2);
+        } else {         // 64 rows (m) x 16 doubles (k): 512 chunks
+            Bs = As + NB * G_LDA;
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) cp_async16(As + (lrow + 32 * hh) * G_LDA + lch * 2, A + (size_t)(m0 + lrow + 32 * hh) * ld + k + lch * 2);
+        }
+        if (BT) {        // B^T: 128 rows (n) x 16 doubles (k): 1024 chunks
+#pragma unroll
+            for (int hh = 0; hh < 4; ++hh) cp_async16(Bs + (lrow + 32 * hh) * G_LDBT + lch * 2, B + (size_t)(n0 + lrow + 32 * hh) * ld + k + lch * 2);
+        } else {         // 16 rows (k) x 128 doubles (n): 1024 chunks
+#pragma unroll
+            for (int hh = 0; hh < 4; ++hh) cp_async16(Bs + (vrow + 4 * hh) * G_LDB + vch * 2, B + (size_t)(k + vrow + 4 * hh) * ld + n0 + vch * 2);
+        }
+    };
+    double acc[4][4][2] = {};
+    for (int s = 0; s < GST - 1; ++s) {
+        if (s < nk) stage_load(s, s);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nk; ++kt) {
+        cp_async_wait<GST - 2>();
+        __syncthreads();
+        const int nx = kt + GST - 1;
+        if (nx < nk) stage_load(nx % GST, nx);
+        cp_async_commit();
+        const double* As = sm + (size_t)(kt % GST) * (GEMM_STAGE / 8);
+        const double* Bs = As + (AT ? GK * G_LDAT : NB * G_LDA);
+        warp_mma<BT, GK / 4, AT>(acc, AT ? As + wm * 32 : As + wm * 32 * G_LDA, AT ? G_LDAT : G_LDA,
+                                 BT ? Bs + wn * 32 * G_LDBT : Bs + wn * 32, BT ? G_LDBT : G_LDB, lane);
+    }
+    cp_async_wait<0>();
+    const double sgn = negate ? -1.0 : 1.0;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            const int m = m0 + wm * 32 + mi * 8 + r, n = n0 + wn * 32 + ni * 8 + c * 2;
+            *reinterpret_cast<double2*>(C + (size_t)m * ld + n) = make_double2(sgn * acc[mi][ni][0], sgn * acc[mi][ni][1]);
+        }
+}
+
+// first level of the recursive inverse (h = 1): pairs of 64 x 64 blocks, X_aa = Dinv_a, X_bb = Dinv_b,
+// X_ba = -Dinv_b (L_ba Dinv_a); one CTA (128 threads) per pair of block rows (2g, 2g + 1)
+__global__ void __launch_bounds__(128) gp_trtri_leaf_kernel(const double* L, const double* Dinv, int Mp, double* X) {
     extern __shared__ double sm[];
     double* As = sm;
     double* Bs = sm + NB * LDT;
     double* Ss = sm + 2 * NB * LDT;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 1, wn = w & 1;
-    const int nb = Mp / NB, j = blockIdx.x;
     const int r = lane >> 2, c = lane & 3;
-    for (int e = tid; e < NB * NB; e += 128)
-        X[(size_t)(j * NB + e / NB) * Mp + j * NB + e % NB] = Dinv[(size_t)j * NB * NB + e];
+    const int a = 2 * blockIdx.x, b = a + 1;
+    const double* Da = Dinv + (size_t)a * NB * NB;
+    const double* Db = Dinv + (size_t)b * NB * NB;
+    for (int e = tid; e < NB * NB; e += 128) {
+        X[(size_t)(a * NB + e / NB) * Mp + a * NB + e % NB] = Da[e];
+        X[(size_t)(b * NB + e / NB) * Mp + b * NB + e % NB] = Db[e];
+        X[(size_t)(a * NB + e / NB) * Mp + b * NB + e % NB] = 0.0;        // above the diagonal
+    }
+    load_tile(As, L + (size_t)b * NB * Mp + (size_t)a * NB, Mp, tid, 128);
+    load_tile(Bs, Da, NB, tid, 128);
     __syncthreads();
-    for (int i = j + 1; i < nb; ++i) {
-        double acc[4][4][2] = {};
-        for (int k = j; k < i; ++k) {
-            load_tile(As, L + (size_t)i * NB * Mp + (size_t)k * NB, Mp, tid, 128);
-            load_tile(Bs, X + (size_t)k * NB * Mp + (size_t)j * NB, Mp, tid, 128);
-            __syncthreads();
-            warp_mma<false, NB / 4>(acc, As + wm * 32 * LDT, LDT, Bs + wn * 32, LDT, lane);
-            __syncthreads();
-        }
-#pragma unroll
-        for (int mi = 0; mi < 4; ++mi)
-#pragma unroll
-            for (int ni = 0; ni < 4; ++ni) {
-                double* q = Ss + (wm * 32 + mi * 8 + r) * LDT + wn * 32 + ni * 8 + c * 2;
-                q[0] = acc[mi][ni][0];
-                q[1] = acc[mi][ni][1];
-            }
-        load_tile(As, Dinv + (size_t)i * NB * NB, NB, tid, 128);
-        __syncthreads();
-        double out[4][4][2] = {};
-        warp_mma<false, NB / 4>(out, As + wm * 32 * LDT, LDT, Ss + wn * 32, LDT, lane);
-        double* Xij = X + (size_t)i * NB * Mp + (size_t)j * NB;
-#pragma unroll
-        for (int mi = 0; mi < 4; ++mi)
-#pragma unroll
-            for (int ni = 0; ni < 4; ++ni) {
-                double* q = Xij + (size_t)(wm * 32 + mi * 8 + r) * Mp + wn * 32 + ni * 8 + c * 2;
-                q[0] = -out[mi][ni][0];
-                q[1] = -out[mi][ni][1];
-            }
-        __threadfence_block();
-        __syncthreads();             // X_ij is read back by this CTA in the next steps
-    }
-}
-
-// Kinv_ij = sum_{k >= i} X_ki^T X_kj for block pairs i >= j (lower triangle of K^-1).
-__global__ void __launch_bounds__(128) gp_lauum_kernel(const double* X, int Mp, double* Kinv) {
-    extern __shared__ double sm[];
-    double* As = sm;
-    double* Bs = sm + NB * LDT;
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 1, wn = w & 1;
-    const int nb = Mp / NB;
-    const int p = blockIdx.x;
-    int i = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
-    while ((i + 1) * (i + 2) / 2 <= p) ++i;
-    while (i * (i + 1) / 2 > p) --i;
-    const int j = p - i * (i + 1) / 2;
     double acc[4][4][2] = {};
-    for (int k = i; k < nb; ++k) {
-        load_tile_t(As, X + (size_t)k * NB * Mp + (size_t)i * NB, Mp, tid, 128);     // As[m][kk] = X_ki[kk][m]
-        load_tile(Bs, X + (size_t)k * NB * Mp + (size_t)j * NB, Mp, tid, 128);
-        __syncthreads();
-        warp_mma<false, NB / 4>(acc, As + wm * 32 * LDT, LDT, Bs + wn * 32, LDT, lane);
-        __syncthreads();
-    }
-    const int r = lane >> 2, c = lane & 3;
-    double* Cij = Kinv + (size_t)i * NB * Mp + (size_t)j * NB;
+    warp_mma<false, NB / 4>(acc, As + wm * 32 * LDT, LDT, Bs + wn * 32, LDT, lane);
 #pragma unroll
     for (int mi = 0; mi < 4; ++mi)
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) {
-            double* q = Cij + (size_t)(wm * 32 + mi * 8 + r) * Mp + wn * 32 + ni * 8 + c * 2;
+            double* q = Ss + (wm * 32 + mi * 8 + r) * LDT + wn * 32 + ni * 8 + c * 2;
             q[0] = acc[mi][ni][0];
             q[1] = acc[mi][ni][1];
+        }
+    __syncthreads();
+    load_tile(As, Db, NB, tid, 128);
+    __syncthreads();
+    double out[4][4][2] = {};
+    warp_mma<false, NB / 4>(out, As + wm * 32 * LDT, LDT, Ss + wn * 32, LDT, lane);
+    double* Xba = X + (size_t)b * NB * Mp + (size_t)a * NB;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            double* q = Xba + (size_t)(wm * 32 + mi * 8 + r) * Mp + wn * 32 + ni * 8 + c * 2;
+            q[0] = -out[mi][ni][0];
+            q[1] = -out[mi][ni][1];
         }
 }
 
@@ -839,7 +920,7 @@ static size_t al(size_t x) { return (x + 255) / 256 * 256; }
 int GpModel::var_slots(int sms) { return VAR_CTAS_PER_SM * sms; }
 
 size_t GpModel::workspace_bytes(int Mmax, int D, int nout, int nslots) {
-    const size_t Mp = (size_t)(Mmax + NB - 1) / NB * NB;
+    const size_t Mp = pad_m(Mmax);
     size_t b = 256;
     b += al(Mp * D * 8);                 // Xs
     b += al(Mp * Mp * 8);                // L
@@ -869,11 +950,12 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
         GPF_CUDA(cudaFuncSetAttribute(gp_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
         GPF_CUDA(cudaFuncSetAttribute(gp_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
         GPF_CUDA(cudaFuncSetAttribute(gp_var_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)VAR_SMEM));
-        GPF_CUDA(cudaFuncSetAttribute(gp_trtri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm3));
-        GPF_CUDA(cudaFuncSetAttribute(gp_lauum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
+        GPF_CUDA(cudaFuncSetAttribute(gp_trtri_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm3));
+        GPF_CUDA(cudaFuncSetAttribute(gp_gemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
+        GPF_CUDA(cudaFuncSetAttribute(gp_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
     }
     if (bytes < workspace_bytes(Mmax, D, nout, nslots)) { set_error("GP workspace too small"); return GPF_E_INVALID; }
-    const size_t Mpm = (size_t)(Mmax + NB - 1) / NB * NB;
+    const size_t Mpm = pad_m(Mmax);
     unsigned char* p = reinterpret_cast<unsigned char*>(al(reinterpret_cast<size_t>(ws)));
     Xs = reinterpret_cast<double*>(p); p += al(Mpm * D * 8);
     L = reinterpret_cast<double*>(p); p += al(Mpm * Mpm * 8);
@@ -897,7 +979,7 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
                     cudaStream_t s) {
     if (M_ < 1 || M_ > Mmax) { set_error("training-set size outside [1, M_max]"); return GPF_E_INVALID; }
     M = M_;
-    Mp = (M + NB - 1) / NB * NB;
+    Mp = (int)pad_m(M);
     kp.D = D;
     kp.amp = exp(log_amp);
     for (int k = 0; k < GP_MAXD; ++k) kp.s[k] = k < D ? exp(-log_scale[k]) : 0.0;
@@ -945,7 +1027,7 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
 }
 
 size_t GpModel::train_workspace_bytes(int Mmax) {
-    const size_t Mp = (size_t)(Mmax + NB - 1) / NB * NB, nb = Mp / NB;
+    const size_t Mp = pad_m(Mmax), nb = Mp / NB;
     return 256 + 2 * al(Mp * Mp * 8) + al(nb * (nb + 1) / 2 * (1 + GP_MAXD) * 8) + al((2 + GP_MAXD) * 8);
 }
 
@@ -960,11 +1042,31 @@ int GpModel::nlml(void* work, size_t bytes, double* loss, double* grad, cudaStre
     double* part = reinterpret_cast<double*>(p); p += al((size_t)ntile * (1 + GP_MAXD) * 8);
     double* out = reinterpret_cast<double*>(p);
     const size_t sm3 = (size_t)3 * NB * LDT * 8, sm2 = (size_t)2 * NB * LDT * 8;
-    gp_trtri_kernel<<<nb, 128, sm3, s>>>(L, Dinv, Mp, X);
-    gp_lauum_kernel<<<ntile, 128, sm2, s>>>(X, Mp, Kinv);
+    // X = L^-1 by recursive doubling over the block rows (nb is even: Mp is a multiple of 128):
+    //   level 0 pairs of 64-blocks (leaf kernel); level h = 2, 4, ...: X21 = -X22 (L21 X11), two batched GEMMs
+    //   whose tiles all run at once (the block-column kernel this replaces was one serial chain per column:
+    //   141 of the 160 ms of an objective evaluation at M = 10^4, DMMA pipe 18 % busy: profiles/r2a)
+    gp_trtri_leaf_kernel<<<nb / 2, 128, sm3, s>>>(L, Dinv, Mp, X);
+    g_launches += 1;
+    for (int h = 2; h < nb; h *= 2) {
+        GemmJob J;
+        J.Mp = Mp; J.h = h; J.L = L; J.X = X; J.T = Kinv;          // Kinv's storage is free until the last step
+        const dim3 grid(h, h / 2, (nb + 2 * h - 1) / (2 * h));      // (right block rows, left 128-column tiles, groups)
+        J.mode = GEMM_TRTRI_T;
+        gp_gemm_kernel<false, false><<<grid, 256, GEMM_SMEM, s>>>(J);
+        J.mode = GEMM_TRTRI_X;
+        gp_gemm_kernel<false, false><<<grid, 256, GEMM_SMEM, s>>>(J);
+        g_launches += 2;
+    }
+    {
+        GemmJob J;
+        J.mode = GEMM_LAUUM; J.Mp = Mp; J.h = 0; J.L = L; J.X = X; J.T = Kinv;
+        gp_gemm_kernel<true, false><<<dim3(nb, Mp / NQ), 256, GEMM_SMEM, s>>>(J);
+        g_launches += 1;
+    }
     gp_grad_kernel<<<ntile, 256, 0, s>>>(Kinv, alpha, Xs, M, Mp, D, nout, kp, part);
     gp_nlml_finish_kernel<<<1, 256, 0, s>>>(L, alpha, ycopy, M, Mp, nout, part, ntile, out);
-    g_launches += 4;
+    g_launches += 2;
     GPF_CUDA(cudaGetLastError());
     double h[2 + GP_MAXD];
     GPF_CUDA(cudaMemcpyAsync(h, out, sizeof(h), cudaMemcpyDeviceToHost, s));
@@ -1026,7 +1128,7 @@ int GpModel::build_mean1d(cudaStream_t s) {
     GPF_CUDA(cudaStreamSynchronize(s));
     Mean1DHost H;
     H.build(u_host.data(), a.data(), M);
-    const size_t Mpm = (size_t)(Mmax + NB - 1) / NB * NB;
+    const size_t Mpm = pad_m(Mmax);
     double* d[5] = {t1d, t1d + Mpm, t1d + 2 * Mpm, t1d + 3 * Mpm, t1d + 4 * Mpm};
     const std::vector<double>* h[5] = {&H.u, &H.A, &H.B, &H.C, &H.D};
     for (int k = 0; k < 5; ++k) GPF_CUDA(cudaMemcpyAsync(d[k], h[k]->data(), (size_t)M * 8, cudaMemcpyHostToDevice, s));
@@ -1135,7 +1237,7 @@ __global__ void __launch_bounds__(256) gp_var1d_kernel(Var1D T, GpKern kp, const
 int GpModel::build_var1d(cudaStream_t s) {
     Var1DHost H;
     H.build(u_host.data(), M, kp.amp, yerr_last);
-    const size_t Mpm = (size_t)(Mmax + NB - 1) / NB * NB;
+    const size_t Mpm = pad_m(Mmax);
     GPF_CUDA(cudaMemcpyAsync(v1d, H.u.data(), (size_t)M * 8, cudaMemcpyHostToDevice, s));
     GPF_CUDA(cudaMemcpyAsync(v1d + Mpm, H.Pf.data(), (size_t)3 * M * 8, cudaMemcpyHostToDevice, s));
     GPF_CUDA(cudaMemcpyAsync(v1d + 4 * Mpm, H.Pb.data(), (size_t)3 * M * 8, cudaMemcpyHostToDevice, s));
