@@ -282,7 +282,15 @@ int gpf_gp_set_arith(gpf_gp* g, int arith) {
     GPF_CATCH
 }
 int gpf_gp_destroy(gpf_gp* g) {
-    GPF_TRY delete g; return GPF_OK; GPF_CATCH
+    GPF_TRY
+    if (g) {
+        if (g->G.side) { cudaStreamSynchronize(g->G.side); cudaStreamDestroy(g->G.side); }
+        if (g->G.ev_strip) cudaEventDestroy(g->G.ev_strip);
+        if (g->G.ev_rest) cudaEventDestroy(g->G.ev_rest);
+    }
+    delete g;
+    return GPF_OK;
+    GPF_CATCH
 }
 int gpf_gp_factor(gpf_gp* g, const double* Xtrain, int M, double log_amp, const double* log_scale, double yerr,
                   const double* Y, void* stream) {

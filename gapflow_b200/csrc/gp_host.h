@@ -18,6 +18,8 @@ struct FvSolver;
 
 struct GpModel {
     int Mmax, D, nout, M, Mp, nslots;
+    cudaStream_t side = nullptr;          // second stream of the factorisation (trailing update beside the next panel)
+    cudaEvent_t ev_strip = nullptr, ev_rest = nullptr;
     bool fast_arith = true;   // gpf_gp_set_arith: contracted exp / sqrt in the mean kernel (1e-12; the GP tolerance is 1e-9)
     GpKern kp;
     // carved from the caller's workspace

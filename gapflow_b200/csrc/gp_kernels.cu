@@ -238,21 +238,17 @@ __global__ void __launch_bounds__(128) gp_panel_kernel(double* A, int Mp, int k,
 }
 
 // ------------------------------------------------------------------------------------
-// Cholesky step k, part 3: trailing update  A[i,j] -= A[i,k] A[j,k]^T  for k < j <= i.
-// One CTA per lower block pair (linear index -> (i, j)).
+// Cholesky step k, part 3: update of the rest of the OUTER panel  A[i,j] -= A[i,k] A[j,k]^T  for the block columns
+// k < j < jend of the 256-wide outer panel and block rows i >= j (2D grid: i = k + 1 + x, j = k + 1 + y).  Everything
+// right of the outer panel is updated once per outer panel by the GEMM engine (GEMM_SYRK, k-depth 256).
 // ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) gp_syrk_kernel(double* A, int Mp, int k) {
     extern __shared__ double sm[];
     double* As = sm;
     double* Bs = sm + NB * LDT;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, wm = w >> 1, wn = w & 1;
-    // pair index p -> (ii, jj), jj <= ii, in the trailing matrix
-    const int p = blockIdx.x;
-    int ii = (int)((sqrt(8.0 * p + 1.0) - 1.0) * 0.5);
-    while ((ii + 1) * (ii + 2) / 2 <= p) ++ii;
-    while (ii * (ii + 1) / 2 > p) --ii;
-    const int jj = p - ii * (ii + 1) / 2;
-    const int i = k + 1 + ii, j = k + 1 + jj;
+    const int i = k + 1 + blockIdx.x, j = k + 1 + blockIdx.y;
+    if (j > i) return;
     const double* Aik = A + (size_t)i * NB * Mp + (size_t)k * NB;
     const double* Ajk = A + (size_t)j * NB * Mp + (size_t)k * NB;
     for (int e = tid; e < NB * NB; e += 128) {
@@ -684,8 +680,9 @@ __device__ __forceinline__ void load_tile_t(double* dst, const double* src, int 
 //   GEMM_TRTRI_T   T = L21 X11        one level of the recursive inverse, first product   (NN)  -> T
 //   GEMM_TRTRI_X   X21 = -X22 T       second product                                      (NN)  -> X
 //   GEMM_LAUUM     Kinv = X^T X       lower triangle                                      (TN)  -> Kinv
+//   GEMM_SYRK      A22 -= A21 A21^T   trailing update of the blocked Cholesky, k-depth = the 256-wide outer panel (NT)
 // ------------------------------------------------------------------------------------
-enum { GEMM_TRTRI_T = 0, GEMM_TRTRI_X = 1, GEMM_LAUUM = 2 };
+enum { GEMM_TRTRI_T = 0, GEMM_TRTRI_X = 1, GEMM_LAUUM = 2, GEMM_SYRK = 3 };
 constexpr int GK = 16;                                   // k-depth of a pipeline slice
 constexpr int GST = 3;
 constexpr int G_LDA = GK + 4, G_LDAT = NB + 4, G_LDB = NQ + 4, G_LDBT = GK + 4;
@@ -700,6 +697,8 @@ struct GemmJob {
     const double* L;     // TRTRI_T: the Cholesky factor
     double* X;           // the inverse under construction (TRTRI), its input (LAUUM)
     double* T;           // TRTRI: scratch with the layout of X;  LAUUM: Kinv
+    int kb0, kb1;        // SYRK: the outer panel's block columns [kb0, kb1) (the k range); rows and columns from block kb1
+    int ct0;             // SYRK: first 128-column tile (relative to block kb1) of this launch
 };
 
 template <bool AT, bool BT>
@@ -713,8 +712,16 @@ __global__ void __launch_bounds__(256, 2) gp_gemm_kernel(const GemmJob J) {
     int m0, n0, k0, k1;
     const double *A, *B;
     double* C;
-    bool negate = false;
-    if (J.mode == GEMM_LAUUM) {
+    bool negate = false, subtract = false;
+    if (J.mode == GEMM_SYRK) {
+        // A[m, n] -= sum_{k in panel} A[m, k] A[n, k]: lower triangle of the trailing matrix (tiles that straddle the
+        // diagonal also touch entries above it, which nothing reads)
+        m0 = (J.kb1 + blockIdx.x) * NB; n0 = J.kb1 * NB + (J.ct0 + blockIdx.y) * NQ;
+        if (n0 > m0 + NB - 1 || n0 >= J.Mp) return;
+        k0 = J.kb0 * NB; k1 = J.kb1 * NB;
+        A = J.X; B = J.X; C = J.X;
+        subtract = true;
+    } else if (J.mode == GEMM_LAUUM) {
         // Kinv[m, n] = sum_{k >= m} X[k, m] X[k, n] for n0 <= m0 + 63 (X is lower triangular: X[k, .] = 0 left of k)
         m0 = blockIdx.x * NB; n0 = blockIdx.y * NQ;
         if (n0 > m0 + NB - 1) return;
@@ -782,7 +789,9 @@ __global__ void __launch_bounds__(256, 2) gp_gemm_kernel(const GemmJob J) {
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) {
             const int m = m0 + wm * 32 + mi * 8 + r, n = n0 + wn * 32 + ni * 8 + c * 2;
-            *reinterpret_cast<double2*>(C + (size_t)m * ld + n) = make_double2(sgn * acc[mi][ni][0], sgn * acc[mi][ni][1]);
+            double2* dst = reinterpret_cast<double2*>(C + (size_t)m * ld + n);
+            if (subtract) { const double2 o = *dst; *dst = make_double2(o.x - acc[mi][ni][0], o.y - acc[mi][ni][1]); }
+            else *dst = make_double2(sgn * acc[mi][ni][0], sgn * acc[mi][ni][1]);
         }
 }
 
@@ -953,6 +962,7 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
         GPF_CUDA(cudaFuncSetAttribute(gp_trtri_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm3));
         GPF_CUDA(cudaFuncSetAttribute(gp_gemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
         GPF_CUDA(cudaFuncSetAttribute(gp_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
+        GPF_CUDA(cudaFuncSetAttribute(gp_gemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
     }
     if (bytes < workspace_bytes(Mmax, D, nout, nslots)) { set_error("GP workspace too small"); return GPF_E_INVALID; }
     const size_t Mpm = pad_m(Mmax);
@@ -1004,16 +1014,51 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
     const int nb = Mp / NB;
     const size_t sm2 = (size_t)2 * NB * LDT * 8;
     const size_t smp = (size_t)2 * NB * (NB + 1) * 8;
-    for (int k = 0; k < nb; ++k) {
-        gp_potrf_diag_kernel<<<1, 256, smp, s>>>(L, Mp, k, Dinv, info);
+    // Blocked right-looking Cholesky with a 256-wide outer panel (4 blocks of 64).  Inside the panel: diagonal block,
+    // panel solve over all rows below, update of the panel's remaining columns.  Everything right of the panel is
+    // updated once per panel by the GEMM engine with k-depth 256 -- first the strip that the NEXT panel consists of
+    // (on the caller's stream, which then factors that panel), the rest concurrently on a second stream: the serial
+    // chain of small kernels (diagonal blocks: 6 ms per factorisation) runs under the large update, not after it.
+    constexpr int KO = 4;
+    if (!side) {
+        GPF_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+        GPF_CUDA(cudaEventCreateWithFlags(&ev_strip, cudaEventDisableTiming));
+        GPF_CUDA(cudaEventCreateWithFlags(&ev_rest, cudaEventDisableTiming));
+    }
+    bool rest_pending = false;
+    for (int K0 = 0; K0 < nb; K0 += KO) {
+        const int kend = std::min(K0 + KO, nb);
+        for (int k = K0; k < kend; ++k) {
+            gp_potrf_diag_kernel<<<1, 256, smp, s>>>(L, Mp, k, Dinv, info);
+            g_launches++;
+            const int rem = nb - 1 - k;
+            if (rem > 0) {
+                gp_panel_kernel<<<rem, 128, sm2, s>>>(L, Mp, k, Dinv);
+                g_launches++;
+                const int ncol = kend - 1 - k;
+                if (ncol > 0) { gp_syrk_kernel<<<dim3(rem, ncol), 128, sm2, s>>>(L, Mp, k); g_launches++; }
+            }
+        }
+        if (kend >= nb) break;
+        // trailing update with this panel: rows and columns from block kend on
+        if (rest_pending) { GPF_CUDA(cudaStreamWaitEvent(s, ev_rest, 0)); rest_pending = false; }   // columns it is about to change
+        GemmJob J;
+        J.mode = GEMM_SYRK; J.Mp = Mp; J.h = 0; J.L = L; J.X = L; J.T = L; J.kb0 = K0; J.kb1 = kend;
+        const int rows = nb - kend, ctiles = (rows + 1) / 2, strip = std::min(KO / 2, ctiles);
+        if (ctiles > strip) GPF_CUDA(cudaEventRecord(ev_strip, s));    // the panel is final: the side stream may read it
+        J.ct0 = 0;
+        gp_gemm_kernel<false, true><<<dim3(rows, strip), 256, GEMM_SMEM, s>>>(J);
         g_launches++;
-        const int rem = nb - 1 - k;
-        if (rem > 0) {
-            gp_panel_kernel<<<rem, 128, sm2, s>>>(L, Mp, k, Dinv);
-            gp_syrk_kernel<<<rem * (rem + 1) / 2, 128, sm2, s>>>(L, Mp, k);
-            g_launches += 2;
+        if (ctiles > strip) {
+            GPF_CUDA(cudaStreamWaitEvent(side, ev_strip, 0));
+            J.ct0 = strip;
+            gp_gemm_kernel<false, true><<<dim3(rows, ctiles - strip), 256, GEMM_SMEM, side>>>(J);
+            g_launches++;
+            GPF_CUDA(cudaEventRecord(ev_rest, side));
+            rest_pending = true;
         }
     }
+    if (rest_pending) GPF_CUDA(cudaStreamWaitEvent(s, ev_rest, 0));
     // alpha: the right-hand sides are in `alpha`; the variance kernel's scratch serves as the z vector
     double* zvec = scratch;
     for (int k = 0; k < nb; ++k) { gp_trsv_fwd_kernel<<<nb - k, 256, 0, s>>>(L, Mp, k, Dinv, alpha, zvec, nout); g_launches++; }
