@@ -154,47 +154,92 @@ __global__ void gp_build_K_kernel(const double* Xs, int M, int Mp, int D, double
 // Cholesky step k, part 1: factor the diagonal block in shared memory, write L_kk back
 // and inv(L_kk) to Dinv[k].  One CTA of 256 threads.  info != 0: not positive definite.
 // ------------------------------------------------------------------------------------
+constexpr size_t POTRF_SMEM = (size_t)(2 * NB * (NB + 1) + 3 * NB) * 8;     // L_kk, its inverse, two pivot columns, 1 / diagonal
+
+// 1 / sqrt(d) to full precision: hardware seed (2^-22) and two Newton steps
+__device__ __forceinline__ double rsqrt_full(double d) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    double e = fma(-d * y, y, 1.0);
+    y = fma(y * e, fma(e, 0.375, 0.5), y);         // y (1 + e/2 + 3 e^2/8)
+    e = fma(-d * y, y, 1.0);
+    return fma(y * e, 0.5, y);
+}
+
 __global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, int k, double* Dinv, int* info) {
     extern __shared__ double potrf_sm[];
-    double (*S)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);                  // working copy, then inv(L_kk)
+    double (*X)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);                   // inv(L_kk)
     double (*Lm)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm + NB * (NB + 1));  // L_kk
+    double* colbuf = potrf_sm + 2 * NB * (NB + 1);                                          // [2][NB] the pivot column, raw
+    double* rdiag = colbuf + 2 * NB;                                                        // 1 / L_jj
     const int tid = threadIdx.x;
     double* Akk = A + (size_t)k * NB * Mp + (size_t)k * NB;
-    for (int e = tid; e < NB * NB; e += 256) S[e / NB][e % NB] = Akk[(size_t)(e / NB) * Mp + e % NB];
-    __syncthreads();
-    // right-looking, one barrier per column: every thread forms 1 / sqrt(d_jj) itself and scales the two column
-    // entries of its update on the fly (column j of S is never written by the update of step j), the scaled column
-    // goes to Lm.  16 x 16 threads sweep the trailing triangle only.  (r2a: the version with three barriers per
-    // column and a one-thread-per-column inverse took 92 us per block, 14 of the 41 ms of a factorisation.)
+    // The block lives in registers: thread (ty, tx) of 16 x 16 owns the cells (ty + 16 p, tx + 16 q).  Per column one
+    // barrier: the owners of the next pivot column publish it (raw) in shared memory, every thread forms 1 / sqrt(d_jj)
+    // itself and updates its 16 cells with 16 independent multiply-adds.  (The version that kept the block in shared
+    // memory spent 69 us per block, 11 ms per factorisation at M = 10^4 -- the serial chain of the whole Cholesky.)
     const int ty = tid >> 4, tx = tid & 15;
+    double a[4][4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) a[p][q] = Akk[(size_t)(ty + 16 * p) * Mp + tx + 16 * q];
+    if (tx == 0) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) colbuf[ty + 16 * p] = a[p][0];
+    }
+    __syncthreads();
     for (int j = 0; j < NB; ++j) {
-        const double d = S[j][j];
+        const double* cb = colbuf + (j & 1) * NB;
+        const double d = cb[j];
         if (tid == 0 && !(d > 0.0)) atomicExch(info, k * NB + j + 1);
-        const double djj = sqrt(d), inv = 1.0 / djj;
-        if (tid >= j && tid < NB) Lm[tid][j] = (tid == j) ? djj : S[tid][j] * inv;
-        if (tid < j) Lm[tid][j] = 0.0;
-        for (int i = j + 1 + ty; i < NB; i += 16) {
-            const double lij = S[i][j] * inv;
-            for (int c = j + 1 + tx; c <= i; c += 16) S[i][c] -= lij * (S[c][j] * inv);
+        const double inv = rsqrt_full(d);
+        double lr[4], lc[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) { lr[p] = cb[ty + 16 * p] * inv; lc[p] = cb[tx + 16 * p] * inv; }
+        if (tx == (j & 15)) {                       // owners of column j: the finished column of L
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const int i = ty + 16 * p;
+                Lm[i][j] = i > j ? lr[p] : (i == j ? d * inv : 0.0);
+            }
+            if (ty == 0) rdiag[j] = inv;
+        }
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (ty + 16 * p > j && tx + 16 * q > j) a[p][q] = fma(-lr[p], lc[q], a[p][q]);
+        if (j + 1 < NB && tx == ((j + 1) & 15)) {   // publish the next pivot column
+            double* nb_ = colbuf + ((j + 1) & 1) * NB;
+            const int q1 = (j + 1) >> 4;
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+                nb_[ty + 16 * p] = q1 == 0 ? a[p][0] : (q1 == 1 ? a[p][1] : (q1 == 2 ? a[p][2] : a[p][3]));
         }
         __syncthreads();
     }
-    // X = inv(L_kk) into S, four threads per column: X_cc = 1 / L_cc, X_ic = -(sum_{j=c}^{i-1} L_ij X_jc) / L_ii with
+    // X = inv(L_kk), four threads per column: X_cc = 1 / L_cc, X_ic = -(sum_{j=c}^{i-1} L_ij X_jc) / L_ii with
     // the sum split over the four threads (j = c + p, c + p + 4, ...) and folded by two shuffles; the four threads
     // of a column sit in one warp, rows advance in lock step
     {
         const int c = tid >> 2, p = tid & 3;
         const int c_first = (tid >> 5) * 8;               // first of the warp's 8 columns: the warp walks rows c_first + 1 ..
-        for (int i = 0; i < c; ++i) if (p == 0) S[i][c] = 0.0;
-        if (p == 0) S[c][c] = 1.0 / Lm[c][c];
+        for (int i = 0; i < c; ++i) if (p == 0) X[i][c] = 0.0;
+        if (p == 0) X[c][c] = rdiag[c];
         __syncwarp();
         for (int i = c_first + 1; i < NB; ++i) {          // warp-uniform trip count (full-mask shuffles)
             const bool act = i > c;
-            double s = 0.0;
-            if (act) for (int j = c + p; j < i; j += 4) s += Lm[i][j] * S[j][c];
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            if (act && p == 0) S[i][c] = -s / Lm[i][i];
+            double s0 = 0.0, s1 = 0.0;
+            if (act) {
+                int j = c + p;
+                for (; j + 4 < i; j += 8) { s0 = fma(Lm[i][j], X[j][c], s0); s1 = fma(Lm[i][j + 4], X[j + 4][c], s1); }
+                if (j < i) s0 = fma(Lm[i][j], X[j][c], s0);
+            }
+            double sum = s0 + s1;
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            if (act && p == 0) X[i][c] = -sum * rdiag[i];
             __syncwarp();
         }
     }
@@ -203,7 +248,7 @@ __global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, i
     for (int e = tid; e < NB * NB; e += 256) {
         const int i = e / NB, c = e % NB;
         Akk[(size_t)i * Mp + c] = Lm[i][c];
-        Dk[e] = S[i][c];
+        Dk[e] = X[i][c];
     }
 }
 
@@ -955,7 +1000,7 @@ int GpModel::init(int Mmax_, int D_, int nout_, void* ws, size_t bytes) {
         // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: set it for the device
         // of every model (cheap), not once per process
         const int sm2 = (int)((size_t)2 * NB * LDT * 8), sm3 = (int)((size_t)3 * NB * LDT * 8);
-        GPF_CUDA(cudaFuncSetAttribute(gp_potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)2 * NB * (NB + 1) * 8)));
+        GPF_CUDA(cudaFuncSetAttribute(gp_potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)POTRF_SMEM));
         GPF_CUDA(cudaFuncSetAttribute(gp_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
         GPF_CUDA(cudaFuncSetAttribute(gp_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm2));
         GPF_CUDA(cudaFuncSetAttribute(gp_var_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)VAR_SMEM));
@@ -1013,7 +1058,7 @@ int GpModel::factor(const double* Xtrain, int M_, double log_amp, const double* 
     g_launches++;
     const int nb = Mp / NB;
     const size_t sm2 = (size_t)2 * NB * LDT * 8;
-    const size_t smp = (size_t)2 * NB * (NB + 1) * 8;
+    const size_t smp = POTRF_SMEM;
     // Blocked right-looking Cholesky with a 256-wide outer panel (4 blocks of 64).  Inside the panel: diagonal block,
     // panel solve over all rows below, update of the panel's remaining columns.  Everything right of the panel is
     // updated once per panel by the GEMM engine with k-depth 256 -- first the strip that the NEXT panel consists of
