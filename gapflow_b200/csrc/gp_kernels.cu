@@ -154,7 +154,7 @@ __global__ void gp_build_K_kernel(const double* Xs, int M, int Mp, int D, double
 // Cholesky step k, part 1: factor the diagonal block in shared memory, write L_kk back
 // and inv(L_kk) to Dinv[k].  One CTA of 256 threads.  info != 0: not positive definite.
 // ------------------------------------------------------------------------------------
-constexpr size_t POTRF_SMEM = (size_t)(2 * NB * (NB + 1) + 3 * NB) * 8;     // L_kk, its inverse, two pivot columns, 1 / diagonal
+constexpr size_t POTRF_SMEM = (size_t)(2 * NB * (NB + 1) + 4 * NB) * 8;     // L_kk, its inverse, two pivot columns, two pivot rows
 
 // 1 / sqrt(d) to full precision: hardware seed (2^-22) and two Newton steps
 __device__ __forceinline__ double rsqrt_full(double d) {
@@ -170,80 +170,80 @@ __global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, i
     extern __shared__ double potrf_sm[];
     double (*X)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);                   // inv(L_kk)
     double (*Lm)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm + NB * (NB + 1));  // L_kk
-    double* colbuf = potrf_sm + 2 * NB * (NB + 1);                                          // [2][NB] the pivot column, raw
-    double* rdiag = colbuf + 2 * NB;                                                        // 1 / L_jj
+    double* colbuf = potrf_sm + 2 * NB * (NB + 1);                                          // [2][NB] the pivot column of A, raw
+    double* rowbuf = colbuf + 2 * NB;                                                       // [2][NB] the pivot row of B, raw
     const int tid = threadIdx.x;
     double* Akk = A + (size_t)k * NB * Mp + (size_t)k * NB;
-    // The block lives in registers: thread (ty, tx) of 16 x 16 owns the cells (ty + 16 p, tx + 16 q).  Per column one
-    // barrier: the owners of the next pivot column publish it (raw) in shared memory, every thread forms 1 / sqrt(d_jj)
-    // itself and updates its 16 cells with 16 independent multiply-adds.  (The version that kept the block in shared
-    // memory spent 69 us per block, 11 ms per factorisation at M = 10^4 -- the serial chain of the whole Cholesky.)
+    // Factor and invert in one sweep, both blocks in registers: thread (ty, tx) of 16 x 16 owns the cells
+    // (ty + 16 p, tx + 16 q) of the working copy a of A_kk and of b, which starts as the identity and carries the
+    // forward substitution L X = I along (row j of X is row j of b over L_jj once the columns before j are eliminated).
+    // Per column ONE barrier: the owners of the next pivot column of a and pivot row of b publish them (raw) in shared
+    // memory, every thread forms 1 / sqrt(d_jj) itself and updates its 32 cells with independent multiply-adds.
+    // (With the block in shared memory, three barriers per column and a separate inverse: 69 us per block, 11 ms per
+    // factorisation at M = 10^4 -- the serial chain that the trailing updates cannot hide.)
     const int ty = tid >> 4, tx = tid & 15;
-    double a[4][4];
+    double a[4][4], b[4][4];
 #pragma unroll
     for (int p = 0; p < 4; ++p)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) a[p][q] = Akk[(size_t)(ty + 16 * p) * Mp + tx + 16 * q];
+        for (int q = 0; q < 4; ++q) {
+            a[p][q] = Akk[(size_t)(ty + 16 * p) * Mp + tx + 16 * q];
+            b[p][q] = (ty + 16 * p == tx + 16 * q) ? 1.0 : 0.0;
+        }
     if (tx == 0) {
 #pragma unroll
         for (int p = 0; p < 4; ++p) colbuf[ty + 16 * p] = a[p][0];
     }
+    if (ty == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) rowbuf[tx + 16 * q] = b[0][q];
+    }
     __syncthreads();
     for (int j = 0; j < NB; ++j) {
         const double* cb = colbuf + (j & 1) * NB;
+        const double* rb = rowbuf + (j & 1) * NB;
         const double d = cb[j];
         if (tid == 0 && !(d > 0.0)) atomicExch(info, k * NB + j + 1);
         const double inv = rsqrt_full(d);
-        double lr[4], lc[4];
+        double lr[4], lc[4], xr[4];
 #pragma unroll
-        for (int p = 0; p < 4; ++p) { lr[p] = cb[ty + 16 * p] * inv; lc[p] = cb[tx + 16 * p] * inv; }
+        for (int p = 0; p < 4; ++p) { lr[p] = cb[ty + 16 * p] * inv; lc[p] = cb[tx + 16 * p] * inv; xr[p] = rb[tx + 16 * p] * inv; }
         if (tx == (j & 15)) {                       // owners of column j: the finished column of L
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
                 const int i = ty + 16 * p;
                 Lm[i][j] = i > j ? lr[p] : (i == j ? d * inv : 0.0);
             }
-            if (ty == 0) rdiag[j] = inv;
+        }
+        if (ty == (j & 15)) {                       // owners of row j: the finished row of the inverse
+#pragma unroll
+            for (int q = 0; q < 4; ++q) X[j][tx + 16 * q] = xr[q];
         }
 #pragma unroll
         for (int p = 0; p < 4; ++p)
 #pragma unroll
             for (int q = 0; q < 4; ++q)
-                if (ty + 16 * p > j && tx + 16 * q > j) a[p][q] = fma(-lr[p], lc[q], a[p][q]);
-        if (j + 1 < NB && tx == ((j + 1) & 15)) {   // publish the next pivot column
-            double* nb_ = colbuf + ((j + 1) & 1) * NB;
+                if (ty + 16 * p > j) {
+                    if (tx + 16 * q > j) a[p][q] = fma(-lr[p], lc[q], a[p][q]);
+                    b[p][q] = fma(-lr[p], xr[q], b[p][q]);
+                }
+        if (j + 1 < NB) {                           // publish the next pivot column of a and pivot row of b
             const int q1 = (j + 1) >> 4;
+            double* nc = colbuf + ((j + 1) & 1) * NB;
+            double* nr = rowbuf + ((j + 1) & 1) * NB;
+            if (tx == ((j + 1) & 15)) {
 #pragma unroll
-            for (int p = 0; p < 4; ++p)
-                nb_[ty + 16 * p] = q1 == 0 ? a[p][0] : (q1 == 1 ? a[p][1] : (q1 == 2 ? a[p][2] : a[p][3]));
+                for (int p = 0; p < 4; ++p)
+                    nc[ty + 16 * p] = q1 == 0 ? a[p][0] : (q1 == 1 ? a[p][1] : (q1 == 2 ? a[p][2] : a[p][3]));
+            }
+            if (ty == ((j + 1) & 15)) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    nr[tx + 16 * q] = q1 == 0 ? b[0][q] : (q1 == 1 ? b[1][q] : (q1 == 2 ? b[2][q] : b[3][q]));
+            }
         }
         __syncthreads();
     }
-    // X = inv(L_kk), four threads per column: X_cc = 1 / L_cc, X_ic = -(sum_{j=c}^{i-1} L_ij X_jc) / L_ii with
-    // the sum split over the four threads (j = c + p, c + p + 4, ...) and folded by two shuffles; the four threads
-    // of a column sit in one warp, rows advance in lock step
-    {
-        const int c = tid >> 2, p = tid & 3;
-        const int c_first = (tid >> 5) * 8;               // first of the warp's 8 columns: the warp walks rows c_first + 1 ..
-        for (int i = 0; i < c; ++i) if (p == 0) X[i][c] = 0.0;
-        if (p == 0) X[c][c] = rdiag[c];
-        __syncwarp();
-        for (int i = c_first + 1; i < NB; ++i) {          // warp-uniform trip count (full-mask shuffles)
-            const bool act = i > c;
-            double s0 = 0.0, s1 = 0.0;
-            if (act) {
-                int j = c + p;
-                for (; j + 4 < i; j += 8) { s0 = fma(Lm[i][j], X[j][c], s0); s1 = fma(Lm[i][j + 4], X[j + 4][c], s1); }
-                if (j < i) s0 = fma(Lm[i][j], X[j][c], s0);
-            }
-            double sum = s0 + s1;
-            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-            if (act && p == 0) X[i][c] = -sum * rdiag[i];
-            __syncwarp();
-        }
-    }
-    __syncthreads();
     double* Dk = Dinv + (size_t)k * NB * NB;
     for (int e = tid; e < NB * NB; e += 256) {
         const int i = e / NB, c = e % NB;
