@@ -166,6 +166,72 @@ __device__ __forceinline__ double rsqrt_full(double d) {
     return fma(y * e, 0.5, y);
 }
 
+// Columns 16 Q1 .. 16 Q1 + 15 of the in-register factor-and-invert sweep (see gp_potrf_diag_kernel).  Q1 is a
+// template parameter so that every register index is static and the cells that cannot change any more (block rows
+// above Q1; block columns of a left of Q1, of b right of Q1) drop out of the code: only the 16-wide band that
+// contains the pivot needs a run-time comparison.
+template <int Q1>
+__device__ __forceinline__ void potrf_phase(double (&a)[4][4], double (&b)[4][4], double (*Lm)[NB + 1], double (*X)[NB + 1],
+                                            double* colbuf, double* rowbuf, int ty, int tx, int k, int* info) {
+    for (int jt = 0; jt < 16; ++jt) {
+        const int j = 16 * Q1 + jt;
+        const double* cb = colbuf + (j & 1) * NB;
+        const double* rb = rowbuf + (j & 1) * NB;
+        const double d = cb[j];
+        if (ty == 0 && tx == 0 && !(d > 0.0)) atomicExch(info, k * NB + j + 1);
+        const double inv = rsqrt_full(d);
+        double lr[4], lc[4], xr[4];
+#pragma unroll
+        for (int p = Q1; p < 4; ++p) { lr[p] = cb[ty + 16 * p] * inv; lc[p] = cb[tx + 16 * p] * inv; }
+#pragma unroll
+        for (int q = 0; q <= Q1; ++q) xr[q] = rb[tx + 16 * q] * inv;
+        if (tx == jt) {                             // owners of column j: the finished column of L (zeros above are preset)
+            if (ty >= jt) Lm[ty + 16 * Q1][j] = ty > jt ? lr[Q1] : d * inv;
+#pragma unroll
+            for (int p = Q1 + 1; p < 4; ++p) Lm[ty + 16 * p][j] = lr[p];
+        }
+        if (ty == jt) {                             // owners of row j: the finished row of the inverse
+#pragma unroll
+            for (int q = 0; q <= Q1; ++q) X[j][tx + 16 * q] = xr[q];
+        }
+        // rows below the pivot: a -= l_i l_c right of the pivot column, b -= l_i x_c (x_c = 0 right of the pivot)
+        const bool row_band = ty > jt, col_band = tx > jt;
+#pragma unroll
+        for (int p = Q1; p < 4; ++p) {
+            if (p == Q1 && !row_band) continue;
+            if (col_band) a[p][Q1] = fma(-lr[p], lc[Q1], a[p][Q1]);
+#pragma unroll
+            for (int q = Q1 + 1; q < 4; ++q) a[p][q] = fma(-lr[p], lc[q], a[p][q]);
+#pragma unroll
+            for (int q = 0; q <= Q1; ++q) b[p][q] = fma(-lr[p], xr[q], b[p][q]);
+        }
+        // publish the next pivot column of a and pivot row of b
+        double* nc = colbuf + ((j + 1) & 1) * NB;
+        double* nr = rowbuf + ((j + 1) & 1) * NB;
+        if (jt < 15) {
+            if (tx == jt + 1) {
+#pragma unroll
+                for (int p = Q1; p < 4; ++p) nc[ty + 16 * p] = a[p][Q1];
+            }
+            if (ty == jt + 1) {
+#pragma unroll
+                for (int q = 0; q <= Q1; ++q) nr[tx + 16 * q] = b[Q1][q];
+            }
+        } else if (Q1 < 3) {
+            constexpr int QN = Q1 < 3 ? Q1 + 1 : 3;
+            if (tx == 0) {
+#pragma unroll
+                for (int p = QN; p < 4; ++p) nc[ty + 16 * p] = a[p][QN];
+            }
+            if (ty == 0) {
+#pragma unroll
+                for (int q = 0; q <= QN; ++q) nr[tx + 16 * q] = b[QN][q];
+            }
+        }
+        __syncthreads();
+    }
+}
+
 __global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, int k, double* Dinv, int* info) {
     extern __shared__ double potrf_sm[];
     double (*X)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);                   // inv(L_kk)
@@ -178,7 +244,7 @@ __global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, i
     // (ty + 16 p, tx + 16 q) of the working copy a of A_kk and of b, which starts as the identity and carries the
     // forward substitution L X = I along (row j of X is row j of b over L_jj once the columns before j are eliminated).
     // Per column ONE barrier: the owners of the next pivot column of a and pivot row of b publish them (raw) in shared
-    // memory, every thread forms 1 / sqrt(d_jj) itself and updates its 32 cells with independent multiply-adds.
+    // memory, every thread forms 1 / sqrt(d_jj) itself and updates its cells with independent multiply-adds.
     // (With the block in shared memory, three barriers per column and a separate inverse: 69 us per block, 11 ms per
     // factorisation at M = 10^4 -- the serial chain that the trailing updates cannot hide.)
     const int ty = tid >> 4, tx = tid & 15;
@@ -190,60 +256,17 @@ __global__ void __launch_bounds__(256) gp_potrf_diag_kernel(double* A, int Mp, i
             a[p][q] = Akk[(size_t)(ty + 16 * p) * Mp + tx + 16 * q];
             b[p][q] = (ty + 16 * p == tx + 16 * q) ? 1.0 : 0.0;
         }
+    for (int e = tid; e < 2 * NB * (NB + 1); e += 256) potrf_sm[e] = 0.0;     // X and Lm: the zero triangles
     if (tx == 0) {
 #pragma unroll
         for (int p = 0; p < 4; ++p) colbuf[ty + 16 * p] = a[p][0];
     }
-    if (ty == 0) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) rowbuf[tx + 16 * q] = b[0][q];
-    }
+    if (ty == 0) rowbuf[tx] = b[0][0];
     __syncthreads();
-    for (int j = 0; j < NB; ++j) {
-        const double* cb = colbuf + (j & 1) * NB;
-        const double* rb = rowbuf + (j & 1) * NB;
-        const double d = cb[j];
-        if (tid == 0 && !(d > 0.0)) atomicExch(info, k * NB + j + 1);
-        const double inv = rsqrt_full(d);
-        double lr[4], lc[4], xr[4];
-#pragma unroll
-        for (int p = 0; p < 4; ++p) { lr[p] = cb[ty + 16 * p] * inv; lc[p] = cb[tx + 16 * p] * inv; xr[p] = rb[tx + 16 * p] * inv; }
-        if (tx == (j & 15)) {                       // owners of column j: the finished column of L
-#pragma unroll
-            for (int p = 0; p < 4; ++p) {
-                const int i = ty + 16 * p;
-                Lm[i][j] = i > j ? lr[p] : (i == j ? d * inv : 0.0);
-            }
-        }
-        if (ty == (j & 15)) {                       // owners of row j: the finished row of the inverse
-#pragma unroll
-            for (int q = 0; q < 4; ++q) X[j][tx + 16 * q] = xr[q];
-        }
-#pragma unroll
-        for (int p = 0; p < 4; ++p)
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-                if (ty + 16 * p > j) {
-                    if (tx + 16 * q > j) a[p][q] = fma(-lr[p], lc[q], a[p][q]);
-                    b[p][q] = fma(-lr[p], xr[q], b[p][q]);
-                }
-        if (j + 1 < NB) {                           // publish the next pivot column of a and pivot row of b
-            const int q1 = (j + 1) >> 4;
-            double* nc = colbuf + ((j + 1) & 1) * NB;
-            double* nr = rowbuf + ((j + 1) & 1) * NB;
-            if (tx == ((j + 1) & 15)) {
-#pragma unroll
-                for (int p = 0; p < 4; ++p)
-                    nc[ty + 16 * p] = q1 == 0 ? a[p][0] : (q1 == 1 ? a[p][1] : (q1 == 2 ? a[p][2] : a[p][3]));
-            }
-            if (ty == ((j + 1) & 15)) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    nr[tx + 16 * q] = q1 == 0 ? b[0][q] : (q1 == 1 ? b[1][q] : (q1 == 2 ? b[2][q] : b[3][q]));
-            }
-        }
-        __syncthreads();
-    }
+    potrf_phase<0>(a, b, Lm, X, colbuf, rowbuf, ty, tx, k, info);
+    potrf_phase<1>(a, b, Lm, X, colbuf, rowbuf, ty, tx, k, info);
+    potrf_phase<2>(a, b, Lm, X, colbuf, rowbuf, ty, tx, k, info);
+    potrf_phase<3>(a, b, Lm, X, colbuf, rowbuf, ty, tx, k, info);
     double* Dk = Dinv + (size_t)k * NB * NB;
     for (int e = tid; e < NB * NB; e += 256) {
         const int i = e / NB, c = e % NB;

@@ -1,5 +1,5 @@
 """Short GP workload for ncu (BASELINE config 4 shapes): one factorisation at M = 10^4, the dense variance on
-one wave of query tiles (148 x 128 cells), the D = 3 two-output mean on 2^18 cells, one training objective.
+one wave of query tiles (296 x 128 cells), the D = 3 two-output mean on 2^18 cells, one training objective.
 Order of the kernels: build_K, (potrf_diag, panel, syrk) x 157, trsv x 314, mean, var, argmax, mean (2^18),
 trtri, lauum, grad, nlml_finish.   python tools/gp_profile.py [M]"""
 import os
@@ -19,7 +19,7 @@ ls = np.log(np.std(X, axis=0))
 g = GPModel(M, 3, 2)
 g.factor(X, Y, 0.0, ls, 4e-3)
 xt = torch.as_tensor(rng.uniform(X.min(0), X.max(0), (1 << 18, 3)), device='cuda')
-m, v = g.repredict_mean_var(xt[:148 * 128].contiguous(), 1.5e-8)
+m, v = g.repredict_mean_var(xt[:296 * 128].contiguous(), 1.5e-8)      # one full wave: 2 CTAs per SM x 148 SMs x 128 query cells
 mm = g.repredict_mean(xt)
 loss, grad = g.nlml()
 torch.cuda.synchronize()
