@@ -31,6 +31,7 @@ F_Q, F_TOPO, F_EXTRA = 0, 1, 2
 PART_ALL, PART_EDGE, PART_INTERIOR = 0, 1, 2
 IPC_HANDLE_BYTES = 64
 PEER_BLOB_BYTES = 96
+SLIP = {'top': 0, 'both': 1}
 PIEZO_IDS = {'Barus': 2, 'Roelands': 3, 'Dukler': 4, 'McAdams': 5}       # GPF_PIEZO_*; any other name: 1 (identity)
 PIEZO_KEYS = {'Barus': ['aB'], 'Roelands': ['mu_inf', 'p_ref', 'z'], 'Dukler': ['eta_v', 'rho_l', 'rho_v'],
               'McAdams': ['eta_v', 'rho_l', 'rho_v']}
@@ -112,6 +113,8 @@ SIGNATURES = {
     "gpf_stress_bottom": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
     "gpf_stress_top": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
     "gpf_stress_avg": (_i, [_cfgp, _dp, _dp, _dp, _dp, _sz, _vp]),
+    "gpf_stress_ex": (_i, [_cfgp, _i, _i, _dp, _dp, _dp, _dp, _dp, _dp, _sz, _vp]),
+    "gpf_selftest_stress_ex_host": (_i, [_cfgp, _i, _i, _dp, _dp, _dp, _dp, _dp, _dp, _sz]),
     "gpf_gp_workspace_bytes": (_i, [_i, _i, _i, C.POINTER(C.c_size_t)]),
     "gpf_gp_create": (_i, [_i, _i, _i, _vp, _sz, C.POINTER(_vp)]),
     "gpf_gp_destroy": (_i, [_vp]),

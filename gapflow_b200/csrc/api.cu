@@ -253,6 +253,21 @@ int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
     GPF_TRY NEED(cfg && (n == 0 || (q && h && out))) return launch_stress(*cfg, 2, q, h, Ls, out, n, (cudaStream_t)stream); GPF_CATCH
 }
 
+int gpf_stress_ex(const gpf_fv_cfg* cfg, int which, int slip, const double* q, const double* h, const double* Ls,
+                  const double* dqx, const double* dqy, double* out, size_t n, void* stream) {
+    GPF_TRY NEED(cfg && (n == 0 || (q && h && out)))
+    if (slip != GPF_SLIP_TOP && slip != GPF_SLIP_BOTH) { set_error("slip: GPF_SLIP_TOP or GPF_SLIP_BOTH"); return GPF_E_INVALID; }
+    return launch_stress_ex(*cfg, which, slip == GPF_SLIP_BOTH, q, h, Ls, dqx, dqy, out, n, (cudaStream_t)stream);
+    GPF_CATCH
+}
+int gpf_selftest_stress_ex_host(const gpf_fv_cfg* cfg, int which, int slip, const double* q, const double* h, const double* Ls,
+                                const double* dqx, const double* dqy, double* out, size_t n) {
+    GPF_TRY NEED(cfg && (n == 0 || (q && h && out)))
+    if (slip != GPF_SLIP_TOP && slip != GPF_SLIP_BOTH) { set_error("slip: GPF_SLIP_TOP or GPF_SLIP_BOTH"); return GPF_E_INVALID; }
+    return stress_ex_host(*cfg, which, slip == GPF_SLIP_BOTH, q, h, Ls, dqx, dqy, out, n);
+    GPF_CATCH
+}
+
 int gpf_gp_workspace_bytes(int M_max, int D, int n_out, size_t* bytes) {
     GPF_TRY
     if (!bytes || M_max < 1 || D < 1 || D > 8 || n_out < 1 || n_out > 2) { set_error("bad GP dimensions (D <= 8, n_out <= 2)"); return GPF_E_INVALID; }

@@ -141,6 +141,11 @@ int launch_eos(const gpf_fv_cfg& c, const double* dens, double* out, size_t n, b
 int launch_stress(const gpf_fv_cfg& c, int which, const double* q, const double* h, const double* Ls,
                   double* out, size_t n, cudaStream_t s);
 
+int launch_stress_ex(const gpf_fv_cfg& c, int which, int slip_both, const double* q, const double* h, const double* Ls,
+                     const double* dqx, const double* dqy, double* out, size_t n, cudaStream_t s);
+int stress_ex_host(const gpf_fv_cfg& c, int which, int slip_both, const double* q, const double* h, const double* Ls,
+                   const double* dqx, const double* dqy, double* out, size_t n);
+
 int launch_selftest_div(unsigned long long n, unsigned long long seed, unsigned long long* out_host, cudaStream_t s);
 
 }  // namespace gpf

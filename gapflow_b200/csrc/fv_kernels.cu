@@ -8,6 +8,7 @@
 #include "fv_pass.cuh"
 #include "fv_host.h"
 #include "slab_comm.cuh"
+#include "closures_slip_gen.cuh"
 
 namespace gpf {
 
@@ -547,6 +548,28 @@ __global__ void stress_kernel(ViscParams vp, int which, const double* q, const d
         stress_avg<LS>(c, V, t0, t1, t2);
         out[i] = t0; out[n + i] = t1; out[2 * n + i] = t2;
     }
+}
+
+// general form of the same three functions: slip at the top wall or at both walls, in-plane gradients of
+// (rho, jx, jy) given (viscous.py:37-786 with dqx, dqy, slip).  Closed forms derived in tools/derive_slip_closures.py.
+__host__ __device__ inline void stress_ex_cell(int which, int both, const SlipIn& in, double* out) {
+    if (both) { if (which == 0) slip_both_bottom(in, out); else if (which == 1) slip_both_top(in, out); else slip_both_avg(in, out); }
+    else { if (which == 0) slip_top_bottom(in, out); else if (which == 1) slip_top_top(in, out); else slip_top_avg(in, out); }
+}
+__global__ void stress_ex_kernel(ViscParams vp, int which, int both, const double* q, const double* h, const double* Ls,
+                                 const double* dqx, const double* dqy, double* out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    SlipIn in;
+    in.h = h[i]; in.hx = h[n + i]; in.hy = h[2 * n + i]; in.Ls = Ls ? Ls[i] : 0.0;
+    in.U = vp.U; in.V = vp.V; in.eta = vp.eta; in.zeta = vp.zeta;
+    in.q0 = q[i]; in.q1 = q[n + i]; in.q2 = q[2 * n + i];
+    in.dx0 = dqx ? dqx[i] : 0.0; in.dx1 = dqx ? dqx[n + i] : 0.0; in.dx2 = dqx ? dqx[2 * n + i] : 0.0;
+    in.dy0 = dqy ? dqy[i] : 0.0; in.dy1 = dqy ? dqy[n + i] : 0.0; in.dy2 = dqy ? dqy[2 * n + i] : 0.0;
+    double o[6];
+    stress_ex_cell(which, both, in, o);
+    const int nc = which == 2 ? 3 : 6;
+    for (int k = 0; k < nc; ++k) out[k * n + i] = o[k];
 }
 
 // =====================================================================================
@@ -1892,6 +1915,38 @@ int launch_stress(const gpf_fv_cfg& c, int which, const double* q, const double*
     return GPF_OK;
 }
 
+
+int launch_stress_ex(const gpf_fv_cfg& c, int which, int slip_both, const double* q, const double* h, const double* Ls,
+                     const double* dqx, const double* dqy, double* out, size_t n, cudaStream_t s) {
+    if (which < 0 || which > 2) { set_error("which: 0 stress_bottom, 1 stress_top, 2 stress_avg"); return GPF_E_INVALID; }
+    if (n == 0) return GPF_OK;
+    ViscParams vp;
+    vp.U = c.U; vp.V = c.V; vp.eta = c.eta; vp.zeta = c.zeta;
+    vp.v1 = vp.v2 = vp.two_eta = vp.two_v2 = 0.0;
+    stress_ex_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(vp, which, slip_both ? 1 : 0, q, h, Ls, dqx, dqy, out, n);
+    g_launches++;
+    GPF_CUDA(cudaGetLastError());
+    return GPF_OK;
+}
+
+// the same routine on the host (CPU tests of the derived closed forms against the golden vectors)
+int stress_ex_host(const gpf_fv_cfg& c, int which, int slip_both, const double* q, const double* h, const double* Ls,
+                   const double* dqx, const double* dqy, double* out, size_t n) {
+    if (which < 0 || which > 2) { set_error("which: 0 stress_bottom, 1 stress_top, 2 stress_avg"); return GPF_E_INVALID; }
+    const int nc = which == 2 ? 3 : 6;
+    for (size_t i = 0; i < n; ++i) {
+        SlipIn in;
+        in.h = h[i]; in.hx = h[n + i]; in.hy = h[2 * n + i]; in.Ls = Ls ? Ls[i] : 0.0;
+        in.U = c.U; in.V = c.V; in.eta = c.eta; in.zeta = c.zeta;
+        in.q0 = q[i]; in.q1 = q[n + i]; in.q2 = q[2 * n + i];
+        in.dx0 = dqx ? dqx[i] : 0.0; in.dx1 = dqx ? dqx[n + i] : 0.0; in.dx2 = dqx ? dqx[2 * n + i] : 0.0;
+        in.dy0 = dqy ? dqy[i] : 0.0; in.dy1 = dqy ? dqy[n + i] : 0.0; in.dy2 = dqy ? dqy[2 * n + i] : 0.0;
+        double o[6];
+        stress_ex_cell(which, slip_both, in, o);
+        for (int k = 0; k < nc; ++k) out[k * n + i] = o[k];
+    }
+    return GPF_OK;
+}
 
 // ---- self-test of the branch-free reciprocal / quotient against the IEEE operations -------
 __global__ void selftest_div_kernel(unsigned long long n, unsigned long long seed, unsigned long long* out) {

@@ -202,8 +202,13 @@ def eos_sound_velocity(density, prop):
     return out
 
 
-def _stress(name, ncomp, q, h, U, V, eta, zeta, Ls):
+def _stress(name, ncomp, q, h, U, V, eta, zeta, Ls, dqx=None, dqy=None, slip="top"):
+    """stress_bottom / stress_top / stress_avg(q, h, U, V, eta, zeta, Ls, dqx=None, dqy=None, slip="top") of
+    GaPFlow/models/viscous.py:37, 281, 612 on CUDA float64 tensors.  The driver's call (slip="top", no gradients)
+    takes the bit-exact kernels; gradients or slip="both" the derived closed forms (gpf_stress_ex, <= 1e-12)."""
     lib = _capi.load()
+    if slip not in _capi.SLIP:
+        raise ValueError("slip must be 'top' or 'both'")       # viscous.py has no other branch
     cfg = _pure_cfg(dict(EOS='DH', rho0=1., P0=0., C1=1., C2=2., shear=eta, bulk=zeta), dict(U=U, V=V))
     q = q.contiguous()
     h = h[:3].contiguous()
@@ -211,21 +216,30 @@ def _stress(name, ncomp, q, h, U, V, eta, zeta, Ls):
     out = torch.empty((ncomp, *q.shape[1:]), dtype=torch.float64, device=q.device)
     lsp = C.c_void_p(0)
     if Ls is not None:
-        Ls = torch.broadcast_to(Ls, q.shape[1:]).contiguous()
+        Ls = torch.broadcast_to(torch.as_tensor(Ls, dtype=torch.float64, device=q.device), q.shape[1:]).contiguous()
         lsp = C.c_void_p(Ls.data_ptr())
-    _capi.check(getattr(lib, name)(C.byref(cfg), C.c_void_p(q.data_ptr()), C.c_void_p(h.data_ptr()), lsp,
-                                   C.c_void_p(out.data_ptr()), n,
-                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if dqx is None and dqy is None and slip == "top":
+        _capi.check(getattr(lib, name)(C.byref(cfg), C.c_void_p(q.data_ptr()), C.c_void_p(h.data_ptr()), lsp,
+                                       C.c_void_p(out.data_ptr()), n, stream))
+        return out
+    gx = None if dqx is None else dqx.contiguous()
+    gy = None if dqy is None else dqy.contiguous()
+    which = {"gpf_stress_bottom": 0, "gpf_stress_top": 1, "gpf_stress_avg": 2}[name]
+    _capi.check(lib.gpf_stress_ex(C.byref(cfg), which, _capi.SLIP[slip], C.c_void_p(q.data_ptr()), C.c_void_p(h.data_ptr()), lsp,
+                                  C.c_void_p(gx.data_ptr()) if gx is not None else None,
+                                  C.c_void_p(gy.data_ptr()) if gy is not None else None,
+                                  C.c_void_p(out.data_ptr()), n, stream))
     return out
 
 
-def stress_bottom(q, h, U, V, eta, zeta, Ls=None):
-    return _stress("gpf_stress_bottom", 6, q, h, U, V, eta, zeta, Ls)
+def stress_bottom(q, h, U, V, eta, zeta, Ls=None, dqx=None, dqy=None, slip="top"):
+    return _stress("gpf_stress_bottom", 6, q, h, U, V, eta, zeta, Ls, dqx, dqy, slip)
 
 
-def stress_top(q, h, U, V, eta, zeta, Ls=None):
-    return _stress("gpf_stress_top", 6, q, h, U, V, eta, zeta, Ls)
+def stress_top(q, h, U, V, eta, zeta, Ls=None, dqx=None, dqy=None, slip="top"):
+    return _stress("gpf_stress_top", 6, q, h, U, V, eta, zeta, Ls, dqx, dqy, slip)
 
 
-def stress_avg(q, h, U, V, eta, zeta, Ls=None):
-    return _stress("gpf_stress_avg", 3, q, h, U, V, eta, zeta, Ls)
+def stress_avg(q, h, U, V, eta, zeta, Ls=None, dqx=None, dqy=None, slip="top"):
+    return _stress("gpf_stress_avg", 3, q, h, U, V, eta, zeta, Ls, dqx, dqy, slip)

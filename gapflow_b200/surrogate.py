@@ -34,7 +34,9 @@ TINYGP_JITTER = float(np.sqrt(np.finfo(np.float64).eps))
 
 
 def _normalizer(x):
-    """db.py:264-266."""
+    """db.py:264-266: column max-abs floored at 1e-12; host arrays or CUDA tensors (evaluated where the data is)."""
+    if isinstance(x, torch.Tensor):
+        return torch.clamp(x.abs().amax(dim=0), min=1e-12)
     return np.maximum(np.max(np.abs(x), axis=0), 1e-12)
 
 
@@ -51,19 +53,26 @@ class Mock:
         self.device = device
 
     def run_batch(self, X):
-        """X (n, 7) host -> Y (n, 13), Yerr (n, 13) host; one device evaluation of the three closures."""
+        """X (n, 7) -> Y (n, 13), Yerr (n, 13): one device evaluation of the three closures.  A CUDA tensor in gives
+        CUDA tensors out (nothing crosses the host: large synthetic training sets); a host array in
+        gives host arrays out (what ``Database.add_data`` keeps, db.py:343-369)."""
         dev = self.device or torch.device('cuda', torch.cuda.current_device())
-        Xd = torch.as_tensor(np.ascontiguousarray(np.atleast_2d(X), dtype=np.float64), device=dev)
+        on_device = isinstance(X, torch.Tensor) and X.is_cuda
+        Xd = X.to(torch.float64) if on_device else torch.as_tensor(np.ascontiguousarray(np.atleast_2d(X), dtype=np.float64), device=dev)
+        Xd = Xd.reshape(-1, Xd.shape[-1])
         q, h, Ls = Xd[:, :3].T.contiguous(), Xd[:, 3:6].T.contiguous(), Xd[:, 6].contiguous()
         U, V, eta, zeta = self.geo['U'], self.geo['V'], self.prop['shear'], self.prop['bulk']
         n_p, n_s0, n_s1 = (d * s for d, s in zip(self.draws, (self.noise[0], self.noise[1], self.noise[1])))
         bot = _fv.stress_bottom(q, h, U, V, eta, zeta, Ls) + n_s0
         top = _fv.stress_top(q, h, U, V, eta, zeta, Ls) + n_s1
         p = _fv.eos_pressure(q[0].contiguous(), self.prop) + n_p
-        Y = torch.cat([p[None, :], bot, top], dim=0).T.cpu().numpy()
+        Yd = torch.cat([p[None, :], bot, top], dim=0).T.contiguous()
         s = self.noise[1]
-        Ye = np.tile(np.array([self.noise[0], 0., 0., 0., s, s, 0., 0., 0., 0., s, s, 0.]), (len(Y), 1))
-        return Y, Ye
+        err_row = [self.noise[0], 0., 0., 0., s, s, 0., 0., 0., 0., s, s, 0.]
+        if on_device:
+            return Yd, torch.tensor(err_row, dtype=torch.float64, device=Xd.device).repeat(Yd.shape[0], 1)
+        Y = Yd.cpu().numpy()
+        return Y, np.tile(np.array(err_row), (len(Y), 1))
 
     def run(self, X, tag=None):
         Y, Ye = self.run_batch(np.asarray(X, dtype=float)[None, :])

@@ -278,6 +278,22 @@ int gpf_stress_top(const gpf_fv_cfg* cfg, const double* q, const double* h, cons
 int gpf_stress_avg(const gpf_fv_cfg* cfg, const double* q, const double* h, const double* Ls,
                    double* out, size_t n, void* stream);
 
+/* The general signatures stress_bottom / stress_top / stress_avg(q, h, U, V, eta, zeta, Ls, dqx, dqy, slip)
+ * (viscous.py:37, 281, 612): which = 0 bottom (6, n), 1 top (6, n), 2 avg (3, n); slip = GPF_SLIP_TOP (the
+ * reference's default, "top") or GPF_SLIP_BOTH ("both"); dqx, dqy (3, n): in-plane gradients of (rho, jx, jy), NULL =
+ * zero.  The time step never takes this route (WallStress / BulkStress call slip = "top" with zero gradients:
+ * stress.py:328-344, 452-459 -- gpf_stress_* above, bit-exact); it exists for the reference's analytic tests
+ * (tests/test_analytic.py:31-123) and for users of the pure functions.  Closed forms derived from the parabolic
+ * velocity profile with Navier slip and the Newtonian stress (tools/derive_slip_closures.py ->
+ * csrc/closures_slip_gen.cuh): equal to the reference's expanded polynomials to rounding (<= 1e-12 of the largest
+ * component), not bit for bit. */
+enum { GPF_SLIP_TOP = 0, GPF_SLIP_BOTH = 1 };
+int gpf_stress_ex(const gpf_fv_cfg* cfg, int which, int slip, const double* q, const double* h, const double* Ls,
+                  const double* dqx, const double* dqy, double* out, size_t n, void* stream);
+/* the same routine evaluated on the HOST (host arrays; no device call): CPU tests of the closed forms */
+int gpf_selftest_stress_ex_host(const gpf_fv_cfg* cfg, int which, int slip, const double* q, const double* h,
+                                const double* Ls, const double* dqx, const double* dqy, double* out, size_t n);
+
 /* The same two exchanges over peer memory instead of a communication library: every rank owns a
  * small buffer that its peers map through CUDA IPC (one node, NVLink / NVSwitch).  The sending
  * kernel stores the edge rows (the folded record) straight into the receivers' buffers and then

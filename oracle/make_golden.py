@@ -101,6 +101,17 @@ def closure_vectors(seed=20251104, shape=(23, 17)):
         for ls_name, ls in (('ls0', np.zeros_like(Ls)), ('ls', Ls)):
             for fn in ('stress_bottom', 'stress_top', 'stress_avg'):
                 out[f'{fn}_{k}_{ls_name}'] = getattr(R['viscous'], fn)(q, h, U, V, eta, zeta, ls)
+    # the general signatures (viscous.py:37, 281, 612): slip at both walls, in-plane gradients
+    rg = np.random.default_rng(seed + 1)           # its own generator: the draws below stay what they were
+    out['dqx'] = np.stack([1e4 * rg.standard_normal(shape), 3e3 * rg.standard_normal(shape), 3e2 * rg.standard_normal(shape)])
+    out['dqy'] = np.stack([1e4 * rg.standard_normal(shape), 3e2 * rg.standard_normal(shape), 3e3 * rg.standard_normal(shape)])
+    for k, (U, V, eta, zeta) in enumerate(out['visc_params']):
+        for slip in ('top', 'both'):
+            for g_name, gx, gy in (('dq0', None, None), ('dq', out['dqx'], out['dqy'])):
+                if slip == 'top' and g_name == 'dq0':
+                    continue                       # the driver's call: covered bit for bit above
+                for fn in ('stress_bottom', 'stress_top', 'stress_avg'):
+                    out[f'{fn}_{k}_{slip}_{g_name}'] = getattr(R['viscous'], fn)(q, h, U, V, eta, zeta, Ls, dqx=gx, dqy=gy, slip=slip)
     for p in EOS_PROPS:
         mu, w = EOS_DENS[p['EOS']]
         d = mu * (1 + w * (rng.random(shape) - 0.5) * 2) if p['EOS'] != 'Bayada' else rng.random(shape) * 900.

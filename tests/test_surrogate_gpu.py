@@ -135,6 +135,23 @@ def _compare_models(o, drv, rtol=REL_GP):
         assert np.isclose(mp.variance_tol, mo.variance_tol, rtol=1e-12), k
 
 
+def test_device_mock_md_and_normalisers_stay_on_the_device():
+    """Mock.run_batch and the max-abs normalisers on CUDA tensors: same numbers as the host route."""
+    from gapflow_b200.surrogate import Mock, _normalizer
+    d, _ = SC.inputs('slip2d', nx=12, ny=10)
+    rng = np.random.default_rng(4)
+    X = np.column_stack([rng.uniform(0.7, 0.9, 500), rng.uniform(0.02, 0.08, 500), rng.uniform(-0.01, 0.01, 500),
+                         rng.uniform(10., 14., 500), rng.uniform(-0.01, 0.01, 500), rng.uniform(-0.01, 0.01, 500),
+                         rng.uniform(0., 1., 500)])
+    md = Mock(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS)
+    Yh, Eh = md.run_batch(X)
+    Yd, Ed = md.run_batch(torch.as_tensor(X, device='cuda'))
+    assert Yd.is_cuda and Ed.is_cuda
+    assert np.array_equal(Yd.cpu().numpy(), Yh) and np.array_equal(Ed.cpu().numpy(), Eh)
+    assert np.array_equal(_normalizer(Yd).cpu().numpy(), _normalizer(Yh))
+    assert np.array_equal(_normalizer(torch.as_tensor(X, device='cuda')).cpu().numpy(), _normalizer(X))
+
+
 @pytest.mark.parametrize('name,kw,steps', [
     ('slip1d', dict(nx=100, atol=0.6, al_steps=3), 8),           # BASELINE config 3 scaled: active learning fires
     ('slip2d', dict(nx=24, ny=20, atol=0.8, al_steps=2), 4),     # BASELINE config 4 scaled: press + xz + yz models
