@@ -103,14 +103,16 @@ __device__ __forceinline__ double exp_neg_fast(double x, const double* T, const 
     const double t = T[k & 31] * p;
     return __hiloint2double(__double2hiint(t) + ((k >> 5) << 20), __double2loint(t));
 }
-// sqrt(d), d > 0 (the caller starts its sum of squares at 1e-300): one correction of d * rsqrt.approx(d)
-// (2^-22 seed): relative error ~1e-13
+// sqrt(d), d > 0 (the caller starts its sum of squares at 1e-300): two corrections of d * rsqrt.approx(d) (2^-22 seed).
+// One correction leaves 8e-14, which the cancellation in sum_j alpha_j k_j (|alpha| ~ 10^3) turned into 1.5e-10 on the
+// mean of BASELINE config 4 (r2n); with two the contracted mean is as close to the oracle as the exact one.
 __device__ __forceinline__ double sqrt_fast(double d, const FastK& K) {
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
-    const double g = d * y;
-    const double e = fma(-g, g, d);
-    return fma(e, K.half * y, g);
+    const double hy = K.half * y;
+    double g = d * y;
+    g = fma(fma(-g, g, d), hy, g);
+    return fma(fma(-g, g, d), hy, g);
 }
 
 // warp tile 32 x 32 of a CTA tile: acc[mi][ni][2] += A(32 x 4*KK, row-major in smem) x B
