@@ -32,9 +32,7 @@ _GEO_KEYS = {'inclined': ['hmax', 'hmin'], 'parabolic': ['hmin', 'hmax'], 'cdc':
 
 def sanitize_options(d):
     return {'output': str(d.get('output', 'example')), 'write_freq': int(d.get('write_freq', 1000)),
-            'use_tstamp': bool(d.get('use_tstamp', True)), 'silent': bool(d.get('silent', False)),
-            # not in the reference: the run loop's frames leave the device on a side stream while the next steps run
-            'async_write': bool(d.get('async_write', True))}
+            'use_tstamp': bool(d.get('use_tstamp', True)), 'silent': bool(d.get('silent', False))}
 
 
 def _axis(out, d, n, L, dl, n_default):

@@ -106,19 +106,6 @@ class FVSolver:
         torch.cuda.current_stream(self.device).synchronize()
         return outs[0][0], outs[1], outs[2], outs[3]
 
-    def closures_into(self, pressure, wall_xz, wall_yz, stale=False):
-        """the same fields into caller-owned CUDA tensors (1 / 12 / 12 planes), enqueued on the current stream without
-        a synchronisation: the staging step of an asynchronous ``Problem.write()``"""
-        _capi.check(self.lib.gpf_fv_closures_of(self.h, 1 if stale else 0, C.c_void_p(pressure.data_ptr()),
-                                                C.c_void_p(wall_xz.data_ptr()), C.c_void_p(wall_yz.data_ptr()), None, 1,
-                                                self._stream()))
-
-    def snapshot_q(self, out):
-        """the current q into a CUDA tensor (3, Nx+2, Ny+2) on the current stream, no synchronisation"""
-        p, dev = _ptr(out)
-        assert dev == 1
-        _capi.check(self.lib.gpf_fv_download(self.h, _capi.F_Q, p, 3, 1, self._stream()))
-
     # -- time loop --------------------------------------------------------------------
     def viscosity(self, stale=False):
         """The shear-viscosity field (Nx+2, Ny+2) of the current q (``stale``: of the last corrector pass's

@@ -334,15 +334,13 @@ class Problem:
                 else:
                     n = wf - self.step % wf                       # up to the next multiple of write_freq
                     self._solver.step(n, until_converged=True)    # loop condition evaluated on the device
-                self._flush_staged()                 # the previous frame goes to disk while these steps run
                 self._q_synced, self._clos_cache = False, None
                 self._pull()
                 if self._par.world > 1:              # a termination signal reaches one rank: all ranks leave together
                     self._stop = any(self._par.coll.allgather(bool(self._stop)))
                 if self.step % wf == 0 and not silent:
-                    self.write(staged=True)
+                    self.write()
         finally:
-            self._flush_staged()
             for s, h in old.items():
                 signal.signal(s, h)
         if not keep_open:
@@ -354,7 +352,6 @@ class Problem:
     def _post_run(self):
         walltime = datetime.now() - self._tic
         silent = self.options['silent']
-        self._flush_staged()
         if self.step % max(1, int(self.options['write_freq'])) != 0 and not silent:
             self.write()
         if not silent and self._sol is not None:
@@ -431,64 +428,10 @@ class Problem:
         """a device field over this rank's padded rows -> the global host array"""
         return dev_field.cpu().numpy() if self._par.world == 1 else self._solver.gather_rows(dev_field)
 
-    # -- output staging (SURVEY 8(f) row 2): the frame leaves the device on a side stream -------------------------------
-    def _can_stage(self):
-        return self._sol is not None and self._par.world == 1 and self._sur is None and self.options.get('async_write', True)
-
-    def _stage_fields(self):
-        """Snapshot q and the closure fields of this frame into device staging tensors (on the solver's stream: ordered
-        after the steps so far, before the next ones, which may overwrite the rotating buffers) and start their copy to
-        pinned host memory on a side stream.  The loop goes on enqueuing steps; ``_flush_staged`` writes the frame."""
-        import torch
-        sv = self._solver
-        if getattr(self, '_stage', None) is None:
-            shp = sv.shape
-            mk = lambda n: torch.empty((n, *shp), dtype=torch.float64, device=sv.device)
-            pin = lambda n: torch.empty((n, *shp), dtype=torch.float64, pin_memory=True)
-            self._stage = dict(dev=[mk(3), mk(1), mk(12), mk(12)], host=[pin(3), pin(1), pin(12), pin(12)],
-                               stream=torch.cuda.Stream(device=sv.device), ready=torch.cuda.Event(), done=torch.cuda.Event(),
-                               pending=False)
-        st = self._stage
-        q, p, wxz, wyz = st['dev']
-        sv.snapshot_q(q)
-        sv.closures_into(p, wxz, wyz, stale=bool(self.step))
-        st['ready'].record(torch.cuda.current_stream(sv.device))
-        with torch.cuda.stream(st['stream']):
-            st['stream'].wait_event(st['ready'])
-            for d, h in zip(st['dev'], st['host']):
-                h.copy_(d, non_blocking=True)
-            st['done'].record(st['stream'])
-        st['pending'] = True
-
-    def _flush_staged(self):
-        st = getattr(self, '_stage', None)
-        if st is None or not st['pending']:
-            return
-        st['done'].synchronize()
-        q, p, wxz, wyz = (h.numpy() for h in st['host'])
-        f = self._frames
-        self._sol.variables['solution'][f, :, 0] = q
-        self._sol.variables['pressure'][f] = p[0]
-        self._sol.variables['wall_stress_xz'][f, :, 0] = wxz
-        self._sol.variables['wall_stress_yz'][f, :, 0] = wyz
-        self._frames += 1
-        self._sol.flush()
-        st['pending'] = False
-
-    def write(self, scalars=True, fields=True, params=True, staged=False):
-        """problem.py:616-637.  ``staged`` (the run loop's writes): the fields leave the device asynchronously and
-        reach the file while the next steps run; a direct call writes synchronously, as the reference does."""
+    def write(self, scalars=True, fields=True, params=True):
+        """problem.py:616-637."""
         if self.step is None:
             self._pre_run()
-        self._flush_staged()
-        if staged and fields and self._can_stage():
-            if scalars:
-                sc = self._scalars()
-                print(f"{self.step:<6d} {sc.dt:.4e} {self.simtime:.4e} {sc.cfl:.4e} {self.residual:.4e}")
-                for k, v in zip(self.history, (self.step, self.simtime, sc.ekin, self.residual, sc.v_sound)):
-                    self.history[k].append(v)
-            self._stage_fields()
-            return
         if scalars:
             sc = self._scalars()
             if self._root:
