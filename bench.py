@@ -14,9 +14,10 @@ validity test, reductions) + the scalar bookkeeping kernel.  `value` times K ste
 fields resident in HBM; `e2e` times the host-buffer entry point (pinned host q uploaded and
 downloaded every step).  Extra blocks of the same JSON line:
 
-  slab_parity   N > 1: before the timed region, 3 steps of a 2048*N x 2048 journal on the N slabs
+  slab_parity   N > 1: after the measurement, 3 steps of a 2048*N x 2048 journal on the N slabs
                 (real processes, peer memory over NVLink) against the single-domain run of rank 0,
-                compared bit for bit on the device
+                compared bit for bit on the device; under a deadline, so that the line is printed
+                whatever happens in it
   slider4096    N = 1: BASELINE config 2 (round 1's headline workload), same measurement
   variants      N = 1: the general kernel (dh/dy != 0), the slip-length (LS) and the
                 viscosity-field (VF) variants at 4096^2
@@ -171,6 +172,9 @@ class ClockSampler:
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            t0 = time.perf_counter()                 # nvidia-smi takes up to a second to come up on an 8-GPU box: the first
+            while not self.rows and time.perf_counter() - t0 < 5.0 and self.proc.poll() is None:   # row before the timed region
+                time.sleep(0.02)
         except OSError:
             self.proc = None
         return self
@@ -506,10 +510,7 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    parity = None
-    if world > 1 and not args.no_parity:
-        parity = slab_parity(torch, dist, world, rank)
-        barrier()
+    parity = None          # N > 1: runs AFTER the measurement, under a deadline (end of this function)
 
     n = args.cells
     d = journal_inputs(n * world, n)
@@ -675,16 +676,17 @@ def run_gpu(args):
         if not args.no_gp:
             gp = guarded("gp", lambda: gp_block(torch, lib, args, local))
 
-    if world > 1 and not args.no_gp and args.gp_coupled_steps > 0:
-        # GP half of the metric at N > 1: the GP-coupled step of BASELINE config 4 on N slabs (training set and factor
-        # replicated, query cells partitioned with the slabs): strong scaling of a fixed 1024^2 x 10^4 problem
-        def gp_slabs():
-            import bench_gp as BG
-            ca = argparse.Namespace(coupled_n=1024, M=args.gp_M, coupled_steps=args.gp_coupled_steps, no_cpu=True)
-            return {"coupled_step": BG.coupled_step(torch, np, lib, ca, world=world), "scaling": "strong"}
-        gp = guarded("gp", gp_slabs)
+    if world > 1 and args.gp_slabs and args.gp_coupled_steps > 0:
+        # GP half of the metric at N > 1 (opt-in): the GP-coupled step of BASELINE config 4 on N slabs (training set and
+        # factor replicated, query cells partitioned with the slabs): strong scaling of a fixed 1024^2 x 10^4 problem.
+        # Not under `guarded`: collective code must fail on every rank or on none.  `torchrun ... bench_gp.py` measures
+        # the same step on its own (profiles/r1z_bench_gp_n2.json).
+        import bench_gp as BG
+        ca = argparse.Namespace(coupled_n=1024, M=args.gp_M, coupled_steps=args.gp_coupled_steps, no_cpu=True)
+        gp = {"coupled_step": BG.coupled_step(torch, np, lib, ca, world=world), "scaling": "strong"}
         barrier()
 
+    line = None
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:
@@ -713,10 +715,51 @@ def run_gpu(args):
             "slab_parity": parity, "gp": gp, "notes": notes,
             "final": {"step": int(sc.step), "dt": sc.dt, "residual": sc.residual},
         }
+    if world == 1:
         emit(line)
-    if world > 1:
-        solver.close()
-        dist.destroy_process_group()
+        return
+    # ---- N > 1: the measurement is complete.  slab_parity runs last and under a deadline: whatever happens in it,
+    # rank 0 prints the line (with the parity result, or with what went wrong) and every rank exits 0.
+    solver.close()
+    del solver
+    torch.cuda.empty_cache()
+
+    def finish(par):
+        if rank == 0:
+            line["slab_parity"] = par
+            emit(line)
+
+    if args.no_parity:
+        finish(None)
+    else:
+        finish(run_with_deadline(lambda: slab_parity(torch, dist, world, rank), args.parity_deadline, rank, finish))
+    dist.destroy_process_group()
+
+
+def run_with_deadline(fn, seconds, rank, finish):
+    """fn() under a watchdog.  A collective that hangs cannot be interrupted, so if fn has not returned after `seconds`
+    (or raises: the other ranks may then be stuck in a collective) rank 0 prints the line through `finish` with the
+    reason and every rank leaves with exit code 0."""
+    done = threading.Event()
+
+    def bail(reason):
+        finish({"bit_exact": None, "error": reason})
+        sys.stderr.write(f"[bench] rank {rank}: slab_parity abandoned: {reason}\n")
+        sys.stderr.flush()
+        time.sleep(0.0 if rank == 0 else 3.0)          # rank 0's line first
+        os._exit(0)
+
+    def watch():
+        if not done.wait(seconds):
+            bail(f"did not finish within {seconds:.0f} s")
+
+    threading.Thread(target=watch, daemon=True).start()
+    try:
+        out = fn()
+    except BaseException as e:          # noqa: BLE001
+        bail(f"{type(e).__name__}: {e}")
+    done.set()
+    return out
 
 
 _RESULT_FD = None
@@ -732,9 +775,19 @@ def _claim_stdout():
     os.dup2(2, 1)
 
 
+_EMIT_LOCK = threading.Lock()
+_EMITTED = False
+
+
 def emit(line):
-    sys.stdout.flush()
-    os.write(_RESULT_FD if _RESULT_FD is not None else 1, (json.dumps(line) + "\n").encode())
+    """the ONE JSON line; a second call (watchdog against normal completion) is ignored"""
+    global _EMITTED
+    with _EMIT_LOCK:
+        if _EMITTED:
+            return
+        _EMITTED = True
+        sys.stdout.flush()
+        os.write(_RESULT_FD if _RESULT_FD is not None else 1, (json.dumps(line) + "\n").encode())
 
 
 def main():
@@ -752,6 +805,8 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip slider4096 / variants (N = 1)")
     ap.add_argument("--no-gp", action="store_true", help="skip the GP block (N = 1)")
     ap.add_argument("--no-parity", action="store_true", help="skip slab_parity (N > 1)")
+    ap.add_argument("--parity-deadline", type=float, default=300.0, help="seconds slab_parity may take before the line is printed without it")
+    ap.add_argument("--gp-slabs", action="store_true", help="N > 1: also time the GP-coupled step on the slabs (see bench_gp.py)")
     ap.add_argument("--gp-M", type=int, default=10000)
     ap.add_argument("--gp-var-sample", type=int, default=75776,
                     help="query cells of the timed variance call: 2 x 296 x 128 = two full waves of the variance kernel")

@@ -94,6 +94,7 @@ SIGNATURES = {
     "gpf_comm_set_timeout": (_i, [_vp, C.c_double]),
     "gpf_fv_peer_export": (_i, [_vp, _vp]),
     "gpf_comm_attach": (_i, [_vp, _vp, _vp, _i, _i]),
+    "gpf_comm_detach": (_i, [_vp]),
     "gpf_comm_connect_local": (_i, [_vp, C.POINTER(C.c_void_p)]),
     "gpf_comm_attach_local": (_i, [_vp, _vp, _vp, _i, _vp, _i]),
     "gpf_fv_slab_pass": (_i, [_vp, _vp, _i, _vp]),

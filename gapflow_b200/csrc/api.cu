@@ -345,6 +345,9 @@ int gpf_fv_peer_export(gpf_fv* s, unsigned char* blob) {
 int gpf_comm_attach(gpf_comm* c, gpf_fv* s, const unsigned char* blobs, int lo, int hi) {
     GPF_TRY NEED(c && s && blobs) return c->C.attach(s->S, blobs, lo, hi); GPF_CATCH
 }
+int gpf_comm_detach(gpf_comm* c) {
+    GPF_TRY NEED(c) return c->C.detach(); GPF_CATCH
+}
 int gpf_comm_connect_local(gpf_comm* c, gpf_comm* const* all) {
     GPF_TRY NEED(c && all)
     std::vector<SlabComm*> v(c->C.lay.world);

@@ -1570,6 +1570,20 @@ int SlabComm::attach_local(const FvSolver& S, const FvSolver* lo_s, int lo, cons
     return GPF_OK;
 }
 
+int SlabComm::detach() {
+    if (!local_only) {
+        if (peer_map[0]) cudaIpcCloseMemHandle(peer_map[0]);
+        if (peer_map[1] && peer_map[1] != peer_map[0]) cudaIpcCloseMemHandle(peer_map[1]);
+    }
+    cudaGetLastError();
+    peer_map[0] = peer_map[1] = nullptr;
+    for (int sd = 0; sd < 2; ++sd)
+        for (int k = 0; k < 3; ++k) peer_q[sd][k] = nullptr;
+    attached = false;
+    if (step_graph) { cudaGraphExecDestroy(step_graph); step_graph = nullptr; }     // captured with the fused passes
+    return GPF_OK;
+}
+
 int SlabComm::connect_local(SlabComm* const* all) {
     for (int r = 0; r < lay.world; ++r) {
         if (!all[r] || !all[r]->local || all[r]->lay.world != lay.world || all[r]->lay.Ny2 != lay.Ny2) { set_error("gpf_comm_connect_local: bad communicator table"); return GPF_E_INVALID; }

@@ -68,6 +68,7 @@ struct SlabComm {
     int attach(const struct FvSolver& S, const unsigned char* blobs, int lo, int hi);   // [world][GPF_PEER_BLOB_BYTES]
     int attach_local(const struct FvSolver& S, const struct FvSolver* lo_s, int lo, const struct FvSolver* hi_s, int hi);
     int connect_local(SlabComm* const* all);
+    int detach();                          // back to the exchange kernels: unmaps the neighbours' q buffers
 };
 
 }  // namespace gpf

@@ -167,8 +167,20 @@ class SlabSolver:
                 dist.all_gather(parts, mine_b, group=group)
                 blobs = (C.c_ubyte * (self.world * nb)).from_buffer_copy(torch.cat(parts).cpu().numpy().tobytes())
                 lo, hi = self._neighbours()
-                _capi.check(self.lib.gpf_comm_attach(comm, self.h, blobs, lo, hi))
-                self.fused = True
+                rc = self.lib.gpf_comm_attach(comm, self.h, blobs, lo, hi)
+                # an attach that fails on one rank only (a mapping refused) must not leave the ranks with different
+                # step graphs, nor one rank raising while the others wait in a collective: agree, then all or none
+                ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=dev)
+                dist.all_gather(oks, ok, group=group)
+                if all(int(o.item()) for o in oks):
+                    self.fused = True
+                else:
+                    why = self.lib.gpf_last_error().decode() if rc != 0 else "another rank could not map its neighbour"
+                    self.lib.gpf_comm_detach(comm)
+                    if self.rank == 0 or rc != 0:
+                        import warnings
+                        warnings.warn(f"gapflow_b200 rank {self.rank}: fused slab exchange not available ({why}); "
+                                      "the slab step keeps its exchange kernels")
             elif rc != 0 and self.rank == 0:
                 import warnings
                 warnings.warn("gapflow_b200: the solver workspace cannot be exported over CUDA IPC ("

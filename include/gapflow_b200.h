@@ -343,6 +343,9 @@ int gpf_fv_slab_step(gpf_fv* s, gpf_comm* c, int lo, int hi, int n, double* recs
 #define GPF_PEER_BLOB_BYTES 96
 int gpf_fv_peer_export(gpf_fv* s, unsigned char* blob);
 int gpf_comm_attach(gpf_comm* c, gpf_fv* s, const unsigned char* blobs /* [world][GPF_PEER_BLOB_BYTES] */, int lo, int hi);
+/* undo gpf_comm_attach (every rank, or none: the ranks' step graphs must match): gpf_fv_slab_step runs the exchange
+ * kernels again.  For a caller whose attach failed on SOME rank. */
+int gpf_comm_detach(gpf_comm* c);
 int gpf_comm_connect_local(gpf_comm* c, gpf_comm* const* all /* [world] */);
 int gpf_comm_attach_local(gpf_comm* c, gpf_fv* s, gpf_fv* lo_solver, int lo, gpf_fv* hi_solver, int hi);
 /* one pass (0 predictor, 1 corrector) with the exchange fused in; the step ends with gpf_fv_finish_recv */

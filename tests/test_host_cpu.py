@@ -1,5 +1,6 @@
 """CPU: host-side logic of the binding that needs no device."""
 import copy
+import os
 
 import pytest
 
@@ -44,3 +45,39 @@ def test_viscosity_blocks_are_refused_on_slabs():
     """The pressure gradient at a halo row needs a second halo row: refused, not silently wrong."""
     with pytest.raises(NotImplementedError):
         _cfg({'thinning': {'name': 'Eyring', 'tauE': 5e5}}, halo=(True, False))
+
+
+def test_bench_prints_its_line_once_whatever_slab_parity_does(tmp_path):
+    """bench.py at N > 1: slab_parity runs under a deadline after the measurement.  A hang or an exception in it must
+    still leave exactly ONE JSON line on stdout and exit code 0 (os._exit from the watchdog); a normal return too."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "deadline.py"
+    script.write_text(
+        "import sys, time\n"
+        f"sys.path.insert(0, {root!r})\n"
+        "import bench\n"
+        "mode = sys.argv[1]\n"
+        "line = {'metric': 'x', 'slab_parity': None}\n"
+        "def finish(par):\n"
+        "    line['slab_parity'] = par\n"
+        "    bench.emit(line)\n"
+        "def fn():\n"
+        "    if mode == 'hang': time.sleep(60)\n"
+        "    if mode == 'raise': raise RuntimeError('boom')\n"
+        "    return {'bit_exact': True}\n"
+        "finish(bench.run_with_deadline(fn, 1.0, 0, finish))\n"
+        "finish({'bit_exact': 'second call must be ignored'})\n")
+    for mode, want in (('ok', True), ('hang', None), ('raise', None)):
+        r = subprocess.run([sys.executable, str(script), mode], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, (mode, r.stderr[-500:])
+        lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+        assert len(lines) == 1, (mode, lines)
+        par = json.loads(lines[0])['slab_parity']
+        assert par['bit_exact'] is want, (mode, par)
+        if mode == 'hang':
+            assert 'did not finish' in par['error']
+        if mode == 'raise':
+            assert 'boom' in par['error']
