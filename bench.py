@@ -496,6 +496,21 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = _capi.load()
     notes = []
+    if world > 1 and args.deadline > 0:
+        # ranks that wait on one another cannot be interrupted from inside: if the job has not printed its line after
+        # `--deadline` seconds, rank 0 prints a line that says so (value null) and every rank exits 1 -- a bounded failure
+        def overall():
+            time.sleep(args.deadline)
+            sys.stderr.write(f"[bench] rank {rank}: no result after {args.deadline:.0f} s, giving up\n")
+            sys.stderr.flush()
+            if rank == 0:
+                emit({"metric": "FV cell-updates/s", "value": None, "unit": "cell-updates/s", "n_gpus": world,
+                      "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+                      "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": workload_text(args.cells, world)},
+                      "error": f"the {world}-rank job did not finish within {args.deadline:.0f} s (--deadline)"})
+            os._exit(1)
+        threading.Thread(target=overall, daemon=True).start()
 
     def guarded(name, fn):
         """extra blocks never take the headline down: a failure is recorded in the line"""
@@ -805,7 +820,8 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip slider4096 / variants (N = 1)")
     ap.add_argument("--no-gp", action="store_true", help="skip the GP block (N = 1)")
     ap.add_argument("--no-parity", action="store_true", help="skip slab_parity (N > 1)")
-    ap.add_argument("--parity-deadline", type=float, default=300.0, help="seconds slab_parity may take before the line is printed without it")
+    ap.add_argument("--parity-deadline", type=float, default=180.0, help="seconds slab_parity may take before the line is printed without it")
+    ap.add_argument("--deadline", type=float, default=600.0, help="N > 1: seconds after which a job without a result gives up (0: never)")
     ap.add_argument("--gp-slabs", action="store_true", help="N > 1: also time the GP-coupled step on the slabs (see bench_gp.py)")
     ap.add_argument("--gp-M", type=int, default=10000)
     ap.add_argument("--gp-var-sample", type=int, default=75776,
