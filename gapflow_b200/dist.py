@@ -195,6 +195,9 @@ class SlabSolver:
                 dist.barrier(group=self.ex.group)
             self.lib.gpf_comm_destroy(self._comm)
             self._comm = None
+            if dist.is_initialized():
+                # nobody frees a workspace (when the solver is dropped after close()) that a neighbour still has mapped
+                dist.barrier(group=self.ex.group)
 
     def comm_error(self):
         """True if a device-side wait of THIS rank on a peer timed out (synchronises).  The flag also travels to
