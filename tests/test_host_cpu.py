@@ -81,3 +81,56 @@ def test_bench_prints_its_line_once_whatever_slab_parity_does(tmp_path):
             assert 'did not finish' in par['error']
         if mode == 'raise':
             assert 'boom' in par['error']
+
+
+def _dryrun(tmp_path, port, hang, extra):
+    """bench.py at N = 2 on the CPU: gloo, stand-in solvers (tests/bench_dryrun.py).  -> [(exit code, stdout lines, stderr)]"""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        if hang:
+            env["DRYRUN_HANG"] = hang
+        procs.append(subprocess.Popen([sys.executable, os.path.join(root, "tests", "bench_dryrun.py"), "--gpus", "2", "--steps", "5",
+                                       "--warmup", "3", "--cells", "64"] + extra, env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.PIPE, text=True))
+    out = []
+    for p in procs:
+        o, e = p.communicate(timeout=300)
+        out.append((p.returncode, [ln for ln in o.splitlines() if ln.strip()], e))
+    return out
+
+
+def test_bench_two_ranks_dry_run(tmp_path):
+    """The whole N > 1 control flow of bench.py (collectives in the same order on every rank, the JSON line, slab_parity
+    after the measurement) with two gloo ranks; slab_parity's bit-equality here also says that bench.initial_fields gives
+    the slabs the rows of the single domain's field."""
+    import json
+    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, 29621, None, [])
+    assert rc0 == 0 and rc1 == 0, (e0[-800:], e1[-800:])
+    assert len(l0) == 1 and l1 == []
+    d = json.loads(l0[0])
+    assert d["n_gpus"] == 2 and d["steps"] == 5 and d["value"] > 0 and d["scaling"] == "weak"
+    assert d["slab_parity"]["bit_exact"] is True and d["slab_parity"]["arith"] == ["fast", "exact"]
+    for key in ("metric", "unit", "warmup", "ms_per_step", "higher_is_better", "vs_baseline", "dtype", "data", "config", "clocks",
+                "e2e", "gpu_launches", "roofline", "cpu_baseline"):
+        assert key in d, key
+    assert d["e2e"]["h2d_bytes_per_step"] == 2 * 3 * 66 * 66 * 8
+
+
+def test_bench_two_ranks_with_a_peer_that_hangs(tmp_path):
+    """A rank that hangs in slab_parity: the measured line is printed with the reason, every rank exits 0.  A rank that hangs
+    in the measurement: rank 0 prints a line with value null and an error, exit code 1 -- bounded, never a silent hang."""
+    import json
+    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, 29622, "parity", ["--parity-deadline", "4"])
+    assert rc0 == 0 and rc1 == 0, (e0[-800:], e1[-800:])
+    assert len(l0) == 1 and l1 == []
+    d = json.loads(l0[0])
+    assert d["value"] > 0 and d["slab_parity"]["bit_exact"] is None and "did not finish" in d["slab_parity"]["error"]
+    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, 29623, "main", ["--deadline", "4"])
+    assert rc0 == 1 and rc1 == 1, (rc0, rc1, e0[-800:], e1[-800:])
+    assert len(l0) == 1 and l1 == []
+    d = json.loads(l0[0])
+    assert d["value"] is None and d["n_gpus"] == 2 and "did not finish" in d["error"]
