@@ -23,6 +23,20 @@ def load(relpath, name):
     return mod
 
 
+def load_with_stand_ins(relpath, name, stand_ins):
+    """``load`` for a reference module that imports packages which are not installed but which the functions under test
+    never call: ``stand_ins`` {module name: module object} are in sys.modules only while the file is executed."""
+    import sys
+    put = [k for k in stand_ins if k not in sys.modules]
+    for k in put:
+        sys.modules[k] = stand_ins[k]
+    try:
+        return load(relpath, name)
+    finally:
+        for k in put:
+            del sys.modules[k]
+
+
 def modules():
     """Returns dict(integrate, pressure, sound, viscous, viscosity) of reference modules."""
     return dict(

@@ -1,0 +1,149 @@
+"""Runs the reference's own ``Problem`` class (GaPFlow/problem.py) for FIXED-FORM closures in this container --
+TEST INFRASTRUCTURE ONLY, and only where /root/reference exists.
+
+``import GaPFlow`` needs jax, tinygp, jaxopt, muGrid, ContactMechanics, polars, dtoolcore, netCDF4, matplotlib ...,
+none of which is installed.  The fixed-form update loop (problem.py:509-768, models/stress.py, integrate.py,
+models/pressure.py / viscous.py / sound.py / viscosity.py, topography.py) is plain NumPy; what it takes from those
+packages is
+
+* muGrid: a container of named arrays with a ``.p`` view (``GlobalFieldCollection.real_field``) -- replaced here by a
+  dictionary of NumPy arrays of the same shapes (components first, then the padded grid);
+* jax: decorators and type names at import time (``jax.jit``, ``jax.Array``); nothing of it executes without a GP.
+
+So the missing packages are replaced by inert stand-ins (every function of theirs that would compute something
+raises), GaPFlow's own md / db / viz sub-packages (MD runners, training database, plotting: outside this path) by empty
+ones, and the reference's modules are imported unchanged from where they lie.  What runs is the reference's code:
+``Problem.__init__``, ``_pre_run``, ``update``, the ghost-cell routines, the stress models' ``update``, ``Topography``.
+tests/test_oracle_vs_reference_problem.py holds oracle/fv.py to it bit for bit.
+"""
+import importlib
+import os
+import sys
+import types
+
+import numpy as np
+
+from .ref_loader import REF_ROOT, available  # noqa: F401
+
+_PKG = "GaPFlow"
+
+
+class _Inert:
+    """Attribute / call sink for names that are imported but must never compute anything on this path."""
+
+    def __init__(self, name):
+        self._name = name
+
+    def __getattr__(self, k):
+        if k.startswith('__'):
+            raise AttributeError(k)
+        return _Inert(f"{self._name}.{k}")
+
+    def __call__(self, *a, **k):
+        raise RuntimeError(f"{self._name} is a stand-in (package not installed): the fixed-form path must not call it")
+
+    def __getitem__(self, k):
+        return self
+
+    def __mro_entries__(self, bases):
+        return (object,)
+
+    def __or__(self, other):             # `Name | None` in annotations
+        return self
+
+    __ror__ = __or__
+
+
+_installed = []
+
+
+def _inert_module(name, **attrs):
+    _installed.append(name)
+    m = types.ModuleType(name)
+    m.__dict__.update(attrs)
+    m.__getattr__ = lambda k, _n=name: _Inert(f"{_n}.{k}")          # PEP 562
+    m.__path__ = []                                                  # lets `import name.sub` find our sub-stubs
+    sys.modules[name] = m
+    return m
+
+
+class _Field:
+    def __init__(self, shape):
+        self.p = np.zeros(shape)
+
+    @property
+    def s(self):
+        return self.p
+
+
+class _FieldCollection:
+    """muGrid.GlobalFieldCollection as problem.py uses it: named real fields, components first."""
+
+    def __init__(self, nb_grid_pts, *a, **k):
+        self.nb_grid_pts = tuple(int(n) for n in nb_grid_pts)
+        self.fields = {}
+
+    def real_field(self, name, components=()):
+        if name not in self.fields:
+            self.fields[name] = _Field(tuple(components) + self.nb_grid_pts)
+        return self.fields[name]
+
+    register_real_field = real_field
+
+    def get_real_field(self, name):
+        return self.fields[name]
+
+
+def _install_stand_ins():
+    jit = lambda f=None, **k: f if f is not None else (lambda g: g)          # noqa: E731
+    jax = _inert_module('jax', jit=jit, Array=np.ndarray, numpy=np,
+                        config=types.SimpleNamespace(update=lambda *a, **k: None))
+    sys.modules['jax.numpy'] = np
+    _installed.append('jax.numpy')
+    jax.random = _inert_module('jax.random')
+    _inert_module('jaxopt')
+    _inert_module('tinygp')
+    mg = _inert_module('muGrid', GlobalFieldCollection=_FieldCollection)
+    mg.Field = _inert_module('muGrid.Field', wrap_field=lambda f: f)
+    for name in ('ContactMechanics', 'polars', 'dtoolcore', 'dtool_lookup_api', 'netCDF4', 'matplotlib', 'matplotlib.pyplot',
+                 'matplotlib.animation', 'IPython', 'IPython.display', 'ruamel', 'ruamel.yaml'):
+        if name not in sys.modules:
+            _inert_module(name)
+
+
+_problem_cls = None
+
+
+def reference_problem():
+    """The reference's Problem class, imported from REF_ROOT with the stand-ins above."""
+    global _problem_cls
+    if _problem_cls is not None:
+        return _problem_cls
+    if not available():
+        raise RuntimeError("reference tree not present")
+    if _PKG in sys.modules:
+        raise RuntimeError("a GaPFlow package is already imported")
+    _install_stand_ins()
+    pkg = types.ModuleType(_PKG)
+    pkg.__path__ = [os.path.join(REF_ROOT, _PKG)]
+    pkg.__version__ = "reference"
+    sys.modules[_PKG] = pkg
+    # the reference's own sub-packages that lie outside the fixed-form path
+    _inert_module(f'{_PKG}.db', Database=type('Database', (), {}))
+    _inert_module(f'{_PKG}.md', **{n: type(n, (), {}) for n in ('Mock', 'LennardJones', 'GoldAlkane')})
+    viz = _inert_module(f'{_PKG}.viz')
+    viz.plotting = _inert_module(f'{_PKG}.viz.plotting')
+    viz.animations = _inert_module(f'{_PKG}.viz.animations')
+    _problem_cls = importlib.import_module(f'{_PKG}.problem').Problem
+    return _problem_cls
+
+
+def release():
+    """Takes the stand-ins and the reference package out of sys.modules again (the loaded classes keep working: they hold
+    what they imported), so that nothing else in the process mistakes a stand-in for an installed package."""
+    global _problem_cls
+    for name in list(sys.modules):
+        if name == _PKG or name.startswith(_PKG + '.') or name in _installed:
+            del sys.modules[name]
+    _installed.clear()
+    _problem_cls = None

@@ -6,7 +6,6 @@ import contextlib
 import glob
 import io
 import os
-import sys
 import types
 
 import numpy as np
@@ -20,8 +19,7 @@ pytestmark = pytest.mark.skipif(not ref_loader.available(), reason="reference tr
 
 @pytest.fixture(scope="module")
 def ref_io():
-    sys.modules.setdefault('polars', types.ModuleType('polars'))
-    return ref_loader.load("GaPFlow/io.py", "_ref_io")
+    return ref_loader.load_with_stand_ins("GaPFlow/io.py", "_ref_io", {'polars': types.ModuleType('polars')})
 
 
 def _norm(x):

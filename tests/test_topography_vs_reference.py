@@ -3,7 +3,6 @@ reference's own Topography class (GaPFlow/topography.py:38-255), bit for bit, fo
 `flip`, 1D and 2D grids, and for the row windows the slab decomposition asks for.  topography.py imports
 ContactMechanics (elastic deformation, out of scope) and muGrid's field wrapper; the module is loaded by file path with
 stand-ins for both: the wrapper becomes a plain array holder, so Topography.__init__ itself runs unchanged."""
-import sys
 import types
 
 import numpy as np
@@ -24,13 +23,11 @@ class _Holder:
 
 @pytest.fixture(scope="module")
 def ref_topo():
-    sys.modules.setdefault('ContactMechanics', types.ModuleType('ContactMechanics'))
     mg, mf = types.ModuleType('muGrid'), types.ModuleType('muGrid.Field')
     mf.wrap_field = lambda f: f
     mg.Field = mf
-    sys.modules.setdefault('muGrid', mg)
-    sys.modules.setdefault('muGrid.Field', mf)
-    return ref_loader.load("GaPFlow/topography.py", "_ref_topography")
+    return ref_loader.load_with_stand_ins("GaPFlow/topography.py", "_ref_topography",
+                                          {'ContactMechanics': types.ModuleType('ContactMechanics'), 'muGrid': mg, 'muGrid.Field': mf})
 
 
 class _Fields:
