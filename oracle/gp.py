@@ -24,7 +24,8 @@ golden vector for GP values; its only GP test (tests/test_inference.py:86-111) i
 published algorithm as restated here: DirectSolver = dense Cholesky of K + diag; Matern32(r) =
 (1 + sqrt(3) r) exp(-sqrt(3) r); Linear(scale, k)(x1, x2) = k(scale*x1, scale*x2); L2Distance =
 sqrt(sum((x1 - x2)**2)).  The conditioned GP's diagonal jitter (``noise``) is an INPUT here.
-What stands in for the missing pin: tests/test_gp_oracle.py holds this file to an independent implementation of the same
+What stands in for the missing pin (next to tests/test_surrogate_oracle_vs_reference.py, which executes the reference's
+own code around the tinygp calls): tests/test_gp_oracle.py holds this file to an independent implementation of the same
 published algorithm (scikit-learn's GaussianProcessRegressor, amp * Matern(nu=1.5) with one length scale per input,
 alpha = yerr^2): mean 1e-9, variance 1e-9 amp, log marginal likelihood 1e-10, its gradient 1e-7.
 """

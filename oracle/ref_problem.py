@@ -95,55 +95,92 @@ class _FieldCollection:
 
 
 def _install_stand_ins():
+    from . import tinygp_stand_in as T
     jit = lambda f=None, **k: f if f is not None else (lambda g: g)          # noqa: E731
-    jax = _inert_module('jax', jit=jit, Array=np.ndarray, numpy=np,
+    jax = _inert_module('jax', jit=jit, Array=np.ndarray, numpy=np, grad=T.grad, vmap=T.vmap,
                         config=types.SimpleNamespace(update=lambda *a, **k: None))
     sys.modules['jax.numpy'] = np
     _installed.append('jax.numpy')
-    jax.random = _inert_module('jax.random')
-    _inert_module('jaxopt')
-    _inert_module('tinygp')
+    jax.random = _inert_module('jax.random', key=T.Random.key, split=T.Random.split, normal=T.Random.normal,
+                               uniform=T.Random.uniform, choice=T.Random.choice)
+    _inert_module('jaxopt', ScipyMinimize=T.ScipyMinimize)
+    _inert_module('tinygp', GaussianProcess=T.GaussianProcess,
+                  kernels=types.SimpleNamespace(stationary=types.SimpleNamespace(Matern32=T.Matern32),
+                                                distance=types.SimpleNamespace(L2Distance=T.L2Distance)),
+                  transforms=types.SimpleNamespace(Linear=T.Linear))
     mg = _inert_module('muGrid', GlobalFieldCollection=_FieldCollection)
     mg.Field = _inert_module('muGrid.Field', wrap_field=lambda f: f)
+
+    class YAML:                                  # ruamel.yaml.YAML(): configured at import time, used only for dtool readmes
+        explicit_start = False
+
+        def indent(self, *a, **k):
+            pass
     for name in ('ContactMechanics', 'polars', 'dtoolcore', 'dtool_lookup_api', 'netCDF4', 'matplotlib', 'matplotlib.pyplot',
                  'matplotlib.animation', 'IPython', 'IPython.display', 'ruamel', 'ruamel.yaml'):
         if name not in sys.modules:
-            _inert_module(name)
+            _inert_module(name, **({'YAML': YAML} if name == 'ruamel.yaml' else {}))
 
 
-_problem_cls = None
+_ref = None
 
 
-def reference_problem():
-    """The reference's Problem class, imported from REF_ROOT with the stand-ins above."""
-    global _problem_cls
-    if _problem_cls is not None:
-        return _problem_cls
+def reference_package():
+    """namespace(Problem, Database, Mock, read_yaml_input): the reference's classes, imported from REF_ROOT with the
+    stand-ins above.  ``Mock`` is the reference's mock MD with the dtool bookkeeping of ``MolecularDynamics.run``
+    (md/base.py:190-240: dataset directories, readme files) left out -- ``run`` is build_input_files + read_output."""
+    global _ref
+    if _ref is not None:
+        return _ref
     if not available():
         raise RuntimeError("reference tree not present")
     if _PKG in sys.modules:
         raise RuntimeError("a GaPFlow package is already imported")
     _install_stand_ins()
+    root = os.path.join(REF_ROOT, _PKG)
     pkg = types.ModuleType(_PKG)
-    pkg.__path__ = [os.path.join(REF_ROOT, _PKG)]
+    pkg.__path__ = [root]
     pkg.__version__ = "reference"
     sys.modules[_PKG] = pkg
-    # the reference's own sub-packages that lie outside the fixed-form path
-    _inert_module(f'{_PKG}.db', Database=type('Database', (), {}))
-    _inert_module(f'{_PKG}.md', **{n: type(n, (), {}) for n in ('Mock', 'LennardJones', 'GoldAlkane')})
+    _installed.append(_PKG)
+    # the reference's own sub-packages that lie outside the path: plotting, MD runners (LAMMPS, MPI)
     viz = _inert_module(f'{_PKG}.viz')
     viz.plotting = _inert_module(f'{_PKG}.viz.plotting')
     viz.animations = _inert_module(f'{_PKG}.viz.animations')
-    _problem_cls = importlib.import_module(f'{_PKG}.problem').Problem
-    return _problem_cls
+    md = types.ModuleType(f'{_PKG}.md')
+    md.__path__ = [os.path.join(root, 'md')]
+    sys.modules[f'{_PKG}.md'] = md
+    _inert_module(f'{_PKG}.md.runner')
+    ref_mock = importlib.import_module(f'{_PKG}.md.mock').Mock
+
+    class Mock(ref_mock):
+        def run(self, X, tag):
+            self.build_input_files(None, None, X)
+            return self.read_output()
+    md.Mock, md.LennardJones, md.GoldAlkane = Mock, type('LennardJones', (), {}), type('GoldAlkane', (), {})
+    db = importlib.import_module(f'{_PKG}.db')
+    from scipy.stats import qmc as _qmc
+    from .tinygp_stand_in import Random
+    # db.py:313 draws an UNSEEDED Latin hypercube / Sobol sequence: here from the generator of the latest jax.random.key
+    db.qmc = types.SimpleNamespace(scale=_qmc.scale,
+                                   LatinHypercube=lambda d: _qmc.LatinHypercube(d=d, seed=Random.current),
+                                   Sobol=lambda d, **k: _qmc.Sobol(d=d, seed=Random.current, **k))
+    problem = importlib.import_module(f'{_PKG}.problem')
+    _ref = types.SimpleNamespace(Problem=problem.Problem, Database=db.Database, Mock=Mock,
+                                 read_yaml_input=sys.modules[f'{_PKG}.io'].read_yaml_input)
+    return _ref
+
+
+def reference_problem():
+    return reference_package().Problem
 
 
 def release():
     """Takes the stand-ins and the reference package out of sys.modules again (the loaded classes keep working: they hold
     what they imported), so that nothing else in the process mistakes a stand-in for an installed package."""
-    global _problem_cls
+    global _ref
     for name in list(sys.modules):
         if name == _PKG or name.startswith(_PKG + '.') or name in _installed:
             del sys.modules[name]
     _installed.clear()
-    _problem_cls = None
+    _ref = None

@@ -16,8 +16,11 @@ Follows (reference file:line):
 * GaPFlow/models/stress.py:289-362, 600-622   update: GP means scattered into the closure fields
 * GaPFlow/problem.py:412-443, 509-586  _pre_run, update, _post_update with GP models         -> SurrogateFVOracle
 
-PARITY UNPINNED at the JAX boundary (see oracle/gp.py): tinygp, jax and jaxopt are absent.  What that
-leaves as INPUTS here, identical for the oracle and the product in every test:
+PARITY UNPINNED at the JAX boundary (see oracle/gp.py): tinygp, jax and jaxopt are absent.  Everything the reference
+itself owns around that boundary IS pinned, by executing it: tests/test_surrogate_oracle_vs_reference.py runs the
+reference's Problem / GaussianProcessSurrogate / Pressure / WallStress / Database / Mock classes (oracle/ref_problem.py,
+with oracle/tinygp_stand_in.py in tinygp's place) next to this file, step by step.  What the missing packages
+leave as INPUTS here, identical for the oracle and the product in every test:
   * the hyperparameters: ``optimizer(model) -> (log_amp, log_scale)``; the default is SciPy BFGS from
     params_init on the restated objective (gp.py:320-321 uses jaxopt.ScipyMinimize);
   * the three standard-normal draws of the mock MD (mock.py:82-88 draws them from jax.random.key(123),
