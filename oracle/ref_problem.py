@@ -61,7 +61,11 @@ def _inert_module(name, **attrs):
     _installed.append(name)
     m = types.ModuleType(name)
     m.__dict__.update(attrs)
-    m.__getattr__ = lambda k, _n=name: _Inert(f"{_n}.{k}")          # PEP 562
+    def missing(k, _n=name):                                         # PEP 562
+        if k.startswith('__'):
+            raise AttributeError(k)
+        return _Inert(f"{_n}.{k}")
+    m.__getattr__ = missing
     m.__path__ = []                                                  # lets `import name.sub` find our sub-stubs
     sys.modules[name] = m
     return m

@@ -119,3 +119,24 @@ def test_committed_golden_vectors_are_what_the_reference_computes(RefProblem, go
         assert same(p.q, gs[f'{name}_q{tag}']), (name, tag)
         s = np.array([p.dt, p.residual, p.kinetic_energy, p.v_max, p.pressure.v_sound, p.mass])
         assert same(s, gs[f'{name}_s{tag}']), (name, tag)
+
+
+@pytest.mark.parametrize('tol, max_it', [(1e-4, 10_000), (1e-12, 150)])
+def test_run_loop_stops_where_the_reference_s_does(RefProblem, tol, max_it):
+    """Problem.run (problem.py:368-410): until the last five residuals are below `tol`, or `max_it` steps"""
+    import sys
+    from gapflow_b200 import config
+    from oracle.fv import FVOracle
+    from tests.test_problem_gpu import SOMMERFELD
+    text = SOMMERFELD.replace("tol: 1e-8", f"tol: {tol}").replace("max_it: 10_000", f"max_it: {max_it}")
+    d = config.read_yaml_string(text)
+    o = FVOracle(d['grid'], d['geometry'], d['properties'], d['numerics'])
+    o.run()
+    with io.StringIO(text) as f, contextlib.redirect_stdout(io.StringIO()):
+        rd = sys.modules['GaPFlow.io'].read_yaml_input(f)
+        rd['options']['silent'] = True
+        p = RefProblem._from_dict(rd)
+        p.run()
+    assert o.step == p.step and (o.step < max_it) == (tol > 1e-6) and o.step > 50
+    assert np.array_equal(o.q, p.q) and o.dt == p.dt and o.simtime == p.simtime
+    assert list(o.residual_buffer) == list(p.residual_buffer)
