@@ -1,4 +1,4 @@
-"""CPU, world_size 2 and 3 over gloo: the slab partition, neighbour table, message pairing and
+"""CPU, world_size 2, 3, 4 and 8 over gloo: the slab partition, neighbour table, message pairing and
 rank-ordered scalar fold of gapflow_b200/dist.py reproduce the single-domain result
 bit-for-bit (q, dt) when they drive the NumPy oracle on slabs (tests/slab_oracle.py)."""
 import os
@@ -47,7 +47,10 @@ def _worker(rank, world, port, name, out_path):
 
 
 @pytest.mark.parametrize("name,world", [("journal2d_periodic", 2), ("slider2d_xDN", 2), ("slider2d_allDN_slip", 3),
-                                        ("journal2d_flip_mc0", 2)])
+                                        ("journal2d_flip_mc0", 2),
+                                        # the rank counts of the scaling run: a ring of 4 and of 8 (uneven slabs: 37 rows), and
+                                        # different masks on the two x sides held by different ranks
+                                        ("journal2d_periodic", 4), ("journal2d_periodic", 8), ("asym_x_mc1", 4)])
 def test_slab_oracle_matches_single_domain(tmp_path, name, world):
     out = str(tmp_path / "out.npz")
     mp.spawn(_worker, args=(world, _free_port(), name, out), nprocs=world, join=True)
