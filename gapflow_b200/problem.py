@@ -175,7 +175,8 @@ class Problem:
             return cls._from_dict(config.read_yaml_input(f))
 
     @classmethod
-    def _from_dict(cls, d):
+    def _from_dict(cls, input_dict):
+        d = input_dict
         # problem.py:207-249: a db section builds the Database around the mock MD (md section absent) --
         # LAMMPS runners (md section present) stay with the reference
         gp, db, database = d.get('gp'), d.get('db'), None
@@ -197,6 +198,17 @@ class Problem:
             self._q_synced = True
         self._q_exposed = True
         return self._q_host
+
+    # problem.py:319-331 (over the padded array, ghost cells included)
+    q_has_nan = property(lambda self: bool(np.any(np.isnan(self.q))))
+    q_has_negative_density = property(lambda self: bool(np.any(self.q[0] < 0.)))
+    q_is_valid = property(lambda self: not self.q_has_nan and not self.q_has_negative_density)
+
+    def _communicate_ghost_buffers(self):
+        """problem.py:676-707 on the current field: scripts call it after writing into ``q``."""
+        self._sync_to_device()
+        self._solver.fill_ghosts()
+        self._q_synced, self._clos_cache, self._scal_stale = False, None, True
 
     def _sync_to_device(self):
         if self._q_exposed:
