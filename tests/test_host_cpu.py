@@ -83,10 +83,14 @@ def test_bench_prints_its_line_once_whatever_slab_parity_does(tmp_path):
             assert 'boom' in par['error']
 
 
-def _dryrun(tmp_path, port, hang, extra):
+def _dryrun(tmp_path, hang, extra):
     """bench.py at N = 2 on the CPU: gloo, stand-in solvers (tests/bench_dryrun.py).  -> [(exit code, stdout lines, stderr)]"""
+    import socket
     import subprocess
     import sys
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0))
+        port = so.getsockname()[1]
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     procs = []
     for r in range(2):
@@ -108,7 +112,7 @@ def test_bench_two_ranks_dry_run(tmp_path):
     after the measurement) with two gloo ranks; slab_parity's bit-equality here also says that bench.initial_fields gives
     the slabs the rows of the single domain's field."""
     import json
-    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, 29621, None, [])
+    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, None, [])
     assert rc0 == 0 and rc1 == 0, (e0[-800:], e1[-800:])
     assert len(l0) == 1 and l1 == []
     d = json.loads(l0[0])
@@ -124,12 +128,12 @@ def test_bench_two_ranks_with_a_peer_that_hangs(tmp_path):
     """A rank that hangs in slab_parity: the measured line is printed with the reason, every rank exits 0.  A rank that hangs
     in the measurement: rank 0 prints a line with value null and an error, exit code 1 -- bounded, never a silent hang."""
     import json
-    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, 29622, "parity", ["--parity-deadline", "4"])
+    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, "parity", ["--parity-deadline", "4"])
     assert rc0 == 0 and rc1 == 0, (e0[-800:], e1[-800:])
     assert len(l0) == 1 and l1 == []
     d = json.loads(l0[0])
     assert d["value"] > 0 and d["slab_parity"]["bit_exact"] is None and "did not finish" in d["slab_parity"]["error"]
-    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, 29623, "main", ["--deadline", "4"])
+    (rc0, l0, e0), (rc1, l1, e1) = _dryrun(tmp_path, "main", ["--deadline", "4"])
     assert rc0 == 1 and rc1 == 1, (rc0, rc1, e0[-800:], e1[-800:])
     assert len(l0) == 1 and l1 == []
     d = json.loads(l0[0])
