@@ -184,6 +184,13 @@ def make_cfg(grid, geo, prop, numerics, has_extra=False, halo=(False, False), ha
     lib = load()
     c = FvCfg()
     c.Nx, c.Ny, c.dx, c.dy = grid['Nx'], grid['Ny'], grid['dx'], grid['dy']
+    # The reference reads the Dirichlet value of the OPPOSITE-named side whenever a side is not periodic, for Neumann
+    # components too (problem.py:682-707 -> :738-753), and its sanitiser stores that value only for sides that have a
+    # 'D' component (io.py:183-191, 212-220): on a non-periodic axis both sides need one, or the first ghost fill ends
+    # in this KeyError.  Same inputs refused, same exception, here already at construction.
+    for side, looked_up in (('xE', 'xW'), ('xW', 'xE'), ('yS', 'yN'), ('yN', 'yS')):
+        if not all(grid[f'bc_{side}_P']) and f'bc_{looked_up}_D_val' not in grid:
+            raise KeyError(f'bc_{looked_up}_D_val')
     masks = (C.c_uint8 * 36)()
     vals = (C.c_double * 4)()
     for s, side in enumerate(['xE', 'xW', 'yS', 'yN']):

@@ -249,7 +249,7 @@ class FVOracle:
             side = 'yS' if direction > 0 else 'yN'
             mask = g[f'bc_{side}_{bc_type}']
             adj = q[mask, :, -2:-1] if direction > 0 else q[mask, :, 1:2]
-        target = g.get(f'bc_{side}_D_val')
+        target = g[f'bc_{side}_D_val']      # read for 'N' too (problem.py:738-753): KeyError when that side has no 'D' (io.py:183-191)
         a1, a2, q2 = 0.5, 0.0, 0.0
         if bc_type == 'D':
             return (target - a1 * adj + a2 * q2) / (a1 - a2)
