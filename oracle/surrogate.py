@@ -104,7 +104,9 @@ class Database:
         elif db['init_method'] == 'lhc':
             samples = qmc.scale(qmc.LatinHypercube(d=len(active), seed=rng).random(n=Nsample), lo, hi)
         else:
-            m = int(np.log2(Nsample))
+            m = int(np.log2(Nsample))                     # db.py:418-424: the next power of two, not the previous one
+            if 2**m != Nsample:
+                m = int(np.ceil(np.log2(Nsample)))
             samples = qmc.scale(qmc.Sobol(d=len(active), seed=rng).random_base2(m=m), lo, hi)
             Nsample = samples.shape[0]
         choice = rng.choice(Xtest.shape[0], size=Nsample, replace=False)

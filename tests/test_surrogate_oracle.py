@@ -77,6 +77,23 @@ def test_product_database_matches_oracle_database():
     assert np.all(pdb._Xtrain[:, 2] != 0.0)               # 2D: the y flux is sampled too (db.py:300-302)
 
 
+@pytest.mark.parametrize('method, size, want', [('rand', 7, 7), ('lhc', 9, 9), ('sobol', 8, 8), ('sobol', 10, 16), ('sobol', 5, 8)])
+def test_initial_design_methods_and_sizes(method, size, want):
+    """db.py:313-333, 398-425: the three design methods; a Sobol design that is not a power of two is rounded UP to the
+    next one (held to the executed reference by tests/test_surrogate_oracle_vs_reference.py, which found a rounding down
+    here).  Product and oracle databases draw the same design."""
+    from gapflow_b200.surrogate import Database
+    d, o, _ = _oracle('slip1d', nx=40)
+    cfg = dict(d['db'], init_method=method, init_size=size)
+    X = o.models['zz']._Xtest
+    md = OS.MockMD(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS)
+    db, pdb = OS.Database(md, dict(cfg)), Database(md, dict(cfg))
+    db.initialize(X, 1)
+    pdb.initialize(X, 1)
+    assert db.size == pdb.size == want
+    assert np.array_equal(db._Xtrain, pdb._Xtrain) and np.array_equal(db._Ytrain, pdb._Ytrain)
+
+
 def test_targets_and_scales_of_the_three_models():
     """stress.py:204-262, 551-570."""
     d, o, db = _oracle('slip2d', nx=12, ny=10)

