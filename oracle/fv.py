@@ -13,6 +13,12 @@ Follows (reference file:line):
 * GaPFlow/topography.py:38-255 grid + gap geometries   -> midpoint_grid / make_topography
 
 Arrays have the reference's shapes: (ncomp, Nx+2, Ny+2), C order, float64.
+
+PINNED: bit for bit to the golden vectors written from the reference's own functions (oracle/make_golden.py,
+tests/test_oracle_golden.py), and -- where the reference tree is present -- to the reference's own ``Problem`` class
+EXECUTED next to it (oracle/ref_problem.py; tests/test_oracle_vs_reference_problem.py: every golden case, ghost cells
+on garbage, the invalid-state exit, the run loop; tests/test_oracle_vs_reference_random.py: seeded random configurations),
+and it passes the reference's known-answer tests (tests/test_oracle_known_answers.py).
 """
 from collections import deque
 import numpy as np

@@ -11,7 +11,9 @@ Run in the build container (needs /root/reference):
   grids, the solution after 1 and 3 steps of the reference's update loop, where every
   arithmetic function (closures, predictor_corrector, source) is the reference's own,
   imported by file path; only the ~40-line driver and ghost-cell code of
-  GaPFlow/problem.py (not importable: needs muGrid/JAX) is the restatement in oracle/fv.py.
+  GaPFlow/problem.py (not importable as it is: needs muGrid/JAX) is the restatement in oracle/fv.py --
+  which tests/test_oracle_vs_reference_problem.py holds to the reference's Problem class executed with stand-ins for
+  those packages (oracle/ref_problem.py), together with this file's output.
 """
 import os
 
