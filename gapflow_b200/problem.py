@@ -264,6 +264,12 @@ class Problem:
         return sc
 
     def _closures(self):
+        if not self.step and not self._stop:
+            # The reference's stress models fill their fields in update() only (stress.py:289-362, 427-459, 600-622):
+            # until the first step they hold the zeros they were created with, and frame 0 of sol.nc is written that way
+            # (problem.py:397, 629).  (_finalize evaluates them, problem.py:604-607: an invalid FIRST step shows closures.)
+            nx, ny = self.grid['Nx'] + 2, self.grid['Ny'] + 2
+            return tuple(np.zeros((n, nx, ny)) if n else np.zeros((nx, ny)) for n in (0, 12, 12, 3))
         if self._clos_cache is None:
             self._sync_to_device()
             if self._par.world == 1:

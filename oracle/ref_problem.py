@@ -98,6 +98,41 @@ class _FieldCollection:
         return self.fields[name]
 
 
+class FileIONetCDF:
+    """muGrid.FileIONetCDF as problem.py:166-205, 629 uses it; frames are kept in memory (``opened`` lists the files)."""
+    opened = []
+
+    def __init__(self, path, mode=None, *a, **k):
+        self.path, self.frames, self.closed = path, [], False
+        FileIONetCDF.opened.append(self)
+
+    def register_field_collection(self, fc, field_names=None):
+        self.fc, self.names = fc, list(field_names if field_names is not None else fc.fields)
+
+    def append_frame(self):
+        return self
+
+    def write(self):
+        self.frames.append({n: self.fc.get_real_field(n).p.copy() for n in self.names})
+
+    def close(self):
+        self.closed = True
+
+
+class DataFrame:
+    """polars.DataFrame(dict).write_csv(path) as io.py:95-97 uses it: header = keys, one row per entry"""
+
+    def __init__(self, data):
+        self.data = {k: list(v) for k, v in data.items()}
+
+    def write_csv(self, fname):
+        import csv
+        with open(fname, 'w', newline='') as f:
+            w = csv.writer(f)
+            w.writerow(list(self.data))
+            w.writerows(zip(*[[float(x) if np.ndim(x) == 0 else np.asarray(x).tolist() for x in col] for col in self.data.values()]))
+
+
 def _install_stand_ins():
     from . import tinygp_stand_in as T
     jit = lambda f=None, **k: f if f is not None else (lambda g: g)          # noqa: E731
@@ -112,7 +147,8 @@ def _install_stand_ins():
                   kernels=types.SimpleNamespace(stationary=types.SimpleNamespace(Matern32=T.Matern32),
                                                 distance=types.SimpleNamespace(L2Distance=T.L2Distance)),
                   transforms=types.SimpleNamespace(Linear=T.Linear))
-    mg = _inert_module('muGrid', GlobalFieldCollection=_FieldCollection)
+    mg = _inert_module('muGrid', GlobalFieldCollection=_FieldCollection, FileIONetCDF=FileIONetCDF,
+                       OpenMode=types.SimpleNamespace(Overwrite='w', Read='r', Append='a'))
     mg.Field = _inert_module('muGrid.Field', wrap_field=lambda f: f)
 
     class YAML:                                  # ruamel.yaml.YAML(): configured at import time, used only for dtool readmes
@@ -123,7 +159,7 @@ def _install_stand_ins():
     for name in ('ContactMechanics', 'polars', 'dtoolcore', 'dtool_lookup_api', 'netCDF4', 'matplotlib', 'matplotlib.pyplot',
                  'matplotlib.animation', 'IPython', 'IPython.display', 'ruamel', 'ruamel.yaml'):
         if name not in sys.modules:
-            _inert_module(name, **({'YAML': YAML} if name == 'ruamel.yaml' else {}))
+            _inert_module(name, **({'YAML': YAML} if name == 'ruamel.yaml' else {'DataFrame': DataFrame} if name == 'polars' else {}))
 
 
 _ref = None

@@ -1,0 +1,180 @@
+"""CPU: the HOST logic of the product's ``gapflow_b200.problem.Problem`` -- host edits of ``q`` / ``dt`` /
+``kinetic_energy_old``, the stale closure fields, the run loop and its device batches, when frames and history rows are
+written and what they hold -- with the device solver replaced by an oracle-backed double (tests/host_double.py), held to
+the reference's own ``Problem`` EXECUTED next to it (oracle/ref_problem.py).  The CUDA solver behind the same class is
+what tests/test_problem_gpu.py runs; nothing in the product imports the double."""
+import contextlib
+import csv
+import io
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ref_loader
+from tests import cases
+from tests.host_double import OracleFVSolver
+from tests.test_problem_gpu import DECAY, JOURNAL2D, SOMMERFELD
+
+pytestmark = pytest.mark.skipif(not ref_loader.available(), reason="reference tree not present")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    from oracle import ref_problem
+    yield ref_problem.reference_package()
+    ref_problem.release()
+
+
+@pytest.fixture
+def Host(monkeypatch):
+    import gapflow_b200.problem as P
+    monkeypatch.setattr(P, 'FVSolver', OracleFVSolver)
+    return P.Problem
+
+
+def _ref(ref, text, silent=True, **opts):
+    with io.StringIO(text) as f, contextlib.redirect_stdout(io.StringIO()):
+        rd = ref.read_yaml_input(f)
+        rd['options']['silent'] = silent
+        rd['options'].update(opts)
+        return ref.Problem._from_dict(rd)
+
+
+def _same(a, r, tag):
+    assert np.array_equal(a.q, r.q), tag
+    assert a.dt == r.dt and a.step == r.step and a.simtime == r.simtime and a.residual == r.residual, tag
+    assert list(a.residual_buffer) == list(r.residual_buffer) and bool(a.converged) == bool(r.converged), tag
+    assert a.mass == r.mass and a.kinetic_energy == r.kinetic_energy and a.v_max == r.v_max, tag
+    assert a.dt_crit == r.dt_crit and a.cfl == r.cfl and a.pressure.v_sound == r.pressure.v_sound, tag
+    assert a.kinetic_energy_old == r.kinetic_energy_old, tag
+    # the closure fields as the reference holds them between steps: one pass stale (problem.py:532-540 vs :563)
+    assert np.array_equal(a.pressure.pressure, r.pressure.pressure), tag
+    assert np.array_equal(a.wall_stress_xz.full, r.wall_stress_xz.full), tag
+    assert np.array_equal(a.wall_stress_xz.lower, r.wall_stress_xz.lower), tag
+    assert np.array_equal(a.wall_stress_yz.upper, r.wall_stress_yz.upper), tag
+    assert np.array_equal(a.bulk_stress.stress, r.bulk_stress.stress), tag
+    assert np.array_equal(a.topo.h, r.topo.h) and np.array_equal(a.topo.x, r.topo.x), tag
+
+
+@pytest.mark.parametrize('name', ['journal2d_periodic', 'slider2d_xDN', 'asym_xy_mc0', 'journal2d_flip_mc0', 'slider2d_barus_eyring'])
+def test_update_with_host_edits_like_the_reference(ref, Host, name):
+    text = cases.STEP_CASES[name]['yaml']
+    a, r = Host.from_string(text), _ref(ref, text)
+    bump = 1 + 1e-6 * np.random.default_rng(3).standard_normal(a.q[0].shape)
+    for p in (a, r):
+        p.q[0] *= bump                              # edit before the first step (tests/test_wave_decay.py:101)
+        with contextlib.redirect_stdout(io.StringIO()):
+            p._pre_run()
+    _same(a, r, 'pre_run')
+    for k in range(3):
+        a.update()
+        r.update()
+        _same(a, r, k)
+    for p in (a, r):
+        p.q[1] += 1e-4                              # edit mid-run, no _pre_run
+        p.kinetic_energy_old = p.kinetic_energy     # tests/test_wave_decay.py:102
+        p.dt = 0.5 * p.dt
+    assert a.dt == r.dt
+    for k in range(2):
+        a.update()
+        r.update()
+        _same(a, r, ('edited', k))
+    assert a.q_is_valid and not a.q_has_nan and not a.q_has_negative_density
+    for p in (a, r):                                # garbage in the ghost cells, then the reference's refill
+        p.q[:, 0, :] = 7.
+        p.q[:, :, -1] = -3.
+        p._communicate_ghost_buffers()
+    assert np.array_equal(a.q, r.q)
+    a.update()
+    r.update()
+    _same(a, r, 'refilled')
+
+
+def test_invalid_step_restores_the_field_and_stops(ref, Host):
+    text = cases.STEP_CASES['slider2d_xDN']['yaml']
+    a, r = Host.from_string(text), _ref(ref, text)
+    for p in (a, r):
+        with contextlib.redirect_stdout(io.StringIO()):
+            p._pre_run()
+            p.update()
+            p.dt = 1e-3
+            for _ in range(3):
+                p.update()
+    assert a._stop and r._stop and a.step == r.step
+    assert np.array_equal(a.q, r.q) and np.array_equal(a.pressure.pressure, r.pressure.pressure)
+
+
+@pytest.mark.parametrize('tol, max_it, wf', [(1e-4, 10_000, 1000), (1e-12, 130, 50), (1e-4, 10_000, 37)])
+def test_run_loop_and_outputs(ref, Host, tmp_path, tol, max_it, wf):
+    """run(): stops where the reference stops (convergence or max_it), whatever the batch length; frames of sol.nc and
+    rows of history.csv at the reference's steps with the reference's contents; config.yml; topo.nc"""
+    from scipy.io import netcdf_file
+    from oracle.ref_problem import FileIONetCDF
+    text = SOMMERFELD.replace("tol: 1e-8", f"tol: {tol}").replace("max_it: 10_000", f"max_it: {max_it}") \
+        .replace("write_freq: 1000", f"write_freq: {wf}").replace("silent: True", "silent: False")
+    outs = []
+    for k, make in enumerate((lambda t: Host.from_string(t), lambda t: _ref(ref, t, silent=False, output=str(tmp_path / 'r' / 'run')))):
+        t = text.replace("output: data/journal", f"output: {tmp_path / 'a' / 'run'}\n    use_tstamp: False")
+        FileIONetCDF.opened.clear()
+        with contextlib.redirect_stdout(io.StringIO()):
+            p = make(t)
+            p.run()
+        outs.append(p)
+    a, r = outs
+    assert a.step == r.step and (a.step < max_it) == (tol > 1e-6)
+    assert np.array_equal(a.q, r.q) and a.dt == r.dt and a.simtime == r.simtime
+    for key in r.history:
+        assert np.array_equal(np.array(a.history[key], dtype=float), np.array(r.history[key], dtype=float)), key
+    topo_r, sol_r = FileIONetCDF.opened
+    assert sol_r.closed
+    with netcdf_file(os.path.join(a.outdir, 'sol.nc'), 'r', mmap=False) as f:
+        sol = {k: np.array(v[:]) for k, v in f.variables.items()}
+    assert sol['solution'].shape[0] == len(sol_r.frames) == len(r.history['step'])
+    for i, fr in enumerate(sol_r.frames):
+        assert np.array_equal(sol['solution'][i, :, 0], fr['solution']), i
+        assert np.array_equal(sol['pressure'][i], fr['pressure']), i
+        assert np.array_equal(sol['wall_stress_xz'][i, :, 0], fr['wall_stress_xz']), i
+        assert np.array_equal(sol['wall_stress_yz'][i, :, 0], fr['wall_stress_yz']), i
+    with netcdf_file(os.path.join(a.outdir, 'topo.nc'), 'r', mmap=False) as f:
+        assert np.array_equal(np.array(f.variables['topography'][:])[0, :, 0], topo_r.frames[0]['topography'])
+    rows = {}
+    for who, d in (('a', a.outdir), ('r', r.outdir)):
+        with open(os.path.join(d, 'history.csv')) as f:
+            rows[who] = list(csv.reader(f))
+    assert rows['a'][0] == rows['r'][0] == ['step', 'time', 'ekin', 'residual', 'vsound']
+    assert np.array_equal(np.array(rows['a'][1:], dtype=float), np.array(rows['r'][1:], dtype=float))
+    import yaml
+    ca, cr = (yaml.safe_load(open(os.path.join(d, 'config.yml'))) for d in (a.outdir, r.outdir))
+    assert set(cr) - {'version'} == set(ca) - {'version'}
+    for key in ('grid', 'numerics', 'geo', 'prop'):
+        assert ca[key] == cr[key], key
+
+
+def test_wave_decay_script_runs_unchanged(ref, Host):
+    """the body of tests/test_wave_decay.py:85-108 (writes into q, assigns kinetic_energy_old, reads simtime) on both"""
+    out = []
+    for make in (Host.from_string, lambda t: _ref(ref, t)):
+        with contextlib.redirect_stdout(io.StringIO()):
+            p = make(DECAY)
+            p._pre_run()
+        kn = 2. * 2. * np.pi / p.grid['Lx']
+        x = p.topo.x[1:-1, 1]
+        p.q[2, 1:-1, :] = np.sin(kn * x)[:, None]
+        p.kinetic_energy_old = p.kinetic_energy
+        for _ in range(20):
+            p.update()
+        out.append((p.q.copy(), p.simtime, p.residual))
+    assert np.array_equal(out[0][0], out[1][0]) and out[0][1:] == out[1][1:]
+
+
+def test_mass_conservation_script(ref, Host):
+    a, r = Host.from_string(JOURNAL2D.format(n=20)), _ref(ref, JOURNAL2D.format(n=20))
+    for p in (a, r):
+        with contextlib.redirect_stdout(io.StringIO()):
+            p._pre_run()
+    m0 = a.mass.copy()                                     # tests/test_mass_conservation.py:71 calls .copy() on it
+    for _ in range(10):
+        a.update()
+        r.update()
+    assert a.mass == r.mass and np.isclose(a.mass, m0)
