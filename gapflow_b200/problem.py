@@ -438,7 +438,7 @@ class Problem:
         for key, name in (('xz', 'wall_stress_xz_var'), ('yz', 'wall_stress_yz_var'), ('zz', 'pressure_var')):
             m = self.gp_models.get(key)
             if m is not None:
-                v = m.variance
+                v = m.variance if (self.step or self._stop) else None      # the FIELD is filled in update() only, like the closures
                 out[name] = np.zeros((self.grid['Nx'] + 2, self.grid['Ny'] + 2)) if v is None else self._gather_field(v)
         return out
 

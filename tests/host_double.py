@@ -91,3 +91,174 @@ class OracleFVSolver:
             if o._stop or (until_converged and (o.converged or o.step >= o.max_it)):
                 break
             o.update()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# GP-coupled step: doubles for the device pieces gapflow_b200/surrogate.py drives (the pass kernels with GP closures, the
+# feature kernel, the GP model).  SurrogateDriver / SurrogateModel / Database -- the host logic -- run unchanged.
+# ---------------------------------------------------------------------------------------------------------------------
+import ctypes as C  # noqa: E402
+
+import torch  # noqa: E402
+
+from oracle import closures as OC  # noqa: E402
+from oracle import gp as OG  # noqa: E402
+from oracle.fv import predictor_corrector, source  # noqa: E402
+
+
+class _SurrogateOracle(FVOracle):
+    """FVOracle whose sound speed is the one handed in with the step's fold (stress.py:522-537 evaluated by the driver)"""
+    c2 = None
+
+    @property
+    def v_sound(self):
+        if self.c2 is not None:
+            return np.sqrt(self.c2)
+        return OC.eos_sound_velocity(self.q[0], self.prop).max()
+
+
+class OracleSurrogateSolver(OracleFVSolver):
+    """OracleFVSolver + what SurrogateDriver asks of the device: gpf_fv_set_surrogate, gpf_fv_pass, gpf_gp_features_of,
+    gpf_fv_reduce_local / gpf_fv_finish_surrogate (reached through FakeLib below)."""
+
+    def __init__(self, grid, geo, prop, numerics, topo=None, extra=None, arith='exact', **kw):
+        super().__init__(grid, geo, prop, numerics, topo=topo, extra=extra, arith=arith)
+        self.o.__class__ = _SurrogateOracle
+        self.h, self.device = self, torch.device('cpu')
+        self.bound = {}
+        self.stage = {}
+
+    def _stream(self):
+        return None
+
+    def field(self, rel):
+        """the q of rotating buffer `rel`: 0 the step's input, 1 the predictor's output, 2 the new field"""
+        return self.stage.get(rel, self.o.q) if rel else (self.stage.get(0, self.o.q) if self._in_step else self.o.q)
+
+    _in_step = False
+
+    def run_pass(self, i):
+        o = self.o
+        if i == 0:
+            self._in_step = True
+            self.stage = {0: o.q.copy()}
+            self._dt = o.dt
+        FVOracle.closures(o)                                   # fixed-form everything, then the GP means on top
+        n = self.shape[0] * self.shape[1]
+        for key, (ptr, scale) in self.bound.items():
+            if ptr is None:
+                continue
+            nout = 1 if key == 'zz' else 2
+            m = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(nout * n,)).reshape(nout, *self.shape) * scale
+            if key == 'zz':
+                o.pressure[...] = m[0]
+            else:
+                f, oi = (o.wall_xz, 4) if key == 'xz' else (o.wall_yz, 3)
+                f[oi], f[oi + 6] = m[0], m[1]
+        d = o.directions()[i]
+        fX, fY = predictor_corrector(o.q, o.pressure, o.bulk, d)
+        src = source(o.q, o.topo, o.bulk, o.wall_xz[:6] + o.wall_yz[:6], o.wall_xz[6:] + o.wall_yz[6:])
+        o.q[...] = o.q - self._dt * (fX / o.grid['dx'] + fY / o.grid['dy'] - src)
+        o.fill_ghosts()
+        if i == 0:
+            self.stage[1] = o.q
+        else:
+            o.q[...] = (o.q + self.stage[0]) / 2.0
+            self._valid = o.q_is_valid
+            if self._valid:
+                o.fill_ghosts()
+            self.stage[2] = o.q
+
+    def finish(self, mode, c2):
+        from gapflow_b200 import _capi
+        o = self.o
+        o.c2 = c2 if c2 > 0 or c2 != c2 else None
+        if mode == _capi.FIN_STEP:
+            self._in_step = False
+            if self._valid:
+                ekin = o.kinetic_energy
+                o.residual = abs(ekin - o.kinetic_energy_old) / o.kinetic_energy_old / o.cfl
+                o.residual_buffer.append(o.residual)
+                o.kinetic_energy_old = ekin
+                o.step += 1
+                o.simtime += o.dt
+                if self.numerics['adaptive']:
+                    o.dt = self.numerics['CFL'] * o.dt_crit
+            else:
+                o.q[...] = self.stage[0]
+                o._stop = True
+        elif mode in (_capi.FIN_PRERUN, _capi.FIN_PRERUN_KEEP_EKIN):
+            self.pre_run(reset_ekin_old=mode == _capi.FIN_PRERUN)
+
+
+class FakeLib:
+    """the entry points of libgapflow_b200.so that gapflow_b200/surrogate.py calls, on the doubles above"""
+
+    def gpf_fv_set_surrogate(self, h, p, ps, xz, xs, yz, ys):
+        h.bound = {'zz': (p, ps), 'xz': (xz, xs), 'yz': (yz, ys)}
+        return 0
+
+    def gpf_fv_pass(self, h, i, stream):
+        h.run_pass(i)
+        return 0
+
+    def gpf_fv_reduce_local(self, h, kind, rec, stream):
+        return 0
+
+    def gpf_fv_finish_surrogate(self, h, mode, rec, world, c2, stream):
+        h.finish(mode, c2)
+        return 0
+
+
+class CapiShim:
+    """gapflow_b200._capi as surrogate.py sees it, with load() -> FakeLib"""
+
+    def __init__(self):
+        from gapflow_b200 import _capi
+        self._real, self._lib = _capi, FakeLib()
+
+    def load(self):
+        return self._lib
+
+    def check(self, rc):
+        assert rc == 0
+
+    def __getattr__(self, k):
+        return getattr(self._real, k)
+
+
+def features(solver, rel, X_scale, active_dims):
+    """gpf_gp_features_of: (Np, D) normalised, column-selected features of rotating buffer `rel` (gp.py:223-232)"""
+    o = solver.o
+    F = np.vstack([solver.field(rel), o.topo[:3], o.extra]).reshape(7, -1).T
+    return torch.from_numpy(np.ascontiguousarray((F / np.asarray(X_scale, dtype=float).reshape(7))[:, [int(d) for d in active_dims]]))
+
+
+class OracleGPModel:
+    """gapflow_b200.gp.GPModel on oracle/gp.py"""
+
+    def __init__(self, M_max, D, n_out, device=None):
+        self.M_max, self.D, self.n_out, self.M = M_max, D, n_out, 0
+
+    def factor(self, X, Y, log_amp, log_scale, yerr):
+        self.X, self.log_amp, self.log_scale = np.array(X, dtype=float), float(log_amp), np.array(log_scale, dtype=float)
+        self.M = len(self.X)
+        self.L = OG.build(self.X, yerr, self.log_amp, self.log_scale)
+        self.alpha = OG.alpha(self.L, Y)
+
+    def train(self, X, Y, yerr, log_amp0, log_scale0):
+        la, ls, _ = OG.train(X, Y, yerr, log_amp0, log_scale0)
+        self.factor(X, Y, la, ls, yerr)
+
+    def repredict_mean(self, X, with_gradient_max=False):
+        X = X.numpy()
+        mean = torch.from_numpy(np.ascontiguousarray(OG.repredict_mean(self.X, self.log_amp, self.log_scale, self.alpha, X)))
+        if with_gradient_max:
+            g = OG.dmean_dx0(self.X, self.log_amp, self.log_scale, self.alpha, X)
+            return mean, (float('nan') if np.isnan(g).any() else float(g.max()))
+        return mean
+
+    def repredict_mean_var(self, X, noise=0.0):
+        mean, var = OG.repredict_mean_var(self.X, self.log_amp, self.log_scale, self.L, self.alpha, noise, X.numpy())
+        self.argmax, self._vmax_norm = int(np.argmax(var)), float(np.max(var))
+        return torch.from_numpy(np.ascontiguousarray(mean)), torch.from_numpy(np.ascontiguousarray(var))

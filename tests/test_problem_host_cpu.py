@@ -178,3 +178,113 @@ def test_mass_conservation_script(ref, Host):
         a.update()
         r.update()
     assert a.mass == r.mass and np.isclose(a.mass, m0)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# GP-coupled step: SurrogateDriver / SurrogateModel / Database of gapflow_b200/surrogate.py (host logic) on doubles of the
+# device pieces, against the executed reference with the stated tinygp stand-in
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.fixture
+def HostGP(monkeypatch):
+    import gapflow_b200.problem as P
+    import gapflow_b200.surrogate as S
+    from tests import host_double as HD
+    monkeypatch.setattr(P, 'FVSolver', HD.OracleSurrogateSolver)
+    monkeypatch.setattr(S, 'GPModel', HD.OracleGPModel)
+    monkeypatch.setattr(S, '_features', HD.features)
+    monkeypatch.setattr(S, '_capi', HD.CapiShim())
+    return P.Problem
+
+
+FIELD = {'zz': 'pressure', 'xz': 'wall_stress_xz', 'yz': 'wall_stress_yz'}
+
+
+def _gp_pair(ref, HostGP, text, nx, ny):
+    from gapflow_b200 import config
+    from gapflow_b200.surrogate import Database
+    from oracle import surrogate as OS
+    from oracle import tinygp_stand_in as T
+    from tests import surrogate_cases as SC
+    extra = SC.slip_length(nx, ny)
+    d = config.read_yaml_string(text)
+    with io.StringIO(text) as f, contextlib.redirect_stdout(io.StringIO()):
+        rd = ref.read_yaml_input(f)
+    rd['options']['silent'] = True
+    rd['db']['dtool_path'] = None
+    T.HOOKS['draws'] = SC.DRAWS
+    T.HOOKS['optimizer'] = lambda p0, X=None, **k: dict(zip(('log_amp', 'log_scale'),
+                                                            SC.fixed_optimizer(type('M', (), {'Xtrain': X}))))
+    database = Database(OS.MockMD(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS), d['db'])
+    a = HostGP(d['options'], d['grid'], d['numerics'], d['properties'], d['geometry'], d['gp'], database, extra_field=extra)
+    for m in a.gp_models.values():
+        m.optimizer = SC.fixed_optimizer
+    with contextlib.redirect_stdout(io.StringIO()):
+        rdb = ref.Database(ref.Mock(rd['properties'], rd['geometry'], rd['gp']), rd['db'])
+        r = ref.Problem(rd['options'], rd['grid'], rd['numerics'], rd['properties'], rd['geometry'], gp=rd['gp'],
+                        database=rdb, extra_field=extra)
+        for p in (a, r):
+            p.q[...] = SC.perturb(p.q)
+            p._communicate_ghost_buffers()
+            p._pre_run()
+    return a, database, r, rdb
+
+
+def _rel(x, y):
+    return np.abs(np.asarray(x) - np.asarray(y)).max() / max(np.abs(np.asarray(y)).max(), 1e-300)
+
+
+def _same_gp(a, adb, r, rdb, tag, tol):
+    assert adb.size == rdb.size, tag
+    assert _rel(adb._Xtrain, rdb._Xtrain) <= tol and _rel(adb._Ytrain, rdb._Ytrain) <= max(tol, 1e-11), tag
+    assert _rel(a.q, r.q) <= tol and abs(a.dt - r.dt) <= tol * r.dt and a.step == r.step, tag
+    assert abs(a.residual - r.residual) <= 1e-9 * max(abs(r.residual), 1e-300), tag
+    assert abs(a.pressure.v_sound - float(r.pressure.v_sound)) <= 1e-9 * float(r.pressure.v_sound), tag
+    assert _rel(a.pressure.pressure, r.pressure.pressure) <= tol, tag
+    assert _rel(a.wall_stress_xz.full, r.wall_stress_xz.full) <= tol and _rel(a.wall_stress_yz.full, r.wall_stress_yz.full) <= tol, tag
+    assert set(a.gp_models) == {k for k, f in FIELD.items() if getattr(r, f).is_gp_model}, tag
+    for k, m in a.gp_models.items():
+        rm = getattr(r, FIELD[k])
+        unit = m.kernel_variance * m.Yscale**2
+        assert m.last_fit_train_size == rm.last_fit_train_size and m._pause == rm._pause and m._step == rm._step, (tag, k)
+        assert np.abs(m.variance.numpy() - np.asarray(rm._predictive_var)).max() <= 1e-9 * unit, (tag, k)
+        name = FIELD[k] + '_var'
+        assert np.abs(a._variance_fields()[name] - rm.variance).max() <= 1e-9 * unit, (tag, k)      # what sol.nc gets
+        assert abs(m.maximum_variance - rm.maximum_variance) <= 1e-9 * unit and m.trusted == bool(rm.trusted), (tag, k)
+        assert abs(m.variance_tol - rm.variance_tol) <= max(tol, 1e-11) * rm.variance_tol, (tag, k)
+        for key, hist in m.history.items():
+            assert len(hist) == len(rm.history[key]) and (not hist or _rel(np.array(hist, dtype=float), rm.history[key]) <= 1e-9), (tag, k, key)
+
+
+@pytest.mark.parametrize('name, kw, steps', [
+    ('slip1d', dict(nx=100, atol=0.6, al_steps=3), 8),
+    ('slip2d', dict(nx=24, ny=20, atol=0.8, al_steps=2), 4),
+    ('slip1d', dict(nx=60, atol=0.05, al_steps=2), 6),
+])
+def test_gp_coupled_host_logic_like_the_reference(ref, HostGP, name, kw, steps):
+    from tests import surrogate_cases as SC
+    d, text = SC.inputs(name, **kw)
+    a, adb, r, rdb = _gp_pair(ref, HostGP, text, d['grid']['Nx'], d['grid']['Ny'])
+    _same_gp(a, adb, r, rdb, 'pre_run', 1e-12)
+    grew = False
+    for k in range(steps):
+        n = adb.size
+        with contextlib.redirect_stdout(io.StringIO()):
+            a.update()
+            r.update()
+        _same_gp(a, adb, r, rdb, k, 1e-12)
+        grew = grew or adb.size > n
+    assert grew
+
+
+@pytest.mark.parametrize('block', range(4))
+def test_gp_coupled_host_logic_random_configurations(ref, HostGP, block):
+    from tests.test_surrogate_oracle_vs_reference import _random_text
+    for seed in range(block * 5, block * 5 + 5):
+        text, nx, ny = _random_text(seed)
+        a, adb, r, rdb = _gp_pair(ref, HostGP, text, nx, ny)
+        _same_gp(a, adb, r, rdb, (seed, 'pre_run'), 1e-9)
+        for k in range(5):
+            with contextlib.redirect_stdout(io.StringIO()):
+                a.update()
+                r.update()
+            _same_gp(a, adb, r, rdb, (seed, k), 1e-9)

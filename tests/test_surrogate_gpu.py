@@ -413,7 +413,8 @@ def test_problem_with_gp_on_slabs_writes_the_same_files(tmp_path, world):
     a, b = _read_nc(os.path.join(one.outdir, 'sol.nc')), _read_nc(os.path.join(ranks[0][0], 'sol.nc'))
     assert {'pressure_var', 'wall_stress_xz_var'} <= set(a) and sorted(a) == sorted(b)
     assert a['pressure_var'].shape == a['pressure'].shape and np.isfinite(a['pressure_var']).all()
-    assert a['pressure_var'].max() > 0.0                       # a variance was computed before the first frame (gp.py:468)
+    assert a['pressure_var'].max() > 0.0                       # frames after the first step hold a computed variance (gp.py:468);
+    #                                                            frame 0 the zeros the reference's field starts with
     for k in a:
         assert np.array_equal(a[k], b[k]), k
     for _, step, size, X, q in ranks:
