@@ -288,3 +288,62 @@ def test_gp_coupled_host_logic_random_configurations(ref, HostGP, block):
                 a.update()
                 r.update()
             _same_gp(a, adb, r, rdb, (seed, k), 1e-9)
+
+
+def test_gp_run_outputs_like_the_reference(ref, HostGP, tmp_path):
+    """run() with GP closures and outputs: frames of sol.nc (variance fields included, zeros in frame 0), history.csv,
+    gp_zz.csv / gp_xz.csv (hyper-parameter history rows at the reference's steps), Xtrain.npy / Ytrain.npy"""
+    from scipy.io import netcdf_file
+    from gapflow_b200 import config
+    from gapflow_b200.surrogate import Database
+    from oracle import surrogate as OS
+    from oracle import tinygp_stand_in as T
+    from oracle.ref_problem import FileIONetCDF
+    from tests import surrogate_cases as SC
+    T.HOOKS['draws'] = SC.DRAWS
+    T.HOOKS['optimizer'] = lambda p0, X=None, **k: dict(zip(('log_amp', 'log_scale'),
+                                                            SC.fixed_optimizer(type('M', (), {'Xtrain': X}))))
+    extra = SC.slip_length(64, 1)
+    outs = {}
+    for who in ('a', 'r'):
+        _, text = SC.inputs('slip1d', nx=64, max_it=12, wf=5, out=str(tmp_path / who / 'run'), silent=False, atol=0.8, al_steps=2)
+        FileIONetCDF.opened.clear()
+        with contextlib.redirect_stdout(io.StringIO()):
+            if who == 'a':
+                d = config.read_yaml_string(text)
+                db = Database(OS.MockMD(d['properties'], d['geometry'], d['gp'], draws=SC.DRAWS), d['db'])
+                p = HostGP(d['options'], d['grid'], d['numerics'], d['properties'], d['geometry'], d['gp'], db, extra_field=extra)
+                for m in p.gp_models.values():
+                    m.optimizer = SC.fixed_optimizer
+            else:
+                with io.StringIO(text) as f:
+                    rd = ref.read_yaml_input(f)
+                rd['db']['dtool_path'] = None
+                db = ref.Database(ref.Mock(rd['properties'], rd['geometry'], rd['gp']), rd['db'])
+                p = ref.Problem(rd['options'], rd['grid'], rd['numerics'], rd['properties'], rd['geometry'], gp=rd['gp'],
+                                database=db, extra_field=extra)
+            p.run()
+        outs[who] = (p, db)
+    (a, adb), (r, rdb) = outs['a'], outs['r']
+    assert a.step == r.step == 12 and adb.size == rdb.size > 10
+    sol_r = FileIONetCDF.opened[-1]
+    with netcdf_file(os.path.join(a.outdir, 'sol.nc'), 'r', mmap=False) as f:
+        sol = {k: np.array(v[:]) for k, v in f.variables.items()}
+    assert sol['solution'].shape[0] == len(sol_r.frames) == 4               # steps 0, 5, 10, 12
+    for i, fr in enumerate(sol_r.frames):
+        assert _rel(sol['solution'][i, :, 0], fr['solution']) <= 1e-12, i
+        for name in ('pressure', 'pressure_var', 'wall_stress_xz_var'):
+            assert np.abs(sol[name][i] - fr[name]).max() <= 1e-9 * max(np.abs(fr[name]).max(), 1e-300), (i, name)
+        assert _rel(sol['wall_stress_xz'][i, :, 0], fr['wall_stress_xz']) <= 1e-12, i
+    assert not sol['pressure_var'][0].any() and sol['pressure_var'][1].any()
+    for name in ('history.csv', 'gp_zz.csv', 'gp_xz.csv'):
+        rows = []
+        for p in (a, r):
+            with open(os.path.join(p.outdir, name)) as f:
+                rows.append(list(csv.reader(f)))
+        assert rows[0][0] == rows[1][0], name                                # the same columns in the same order
+        assert len(rows[0]) == len(rows[1]) > 1, name
+        A, R = np.array(rows[0][1:], dtype=float), np.array(rows[1][1:], dtype=float)
+        assert np.allclose(A, R, rtol=1e-9, atol=0), name
+    for name in ('Xtrain.npy', 'Ytrain.npy', 'Ytrain_err.npy'):
+        assert _rel(np.load(os.path.join(a.outdir, name)), np.load(os.path.join(r.outdir, name))) <= 1e-11, name
